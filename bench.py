@@ -1,0 +1,374 @@
+#!/usr/bin/env python
+"""bench.py -- throughput of the sketch-rnn hot path on B200 (driver contract).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--workload NAME] [--precision f32|bf16]
+  python bench.py --impl reference ...      # the CPU restatement of the reference graph, timed
+
+Workloads (BASELINE.json configs):
+  train_h512_l3_b800  configs[3]: 3-layer LSTM rnn_size 512, 24 mixtures, global batch 800,
+                      seq 300, data-parallel over N GPUs (default; metric train stroke-steps/s)
+  train_kanji         configs[0]: the reference default, 2-layer LSTM 256, batch 100, seq 300
+  train_gru / train_rnn   configs[2]
+  sample_8192         configs[4]: 8192 concurrent sketches x 300 steps, sharded over N GPUs
+
+One "step" = one full training step (forward, MDN loss, BPTT, global-norm clip, Adam; plus the
+gradient all-reduce when N > 1) over one synthetic batch, or one whole sampling call.  Rank 0
+prints ONE JSON line.  Inputs are synthetic (the dataset and checkpoint blobs are absent from the
+reference mount) with the shapes and statistics of SURVEY.md 8(d).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+WORKLOADS = {
+    "train_h512_l3_b800": dict(kind="train", model="lstm", H=512, L=3, M=24, B=800, T=300),
+    "train_kanji": dict(kind="train", model="lstm", H=256, L=2, M=24, B=100, T=300),
+    "train_gru": dict(kind="train", model="gru", H=256, L=2, M=24, B=100, T=300),
+    "train_rnn": dict(kind="train", model="rnn", H=256, L=2, M=24, B=100, T=300),
+    "sample_8192": dict(kind="sample", model="lstm", H=256, L=2, M=24, B=8192, T=300),
+}
+
+
+def fwd_flops_per_stroke_step(w):
+    """sum_l 2*(I_l+H)*G + 2*H*NOUT."""
+    ng = {"lstm": 4, "gru": 3, "rnn": 1}[w["model"]]
+    H, L, NOUT = w["H"], w["L"], 3 + 6 * w["M"]
+    f = 2 * H * NOUT
+    for l in range(L):
+        I = 5 if l == 0 else H
+        f += 2 * (I + H) * ng * H
+    return f
+
+
+def load_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return dict(hbm=d["hbm_gbs"], tc_burst=d["bf16_tflops"], tc_sustained=d["bf16_tflops_sustained"],
+                    src="measured")
+    return dict(hbm=6650.0, tc_burst=1590.0, tc_sustained=1400.0, src="fallback")
+
+
+class ClockSampler(threading.Thread):
+    """nvidia-smi clocks / throttle reasons sampled during the timed region."""
+
+    def __init__(self, index):
+        threading.Thread.__init__(self, daemon=True)
+        self.index = index
+        self.samples = []
+        self.stop_flag = False
+
+    def run(self):
+        q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,"
+             "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+             "clocks_event_reasons.sw_power_cap")
+        while not self.stop_flag:
+            try:
+                out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + q,
+                                      "--format=csv,noheader,nounits"], capture_output=True, text=True,
+                                     timeout=5).stdout.strip()
+                if out:
+                    self.samples.append([s.strip() for s in out.split(",")])
+            except Exception:
+                pass
+            time.sleep(0.2)
+
+    def summary(self):
+        self.stop_flag = True
+        sm, mx, reasons = [], 0, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for s in self.samples:
+            try:
+                sm.append(float(s[0]))
+                mx = max(mx, float(s[1]))
+                for n, v in zip(names, s[2:6]):
+                    if v.lower().startswith("active"):
+                        reasons.add(n)
+            except Exception:
+                pass
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": mx or None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# --------------------------------------------------------------------------------------------
+# CPU arm: the oracle (NumPy restatement of the reference graph) on the host cores
+# --------------------------------------------------------------------------------------------
+def cpu_baseline(w, max_rows=None):
+    """Times the oracle on a bounded sample of the workload. Returns (value, unit, cores, sample)."""
+    from oracle import sketch_oracle as so
+    cores = os.cpu_count() or 1
+    cfg = so.Config(model=w["model"], rnn_size=w["H"], num_layers=w["L"], num_mixture=w["M"],
+                    batch_size=w["B"], seq_length=w["T"], keep_prob=0.8)
+    params = so.init_params(cfg, seed=0)
+    if w["kind"] == "train":
+        # ~10-30 s of CPU work: scale the batch rows down, keep T and the model
+        Bs = max_rows or max(4, min(w["B"], int(2.0e11 / (3.0 * fwd_flops_per_stroke_step(w) * w["T"]))))
+        x, y = so.synthetic_batch(Bs, w["T"], seed=1)
+        mask = so.synthetic_dropout_mask(cfg, Bs, w["T"])
+        opt = so.AdamState(cfg)
+        st = so.zero_state(cfg, Bs)
+        t0 = time.time()
+        so.train_step(cfg, params, opt, x, y, st, 0.005, mask)
+        dt = time.time() - t0
+        return Bs * w["T"] / dt, "stroke-steps/s", cores, \
+            "1 oracle train step on %d of %d batch rows x %d steps (NumPy fp32, BLAS threads=all)" % (Bs, w["B"], w["T"])
+    from oracle import sampler_ref
+    ns, steps = 2, w["T"]
+    u = np.random.RandomState(1).rand(ns, steps, 4).astype(np.float32)
+    t0 = time.time()
+    for i in range(ns):
+        sampler_ref.sample(cfg, params, u[i], steps, 0.1, 0.1, False)
+    dt = time.time() - t0
+    return ns / dt, "sketches/s", 1, "%d sketches x %d steps through oracle/sampler_ref.c (scalar C, 1 thread)" % (ns, steps)
+
+
+def run_reference(args, w):
+    """--impl reference: the reference's own path cannot run (Python 2 + TensorFlow 0.x); the
+    timed stand-in is the oracle port of its graph on the host cores, same config and metric."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    vals = []
+    info = None
+    for i in range(max(1, args.warmup > 0) + args.steps):
+        v, unit, cores, sample = cpu_baseline(w)
+        info = (unit, cores, sample)
+        if i >= (1 if args.warmup > 0 else 0):
+            vals.append(v)
+        if len(vals) >= args.steps:
+            break
+    value = float(np.median(vals))
+    unit, cores, sample = info
+    metric = "train_stroke_steps_per_sec" if w["kind"] == "train" else "sampled_sketches_per_sec"
+    line = {"impl": "reference", "metric": metric, "value": value, "unit": unit, "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": None, "higher_is_better": True,
+            "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": workload_config(args, w),
+            "cpu_baseline": {"value": value, "unit": unit, "cores": cores, "kind": "port", "sample": sample},
+            "e2e": {"value": value, "unit": unit, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line))
+
+
+def workload_config(args, w):
+    c = {"workload": args.workload, "cell": w["model"], "rnn_size": w["H"], "num_layers": w["L"],
+         "num_mixture": w["M"], "seq_length": w["T"], "precision": args.precision,
+         "cache": "per-step activations (%.0f MB) exceed the 126 MB L2; no explicit flush" % act_mb(w)}
+    if w["kind"] == "train":
+        c.update({"global_batch": w["B"], "keep_prob": 0.8, "grad_clip": 5.0,
+                  "parallelism": "dp%d (batch rows sharded, fp32 gradient all-reduce)" % args.gpus})
+    else:
+        c.update({"n_sketches": w["B"], "temperature": 0.1, "stop_if_eoc": False,
+                  "parallelism": "sketches sharded over %d GPU(s), no communication" % args.gpus})
+    return c
+
+
+def act_mb(w):
+    ng = {"lstm": 4, "gru": 3, "rnn": 1}[w["model"]]
+    return w["B"] * w["T"] * w["L"] * (ng + 3) * w["H"] * 4 / 1e6
+
+
+# --------------------------------------------------------------------------------------------
+# GPU arm
+# --------------------------------------------------------------------------------------------
+def run_ours(args, w):
+    import torch
+    import torch.distributed as dist
+    from oracle import sketch_oracle as so   # synthetic inputs + initialiser only (not timed)
+    from sketch_rnn_b200 import _lib
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda:%d" % local))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda:%d" % local)
+    assert args.gpus == world, "--gpus %d but WORLD_SIZE=%d (launch with torchrun)" % (args.gpus, world)
+    assert w["B"] % world == 0
+    Bl = w["B"] // world
+    T = w["T"]
+    cfg = so.Config(model=w["model"], rnn_size=w["H"], num_layers=w["L"], num_mixture=w["M"],
+                    batch_size=w["B"], seq_length=T, keep_prob=0.8)
+    params = so.init_params(cfg, seed=0)
+    h = _lib.Handle(model=w["model"], rnn_size=w["H"], num_layers=w["L"], num_mixture=w["M"],
+                    batch_size=Bl if w["kind"] == "train" else 0, seq_length=T if w["kind"] == "train" else 0,
+                    keep_prob=0.8, precision=args.precision, device=local)
+    h.set_params_dict(params)
+    S = h.S
+    peaks = load_peaks()
+    clocks = ClockSampler(local)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    lr = 0.005
+    if w["kind"] == "train":
+        xg, yg = so.synthetic_batch(w["B"], T, seed=1)
+        x_host = np.ascontiguousarray(xg[rank * Bl:(rank + 1) * Bl])
+        y_host = np.ascontiguousarray(yg[rank * Bl:(rank + 1) * Bl])
+        x = torch.from_numpy(x_host).to(dev)
+        y = torch.from_numpy(y_host).to(dev)
+        state = torch.zeros((w["L"], Bl, S), dtype=torch.float32, device=dev)
+        loss_rows = w["B"] * T
+
+        def step(i):
+            nonlocal state
+            losses, state = h.loss_grad(x, y, state, seed=1000 + i, row0=rank * Bl, loss_rows=loss_rows)
+            if world > 1:
+                dist.all_reduce(h.grads_tensor())
+                dist.all_reduce(losses)
+            h.apply_clip_adam(lr)
+            return losses
+
+        units_per_step = w["B"] * T
+        unit, metric = "stroke-steps/s", "train_stroke_steps_per_sec"
+    else:
+        def step(i):
+            return h.sample(Bl, T, 0.1, 0.1, False, seed=7 + i, sketch0=rank * Bl)[1]
+
+        units_per_step = w["B"]
+        unit, metric = "sketches/s", "sampled_sketches_per_sec"
+
+    for i in range(args.warmup):
+        step(i)
+    barrier()
+    l0 = h.launch_count()
+    clocks.start()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record()
+    last = None
+    for i in range(args.steps):
+        last = step(args.warmup + i)
+    ev1.record()
+    barrier()
+    ms = ev0.elapsed_time(ev1)
+    launches = h.launch_count() - l0
+    t = torch.tensor([ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t.item())
+    clk = clocks.summary()
+    ms_per_step = ms / args.steps
+    value = units_per_step / (ms_per_step * 1e-3)
+
+    # per-category kernel time, measured live with CUDA events around every launch (separate pass,
+    # so the event overhead is not inside the headline number)
+    h.profile_enable(True)
+    for i in range(min(args.steps, 3)):
+        step(args.warmup + args.steps + i)
+    prof = h.profile_read()
+    h.profile_enable(False)
+    nprof = min(args.steps, 3)
+    kern_ms = {k: v[0] / nprof for k, v in prof.items() if v[1] > 0}
+    kern_cnt = {k: v[1] // nprof for k, v in prof.items() if v[1] > 0}
+
+    # e2e through the host-buffer entry point: H2D of the step's inputs + D2H of its result inside
+    e2e = None
+    if w["kind"] == "train" and world == 1:
+        st_host = np.zeros((w["L"], Bl, S), dtype=np.float32)
+        for i in range(2):
+            h.train_step_host(x_host, y_host, st_host, lr, seed=i)
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        ne = max(3, min(args.steps, 10))
+        for i in range(ne):
+            h.train_step_host(x_host, y_host, st_host, lr, seed=10 + i)
+        torch.cuda.synchronize()
+        dt = (time.perf_counter() - t0) / ne
+        e2e = {"value": units_per_step / dt, "unit": unit,
+               "h2d_bytes_per_step": int(x_host.nbytes + y_host.nbytes + st_host.nbytes),
+               "d2h_bytes_per_step": int(12 + st_host.nbytes)}
+    elif w["kind"] == "train":
+        # multi-GPU: pinned host batch -> device, step, losses back, all inside the timed region
+        xp, yp = torch.from_numpy(x_host).pin_memory(), torch.from_numpy(y_host).pin_memory()
+        barrier()
+        t0 = time.perf_counter()
+        ne = max(3, min(args.steps, 10))
+        for i in range(ne):
+            x.copy_(xp, non_blocking=True)
+            y.copy_(yp, non_blocking=True)
+            losses = step(5000 + i)
+            losses.cpu()
+        barrier()
+        dt = torch.tensor([(time.perf_counter() - t0) / ne], dtype=torch.float64, device=dev)
+        dist.all_reduce(dt, op=dist.ReduceOp.MAX)
+        e2e = {"value": units_per_step / float(dt.item()), "unit": unit,
+               "h2d_bytes_per_step": int(2 * x_host.nbytes) * world, "d2h_bytes_per_step": 12 * world}
+    else:
+        barrier()
+        t0 = time.perf_counter()
+        ne = 3
+        for i in range(ne):
+            strokes, lengths, _ = h.sample(Bl, T, 0.1, 0.1, False, seed=100 + i, sketch0=rank * Bl)
+            sh = strokes.cpu()
+            lengths.cpu()
+        barrier()
+        dt = torch.tensor([(time.perf_counter() - t0) / ne], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(dt, op=dist.ReduceOp.MAX)
+        e2e = {"value": units_per_step / float(dt.item()), "unit": unit, "h2d_bytes_per_step": 0,
+               "d2h_bytes_per_step": int(sh.numel() * 4 + Bl * 4) * world}
+
+    if rank == 0:
+        fl = fwd_flops_per_stroke_step(w)
+        if w["kind"] == "train":
+            flops_step = 3.0 * fl * Bl * T   # per GPU
+        else:
+            flops_step = 1.0 * fl * Bl * T
+        # dominant kernel by measured time
+        dom = max(kern_ms, key=kern_ms.get) if kern_ms else None
+        tc = args.precision == "bf16"
+        peak = peaks["tc_sustained"] if tc else 2 * 128 * 148 * 1.965e-3  # fp32 CUDA-core TFLOP/s nominal
+        ach = flops_step / (ms_per_step * 1e-3) / 1e12
+        roof = {"bound": "tensor", "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": ach / peak,
+                "traffic": None, "kernel": "whole step (all kernels)",
+                "peak_source": ("MEASURED_PEAKS.json bf16 sustained (%s)" % peaks["src"]) if tc else
+                "fp32 CUDA-core nominal 148 SM x 128 lanes x 2 x 1.965 GHz (this path runs no tensor-core math)",
+                "per_kernel_ms": kern_ms, "per_kernel_launches": kern_cnt, "dominant": dom}
+        cb = None
+        if world == 1 and not args.no_cpu:
+            v, u, cores, sample = cpu_baseline(w)
+            cb = {"value": v, "unit": u, "cores": cores, "kind": "port", "sample": sample}
+        line = {"metric": metric, "value": value, "unit": unit, "n_gpus": world, "steps": args.steps,
+                "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True,
+                "scaling": "strong", "vs_baseline": None, "dtype": args.precision, "data": "synthetic",
+                "config": workload_config(args, w), "clocks": clk, "e2e": e2e,
+                "gpu_launches": int(launches), "roofline": roof, "cpu_baseline": cb,
+                "last_loss": [float(v) for v in last.float().cpu().numpy()[:3]] if w["kind"] == "train" else None}
+        print(json.dumps(line))
+    h.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="train_h512_l3_b800", choices=sorted(WORKLOADS))
+    ap.add_argument("--precision", default="f32", choices=["f32", "bf16"])
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    args = ap.parse_args()
+    w = WORKLOADS[args.workload]
+    if args.impl == "reference":
+        run_reference(args, w)
+    else:
+        run_ours(args, w)
+
+
+if __name__ == "__main__":
+    main()

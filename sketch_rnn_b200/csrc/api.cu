@@ -1,0 +1,441 @@
+// api.cu -- the extern "C" surface of libskrnn.so (include/skrnn.h): handle lifetime, TF-layout
+// parameter vector, and the orchestration of one forward / loss+BPTT / optimiser step out of the
+// kernels in the other translation units.
+#include <stdarg.h>
+#include <string.h>
+
+#include "common.cuh"
+
+static thread_local char g_err[1024] = "";
+
+void sk_set_error(const char *fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+
+namespace {
+
+const char *kCellScope[3] = {"BasicLSTMCell", "GRUCell", "BasicRNNCell"};
+
+void add_tensor(skrnn_handle *h, const std::string &name, int rows, int cols, int64_t *off) {
+  SkTensor t;
+  t.name = name;
+  t.offset = h->P;
+  t.rows = rows;
+  t.cols = cols;
+  *off = h->P;
+  h->P += (int64_t)rows * cols;
+  h->tensors.push_back(t);
+}
+
+// tf.trainable_variables() order and TF shapes (model.py:45-47, then MultiRNNCell/Cell{l}).
+void build_layout(skrnn_handle *h) {
+  const int H = h->H;
+  h->P = 0;
+  add_tensor(h, "rnn_mdn/output_w", H, h->NOUT, &h->off_out_w);
+  add_tensor(h, "rnn_mdn/output_b", 1, h->NOUT, &h->off_out_b);
+  for (int l = 0; l < h->L; ++l) {
+    SkLayerParams &lp = h->lp[l];
+    lp.I = (l == 0) ? 5 : H;
+    char base[128];
+    snprintf(base, sizeof(base), "rnn_mdn/MultiRNNCell/Cell%d/%s/", l, kCellScope[h->cfg.cell]);
+    lp.w[1] = lp.b[1] = 0;
+    lp.ncol[1] = 0;
+    if (h->cfg.cell == SKRNN_CELL_GRU) {
+      lp.ncol[0] = 2 * H;
+      lp.ncol[1] = H;
+      add_tensor(h, std::string(base) + "Gates/Linear/Matrix", lp.I + H, 2 * H, &lp.w[0]);
+      add_tensor(h, std::string(base) + "Gates/Linear/Bias", 1, 2 * H, &lp.b[0]);
+      add_tensor(h, std::string(base) + "Candidate/Linear/Matrix", lp.I + H, H, &lp.w[1]);
+      add_tensor(h, std::string(base) + "Candidate/Linear/Bias", 1, H, &lp.b[1]);
+    } else {
+      lp.ncol[0] = h->G;
+      add_tensor(h, std::string(base) + "Linear/Matrix", lp.I + H, h->G, &lp.w[0]);
+      add_tensor(h, std::string(base) + "Linear/Bias", 1, h->G, &lp.b[0]);
+    }
+  }
+}
+
+void free_workspace(SkWorkspace &w) {
+  cudaFree(w.x_tm);
+  for (int l = 0; l < SK_MAX_LAYERS; ++l) {
+    cudaFree(w.xw[l]);
+    cudaFree(w.hprev[l]);
+    cudaFree(w.cprev[l]);
+    cudaFree(w.out[l]);
+    w.xw[l] = w.hprev[l] = w.cprev[l] = w.out[l] = nullptr;
+  }
+  cudaFree(w.dout);
+  cudaFree(w.logits);
+  w.x_tm = w.dout = w.logits = nullptr;
+  w.cap_rows = 0;
+}
+
+int ensure_workspace(skrnn_handle *h, int B, int T) {
+  const int64_t rows = (int64_t)B * T;
+  SkWorkspace &w = h->ws;
+  if (rows <= w.cap_rows) return 0;
+  SK_CUDA(cudaDeviceSynchronize());
+  free_workspace(w);
+  SK_CUDA(cudaMalloc(&w.x_tm, rows * 5 * sizeof(float)));
+  for (int l = 0; l < h->L; ++l) {
+    SK_CUDA(cudaMalloc(&w.xw[l], rows * h->G * sizeof(float)));
+    SK_CUDA(cudaMalloc(&w.hprev[l], rows * h->H * sizeof(float)));
+    if (h->cfg.cell != SKRNN_CELL_RNN) SK_CUDA(cudaMalloc(&w.cprev[l], rows * h->H * sizeof(float)));
+    SK_CUDA(cudaMalloc(&w.out[l], rows * h->H * sizeof(float)));
+  }
+  SK_CUDA(cudaMalloc(&w.dout, rows * h->H * sizeof(float)));
+  SK_CUDA(cudaMalloc(&w.logits, rows * h->NOUT * sizeof(float)));
+  w.cap_rows = rows;
+  return 0;
+}
+
+int check_shape(skrnn_handle *h, int B, int T) {
+  SK_CHECK(h != nullptr, "null handle");
+  SK_CHECK(B > 0 && T > 0, "batch %d and sequence length %d must be positive", B, T);
+  SK_CUDA(cudaSetDevice(h->cfg.device));
+  return ensure_workspace(h, B, T);
+}
+
+// forward unroll of the whole stack + output projection (model.py:97-99)
+int run_forward(skrnn_handle *h, cudaStream_t st, int B, int T, const float *x, const float *state_in,
+                float *state_out, const float *mask, uint64_t seed, int row0, bool training) {
+  const int H = h->H, G = h->G;
+  const int64_t R = (int64_t)B * T;
+  SK_TRY(sk_transpose_x(h, st, B, T, x));
+  for (int l = 0; l < h->L; ++l) {
+    const SkLayerParams &lp = h->lp[l];
+    const float *X = (l == 0) ? h->ws.x_tm : h->ws.out[l - 1];
+    if (h->cfg.cell == SKRNN_CELL_GRU) {
+      SK_TRY(sk_gemm_f32(h, st, (int)R, 2 * H, lp.I, X, lp.I, true, h->params + lp.w[0], 2 * H, true,
+                         h->ws.xw[l], G, h->params + lp.b[0], false));
+      SK_TRY(sk_gemm_f32(h, st, (int)R, H, lp.I, X, lp.I, true, h->params + lp.w[1], H, true,
+                         h->ws.xw[l] + 2 * H, G, h->params + lp.b[1], false));
+    } else {
+      SK_TRY(sk_gemm_f32(h, st, (int)R, G, lp.I, X, lp.I, true, h->params + lp.w[0], G, true, h->ws.xw[l],
+                         G, h->params + lp.b[0], false));
+    }
+    SK_TRY(sk_rnn_forward_layer(h, st, l, B, T, x, state_in + (size_t)l * B * h->S,
+                                state_out + (size_t)l * B * h->S, mask, seed, row0, training));
+  }
+  SK_TRY(sk_gemm_f32(h, st, (int)R, h->NOUT, H, h->ws.out[h->L - 1], H, true, h->params + h->off_out_w,
+                     h->NOUT, true, h->ws.logits, h->NOUT, h->params + h->off_out_b, false));
+  return 0;
+}
+
+}  // namespace
+
+extern "C" {
+
+const char *skrnn_last_error(void) { return g_err; }
+const char *skrnn_version(void) { return "skrnn 0.1 sm_100a"; }
+
+int skrnn_create(const skrnn_config *cfg, skrnn_handle **out) {
+  SK_CHECK(cfg != nullptr && out != nullptr, "skrnn_create: null argument");
+  *out = nullptr;
+  if (cfg->cell < 0 || cfg->cell > 2) {
+    sk_set_error("model type not supported: %d", cfg->cell);  // model.py:21
+    return 1;
+  }
+  SK_CHECK(cfg->rnn_size > 0 && cfg->rnn_size % 8 == 0, "rnn_size %d must be a positive multiple of 8", cfg->rnn_size);
+  SK_CHECK(cfg->num_layers >= 1 && cfg->num_layers <= SK_MAX_LAYERS, "num_layers %d out of range", cfg->num_layers);
+  SK_CHECK(cfg->num_mixture >= 1 && cfg->num_mixture <= 128, "num_mixture %d out of range [1,128]", cfg->num_mixture);
+  SK_CHECK(cfg->keep_prob > 0.f && cfg->keep_prob <= 1.f, "keep_prob %f out of (0,1]", cfg->keep_prob);
+  SK_CHECK(cfg->precision == SKRNN_PREC_F32 || cfg->precision == SKRNN_PREC_BF16, "unknown precision %d", cfg->precision);
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || ndev == 0) {
+    sk_set_error("libskrnn needs an NVIDIA B200 (sm_100) GPU; there is no CPU fallback: %s",
+                 e != cudaSuccess ? cudaGetErrorString(e) : "no CUDA device");
+    return 2;
+  }
+  SK_CHECK(cfg->device >= 0 && cfg->device < ndev, "device %d out of range (have %d)", cfg->device, ndev);
+  SK_CUDA(cudaSetDevice(cfg->device));
+  cudaDeviceProp prop;
+  SK_CUDA(cudaGetDeviceProperties(&prop, cfg->device));
+  SK_CHECK(prop.major == 10, "libskrnn is built for sm_100a only; device %d is sm_%d%d", cfg->device, prop.major, prop.minor);
+
+  skrnn_handle *h = new skrnn_handle();
+  h->cfg = *cfg;
+  h->H = cfg->rnn_size;
+  h->L = cfg->num_layers;
+  h->M = cfg->num_mixture;
+  h->NOUT = 3 + 6 * h->M;
+  h->NGATE = cfg->cell == SKRNN_CELL_LSTM ? 4 : (cfg->cell == SKRNN_CELL_GRU ? 3 : 1);
+  h->G = h->NGATE * h->H;
+  h->S = cfg->cell == SKRNN_CELL_LSTM ? 2 * h->H : h->H;
+  h->num_sms = prop.multiProcessorCount;
+  h->cluster_size = 8;
+  build_layout(h);
+  auto fail = [&](void) { skrnn_destroy(h); return 1; };
+  size_t pb = (size_t)h->P * sizeof(float);
+  if (cudaMalloc(&h->params, pb) != cudaSuccess || cudaMalloc(&h->grads, pb) != cudaSuccess ||
+      cudaMalloc(&h->adam_m, pb) != cudaSuccess || cudaMalloc(&h->adam_v, pb) != cudaSuccess ||
+      cudaMalloc(&h->scal, 8 * sizeof(double)) != cudaSuccess ||
+      cudaMalloc(&h->sync_ctr, 4 * sizeof(unsigned int)) != cudaSuccess) {
+    sk_set_error("skrnn_create: cudaMalloc of %zu B x4 failed", pb);
+    return fail();
+  }
+  cudaMemset(h->params, 0, pb);
+  cudaMemset(h->grads, 0, pb);
+  cudaMemset(h->adam_m, 0, pb);
+  cudaMemset(h->adam_v, 0, pb);
+  cudaMemset(h->scal, 0, 8 * sizeof(double));
+  cudaMemset(h->sync_ctr, 0, 4 * sizeof(unsigned int));
+  h->ws.wpack_floats = (int64_t)h->cluster_size * h->H * 256;
+  if (cudaMalloc(&h->ws.wpack, h->ws.wpack_floats * sizeof(float)) != cudaSuccess) {
+    sk_set_error("skrnn_create: cudaMalloc of weight pack failed");
+    return fail();
+  }
+  if (cfg->batch_size > 0 && cfg->seq_length > 0 && ensure_workspace(h, cfg->batch_size, cfg->seq_length) != 0)
+    return fail();
+  if (cudaDeviceSynchronize() != cudaSuccess) {
+    sk_set_error("skrnn_create: device error after initialisation");
+    return fail();
+  }
+  *out = h;
+  return 0;
+}
+
+void skrnn_destroy(skrnn_handle *h) {
+  if (!h) return;
+  cudaSetDevice(h->cfg.device);
+  cudaDeviceSynchronize();
+  free_workspace(h->ws);
+  cudaFree(h->ws.wpack);
+  cudaFree(h->params);
+  cudaFree(h->grads);
+  cudaFree(h->adam_m);
+  cudaFree(h->adam_v);
+  cudaFree(h->scal);
+  cudaFree(h->sync_ctr);
+  cudaFree(h->st_x);
+  cudaFree(h->st_y);
+  cudaFree(h->st_state);
+  cudaFree(h->st_loss);
+  cudaFree(h->samp_state);
+  cudaFreeHost(h->pin_x);
+  cudaFreeHost(h->pin_y);
+  cudaFreeHost(h->pin_state);
+  cudaFreeHost(h->pin_loss);
+  for (auto &r : h->prof) { cudaEventDestroy(r.a); cudaEventDestroy(r.b); }
+  for (auto e : h->prof_pool) cudaEventDestroy(e);
+  delete h;
+}
+
+int64_t skrnn_param_count(const skrnn_handle *h) { return h ? h->P : -1; }
+int32_t skrnn_num_tensors(const skrnn_handle *h) { return h ? (int32_t)h->tensors.size() : -1; }
+
+int skrnn_tensor_info(const skrnn_handle *h, int32_t index, char *name_buf, int32_t name_cap,
+                      int64_t *offset, int32_t *rows, int32_t *cols) {
+  SK_CHECK(h != nullptr, "null handle");
+  SK_CHECK(index >= 0 && index < (int32_t)h->tensors.size(), "tensor index %d out of range", index);
+  const SkTensor &t = h->tensors[index];
+  if (name_buf && name_cap > 0) {
+    strncpy(name_buf, t.name.c_str(), name_cap - 1);
+    name_buf[name_cap - 1] = 0;
+  }
+  if (offset) *offset = t.offset;
+  if (rows) *rows = t.rows;
+  if (cols) *cols = t.cols;
+  return 0;
+}
+
+int skrnn_set_params(skrnn_handle *h, const float *host_params, int64_t count) {
+  SK_CHECK(h && host_params, "null argument");
+  SK_CHECK(count == h->P, "set_params: expected %lld floats, got %lld", (long long)h->P, (long long)count);
+  SK_CUDA(cudaSetDevice(h->cfg.device));
+  SK_CUDA(cudaMemcpy(h->params, host_params, count * sizeof(float), cudaMemcpyHostToDevice));
+  return 0;
+}
+
+int skrnn_get_params(skrnn_handle *h, float *host_params, int64_t count) {
+  SK_CHECK(h && host_params, "null argument");
+  SK_CHECK(count == h->P, "get_params: expected %lld floats, got %lld", (long long)h->P, (long long)count);
+  SK_CUDA(cudaSetDevice(h->cfg.device));
+  SK_CUDA(cudaMemcpy(host_params, h->params, count * sizeof(float), cudaMemcpyDeviceToHost));
+  return 0;
+}
+
+int skrnn_set_adam_state(skrnn_handle *h, const float *host_m, const float *host_v, int64_t count,
+                         double beta1_power, double beta2_power) {
+  SK_CHECK(h, "null handle");
+  SK_CHECK(count == h->P, "set_adam_state: expected %lld floats, got %lld", (long long)h->P, (long long)count);
+  SK_CUDA(cudaSetDevice(h->cfg.device));
+  if (host_m) SK_CUDA(cudaMemcpy(h->adam_m, host_m, count * sizeof(float), cudaMemcpyHostToDevice));
+  if (host_v) SK_CUDA(cudaMemcpy(h->adam_v, host_v, count * sizeof(float), cudaMemcpyHostToDevice));
+  h->beta1_power = beta1_power;
+  h->beta2_power = beta2_power;
+  return 0;
+}
+
+int skrnn_get_adam_state(skrnn_handle *h, float *host_m, float *host_v, int64_t count,
+                         double *beta1_power, double *beta2_power) {
+  SK_CHECK(h, "null handle");
+  SK_CHECK(count == h->P, "get_adam_state: expected %lld floats, got %lld", (long long)h->P, (long long)count);
+  SK_CUDA(cudaSetDevice(h->cfg.device));
+  if (host_m) SK_CUDA(cudaMemcpy(host_m, h->adam_m, count * sizeof(float), cudaMemcpyDeviceToHost));
+  if (host_v) SK_CUDA(cudaMemcpy(host_v, h->adam_v, count * sizeof(float), cudaMemcpyDeviceToHost));
+  if (beta1_power) *beta1_power = h->beta1_power;
+  if (beta2_power) *beta2_power = h->beta2_power;
+  return 0;
+}
+
+float *skrnn_params_dev(skrnn_handle *h) { return h ? h->params : nullptr; }
+float *skrnn_grads_dev(skrnn_handle *h) { return h ? h->grads : nullptr; }
+int64_t skrnn_launch_count(const skrnn_handle *h) { return h ? h->launches : -1; }
+
+int skrnn_profile_enable(skrnn_handle *h, int32_t on) {
+  SK_CHECK(h != nullptr, "null handle");
+  h->prof_on = on != 0;
+  return 0;
+}
+
+int skrnn_profile_read(skrnn_handle *h, double *ms_out, int64_t *count_out) {
+  SK_CHECK(h != nullptr && ms_out && count_out, "null argument");
+  SK_CUDA(cudaSetDevice(h->cfg.device));
+  SK_CUDA(cudaDeviceSynchronize());
+  for (int i = 0; i < SK_NUM_CAT; ++i) { ms_out[i] = 0.0; count_out[i] = 0; }
+  for (auto &r : h->prof) {
+    float ms = 0.f;
+    if (cudaEventElapsedTime(&ms, r.a, r.b) == cudaSuccess) { ms_out[r.cat] += ms; count_out[r.cat]++; }
+    h->prof_pool.push_back(r.a);
+    h->prof_pool.push_back(r.b);
+  }
+  h->prof.clear();
+  return 0;
+}
+
+int skrnn_forward(skrnn_handle *h, int32_t B, int32_t T, const float *x_dev, const float *state_in_dev,
+                  float *mdn_out_dev, float *state_out_dev, void *stream) {
+  SK_TRY(check_shape(h, B, T));
+  SK_CHECK(x_dev && state_in_dev && state_out_dev, "forward: null buffer");
+  SK_CHECK(h->cfg.precision == SKRNN_PREC_F32, "precision %d not built yet", h->cfg.precision);
+  cudaStream_t st = (cudaStream_t)stream;
+  SK_TRY(run_forward(h, st, B, T, x_dev, state_in_dev, state_out_dev, nullptr, 0, 0, false));
+  if (mdn_out_dev) {
+    SK_CUDA(cudaMemsetAsync(h->scal, 0, 3 * sizeof(double), st));
+    SK_TRY(sk_head(h, st, B, T, nullptr, mdn_out_dev, false, (int64_t)B * T));
+  }
+  return 0;
+}
+
+int skrnn_loss_grad(skrnn_handle *h, int32_t B, int32_t T, const float *x_dev, const float *y_dev,
+                    const float *state_in_dev, const float *dropout_mask_dev, uint64_t seed, int32_t row0,
+                    int64_t loss_rows, float *losses_dev, float *state_out_dev, void *stream) {
+  SK_TRY(check_shape(h, B, T));
+  SK_CHECK(x_dev && y_dev && state_in_dev && state_out_dev && losses_dev, "loss_grad: null buffer");
+  SK_CHECK(loss_rows >= (int64_t)B * T, "loss_rows %lld smaller than B*T", (long long)loss_rows);
+  SK_CHECK(h->cfg.precision == SKRNN_PREC_F32, "precision %d not built yet", h->cfg.precision);
+  cudaStream_t st = (cudaStream_t)stream;
+  const int H = h->H, G = h->G, NOUT = h->NOUT;
+  const int R = B * T;
+  SK_CUDA(cudaMemsetAsync(h->grads, 0, (size_t)h->P * sizeof(float), st));
+  SK_CUDA(cudaMemsetAsync(h->scal, 0, 3 * sizeof(double), st));
+  SK_TRY(run_forward(h, st, B, T, x_dev, state_in_dev, state_out_dev, dropout_mask_dev, seed, row0, true));
+  SK_TRY(sk_head(h, st, B, T, y_dev, nullptr, true, loss_rows));
+  SK_TRY(sk_finalize_losses(h, st, losses_dev));
+  // head backward: d output_w, d output_b, d(top layer output)
+  const float *top = h->ws.out[h->L - 1];
+  SK_TRY(sk_gemm_f32(h, st, H, NOUT, R, top, H, false, h->ws.logits, NOUT, true, h->grads + h->off_out_w,
+                     NOUT, nullptr, true));
+  SK_TRY(sk_colsum(h, st, h->ws.logits, R, NOUT, NOUT, h->grads + h->off_out_b));
+  SK_TRY(sk_gemm_f32(h, st, R, H, NOUT, h->ws.logits, NOUT, true, h->params + h->off_out_w, NOUT, false,
+                     h->ws.dout, H, nullptr, false));
+  for (int l = h->L - 1; l >= 0; --l) {
+    const SkLayerParams &lp = h->lp[l];
+    SK_TRY(sk_rnn_backward_layer(h, st, l, B, T, x_dev, dropout_mask_dev, seed, row0, true));
+    const float *X = (l == 0) ? h->ws.x_tm : h->ws.out[l - 1];
+    const float *dpre = h->ws.xw[l];
+    const int I = lp.I;
+    if (h->cfg.cell == SKRNN_CELL_GRU) {
+      const float *dg = dpre, *dc = dpre + 2 * H;
+      float *gWg = h->grads + lp.w[0], *gWc = h->grads + lp.w[1];
+      SK_TRY(sk_gemm_f32(h, st, I, 2 * H, R, X, I, false, dg, G, true, gWg, 2 * H, nullptr, true));
+      SK_TRY(sk_gemm_f32(h, st, H, 2 * H, R, h->ws.hprev[l], H, false, dg, G, true, gWg + (size_t)I * 2 * H, 2 * H, nullptr, true));
+      SK_TRY(sk_colsum(h, st, dg, R, 2 * H, G, h->grads + lp.b[0]));
+      SK_TRY(sk_gemm_f32(h, st, I, H, R, X, I, false, dc, G, true, gWc, H, nullptr, true));
+      SK_TRY(sk_gemm_f32(h, st, H, H, R, h->ws.cprev[l], H, false, dc, G, true, gWc + (size_t)I * H, H, nullptr, true));
+      SK_TRY(sk_colsum(h, st, dc, R, H, G, h->grads + lp.b[1]));
+      if (l > 0) {
+        SK_TRY(sk_gemm_f32(h, st, R, I, 2 * H, dg, G, true, h->params + lp.w[0], 2 * H, false, h->ws.dout, H, nullptr, false));
+        SK_TRY(sk_gemm_f32(h, st, R, I, H, dc, G, true, h->params + lp.w[1], H, false, h->ws.dout, H, nullptr, true));
+      }
+    } else {
+      float *gW = h->grads + lp.w[0];
+      SK_TRY(sk_gemm_f32(h, st, I, G, R, X, I, false, dpre, G, true, gW, G, nullptr, true));
+      SK_TRY(sk_gemm_f32(h, st, H, G, R, h->ws.hprev[l], H, false, dpre, G, true, gW + (size_t)I * G, G, nullptr, true));
+      SK_TRY(sk_colsum(h, st, dpre, R, G, G, h->grads + lp.b[0]));
+      if (l > 0)
+        SK_TRY(sk_gemm_f32(h, st, R, I, G, dpre, G, true, h->params + lp.w[0], G, false, h->ws.dout, H, nullptr, false));
+    }
+  }
+  return 0;
+}
+
+int skrnn_apply_clip_adam(skrnn_handle *h, float lr, float *gnorm_out_dev, void *stream) {
+  SK_CHECK(h != nullptr, "null handle");
+  SK_CUDA(cudaSetDevice(h->cfg.device));
+  return sk_clip_adam(h, (cudaStream_t)stream, lr, gnorm_out_dev);
+}
+
+int skrnn_train_step_host(skrnn_handle *h, int32_t B, int32_t T, const float *x_host, const float *y_host,
+                          float *state_host, float lr, uint64_t seed, float *losses_host) {
+  SK_TRY(check_shape(h, B, T));
+  SK_CHECK(x_host && y_host && state_host && losses_host, "train_step_host: null buffer");
+  const int64_t rows = (int64_t)B * T;
+  const int64_t nstate = (int64_t)h->L * B * h->S;
+  if (rows > h->st_rows) {
+    cudaFree(h->st_x); cudaFree(h->st_y); cudaFreeHost(h->pin_x); cudaFreeHost(h->pin_y);
+    h->st_x = h->st_y = h->pin_x = h->pin_y = nullptr;
+    h->st_rows = 0;
+    SK_CUDA(cudaMalloc(&h->st_x, rows * 5 * sizeof(float)));
+    SK_CUDA(cudaMalloc(&h->st_y, rows * 5 * sizeof(float)));
+    SK_CUDA(cudaMallocHost(&h->pin_x, rows * 5 * sizeof(float)));
+    SK_CUDA(cudaMallocHost(&h->pin_y, rows * 5 * sizeof(float)));
+    h->st_rows = rows;
+  }
+  if (nstate > h->st_state_n) {
+    cudaFree(h->st_state); cudaFreeHost(h->pin_state);
+    h->st_state = h->pin_state = nullptr;
+    h->st_state_n = 0;
+    SK_CUDA(cudaMalloc(&h->st_state, nstate * sizeof(float)));
+    SK_CUDA(cudaMallocHost(&h->pin_state, nstate * sizeof(float)));
+    h->st_state_n = nstate;
+  }
+  if (!h->st_loss) {
+    SK_CUDA(cudaMalloc(&h->st_loss, 4 * sizeof(float)));
+    SK_CUDA(cudaMallocHost(&h->pin_loss, 4 * sizeof(float)));
+  }
+  cudaStream_t st = 0;
+  memcpy(h->pin_x, x_host, rows * 5 * sizeof(float));
+  memcpy(h->pin_y, y_host, rows * 5 * sizeof(float));
+  memcpy(h->pin_state, state_host, nstate * sizeof(float));
+  SK_CUDA(cudaMemcpyAsync(h->st_x, h->pin_x, rows * 5 * sizeof(float), cudaMemcpyHostToDevice, st));
+  SK_CUDA(cudaMemcpyAsync(h->st_y, h->pin_y, rows * 5 * sizeof(float), cudaMemcpyHostToDevice, st));
+  SK_CUDA(cudaMemcpyAsync(h->st_state, h->pin_state, nstate * sizeof(float), cudaMemcpyHostToDevice, st));
+  SK_TRY(skrnn_loss_grad(h, B, T, h->st_x, h->st_y, h->st_state, nullptr, seed, 0, rows, h->st_loss,
+                         h->st_state, st));
+  SK_TRY(sk_clip_adam(h, st, lr, h->st_loss + 3));
+  SK_CUDA(cudaMemcpyAsync(h->pin_loss, h->st_loss, 4 * sizeof(float), cudaMemcpyDeviceToHost, st));
+  SK_CUDA(cudaMemcpyAsync(h->pin_state, h->st_state, nstate * sizeof(float), cudaMemcpyDeviceToHost, st));
+  SK_CUDA(cudaStreamSynchronize(st));
+  memcpy(losses_host, h->pin_loss, 3 * sizeof(float));
+  memcpy(state_host, h->pin_state, nstate * sizeof(float));
+  return 0;
+}
+
+int skrnn_sample(skrnn_handle *h, int32_t n_sketches, int32_t num_steps, float temp_mixture, float temp_pen,
+                 int32_t stop_if_eoc, const float *uniforms_dev, uint64_t seed, int32_t sketch0,
+                 float *strokes_dev, int32_t *lengths_dev, float *mix_params_dev, void *stream) {
+  SK_CHECK(h != nullptr, "null handle");
+  SK_CHECK(strokes_dev && lengths_dev, "sample: null output buffer");
+  SK_CHECK(temp_mixture > 0.f && temp_pen > 0.f, "sample: temperatures must be positive");
+  SK_CUDA(cudaSetDevice(h->cfg.device));
+  return sk_sample_f32(h, (cudaStream_t)stream, n_sketches, num_steps, temp_mixture, temp_pen, stop_if_eoc,
+                       uniforms_dev, seed, sketch0, strokes_dev, lengths_dev, mix_params_dev);
+}
+
+}  // extern "C"

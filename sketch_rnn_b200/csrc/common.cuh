@@ -1,0 +1,136 @@
+// common.cuh -- internal declarations shared by the libskrnn translation units.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <algorithm>
+#include <string>
+#include <vector>
+
+#include "../../include/skrnn.h"
+
+#define SK_MAX_LAYERS 8
+
+void sk_set_error(const char *fmt, ...);
+
+#define SK_CUDA(expr)                                                                     \
+  do {                                                                                    \
+    cudaError_t _e = (expr);                                                              \
+    if (_e != cudaSuccess) {                                                              \
+      sk_set_error("%s:%d: %s failed: %s", __FILE__, __LINE__, #expr, cudaGetErrorString(_e)); \
+      return 1;                                                                           \
+    }                                                                                     \
+  } while (0)
+
+#define SK_CHECK(cond, ...)       \
+  do {                            \
+    if (!(cond)) {                \
+      sk_set_error(__VA_ARGS__);  \
+      return 1;                   \
+    }                             \
+  } while (0)
+
+#define SK_TRY(expr)          \
+  do {                        \
+    int _r = (expr);          \
+    if (_r != 0) return _r;   \
+  } while (0)
+
+struct SkTensor {
+  std::string name;
+  int64_t offset;
+  int rows, cols;  // bias: rows = 1
+};
+
+// Per-layer addressing of the flat parameter / gradient vector (TF layouts, include/skrnn.h).
+struct SkLayerParams {
+  int I;            // input width (5 for layer 0 else H)
+  int64_t w[2];     // Matrix offsets: lstm/rnn {W, -}, gru {Gates, Candidate}
+  int64_t b[2];     // Bias offsets
+  int ncol[2];      // Matrix column counts
+};
+
+struct SkWorkspace {   // time-major activations for one (B, T) capacity
+  int64_t cap_rows = 0;  // T*B rows allocated
+  int capB = 0, capT = 0;
+  float *x_tm = nullptr;                    // [T,B,5]
+  float *xw[SK_MAX_LAYERS] = {nullptr};     // [T,B,G]: input projection -> gate activations -> d(pre)
+  float *hprev[SK_MAX_LAYERS] = {nullptr};  // [T,B,H]: h fed to step t (post eoc reset)
+  float *cprev[SK_MAX_LAYERS] = {nullptr};  // [T,B,H]: lstm c fed to step t; gru: r*h of step t
+  float *out[SK_MAX_LAYERS] = {nullptr};    // [T,B,H]: layer output (pre reset; top layer: after dropout)
+  float *dout = nullptr;                    // [T,B,H]: gradient wrt a layer's output (reused per layer)
+  float *logits = nullptr;                  // [T*B,NOUT]: logits -> d(logits)
+  float *wpack = nullptr;                   // per-CTA packed recurrent weight slices (fwd or bwd)
+  int64_t wpack_floats = 0;
+};
+
+struct skrnn_handle {
+  skrnn_config cfg;
+  int H, L, M, NOUT, G, S, NGATE;
+  int64_t P;
+  std::vector<SkTensor> tensors;
+  SkLayerParams lp[SK_MAX_LAYERS];
+  int64_t off_out_w, off_out_b;
+  float *params = nullptr, *grads = nullptr, *adam_m = nullptr, *adam_v = nullptr;
+  double beta1_power = 0.9, beta2_power = 0.999;
+  SkWorkspace ws;
+  // small device scratch: [0..2] loss accumulators (double), [3] grad sumsq (double), [4] barrier ctr
+  double *scal = nullptr;
+  unsigned int *sync_ctr = nullptr;
+  // staging buffers for the *_host entry points
+  float *st_x = nullptr, *st_y = nullptr, *st_state = nullptr, *st_loss = nullptr;
+  float *pin_x = nullptr, *pin_y = nullptr, *pin_state = nullptr, *pin_loss = nullptr;
+  int64_t st_rows = 0, st_state_n = 0;
+  float *samp_state = nullptr;  // sampler: per-sketch recurrent state [n,L,S]
+  int64_t samp_state_n = 0;
+  int num_sms = 0;
+  int64_t launches = 0;
+  int cluster_size = 1;
+  // optional per-category kernel timing (skrnn_profile_*): CUDA events around every launch
+  bool prof_on = false;
+  struct ProfRec { int cat; cudaEvent_t a, b; };
+  std::vector<ProfRec> prof;
+  std::vector<cudaEvent_t> prof_pool;
+};
+
+enum { SK_CAT_GEMM = 0, SK_CAT_RNN_FWD = 1, SK_CAT_RNN_BWD = 2, SK_CAT_HEAD = 3, SK_CAT_OPTIM = 4,
+       SK_CAT_MISC = 5, SK_CAT_SAMPLER = 6, SK_CAT_TC_GEMM = 7, SK_NUM_CAT = 8 };
+
+// RAII scope: counts the launch and, when profiling is on, brackets it with events on `st`.
+struct SkLaunch {
+  skrnn_handle *h; cudaStream_t st; cudaEvent_t b = nullptr;
+  SkLaunch(skrnn_handle *h_, cudaStream_t st_, int cat) : h(h_), st(st_) {
+    h->launches++;
+    if (!h->prof_on) return;
+    cudaEvent_t a;
+    auto get = [&]() { cudaEvent_t e; if (!h->prof_pool.empty()) { e = h->prof_pool.back(); h->prof_pool.pop_back(); } else cudaEventCreate(&e); return e; };
+    a = get(); b = get();
+    cudaEventRecord(a, st);
+    h->prof.push_back({cat, a, b});
+  }
+  ~SkLaunch() { if (b) cudaEventRecord(b, st); }
+};
+
+// ---- kernels.cu launchers (all stream-ordered; return 0 / non-zero with sk_set_error) ----
+// C[M,N] (+)= A[M,K] * B[K,N] (+ bias[N]).  a_kcontig: A stored [M][lda] else [K][lda];
+// b_ncontig: B stored [K][ldb] else [N][ldb].  accumulate: atomically add into C (split-K ok).
+int sk_gemm_f32(skrnn_handle *h, cudaStream_t st, int M, int N, int K, const float *A, int lda,
+                bool a_kcontig, const float *B, int ldb, bool b_ncontig, float *C, int ldc,
+                const float *bias, bool accumulate);
+int sk_colsum(skrnn_handle *h, cudaStream_t st, const float *A, int64_t rows, int cols, int lda,
+              float *out);  // out[c] += sum_r A[r][c]
+
+int sk_rnn_forward_layer(skrnn_handle *h, cudaStream_t st, int l, int B, int T, const float *x_bt5,
+                         const float *state_in, float *state_out, const float *mask, uint64_t seed,
+                         int row0, bool training);
+int sk_rnn_backward_layer(skrnn_handle *h, cudaStream_t st, int l, int B, int T, const float *x_bt5,
+                          const float *mask, uint64_t seed, int row0, bool training);
+
+int sk_head(skrnn_handle *h, cudaStream_t st, int B, int T, const float *y_bt5, float *mdn_out,
+            bool want_grad, int64_t loss_rows);
+int sk_finalize_losses(skrnn_handle *h, cudaStream_t st, float *losses_dev);
+int sk_clip_adam(skrnn_handle *h, cudaStream_t st, float lr, float *gnorm_out);
+int sk_transpose_x(skrnn_handle *h, cudaStream_t st, int B, int T, const float *x_bt5);
+int sk_sample_f32(skrnn_handle *h, cudaStream_t st, int n, int steps, float temp_mix, float temp_pen,
+                  int stop_if_eoc, const float *uniforms, uint64_t seed, int sketch0, float *strokes,
+                  int *lengths, float *mixp);

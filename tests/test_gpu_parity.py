@@ -1,0 +1,257 @@
+"""GPU parity: the CUDA path (through the C ABI in include/skrnn.h) against the CPU oracle on the
+same seeded inputs.  Tolerances are the ones BASELINE.json's north_star states: loss / gradients
+1e-4 relative on the fp32 path, MDN parameters 1e-4, sampled strokes bit-exact."""
+import numpy as np
+import pytest
+
+from oracle import sketch_oracle as so
+from oracle import sampler_ref
+
+pytestmark = pytest.mark.gpu
+
+TOL = 1e-4
+
+
+def rel_err(a, ref):
+    a = np.asarray(a, dtype=np.float64)
+    ref = np.asarray(ref, dtype=np.float64)
+    return float(np.max(np.abs(a - ref)) / (np.max(np.abs(ref)) + 1e-30))
+
+
+def make_handle(cfg, params, B=0, T=0, precision="f32"):
+    from sketch_rnn_b200 import _lib
+    h = _lib.Handle(model=cfg.model, rnn_size=cfg.rnn_size, num_layers=cfg.num_layers,
+                    num_mixture=cfg.num_mixture, batch_size=B, seq_length=T, keep_prob=cfg.keep_prob,
+                    grad_clip=cfg.grad_clip, stroke_importance_factor=cfg.stroke_importance_factor,
+                    data_scale=cfg.data_scale, precision=precision)
+    h.set_params_dict(params)
+    return h
+
+
+def stack_state(state):
+    return np.ascontiguousarray(np.stack(state, 0), dtype=np.float32)
+
+
+def f64(params):
+    return {k: v.astype(np.float64) for k, v in params.items()}
+
+
+CASES = [
+    # model, H, L, M, B, T
+    ("lstm", 16, 2, 3, 5, 7),
+    ("lstm", 32, 3, 4, 19, 9),
+    ("gru", 16, 2, 3, 5, 7),
+    ("gru", 64, 3, 5, 11, 6),
+    ("rnn", 16, 2, 3, 5, 7),
+    ("rnn", 40, 3, 24, 9, 8),
+    ("lstm", 256, 2, 24, 23, 12),
+    ("gru", 256, 2, 24, 10, 10),
+    ("lstm", 512, 2, 24, 9, 5),
+]
+
+
+def _case(model, H, L, M, B, T, seed=0, keep=0.8):
+    cfg = so.Config(model=model, rnn_size=H, num_layers=L, num_mixture=M, batch_size=B, seq_length=T,
+                    keep_prob=keep)
+    params = so.init_params(cfg, seed=seed + 1, trained_like=True)
+    x, y = so.synthetic_batch(B, T, seed=seed + 2, p_eoc=0.15)
+    x[0, 0, 2:5] = [0, 1, 0]   # eoc on the very first step of row 0
+    x[-1, -1, 2:5] = [0, 1, 0]  # and on the very last step of the last row
+    s0 = so.synthetic_state(cfg, B, seed=seed)
+    mask = so.synthetic_dropout_mask(cfg, B, T, seed=seed)
+    return cfg, params, x, y, s0, mask
+
+
+@pytest.mark.parametrize("model,H,L,M,B,T", CASES)
+def test_forward_mdn_and_state(model, H, L, M, B, T):
+    cfg, params, x, y, s0, _ = _case(model, H, L, M, B, T)
+    ref = so.forward(cfg, f64(params), x.astype(np.float64), [s.astype(np.float64) for s in s0])
+    h = make_handle(cfg, params, B, T)
+    mdn, state_out = h.forward(x, stack_state(s0))
+    mdn = mdn.cpu().numpy()
+    state_out = state_out.cpu().numpy()
+    Mx = cfg.num_mixture
+    names = ["pi", "mu1", "mu2", "sigma1", "sigma2", "corr"]
+    assert rel_err(mdn[:, 0:3], ref["mdn"]["pen"]) < TOL
+    for i, n in enumerate(names):
+        got = mdn[:, 3 + i * Mx:3 + (i + 1) * Mx]
+        assert rel_err(got, ref["mdn"][n]) < TOL, n
+    for l in range(L):
+        assert rel_err(state_out[l], ref["final_state"][l]) < TOL
+    h.close()
+
+
+@pytest.mark.parametrize("model,H,L,M,B,T", CASES)
+def test_loss_and_gradients(model, H, L, M, B, T):
+    cfg, params, x, y, s0, mask = _case(model, H, L, M, B, T)
+    losses_ref, grads_ref, fstate_ref, _ = so.loss_and_grads(
+        cfg, f64(params), x.astype(np.float64), y.astype(np.float64),
+        [s.astype(np.float64) for s in s0], mask.astype(np.float64))
+    h = make_handle(cfg, params, B, T)
+    losses, state_out = h.loss_grad(x, y, stack_state(s0), dropout_mask=mask)
+    losses = losses.cpu().numpy()
+    g = h.get_params_dict(h.grads_tensor().cpu().numpy())
+    for i in range(3):
+        assert abs(losses[i] - losses_ref[i]) <= TOL * abs(losses_ref[i]) + 1e-6, (i, losses, losses_ref)
+    gscale = max(np.max(np.abs(v)) for v in grads_ref.values())
+    for n in grads_ref:
+        err = np.max(np.abs(g[n].astype(np.float64) - grads_ref[n])) / gscale
+        assert err < TOL, (n, err)
+        assert rel_err(g[n], grads_ref[n]) < 20 * TOL, (n, rel_err(g[n], grads_ref[n]))
+    so_state = state_out.cpu().numpy()
+    for l in range(L):
+        assert rel_err(so_state[l], fstate_ref[l]) < TOL
+    h.close()
+
+
+def test_sharded_loss_matches_full_batch():
+    """Two data-parallel shards (rows 0..B/2, B/2..B) summed == the full batch."""
+    cfg, params, x, y, s0, mask = _case("lstm", 32, 2, 4, 12, 6)
+    h = make_handle(cfg, params, 12, 6)
+    st = stack_state(s0)
+    losses, _ = h.loss_grad(x, y, st, dropout_mask=mask)
+    g_full = h.grads_tensor().cpu().numpy().copy()
+    l_full = losses.cpu().numpy()
+    acc_g, acc_l = 0, 0
+    for r in range(2):
+        sl = slice(6 * r, 6 * r + 6)
+        lo, _ = h.loss_grad(x[sl], y[sl], np.ascontiguousarray(st[:, sl]), dropout_mask=mask[sl], row0=6 * r,
+                            loss_rows=12 * 6)
+        acc_g = acc_g + h.grads_tensor().cpu().numpy()
+        acc_l = acc_l + lo.cpu().numpy()
+    assert rel_err(acc_g, g_full) < TOL
+    assert rel_err(acc_l, l_full) < TOL
+    h.close()
+
+
+def test_philox_dropout_is_shard_invariant():
+    """In-kernel dropout is keyed by the global row, so sharding does not change the mask."""
+    cfg, params, x, y, s0, _ = _case("lstm", 32, 2, 4, 8, 6)
+    h = make_handle(cfg, params, 8, 6)
+    st = stack_state(s0)
+    lo, _ = h.loss_grad(x, y, st, seed=1234)
+    g_full = h.grads_tensor().cpu().numpy().copy()
+    acc = 0
+    for r in range(2):
+        sl = slice(4 * r, 4 * r + 4)
+        h.loss_grad(x[sl], y[sl], np.ascontiguousarray(st[:, sl]), seed=1234, row0=4 * r, loss_rows=48)
+        acc = acc + h.grads_tensor().cpu().numpy()
+    assert rel_err(acc, g_full) < TOL
+    lo2, _ = h.loss_grad(x, y, st, seed=99)
+    assert abs(float(lo2[0]) - float(lo[0])) > 0  # a different seed draws a different mask
+    h.close()
+
+
+@pytest.mark.parametrize("model", ["lstm", "gru", "rnn"])
+def test_train_steps_clip_adam(model):
+    """Three sess.run(train_op) steps with state carry (train.py:85-86): weights, Adam slots and
+    losses track the oracle; the first step clips (gn > 5), later ones may not."""
+    cfg, params, x, y, s0, mask = _case(model, 32, 2, 4, 6, 8)
+    p64 = f64(params)
+    opt = so.AdamState(cfg, dtype=np.float64)
+    h = make_handle(cfg, params, 6, 8)
+    st_ref = [s.astype(np.float64) for s in s0]
+    st = stack_state(s0)
+    import torch
+    for step in range(3):
+        lr = 0.005 * (0.99 ** step)
+        losses_ref, st_ref, gn_ref = so.train_step(cfg, p64, opt, x.astype(np.float64), y.astype(np.float64),
+                                                   st_ref, lr, mask.astype(np.float64))
+        losses, st_t = h.loss_grad(x, y, st, dropout_mask=mask)
+        gn = h.apply_clip_adam(lr)
+        torch.cuda.synchronize()
+        st = st_t.cpu().numpy()
+        assert abs(float(gn) - gn_ref) <= TOL * gn_ref
+        assert abs(float(losses[0]) - losses_ref[0]) <= 5 * TOL * abs(losses_ref[0])
+    got = h.get_params_dict()
+    for n in p64:
+        assert rel_err(got[n], p64[n]) < 5 * TOL, n
+    m, v, b1, b2 = h.get_adam_state()
+    assert abs(b1 - opt.beta1_power) < 1e-12 and abs(b2 - opt.beta2_power) < 1e-12
+    md = h.get_params_dict(m)
+    for n in p64:
+        assert rel_err(md[n], opt.m[n]) < 5 * TOL, n
+    h.close()
+
+
+def test_train_step_host_entry_point():
+    cfg, params, x, y, s0, _ = _case("lstm", 32, 2, 4, 6, 8, keep=1.0)
+    p64 = f64(params)
+    opt = so.AdamState(cfg, dtype=np.float64)
+    losses_ref, st_ref, _ = so.train_step(cfg, p64, opt, x.astype(np.float64), y.astype(np.float64),
+                                          [s.astype(np.float64) for s in s0], 0.005)
+    h = make_handle(cfg, params, 6, 8)
+    st = stack_state(s0)
+    losses = h.train_step_host(x, y, st, 0.005)
+    assert rel_err(losses, losses_ref) < TOL
+    for l in range(2):
+        assert rel_err(st[l], st_ref[l]) < TOL
+    got = h.get_params_dict()
+    for n in p64:
+        assert rel_err(got[n], p64[n]) < 5 * TOL, n
+    h.close()
+
+
+@pytest.mark.parametrize("model,H,L,M", [("lstm", 16, 2, 3), ("gru", 32, 2, 5), ("rnn", 24, 3, 4),
+                                         ("lstm", 256, 2, 24)])
+def test_sampler_bit_exact(model, H, L, M):
+    """Sampled stroke sequences are bit-identical to the CPU restatement when both are fed the same
+    uniforms; covers temperature, stop_if_eoc and several sketches per CTA."""
+    cfg = so.Config(model=model, rnn_size=H, num_layers=L, num_mixture=M)
+    params = so.init_params(cfg, seed=7, trained_like=True)
+    h = make_handle(cfg, params)
+    steps = 40
+    for n, temp, stop in [(1, 1.0, False), (1, 0.1, True), (7, 0.5, False), (21, 0.3, True)]:
+        u = np.random.RandomState(n).rand(n, steps, 4).astype(np.float32)
+        strokes, lengths, mixp = h.sample(n, steps, temp, temp, stop, uniforms=u, want_params=True)
+        strokes, lengths, mixp = strokes.cpu().numpy(), lengths.cpu().numpy(), mixp.cpu().numpy()
+        for i in range(n):
+            ref_s, ref_p = sampler_ref.sample(cfg, params, u[i], steps, temp, temp, stop, want_params=True)
+            k = ref_s.shape[0]
+            assert lengths[i] == k, (i, lengths[i], k)
+            assert np.array_equal(strokes[i, :k].view(np.uint32), ref_s.view(np.uint32)), (model, n, i)
+            assert np.all(strokes[i, k:] == 0)
+            assert np.array_equal(mixp[i, :k].view(np.uint32), ref_p.view(np.uint32))
+    h.close()
+
+
+def test_sampler_against_numpy_transcription():
+    """Independent check of the sampler against the NumPy transcription of model.py:187-264."""
+    cfg = so.Config(model="lstm", rnn_size=32, num_layers=2, num_mixture=6)
+    params = so.init_params(cfg, seed=11, trained_like=True)
+    h = make_handle(cfg, params)
+    u = np.random.RandomState(5).rand(3, 30, 4).astype(np.float32)
+    strokes, lengths, _ = h.sample(3, 30, 0.4, 0.4, False, uniforms=u)
+    strokes = strokes.cpu().numpy()
+    for i in range(3):
+        ref, _ = so.sample(cfg, params, u[i], 30, 0.4, 0.4, False)
+        assert np.array_equal(strokes[i, :, 2:], ref[:, 2:])
+        assert np.max(np.abs(strokes[i, :, :2] - ref[:, :2])) < 1e-3 * cfg.data_scale
+    h.close()
+
+
+def test_sampler_philox_seeded_mode_runs_and_is_deterministic():
+    cfg = so.Config(model="lstm", rnn_size=32, num_layers=2, num_mixture=6)
+    params = so.init_params(cfg, seed=11, trained_like=True)
+    h = make_handle(cfg, params)
+    a, la, _ = h.sample(9, 20, 0.5, 0.5, False, seed=42)
+    b, lb, _ = h.sample(9, 20, 0.5, 0.5, False, seed=42)
+    c, _, _ = h.sample(9, 20, 0.5, 0.5, False, seed=43)
+    assert np.array_equal(a.cpu().numpy(), b.cpu().numpy())
+    assert not np.array_equal(a.cpu().numpy(), c.cpu().numpy())
+    # sharding invariance: sketches 4..8 drawn as their own call with sketch0=4
+    d, _, _ = h.sample(5, 20, 0.5, 0.5, False, seed=42, sketch0=4)
+    assert np.array_equal(a.cpu().numpy()[4:], d.cpu().numpy())
+    h.close()
+
+
+def test_errors_are_reported_not_thrown():
+    from sketch_rnn_b200 import _lib
+    with pytest.raises(Exception, match="model type not supported"):
+        _lib.Handle(model="transformer")
+    with pytest.raises(_lib.SkrnnError, match="multiple of 8"):
+        _lib.Handle(model="lstm", rnn_size=30)
+    h = _lib.Handle(model="lstm", rnn_size=16, num_layers=2, num_mixture=3)
+    with pytest.raises(_lib.SkrnnError, match="expected"):
+        h.set_params(np.zeros(5, dtype=np.float32))
+    h.close()
