@@ -158,6 +158,15 @@ SKRNN_API int64_t skrnn_launch_count(const skrnn_handle *h);
 SKRNN_API int skrnn_profile_enable(skrnn_handle *h, int32_t on);
 SKRNN_API int skrnn_profile_read(skrnn_handle *h, double *ms_out, int64_t *count_out);
 
+/* Diagnostic (no reference counterpart): runs the bf16 tcgen05/TMA GEMM building block on caller
+ * buffers so tests can check it against a library matmul.  C[M,N] (+)= A*B (+bias), A/B bf16 device
+ * matrices, *_kmajor != 0: K contiguous ([M][lda] resp. [N][ldb]); == 0: M resp. N contiguous
+ * ([K][lda] resp. [K][ldb]).  overrides: NULL, or six descriptor strides for bring-up sweeps. */
+SKRNN_API int skrnn_debug_gemm_bf16(skrnn_handle *h, int32_t M, int32_t N, int32_t K, const void *a_dev,
+                          int32_t lda, int32_t a_kmajor, const void *b_dev, int32_t ldb, int32_t b_kmajor,
+                          float *c_dev, int32_t ldc, const float *bias_dev, int32_t accumulate,
+                          const uint32_t *overrides, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -52,6 +52,8 @@ SYMBOLS = {
     "skrnn_sample": (C.c_int, [_P, C.c_int32, C.c_int32, C.c_float, C.c_float, C.c_int32, _P, C.c_uint64,
                                C.c_int32, _P, _P, _P, _P]),
     "skrnn_launch_count": (C.c_int64, [_P]),
+    "skrnn_debug_gemm_bf16": (C.c_int, [_P, C.c_int32, C.c_int32, C.c_int32, _P, C.c_int32, C.c_int32, _P, C.c_int32,
+                                        C.c_int32, _P, C.c_int32, _P, C.c_int32, _P, _P]),
     "skrnn_profile_enable": (C.c_int, [_P, C.c_int32]),
     "skrnn_profile_read": (C.c_int, [_P, C.POINTER(C.c_double), C.POINTER(C.c_int64)]),
 }
@@ -230,6 +232,21 @@ class Handle(object):
                                     strokes.data_ptr(), lengths.data_ptr(),
                                     mixp.data_ptr() if want_params else None, _stream_ptr(stream)))
         return strokes, lengths, mixp
+
+    def debug_gemm_bf16(self, a, a_kmajor, b, b_kmajor, M, N, K, bias=None, accumulate=False, c=None,
+                        overrides=None):
+        """C[M,N] (+)= A*B through the tcgen05 GEMM.  a, b: 2-D torch bf16 CUDA tensors in their
+        storage layout ([M,K] or [K,M] resp. [N,K] or [K,N])."""
+        import torch
+        assert a.dtype == torch.bfloat16 and b.dtype == torch.bfloat16
+        if c is None:
+            c = torch.zeros((M, N), dtype=torch.float32, device=a.device)
+        ov = (C.c_uint32 * 6)(*overrides) if overrides is not None else None
+        check(self.lib.skrnn_debug_gemm_bf16(self._h, M, N, K, a.data_ptr(), a.stride(0), 1 if a_kmajor else 0,
+                                             b.data_ptr(), b.stride(0), 1 if b_kmajor else 0, c.data_ptr(),
+                                             c.stride(0), bias.data_ptr() if bias is not None else None,
+                                             1 if accumulate else 0, ov, _stream_ptr(None)))
+        return c
 
     def launch_count(self):
         return int(self.lib.skrnn_launch_count(self._h))

@@ -287,6 +287,19 @@ float *skrnn_params_dev(skrnn_handle *h) { return h ? h->params : nullptr; }
 float *skrnn_grads_dev(skrnn_handle *h) { return h ? h->grads : nullptr; }
 int64_t skrnn_launch_count(const skrnn_handle *h) { return h ? h->launches : -1; }
 
+int skrnn_debug_gemm_bf16(skrnn_handle *h, int32_t M, int32_t N, int32_t K, const void *a_dev, int32_t lda,
+                          int32_t a_kmajor, const void *b_dev, int32_t ldb, int32_t b_kmajor, float *c_dev,
+                          int32_t ldc, const float *bias_dev, int32_t accumulate, const uint32_t *overrides,
+                          void *stream) {
+  SK_CHECK(h && a_dev && b_dev && c_dev, "debug_gemm: null argument");
+  SK_CUDA(cudaSetDevice(h->cfg.device));
+  for (int i = 0; i < 6; ++i) g_tc_override[i] = overrides ? overrides[i] : 0;
+  int rc = sk_gemm_tc(h, (cudaStream_t)stream, M, N, K, a_dev, lda, a_kmajor != 0, b_dev, ldb, b_kmajor != 0,
+                      c_dev, ldc, bias_dev, accumulate != 0);
+  for (int i = 0; i < 6; ++i) g_tc_override[i] = 0;
+  return rc;
+}
+
 int skrnn_profile_enable(skrnn_handle *h, int32_t on) {
   SK_CHECK(h != nullptr, "null handle");
   h->prof_on = on != 0;

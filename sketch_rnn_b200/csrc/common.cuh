@@ -117,6 +117,10 @@ struct SkLaunch {
 int sk_gemm_f32(skrnn_handle *h, cudaStream_t st, int M, int N, int K, const float *A, int lda,
                 bool a_kcontig, const float *B, int ldb, bool b_ncontig, float *C, int ldc,
                 const float *bias, bool accumulate);
+// bf16 tensor-core GEMM (gemm_tc.cu): operands bf16, K-major (K contiguous) or MN-major.
+int sk_gemm_tc(skrnn_handle *h, cudaStream_t st, int M, int N, int K, const void *A, int lda, bool a_kmajor,
+               const void *B, int ldb, bool b_kmajor, float *C, int ldc, const float *bias, bool accumulate);
+extern uint32_t g_tc_override[6];
 int sk_colsum(skrnn_handle *h, cudaStream_t st, const float *A, int64_t rows, int cols, int lda,
               float *out);  // out[c] += sum_r A[r][c]
 

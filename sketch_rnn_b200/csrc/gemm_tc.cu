@@ -1,0 +1,295 @@
+// gemm_tc.cu -- bf16 tensor-core GEMM for sm_100a: TMA (cp.async.bulk.tensor) feeds a 3-stage
+// shared-memory ring, one elected thread issues tcgen05.mma with the fp32 accumulator in TMEM, four
+// epilogue warps read it back with tcgen05.ld.  Used by the bf16 path for the hoisted products of
+// the cell stack (reference model.py:77 via TF _linear: X_l * Wx for all timesteps at once), the
+// output projection (model.py:98-99) and every weight / input gradient of model.py:182.
+//
+//   C[M,N] (+)= A[M,K] * B[K,N] (+ bias[N]),   A, B bf16, C fp32
+//
+// Either operand may be K-major (K contiguous in memory) or MN-major (M resp. N contiguous); both
+// are loaded with 128-byte-swizzled TMA boxes and described to the tensor core with the matching
+// canonical shared-memory descriptor, so X^T * dY (both operands MN-major, K = B*T rows) needs no
+// transposed copy.  Split-K over blockIdx.z with an atomic fp32 epilogue serves the tall-skinny
+// weight-gradient products.
+#include <cuda.h>
+#include <cuda_bf16.h>
+
+#include "common.cuh"
+
+namespace {
+
+constexpr int BM = 128, BN = 128, BK = 64;
+constexpr int STAGES = 3;
+constexpr int A_BYTES = BM * BK * 2, B_BYTES = BN * BK * 2;
+constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+constexpr int TC_THREADS = 192;  // warp 0: TMA, warp 1: MMA + TMEM alloc, warps 2-5: epilogue
+constexpr int TC_SMEM = STAGES * STAGE_BYTES + 1024 /*align*/ + 256 /*barriers*/;
+
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+  uint32_t done;
+  do {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+        "selp.u32 %0, 1, 0, p;\n"
+        "}\n" : "=r"(done) : "r"(bar), "r"(parity) : "memory");
+  } while (!done);
+}
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap *map, uint32_t bar, int c0, int c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+      ::"r"(dst), "l"(reinterpret_cast<uint64_t>(map)), "r"(bar), "r"(c0), "r"(c1) : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_commit(uint32_t bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void tc_mma_bf16(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
+                                            uint32_t accumulate) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "setp.ne.b32 p, %4, 0;\n"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n"
+      "}\n" ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void tc_ld32(uint32_t taddr, uint32_t *r) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+        "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]),
+        "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]),
+        "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+      : "r"(taddr));
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
+// Shared-memory matrix descriptor (PTX ISA "tcgen05 shared memory descriptor"): start address,
+// leading / stride byte offsets in 16-byte units, version 1, 128-byte swizzle.
+__device__ __forceinline__ uint64_t make_desc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+  uint64_t d = 0;
+  d |= (uint64_t)((saddr >> 4) & 0x3fff);
+  d |= (uint64_t)((lbo_bytes >> 4) & 0x3fff) << 16;
+  d |= (uint64_t)((sbo_bytes >> 4) & 0x3fff) << 32;
+  d |= (uint64_t)1 << 46;  // descriptor version (Blackwell)
+  d |= (uint64_t)2 << 61;  // SWIZZLE_128B
+  return d;
+}
+
+struct TcArgs {
+  int M, N, K;
+  float *C;
+  int ldc;
+  const float *bias;
+  int accumulate;
+  int kb_per_split;
+  uint32_t lbo_a, sbo_a, adv_a, lbo_b, sbo_b, adv_b;  // descriptor strides / per-UMMA_K advance (bytes)
+};
+
+template <bool A_KMAJOR, bool B_KMAJOR>
+__global__ void __launch_bounds__(TC_THREADS, 2)
+gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, TcArgs a) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const uint32_t bars = base + STAGES * STAGE_BYTES;  // full[S], empty[S], tmem_full, tmem holder
+  const uint32_t bar_full = bars, bar_empty = bars + 8 * STAGES, bar_tmem = bars + 16 * STAGES;
+  const uint32_t tmem_holder = bars + 16 * STAGES + 8;
+  uint8_t *gen_base = smem_raw + (base - smem_u32(smem_raw));
+  volatile uint32_t *tmem_holder_ptr = reinterpret_cast<volatile uint32_t *>(gen_base + STAGES * STAGE_BYTES + 16 * STAGES + 8);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int m0 = blockIdx.y * BM, n0 = blockIdx.x * BN;
+  const int nkb_total = (a.K + BK - 1) / BK;
+  const int kb_beg = blockIdx.z * a.kb_per_split;
+  const int kb_end = min(nkb_total, kb_beg + a.kb_per_split);
+  const int nkb = kb_end - kb_beg;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < STAGES; ++s) { mbar_init(bar_full + 8 * s, 1); mbar_init(bar_empty + 8 * s, 1); }
+    mbar_init(bar_tmem, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmA)) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmB)) : "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_holder), "r"(BN) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_acc = *tmem_holder_ptr;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      for (int i = 0; i < nkb; ++i) {
+        const int s = i % STAGES, ph = (i / STAGES) & 1;
+        mbar_wait(bar_empty + 8 * s, ph ^ 1);
+        const uint32_t sa = base + s * STAGE_BYTES, sb = sa + A_BYTES;
+        mbar_expect_tx(bar_full + 8 * s, STAGE_BYTES);
+        const int k0 = (kb_beg + i) * BK;
+        if (A_KMAJOR) {
+          tma_load_2d(sa, &tmA, bar_full + 8 * s, k0, m0);
+        } else {
+          tma_load_2d(sa, &tmA, bar_full + 8 * s, m0, k0);
+          tma_load_2d(sa + A_BYTES / 2, &tmA, bar_full + 8 * s, m0 + 64, k0);
+        }
+        if (B_KMAJOR) {
+          tma_load_2d(sb, &tmB, bar_full + 8 * s, k0, n0);
+        } else {
+          tma_load_2d(sb, &tmB, bar_full + 8 * s, n0, k0);
+          tma_load_2d(sb + B_BYTES / 2, &tmB, bar_full + 8 * s, n0 + 64, k0);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      // instruction descriptor: D fp32, A/B bf16, majors, N>>3, M>>4
+      const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((A_KMAJOR ? 0u : 1u) << 15) |
+                             ((B_KMAJOR ? 0u : 1u) << 16) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+      for (int i = 0; i < nkb; ++i) {
+        const int s = i % STAGES, ph = (i / STAGES) & 1;
+        mbar_wait(bar_full + 8 * s, ph);
+        tc_fence_after();
+        const uint32_t sa = base + s * STAGE_BYTES, sb = sa + A_BYTES;
+        const uint64_t da = make_desc(sa, a.lbo_a, a.sbo_a), db = make_desc(sb, a.lbo_b, a.sbo_b);
+#pragma unroll
+        for (int k = 0; k < BK / 16; ++k) {
+          tc_mma_bf16(tmem_acc, da + (uint64_t)((a.adv_a * k) >> 4), db + (uint64_t)((a.adv_b * k) >> 4), idesc,
+                      (i > 0 || k > 0) ? 1u : 0u);
+        }
+        tc_commit(bar_empty + 8 * s);  // frees the smem slot once these MMAs have read it
+      }
+      tc_commit(bar_tmem);  // accumulator complete
+    }
+  } else {
+    // epilogue: warp w may touch TMEM lanes [32*(w%4), +32)
+    const int q = warp & 3;
+    const int m = m0 + 32 * q + lane;
+    if (nkb > 0) {
+      mbar_wait(bar_tmem, 0);
+      tc_fence_after();
+#pragma unroll 1
+      for (int c = 0; c < BN / 32; ++c) {
+        uint32_t r[32];
+        tc_ld32(tmem_acc + ((uint32_t)(32 * q) << 16) + (uint32_t)(c * 32), r);
+        if (m < a.M) {
+          float *dst = a.C + (size_t)m * a.ldc + n0 + c * 32;
+          const bool add_bias = a.bias != nullptr && blockIdx.z == 0;
+#pragma unroll
+          for (int j = 0; j < 32; ++j) {
+            const int n = n0 + c * 32 + j;
+            if (n < a.N) {
+              float v = __uint_as_float(r[j]);
+              if (add_bias) v += __ldg(a.bias + n);
+              if (a.accumulate) atomicAdd(dst + j, v);
+              else dst[j] = v;
+            }
+          }
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_acc), "r"(BN) : "memory");
+  }
+}
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
+                                  const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn get_encode() {
+  static EncodeTiledFn fn = nullptr;
+  if (fn) return fn;
+  void *p = nullptr;
+  cudaDriverEntryPointQueryResult q;
+  if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess || p == nullptr)
+    return nullptr;
+  fn = reinterpret_cast<EncodeTiledFn>(p);
+  return fn;
+}
+
+// 2-D bf16 tensor map: `inner` contiguous elements per row, `outer` rows of `ld` elements.
+int make_map(CUtensorMap *m, const void *ptr, int64_t inner, int64_t outer, int64_t ld, int box_inner, int box_outer) {
+  EncodeTiledFn enc = get_encode();
+  SK_CHECK(enc != nullptr, "cuTensorMapEncodeTiled is not available from the driver");
+  SK_CHECK((reinterpret_cast<uintptr_t>(ptr) & 15) == 0 && (ld * 2) % 16 == 0,
+           "TMA operand must be 16-byte aligned with a row pitch that is a multiple of 8 bf16 (ld=%lld)", (long long)ld);
+  cuuint64_t gdim[2] = {(cuuint64_t)inner, (cuuint64_t)outer};
+  cuuint64_t gstr[1] = {(cuuint64_t)ld * 2};
+  cuuint32_t box[2] = {(cuuint32_t)box_inner, (cuuint32_t)box_outer};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void *>(ptr), gdim, gstr, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  SK_CHECK(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed with %d (inner %lld outer %lld ld %lld)", (int)r,
+           (long long)inner, (long long)outer, (long long)ld);
+  return 0;
+}
+
+}  // namespace
+
+// Debug knobs for bring-up (descriptor stride sweep from the tests); 0 = use the defaults.
+uint32_t g_tc_override[6] = {0, 0, 0, 0, 0, 0};
+
+int sk_gemm_tc(skrnn_handle *h, cudaStream_t st, int M, int N, int K, const void *A, int lda, bool a_kmajor,
+               const void *B, int ldb, bool b_kmajor, float *C, int ldc, const float *bias, bool accumulate) {
+  if (M <= 0 || N <= 0 || K <= 0) return 0;
+  CUtensorMap tmA, tmB;
+  if (a_kmajor) SK_TRY(make_map(&tmA, A, K, M, lda, BK, BM));
+  else SK_TRY(make_map(&tmA, A, M, K, lda, 64, BK));
+  if (b_kmajor) SK_TRY(make_map(&tmB, B, K, N, ldb, BK, BN));
+  else SK_TRY(make_map(&tmB, B, N, K, ldb, 64, BK));
+  TcArgs a;
+  a.M = M; a.N = N; a.K = K; a.C = C; a.ldc = ldc; a.bias = bias; a.accumulate = accumulate ? 1 : 0;
+  // K-major SW128: rows of 128 B, 8-row groups 1024 B apart; next UMMA_K (16 el) is +32 B.
+  // MN-major SW128: 64-element MN chunks 8192 B apart (LBO), 8-k-row groups 1024 B apart (SBO);
+  // next UMMA_K is two groups = +2048 B.
+  a.lbo_a = a_kmajor ? 0 : 8192; a.sbo_a = 1024; a.adv_a = a_kmajor ? 32 : 2048;
+  a.lbo_b = b_kmajor ? 0 : 8192; a.sbo_b = 1024; a.adv_b = b_kmajor ? 32 : 2048;
+  if (g_tc_override[0]) a.lbo_a = g_tc_override[0];
+  if (g_tc_override[1]) a.sbo_a = g_tc_override[1];
+  if (g_tc_override[2]) a.adv_a = g_tc_override[2];
+  if (g_tc_override[3]) a.lbo_b = g_tc_override[3];
+  if (g_tc_override[4]) a.sbo_b = g_tc_override[4];
+  if (g_tc_override[5]) a.adv_b = g_tc_override[5];
+  const int gx = (N + BN - 1) / BN, gy = (M + BM - 1) / BM;
+  const int nkb = (K + BK - 1) / BK;
+  int nsplit = 1;
+  if (accumulate) {
+    int tiles = gx * gy;
+    int want = (2 * h->num_sms + tiles - 1) / tiles;
+    nsplit = std::max(1, std::min(want, (nkb + 7) / 8));
+  }
+  a.kb_per_split = (nkb + nsplit - 1) / nsplit;
+  nsplit = (nkb + a.kb_per_split - 1) / a.kb_per_split;
+  dim3 grid(gx, gy, nsplit);
+  SkLaunch scope(h, st, SK_CAT_TC_GEMM);
+#define SK_TC_LAUNCH(AK, BKM)                                                                                  \
+  do {                                                                                                         \
+    SK_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<AK, BKM>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM)); \
+    gemm_tc_kernel<AK, BKM><<<grid, TC_THREADS, TC_SMEM, st>>>(tmA, tmB, a);                                   \
+  } while (0)
+  if (a_kmajor && b_kmajor) SK_TC_LAUNCH(true, true);
+  else if (a_kmajor && !b_kmajor) SK_TC_LAUNCH(true, false);
+  else if (!a_kmajor && b_kmajor) SK_TC_LAUNCH(false, true);
+  else SK_TC_LAUNCH(false, false);
+#undef SK_TC_LAUNCH
+  SK_CUDA(cudaGetLastError());
+  return 0;
+}
