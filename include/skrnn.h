@@ -158,6 +158,30 @@ SKRNN_API int64_t skrnn_launch_count(const skrnn_handle *h);
 SKRNN_API int skrnn_profile_enable(skrnn_handle *h, int32_t on);
 SKRNN_API int skrnn_profile_read(skrnn_handle *h, double *ms_out, int64_t *count_out);
 
+/* No counterpart in the reference.  The clip + Adam update of skrnn_apply_clip_adam for callers
+ * that hold the buffers themselves and cannot let this library allocate device memory: a trainer
+ * whose parameters, gradients and Adam slots sit in a framework-managed pool (the pool usually
+ * owns the whole GPU already, so a cudaMalloc issued from here would fail or fragment it), or any
+ * context in which allocating is not permitted.  Creating a handle is not an option for them --
+ * skrnn_create allocates weights, slots and workspaces.
+ *   n                 number of float32 parameters, 1 .. SKRNN_NOALLOC_MAX_PARAMS; more is an error
+ *   grads_dev         [n] in;  params_dev, m_dev, v_dev  [n] in/out (updated in place)
+ *   lr, grad_clip     learning rate and clip norm (model.py:182-183)
+ *   beta1_power, beta2_power   0.9^t and 0.999^t for this step t >= 1 (the caller advances them)
+ *   gnorm_out_dev     [1] global norm before clipping, or NULL
+ * Its only scratch memory is a fixed array of SKRNN_NOALLOC_SCRATCH_BYTES inside the library image
+ * (one copy per GPU that loads the library, held until exit).  The call performs no cudaMalloc,
+ * cudaFree or allocating library call.  Every call on a device shares that array and it keeps the
+ * previous call's contents; what must start at zero is cleared on `stream` at the start of each
+ * call.  Calls that overlap on the GPU race on it: keep them on one stream or otherwise serialise
+ * them.  The first call on a device resolves the array's device address and queries the device;
+ * issue that first call before beginning any stream capture. */
+#define SKRNN_NOALLOC_MAX_PARAMS (8192LL * 4096LL)
+#define SKRNN_NOALLOC_SCRATCH_BYTES (256 + 8192 * 8)
+SKRNN_API int skrnn_clip_adam_noalloc(int64_t n, const float *grads_dev, float *params_dev, float *m_dev,
+                            float *v_dev, float lr, float grad_clip, double beta1_power,
+                            double beta2_power, float *gnorm_out_dev, void *stream);
+
 /* Diagnostic (no reference counterpart): runs the bf16 tcgen05/TMA GEMM building block on caller
  * buffers so tests can check it against a library matmul.  C[M,N] (+)= A*B (+bias), A/B bf16 device
  * matrices, *_kmajor != 0: K contiguous ([M][lda] resp. [N][ldb]); == 0: M resp. N contiguous

@@ -52,6 +52,8 @@ SYMBOLS = {
     "skrnn_sample": (C.c_int, [_P, C.c_int32, C.c_int32, C.c_float, C.c_float, C.c_int32, _P, C.c_uint64,
                                C.c_int32, _P, _P, _P, _P]),
     "skrnn_launch_count": (C.c_int64, [_P]),
+    "skrnn_clip_adam_noalloc": (C.c_int, [C.c_int64, _P, _P, _P, _P, C.c_float, C.c_float, C.c_double, C.c_double,
+                                          _P, _P]),
     "skrnn_debug_gemm_bf16": (C.c_int, [_P, C.c_int32, C.c_int32, C.c_int32, _P, C.c_int32, C.c_int32, _P, C.c_int32,
                                         C.c_int32, _P, C.c_int32, _P, C.c_int32, _P, _P]),
     "skrnn_profile_enable": (C.c_int, [_P, C.c_int32]),
@@ -262,6 +264,23 @@ class Handle(object):
         cnt = (C.c_int64 * 8)()
         check(self.lib.skrnn_profile_read(self._h, ms, cnt))
         return {n: (ms[i], int(cnt[i])) for i, n in enumerate(self.PROFILE_CATEGORIES)}
+
+
+NOALLOC_MAX_PARAMS = 8192 * 4096
+
+
+def clip_adam_noalloc(grads, params, m, v, lr, grad_clip, beta1_power, beta2_power, gnorm_out=None, stream=None):
+    """Clip + Adam on caller-owned torch CUDA float32 tensors, updated in place, without any device
+    allocation inside the library (skrnn_clip_adam_noalloc).  For callers whose tensors come from a
+    framework pool and who cannot create a Handle (that would cudaMalloc).  At most NOALLOC_MAX_PARAMS
+    elements; calls on one device must not overlap (shared fixed scratch)."""
+    n = grads.numel()
+    for t in (grads, params, m, v):
+        assert t.is_cuda and t.is_contiguous() and t.numel() == n and str(t.dtype) == "torch.float32"
+    check(load().skrnn_clip_adam_noalloc(n, grads.data_ptr(), params.data_ptr(), m.data_ptr(), v.data_ptr(),
+                                         lr, grad_clip, beta1_power, beta2_power,
+                                         gnorm_out.data_ptr() if gnorm_out is not None else None,
+                                         _stream_ptr(stream)))
 
 
 def _dev(a, device):
