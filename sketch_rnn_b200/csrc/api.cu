@@ -70,6 +70,16 @@ void free_workspace(SkWorkspace &w) {
   cudaFree(w.dout);
   cudaFree(w.logits);
   w.x_tm = w.dout = w.logits = nullptr;
+  cudaFree(w.x8_bf);
+  cudaFree(w.dpre_bf);
+  cudaFree(w.dlogits_bf);
+  w.x8_bf = w.dpre_bf = w.dlogits_bf = nullptr;
+  for (int l = 0; l < SK_MAX_LAYERS; ++l) {
+    cudaFree(w.out_bf[l]);
+    cudaFree(w.hprev_bf[l]);
+    cudaFree(w.aux_bf[l]);
+    w.out_bf[l] = w.hprev_bf[l] = w.aux_bf[l] = nullptr;
+  }
   w.cap_rows = 0;
 }
 
@@ -88,6 +98,19 @@ int ensure_workspace(skrnn_handle *h, int B, int T) {
   }
   SK_CUDA(cudaMalloc(&w.dout, rows * h->H * sizeof(float)));
   SK_CUDA(cudaMalloc(&w.logits, rows * h->NOUT * sizeof(float)));
+  if (h->cfg.precision == SKRNN_PREC_BF16) {
+    const size_t e = sizeof(__nv_bfloat16);
+    SK_CUDA(cudaMalloc(&w.x8_bf, rows * 8 * e));
+    SK_CUDA(cudaMemset(w.x8_bf, 0, rows * 8 * e));
+    SK_CUDA(cudaMalloc(&w.dpre_bf, rows * h->G * e));
+    SK_CUDA(cudaMalloc(&w.dlogits_bf, rows * h->NOUTP * e));
+    SK_CUDA(cudaMemset(w.dlogits_bf, 0, rows * h->NOUTP * e));
+    for (int l = 0; l < h->L; ++l) {
+      SK_CUDA(cudaMalloc(&w.out_bf[l], rows * h->H * e));
+      SK_CUDA(cudaMalloc(&w.hprev_bf[l], rows * h->H * e));
+      if (h->cfg.cell == SKRNN_CELL_GRU) SK_CUDA(cudaMalloc(&w.aux_bf[l], rows * h->H * e));
+    }
+  }
   w.cap_rows = rows;
   return 0;
 }
@@ -99,29 +122,61 @@ int check_shape(skrnn_handle *h, int B, int T) {
   return ensure_workspace(h, B, T);
 }
 
+// A GEMM operand in both precisions: the fp32 buffer and (bf16 mode) its bf16 mirror.
+struct Op {
+  const float *f;
+  int ldf;
+  const __nv_bfloat16 *b;
+  int ldb;
+};
+Op col_offset(Op o, int c) { return Op{o.f + c, o.ldf, o.b ? o.b + c : nullptr, o.ldb}; }
+Op layer_input(skrnn_handle *h, int l) {
+  if (l == 0) return Op{h->ws.x_tm, 5, h->ws.x8_bf, 8};
+  return Op{h->ws.out[l - 1], h->H, h->ws.out_bf[l - 1], h->H};
+}
+Op weight(skrnn_handle *h, int l, int which) {
+  const int nc = h->lp[l].ncol[which];
+  return Op{h->params + h->lp[l].w[which], nc, h->params_bf ? h->params_bf + h->pbf_w[l][which] : nullptr, nc};
+}
+Op out_weight(skrnn_handle *h) {
+  return Op{h->params + h->off_out_w, h->NOUT, h->params_bf ? h->params_bf + h->pbf_out_w : nullptr, h->NOUTP};
+}
+Op top_output(skrnn_handle *h) { return Op{h->ws.out[h->L - 1], h->H, h->ws.out_bf[h->L - 1], h->H}; }
+Op hprev_op(skrnn_handle *h, int l) { return Op{h->ws.hprev[l], h->H, h->ws.hprev_bf[l], h->H}; }
+Op aux_op(skrnn_handle *h, int l) { return Op{h->ws.cprev[l], h->H, h->ws.aux_bf[l], h->H}; }
+Op dpre_op(skrnn_handle *h, int l) { return Op{h->ws.xw[l], h->G, h->ws.dpre_bf, h->G}; }
+Op dlogits_op(skrnn_handle *h) { return Op{h->ws.logits, h->NOUT, h->ws.dlogits_bf, h->NOUTP}; }
+
+// C[M,N] (+)= A*B (+bias).  a_kc: A stored [M][ld] (K contiguous) else [K][ld]; b_nc: B stored [K][ld]
+// (N contiguous) else [N][ld].  fp32 path: CUDA-core GEMM; bf16 path: tcgen05/TMA GEMM.
+int gemm(skrnn_handle *h, cudaStream_t st, int M, int N, int K, Op A, bool a_kc, Op B, bool b_nc, float *C,
+         int ldc, const float *bias, bool accumulate) {
+  if (h->cfg.precision == SKRNN_PREC_BF16)
+    return sk_gemm_tc(h, st, M, N, K, A.b, A.ldb, a_kc, B.b, B.ldb, !b_nc, C, ldc, bias, accumulate);
+  return sk_gemm_f32(h, st, M, N, K, A.f, A.ldf, a_kc, B.f, B.ldf, b_nc, C, ldc, bias, accumulate);
+}
+
 // forward unroll of the whole stack + output projection (model.py:97-99)
 int run_forward(skrnn_handle *h, cudaStream_t st, int B, int T, const float *x, const float *state_in,
                 float *state_out, const float *mask, uint64_t seed, int row0, bool training) {
   const int H = h->H, G = h->G;
   const int64_t R = (int64_t)B * T;
+  SK_TRY(sk_cast_params(h, st));
   SK_TRY(sk_transpose_x(h, st, B, T, x));
   for (int l = 0; l < h->L; ++l) {
     const SkLayerParams &lp = h->lp[l];
-    const float *X = (l == 0) ? h->ws.x_tm : h->ws.out[l - 1];
+    const Op Xo = layer_input(h, l);
     if (h->cfg.cell == SKRNN_CELL_GRU) {
-      SK_TRY(sk_gemm_f32(h, st, (int)R, 2 * H, lp.I, X, lp.I, true, h->params + lp.w[0], 2 * H, true,
-                         h->ws.xw[l], G, h->params + lp.b[0], false));
-      SK_TRY(sk_gemm_f32(h, st, (int)R, H, lp.I, X, lp.I, true, h->params + lp.w[1], H, true,
-                         h->ws.xw[l] + 2 * H, G, h->params + lp.b[1], false));
+      SK_TRY(gemm(h, st, (int)R, 2 * H, lp.I, Xo, true, weight(h, l, 0), true, h->ws.xw[l], G, h->params + lp.b[0], false));
+      SK_TRY(gemm(h, st, (int)R, H, lp.I, Xo, true, weight(h, l, 1), true, h->ws.xw[l] + 2 * H, G, h->params + lp.b[1], false));
     } else {
-      SK_TRY(sk_gemm_f32(h, st, (int)R, G, lp.I, X, lp.I, true, h->params + lp.w[0], G, true, h->ws.xw[l],
-                         G, h->params + lp.b[0], false));
+      SK_TRY(gemm(h, st, (int)R, G, lp.I, Xo, true, weight(h, l, 0), true, h->ws.xw[l], G, h->params + lp.b[0], false));
     }
     SK_TRY(sk_rnn_forward_layer(h, st, l, B, T, x, state_in + (size_t)l * B * h->S,
                                 state_out + (size_t)l * B * h->S, mask, seed, row0, training));
   }
-  SK_TRY(sk_gemm_f32(h, st, (int)R, h->NOUT, H, h->ws.out[h->L - 1], H, true, h->params + h->off_out_w,
-                     h->NOUT, true, h->ws.logits, h->NOUT, h->params + h->off_out_b, false));
+  SK_TRY(gemm(h, st, (int)R, h->NOUT, H, top_output(h), true, out_weight(h), true, h->ws.logits, h->NOUT,
+              h->params + h->off_out_b, false));
   return 0;
 }
 
@@ -184,6 +239,30 @@ int skrnn_create(const skrnn_config *cfg, skrnn_handle **out) {
   cudaMemset(h->adam_v, 0, pb);
   cudaMemset(h->scal, 0, 8 * sizeof(double));
   cudaMemset(h->sync_ctr, 0, 4 * sizeof(unsigned int));
+  h->NOUTP = (h->NOUT + 7) / 8 * 8;
+  if (cfg->precision == SKRNN_PREC_BF16) {
+    // bf16 weight mirror: every tensor starts on a 16-byte boundary; output_w rows padded to NOUTP
+    std::vector<int64_t> seg;
+    int64_t o = 0;
+    auto add = [&](int64_t src, int rows, int cols, int ldd, int64_t *dst) {
+      *dst = o;
+      seg.insert(seg.end(), {src, o, (int64_t)rows * cols, (int64_t)cols, (int64_t)ldd});
+      o += ((int64_t)rows * ldd + 7) / 8 * 8;
+    };
+    add(h->off_out_w, h->H, h->NOUT, h->NOUTP, &h->pbf_out_w);
+    for (int l = 0; l < h->L; ++l)
+      for (int w = 0; w < (cfg->cell == SKRNN_CELL_GRU ? 2 : 1); ++w)
+        add(h->lp[l].w[w], h->lp[l].I + h->H, h->lp[l].ncol[w], h->lp[l].ncol[w], &h->pbf_w[l][w]);
+    h->pbf_count = o;
+    h->cast_nseg = (int)(seg.size() / 5);
+    if (cudaMalloc(&h->params_bf, o * sizeof(__nv_bfloat16)) != cudaSuccess ||
+        cudaMalloc(&h->cast_seg_dev, seg.size() * sizeof(int64_t)) != cudaSuccess) {
+      sk_set_error("skrnn_create: cudaMalloc of the bf16 weight mirror failed");
+      return fail();
+    }
+    cudaMemset(h->params_bf, 0, o * sizeof(__nv_bfloat16));
+    cudaMemcpy(h->cast_seg_dev, seg.data(), seg.size() * sizeof(int64_t), cudaMemcpyHostToDevice);
+  }
   h->ws.wpack_floats = (int64_t)h->cluster_size * h->H * 256;
   if (cudaMalloc(&h->ws.wpack, h->ws.wpack_floats * sizeof(float)) != cudaSuccess) {
     sk_set_error("skrnn_create: cudaMalloc of weight pack failed");
@@ -216,6 +295,8 @@ void skrnn_destroy(skrnn_handle *h) {
   cudaFree(h->st_state);
   cudaFree(h->st_loss);
   cudaFree(h->samp_state);
+  cudaFree(h->params_bf);
+  cudaFree(h->cast_seg_dev);
   cudaFreeHost(h->pin_x);
   cudaFreeHost(h->pin_y);
   cudaFreeHost(h->pin_state);
@@ -325,7 +406,6 @@ int skrnn_forward(skrnn_handle *h, int32_t B, int32_t T, const float *x_dev, con
                   float *mdn_out_dev, float *state_out_dev, void *stream) {
   SK_TRY(check_shape(h, B, T));
   SK_CHECK(x_dev && state_in_dev && state_out_dev, "forward: null buffer");
-  SK_CHECK(h->cfg.precision == SKRNN_PREC_F32, "precision %d not built yet", h->cfg.precision);
   cudaStream_t st = (cudaStream_t)stream;
   SK_TRY(run_forward(h, st, B, T, x_dev, state_in_dev, state_out_dev, nullptr, 0, 0, false));
   if (mdn_out_dev) {
@@ -341,7 +421,6 @@ int skrnn_loss_grad(skrnn_handle *h, int32_t B, int32_t T, const float *x_dev, c
   SK_TRY(check_shape(h, B, T));
   SK_CHECK(x_dev && y_dev && state_in_dev && state_out_dev && losses_dev, "loss_grad: null buffer");
   SK_CHECK(loss_rows >= (int64_t)B * T, "loss_rows %lld smaller than B*T", (long long)loss_rows);
-  SK_CHECK(h->cfg.precision == SKRNN_PREC_F32, "precision %d not built yet", h->cfg.precision);
   cudaStream_t st = (cudaStream_t)stream;
   const int H = h->H, G = h->G, NOUT = h->NOUT;
   const int R = B * T;
@@ -351,38 +430,34 @@ int skrnn_loss_grad(skrnn_handle *h, int32_t B, int32_t T, const float *x_dev, c
   SK_TRY(sk_head(h, st, B, T, y_dev, nullptr, true, loss_rows));
   SK_TRY(sk_finalize_losses(h, st, losses_dev));
   // head backward: d output_w, d output_b, d(top layer output)
-  const float *top = h->ws.out[h->L - 1];
-  SK_TRY(sk_gemm_f32(h, st, H, NOUT, R, top, H, false, h->ws.logits, NOUT, true, h->grads + h->off_out_w,
-                     NOUT, nullptr, true));
+  SK_TRY(gemm(h, st, H, NOUT, R, top_output(h), false, dlogits_op(h), true, h->grads + h->off_out_w, NOUT, nullptr, true));
   SK_TRY(sk_colsum(h, st, h->ws.logits, R, NOUT, NOUT, h->grads + h->off_out_b));
-  SK_TRY(sk_gemm_f32(h, st, R, H, NOUT, h->ws.logits, NOUT, true, h->params + h->off_out_w, NOUT, false,
-                     h->ws.dout, H, nullptr, false));
+  SK_TRY(gemm(h, st, R, H, NOUT, dlogits_op(h), true, out_weight(h), false, h->ws.dout, H, nullptr, false));
   for (int l = h->L - 1; l >= 0; --l) {
     const SkLayerParams &lp = h->lp[l];
     SK_TRY(sk_rnn_backward_layer(h, st, l, B, T, x_dev, dropout_mask_dev, seed, row0, true));
-    const float *X = (l == 0) ? h->ws.x_tm : h->ws.out[l - 1];
-    const float *dpre = h->ws.xw[l];
+    const Op X = layer_input(h, l);
+    const Op dpre = dpre_op(h, l);
     const int I = lp.I;
     if (h->cfg.cell == SKRNN_CELL_GRU) {
-      const float *dg = dpre, *dc = dpre + 2 * H;
+      const Op dg = dpre, dc = col_offset(dpre, 2 * H);
       float *gWg = h->grads + lp.w[0], *gWc = h->grads + lp.w[1];
-      SK_TRY(sk_gemm_f32(h, st, I, 2 * H, R, X, I, false, dg, G, true, gWg, 2 * H, nullptr, true));
-      SK_TRY(sk_gemm_f32(h, st, H, 2 * H, R, h->ws.hprev[l], H, false, dg, G, true, gWg + (size_t)I * 2 * H, 2 * H, nullptr, true));
-      SK_TRY(sk_colsum(h, st, dg, R, 2 * H, G, h->grads + lp.b[0]));
-      SK_TRY(sk_gemm_f32(h, st, I, H, R, X, I, false, dc, G, true, gWc, H, nullptr, true));
-      SK_TRY(sk_gemm_f32(h, st, H, H, R, h->ws.cprev[l], H, false, dc, G, true, gWc + (size_t)I * H, H, nullptr, true));
-      SK_TRY(sk_colsum(h, st, dc, R, H, G, h->grads + lp.b[1]));
+      SK_TRY(gemm(h, st, I, 2 * H, R, X, false, dg, true, gWg, 2 * H, nullptr, true));
+      SK_TRY(gemm(h, st, H, 2 * H, R, hprev_op(h, l), false, dg, true, gWg + (size_t)I * 2 * H, 2 * H, nullptr, true));
+      SK_TRY(sk_colsum(h, st, dg.f, R, 2 * H, G, h->grads + lp.b[0]));
+      SK_TRY(gemm(h, st, I, H, R, X, false, dc, true, gWc, H, nullptr, true));
+      SK_TRY(gemm(h, st, H, H, R, aux_op(h, l), false, dc, true, gWc + (size_t)I * H, H, nullptr, true));
+      SK_TRY(sk_colsum(h, st, dc.f, R, H, G, h->grads + lp.b[1]));
       if (l > 0) {
-        SK_TRY(sk_gemm_f32(h, st, R, I, 2 * H, dg, G, true, h->params + lp.w[0], 2 * H, false, h->ws.dout, H, nullptr, false));
-        SK_TRY(sk_gemm_f32(h, st, R, I, H, dc, G, true, h->params + lp.w[1], H, false, h->ws.dout, H, nullptr, true));
+        SK_TRY(gemm(h, st, R, I, 2 * H, dg, true, weight(h, l, 0), false, h->ws.dout, H, nullptr, false));
+        SK_TRY(gemm(h, st, R, I, H, dc, true, weight(h, l, 1), false, h->ws.dout, H, nullptr, true));
       }
     } else {
       float *gW = h->grads + lp.w[0];
-      SK_TRY(sk_gemm_f32(h, st, I, G, R, X, I, false, dpre, G, true, gW, G, nullptr, true));
-      SK_TRY(sk_gemm_f32(h, st, H, G, R, h->ws.hprev[l], H, false, dpre, G, true, gW + (size_t)I * G, G, nullptr, true));
-      SK_TRY(sk_colsum(h, st, dpre, R, G, G, h->grads + lp.b[0]));
-      if (l > 0)
-        SK_TRY(sk_gemm_f32(h, st, R, I, G, dpre, G, true, h->params + lp.w[0], G, false, h->ws.dout, H, nullptr, false));
+      SK_TRY(gemm(h, st, I, G, R, X, false, dpre, true, gW, G, nullptr, true));
+      SK_TRY(gemm(h, st, H, G, R, hprev_op(h, l), false, dpre, true, gW + (size_t)I * G, G, nullptr, true));
+      SK_TRY(sk_colsum(h, st, dpre.f, R, G, G, h->grads + lp.b[0]));
+      if (l > 0) SK_TRY(gemm(h, st, R, I, G, dpre, true, weight(h, l, 0), false, h->ws.dout, H, nullptr, false));
     }
   }
   return 0;

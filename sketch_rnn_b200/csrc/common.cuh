@@ -1,6 +1,7 @@
 // common.cuh -- internal declarations shared by the libskrnn translation units.
 #pragma once
 #include <cuda_runtime.h>
+#include <cuda_bf16.h>
 #include <stdint.h>
 #include <stdio.h>
 #include <algorithm>
@@ -61,6 +62,13 @@ struct SkWorkspace {   // time-major activations for one (B, T) capacity
   float *dout = nullptr;                    // [T,B,H]: gradient wrt a layer's output (reused per layer)
   float *logits = nullptr;                  // [T*B,NOUT]: logits -> d(logits)
   float *wpack = nullptr;                   // per-CTA packed recurrent weight slices (fwd or bwd)
+  // bf16 copies feeding the tensor-core GEMMs (precision == SKRNN_PREC_BF16 only)
+  __nv_bfloat16 *x8_bf = nullptr;                    // [T,B,8]: x padded to 8 columns
+  __nv_bfloat16 *out_bf[SK_MAX_LAYERS] = {nullptr};  // [T,B,H]
+  __nv_bfloat16 *hprev_bf[SK_MAX_LAYERS] = {nullptr};
+  __nv_bfloat16 *aux_bf[SK_MAX_LAYERS] = {nullptr};  // gru r*h
+  __nv_bfloat16 *dpre_bf = nullptr;                  // [T,B,G] of the layer being differentiated
+  __nv_bfloat16 *dlogits_bf = nullptr;               // [T*B,NOUTP]
   int64_t wpack_floats = 0;
 };
 
@@ -72,6 +80,14 @@ struct skrnn_handle {
   SkLayerParams lp[SK_MAX_LAYERS];
   int64_t off_out_w, off_out_b;
   float *params = nullptr, *grads = nullptr, *adam_m = nullptr, *adam_v = nullptr;
+  // bf16 mirror of the weights with 16-byte-aligned tensors: per layer the TF matrices as they are
+  // ([I+H, ncol]), and output_w padded to NOUTP columns
+  __nv_bfloat16 *params_bf = nullptr;
+  int64_t pbf_w[SK_MAX_LAYERS][2];
+  int64_t pbf_out_w = 0, pbf_count = 0;
+  int cast_nseg = 0;
+  int64_t *cast_seg_dev = nullptr;  // [nseg][5] = src offset, dst offset, count, cols, dst ld
+  int NOUTP = 0;
   double beta1_power = 0.9, beta2_power = 0.999;
   SkWorkspace ws;
   // small device scratch: [0..2] loss accumulators (double), [3] grad sumsq (double), [4] barrier ctr
@@ -134,6 +150,7 @@ int sk_head(skrnn_handle *h, cudaStream_t st, int B, int T, const float *y_bt5, 
             bool want_grad, int64_t loss_rows);
 int sk_finalize_losses(skrnn_handle *h, cudaStream_t st, float *losses_dev);
 int sk_clip_adam(skrnn_handle *h, cudaStream_t st, float lr, float *gnorm_out);
+int sk_cast_params(skrnn_handle *h, cudaStream_t st);
 int sk_transpose_x(skrnn_handle *h, cudaStream_t st, int B, int T, const float *x_bt5);
 int sk_sample_f32(skrnn_handle *h, cudaStream_t st, int n, int steps, float temp_mix, float temp_pen,
                   int stop_if_eoc, const float *uniforms, uint64_t seed, int sketch0, float *strokes,

@@ -159,14 +159,30 @@ __global__ void colsum_kernel(const float *__restrict__ A, int64_t rows, int col
   }
 }
 
-__global__ void transpose_x_kernel(const float *__restrict__ x, float *__restrict__ x_tm, int B, int T) {
+__global__ void transpose_x_kernel(const float *__restrict__ x, float *__restrict__ x_tm,
+                                   __nv_bfloat16 *__restrict__ x8, int B, int T) {
   int64_t n = (int64_t)B * T * 5;
   for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
     int j = (int)(i % 5);
     int64_t r = i / 5;
     int b = (int)(r % B);
     int t = (int)(r / B);
-    x_tm[i] = x[((int64_t)b * T + t) * 5 + j];
+    float v = x[((int64_t)b * T + t) * 5 + j];
+    x_tm[i] = v;
+    if (x8 != nullptr) x8[r * 8 + j] = __float2bfloat16_rn(v);  // columns 5..7 stay zero from allocation
+  }
+}
+
+// fp32 master weights -> bf16 mirror (16-byte aligned tensors; output_w padded to noutp columns)
+__global__ void cast_params_kernel(const float *__restrict__ p, __nv_bfloat16 *__restrict__ pb, int nseg,
+                                   const int64_t *__restrict__ seg) {
+  // seg[4*s + {0,1,2,3}] = src offset, dst offset, rows*cols (src elements), cols ; dst ld = seg-specific below
+  for (int s = 0; s < nseg; ++s) {
+    const int64_t so = seg[5 * s], dof = seg[5 * s + 1], cnt = seg[5 * s + 2], cols = seg[5 * s + 3], ldd = seg[5 * s + 4];
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < cnt; i += (int64_t)gridDim.x * blockDim.x) {
+      int64_t r = i / cols, c = i % cols;
+      pb[dof + r * ldd + c] = __float2bfloat16_rn(p[so + i]);
+    }
   }
 }
 
@@ -217,7 +233,16 @@ int sk_transpose_x(skrnn_handle *h, cudaStream_t st, int B, int T, const float *
   int64_t n = (int64_t)B * T * 5;
   int blocks = (int)std::min<int64_t>((n + 255) / 256, (int64_t)8 * h->num_sms);
   SkLaunch scope(h, st, SK_CAT_MISC);
-  transpose_x_kernel<<<blocks, 256, 0, st>>>(x_bt5, h->ws.x_tm, B, T);
+  transpose_x_kernel<<<blocks, 256, 0, st>>>(x_bt5, h->ws.x_tm, h->ws.x8_bf, B, T);
+  SK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int sk_cast_params(skrnn_handle *h, cudaStream_t st) {
+  if (h->params_bf == nullptr) return 0;
+  SkLaunch scope(h, st, SK_CAT_MISC);
+  int blocks = (int)std::min<int64_t>((h->P + 255) / 256, (int64_t)4 * h->num_sms);
+  cast_params_kernel<<<blocks, 256, 0, st>>>(h->params, h->params_bf, h->cast_nseg, h->cast_seg_dev);
   SK_CUDA(cudaGetLastError());
   return 0;
 }

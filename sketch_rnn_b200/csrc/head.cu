@@ -25,7 +25,8 @@ __device__ __forceinline__ float warp_sum(float v) {
 // rows are time-major: r = t*B + b.  y is the caller's [B,T,5] target.
 __global__ void __launch_bounds__(256)
 mdn_head_kernel(float *__restrict__ logits, const float *__restrict__ y, float *__restrict__ mdn_out,
-                int B, int T, int M, int want_grad, float inv_rows, float sif, double *__restrict__ scal) {
+                int B, int T, int M, int want_grad, float inv_rows, float sif, double *__restrict__ scal,
+                __nv_bfloat16 *__restrict__ dl_bf, int noutp) {
   const int NOUT = 3 + 6 * M;
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
   const int64_t R = (int64_t)B * T;
@@ -125,21 +126,39 @@ mdn_head_kernel(float *__restrict__ logits, const float *__restrict__ y, float *
           float q = 1.f - rho[j] * rho[j];
           float Z = a * a + bb * bb - 2.f * rho[j] * a * bb;
           float ga = gam * inv_rows;
-          z[3 + k] = ((live ? pi[j] : 0.f) - gam) * inv_rows;
-          z[3 + M + k] = -ga * (a - rho[j] * bb) / (s1[j] * q);
-          z[3 + 2 * M + k] = -ga * (bb - rho[j] * a) / (s2[j] * q);
-          z[3 + 3 * M + k] = -ga * (a * (a - rho[j] * bb) / q - 1.f);
-          z[3 + 4 * M + k] = -ga * (bb * (bb - rho[j] * a) / q - 1.f);
-          z[3 + 5 * M + k] = -ga * (a * bb + rho[j] * (1.f - Z / q));
+          const float g0 = ((live ? pi[j] : 0.f) - gam) * inv_rows;
+          const float g1 = -ga * (a - rho[j] * bb) / (s1[j] * q);
+          const float g2 = -ga * (bb - rho[j] * a) / (s2[j] * q);
+          const float g3 = -ga * (a * (a - rho[j] * bb) / q - 1.f);
+          const float g4 = -ga * (bb * (bb - rho[j] * a) / q - 1.f);
+          const float g5 = -ga * (a * bb + rho[j] * (1.f - Z / q));
+          z[3 + k] = g0;
+          z[3 + M + k] = g1;
+          z[3 + 2 * M + k] = g2;
+          z[3 + 3 * M + k] = g3;
+          z[3 + 4 * M + k] = g4;
+          z[3 + 5 * M + k] = g5;
+          if (dl_bf != nullptr) {
+            __nv_bfloat16 *d = dl_bf + r * noutp + 3 + k;
+            d[0] = __float2bfloat16_rn(g0); d[M] = __float2bfloat16_rn(g1); d[2 * M] = __float2bfloat16_rn(g2);
+            d[3 * M] = __float2bfloat16_rn(g3); d[4 * M] = __float2bfloat16_rn(g4); d[5 * M] = __float2bfloat16_rn(g5);
+          }
         }
       }
       if (lane == 0) {
         const float psum = p_eos + p_eoc + p_cont;
         const float inv_e = 1.0f / (e0 + e1 + e2);
         const float ws = w * inv_rows;
-        z[0] = ws * (e0 * inv_e * psum - p_eos);
-        z[1] = ws * (e1 * inv_e * psum - p_eoc);
-        z[2] = ws * (e2 * inv_e * psum - p_cont);
+        const float q0 = ws * (e0 * inv_e * psum - p_eos), q1 = ws * (e1 * inv_e * psum - p_eoc);
+        const float q2 = ws * (e2 * inv_e * psum - p_cont);
+        z[0] = q0;
+        z[1] = q1;
+        z[2] = q2;
+        if (dl_bf != nullptr) {
+          dl_bf[r * noutp + 0] = __float2bfloat16_rn(q0);
+          dl_bf[r * noutp + 1] = __float2bfloat16_rn(q1);
+          dl_bf[r * noutp + 2] = __float2bfloat16_rn(q2);
+        }
       }
     }
   }
@@ -219,7 +238,8 @@ int sk_head(skrnn_handle *h, cudaStream_t st, int B, int T, const float *y_bt5, 
   SkLaunch scope(h, st, SK_CAT_HEAD);
   mdn_head_kernel<<<blocks, 256, 0, st>>>(h->ws.logits, y_bt5, mdn_out, B, T, h->M, want_grad ? 1 : 0,
                                          (float)(1.0 / (double)loss_rows),
-                                         h->cfg.stroke_importance_factor, h->scal);
+                                         h->cfg.stroke_importance_factor, h->scal,
+                                         want_grad ? h->ws.dlogits_bf : nullptr, h->NOUTP);
   SK_CUDA(cudaGetLastError());
   return 0;
 }

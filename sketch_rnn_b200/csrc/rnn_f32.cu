@@ -72,6 +72,8 @@ struct RnnArgs {
   float *state_out;       // [B,S]
   const float *mask;      // [B,T,H] or null
   const float *wpack;     // packed slices, see pack_weights_kernel
+  // optional bf16 mirrors for the tensor-core GEMMs that consume these activations (null in fp32 mode)
+  __nv_bfloat16 *out_bf, *hprev_bf, *aux_bf, *dpre_bf;
   int w_in_smem;
   int ncp0, ncp1;         // padded column counts of the (up to) two packed matrices
   int k0, k1;             // K of the two packed matrices
@@ -186,6 +188,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) rnn_fwd_kernel(RnnArgs a) {
     if (b < B) {
       float hi = a.state_in[(size_t)b * S + hoff + u0 + u];
       a.hprev[((size_t)0 * B + b) * H + u0 + u] = hi;
+      if (a.hprev_bf) a.hprev_bf[((size_t)0 * B + b) * H + u0 + u] = __float2bfloat16_rn(hi);
       if (CELL == 0) {
         float ci = a.state_in[(size_t)b * S + u0 + u];
         cs[it] = ci;
@@ -217,6 +220,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) rnn_fwd_kernel(RnnArgs a) {
         cs[it] = z;
         hown[it] = hv;
         a.cprev[((size_t)t * B + b) * H + u0 + u] = r * hv;
+        if (a.aux_bf) a.aux_bf[((size_t)t * B + b) * H + u0 + u] = __float2bfloat16_rn(r * hv);
       }
       cluster_sync_all();
       gather_tile<RB>(a.cprev + trow * H, H, H, rows_valid, AT, tid);
@@ -259,8 +263,12 @@ __global__ void __launch_bounds__(NTHREADS, 1) rnn_fwd_kernel(RnnArgs a) {
       float ov = h2;
       if (a.dropout) ov *= drop_scale(a.mask, b, T, t, H, u0 + u, a.row0, a.seed, a.keep);
       a.out[((size_t)t * B + b) * H + u0 + u] = ov;
+      if (a.out_bf) a.out_bf[((size_t)t * B + b) * H + u0 + u] = __float2bfloat16_rn(ov);
       hnext = eoc ? a.state_in[(size_t)b * S + hoff + u0 + u] : h2;
-      if (t + 1 < T) a.hprev[((size_t)(t + 1) * B + b) * H + u0 + u] = hnext;
+      if (t + 1 < T) {
+        a.hprev[((size_t)(t + 1) * B + b) * H + u0 + u] = hnext;
+        if (a.hprev_bf) a.hprev_bf[((size_t)(t + 1) * B + b) * H + u0 + u] = __float2bfloat16_rn(hnext);
+      }
       else a.state_out[(size_t)b * S + hoff + u0 + u] = hnext;
     }
     cluster_sync_all();
@@ -319,20 +327,31 @@ __global__ void __launch_bounds__(NTHREADS, 1) rnn_bwd_kernel(RnnArgs a) {
         float dc2 = (eoc ? 0.f : dcc[it]) + dh2 * o * (1.0f - tc * tc);
         float d_oo = dh2 * tc;
         dcc[it] = dc2 * f;
-        xw[0 * H + u0 + u] = dc2 * j * i * (1.0f - i);
-        xw[1 * H + u0 + u] = dc2 * i * (1.0f - j * j);
-        xw[2 * H + u0 + u] = dc2 * c * f * (1.0f - f);
-        xw[3 * H + u0 + u] = d_oo * o * (1.0f - o);
+        const float d0 = dc2 * j * i * (1.0f - i), d1 = dc2 * i * (1.0f - j * j);
+        const float d2 = dc2 * c * f * (1.0f - f), d3 = d_oo * o * (1.0f - o);
+        xw[0 * H + u0 + u] = d0;
+        xw[1 * H + u0 + u] = d1;
+        xw[2 * H + u0 + u] = d2;
+        xw[3 * H + u0 + u] = d3;
+        if (a.dpre_bf) {
+          __nv_bfloat16 *db = a.dpre_bf + ((size_t)t * B + b) * G + u0 + u;
+          db[0] = __float2bfloat16_rn(d0); db[H] = __float2bfloat16_rn(d1);
+          db[2 * H] = __float2bfloat16_rn(d2); db[3 * H] = __float2bfloat16_rn(d3);
+        }
       } else if (CELL == 1) {
         float r = xw[u0 + u], z = xw[H + u0 + u], cand = xw[2 * H + u0 + u];
         float hv = a.hprev[((size_t)t * B + b) * H + u0 + u];
         float du = dh2 * (hv - cand);
         float dcand = dh2 * (1.0f - z);
-        xw[2 * H + u0 + u] = dcand * (1.0f - cand * cand);
+        const float dpc = dcand * (1.0f - cand * cand);
+        xw[2 * H + u0 + u] = dpc;
+        if (a.dpre_bf) a.dpre_bf[((size_t)t * B + b) * G + 2 * H + u0 + u] = __float2bfloat16_rn(dpc);
         if (n_it < MAXIT) { st_du[n_it] = du; st_dh[n_it] = dh2 * z; st_r[n_it] = r; st_h[n_it] = hv; st_z[n_it] = z; }
       } else {
         float h2 = xw[u0 + u];
-        xw[u0 + u] = dh2 * (1.0f - h2 * h2);
+        const float dp = dh2 * (1.0f - h2 * h2);
+        xw[u0 + u] = dp;
+        if (a.dpre_bf) a.dpre_bf[((size_t)t * B + b) * G + u0 + u] = __float2bfloat16_rn(dp);
       }
     }
     cluster_sync_all();
@@ -352,8 +371,13 @@ __global__ void __launch_bounds__(NTHREADS, 1) rnn_bwd_kernel(RnnArgs a) {
         float r = st_r[n_it], z = st_z[n_it], hv = st_h[n_it];
         float dr = drh * hv;
         st_dh[n_it] += drh * r;
-        xw[u0 + u] = dr * r * (1.0f - r);
-        xw[H + u0 + u] = st_du[n_it] * z * (1.0f - z);
+        const float dpr = dr * r * (1.0f - r), dpz = st_du[n_it] * z * (1.0f - z);
+        xw[u0 + u] = dpr;
+        xw[H + u0 + u] = dpz;
+        if (a.dpre_bf) {
+          a.dpre_bf[((size_t)t * B + b) * G + u0 + u] = __float2bfloat16_rn(dpr);
+          a.dpre_bf[((size_t)t * B + b) * G + H + u0 + u] = __float2bfloat16_rn(dpz);
+        }
       }
       cluster_sync_all();
       if (t == 0) break;
@@ -548,6 +572,10 @@ int run_layer(skrnn_handle *h, cudaStream_t st, bool bwd, int l, int B, int T, c
   a.state_out = state_out;
   a.mask = mask;
   a.wpack = h->ws.wpack;
+  a.out_bf = h->ws.out_bf[l];
+  a.hprev_bf = h->ws.hprev_bf[l];
+  a.aux_bf = h->ws.aux_bf[l];
+  a.dpre_bf = bwd ? h->ws.dpre_bf : nullptr;
   a.w_in_smem = p.wsmem;
   a.ncp0 = p.ncp0; a.ncp1 = p.ncp1; a.k0 = p.k0; a.k1 = p.k1;
   int nclusters = (B + p.RB - 1) / p.RB;

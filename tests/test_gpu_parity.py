@@ -255,3 +255,34 @@ def test_errors_are_reported_not_thrown():
     with pytest.raises(_lib.SkrnnError, match="expected"):
         h.set_params(np.zeros(5, dtype=np.float32))
     h.close()
+
+
+BF16_TOL = 2e-2
+BF16_CASES = [("lstm", 16, 2, 3, 5, 7), ("gru", 64, 3, 5, 11, 6), ("rnn", 40, 3, 24, 9, 8),
+              ("lstm", 256, 2, 24, 23, 12), ("gru", 256, 2, 24, 10, 10), ("lstm", 512, 3, 24, 9, 5)]
+
+
+@pytest.mark.parametrize("model,H,L,M,B,T", BF16_CASES)
+def test_bf16_path_loss_and_gradients(model, H, L, M, B, T):
+    """bf16 tensor-core path (tcgen05 GEMMs): loss and gradients within 2e-2 of the fp64 oracle,
+    MDN parameters within 2e-2 as well (its inputs went through bf16 products)."""
+    cfg, params, x, y, s0, mask = _case(model, H, L, M, B, T)
+    losses_ref, grads_ref, fstate_ref, _ = so.loss_and_grads(
+        cfg, f64(params), x.astype(np.float64), y.astype(np.float64),
+        [s.astype(np.float64) for s in s0], mask.astype(np.float64))
+    h = make_handle(cfg, params, B, T, precision="bf16")
+    losses, state_out = h.loss_grad(x, y, stack_state(s0), dropout_mask=mask)
+    losses = losses.cpu().numpy()
+    g = h.get_params_dict(h.grads_tensor().cpu().numpy())
+    for i in range(3):
+        assert abs(losses[i] - losses_ref[i]) <= BF16_TOL * abs(losses_ref[i]) + 1e-5, (i, losses, losses_ref)
+    gscale = max(np.max(np.abs(v)) for v in grads_ref.values())
+    for n in grads_ref:
+        err = np.max(np.abs(g[n].astype(np.float64) - grads_ref[n])) / gscale
+        assert err < BF16_TOL, (n, err)
+    ref = so.forward(cfg, f64(params), x.astype(np.float64), [s.astype(np.float64) for s in s0])
+    mdn, _ = h.forward(x, stack_state(s0))
+    mdn = mdn.cpu().numpy()
+    assert rel_err(mdn[:, 3:3 + M], ref["mdn"]["pi"]) < BF16_TOL
+    assert rel_err(mdn[:, 3 + M:3 + 2 * M], ref["mdn"]["mu1"]) < BF16_TOL
+    h.close()
