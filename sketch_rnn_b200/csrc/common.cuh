@@ -1,5 +1,6 @@
 // common.cuh -- internal declarations shared by the libskrnn translation units.
 #pragma once
+#include <cuda.h>
 #include <cuda_runtime.h>
 #include <cuda_bf16.h>
 #include <stdint.h>
@@ -70,6 +71,8 @@ struct SkWorkspace {   // time-major activations for one (B, T) capacity
   __nv_bfloat16 *dpre_bf = nullptr;                  // [T,B,G] of the layer being differentiated
   __nv_bfloat16 *dlogits_bf = nullptr;               // [T*B,NOUTP]
   int64_t wpack_floats = 0;
+  float *partial = nullptr;                 // tcgen05 BPTT: per-rank partial d(h) exchange
+  int64_t partial_floats = 0;
 };
 
 struct skrnn_handle {
@@ -102,6 +105,7 @@ struct skrnn_handle {
   int num_sms = 0;
   int64_t launches = 0;
   int cluster_size = 1;
+  bool tc_rnn_disabled = false;
   // optional per-category kernel timing (skrnn_profile_*): CUDA events around every launch
   bool prof_on = false;
   struct ProfRec { int cat; cudaEvent_t a, b; };
@@ -137,6 +141,13 @@ int sk_gemm_f32(skrnn_handle *h, cudaStream_t st, int M, int N, int K, const flo
 int sk_gemm_tc(skrnn_handle *h, cudaStream_t st, int M, int N, int K, const void *A, int lda, bool a_kmajor,
                const void *B, int ldb, bool b_kmajor, float *C, int ldc, const float *bias, bool accumulate);
 extern uint32_t g_tc_override[6];
+// 128B-swizzled tiled tensor map (rank 2 or 3).  elem_bytes: 2 (bf16) or 4 (fp32).
+int sk_make_tmap(CUtensorMap *m, int elem_bytes, const void *ptr, int rank, const uint64_t *dims,
+                 const uint64_t *strides_bytes, const uint32_t *box);
+// tcgen05 recurrent kernels (rnn_tc.cu): return 0 ok, <0 "not eligible, use the fp32 kernels", >0 error
+int sk_rnn_tc_layer(skrnn_handle *h, cudaStream_t st, bool bwd, int l, int B, int T, const float *x_bt5,
+                    const float *state_in, float *state_out, const float *mask, uint64_t seed, int row0,
+                    bool training);
 int sk_colsum(skrnn_handle *h, cudaStream_t st, const float *A, int64_t rows, int cols, int lda,
               float *out);  // out[c] += sum_r A[r][c]
 
