@@ -107,8 +107,8 @@ SKRNN_API int skrnn_forward(skrnn_handle *h, int32_t B, int32_t T, const float *
 /* Replaces the cost / cost_shape / cost_pen fetches and tf.gradients (model.py:176-182):
  * forward with output dropout, MDN loss, BPTT.  The UNCLIPPED gradient lands in
  * skrnn_grads_dev(h).
- *   dropout_mask_dev  [B,T,H] of 0/1 or NULL.  NULL: draw the mask in-kernel from a Philox
- *                     counter keyed by (seed, row0 + b, t, unit) when keep_prob < 1.
+ *   dropout_mask_dev  [B,T,H] of 0/1 or NULL.  NULL: draw the mask in-kernel from a counter
+ *                     hash keyed by (seed, row0 + b, t, unit) when keep_prob < 1.
  *   row0, loss_rows   data-parallel sharding: this call holds rows [row0, row0+B) of a global
  *                     batch whose losses/gradients are means over loss_rows = B_global*T rows.
  *                     Single GPU: row0 = 0, loss_rows = B*T.

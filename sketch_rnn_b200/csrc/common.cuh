@@ -71,7 +71,7 @@ struct SkWorkspace {   // time-major activations for one (B, T) capacity
   __nv_bfloat16 *dpre_bf = nullptr;                  // [T,B,G] of the layer being differentiated
   __nv_bfloat16 *dlogits_bf = nullptr;               // [T*B,NOUTP]
   int64_t wpack_floats = 0;
-  float *partial = nullptr;                 // tcgen05 BPTT: per-rank partial d(h) exchange
+  __nv_bfloat16 *partial = nullptr;         // tcgen05 BPTT: per-rank partial d(h) exchange
   int64_t partial_floats = 0;
 };
 

@@ -110,30 +110,37 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       tc_commit(bar_tmem);  // accumulator complete
     }
   } else {
-    // epilogue: warp w may touch TMEM lanes [32*(w%4), +32)
+    // epilogue: warp w may touch TMEM lanes [32*(w%4), +32) = output rows m0 + 32q + lane.  Each
+    // 32x32 block of the accumulator is transposed through shared memory (the pipeline stages are
+    // idle once the accumulator is complete) so that every global store / atomic instruction covers
+    // one contiguous 128-byte row segment.
     const int q = warp & 3;
-    const int m = m0 + 32 * q + lane;
     if (nkb > 0) {
       mbar_wait(bar_tmem, 0);
       tc_fence_after();
+      float *stage = reinterpret_cast<float *>(gen_base) + q * 1024;  // [32][32] floats, rotated columns
+      const bool add_bias = a.bias != nullptr && blockIdx.z == 0;
+      const int mb = m0 + 32 * q;
 #pragma unroll 1
       for (int c = 0; c < BN / 32; ++c) {
         uint32_t r[32];
         tc_ld32(tmem_acc + ((uint32_t)(32 * q) << 16) + (uint32_t)(c * 32), r);
-        if (m < a.M) {
-          float *dst = a.C + (size_t)m * a.ldc + n0 + c * 32;
-          const bool add_bias = a.bias != nullptr && blockIdx.z == 0;
 #pragma unroll
-          for (int j = 0; j < 32; ++j) {
-            const int n = n0 + c * 32 + j;
-            if (n < a.N) {
-              float v = __uint_as_float(r[j]);
-              if (add_bias) v += __ldg(a.bias + n);
-              if (a.accumulate) atomicAdd(dst + j, v);
-              else dst[j] = v;
-            }
+        for (int j = 0; j < 32; ++j) stage[lane * 32 + ((j + lane) & 31)] = __uint_as_float(r[j]);
+        __syncwarp();
+        const int n = n0 + c * 32 + lane;
+        const bool n_ok = n < a.N;
+        const float bv = (add_bias && n_ok) ? __ldg(a.bias + n) : 0.f;
+        const int rows = min(32, a.M - mb);
+        float *dst = a.C + (size_t)mb * a.ldc + n;
+        if (n_ok) {
+          if (a.accumulate) {
+            for (int rr = 0; rr < rows; ++rr) atomicAdd(dst + (size_t)rr * a.ldc, stage[rr * 32 + ((lane + rr) & 31)] + bv);
+          } else {
+            for (int rr = 0; rr < rows; ++rr) dst[(size_t)rr * a.ldc] = stage[rr * 32 + ((lane + rr) & 31)] + bv;
           }
         }
+        __syncwarp();
       }
     }
   }
@@ -183,8 +190,9 @@ int sk_make_tmap(CUtensorMap *m, int elem_bytes, const void *ptr, int rank, cons
                  const uint64_t *strides_bytes, const uint32_t *box) {
   EncodeTiledFn enc = get_encode();
   SK_CHECK(enc != nullptr, "cuTensorMapEncodeTiled is not available from the driver");
-  cuuint64_t gdim[3], gstr[2];
-  cuuint32_t bx[3], es[3] = {1, 1, 1};
+  cuuint64_t gdim[5], gstr[4];
+  cuuint32_t bx[5], es[5] = {1, 1, 1, 1, 1};
+  SK_CHECK(rank >= 2 && rank <= 5, "tensor map rank %d unsupported", rank);
   for (int i = 0; i < rank; ++i) { gdim[i] = dims[i]; bx[i] = box[i]; }
   for (int i = 0; i + 1 < rank; ++i) gstr[i] = strides_bytes[i];
   CUresult r = enc(m, elem_bytes == 2 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32, rank,

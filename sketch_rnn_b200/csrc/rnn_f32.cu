@@ -50,10 +50,7 @@ __device__ __forceinline__ float sigmoidf_(float x) { return 1.0f / (1.0f + expf
 __device__ __forceinline__ float drop_scale(const float *mask, int b, int T, int t, int H, int unit,
                                             int row0, uint64_t seed, float keep) {
   if (mask != nullptr) return mask[((int64_t)b * T + t) * H + unit] * (1.0f / keep);
-  uint32_t r[4];
-  skm_philox4x32((uint32_t)(row0 + b), (uint32_t)t, (uint32_t)(unit >> 2), 0x5eedu, (uint32_t)seed,
-                 (uint32_t)(seed >> 32), r);
-  return skm_u01(r[unit & 3]) < keep ? (1.0f / keep) : 0.0f;
+  return skm_u01(skm_drop_bits(seed, (uint32_t)(row0 + b), (uint32_t)t, (uint32_t)unit)) < keep ? (1.0f / keep) : 0.0f;
 }
 
 struct RnnArgs {

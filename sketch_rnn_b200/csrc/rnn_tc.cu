@@ -28,12 +28,15 @@
 
 namespace {
 
-constexpr int TCR_THREADS = 192;
+constexpr int TCR_EPI_WARPS = 16;                      // 4 TMEM lane quarters x 4 column groups
+constexpr int TCR_THREADS = 64 + 32 * TCR_EPI_WARPS;  // warp 0: TMA, warp 1: MMA, warps 2..17: epilogue
 
 __device__ __forceinline__ void cluster_sync_all() {
   asm volatile("barrier.cluster.arrive.release.aligned;\n" ::: "memory");
   asm volatile("barrier.cluster.wait.acquire.aligned;\n" ::: "memory");
 }
+__device__ __forceinline__ void cluster_arrive() { asm volatile("barrier.cluster.arrive.release.aligned;\n" ::: "memory"); }
+__device__ __forceinline__ void cluster_wait() { asm volatile("barrier.cluster.wait.acquire.aligned;\n" ::: "memory"); }
 __device__ __forceinline__ unsigned cluster_ctarank() {
   unsigned r;
   asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
@@ -44,20 +47,11 @@ __device__ __forceinline__ unsigned cluster_id_x() {
   asm volatile("mov.u32 %0, %%clusterid.x;" : "=r"(r));
   return r;
 }
-__device__ __forceinline__ float sigmoidf_(float x) { return 1.0f / (1.0f + __expf(-x)); }
-__device__ __forceinline__ float tanhf_(float x) {
-  float e = __expf(2.0f * fabsf(x));
-  float r = 1.0f - 2.0f / (e + 1.0f);
-  return copysignf(r, x);
-}
 
 __device__ __forceinline__ float drop_scale(const float *mask, int b, int T, int t, int H, int unit, int row0,
                                             uint64_t seed, float keep) {
   if (mask != nullptr) return mask[((int64_t)b * T + t) * H + unit] * (1.0f / keep);
-  uint32_t r[4];
-  skm_philox4x32((uint32_t)(row0 + b), (uint32_t)t, (uint32_t)(unit >> 2), 0x5eedu, (uint32_t)seed,
-                 (uint32_t)(seed >> 32), r);
-  return skm_u01(r[unit & 3]) < keep ? (1.0f / keep) : 0.0f;
+  return skm_u01(skm_drop_bits(seed, (uint32_t)(row0 + b), (uint32_t)t, (uint32_t)unit)) < keep ? (1.0f / keep) : 0.0f;
 }
 
 struct TcRnnArgs {
@@ -76,24 +70,30 @@ struct TcRnnArgs {
   __nv_bfloat16 *hprev_bf;
   const float *dout;      // [T,B,H] fp32
   __nv_bfloat16 *dpre_bf; // [T,B,G]
-  float *partial;         // [nclusters][2][CS][H][N]
+  __nv_bfloat16 *partial; // [nclusters][2][CS][H][N] partial d(h), bf16
   const uint8_t *wimg;    // per-rank shared-memory images of the weight operand
   int wimg_bytes;
+  int debug;              // SKRNN_TC_DEBUG=1: one CTA prints its per-phase cycle split
 };
 
 // byte offset of fp32 element (row c, unit u) inside one 128B-swizzled staging plane [N][32]
 __device__ __forceinline__ uint32_t plane_off(int c, int u) {
   return (uint32_t)(c * 128 + ((((u >> 2) ^ (c & 7)) & 7) << 4) + ((u & 3) << 2));
 }
+__device__ __forceinline__ float sel4(int k, float a0, float a1, float a2, float a3) {
+  return k == 0 ? a0 : (k == 1 ? a1 : (k == 2 ? a2 : a3));
+}
 
 // ------------------------------------------------------------------------------------------------
 // forward
 // ------------------------------------------------------------------------------------------------
-template <int NCH>  // N = 16 * NCH batch columns per cluster
+// N = 16*NCH batch columns per cluster.  Epilogue warp (quarter q = warp%4, column group cg) owns
+// accumulator rows 32q..32q+31 (row e = 4u+g: unit u, gate g) and columns [cg*N/4, (cg+1)*N/4).
+template <int NCH>
 __global__ void __launch_bounds__(TCR_THREADS, 1)
 lstm_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_h, const __grid_constant__ CUtensorMap tm_xw, TcRnnArgs a) {
   constexpr int N = 16 * NCH;
-  constexpr int NIT = N / 4;  // (unit, column) items per epilogue thread
+  constexpr int CPW = N / 4;  // columns per epilogue warp
   extern __shared__ uint8_t smem_raw[];
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   uint8_t *gbase = smem_raw + (base - smem_u32(smem_raw));
@@ -101,13 +101,15 @@ lstm_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_h, const __grid_consta
   const uint32_t s_w = base;                                  // nkb x [128 rows][128 B]
   const uint32_t s_h = s_w + (uint32_t)nkb * 16384u;          // nkb x [N rows][128 B]
   const uint32_t s_xw = s_h + (uint32_t)nkb * (N * 128);      // 4 planes x [N][32] fp32
-  const uint32_t s_bar = s_xw + 4u * (N * 128);
+  const uint32_t s_init = s_xw + 4u * (N * 128);              // [2][N][32] fp32: fed c / h (eoc reset source)
+  const uint32_t s_bar = s_init + 2u * N * 128;
   const uint32_t bar_h = s_bar;          // [8]
   const uint32_t bar_acc = s_bar + 64;
   const uint32_t bar_xw = s_bar + 72;
   const uint32_t tmem_holder = s_bar + 80;
   volatile uint32_t *tmem_holder_ptr = reinterpret_cast<volatile uint32_t *>(gbase + (tmem_holder - base));
   const uint8_t *xw_gen = gbase + (s_xw - base);
+  float *init_gen = reinterpret_cast<float *>(gbase + (s_init - base));
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int rank = cluster_ctarank();
@@ -115,41 +117,46 @@ lstm_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_h, const __grid_consta
   const int u0 = rank * 32;
   const int S = 2 * H;
 
-  // resident weight operand: straight copy of this rank's pre-swizzled image
-  {
+  {  // resident weight operand: straight copy of this rank's pre-swizzled image
     const uint4 *src = reinterpret_cast<const uint4 *>(a.wimg + (size_t)rank * a.wimg_bytes);
     uint4 *dst = reinterpret_cast<uint4 *>(gbase + (s_w - base));
     for (int i = tid; i < a.wimg_bytes / 16; i += TCR_THREADS) dst[i] = __ldg(src + i);
   }
   if (tid == 0) {
-    for (int i = 0; i < 8; ++i) mbar_init(bar_h + 8 * i, 1);
+    mbar_init(bar_h, 32 * TCR_EPI_WARPS);
     mbar_init(bar_acc, 1);
     mbar_init(bar_xw, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 1) tc_alloc(tmem_holder, (uint32_t)a.tmem_cols);
+  {
+    uint4 *hz = reinterpret_cast<uint4 *>(gbase + (s_h - base));
+    for (int i = tid; i < nkb * N * 8; i += TCR_THREADS) hz[i] = make_uint4(0, 0, 0, 0);
+  }
 
-  // epilogue thread <-> accumulator row e = 32*(warp%4) + lane = 4u+g: unit u, gate g; its items are
-  // the batch columns c = 4*it + g
-  const int e = 32 * (warp & 3) + lane;
-  const int eu = (e >> 2) & 31, eg = e & 3;
-  float cst[NIT];
+  const int q = warp & 3, cg = (warp - 2) >> 2;
+  const int e = 32 * q + lane;
+  const int eu = e >> 2, eg = e & 3;
+  const int uo = u0 + eu;
+  float cst[NCH];
   if (warp >= 2) {
 #pragma unroll
-    for (int it = 0; it < NIT; ++it) {
-      const int b = b0 + 4 * it + eg;
+    for (int it = 0; it < NCH; ++it) {
+      const int c = cg * CPW + 4 * it + eg;
+      const int b = b0 + c;
       cst[it] = 0.f;
       if (b < B) {
-        const float ci = a.state_in[(size_t)b * S + u0 + eu];
-        const float hi = a.state_in[(size_t)b * S + H + u0 + eu];
+        const float ci = a.state_in[(size_t)b * S + uo];
+        const float hi = a.state_in[(size_t)b * S + H + uo];
         cst[it] = ci;
-        a.cprev[((size_t)0 * B + b) * H + u0 + eu] = ci;
-        a.hprev_bf[((size_t)0 * B + b) * H + u0 + eu] = __float2bfloat16_rn(hi);
+        init_gen[(0 * N + c) * 32 + eu] = ci;
+        init_gen[(1 * N + c) * 32 + eu] = hi;
+        a.cprev[(size_t)b * H + uo] = ci;
+        a.hprev_bf[(size_t)b * H + uo] = __float2bfloat16_rn(hi);
       }
     }
   }
-  __threadfence();
-  fence_proxy_async();
+  fence_proxy_async_smem();
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -157,97 +164,160 @@ lstm_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_h, const __grid_consta
   cluster_sync_all();
 
   const uint32_t idesc = make_idesc_bf16(128, N, false, false);
+  uint64_t dA[8], dB[8];
+#pragma unroll
+  for (int kb = 0; kb < 8; ++kb) {
+    dA[kb] = make_desc(s_w + (uint32_t)kb * 16384u, 0, 1024);
+    dB[kb] = make_desc(s_h + (uint32_t)kb * (N * 128), 0, 1024);
+  }
+  long long tk[6] = {0, 0, 0, 0, 0, 0};
+  const bool dbg = a.debug && rank == 0 && cluster_id_x() == 0 && (tid == 64 || tid == 32);
 
   for (int t = 0; t < T; ++t) {
+    long long c0 = 0, c1 = 0, c2 = 0, c3 = 0;
+    if (dbg) c0 = clock64();
     if (warp == 0) {
       if (lane == 0) {
-        fence_proxy_async();
-        for (int kb = 0; kb < nkb; ++kb) {
-          mbar_expect_tx(bar_h + 8 * kb, N * 128);
-          tma_load_3d(s_h + (uint32_t)kb * (N * 128), &tm_h, bar_h + 8 * kb, kb * 64, b0, t);
-        }
         mbar_expect_tx(bar_xw, 4 * N * 128);
-        for (int g = 0; g < 4; ++g) tma_load_3d(s_xw + (uint32_t)g * (N * 128), &tm_xw, bar_xw, g * H + u0, b0, t);
+        tma_load_4d(s_xw, &tm_xw, bar_xw, u0, b0, 0, t);  // the 4 gate planes of my units in one box
       }
     } else if (warp == 1) {
       if (lane == 0) {
-        for (int kb = 0; kb < nkb; ++kb) {
-          mbar_wait(bar_h + 8 * kb, t & 1);
-          tc_fence_after();
-          const uint64_t da = make_desc(s_w + (uint32_t)kb * 16384u, 0, 1024);
-          const uint64_t db = make_desc(s_h + (uint32_t)kb * (N * 128), 0, 1024);
+        mbar_wait(bar_h, t & 1);
+        if (dbg) { c1 = clock64(); c2 = c1; }
+        tc_fence_after();
 #pragma unroll
-          for (int k = 0; k < 4; ++k)
-            tc_mma_bf16(tmem_acc, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (kb > 0 || k > 0) ? 1u : 0u);
-        }
-        tc_commit(bar_acc);
-      }
-    } else {
-      const int q = warp & 3;  // TMEM lane quarter this warp may read
-      // lane index within the 128 accumulator rows = 32q + lane; must equal e for the gate layout
-      mbar_wait(bar_acc, t & 1);
-      tc_fence_after();
-      mbar_wait(bar_xw, t & 1);
-#pragma unroll
-      for (int ch = 0; ch < NCH; ++ch) {
-        uint32_t r[16];
-        tc_ld16(tmem_acc + ((uint32_t)(32 * q) << 16) + (uint32_t)(ch * 16), r);
-#pragma unroll
-        for (int qq = 0; qq < 4; ++qq) {
-          const int it = ch * 4 + qq;
-          const float x0 = __uint_as_float(r[4 * qq + 0]), x1 = __uint_as_float(r[4 * qq + 1]);
-          const float x2 = __uint_as_float(r[4 * qq + 2]), x3 = __uint_as_float(r[4 * qq + 3]);
-          // exchange: after round rr this lane holds gate (eg^rr) of column 4*it + eg
-          float rc[4];
-          rc[0] = eg == 0 ? x0 : (eg == 1 ? x1 : (eg == 2 ? x2 : x3));
-#pragma unroll
-          for (int rr = 1; rr < 4; ++rr) {
-            const int sel = eg ^ rr;
-            const float send = sel == 0 ? x0 : (sel == 1 ? x1 : (sel == 2 ? x2 : x3));
-            rc[rr] = __shfl_xor_sync(0xffffffffu, send, rr);
-          }
-          float pre[4];
-#pragma unroll
-          for (int k = 0; k < 4; ++k) {
-            const int rr = k ^ eg;
-            pre[k] = rr == 0 ? rc[0] : (rr == 1 ? rc[1] : (rr == 2 ? rc[2] : rc[3]));
-          }
-          const int c = 4 * it + eg;
-          const int b = b0 + c;
-          if (b < B) {
+        for (int kb = 0; kb < 8; ++kb) {
+          if (kb < nkb) {
 #pragma unroll
             for (int k = 0; k < 4; ++k)
-              pre[k] += *reinterpret_cast<const float *>(xw_gen + (size_t)k * (N * 128) + plane_off(c, eu));
-            const float ig = sigmoidf_(pre[0]), jg = tanhf_(pre[1]), fg = sigmoidf_(pre[2] + 1.0f), og = sigmoidf_(pre[3]);
-            const float c2 = cst[it] * fg + ig * jg;
-            const float h2 = tanhf_(c2) * og;
-            float *ac = a.acts + ((size_t)t * B + b) * G + u0 + eu;
+              tc_mma_bf16(tmem_acc, dA[kb] + (uint64_t)(2 * k), dB[kb] + (uint64_t)(2 * k), idesc, (kb > 0 || k > 0) ? 1u : 0u);
+          }
+        }
+        tc_commit(bar_acc);
+        if (dbg) { c3 = clock64(); tk[0] += c1 - c0; tk[1] += c2 - c1; tk[2] += c3 - c2; }
+      }
+    } else {
+      // h_{t-1} tile of my cluster's rows (all H units, written by all ranks last step): L2 -> swizzled smem
+      {
+        const int cpr = H >> 3;  // 16-byte chunks per row
+        const int et = tid - 64;
+        for (int i = et; i < N * cpr; i += 32 * TCR_EPI_WARPS) {
+          const int n = i / cpr, ch = i - n * cpr;
+          const int b = b0 + n;
+          uint4 v = make_uint4(0, 0, 0, 0);
+          if (b < B) v = __ldcg(reinterpret_cast<const uint4 *>(a.hprev_bf + ((size_t)t * B + b) * H) + ch);
+          const uint32_t off = (uint32_t)((ch >> 3) * (N * 128) + n * 128 + (((ch & 7) ^ (n & 7)) << 4));
+          *reinterpret_cast<uint4 *>(gbase + (s_h - base) + off) = v;
+        }
+        fence_proxy_async_smem();
+        mbar_arrive(bar_h);
+      }
+      // everything that does not depend on the recurrence is fetched before waiting for the MMA
+      uint32_t eoc_bits = 0;
+      float dsc[NCH];
+#pragma unroll
+      for (int it = 0; it < NCH; ++it) {
+        const int b = b0 + cg * CPW + 4 * it + eg;
+        dsc[it] = 1.0f;
+        if (b < B) {
+          if (__ldg(a.x_bt5 + ((size_t)b * T + t) * 5 + 3) > 0.f) eoc_bits |= 1u << it;
+          if (a.dropout) dsc[it] = drop_scale(a.mask, b, T, t, H, uo, a.row0, a.seed, a.keep);
+        }
+      }
+      if (dbg) c1 = clock64();
+      mbar_wait(bar_acc, t & 1);
+      if (dbg) c2 = clock64();
+      tc_fence_after();
+      uint32_t r[CPW];
+      tc_ldn<CPW>(tmem_acc + ((uint32_t)(32 * q) << 16) + (uint32_t)(cg * CPW), r);
+      mbar_wait(bar_xw, t & 1);
+      if (dbg) c3 = clock64();
+      const int s1 = eg ^ 1, s2 = eg ^ 2, s3 = eg ^ 3;
+      constexpr bool DEFER = NCH <= 2;  // small tiles are latency-bound: publish h first, store the rest after arriving
+      float sv[DEFER ? NCH : 1][7];
+#pragma unroll
+      for (int it = 0; it < NCH; ++it) {
+        const float x0 = __uint_as_float(r[4 * it + 0]), x1 = __uint_as_float(r[4 * it + 1]);
+        const float x2 = __uint_as_float(r[4 * it + 2]), x3 = __uint_as_float(r[4 * it + 3]);
+        // 4-lane exchange: round rr brings gate (eg^rr) of column 4*it + eg from lane^rr
+        const float r0 = sel4(eg, x0, x1, x2, x3);
+        const float r1 = __shfl_xor_sync(0xffffffffu, sel4(s1, x0, x1, x2, x3), 1);
+        const float r2 = __shfl_xor_sync(0xffffffffu, sel4(s2, x0, x1, x2, x3), 2);
+        const float r3 = __shfl_xor_sync(0xffffffffu, sel4(s3, x0, x1, x2, x3), 3);
+        const float p0 = sel4(eg, r0, r1, r2, r3), p1 = sel4(s1, r0, r1, r2, r3);
+        const float p2 = sel4(s2, r0, r1, r2, r3), p3 = sel4(s3, r0, r1, r2, r3);
+        const int c = cg * CPW + 4 * it + eg;
+        const int b = b0 + c;
+        if (b < B) {
+          const uint32_t po = plane_off(c, eu);
+          const float ig = sigmoid_approx(p0 + *reinterpret_cast<const float *>(xw_gen + 0 * (N * 128) + po));
+          const float jg = tanh_approx(p1 + *reinterpret_cast<const float *>(xw_gen + 1 * (N * 128) + po));
+          const float fg = sigmoid_approx(p2 + *reinterpret_cast<const float *>(xw_gen + 2 * (N * 128) + po) + 1.0f);
+          const float og = sigmoid_approx(p3 + *reinterpret_cast<const float *>(xw_gen + 3 * (N * 128) + po));
+          const float c2 = fmaf(cst[it], fg, ig * jg);
+          const float h2 = tanh_approx(c2) * og;
+          const bool eoc = (eoc_bits >> it) & 1u;
+          const float cn = eoc ? init_gen[(0 * N + c) * 32 + eu] : c2;
+          const float hn = eoc ? init_gen[(1 * N + c) * 32 + eu] : h2;
+          cst[it] = cn;
+          const size_t row = (size_t)t * B + b;
+          if (t + 1 < T) a.hprev_bf[(row + B) * H + uo] = __float2bfloat16_rn(hn);  // exchange medium first
+          if constexpr (DEFER) {
+            sv[it][0] = ig; sv[it][1] = jg; sv[it][2] = fg; sv[it][3] = og;
+            sv[it][4] = h2 * dsc[it]; sv[it][5] = cn; sv[it][6] = hn;
+          } else {
+            float *ac = a.acts + row * G + uo;
             ac[0] = ig; ac[H] = jg; ac[2 * H] = fg; ac[3 * H] = og;
-            const bool eoc = a.x_bt5[((size_t)b * T + t) * 5 + 3] > 0.f;
-            float ov = h2;
-            if (a.dropout) ov *= drop_scale(a.mask, b, T, t, H, u0 + eu, a.row0, a.seed, a.keep);
-            a.out_bf[((size_t)t * B + b) * H + u0 + eu] = __float2bfloat16_rn(ov);
-            const float cn = eoc ? a.state_in[(size_t)b * S + u0 + eu] : c2;
-            const float hn = eoc ? a.state_in[(size_t)b * S + H + u0 + eu] : h2;
-            cst[it] = cn;
+            a.out_bf[row * H + uo] = __float2bfloat16_rn(h2 * dsc[it]);
             if (t + 1 < T) {
-              a.cprev[((size_t)(t + 1) * B + b) * H + u0 + eu] = cn;
-              a.hprev_bf[((size_t)(t + 1) * B + b) * H + u0 + eu] = __float2bfloat16_rn(hn);
+              a.cprev[(row + B) * H + uo] = cn;
             } else {
-              a.state_out[(size_t)b * S + u0 + eu] = cn;
-              a.state_out[(size_t)b * S + H + u0 + eu] = hn;
+              a.state_out[(size_t)b * S + uo] = cn;
+              a.state_out[(size_t)b * S + H + uo] = hn;
             }
           }
         }
       }
-      __threadfence();
-      fence_proxy_async();
+      if (dbg) { long long c4 = clock64(); tk[0] += c1 - c0; tk[1] += c2 - c1; tk[2] += c3 - c2; tk[3] += c4 - c3; c0 = c4; }
+      if constexpr (DEFER) {
+        __syncwarp();
+        tc_fence_before();
+        cluster_arrive();  // release: the h stores above are what the other ranks wait for
+#pragma unroll
+        for (int it = 0; it < NCH; ++it) {
+          const int b = b0 + cg * CPW + 4 * it + eg;
+          if (b < B) {
+            const size_t row = (size_t)t * B + b;
+            float *ac = a.acts + row * G + uo;
+            ac[0] = sv[it][0]; ac[H] = sv[it][1]; ac[2 * H] = sv[it][2]; ac[3 * H] = sv[it][3];
+            a.out_bf[row * H + uo] = __float2bfloat16_rn(sv[it][4]);
+            if (t + 1 < T) {
+              a.cprev[(row + B) * H + uo] = sv[it][5];
+            } else {
+              a.state_out[(size_t)b * S + uo] = sv[it][5];
+              a.state_out[(size_t)b * S + H + uo] = sv[it][6];
+            }
+          }
+        }
+        cluster_wait();
+        tc_fence_after();
+        if (dbg && tid == 64) tk[4] += clock64() - c0;
+        continue;
+      }
     }
     __syncwarp();
     tc_fence_before();
-    cluster_sync_all();
+    cluster_sync_all();  // arrive.release publishes the h stores to the other ranks
     tc_fence_after();
+    if (dbg && tid == 64) tk[4] += clock64() - c0;
   }
+  if (dbg && tid == 32)
+    printf("[tc fwd N=%d] MMA thread cycles/step: barrier->h tile ready %lld, (unused) %lld, issue+commit %lld\n", N,
+           tk[0] / T, tk[1] / T, tk[2] / T);
+  if (dbg && tid == 64)
+    printf("[tc fwd N=%d] epilogue cycles/step: prefetch %lld, wait acc %lld, tmem ld + xw wait %lld, items+stores+fence %lld, cluster barrier %lld\n",
+           N, tk[0] / T, tk[1] / T, tk[2] / T, tk[3] / T, tk[4] / T);
   __syncthreads();
   if (warp == 1) tc_dealloc(tmem_acc, (uint32_t)a.tmem_cols);
 }
@@ -255,11 +325,13 @@ lstm_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_h, const __grid_consta
 // ------------------------------------------------------------------------------------------------
 // backward
 // ------------------------------------------------------------------------------------------------
+// Elementwise items: thread (unit u = e/4, sub = e%4, column group cg) owns the NCH consecutive
+// columns c = cg*N/4 + sub*NCH + it of unit u.
 template <int NCH>
 __global__ void __launch_bounds__(TCR_THREADS, 1)
 lstm_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm_acts, TcRnnArgs a) {
   constexpr int N = 16 * NCH;
-  constexpr int NIT = N / 4;
+  constexpr int CPW = N / 4;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   uint8_t *gbase = smem_raw + (base - smem_u32(smem_raw));
@@ -290,69 +362,77 @@ lstm_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm_acts, TcRnnArgs a) {
   }
   if (tid == 0) {
     mbar_init(bar_acts, 1);
-    mbar_init(bar_ready, 128);
+    mbar_init(bar_ready, 32 * TCR_EPI_WARPS);
     mbar_init(bar_acc, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 1) tc_alloc(tmem_holder, (uint32_t)a.tmem_cols);
-  fence_proxy_async();
+  fence_proxy_async_smem();
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_acc = *tmem_holder_ptr;
   cluster_sync_all();
 
-  // epilogue thread e: unit u = e/4, column block g = e%4 -> columns [g*NIT, (g+1)*NIT)
-  const int e = 32 * (warp & 3) + lane;
-  const int eu = (e >> 2) & 31, eg = e & 3;
-  float dhc[NIT], dcc[NIT];
+  const int q = warp & 3, cg = (warp - 2) >> 2;
+  const int e = 32 * q + lane;
+  const int eu = e >> 2, esub = e & 3;
+  const int uo = u0 + eu;
+  const int c_first = cg * CPW + esub * NCH;
+  float dhc[NCH], dcc[NCH];
+  uint64_t dBk[2];
+  dBk[0] = make_desc(s_b, 0, 1024);
+  dBk[1] = make_desc(s_b + (uint32_t)(N * 128), 0, 1024);
 #pragma unroll
-  for (int it = 0; it < NIT; ++it) { dhc[it] = 0.f; dcc[it] = 0.f; }
+  for (int it = 0; it < NCH; ++it) { dhc[it] = 0.f; dcc[it] = 0.f; }
   const uint32_t idesc = make_idesc_bf16(128, N, false, false);
-  float *part_base = a.partial + (size_t)cid * 2 * CS * H * N;
+  __nv_bfloat16 *part_base = a.partial + (size_t)cid * 2 * CS * H * N;
 
   for (int t = T - 1, step = 0; t >= 0; --t, ++step) {
     const int par = step & 1;
     if (warp == 0) {
       if (lane == 0) {
         mbar_expect_tx(bar_acts, 4 * N * 128);
-        for (int g = 0; g < 4; ++g) tma_load_3d(s_ac + (uint32_t)g * (N * 128), &tm_acts, bar_acts, g * H + u0, b0, t);
+        tma_load_4d(s_ac, &tm_acts, bar_acts, u0, b0, 0, t);
       }
     } else if (warp >= 2) {
-      // prefetch the per-item global inputs before waiting on the staged activations
-      float d_o[NIT], cp[NIT];
-      bool eoc[NIT];
+      // per-item global inputs, fetched before waiting on the staged activations
+      float d_o[NCH], cp[NCH];
+      uint32_t eoc_bits = 0;
 #pragma unroll
-      for (int it = 0; it < NIT; ++it) {
-        const int b = b0 + eg * NIT + it;
-        d_o[it] = 0.f; cp[it] = 0.f; eoc[it] = false;
+      for (int it = 0; it < NCH; ++it) {
+        const int b = b0 + c_first + it;
+        d_o[it] = 0.f; cp[it] = 0.f;
         if (b < B) {
-          d_o[it] = a.dout[((size_t)t * B + b) * H + u0 + eu];
-          cp[it] = a.cprev[((size_t)t * B + b) * H + u0 + eu];
-          eoc[it] = a.x_bt5[((size_t)b * T + t) * 5 + 3] > 0.f;
+          const size_t row = (size_t)t * B + b;
+          d_o[it] = a.dout[row * H + uo];
+          cp[it] = a.cprev[row * H + uo];
+          if (__ldg(a.x_bt5 + ((size_t)b * T + t) * 5 + 3) > 0.f) eoc_bits |= 1u << it;
+          if (a.dropout) d_o[it] *= drop_scale(a.mask, b, T, t, H, uo, a.row0, a.seed, a.keep);
         }
       }
       mbar_wait(bar_acts, step & 1);
 #pragma unroll
-      for (int it = 0; it < NIT; ++it) {
-        const int c = eg * NIT + it;
+      for (int it = 0; it < NCH; ++it) {
+        const int c = c_first + it;
         const int b = b0 + c;
         if (b < B) {
-          const float ig = *reinterpret_cast<const float *>(ac_gen + 0 * (N * 128) + plane_off(c, eu));
-          const float jg = *reinterpret_cast<const float *>(ac_gen + 1 * (N * 128) + plane_off(c, eu));
-          const float fg = *reinterpret_cast<const float *>(ac_gen + 2 * (N * 128) + plane_off(c, eu));
-          const float og = *reinterpret_cast<const float *>(ac_gen + 3 * (N * 128) + plane_off(c, eu));
-          float dd = d_o[it];
-          if (a.dropout) dd *= drop_scale(a.mask, b, T, t, H, u0 + eu, a.row0, a.seed, a.keep);
-          const float dh2 = dd + (eoc[it] ? 0.f : dhc[it]);
-          const float tc = tanhf_(cp[it] * fg + ig * jg);
-          const float dc2 = (eoc[it] ? 0.f : dcc[it]) + dh2 * og * (1.0f - tc * tc);
+          const uint32_t po = plane_off(c, eu);
+          const float ig = *reinterpret_cast<const float *>(ac_gen + 0 * (N * 128) + po);
+          const float jg = *reinterpret_cast<const float *>(ac_gen + 1 * (N * 128) + po);
+          const float fg = *reinterpret_cast<const float *>(ac_gen + 2 * (N * 128) + po);
+          const float og = *reinterpret_cast<const float *>(ac_gen + 3 * (N * 128) + po);
+          const bool eoc = (eoc_bits >> it) & 1u;
+          const float dh2 = d_o[it] + (eoc ? 0.f : dhc[it]);
+          const float tc = tanh_approx(fmaf(cp[it], fg, ig * jg));
+          const float dc2 = (eoc ? 0.f : dcc[it]) + dh2 * og * (1.0f - tc * tc);
           dcc[it] = dc2 * fg;
           const float d0 = dc2 * jg * ig * (1.0f - ig), d1 = dc2 * ig * (1.0f - jg * jg);
           const float d2 = dc2 * cp[it] * fg * (1.0f - fg), d3 = dh2 * tc * og * (1.0f - og);
-          float *ac = a.acts + ((size_t)t * B + b) * G + u0 + eu;
+          const size_t row = (size_t)t * B + b;
+          float *ac = a.acts + row * G + uo;
           ac[0] = d0; ac[H] = d1; ac[2 * H] = d2; ac[3 * H] = d3;
-          __nv_bfloat16 *db = a.dpre_bf + ((size_t)t * B + b) * G + u0 + eu;
+          __nv_bfloat16 *db = a.dpre_bf + row * G + uo;
           const __nv_bfloat16 h0 = __float2bfloat16_rn(d0), h1 = __float2bfloat16_rn(d1);
           const __nv_bfloat16 h2 = __float2bfloat16_rn(d2), h3 = __float2bfloat16_rn(d3);
           db[0] = h0; db[H] = h1; db[2 * H] = h2; db[3 * H] = h3;
@@ -366,7 +446,7 @@ lstm_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm_acts, TcRnnArgs a) {
           *reinterpret_cast<uint2 *>(b_gen + off) = pk;
         }
       }
-      fence_proxy_async();
+      fence_proxy_async_smem();
       mbar_arrive(bar_ready);
     }
     if (t > 0) {
@@ -378,34 +458,34 @@ lstm_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm_acts, TcRnnArgs a) {
 #pragma unroll
             for (int kb = 0; kb < 2; ++kb) {
               const uint64_t da = make_desc(s_w + (uint32_t)kb * (HP * 128) + (uint32_t)mt * 16384u, 0, 1024);
-              const uint64_t db = make_desc(s_b + (uint32_t)kb * (N * 128), 0, 1024);
 #pragma unroll
               for (int k = 0; k < 4; ++k)
-                tc_mma_bf16(tmem_acc + (uint32_t)(mt * N), da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc,
+                tc_mma_bf16(tmem_acc + (uint32_t)(mt * N), da + (uint64_t)(2 * k), dBk[kb] + (uint64_t)(2 * k), idesc,
                             (kb > 0 || k > 0) ? 1u : 0u);
             }
           }
           tc_commit(bar_acc);
         }
       } else if (warp >= 2) {
-        const int q = warp & 3;
         mbar_wait(bar_acc, step & 1);
         tc_fence_after();
         for (int mt = 0; mt < nmt; ++mt) {
-          const int m = mt * 128 + 32 * q + lane;  // hidden unit this lane's accumulator row belongs to
-          float *dst = part_base + ((size_t)(par * CS + rank) * H + m) * N;
+          const int m = mt * 128 + e;  // hidden unit of this lane's accumulator row
+          __nv_bfloat16 *dst = part_base + ((size_t)(par * CS + rank) * H + m) * N + cg * CPW;
+          uint32_t r[CPW];
+          tc_ldn<CPW>(tmem_acc + ((uint32_t)(32 * q) << 16) + (uint32_t)(mt * N + cg * CPW), r);
+          if (m < H) {
 #pragma unroll
-          for (int ch = 0; ch < NCH; ++ch) {
-            uint32_t r[16];
-            tc_ld16(tmem_acc + ((uint32_t)(32 * q) << 16) + (uint32_t)(mt * N + ch * 16), r);
-            if (m < H) {
-#pragma unroll
-              for (int j = 0; j < 4; ++j)
-                *reinterpret_cast<uint4 *>(dst + ch * 16 + 4 * j) = make_uint4(r[4 * j], r[4 * j + 1], r[4 * j + 2], r[4 * j + 3]);
+            for (int j = 0; j < CPW / 4; ++j) {
+              const __nv_bfloat162 lo = __floats2bfloat162_rn(__uint_as_float(r[4 * j]), __uint_as_float(r[4 * j + 1]));
+              const __nv_bfloat162 hi = __floats2bfloat162_rn(__uint_as_float(r[4 * j + 2]), __uint_as_float(r[4 * j + 3]));
+              uint2 pk;
+              pk.x = *reinterpret_cast<const uint32_t *>(&lo);
+              pk.y = *reinterpret_cast<const uint32_t *>(&hi);
+              *reinterpret_cast<uint2 *>(dst + 4 * j) = pk;
             }
           }
         }
-        __threadfence();
       }
     }
     __syncwarp();
@@ -415,13 +495,21 @@ lstm_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm_acts, TcRnnArgs a) {
     if (t > 0 && warp >= 2) {
       // d(h_{t-1}) for my units = sum over ranks (fixed order) of their partials
 #pragma unroll
-      for (int it = 0; it < NIT; ++it) dhc[it] = 0.f;
+      for (int it = 0; it < NCH; ++it) dhc[it] = 0.f;
       for (int r = 0; r < CS; ++r) {
-        const float *src = part_base + ((size_t)(par * CS + r) * H + u0 + eu) * N + eg * NIT;
+        const __nv_bfloat16 *src = part_base + ((size_t)(par * CS + r) * H + uo) * N + c_first;
+        if constexpr (NCH % 4 == 0) {
 #pragma unroll
-        for (int it = 0; it < NIT; it += 4) {
-          const float4 v = __ldcg(reinterpret_cast<const float4 *>(src + it));
-          dhc[it] += v.x; dhc[it + 1] += v.y; dhc[it + 2] += v.z; dhc[it + 3] += v.w;
+          for (int it = 0; it < NCH; it += 4) {
+            const uint2 v = __ldcg(reinterpret_cast<const uint2 *>(src + it));
+            const float2 f0 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162 *>(&v.x));
+            const float2 f1 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162 *>(&v.y));
+            dhc[it] += f0.x; dhc[it + 1] += f0.y; dhc[it + 2] += f1.x; dhc[it + 3] += f1.y;
+          }
+        } else {
+#pragma unroll
+          for (int it = 0; it < NCH; ++it)
+            dhc[it] += __bfloat162float(__ushort_as_bfloat16(__ldcg(reinterpret_cast<const unsigned short *>(src + it))));
         }
       }
     }
@@ -504,7 +592,7 @@ int launch_bwd(const CUtensorMap &tm_acts, const TcRnnArgs &a, int nclusters, si
 size_t smem_need(bool bwd, int H, int N) {
   const int nkb = (H + 63) / 64, HP = (H + 127) / 128 * 128;
   size_t s = bwd ? (size_t)2 * HP * 128 + 2 * (size_t)N * 128 + 4 * (size_t)N * 128
-                 : (size_t)nkb * 16384 + (size_t)nkb * N * 128 + 4 * (size_t)N * 128;
+                 : (size_t)nkb * 16384 + (size_t)nkb * N * 128 + 4 * (size_t)N * 128 + 2 * (size_t)N * 128;
   return s + 1024 + 256;
 }
 
@@ -561,12 +649,18 @@ int sk_rnn_tc_layer(skrnn_handle *h, cudaStream_t st, bool bwd, int l, int B, in
   a.dout = h->ws.dout; a.dpre_bf = h->ws.dpre_bf;
   a.wimg = reinterpret_cast<const uint8_t *>(h->ws.wpack);
   a.wimg_bytes = img_bytes;
+  {
+    static int dbg_env = -1;
+    if (dbg_env < 0) { const char *e = getenv("SKRNN_TC_DEBUG"); dbg_env = (e && e[0] == '1') ? 1 : 0; }
+    a.debug = dbg_env;
+  }
   CUtensorMap tm_xw;
   {
-    uint64_t dims[3] = {(uint64_t)h->G, (uint64_t)B, (uint64_t)T};
-    uint64_t str[2] = {(uint64_t)h->G * 4, (uint64_t)B * h->G * 4};
-    uint32_t box[3] = {32, (uint32_t)N, 1};
-    SK_TRY(sk_make_tmap(&tm_xw, 4, h->ws.xw[l], 3, dims, str, box));
+    // xw[t][b][g*H + u] viewed as (u, b, g, t): one box fetches the 4 gate planes of 32 units for N rows
+    uint64_t dims[4] = {(uint64_t)H, (uint64_t)B, 4, (uint64_t)T};
+    uint64_t str[3] = {(uint64_t)h->G * 4, (uint64_t)H * 4, (uint64_t)B * h->G * 4};
+    uint32_t box[4] = {32, (uint32_t)N, 4, 1};
+    SK_TRY(sk_make_tmap(&tm_xw, 4, h->ws.xw[l], 4, dims, str, box));
   }
   int rc = 0;
   if (!bwd) {
@@ -587,7 +681,7 @@ int sk_rnn_tc_layer(skrnn_handle *h, cudaStream_t st, bool bwd, int l, int B, in
       cudaFree(h->ws.partial);
       h->ws.partial = nullptr;
       h->ws.partial_floats = 0;
-      SK_CUDA(cudaMalloc(&h->ws.partial, need * sizeof(float)));
+      SK_CUDA(cudaMalloc(&h->ws.partial, need * sizeof(__nv_bfloat16)));
       h->ws.partial_floats = need;
     }
     a.partial = h->ws.partial;

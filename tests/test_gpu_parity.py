@@ -124,7 +124,7 @@ def test_sharded_loss_matches_full_batch():
     h.close()
 
 
-def test_philox_dropout_is_shard_invariant():
+def test_in_kernel_dropout_is_shard_invariant():
     """In-kernel dropout is keyed by the global row, so sharding does not change the mask."""
     cfg, params, x, y, s0, _ = _case("lstm", 32, 2, 4, 8, 6)
     h = make_handle(cfg, params, 8, 6)
