@@ -68,7 +68,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   const uint32_t tmem_acc = *tmem_holder_ptr;
 
   if (warp == 0) {
-    if (lane == 0) {
+    if (elect_one()) {
       for (int i = 0; i < nkb; ++i) {
         const int s = i % STAGES, ph = (i / STAGES) & 1;
         mbar_wait(bar_empty + 8 * s, ph ^ 1);
@@ -90,7 +90,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
+    if (elect_one()) {
       // instruction descriptor: D fp32, A/B bf16, majors, N>>3, M>>4
       const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((A_KMAJOR ? 0u : 1u) << 15) |
                              ((B_KMAJOR ? 0u : 1u) << 16) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);

@@ -73,6 +73,7 @@ struct TcRnnArgs {
   __nv_bfloat16 *partial; // [nclusters][2][CS][H][N] partial d(h), bf16
   const uint8_t *wimg;    // per-rank shared-memory images of the weight operand
   int wimg_bytes;
+  int a_tmem;             // forward: weights live in tensor memory (wimg is plain row-major [128][nkb*64] bf16)
   int debug;              // SKRNN_TC_DEBUG=1: one CTA prints its per-phase cycle split
 };
 
@@ -98,8 +99,8 @@ lstm_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_h, const __grid_consta
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   uint8_t *gbase = smem_raw + (base - smem_u32(smem_raw));
   const int H = a.H, G = a.G, B = a.B, T = a.T, nkb = a.nkb;
-  const uint32_t s_w = base;                                  // nkb x [128 rows][128 B]
-  const uint32_t s_h = s_w + (uint32_t)nkb * 16384u;          // nkb x [N rows][128 B]
+  const uint32_t s_w = base;                                  // nkb x [128 rows][128 B] (unless weights sit in TMEM)
+  const uint32_t s_h = s_w + (a.a_tmem ? 0u : (uint32_t)nkb * 16384u);  // nkb x [N rows][128 B]
   const uint32_t s_xw = s_h + (uint32_t)nkb * (N * 128);      // 4 planes x [N][32] fp32
   const uint32_t s_init = s_xw + 4u * (N * 128);              // [2][N][32] fp32: fed c / h (eoc reset source)
   const uint32_t s_bar = s_init + 2u * N * 128;
@@ -117,7 +118,7 @@ lstm_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_h, const __grid_consta
   const int u0 = rank * 32;
   const int S = 2 * H;
 
-  {  // resident weight operand: straight copy of this rank's pre-swizzled image
+  if (!a.a_tmem) {  // resident weight operand: straight copy of this rank's pre-swizzled image
     const uint4 *src = reinterpret_cast<const uint4 *>(a.wimg + (size_t)rank * a.wimg_bytes);
     uint4 *dst = reinterpret_cast<uint4 *>(gbase + (s_w - base));
     for (int i = tid; i < a.wimg_bytes / 16; i += TCR_THREADS) dst[i] = __ldg(src + i);
@@ -161,6 +162,23 @@ lstm_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_h, const __grid_consta
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_acc = *tmem_holder_ptr;
+  const uint32_t tmem_a = tmem_acc + (uint32_t)((N + 31) / 32 * 32);  // weight operand columns, after the accumulator
+  if (a.a_tmem && warp >= 2 && warp < 6) {
+    // row e = 32q + lane of the weight slice: nkb*64 bf16 = nkb*32 packed columns, 32 columns per tcgen05.st
+    const uint32_t *src = reinterpret_cast<const uint32_t *>(a.wimg + (size_t)rank * a.wimg_bytes) + (size_t)e * (nkb * 32);
+    for (int cb = 0; cb < nkb; ++cb) {
+      uint32_t v[32];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const uint4 x = __ldg(reinterpret_cast<const uint4 *>(src + cb * 32) + j);
+        v[4 * j] = x.x; v[4 * j + 1] = x.y; v[4 * j + 2] = x.z; v[4 * j + 3] = x.w;
+      }
+      tc_st32(tmem_a + ((uint32_t)(32 * q) << 16) + (uint32_t)(cb * 32), v);
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
   cluster_sync_all();
 
   const uint32_t idesc = make_idesc_bf16(128, N, false, false);
@@ -171,32 +189,37 @@ lstm_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_h, const __grid_consta
     dB[kb] = make_desc(s_h + (uint32_t)kb * (N * 128), 0, 1024);
   }
   long long tk[6] = {0, 0, 0, 0, 0, 0};
-  const bool dbg = a.debug && rank == 0 && cluster_id_x() == 0 && (tid == 64 || tid == 32);
+  const bool dbg = a.debug && rank == 0 && cluster_id_x() == 0 && (tid == 64 || warp == 1);
 
   for (int t = 0; t < T; ++t) {
     long long c0 = 0, c1 = 0, c2 = 0, c3 = 0;
     if (dbg) c0 = clock64();
     if (warp == 0) {
-      if (lane == 0) {
+      if (elect_one()) {
         mbar_expect_tx(bar_xw, 4 * N * 128);
         tma_load_4d(s_xw, &tm_xw, bar_xw, u0, b0, 0, t);  // the 4 gate planes of my units in one box
       }
     } else if (warp == 1) {
-      if (lane == 0) {
-        mbar_wait(bar_h, t & 1);
-        if (dbg) { c1 = clock64(); c2 = c1; }
-        tc_fence_after();
+      mbar_wait(bar_h, t & 1);
+      if (dbg) { c1 = clock64(); c2 = c1; }
+      tc_fence_after();
+      if (elect_one()) {
 #pragma unroll
         for (int kb = 0; kb < 8; ++kb) {
           if (kb < nkb) {
 #pragma unroll
-            for (int k = 0; k < 4; ++k)
-              tc_mma_bf16(tmem_acc, dA[kb] + (uint64_t)(2 * k), dB[kb] + (uint64_t)(2 * k), idesc, (kb > 0 || k > 0) ? 1u : 0u);
+            for (int k = 0; k < 4; ++k) {
+              if (a.a_tmem)
+                tc_mma_bf16_ts(tmem_acc, tmem_a + (uint32_t)(kb * 32 + k * 8), dB[kb] + (uint64_t)(2 * k), idesc, (kb > 0 || k > 0) ? 1u : 0u);
+              else
+                tc_mma_bf16(tmem_acc, dA[kb] + (uint64_t)(2 * k), dB[kb] + (uint64_t)(2 * k), idesc, (kb > 0 || k > 0) ? 1u : 0u);
+            }
           }
         }
         tc_commit(bar_acc);
-        if (dbg) { c3 = clock64(); tk[0] += c1 - c0; tk[1] += c2 - c1; tk[2] += c3 - c2; }
       }
+      __syncwarp();
+      if (dbg) { c3 = clock64(); tk[0] += c1 - c0; tk[1] += c2 - c1; tk[2] += c3 - c2; }
     } else {
       // h_{t-1} tile of my cluster's rows (all H units, written by all ranks last step): L2 -> swizzled smem
       {
@@ -391,7 +414,7 @@ lstm_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm_acts, TcRnnArgs a) {
   for (int t = T - 1, step = 0; t >= 0; --t, ++step) {
     const int par = step & 1;
     if (warp == 0) {
-      if (lane == 0) {
+      if (elect_one()) {
         mbar_expect_tx(bar_acts, 4 * N * 128);
         tma_load_4d(s_ac, &tm_acts, bar_acts, u0, b0, 0, t);
       }
@@ -451,9 +474,9 @@ lstm_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm_acts, TcRnnArgs a) {
     }
     if (t > 0) {
       if (warp == 1) {
-        if (lane == 0) {
-          mbar_wait(bar_ready, step & 1);
-          tc_fence_after();
+        mbar_wait(bar_ready, step & 1);
+        tc_fence_after();
+        if (elect_one()) {
           for (int mt = 0; mt < nmt; ++mt) {
 #pragma unroll
             for (int kb = 0; kb < 2; ++kb) {
@@ -466,6 +489,7 @@ lstm_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm_acts, TcRnnArgs a) {
           }
           tc_commit(bar_acc);
         }
+        __syncwarp();
       } else if (warp >= 2) {
         mbar_wait(bar_acc, step & 1);
         tc_fence_after();
@@ -542,7 +566,11 @@ __global__ void pack_tc_image_kernel(int bwd, const float *__restrict__ mat, int
     const int chunk = within >> 3, el = within & 7;
     const int kloc = ((chunk ^ (m & 7)) << 3) + el;  // un-swizzle: logical k within the block
     const int k = kb * 64 + kloc;
-    if (!bwd) {
+    if (bwd == 2) {  // forward weights for tensor memory: plain row-major [128 rows m=4u+g][nkb*64]
+      const int mm = (int)(o / ((int64_t)nkb * 64)), kk2 = (int)(o % ((int64_t)nkb * 64));
+      const int u = mm >> 2, g = mm & 3;
+      if (kk2 < H) v = mat[(size_t)(I + kk2) * G + g * H + u0 + u];
+    } else if (!bwd) {
       const int u = m >> 2, g = m & 3;
       if (k < H) v = mat[(size_t)(I + k) * G + g * H + u0 + u];
     } else {
@@ -589,10 +617,10 @@ int launch_bwd(const CUtensorMap &tm_acts, const TcRnnArgs &a, int nclusters, si
   return 0;
 }
 
-size_t smem_need(bool bwd, int H, int N) {
+size_t smem_need(bool bwd, int H, int N, bool a_tmem) {
   const int nkb = (H + 63) / 64, HP = (H + 127) / 128 * 128;
   size_t s = bwd ? (size_t)2 * HP * 128 + 2 * (size_t)N * 128 + 4 * (size_t)N * 128
-                 : (size_t)nkb * 16384 + (size_t)nkb * N * 128 + 4 * (size_t)N * 128 + 2 * (size_t)N * 128;
+                 : (a_tmem ? 0 : (size_t)nkb * 16384) + (size_t)nkb * N * 128 + 4 * (size_t)N * 128 + 2 * (size_t)N * 128;
   return s + 1024 + 256;
 }
 
@@ -613,30 +641,35 @@ int sk_rnn_tc_layer(skrnn_handle *h, cudaStream_t st, bool bwd, int l, int B, in
   const int CS = H / 32;
   const int nkb = (H + 63) / 64, HP = (H + 127) / 128 * 128;
   // batch tile: the smallest N whose cluster count fits on the GPU at once, within shared memory / TMEM
+  static int atm_env = -1;
+  if (atm_env < 0) { const char *e = getenv("SKRNN_TC_ATMEM"); atm_env = (e && e[0] == '0') ? 0 : 1; }
+  const bool a_tmem = !bwd && atm_env;
   int N = 0;
   const int cap_clusters = std::max(1, h->num_sms / CS - (CS >= 8 ? 2 : 0));
   for (int cand : {16, 32, 64, 128}) {
-    if (smem_need(bwd, H, cand) > 227 * 1024) break;
+    if (smem_need(bwd, H, cand, a_tmem) > 227 * 1024) break;
+    if (a_tmem && (cand + 31) / 32 * 32 + nkb * 32 > 512) break;
     if (bwd && (HP / 128) * cand > 512) break;
     N = cand;
     if ((B + cand - 1) / cand <= cap_clusters) break;
   }
   if (N == 0) return -1;
   const int nclusters = (B + N - 1) / N;
-  const size_t smem = smem_need(bwd, H, N);
+  const size_t smem = smem_need(bwd, H, N, a_tmem);
   const int img_bytes = bwd ? 2 * HP * 128 : nkb * 16384;
   SK_CHECK((int64_t)img_bytes * CS <= h->ws.wpack_floats * 4, "weight image workspace too small");
   {
     SkLaunch scope(h, st, SK_CAT_MISC);
     int64_t total = (int64_t)img_bytes / 2 * CS;
     int blocks = (int)std::min<int64_t>((total + 255) / 256, (int64_t)4 * h->num_sms);
-    pack_tc_image_kernel<<<blocks, 256, 0, st>>>(bwd ? 1 : 0, h->params + h->lp[l].w[0], h->lp[l].I, H, CS, nkb, HP,
+    pack_tc_image_kernel<<<blocks, 256, 0, st>>>(bwd ? 1 : (a_tmem ? 2 : 0), h->params + h->lp[l].w[0], h->lp[l].I, H, CS, nkb, HP,
                                                 img_bytes, reinterpret_cast<uint8_t *>(h->ws.wpack));
     SK_CUDA(cudaGetLastError());
   }
   TcRnnArgs a = {};
   a.B = B; a.T = T; a.H = H; a.G = h->G; a.N = N; a.CS = CS; a.nkb = nkb;
-  int cols = bwd ? (HP / 128) * N : N;
+  int cols = bwd ? (HP / 128) * N : (a_tmem ? (N + 31) / 32 * 32 + nkb * 32 : N);
+  a.a_tmem = a_tmem ? 1 : 0;
   int tc = 32;
   while (tc < cols) tc <<= 1;
   a.tmem_cols = tc;
