@@ -1,0 +1,197 @@
+"""Data path and drawing helpers with the reference's names and behaviour (reference utils.py).
+
+`SketchLoader` keeps the reference semantics line for line (utils.py:105-283) -- same `.cpkl`
+format, same batch layout, same order of `np.random` calls -- so a given NumPy seed produces the
+same batches as the Python 2 original would.  The SVG writer emits the same document structure
+as `draw_stroke_color_array` (utils.py:32-83) as plain text (svgwrite / IPython are not needed).
+"""
+import os
+import pickle
+import random
+
+import numpy as np
+
+
+def calculate_start_point(data, factor=1.0, block_size=200):
+    """Reference utils.py:10-30: running-sum bounding box with per-step round(.., 3)."""
+    sx = sy = 0
+    maxx = minx = maxy = miny = 0
+    for i in range(len(data)):
+        sx += round(float(data[i, 0]) * factor, 3)
+        sy += round(float(data[i, 1]) * factor, 3)
+        maxx = max(maxx, sx)
+        minx = min(minx, sx)
+        maxy = max(maxy, sy)
+        miny = min(miny, sy)
+    abs_x = block_size / 2 - (maxx - minx) / 2 - minx
+    abs_y = block_size / 2 - (maxy - miny) / 2 - miny
+    return abs_x, abs_y, (maxx - minx), (maxy - miny)
+
+
+def draw_stroke_color_array(data, factor=1, svg_filename="sample.svg", stroke_width=1, block_size=200,
+                            maxcol=5, svg_only=False, color_mode=True):
+    """Reference utils.py:32-83 as a plain-text SVG writer (svgwrite / IPython are not needed): a white
+    rectangle, then for every sketch j (cell j % maxcol, j // maxcol of a grid of block_size cells,
+    centred by calculate_start_point) one <path> per point -- "M prev L cur" while the pen is down,
+    a bare "M cur" right after a pen lift -- stroked and filled in a colour that is re-drawn from
+    random.randint(0, 225)^3 after every lift (utils.py:45,69), or "#000" when color_mode is False."""
+    num_char = len(data)
+    if num_char < 1:
+        return None
+    max_color_intensity = 225
+
+    def new_color():
+        return "rgb(%d,%d,%d)" % (random.randint(0, max_color_intensity), random.randint(0, max_color_intensity),
+                                  random.randint(0, max_color_intensity))
+
+    numrow = np.ceil(float(num_char) / float(maxcol))
+    width, height = block_size * (min(num_char, maxcol)), block_size * numrow
+    out = ['<?xml version="1.0" encoding="utf-8" ?>',
+           '<svg baseProfile="full" height="%s" version="1.1" width="%s" xmlns="http://www.w3.org/2000/svg" '
+           'xmlns:ev="http://www.w3.org/2001/xml-events" xmlns:xlink="http://www.w3.org/1999/xlink"><defs />'
+           % (height, width),
+           '<rect fill="white" height="%s" width="%s" x="0" y="0" />' % (height, width)]
+    the_color = new_color()
+    for j in range(num_char):
+        lift_pen = 0
+        cdata = data[j]
+        abs_x, abs_y, _, _ = calculate_start_point(cdata, factor, block_size)
+        abs_x += (j % maxcol) * block_size
+        abs_y += (j // maxcol) * block_size
+        for i in range(len(cdata)):
+            x = round(float(cdata[i, 0]) * factor, 3)
+            y = round(float(cdata[i, 1]) * factor, 3)
+            prev_x, prev_y = round(abs_x, 3), round(abs_y, 3)
+            abs_x += x
+            abs_y += y
+            if lift_pen == 1:
+                p = "M %s,%s " % (abs_x, abs_y)
+                the_color = new_color()
+            else:
+                p = "M %s,%s L %s,%s " % (prev_x, prev_y, abs_x, abs_y)
+            lift_pen = max(cdata[i, 2], cdata[i, 3])  # lift pen on eos or eoc
+            if not color_mode:
+                the_color = "#000"
+            out.append('<path d="%s" fill="%s" stroke="%s" stroke-width="%s" />' % (p, the_color, the_color, stroke_width))
+    out.append("</svg>")
+    text = "".join(out)
+    if svg_filename:
+        with open(svg_filename, "w") as f:
+            f.write(text)
+    return text
+
+
+def draw_stroke_color(data, factor=1, svg_filename="sample.svg", stroke_width=1, block_size=200, maxcol=5,
+                      svg_only=False, color_mode=True):
+    """Reference utils.py:85-103: split one long stroke sequence at the eoc points and draw the pieces."""
+    def split_sketch(d):  # one piece per eoc; the trailing stub without an eoc is dropped
+        counter, result = 0, []
+        for i in range(len(d)):
+            if d[i, 3] > 0:
+                result.append(d[counter:i + 1])
+                counter = i + 1
+        return result
+    data = np.array(data, dtype=np.float32)
+    return draw_stroke_color_array(split_sketch(data), factor, svg_filename, stroke_width, block_size, maxcol,
+                                   svg_only, color_mode)
+
+
+class SketchLoader(object):
+    """The reference's data path (utils.py:105-283) with the per-point Python loop replaced by a
+    per-sketch copy: batches are identical, element for element, for the same `np.random` state.
+
+    What the reference's `next_seq` does, restated: a row of T+1 points walks the corpus from the
+    current pointer; sketch i contributes its first max(1, len_i - 1) raw points (the last raw point is
+    never emitted), the last contributed point is forced to (eos, eoc, cont) = (0, 1, 0), every other
+    point gets cont = 1 unless its eos/eoc is set; a fully consumed sketch advances the pointer, and the
+    pointer advances once more at the end of the row (utils.py:245-253).  Per row two `np.random.rand()`
+    draws scale x and y by U[0.7, 1.3) (utils.py:235-236) and they are drawn before the walk.
+    `data/<name>.cpkl` is a pickled list of float32 [N_i,4] arrays (dx, dy, eos, eoc); a Python 2 pickle
+    loads with encoding='latin1'."""
+
+    def __init__(self, batch_size=50, seq_length=300, scale_factor=1.0, data_filename="kanji", data_dir="./data"):
+        self.data_dir = data_dir
+        self.batch_size = batch_size
+        self.seq_length = seq_length
+        self.scale_factor = scale_factor  # raw coordinates are divided by this
+        data_file = os.path.join(self.data_dir, data_filename + ".cpkl")
+        if not os.path.exists(data_file):
+            # the reference would build the file from raw SVGs here (utils.py:115-117); that preprocessing
+            # step is outside this repository's scope
+            raise IOError("%s not found: build it with the reference's preprocess step" % data_file)
+        self.load_preprocessed(data_file)
+        self.num_samples = len(self.raw_data)
+        self.index = list(range(self.num_samples))
+        self.reset_index_pointer()
+
+    def load_preprocessed(self, data_file):
+        with open(data_file, "rb") as f:
+            raw = pickle.load(f, encoding="latin1")
+        self.raw_data = []
+        self._emit = []  # per sketch: the [m,5] block a row copies while walking over it
+        for d in raw:
+            d = np.array(d, dtype=np.float32)
+            d[:, 0:2] /= self.scale_factor
+            self.raw_data.append(d)
+            m = max(1, len(d) - 1)
+            blk = np.zeros((m, 5), dtype=np.float32)
+            blk[:, 0:4] = d[:m]
+            blk[:, 4] = ((blk[:, 2] <= 0) & (blk[:, 3] <= 0)).astype(np.float32)
+            blk[m - 1, 2:5] = (0.0, 1.0, 0.0)  # end of content overrides end of stroke
+            self._emit.append(blk)
+
+    def _next_row(self, n):
+        sx = np.random.rand() * 0.6 + 0.7
+        sy = np.random.rand() * 0.6 + 0.7
+        row = np.empty((n, 5), dtype=np.float32)
+        filled = 0
+        while filled < n:
+            blk = self._emit[self.index[self.pointer]]
+            take = min(len(blk), n - filled)
+            row[filled:filled + take] = blk[:take]
+            filled += take
+            if take == len(blk):
+                self.tick_index_pointer()
+        self.tick_index_pointer()
+        row[:, 0] *= sx
+        row[:, 1] *= sy
+        return row
+
+    def next_batch(self):
+        """(inputs, targets) = (batch[:, :-1], batch[:, 1:]) of a [B, T+1, 5] batch (utils.py:258-268)."""
+        batch = np.stack([self._next_row(self.seq_length + 1) for _ in range(self.batch_size)]).astype(np.float32)
+        return batch[:, 0:-1], batch[:, 1:]
+
+    def current_data(self):
+        return self.raw_data[self.index[self.pointer]]
+
+    def tick_index_pointer(self):
+        self.pointer += 1
+        if self.pointer >= len(self.raw_data):
+            self.pointer = 0
+            self.epoch_finished = True
+
+    def reset_index_pointer(self):
+        """New epoch: pointer to 0 and a fresh np.random.permutation of the sketch order (utils.py:279-283)."""
+        self.pointer = 0
+        self.epoch_finished = False
+        self.index = np.random.permutation(self.index)
+
+
+def make_synthetic_dataset(path, num_sketches=200, seed=0):
+    """Writes a stand-in corpus in the exact kanji.cpkl format (protocol-2 pickle of a list of float32
+    [N_i,4] arrays, utils.py:190-195,214-215): the real KanjiVG blob is not distributed with the reference."""
+    rng = np.random.RandomState(seed)
+    sketches = []
+    for _ in range(num_sketches):
+        n = int(rng.randint(20, 121))
+        d = np.zeros((n, 4), dtype=np.float32)
+        d[:, 0:2] = rng.normal(0.0, 8.0, size=(n, 2))
+        d[:, 2] = rng.rand(n) < 0.12
+        d[-1, 2] = 1
+        d[-1, 3] = 1
+        sketches.append(d)
+    os.makedirs(os.path.dirname(os.path.abspath(path)), exist_ok=True)
+    with open(path, "wb") as f:
+        pickle.dump(sketches, f, protocol=2)
+    return path

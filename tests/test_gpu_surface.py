@@ -1,0 +1,103 @@
+"""The reference's Python surface on the GPU: Model(args, infer) / Session.run call patterns of train.py and
+sample.py, the state carry, checkpoints in save/<dataset>/, and the two scripts end to end on a synthetic
+corpus (the kanji blob is not distributed with the reference)."""
+import argparse
+import os
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+from oracle import sketch_oracle as so
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _args(**kw):
+    d = dict(rnn_size=32, num_layers=2, model="lstm", batch_size=6, seq_length=8, num_epochs=1, save_every=250,
+             grad_clip=5.0, learning_rate=0.005, decay_rate=0.99, num_mixture=4, data_scale=15.0, keep_prob=1.0,
+             stroke_importance_factor=200.0, dataset_name="toy")
+    d.update(kw)
+    return argparse.Namespace(**d)
+
+
+def test_session_run_patterns_match_oracle():
+    from sketch_rnn_b200.model import Model, Session
+    args = _args()
+    model = Model(args, precision="f32")
+    sess = Session(model)
+    cfg = so.Config(model="lstm", rnn_size=32, num_layers=2, num_mixture=4, batch_size=6, seq_length=8, keep_prob=1.0)
+    params = {k: v.astype(np.float64) for k, v in model.handle.get_params_dict().items()}
+    opt = so.AdamState(cfg, dtype=np.float64)
+    x, y = so.synthetic_batch(6, 8, seed=3, p_eoc=0.1)
+    sess.run(model.assign_lr(0.005 * 0.99 ** 2))
+    state = sess.run(model.initial_state)
+    assert len(state) == 2 and state[0].shape == (6, 64) and not state[0].any()
+    st_ref = so.zero_state(cfg, 6, np.float64)
+    for _ in range(2):  # state carried across batches (train.py:85-86)
+        feed = {model.input_data: x, model.target_data: y, model.initial_state: state}
+        loss, ls, lp, state, _ = sess.run([model.cost, model.cost_shape, model.cost_pen, model.final_state,
+                                          model.train_op], feed)
+        ref, st_ref, _ = so.train_step(cfg, params, opt, x.astype(np.float64), y.astype(np.float64), st_ref,
+                                       0.005 * 0.99 ** 2)
+        assert abs(loss - ref[0]) < 1e-4 * abs(ref[0]) and abs(lp - ref[2]) < 1e-4 * abs(ref[2])
+        assert np.allclose(state[1], st_ref[1], atol=1e-5)
+    out = sess.run([model.pi, model.sigma1, model.pen, model.final_state], {model.input_data: x, model.initial_state: state})
+    fw = so.forward(cfg, params, x.astype(np.float64), [s.astype(np.float64) for s in state])
+    assert np.allclose(out[0], fw["mdn"]["pi"], atol=1e-4) and np.allclose(out[1], fw["mdn"]["sigma1"], rtol=1e-4)
+
+
+def test_infer_mutates_args_and_sample_signature():
+    from sketch_rnn_b200.model import Model
+    args = _args(batch_size=100, seq_length=300)
+    model = Model(args, True)
+    assert args.batch_size == 1 and args.seq_length == 1  # model.py:9-11
+    np.random.seed(0)
+    strokes, params = model.sample(None, 30, 0.5, 0.5, stop_if_eoc=False)
+    assert strokes.shape == (30, 5) and strokes.dtype == np.float32 and len(params) == 30
+    assert len(params[0]) == 7 and params[0][0].shape == (4,) and params[0][6].shape == (3,)
+    assert np.all(strokes[:, 2:].sum(1) == 1)
+    with pytest.raises(Exception, match="model type not supported: foo"):
+        Model(_args(model="foo"))
+
+
+def test_checkpoint_roundtrip(tmp_path):
+    from sketch_rnn_b200.model import Model, Saver, Session, get_checkpoint_state
+    args = _args()
+    m1 = Model(args, precision="f32", seed=5)
+    x, y = so.synthetic_batch(6, 8, seed=3)
+    m1.lr = 0.004
+    m1.train_step(x, y)
+    d = tmp_path / "save" / "toy"
+    d.mkdir(parents=True)
+    Saver(m1).save(Session(m1), str(d / "model.ckpt"), global_step=7)
+    ck = get_checkpoint_state(str(d))
+    assert ck.model_checkpoint_path.endswith("model.ckpt-7")
+    m2 = Model(_args(), precision="f32", seed=9)
+    Saver(m2).restore(Session(m2), ck.model_checkpoint_path)
+    v1, v2 = m1.variables(), m2.variables()
+    assert set(v1) == set(v2) and "rnn_mdn/output_w/Adam_1" in v1 and "beta2_power" in v1
+    for k in v1:
+        assert np.array_equal(np.asarray(v1[k]), np.asarray(v2[k])), k
+    a = m1.train_step(x, y)
+    b = m2.train_step(x, y)
+    assert a[0] == b[0]
+
+
+def test_train_and_sample_scripts_end_to_end(tmp_path):
+    from sketch_rnn_b200 import utils
+    utils.make_synthetic_dataset(str(tmp_path / "data" / "toy.cpkl"), num_sketches=40, seed=1)
+    env = dict(os.environ, PYTHONPATH=ROOT)
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "train.py"), "--dataset_name", "toy", "--rnn_size", "32",
+                        "--num_mixture", "4", "--batch_size", "8", "--seq_length", "20", "--num_epochs", "2",
+                        "--max_batches", "3"], cwd=str(tmp_path), env=env, capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stderr[-2000:]
+    assert "(epoch 0 batch 1), cost = " in r.stdout and "model saved to" in r.stdout
+    assert os.path.exists(str(tmp_path / "save" / "toy" / "config.pkl"))
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "sample.py"), "--dataset_name", "toy", "--num_picture", "2",
+                        "--sample_length", "40", "--max_attempts", "30", "--filename", "out", "--temperature", "0.5"],
+                       cwd=str(tmp_path), env=env, capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stderr[-2000:]
+    assert "loading model: " in r.stdout
