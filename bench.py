@@ -184,7 +184,7 @@ def run_ours(args, w):
     import torch
     import torch.distributed as dist
     from oracle import sketch_oracle as so   # synthetic inputs + initialiser only (not timed)
-    from sketch_rnn_b200 import _lib
+    from sketch_rnn_b200 import _lib, dp
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -225,11 +225,7 @@ def run_ours(args, w):
 
         def step(i):
             nonlocal state
-            losses, state = h.loss_grad(x, y, state, seed=1000 + i, row0=rank * Bl, loss_rows=loss_rows)
-            if world > 1:
-                dist.all_reduce(h.grads_tensor())
-                dist.all_reduce(losses)
-            h.apply_clip_adam(lr)
+            losses, state = dp.dp_train_step(h, x, y, state, lr, 1000 + i, rank * Bl, loss_rows)
             return losses
 
         units_per_step = w["B"] * T
@@ -329,7 +325,7 @@ def run_ours(args, w):
             flops_step = 1.0 * fl * Bl * T
         # dominant kernel by measured time
         dom = max(kern_ms, key=kern_ms.get) if kern_ms else None
-        tc = args.precision == "bf16"
+        tc = args.precision == "bf16" and w["kind"] == "train"
         peak = peaks["tc_sustained"] if tc else 2 * 128 * 148 * 1.965e-3  # fp32 CUDA-core TFLOP/s nominal
         ach = flops_step / (ms_per_step * 1e-3) / 1e12
         roof = {"bound": "tensor", "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": ach / peak,
@@ -343,7 +339,7 @@ def run_ours(args, w):
             cb = {"value": v, "unit": u, "cores": cores, "kind": "port", "sample": sample}
         line = {"metric": metric, "value": value, "unit": unit, "n_gpus": world, "steps": args.steps,
                 "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True,
-                "scaling": "strong", "vs_baseline": None, "dtype": args.precision, "data": "synthetic",
+                "scaling": "strong", "vs_baseline": None, "dtype": args.precision if w["kind"] == "train" else "f32", "data": "synthetic",
                 "config": workload_config(args, w), "clocks": clk, "e2e": e2e,
                 "gpu_launches": int(launches), "roofline": roof, "cpu_baseline": cb,
                 "last_loss": [float(v) for v in last.float().cpu().numpy()[:3]] if w["kind"] == "train" else None}
@@ -360,7 +356,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="train_h512_l3_b800", choices=sorted(WORKLOADS))
-    ap.add_argument("--precision", default="f32", choices=["f32", "bf16"])
+    ap.add_argument("--precision", default="bf16", choices=["f32", "bf16"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     args = ap.parse_args()
     w = WORKLOADS[args.workload]
