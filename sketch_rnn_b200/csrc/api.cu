@@ -69,6 +69,8 @@ void free_workspace(SkWorkspace &w) {
   }
   cudaFree(w.dout);
   cudaFree(w.logits);
+  cudaFree(w.eoc);
+  w.eoc = nullptr;
   w.x_tm = w.dout = w.logits = nullptr;
   cudaFree(w.x8_bf);
   cudaFree(w.dpre_bf);
@@ -90,6 +92,7 @@ int ensure_workspace(skrnn_handle *h, int B, int T) {
   SK_CUDA(cudaDeviceSynchronize());
   free_workspace(w);
   SK_CUDA(cudaMalloc(&w.x_tm, rows * 5 * sizeof(float)));
+  SK_CUDA(cudaMalloc(&w.eoc, rows));
   for (int l = 0; l < h->L; ++l) {
     SK_CUDA(cudaMalloc(&w.xw[l], rows * h->G * sizeof(float)));
     SK_CUDA(cudaMalloc(&w.hprev[l], rows * h->H * sizeof(float)));
@@ -154,6 +157,13 @@ int gemm(skrnn_handle *h, cudaStream_t st, int M, int N, int K, Op A, bool a_kc,
   if (h->cfg.precision == SKRNN_PREC_BF16)
     return sk_gemm_tc(h, st, M, N, K, A.b, A.ldb, a_kc, B.b, B.ldb, !b_nc, C, ldc, bias, accumulate);
   return sk_gemm_f32(h, st, M, N, K, A.f, A.ldf, a_kc, B.f, B.ldf, b_nc, C, ldc, bias, accumulate);
+}
+
+// d(bias) = column sums of d(pre-activation); the bf16 path reads the bf16 mirror (the tcgen05 BPTT kernel
+// does not write an fp32 copy)
+int bias_grad(skrnn_handle *h, cudaStream_t st, Op d, int64_t rows, int cols, float *out) {
+  if (h->cfg.precision == SKRNN_PREC_BF16) return sk_colsum_bf16(h, st, d.b, rows, cols, d.ldb, out);
+  return sk_colsum(h, st, d.f, rows, cols, d.ldf, out);
 }
 
 // forward unroll of the whole stack + output projection (model.py:97-99)
@@ -444,10 +454,10 @@ int skrnn_loss_grad(skrnn_handle *h, int32_t B, int32_t T, const float *x_dev, c
       float *gWg = h->grads + lp.w[0], *gWc = h->grads + lp.w[1];
       SK_TRY(gemm(h, st, I, 2 * H, R, X, false, dg, true, gWg, 2 * H, nullptr, true));
       SK_TRY(gemm(h, st, H, 2 * H, R, hprev_op(h, l), false, dg, true, gWg + (size_t)I * 2 * H, 2 * H, nullptr, true));
-      SK_TRY(sk_colsum(h, st, dg.f, R, 2 * H, G, h->grads + lp.b[0]));
+      SK_TRY(bias_grad(h, st, dg, R, 2 * H, h->grads + lp.b[0]));
       SK_TRY(gemm(h, st, I, H, R, X, false, dc, true, gWc, H, nullptr, true));
       SK_TRY(gemm(h, st, H, H, R, aux_op(h, l), false, dc, true, gWc + (size_t)I * H, H, nullptr, true));
-      SK_TRY(sk_colsum(h, st, dc.f, R, H, G, h->grads + lp.b[1]));
+      SK_TRY(bias_grad(h, st, dc, R, H, h->grads + lp.b[1]));
       if (l > 0) {
         SK_TRY(gemm(h, st, R, I, 2 * H, dg, true, weight(h, l, 0), false, h->ws.dout, H, nullptr, false));
         SK_TRY(gemm(h, st, R, I, H, dc, true, weight(h, l, 1), false, h->ws.dout, H, nullptr, true));
@@ -456,7 +466,7 @@ int skrnn_loss_grad(skrnn_handle *h, int32_t B, int32_t T, const float *x_dev, c
       float *gW = h->grads + lp.w[0];
       SK_TRY(gemm(h, st, I, G, R, X, false, dpre, true, gW, G, nullptr, true));
       SK_TRY(gemm(h, st, H, G, R, hprev_op(h, l), false, dpre, true, gW + (size_t)I * G, G, nullptr, true));
-      SK_TRY(sk_colsum(h, st, dpre.f, R, G, G, h->grads + lp.b[0]));
+      SK_TRY(bias_grad(h, st, dpre, R, G, h->grads + lp.b[0]));
       if (l > 0) SK_TRY(gemm(h, st, R, I, G, dpre, true, weight(h, l, 0), false, h->ws.dout, H, nullptr, false));
     }
   }

@@ -56,6 +56,7 @@ struct SkWorkspace {   // time-major activations for one (B, T) capacity
   int64_t cap_rows = 0;  // T*B rows allocated
   int capB = 0, capT = 0;
   float *x_tm = nullptr;                    // [T,B,5]
+  unsigned char *eoc = nullptr;             // [T,B]: x[b,t,3] > 0
   float *xw[SK_MAX_LAYERS] = {nullptr};     // [T,B,G]: input projection -> gate activations -> d(pre)
   float *hprev[SK_MAX_LAYERS] = {nullptr};  // [T,B,H]: h fed to step t (post eoc reset)
   float *cprev[SK_MAX_LAYERS] = {nullptr};  // [T,B,H]: lstm c fed to step t; gru: r*h of step t
@@ -106,6 +107,7 @@ struct skrnn_handle {
   int64_t launches = 0;
   int cluster_size = 1;
   bool tc_rnn_disabled = false;
+  bool nt_rnn_disabled = false;
   // optional per-category kernel timing (skrnn_profile_*): CUDA events around every launch
   bool prof_on = false;
   struct ProfRec { int cat; cudaEvent_t a, b; };
@@ -144,10 +146,15 @@ extern uint32_t g_tc_override[6];
 // 128B-swizzled tiled tensor map (rank 2 or 3).  elem_bytes: 2 (bf16) or 4 (fp32).
 int sk_make_tmap(CUtensorMap *m, int elem_bytes, const void *ptr, int rank, const uint64_t *dims,
                  const uint64_t *strides_bytes, const uint32_t *box);
+// tcgen05 recurrent kernels, large-batch variant (rnn_nt.cu): 0 ok, -1 not applicable
+int sk_rnn_nt_layer(skrnn_handle *h, cudaStream_t st, bool bwd, int l, int B, int T, const float *state_in,
+                    float *state_out, const float *mask, uint64_t seed, int row0, bool training);
 // tcgen05 recurrent kernels (rnn_tc.cu): return 0 ok, <0 "not eligible, use the fp32 kernels", >0 error
 int sk_rnn_tc_layer(skrnn_handle *h, cudaStream_t st, bool bwd, int l, int B, int T, const float *x_bt5,
                     const float *state_in, float *state_out, const float *mask, uint64_t seed, int row0,
                     bool training);
+int sk_colsum_bf16(skrnn_handle *h, cudaStream_t st, const __nv_bfloat16 *A, int64_t rows, int cols, int lda,
+                   float *out);
 int sk_colsum(skrnn_handle *h, cudaStream_t st, const float *A, int64_t rows, int cols, int lda,
               float *out);  // out[c] += sum_r A[r][c]
 

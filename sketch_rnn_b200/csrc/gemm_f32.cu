@@ -159,8 +159,27 @@ __global__ void colsum_kernel(const float *__restrict__ A, int64_t rows, int col
   }
 }
 
+__global__ void colsum_bf16_kernel(const __nv_bfloat16 *__restrict__ A, int64_t rows, int cols, int lda,
+                                   int64_t rows_per_block, float *__restrict__ out) {
+  __shared__ float red[8][33];
+  int c = blockIdx.x * 32 + threadIdx.x;
+  int64_t r0 = (int64_t)blockIdx.y * rows_per_block;
+  int64_t r1 = min(rows, r0 + rows_per_block);
+  float s = 0.f;
+  if (c < cols)
+    for (int64_t r = r0 + threadIdx.y; r < r1; r += 8) s += __bfloat162float(A[r * lda + c]);
+  red[threadIdx.y][threadIdx.x] = s;
+  __syncthreads();
+  if (threadIdx.y == 0 && c < cols) {
+    float t = 0.f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) t += red[i][threadIdx.x];
+    atomicAdd(out + c, t);
+  }
+}
+
 __global__ void transpose_x_kernel(const float *__restrict__ x, float *__restrict__ x_tm,
-                                   __nv_bfloat16 *__restrict__ x8, int B, int T) {
+                                   __nv_bfloat16 *__restrict__ x8, unsigned char *__restrict__ eoc, int B, int T) {
   int64_t n = (int64_t)B * T * 5;
   for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
     int j = (int)(i % 5);
@@ -169,6 +188,7 @@ __global__ void transpose_x_kernel(const float *__restrict__ x, float *__restric
     int t = (int)(r / B);
     float v = x[((int64_t)b * T + t) * 5 + j];
     x_tm[i] = v;
+    if (j == 3) eoc[r] = v > 0.f ? 1 : 0;  // end-of-content flag of the step's input, time-major
     if (x8 != nullptr) x8[r * 8 + j] = __float2bfloat16_rn(v);  // columns 5..7 stay zero from allocation
   }
 }
@@ -229,11 +249,23 @@ int sk_colsum(skrnn_handle *h, cudaStream_t st, const float *A, int64_t rows, in
   return 0;
 }
 
+int sk_colsum_bf16(skrnn_handle *h, cudaStream_t st, const __nv_bfloat16 *A, int64_t rows, int cols, int lda,
+                   float *out) {
+  if (rows <= 0 || cols <= 0) return 0;
+  int gx = (cols + 31) / 32;
+  int gy = (int)std::min<int64_t>((rows + 255) / 256, (int64_t)std::max(1, 4 * h->num_sms / gx));
+  int64_t rpb = (rows + gy - 1) / gy;
+  SkLaunch scope(h, st, SK_CAT_MISC);
+  colsum_bf16_kernel<<<dim3(gx, gy), dim3(32, 8), 0, st>>>(A, rows, cols, lda, rpb, out);
+  SK_CUDA(cudaGetLastError());
+  return 0;
+}
+
 int sk_transpose_x(skrnn_handle *h, cudaStream_t st, int B, int T, const float *x_bt5) {
   int64_t n = (int64_t)B * T * 5;
   int blocks = (int)std::min<int64_t>((n + 255) / 256, (int64_t)8 * h->num_sms);
   SkLaunch scope(h, st, SK_CAT_MISC);
-  transpose_x_kernel<<<blocks, 256, 0, st>>>(x_bt5, h->ws.x_tm, h->ws.x8_bf, B, T);
+  transpose_x_kernel<<<blocks, 256, 0, st>>>(x_bt5, h->ws.x_tm, h->ws.x8_bf, h->ws.eoc, B, T);
   SK_CUDA(cudaGetLastError());
   return 0;
 }

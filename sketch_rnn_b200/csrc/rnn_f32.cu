@@ -540,6 +540,7 @@ int launch_cell(bool bwd, const Plan &p, const RnnArgs &a, int nc, cudaStream_t 
 int run_layer(skrnn_handle *h, cudaStream_t st, bool bwd, int l, int B, int T, const float *x_bt5,
               const float *state_in, float *state_out, const float *mask, uint64_t seed, int row0,
               bool training) {
+  if (sk_rnn_nt_layer(h, st, bwd, l, B, T, state_in, state_out, mask, seed, row0, training) == 0) return 0;
   {
     int rc = sk_rnn_tc_layer(h, st, bwd, l, B, T, x_bt5, state_in, state_out, mask, seed, row0, training);
     if (rc >= 0) return rc;  // handled by the tcgen05 kernels (0) or failed hard (>0)

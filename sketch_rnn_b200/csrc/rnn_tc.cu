@@ -60,7 +60,7 @@ struct TcRnnArgs {
   int row0, dropout;
   float keep;
   uint64_t seed;
-  const float *x_bt5;
+  const unsigned char *eoc;  // [T,B] end-of-content flag of the input at (t, b)
   const float *state_in;
   float *state_out;
   const float *mask;
@@ -73,6 +73,7 @@ struct TcRnnArgs {
   __nv_bfloat16 *partial; // [nclusters][2][CS][H][N] partial d(h), bf16
   const uint8_t *wimg;    // per-rank shared-memory images of the weight operand
   int wimg_bytes;
+  int mcast;              // forward: the h tile arrives by TMA multicast (each rank fetches 1/CS of it)
   int a_tmem;             // forward: weights live in tensor memory (wimg is plain row-major [128][nkb*64] bf16)
   int debug;              // SKRNN_TC_DEBUG=1: one CTA prints its per-phase cycle split
 };
@@ -98,7 +99,7 @@ lstm_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_h, const __grid_consta
   extern __shared__ uint8_t smem_raw[];
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   uint8_t *gbase = smem_raw + (base - smem_u32(smem_raw));
-  const int H = a.H, G = a.G, B = a.B, T = a.T, nkb = a.nkb;
+  const int H = a.H, B = a.B, T = a.T, nkb = a.nkb;
   const uint32_t s_w = base;                                  // nkb x [128 rows][128 B] (unless weights sit in TMEM)
   const uint32_t s_h = s_w + (a.a_tmem ? 0u : (uint32_t)nkb * 16384u);  // nkb x [N rows][128 B]
   const uint32_t s_xw = s_h + (uint32_t)nkb * (N * 128);      // 4 planes x [N][32] fp32
@@ -107,9 +108,10 @@ lstm_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_h, const __grid_consta
   const uint32_t bar_h = s_bar;          // [8]
   const uint32_t bar_acc = s_bar + 64;
   const uint32_t bar_xw = s_bar + 72;
+  const uint32_t bar_out = s_bar + 88;   // epilogue -> warp 0: gate activations are in the staging planes
   const uint32_t tmem_holder = s_bar + 80;
   volatile uint32_t *tmem_holder_ptr = reinterpret_cast<volatile uint32_t *>(gbase + (tmem_holder - base));
-  const uint8_t *xw_gen = gbase + (s_xw - base);
+  uint8_t *xw_gen = gbase + (s_xw - base);
   float *init_gen = reinterpret_cast<float *>(gbase + (s_init - base));
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -124,9 +126,10 @@ lstm_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_h, const __grid_consta
     for (int i = tid; i < a.wimg_bytes / 16; i += TCR_THREADS) dst[i] = __ldg(src + i);
   }
   if (tid == 0) {
-    mbar_init(bar_h, 32 * TCR_EPI_WARPS);
+    mbar_init(bar_h, a.mcast ? 1 : 32 * TCR_EPI_WARPS);
     mbar_init(bar_acc, 1);
     mbar_init(bar_xw, 1);
+    mbar_init(bar_out, 32 * TCR_EPI_WARPS);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 1) tc_alloc(tmem_holder, (uint32_t)a.tmem_cols);
@@ -157,7 +160,7 @@ lstm_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_h, const __grid_consta
       }
     }
   }
-  fence_proxy_async_smem();
+  fence_proxy_async();
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -196,9 +199,23 @@ lstm_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_h, const __grid_consta
     if (dbg) c0 = clock64();
     if (warp == 0) {
       if (elect_one()) {
+        if (a.mcast) {
+          // every rank expects the whole tile and fetches one half k-block of it for everybody
+          fence_proxy_async();
+          mbar_expect_tx(bar_h, nkb * N * 128);
+          const int kb = rank >> 1, half = rank & 1;
+          tma_load_3d_multicast(s_h + (uint32_t)kb * (N * 128) + (uint32_t)half * (N / 2) * 128, &tm_h, bar_h, kb * 64,
+                                b0 + half * (N / 2), t, (uint16_t)((1u << a.CS) - 1u));
+        }
         mbar_expect_tx(bar_xw, 4 * N * 128);
         tma_load_4d(s_xw, &tm_xw, bar_xw, u0, b0, 0, t);  // the 4 gate planes of my units in one box
+        // the epilogue overwrites the planes in place with the gate activations: one TMA store puts them
+        // back where the pre-activations came from (saved for BPTT)
+        mbar_wait(bar_out, t & 1);
+        tma_store_4d(&tm_xw, s_xw, u0, b0, 0, t);
+        tma_store_wait_read();
       }
+      __syncwarp();
     } else if (warp == 1) {
       mbar_wait(bar_h, t & 1);
       if (dbg) { c1 = clock64(); c2 = c1; }
@@ -222,16 +239,33 @@ lstm_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_h, const __grid_consta
       if (dbg) { c3 = clock64(); tk[0] += c1 - c0; tk[1] += c2 - c1; tk[2] += c3 - c2; }
     } else {
       // h_{t-1} tile of my cluster's rows (all H units, written by all ranks last step): L2 -> swizzled smem
-      {
+      if (!a.mcast) {
         const int cpr = H >> 3;  // 16-byte chunks per row
         const int et = tid - 64;
-        for (int i = et; i < N * cpr; i += 32 * TCR_EPI_WARPS) {
-          const int n = i / cpr, ch = i - n * cpr;
-          const int b = b0 + n;
-          uint4 v = make_uint4(0, 0, 0, 0);
-          if (b < B) v = __ldcg(reinterpret_cast<const uint4 *>(a.hprev_bf + ((size_t)t * B + b) * H) + ch);
-          const uint32_t off = (uint32_t)((ch >> 3) * (N * 128) + n * 128 + (((ch & 7) ^ (n & 7)) << 4));
-          *reinterpret_cast<uint4 *>(gbase + (s_h - base) + off) = v;
+        constexpr int GU = NCH >= 2 ? 2 : 1;  // loads in flight per thread (the tile fetch is L2-bandwidth bound)
+        constexpr int ET = 32 * TCR_EPI_WARPS;
+        const int total = N * cpr;
+        const __nv_bfloat16 *hsrc = a.hprev_bf + (size_t)t * B * H;
+        for (int i0 = et; i0 < total; i0 += ET * GU) {
+          uint4 v[GU];
+#pragma unroll
+          for (int j = 0; j < GU; ++j) {
+            const int i = i0 + j * ET;
+            v[j] = make_uint4(0, 0, 0, 0);
+            if (i < total) {
+              const int n = i / cpr, ch = i - n * cpr;
+              if (b0 + n < B) v[j] = __ldcg(reinterpret_cast<const uint4 *>(hsrc + (size_t)(b0 + n) * H) + ch);
+            }
+          }
+#pragma unroll
+          for (int j = 0; j < GU; ++j) {
+            const int i = i0 + j * ET;
+            if (i < total) {
+              const int n = i / cpr, ch = i - n * cpr;
+              const uint32_t off = (uint32_t)((ch >> 3) * (N * 128) + n * 128 + (((ch & 7) ^ (n & 7)) << 4));
+              *reinterpret_cast<uint4 *>(gbase + (s_h - base) + off) = v[j];
+            }
+          }
         }
         fence_proxy_async_smem();
         mbar_arrive(bar_h);
@@ -244,7 +278,7 @@ lstm_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_h, const __grid_consta
         const int b = b0 + cg * CPW + 4 * it + eg;
         dsc[it] = 1.0f;
         if (b < B) {
-          if (__ldg(a.x_bt5 + ((size_t)b * T + t) * 5 + 3) > 0.f) eoc_bits |= 1u << it;
+          if (__ldg(a.eoc + (size_t)t * B + b)) eoc_bits |= 1u << it;
           if (a.dropout) dsc[it] = drop_scale(a.mask, b, T, t, H, uo, a.row0, a.seed, a.keep);
         }
       }
@@ -274,27 +308,27 @@ lstm_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_h, const __grid_consta
         const int b = b0 + c;
         if (b < B) {
           const uint32_t po = plane_off(c, eu);
-          const float ig = sigmoid_approx(p0 + *reinterpret_cast<const float *>(xw_gen + 0 * (N * 128) + po));
-          const float jg = tanh_approx(p1 + *reinterpret_cast<const float *>(xw_gen + 1 * (N * 128) + po));
-          const float fg = sigmoid_approx(p2 + *reinterpret_cast<const float *>(xw_gen + 2 * (N * 128) + po) + 1.0f);
-          const float og = sigmoid_approx(p3 + *reinterpret_cast<const float *>(xw_gen + 3 * (N * 128) + po));
+          float *x0p = reinterpret_cast<float *>(xw_gen + 0 * (N * 128) + po), *x1p = reinterpret_cast<float *>(xw_gen + 1 * (N * 128) + po);
+          float *x2p = reinterpret_cast<float *>(xw_gen + 2 * (N * 128) + po), *x3p = reinterpret_cast<float *>(xw_gen + 3 * (N * 128) + po);
+          const float ig = sigmoid_approx(p0 + *x0p);
+          const float jg = tanh_approx(p1 + *x1p);
+          const float fg = sigmoid_approx(p2 + *x2p + 1.0f);
+          const float og = sigmoid_approx(p3 + *x3p);
+          *x0p = ig; *x1p = jg; *x2p = fg; *x3p = og;  // staged for the TMA store
           const float c2 = fmaf(cst[it], fg, ig * jg);
           const float h2 = tanh_approx(c2) * og;
           const bool eoc = (eoc_bits >> it) & 1u;
           const float cn = eoc ? init_gen[(0 * N + c) * 32 + eu] : c2;
           const float hn = eoc ? init_gen[(1 * N + c) * 32 + eu] : h2;
           cst[it] = cn;
-          const size_t row = (size_t)t * B + b;
-          if (t + 1 < T) a.hprev_bf[(row + B) * H + uo] = __float2bfloat16_rn(hn);  // exchange medium first
+          const size_t ix = ((size_t)t * B + b) * H + uo, nx = ix + (size_t)B * H;
+          if (t + 1 < T) a.hprev_bf[nx] = __float2bfloat16_rn(hn);  // exchange medium first
           if constexpr (DEFER) {
-            sv[it][0] = ig; sv[it][1] = jg; sv[it][2] = fg; sv[it][3] = og;
             sv[it][4] = h2 * dsc[it]; sv[it][5] = cn; sv[it][6] = hn;
           } else {
-            float *ac = a.acts + row * G + uo;
-            ac[0] = ig; ac[H] = jg; ac[2 * H] = fg; ac[3 * H] = og;
-            a.out_bf[row * H + uo] = __float2bfloat16_rn(h2 * dsc[it]);
+            a.out_bf[ix] = __float2bfloat16_rn(h2 * dsc[it]);
             if (t + 1 < T) {
-              a.cprev[(row + B) * H + uo] = cn;
+              a.cprev[nx] = cn;
             } else {
               a.state_out[(size_t)b * S + uo] = cn;
               a.state_out[(size_t)b * S + H + uo] = hn;
@@ -302,6 +336,9 @@ lstm_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_h, const __grid_consta
           }
         }
       }
+      fence_proxy_async_smem();
+      mbar_arrive(bar_out);
+      if (a.mcast) fence_proxy_async();  // my h stores -> visible to the other ranks' TMA loads
       if (dbg) { long long c4 = clock64(); tk[0] += c1 - c0; tk[1] += c2 - c1; tk[2] += c3 - c2; tk[3] += c4 - c3; c0 = c4; }
       if constexpr (DEFER) {
         __syncwarp();
@@ -312,8 +349,6 @@ lstm_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_h, const __grid_consta
           const int b = b0 + cg * CPW + 4 * it + eg;
           if (b < B) {
             const size_t row = (size_t)t * B + b;
-            float *ac = a.acts + row * G + uo;
-            ac[0] = sv[it][0]; ac[H] = sv[it][1]; ac[2 * H] = sv[it][2]; ac[3 * H] = sv[it][3];
             a.out_bf[row * H + uo] = __float2bfloat16_rn(sv[it][4]);
             if (t + 1 < T) {
               a.cprev[(row + B) * H + uo] = sv[it][5];
@@ -341,6 +376,7 @@ lstm_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_h, const __grid_consta
   if (dbg && tid == 64)
     printf("[tc fwd N=%d] epilogue cycles/step: prefetch %lld, wait acc %lld, tmem ld + xw wait %lld, items+stores+fence %lld, cluster barrier %lld\n",
            N, tk[0] / T, tk[1] / T, tk[2] / T, tk[3] / T, tk[4] / T);
+  if (warp == 0 && elect_one()) tma_store_wait_all();
   __syncthreads();
   if (warp == 1) tc_dealloc(tmem_acc, (uint32_t)a.tmem_cols);
 }
@@ -411,8 +447,12 @@ lstm_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm_acts, TcRnnArgs a) {
   const uint32_t idesc = make_idesc_bf16(128, N, false, false);
   __nv_bfloat16 *part_base = a.partial + (size_t)cid * 2 * CS * H * N;
 
+  long long tk[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  const bool dbg = a.debug && rank == 0 && cid == 0 && tid == 64;
   for (int t = T - 1, step = 0; t >= 0; --t, ++step) {
     const int par = step & 1;
+    long long c0 = 0, c1 = 0, c2 = 0, c3 = 0, c4 = 0, c5 = 0;
+    if (dbg) c0 = clock64();
     if (warp == 0) {
       if (elect_one()) {
         mbar_expect_tx(bar_acts, 4 * N * 128);
@@ -430,11 +470,12 @@ lstm_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm_acts, TcRnnArgs a) {
           const size_t row = (size_t)t * B + b;
           d_o[it] = a.dout[row * H + uo];
           cp[it] = a.cprev[row * H + uo];
-          if (__ldg(a.x_bt5 + ((size_t)b * T + t) * 5 + 3) > 0.f) eoc_bits |= 1u << it;
+          if (__ldg(a.eoc + (size_t)t * B + b)) eoc_bits |= 1u << it;
           if (a.dropout) d_o[it] *= drop_scale(a.mask, b, T, t, H, uo, a.row0, a.seed, a.keep);
         }
       }
       mbar_wait(bar_acts, step & 1);
+      if (dbg) c1 = clock64();
 #pragma unroll
       for (int it = 0; it < NCH; ++it) {
         const int c = c_first + it;
@@ -453,8 +494,6 @@ lstm_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm_acts, TcRnnArgs a) {
           const float d0 = dc2 * jg * ig * (1.0f - ig), d1 = dc2 * ig * (1.0f - jg * jg);
           const float d2 = dc2 * cp[it] * fg * (1.0f - fg), d3 = dh2 * tc * og * (1.0f - og);
           const size_t row = (size_t)t * B + b;
-          float *ac = a.acts + row * G + uo;
-          ac[0] = d0; ac[H] = d1; ac[2 * H] = d2; ac[3 * H] = d3;
           __nv_bfloat16 *db = a.dpre_bf + row * G + uo;
           const __nv_bfloat16 h0 = __float2bfloat16_rn(d0), h1 = __float2bfloat16_rn(d1);
           const __nv_bfloat16 h2 = __float2bfloat16_rn(d2), h3 = __float2bfloat16_rn(d3);
@@ -471,6 +510,7 @@ lstm_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm_acts, TcRnnArgs a) {
       }
       fence_proxy_async_smem();
       mbar_arrive(bar_ready);
+      if (dbg) c2 = clock64();
     }
     if (t > 0) {
       if (warp == 1) {
@@ -492,37 +532,58 @@ lstm_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm_acts, TcRnnArgs a) {
         __syncwarp();
       } else if (warp >= 2) {
         mbar_wait(bar_acc, step & 1);
+        if (dbg) c3 = clock64();
         tc_fence_after();
         for (int mt = 0; mt < nmt; ++mt) {
           const int m = mt * 128 + e;  // hidden unit of this lane's accumulator row
-          __nv_bfloat16 *dst = part_base + ((size_t)(par * CS + rank) * H + m) * N + cg * CPW;
+          (void)m;
           uint32_t r[CPW];
           tc_ldn<CPW>(tmem_acc + ((uint32_t)(32 * q) << 16) + (uint32_t)(mt * N + cg * CPW), r);
-          if (m < H) {
+          // transpose this warp's 32 x CPW block through shared memory (the activation staging planes are
+          // idle now) so that a store instruction covers whole rows: CPW bf16 contiguous per row
+          float *stg = reinterpret_cast<float *>(gbase + (s_ac - base)) + (warp - 2) * (32 * CPW);
 #pragma unroll
-            for (int j = 0; j < CPW / 4; ++j) {
-              const __nv_bfloat162 lo = __floats2bfloat162_rn(__uint_as_float(r[4 * j]), __uint_as_float(r[4 * j + 1]));
-              const __nv_bfloat162 hi = __floats2bfloat162_rn(__uint_as_float(r[4 * j + 2]), __uint_as_float(r[4 * j + 3]));
-              uint2 pk;
-              pk.x = *reinterpret_cast<const uint32_t *>(&lo);
-              pk.y = *reinterpret_cast<const uint32_t *>(&hi);
-              *reinterpret_cast<uint2 *>(dst + 4 * j) = pk;
+          for (int j = 0; j < CPW; ++j) stg[lane * CPW + ((j + lane) & (CPW - 1))] = __uint_as_float(r[j]);
+          __syncwarp();
+          constexpr int PP = CPW / 2;    // bf16 pairs per row
+          constexpr int RPI = 32 / PP;   // rows per store instruction
+          const int prow = lane / PP, pair = lane % PP;
+#pragma unroll
+          for (int r0 = 0; r0 < 32; r0 += RPI) {
+            const int rr = r0 + prow;
+            const int mm = mt * 128 + 32 * q + rr;
+            const float v0 = stg[rr * CPW + ((2 * pair + rr) & (CPW - 1))];
+            const float v1 = stg[rr * CPW + ((2 * pair + 1 + rr) & (CPW - 1))];
+            if (mm < H) {
+              const __nv_bfloat162 pk = __floats2bfloat162_rn(v0, v1);
+              *reinterpret_cast<__nv_bfloat162 *>(part_base + ((size_t)(par * CS + rank) * H + mm) * N + cg * CPW + 2 * pair) = pk;
             }
           }
+          __syncwarp();
         }
       }
     }
+    if (dbg) c4 = clock64();
     __syncwarp();
     tc_fence_before();
     cluster_sync_all();
     tc_fence_after();
+    if (dbg) c5 = clock64();
     if (t > 0 && warp >= 2) {
       // d(h_{t-1}) for my units = sum over ranks (fixed order) of their partials
 #pragma unroll
       for (int it = 0; it < NCH; ++it) dhc[it] = 0.f;
       for (int r = 0; r < CS; ++r) {
         const __nv_bfloat16 *src = part_base + ((size_t)(par * CS + r) * H + uo) * N + c_first;
-        if constexpr (NCH % 4 == 0) {
+        if constexpr (NCH == 8) {
+          const uint4 v = __ldcg(reinterpret_cast<const uint4 *>(src));
+          const float2 f0 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162 *>(&v.x));
+          const float2 f1 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162 *>(&v.y));
+          const float2 f2 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162 *>(&v.z));
+          const float2 f3 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162 *>(&v.w));
+          dhc[0] += f0.x; dhc[1] += f0.y; dhc[2] += f1.x; dhc[3] += f1.y;
+          dhc[4] += f2.x; dhc[5] += f2.y; dhc[6] += f3.x; dhc[7] += f3.y;
+        } else if constexpr (NCH % 4 == 0) {
 #pragma unroll
           for (int it = 0; it < NCH; it += 4) {
             const uint2 v = __ldcg(reinterpret_cast<const uint2 *>(src + it));
@@ -537,7 +598,14 @@ lstm_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm_acts, TcRnnArgs a) {
         }
       }
     }
+    if (dbg && t > 0) {
+      long long c6 = clock64();
+      tk[0] += c1 - c0; tk[1] += c2 - c1; tk[2] += c3 - c2; tk[3] += c4 - c3; tk[4] += c5 - c4; tk[5] += c6 - c5;
+    }
   }
+  if (dbg)
+    printf("[tc bwd N=%d CS=%d] cycles/step: inputs+acts wait %lld, elementwise+stores %lld, MMA wait %lld, tmem ld + partial stores %lld, cluster barrier %lld, partial reads %lld\n",
+           N, CS, tk[0] / (T - 1), tk[1] / (T - 1), tk[2] / (T - 1), tk[3] / (T - 1), tk[4] / (T - 1), tk[5] / (T - 1));
   __syncthreads();
   if (warp == 1) tc_dealloc(tmem_acc, (uint32_t)a.tmem_cols);
 }
@@ -677,7 +745,8 @@ int sk_rnn_tc_layer(skrnn_handle *h, cudaStream_t st, bool bwd, int l, int B, in
   a.dropout = (training && l == h->L - 1 && h->cfg.keep_prob < 1.0f) ? 1 : 0;
   a.keep = h->cfg.keep_prob;
   a.seed = seed;
-  a.x_bt5 = x_bt5; a.state_in = state_in; a.state_out = state_out; a.mask = mask;
+  (void)x_bt5;
+  a.eoc = h->ws.eoc; a.state_in = state_in; a.state_out = state_out; a.mask = mask;
   a.acts = h->ws.xw[l]; a.cprev = h->ws.cprev[l]; a.out_bf = h->ws.out_bf[l]; a.hprev_bf = h->ws.hprev_bf[l];
   a.dout = h->ws.dout; a.dpre_bf = h->ws.dpre_bf;
   a.wimg = reinterpret_cast<const uint8_t *>(h->ws.wpack);
@@ -700,7 +769,10 @@ int sk_rnn_tc_layer(skrnn_handle *h, cudaStream_t st, bool bwd, int l, int B, in
     CUtensorMap tm_h;
     uint64_t dims[3] = {(uint64_t)H, (uint64_t)B, (uint64_t)T};
     uint64_t str[2] = {(uint64_t)H * 2, (uint64_t)B * H * 2};
-    uint32_t box[3] = {64, (uint32_t)N, 1};
+    static int mc_env = -1;
+    if (mc_env < 0) { const char *e = getenv("SKRNN_TC_MCAST"); mc_env = (e && e[0] == '0') ? 0 : 1; }
+    a.mcast = (mc_env && N >= 64 && CS >= 2 && CS == 2 * nkb) ? 1 : 0;
+    uint32_t box[3] = {64, (uint32_t)(a.mcast ? N / 2 : N), 1};
     SK_TRY(sk_make_tmap(&tm_h, 2, h->ws.hprev_bf[l], 3, dims, str, box));
     SkLaunch scope(h, st, SK_CAT_RNN_FWD);
     if (N == 16) rc = launch_fwd<1>(tm_h, tm_xw, a, nclusters, smem, st);
