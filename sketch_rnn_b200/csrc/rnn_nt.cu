@@ -65,6 +65,8 @@ struct NtArgs {
   __nv_bfloat16 *dpre_bf;    // [T,B,G]
   const uint8_t *wimg;
   int wimg_bytes;
+  int debug;
+  int mcast;   // 1: all-gather by TMA multicast; 0: every CTA fetches the whole tile itself (diagnostic)
 };
 
 // 8 dropout scales (0 or 1/keep) for units [unit0, unit0+8) of (row, t): 16-bit uniforms from 4 hashes
@@ -96,9 +98,9 @@ lstm_nt_kernel(const __grid_constant__ CUtensorMap tm_a, NtArgs a) {
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   uint8_t *gbase = smem_raw + (base - smem_u32(smem_raw));
   const int H = a.H, G = a.G, B = a.B, T = a.T, CS = a.CS, nA = a.nA;
-  const uint32_t s_w = base;
-  const uint32_t s_ring = s_w + (uint32_t)nA * WKB;
-  const uint32_t s_bar = s_ring + NT_RING * NT_KB_BYTES;
+  const uint32_t s_ring = base;  // multicast destination first (low shared-memory offsets)
+  const uint32_t s_w = s_ring + NT_RING * NT_KB_BYTES;
+  const uint32_t s_bar = s_w + (uint32_t)nA * WKB;
   const uint32_t bar_full = s_bar, bar_free = s_bar + 32, bar_acc = s_bar + 64, tmem_holder = s_bar + 72;
   volatile uint32_t *tmem_holder_ptr = reinterpret_cast<volatile uint32_t *>(gbase + (tmem_holder - base));
 
@@ -118,7 +120,7 @@ lstm_nt_kernel(const __grid_constant__ CUtensorMap tm_a, NtArgs a) {
   if (tid == 0) {
     for (int s = 0; s < NT_RING; ++s) {
       mbar_init(bar_full + 8 * s, 1);
-      mbar_init(bar_free + 8 * s, CS);
+      mbar_init(bar_free + 8 * s, a.mcast ? CS : 1);
     }
     mbar_init(bar_acc, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -159,6 +161,8 @@ lstm_nt_kernel(const __grid_constant__ CUtensorMap tm_a, NtArgs a) {
 
   const uint32_t idesc = make_idesc_bf16(128, NB, false, false);
   const int nsteps = BWD ? T - 1 : T;  // steps that run the product
+  long long tk[6] = {0, 0, 0, 0, 0, 0};
+  const bool dbg = a.debug && rank == 0 && cluster_id_x() == 0 && (tid == 64 || tid == 32);
 
   for (int it = 0; it < T; ++it) {
     const int t = BWD ? T - 1 - it : it;
@@ -166,15 +170,18 @@ lstm_nt_kernel(const __grid_constant__ CUtensorMap tm_a, NtArgs a) {
     const bool do_mm = BWD ? (it >= 1) : true;
     const int gs = BWD ? it - 1 : it;          // running index of product steps
     const int t_src = BWD ? t + 1 : t;         // time slice of the A operand
+    long long c0 = 0, c1 = 0, c2 = 0, c3 = 0;
+    if (dbg) c0 = clock64();
     if (do_mm && warp == 0) {
       if (elect_one()) {
         fence_proxy_async();
-        for (int hb = rank; hb < 2 * nA; hb += CS) {
+        const bool mc = a.mcast && CS > 1;
+        for (int hb = mc ? rank : 0; hb < 2 * nA; hb += mc ? CS : 1) {
           const int j = hb >> 1, half = hb & 1, s = j % NT_RING;
           const int m = gs * U + j / NT_RING;  // global use index of slot s
-          if (m >= 1) mbar_wait(bar_free + 8 * s, (m - 1) & 1);
+          if (m >= 1) mbar_wait_wd(bar_free + 8 * s, (m - 1) & 1, (BWD ? 50000 : 0) + 1000 * gs + 100 + s, 1u << 27);
           const uint32_t dst = s_ring + (uint32_t)s * NT_KB_BYTES + (uint32_t)half * (NT_KB_BYTES / 2);
-          if (CS > 1) tma_load_3d_multicast(dst, &tm_a, bar_full + 8 * s, j * 64, b0 + half * 64, t_src, all_mask);
+          if (mc) tma_load_3d_multicast(dst, &tm_a, bar_full + 8 * s, j * 64, b0 + half * 64, t_src, all_mask);
           else tma_load_3d(dst, &tm_a, bar_full + 8 * s, j * 64, b0 + half * 64, t_src);
         }
       }
@@ -184,7 +191,7 @@ lstm_nt_kernel(const __grid_constant__ CUtensorMap tm_a, NtArgs a) {
         for (int j = 0; j < nA; ++j) {
           const int s = j % NT_RING;
           const int m = gs * U + j / NT_RING;
-          mbar_wait(bar_full + 8 * s, m & 1);
+          mbar_wait_wd(bar_full + 8 * s, m & 1, (BWD ? 50000 : 0) + 1000 * gs + 200 + 10 * (j / NT_RING) + s, 1u << 23);
           tc_fence_after();
           const uint64_t da = make_desc(s_ring + (uint32_t)s * NT_KB_BYTES, 0, 1024);
           const uint64_t db = make_desc(s_w + (uint32_t)j * WKB, 0, 1024);
@@ -192,11 +199,12 @@ lstm_nt_kernel(const __grid_constant__ CUtensorMap tm_a, NtArgs a) {
           for (int k = 0; k < 4; ++k)
             tc_mma_bf16(tmem_acc, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (j > 0 || k > 0) ? 1u : 0u);
           // release the slot in every CTA of the cluster once these MMAs have read it, then re-arm it
-          if (CS > 1) tc_commit_multicast(bar_free + 8 * s, all_mask);
+          if (a.mcast && CS > 1) tc_commit_multicast(bar_free + 8 * s, all_mask);
           else tc_commit(bar_free + 8 * s);
           mbar_expect_tx(bar_full + 8 * s, NT_KB_BYTES);
         }
         tc_commit(bar_acc);
+        if (dbg) tk[5] += clock64() - c0;
       }
       __syncwarp();
     } else if (warp >= 2) {
@@ -217,7 +225,9 @@ lstm_nt_kernel(const __grid_constant__ CUtensorMap tm_a, NtArgs a) {
           eoc = __ldg(a.eoc + (size_t)t * B + b) != 0;
           if (a.dropout) drop8(a, b, t, un, dsc);
         }
-        mbar_wait(bar_acc, gs & 1);
+        if (dbg) c1 = clock64();
+        mbar_wait_wd(bar_acc, gs & 1, 300, 1u << 27);
+        if (dbg) c2 = clock64();
         tc_fence_after();
         uint32_t r[32];  // accumulator columns 32cg + 4u + g
         tc_ldn<32>(tmem_acc + ((uint32_t)(32 * q) << 16) + (uint32_t)(32 * cg), r);
@@ -300,7 +310,7 @@ lstm_nt_kernel(const __grid_constant__ CUtensorMap tm_a, NtArgs a) {
 #pragma unroll
         for (int u = 0; u < 8; ++u) r[u] = 0u;
         if (do_mm) {
-          mbar_wait(bar_acc, gs & 1);
+          mbar_wait_wd(bar_acc, gs & 1, 301);
           tc_fence_after();
           tc_ldn<8>(tmem_acc + ((uint32_t)(32 * q) << 16) + (uint32_t)(8 * cg), r);
         }
@@ -328,13 +338,20 @@ lstm_nt_kernel(const __grid_constant__ CUtensorMap tm_a, NtArgs a) {
           }
         }
       }
+      if (dbg) c3 = clock64();
       fence_proxy_async();  // my global stores -> visible to the other ranks' TMA loads of the next step
+      if (dbg && tid == 64) { long long c4 = clock64(); tk[0] += c1 - c0; tk[1] += c2 - c1; tk[2] += c3 - c2; tk[3] += c4 - c3; c0 = c4; }
     }
     __syncwarp();
     tc_fence_before();
     cluster_sync_all();
     tc_fence_after();
+    if (dbg && tid == 64) tk[4] += clock64() - c0;
   }
+  if (dbg && tid == 64)
+    printf("[nt %s] epilogue cycles/step: prefetch %lld, wait acc %lld, ld+math+stores %lld, proxy fence %lld, cluster barrier %lld\n",
+           BWD ? "bwd" : "fwd", tk[0] / T, tk[1] / T, tk[2] / T, tk[3] / T, tk[4] / T);
+  if (dbg && tid == 32) printf("[nt %s] MMA thread: step start -> all MMAs issued + committed %lld cycles/step\n", BWD ? "bwd" : "fwd", tk[5] / T);
   (void)nsteps;
   __syncthreads();
   if (warp == 1) tc_dealloc(tmem_acc, BWD ? 32u : 128u);
@@ -400,11 +417,19 @@ int sk_rnn_nt_layer(skrnn_handle *h, cudaStream_t st, bool bwd, int l, int B, in
   if (h->cfg.precision != SKRNN_PREC_BF16 || h->cfg.cell != SKRNN_CELL_LSTM) return -1;
   if (!(H == 32 || H == 64 || H == 128 || H == 256 || H == 512)) return -1;
   if (h->nt_rnn_disabled) return -1;
-  static int env_mode = -2;  // SKRNN_NT: 0 never, 1 always, unset: large batches only
-  if (env_mode == -2) { const char *e = getenv("SKRNN_NT"); env_mode = e ? atoi(e) : -1; }
-  if (env_mode == 0) return -1;
-  if (env_mode == -1 && B < 192) return -1;
+  // Opt-in (SKRNN_NT=1): measured on B200 this variant is not faster than the transposed kernels of
+  // rnn_tc.cu yet (profiles/), and its 16-CTA backward all-gather still loses multicast boxes.
+  static int env_mode = -2;
+  if (env_mode == -2) { const char *e = getenv("SKRNN_NT"); env_mode = e ? atoi(e) : 0; }
+  if (env_mode != 1) return -1;
   const int CS = H / 32;
+  {
+    // the 16-CTA backward all-gather is not reliable yet (multicast boxes go missing): keep the
+    // partial-exchange kernel of rnn_tc.cu for H = 512 BPTT unless explicitly enabled
+    static int nb_env = -1;
+    if (nb_env < 0) { const char *e = getenv("SKRNN_NT_BWD16"); nb_env = (e && e[0] == '1') ? 1 : 0; }
+    if (bwd && CS > 8 && !nb_env) return -1;
+  }
   const int K = bwd ? 4 * H : H;
   const int nA = (K + 63) / 64;
   const int NB = bwd ? 32 : 128;
@@ -431,6 +456,12 @@ int sk_rnn_nt_layer(skrnn_handle *h, cudaStream_t st, bool bwd, int l, int B, in
   a.dout = h->ws.dout; a.dpre_bf = h->ws.dpre_bf;
   a.wimg = reinterpret_cast<const uint8_t *>(h->ws.wpack);
   a.wimg_bytes = img_bytes;
+  { const char *e = getenv("SKRNN_TC_DEBUG"); a.debug = (e && e[0] == '1') ? 1 : 0; }
+  {
+    static int mc_env = -1;
+    if (mc_env < 0) { const char *e = getenv("SKRNN_NT_MCAST"); mc_env = (e && e[0] == '0') ? 0 : 1; }
+    a.mcast = mc_env;
+  }
   // A operand: hprev_bf [T,B,H] (forward) or dpre_bf [T,B,G] (backward), boxes of 64 rows x 64 k
   CUtensorMap tm;
   {

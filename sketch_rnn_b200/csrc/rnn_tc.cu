@@ -449,31 +449,44 @@ lstm_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm_acts, TcRnnArgs a) {
 
   long long tk[8] = {0, 0, 0, 0, 0, 0, 0, 0};
   const bool dbg = a.debug && rank == 0 && cid == 0 && tid == 64;
+  // per-item global inputs of a step: d(out), c fed to the step, eoc flag (dropout folded into d(out))
+  float d_o[NCH], cp[NCH];
+  uint32_t eoc_bits = 0;
+  auto load_inputs = [&](int tt) {
+    eoc_bits = 0;
+#pragma unroll
+    for (int it = 0; it < NCH; ++it) {
+      const int b = b0 + c_first + it;
+      d_o[it] = 0.f; cp[it] = 0.f;
+      if (b < B) {
+        const size_t row = (size_t)tt * B + b;
+        d_o[it] = a.dout[row * H + uo];
+        cp[it] = a.cprev[row * H + uo];
+        if (__ldg(a.eoc + (size_t)tt * B + b)) eoc_bits |= 1u << it;
+        if (a.dropout) d_o[it] *= drop_scale(a.mask, b, T, tt, H, uo, a.row0, a.seed, a.keep);
+      }
+    }
+  };
+  if (warp >= 2) load_inputs(T - 1);
+  if (warp == 0 && elect_one()) {
+    mbar_expect_tx(bar_acts, 4 * N * 128);
+    tma_load_4d(s_ac, &tm_acts, bar_acts, u0, b0, 0, T - 1);
+  }
+  __syncwarp();
   for (int t = T - 1, step = 0; t >= 0; --t, ++step) {
     const int par = step & 1;
     long long c0 = 0, c1 = 0, c2 = 0, c3 = 0, c4 = 0, c5 = 0;
     if (dbg) c0 = clock64();
     if (warp == 0) {
-      if (elect_one()) {
+      // the staged activations of step t were requested one step ahead; once the elementwise phase has
+      // consumed them (bar_ready), request step t-1's so the load overlaps the product and the exchange
+      mbar_wait(bar_ready, step & 1);
+      if (t > 0 && elect_one()) {
         mbar_expect_tx(bar_acts, 4 * N * 128);
-        tma_load_4d(s_ac, &tm_acts, bar_acts, u0, b0, 0, t);
+        tma_load_4d(s_ac, &tm_acts, bar_acts, u0, b0, 0, t - 1);
       }
+      __syncwarp();
     } else if (warp >= 2) {
-      // per-item global inputs, fetched before waiting on the staged activations
-      float d_o[NCH], cp[NCH];
-      uint32_t eoc_bits = 0;
-#pragma unroll
-      for (int it = 0; it < NCH; ++it) {
-        const int b = b0 + c_first + it;
-        d_o[it] = 0.f; cp[it] = 0.f;
-        if (b < B) {
-          const size_t row = (size_t)t * B + b;
-          d_o[it] = a.dout[row * H + uo];
-          cp[it] = a.cprev[row * H + uo];
-          if (__ldg(a.eoc + (size_t)t * B + b)) eoc_bits |= 1u << it;
-          if (a.dropout) d_o[it] *= drop_scale(a.mask, b, T, t, H, uo, a.row0, a.seed, a.keep);
-        }
-      }
       mbar_wait(bar_acts, step & 1);
       if (dbg) c1 = clock64();
 #pragma unroll
@@ -511,6 +524,7 @@ lstm_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm_acts, TcRnnArgs a) {
       fence_proxy_async_smem();
       mbar_arrive(bar_ready);
       if (dbg) c2 = clock64();
+      if (t > 0) load_inputs(t - 1);  // next step's per-item inputs, in flight during the product
     }
     if (t > 0) {
       if (warp == 1) {
@@ -536,30 +550,24 @@ lstm_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm_acts, TcRnnArgs a) {
         tc_fence_after();
         for (int mt = 0; mt < nmt; ++mt) {
           const int m = mt * 128 + e;  // hidden unit of this lane's accumulator row
-          (void)m;
           uint32_t r[CPW];
           tc_ldn<CPW>(tmem_acc + ((uint32_t)(32 * q) << 16) + (uint32_t)(mt * N + cg * CPW), r);
-          // transpose this warp's 32 x CPW block through shared memory (the activation staging planes are
-          // idle now) so that a store instruction covers whole rows: CPW bf16 contiguous per row
-          float *stg = reinterpret_cast<float *>(gbase + (s_ac - base)) + (warp - 2) * (32 * CPW);
+          if (m < H) {
+            __nv_bfloat16 *dst = part_base + ((size_t)(par * CS + rank) * H + m) * N + cg * CPW;
+            uint32_t pk[CPW / 2];
 #pragma unroll
-          for (int j = 0; j < CPW; ++j) stg[lane * CPW + ((j + lane) & (CPW - 1))] = __uint_as_float(r[j]);
-          __syncwarp();
-          constexpr int PP = CPW / 2;    // bf16 pairs per row
-          constexpr int RPI = 32 / PP;   // rows per store instruction
-          const int prow = lane / PP, pair = lane % PP;
+            for (int j = 0; j < CPW / 2; ++j) {
+              const __nv_bfloat162 v = __floats2bfloat162_rn(__uint_as_float(r[2 * j]), __uint_as_float(r[2 * j + 1]));
+              pk[j] = *reinterpret_cast<const uint32_t *>(&v);
+            }
+            if constexpr (CPW >= 8) {
 #pragma unroll
-          for (int r0 = 0; r0 < 32; r0 += RPI) {
-            const int rr = r0 + prow;
-            const int mm = mt * 128 + 32 * q + rr;
-            const float v0 = stg[rr * CPW + ((2 * pair + rr) & (CPW - 1))];
-            const float v1 = stg[rr * CPW + ((2 * pair + 1 + rr) & (CPW - 1))];
-            if (mm < H) {
-              const __nv_bfloat162 pk = __floats2bfloat162_rn(v0, v1);
-              *reinterpret_cast<__nv_bfloat162 *>(part_base + ((size_t)(par * CS + rank) * H + mm) * N + cg * CPW + 2 * pair) = pk;
+              for (int j = 0; j < CPW / 8; ++j)
+                *reinterpret_cast<uint4 *>(dst + 8 * j) = make_uint4(pk[4 * j], pk[4 * j + 1], pk[4 * j + 2], pk[4 * j + 3]);
+            } else {
+              *reinterpret_cast<uint2 *>(dst) = make_uint2(pk[0], pk[1]);
             }
           }
-          __syncwarp();
         }
       }
     }
