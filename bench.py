@@ -323,16 +323,40 @@ def run_ours(args, w):
             flops_step = 3.0 * fl * Bl * T   # per GPU
         else:
             flops_step = 1.0 * fl * Bl * T
-        # dominant kernel by measured time
+        # dominant kernel by measured time; its roofline = algorithmic work of ONE launch / its mean duration
         dom = max(kern_ms, key=kern_ms.get) if kern_ms else None
         tc = args.precision == "bf16" and w["kind"] == "train"
-        peak = peaks["tc_sustained"] if tc else 2 * 128 * 148 * 1.965e-3  # fp32 CUDA-core TFLOP/s nominal
-        ach = flops_step / (ms_per_step * 1e-3) / 1e12
+        ng = {"lstm": 4, "gru": 3, "rnn": 1}[w["model"]]
+        H, L, NOUT = w["H"], w["L"], 3 + 6 * w["M"]
+        rows = Bl * T
+        per_launch_flops = {
+            # one launch = all T steps of one layer: h[B,H] x Wh[H,G] per step (BPTT: d(pre)[B,G] x Wh^T)
+            "rnn_fwd": 2.0 * rows * H * ng * H, "rnn_bwd": 2.0 * rows * H * ng * H,
+            # GEMM launches differ in shape: report the mean over the step's launches
+            "gemm_tc": None, "gemm_f32": None,
+            "sampler": 1.0 * fl * rows,
+        }
+        gemm_total = (flops_step - (3.0 if w["kind"] == "train" else 1.0) * 2.0 * rows * H * ng * H * L) \
+            if w["kind"] == "train" else 0.0
+        n_dom = max(1, kern_cnt.get(dom, 1)) if dom else 1
+        if dom in ("gemm_tc", "gemm_f32"):
+            fpl = gemm_total / n_dom
+        elif dom in per_launch_flops and per_launch_flops[dom]:
+            fpl = per_launch_flops[dom]
+        else:
+            fpl = flops_step / n_dom
+        dur_ms = kern_ms[dom] / n_dom if dom else ms_per_step
+        peak = peaks["tc_sustained"] if tc and dom != "sampler" else 2 * 128 * 148 * 1.965e-3
+        ach = fpl / (dur_ms * 1e-3) / 1e12
+        whole = flops_step / (ms_per_step * 1e-3) / 1e12
         roof = {"bound": "tensor", "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": ach / peak,
-                "traffic": None, "kernel": "whole step (all kernels)",
-                "peak_source": ("MEASURED_PEAKS.json bf16 sustained (%s)" % peaks["src"]) if tc else
-                "fp32 CUDA-core nominal 148 SM x 128 lanes x 2 x 1.965 GHz (this path runs no tensor-core math)",
-                "per_kernel_ms": kern_ms, "per_kernel_launches": kern_cnt, "dominant": dom}
+                "traffic": None, "kernel": dom, "launch_ms": dur_ms, "launches_per_step": n_dom,
+                "algorithmic_flops_per_launch": fpl,
+                "peak_source": ("MEASURED_PEAKS.json bf16 sustained (%s)" % peaks["src"]) if (tc and dom != "sampler") else
+                "fp32 CUDA-core nominal 148 SM x 128 lanes x 2 x 1.965 GHz (this kernel runs no tensor-core math)",
+                "note": "persistent recurrent kernels are bound by per-timestep latency and the L2 exchange of h / d(h), "
+                        "not by the tensor pipe: see DESIGN.md section 4 and profiles/",
+                "whole_step_tflops": whole, "per_kernel_ms": kern_ms, "per_kernel_launches": kern_cnt}
         cb = None
         if world == 1 and not args.no_cpu:
             v, u, cores, sample = cpu_baseline(w)
