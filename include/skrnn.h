@@ -25,6 +25,7 @@
 #ifndef SKRNN_H_
 #define SKRNN_H_
 
+#include <stddef.h>
 #include <stdint.h>
 
 #if defined(__GNUC__)
@@ -181,6 +182,11 @@ SKRNN_API int skrnn_profile_read(skrnn_handle *h, double *ms_out, int64_t *count
 SKRNN_API int skrnn_clip_adam_noalloc(int64_t n, const float *grads_dev, float *params_dev, float *m_dev,
                             float *v_dev, float lr, float grad_clip, double beta1_power,
                             double beta2_power, float *gnorm_out_dev, void *stream);
+
+/* Host-only helper (no GPU work): CRC-32C (Castagnoli) of `n` bytes continued from `crc` (0 to start), the
+ * block checksum of TensorFlow's V1 checkpoint tables that tf.train.Saver reads and writes (train.py:64,74;
+ * sample.py:59-64).  Used by sketch_rnn_b200/checkpoint.py. */
+SKRNN_API uint32_t skrnn_crc32c(uint32_t crc, const void *data, size_t n);
 
 /* Diagnostic (no reference counterpart): runs the bf16 tcgen05/TMA GEMM building block on caller
  * buffers so tests can check it against a library matmul.  C[M,N] (+)= A*B (+bias), A/B bf16 device

@@ -54,6 +54,7 @@ SYMBOLS = {
     "skrnn_launch_count": (C.c_int64, [_P]),
     "skrnn_clip_adam_noalloc": (C.c_int, [C.c_int64, _P, _P, _P, _P, C.c_float, C.c_float, C.c_double, C.c_double,
                                           _P, _P]),
+    "skrnn_crc32c": (C.c_uint32, [C.c_uint32, C.c_char_p, C.c_size_t]),
     "skrnn_debug_gemm_bf16": (C.c_int, [_P, C.c_int32, C.c_int32, C.c_int32, _P, C.c_int32, C.c_int32, _P, C.c_int32,
                                         C.c_int32, _P, C.c_int32, _P, C.c_int32, _P, _P]),
     "skrnn_profile_enable": (C.c_int, [_P, C.c_int32]),

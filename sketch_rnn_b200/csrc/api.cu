@@ -391,6 +391,23 @@ int skrnn_debug_gemm_bf16(skrnn_handle *h, int32_t M, int32_t N, int32_t K, cons
   return rc;
 }
 
+uint32_t skrnn_crc32c(uint32_t crc, const void *data, size_t n) {
+  static uint32_t table[256];
+  static bool init = false;
+  if (!init) {
+    for (uint32_t i = 0; i < 256; ++i) {
+      uint32_t c = i;
+      for (int k = 0; k < 8; ++k) c = (c & 1) ? (c >> 1) ^ 0x82F63B78u : c >> 1;
+      table[i] = c;
+    }
+    init = true;
+  }
+  const unsigned char *p = static_cast<const unsigned char *>(data);
+  uint32_t c = crc ^ 0xFFFFFFFFu;
+  for (size_t i = 0; i < n; ++i) c = table[(c ^ p[i]) & 0xFF] ^ (c >> 8);
+  return c ^ 0xFFFFFFFFu;
+}
+
 int skrnn_profile_enable(skrnn_handle *h, int32_t on) {
   SK_CHECK(h != nullptr, "null handle");
   h->prof_on = on != 0;
