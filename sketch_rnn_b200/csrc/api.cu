@@ -462,6 +462,7 @@ int skrnn_loss_grad(skrnn_handle *h, int32_t B, int32_t T, const float *x_dev, c
   SK_TRY(gemm(h, st, R, H, NOUT, dlogits_op(h), true, out_weight(h), false, h->ws.dout, H, nullptr, false));
   for (int l = h->L - 1; l >= 0; --l) {
     const SkLayerParams &lp = h->lp[l];
+    h->bias_grad_done = false;
     SK_TRY(sk_rnn_backward_layer(h, st, l, B, T, x_dev, dropout_mask_dev, seed, row0, true));
     const Op X = layer_input(h, l);
     const Op dpre = dpre_op(h, l);
@@ -483,7 +484,7 @@ int skrnn_loss_grad(skrnn_handle *h, int32_t B, int32_t T, const float *x_dev, c
       float *gW = h->grads + lp.w[0];
       SK_TRY(gemm(h, st, I, G, R, X, false, dpre, true, gW, G, nullptr, true));
       SK_TRY(gemm(h, st, H, G, R, hprev_op(h, l), false, dpre, true, gW + (size_t)I * G, G, nullptr, true));
-      SK_TRY(bias_grad(h, st, dpre, R, G, h->grads + lp.b[0]));
+      if (!h->bias_grad_done) SK_TRY(bias_grad(h, st, dpre, R, G, h->grads + lp.b[0]));
       if (l > 0) SK_TRY(gemm(h, st, R, I, G, dpre, true, weight(h, l, 0), false, h->ws.dout, H, nullptr, false));
     }
   }

@@ -107,6 +107,7 @@ struct skrnn_handle {
   int64_t launches = 0;
   int cluster_size = 1;
   bool tc_rnn_disabled = false;
+  bool bias_grad_done = false;  // set by a backward recurrent kernel that accumulated d(bias) itself
   bool nt_rnn_disabled = false;
   // optional per-category kernel timing (skrnn_profile_*): CUDA events around every launch
   bool prof_on = false;

@@ -71,6 +71,7 @@ struct TcRnnArgs {
   const float *dout;      // [T,B,H] fp32
   __nv_bfloat16 *dpre_bf; // [T,B,G]
   __nv_bfloat16 *partial; // [nclusters][2][CS][H][N] partial d(h), bf16
+  float *dbias;           // [G] bias gradient accumulator (column sums of d(pre)), or null
   const uint8_t *wimg;    // per-rank shared-memory images of the weight operand
   int wimg_bytes;
   int mcast;              // forward: the h tile arrives by TMA multicast (each rank fetches 1/CS of it)
@@ -439,6 +440,7 @@ lstm_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm_acts, TcRnnArgs a) {
   const int uo = u0 + eu;
   const int c_first = cg * CPW + esub * NCH;
   float dhc[NCH], dcc[NCH];
+  float bsum[4] = {0.f, 0.f, 0.f, 0.f};  // bias gradient of my unit over my columns and all steps
   uint64_t dBk[2];
   dBk[0] = make_desc(s_b, 0, 1024);
   dBk[1] = make_desc(s_b + (uint32_t)(N * 128), 0, 1024);
@@ -506,6 +508,7 @@ lstm_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm_acts, TcRnnArgs a) {
           dcc[it] = dc2 * fg;
           const float d0 = dc2 * jg * ig * (1.0f - ig), d1 = dc2 * ig * (1.0f - jg * jg);
           const float d2 = dc2 * cp[it] * fg * (1.0f - fg), d3 = dh2 * tc * og * (1.0f - og);
+          bsum[0] += d0; bsum[1] += d1; bsum[2] += d2; bsum[3] += d3;
           const size_t row = (size_t)t * B + b;
           __nv_bfloat16 *db = a.dpre_bf + row * G + uo;
           const __nv_bfloat16 h0 = __float2bfloat16_rn(d0), h1 = __float2bfloat16_rn(d1);
@@ -609,6 +612,16 @@ lstm_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm_acts, TcRnnArgs a) {
     if (dbg && t > 0) {
       long long c6 = clock64();
       tk[0] += c1 - c0; tk[1] += c2 - c1; tk[2] += c3 - c2; tk[3] += c4 - c3; tk[4] += c5 - c4; tk[5] += c6 - c5;
+    }
+  }
+  if (warp >= 2 && a.dbias != nullptr) {
+    // the 4 lanes of a unit (column sub-blocks) first, then one atomic per gate
+#pragma unroll
+    for (int g = 0; g < 4; ++g) {
+      float v = bsum[g];
+      v += __shfl_xor_sync(0xffffffffu, v, 1);
+      v += __shfl_xor_sync(0xffffffffu, v, 2);
+      if (esub == 0) atomicAdd(a.dbias + g * H + uo, v);
     }
   }
   if (dbg)
@@ -757,6 +770,8 @@ int sk_rnn_tc_layer(skrnn_handle *h, cudaStream_t st, bool bwd, int l, int B, in
   a.eoc = h->ws.eoc; a.state_in = state_in; a.state_out = state_out; a.mask = mask;
   a.acts = h->ws.xw[l]; a.cprev = h->ws.cprev[l]; a.out_bf = h->ws.out_bf[l]; a.hprev_bf = h->ws.hprev_bf[l];
   a.dout = h->ws.dout; a.dpre_bf = h->ws.dpre_bf;
+  a.dbias = bwd ? h->grads + h->lp[l].b[0] : nullptr;
+  if (bwd) h->bias_grad_done = true;
   a.wimg = reinterpret_cast<const uint8_t *>(h->ws.wpack);
   a.wimg_bytes = img_bytes;
   {
