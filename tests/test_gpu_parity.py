@@ -286,3 +286,45 @@ def test_bf16_path_loss_and_gradients(model, H, L, M, B, T):
     assert rel_err(mdn[:, 3:3 + M], ref["mdn"]["pi"]) < BF16_TOL
     assert rel_err(mdn[:, 3 + M:3 + 2 * M], ref["mdn"]["mu1"]) < BF16_TOL
     h.close()
+
+
+@pytest.mark.parametrize("H,L,B,T", [(32, 1, 1, 1), (64, 2, 3, 2), (128, 2, 17, 5), (256, 1, 129, 3), (256, 2, 300, 4),
+                                     (512, 1, 70, 3), (512, 2, 260, 2)])
+def test_bf16_tcgen05_recurrent_edge_shapes(H, L, B, T):
+    """Shapes that exercise the tcgen05 recurrent kernels' corner cases: one timestep, one row, ragged last
+    cluster, several clusters, every cluster size (1..16 CTAs), all batch tiles (16..128 columns)."""
+    cfg, params, x, y, s0, mask = _case("lstm", H, L, 4, B, T, seed=3)
+    x[:, :, 2:5] = [0, 0, 1]
+    x[::3, T // 2, 2:5] = [0, 1, 0]  # eoc on a third of the rows in the middle of the sequence
+    x[0, 0, 2:5] = [0, 1, 0]
+    losses_ref, grads_ref, fstate_ref, _ = so.loss_and_grads(
+        cfg, f64(params), x.astype(np.float64), y.astype(np.float64),
+        [s.astype(np.float64) for s in s0], mask.astype(np.float64))
+    h = make_handle(cfg, params, B, T, precision="bf16")
+    losses, state_out = h.loss_grad(x, y, stack_state(s0), dropout_mask=mask)
+    losses = losses.cpu().numpy()
+    g = h.get_params_dict(h.grads_tensor().cpu().numpy())
+    assert abs(losses[0] - losses_ref[0]) <= BF16_TOL * abs(losses_ref[0]) + 1e-5, (losses, losses_ref)
+    gscale = max(np.max(np.abs(v)) for v in grads_ref.values())
+    for n in grads_ref:
+        err = np.max(np.abs(g[n].astype(np.float64) - grads_ref[n])) / gscale
+        assert err < BF16_TOL, (n, err)
+    so_state = state_out.cpu().numpy()
+    for l in range(L):
+        assert rel_err(so_state[l], fstate_ref[l]) < BF16_TOL
+    h.close()
+
+
+def test_bf16_in_kernel_dropout_is_shard_invariant():
+    cfg, params, x, y, s0, _ = _case("lstm", 256, 2, 4, 40, 6)
+    h = make_handle(cfg, params, 40, 6, precision="bf16")
+    st = stack_state(s0)
+    h.loss_grad(x, y, st, seed=77)
+    g_full = h.grads_tensor().cpu().numpy().copy()
+    acc = 0
+    for r in range(2):
+        sl = slice(20 * r, 20 * r + 20)
+        h.loss_grad(x[sl], y[sl], np.ascontiguousarray(st[:, sl]), seed=77, row0=20 * r, loss_rows=240)
+        acc = acc + h.grads_tensor().cpu().numpy()
+    assert rel_err(acc, g_full) < 2e-3  # same mask, same bf16 roundings row by row; only sum order differs
+    h.close()
