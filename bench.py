@@ -325,7 +325,10 @@ def run_ours(args, w):
             flops_step = 1.0 * fl * Bl * T
         # dominant kernel by measured time; its roofline = algorithmic work of ONE launch / its mean duration
         dom = max(kern_ms, key=kern_ms.get) if kern_ms else None
-        tc = args.precision == "bf16" and w["kind"] == "train"
+        # bf16 sampling of many LSTM sketches runs per-step tcgen05 GEMMs (csrc/sampler_tc.cu)
+        samp_tc = (w["kind"] != "train" and args.precision == "bf16" and w["model"] == "lstm" and Bl >= 64
+                   and os.environ.get("SKRNN_SAMPLER_EXACT", "0") != "1")
+        tc = args.precision == "bf16" and (w["kind"] == "train" or samp_tc)
         ng = {"lstm": 4, "gru": 3, "rnn": 1}[w["model"]]
         H, L, NOUT = w["H"], w["L"], 3 + 6 * w["M"]
         rows = Bl * T
@@ -337,7 +340,7 @@ def run_ours(args, w):
             "sampler": 1.0 * fl * rows,
         }
         gemm_total = (flops_step - (3.0 if w["kind"] == "train" else 1.0) * 2.0 * rows * H * ng * H * L) \
-            if w["kind"] == "train" else 0.0
+            if w["kind"] == "train" else (flops_step if samp_tc else 0.0)
         n_dom = max(1, kern_cnt.get(dom, 1)) if dom else 1
         if dom in ("gemm_tc", "gemm_f32"):
             fpl = gemm_total / n_dom
@@ -349,21 +352,33 @@ def run_ours(args, w):
         peak = peaks["tc_sustained"] if tc and dom != "sampler" else 2 * 128 * 148 * 1.965e-3
         ach = fpl / (dur_ms * 1e-3) / 1e12
         whole = flops_step / (ms_per_step * 1e-3) / 1e12
-        roof = {"bound": "tensor", "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": ach / peak,
-                "traffic": None, "kernel": dom, "launch_ms": dur_ms, "launches_per_step": n_dom,
-                "algorithmic_flops_per_launch": fpl,
-                "peak_source": ("MEASURED_PEAKS.json bf16 sustained (%s)" % peaks["src"]) if (tc and dom != "sampler") else
-                "fp32 CUDA-core nominal 148 SM x 128 lanes x 2 x 1.965 GHz (this kernel runs no tensor-core math)",
-                "note": "persistent recurrent kernels are bound by per-timestep latency and the L2 exchange of h / d(h), "
-                        "not by the tensor pipe: see DESIGN.md section 4 and profiles/",
-                "whole_step_tflops": whole, "per_kernel_ms": kern_ms, "per_kernel_launches": kern_cnt}
+        if samp_tc and dom == "sampler":
+            # cell-update + draw kernels between the GEMMs: streaming, HBM/L2 bound.  Bytes per sketch-step:
+            # per layer gates 4H fp32 read, c fp32 read+write, h bf16 written twice; logits NOUT fp32 read,
+            # point written (fp32 strokes + fp32/bf16 feedback)
+            bytes_step = rows * (L * (ng * H * 4 + 2 * H * 4 + 2 * H * 2) + NOUT * 4 + 5 * 4 * 2 + 10)
+            ach = bytes_step / n_dom / (dur_ms * 1e-3) / 1e9
+            roof = {"bound": "hbm", "achieved": ach, "peak": peaks["hbm"], "unit": "GB/s", "frac": ach / peaks["hbm"],
+                    "traffic": None, "kernel": "sampler (cell update + draw)", "launch_ms": dur_ms,
+                    "launches_per_step": n_dom, "algorithmic_bytes_per_launch": bytes_step / n_dom,
+                    "peak_source": "MEASURED_PEAKS.json HBM copy (%s)" % peaks["src"],
+                    "whole_step_tflops": whole, "per_kernel_ms": kern_ms, "per_kernel_launches": kern_cnt}
+        else:
+            roof = {"bound": "tensor", "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": ach / peak,
+                    "traffic": None, "kernel": dom, "launch_ms": dur_ms, "launches_per_step": n_dom,
+                    "algorithmic_flops_per_launch": fpl,
+                    "peak_source": ("MEASURED_PEAKS.json bf16 sustained (%s)" % peaks["src"]) if (tc and dom != "sampler") else
+                    "fp32 CUDA-core nominal 148 SM x 128 lanes x 2 x 1.965 GHz (this kernel runs no tensor-core math)",
+                    "note": "persistent recurrent kernels are bound by per-timestep latency and the L2 exchange of h / d(h), "
+                            "not by the tensor pipe: see DESIGN.md section 4 and profiles/",
+                    "whole_step_tflops": whole, "per_kernel_ms": kern_ms, "per_kernel_launches": kern_cnt}
         cb = None
         if world == 1 and not args.no_cpu:
             v, u, cores, sample = cpu_baseline(w)
             cb = {"value": v, "unit": u, "cores": cores, "kind": "port", "sample": sample}
         line = {"metric": metric, "value": value, "unit": unit, "n_gpus": world, "steps": args.steps,
                 "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True,
-                "scaling": "strong", "vs_baseline": None, "dtype": args.precision if w["kind"] == "train" else "f32", "data": "synthetic",
+                "scaling": "strong", "vs_baseline": None, "dtype": args.precision if (w["kind"] == "train" or samp_tc) else "f32", "data": "synthetic",
                 "config": workload_config(args, w), "clocks": clk, "e2e": e2e,
                 "gpu_launches": int(launches), "roofline": roof, "cpu_baseline": cb,
                 "last_loss": [float(v) for v in last.float().cpu().numpy()[:3]] if w["kind"] == "train" else None}

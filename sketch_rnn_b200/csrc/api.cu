@@ -305,6 +305,7 @@ void skrnn_destroy(skrnn_handle *h) {
   cudaFree(h->st_state);
   cudaFree(h->st_loss);
   cudaFree(h->samp_state);
+  cudaFree(h->samp_tc);
   cudaFree(h->params_bf);
   cudaFree(h->cast_seg_dev);
   cudaFreeHost(h->pin_x);
@@ -550,6 +551,14 @@ int skrnn_sample(skrnn_handle *h, int32_t n_sketches, int32_t num_steps, float t
   SK_CHECK(strokes_dev && lengths_dev, "sample: null output buffer");
   SK_CHECK(temp_mixture > 0.f && temp_pen > 0.f, "sample: temperatures must be positive");
   SK_CUDA(cudaSetDevice(h->cfg.device));
+  // bf16 handles with many sketches: per-step tensor-core GEMMs (sampler_tc.cu); SKRNN_SAMPLER_EXACT=1
+  // keeps the bit-exact fp32 persistent kernel
+  const char *ex = getenv("SKRNN_SAMPLER_EXACT");
+  if (!(ex && ex[0] == '1')) {
+    const int r = sk_sample_tc(h, (cudaStream_t)stream, n_sketches, num_steps, temp_mixture, temp_pen, stop_if_eoc,
+                               uniforms_dev, seed, sketch0, strokes_dev, lengths_dev, mix_params_dev);
+    if (r >= 0) return r;
+  }
   return sk_sample_f32(h, (cudaStream_t)stream, n_sketches, num_steps, temp_mixture, temp_pen, stop_if_eoc,
                        uniforms_dev, seed, sketch0, strokes_dev, lengths_dev, mix_params_dev);
 }

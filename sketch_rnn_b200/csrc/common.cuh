@@ -103,6 +103,8 @@ struct skrnn_handle {
   int64_t st_rows = 0, st_state_n = 0;
   float *samp_state = nullptr;  // sampler: per-sketch recurrent state [n,L,S]
   int64_t samp_state_n = 0;
+  void *samp_tc = nullptr;      // throughput sampler buffers (sampler_tc.cu)
+  size_t samp_tc_bytes = 0;
   int num_sms = 0;
   int64_t launches = 0;
   int cluster_size = 1;
@@ -174,3 +176,7 @@ int sk_transpose_x(skrnn_handle *h, cudaStream_t st, int B, int T, const float *
 int sk_sample_f32(skrnn_handle *h, cudaStream_t st, int n, int steps, float temp_mix, float temp_pen,
                   int stop_if_eoc, const float *uniforms, uint64_t seed, int sketch0, float *strokes,
                   int *lengths, float *mixp);
+// bf16 tensor-core throughput sampler (sampler_tc.cu): 0 ok, -1 not applicable, >0 error
+int sk_sample_tc(skrnn_handle *h, cudaStream_t st, int n, int steps, float temp_mix, float temp_pen,
+                 int stop_if_eoc, const float *uniforms, uint64_t seed, int sketch0, float *strokes,
+                 int *lengths, float *mixp);

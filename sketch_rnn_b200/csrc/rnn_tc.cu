@@ -21,6 +21,7 @@
 // giving a partial d(h_{t-1}) for ALL hidden units; partials are exchanged through L2 and summed in a
 // fixed rank order after the cluster barrier.
 #include <stdlib.h>
+#include <type_traits>
 
 #include "common.cuh"
 #include "skrnn_math.h"
@@ -79,12 +80,16 @@ struct TcRnnArgs {
   int debug;              // SKRNN_TC_DEBUG=1: one CTA prints its per-phase cycle split
 };
 
-// byte offset of fp32 element (row c, unit u) inside one 128B-swizzled staging plane [N][32]
-__device__ __forceinline__ uint32_t plane_off(int c, int u) {
-  return (uint32_t)(c * 128 + ((((u >> 2) ^ (c & 7)) & 7) << 4) + ((u & 3) << 2));
-}
-__device__ __forceinline__ float sel4(int k, float a0, float a1, float a2, float a3) {
-  return k == 0 ? a0 : (k == 1 ? a1 : (k == 2 ? a2 : a3));
+// Staging planes are [N columns][32 units] fp32 with the TMA 128B swizzle: element (c, u) sits at byte
+// c*128 + (((u>>2) ^ (c&7)) << 4) + ((u&3) << 2).
+// debug timing: one running 32-bit timestamp per thread, laps accumulate into shared-memory slots
+#define TCR_LAP(slot) do { if (dbg) { const uint32_t now_ = (uint32_t)clock(); (slot) += (long long)(now_ - lapt); lapt = now_; } } while (0)
+
+// y_k = x[g ^ k] for g = lo + 2*hi, branch-free (8 selects)
+__device__ __forceinline__ void perm4(bool lo, bool hi, float x0, float x1, float x2, float x3, float &y0, float &y1,
+                                      float &y2, float &y3) {
+  const float a0 = lo ? x1 : x0, a1 = lo ? x0 : x1, a2 = lo ? x3 : x2, a3 = lo ? x2 : x3;
+  y0 = hi ? a2 : a0; y1 = hi ? a3 : a1; y2 = hi ? a0 : a2; y3 = hi ? a1 : a3;
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -92,7 +97,7 @@ __device__ __forceinline__ float sel4(int k, float a0, float a1, float a2, float
 // ------------------------------------------------------------------------------------------------
 // N = 16*NCH batch columns per cluster.  Epilogue warp (quarter q = warp%4, column group cg) owns
 // accumulator rows 32q..32q+31 (row e = 4u+g: unit u, gate g) and columns [cg*N/4, (cg+1)*N/4).
-template <int NCH>
+template <int NCH, bool DBG>
 __global__ void __launch_bounds__(TCR_THREADS, 1)
 lstm_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_h, const __grid_constant__ CUtensorMap tm_xw, TcRnnArgs a) {
   constexpr int N = 16 * NCH;
@@ -127,7 +132,11 @@ lstm_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_h, const __grid_consta
     for (int i = tid; i < a.wimg_bytes / 16; i += TCR_THREADS) dst[i] = __ldg(src + i);
   }
   if (tid == 0) {
-    mbar_init(bar_h, a.mcast ? 1 : 32 * TCR_EPI_WARPS);
+    if (a.mcast) {
+      for (int kb = 0; kb < nkb; ++kb) mbar_init(bar_h + 8 * kb, 1);  // one per k-block: the product starts as blocks land
+    } else {
+      mbar_init(bar_h, 32 * TCR_EPI_WARPS);
+    }
     mbar_init(bar_acc, 1);
     mbar_init(bar_xw, 1);
     mbar_init(bar_out, 32 * TCR_EPI_WARPS);
@@ -186,26 +195,43 @@ lstm_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_h, const __grid_consta
   cluster_sync_all();
 
   const uint32_t idesc = make_idesc_bf16(128, N, false, false);
-  uint64_t dA[8], dB[8];
+  // operand descriptors of k-block 0; the address field counts 16-byte units, so k-block kb adds a constant
+  const uint64_t dA0 = make_desc(s_w, 0, 1024), dB0 = make_desc(s_h, 0, 1024);
+  __shared__ long long tk[2][6];  // debug cycle counters ([0]: MMA warp, [1]: epilogue thread); shared memory, not registers
+  if (tid < 12) (&tk[0][0])[tid] = 0;
+  const bool dbg = DBG && rank == 0 && cluster_id_x() == 0 && (tid == 64 || warp == 1);
+
+  // per-thread constants of the elementwise phase: item `it` is column cb + 4*it of unit uo
+  const int cb = cg * CPW + eg;
+  const bool g_lo = (eg & 1) != 0, g_hi = (eg & 2) != 0;
+  uint32_t valid = 0;
 #pragma unroll
-  for (int kb = 0; kb < 8; ++kb) {
-    dA[kb] = make_desc(s_w + (uint32_t)kb * 16384u, 0, 1024);
-    dB[kb] = make_desc(s_h + (uint32_t)kb * (N * 128), 0, 1024);
-  }
-  long long tk[6] = {0, 0, 0, 0, 0, 0};
-  const bool dbg = a.debug && rank == 0 && cluster_id_x() == 0 && (tid == 64 || warp == 1);
+  for (int it = 0; it < NCH; ++it)
+    if (b0 + cb + 4 * it < B) valid |= 1u << it;
+  const bool tile_full = b0 + N <= B;
+  // staging-plane address of (column, unit): columns 4 apart flip bit 2 of the 128B-swizzle phase
+  const uint32_t swz = ((((uint32_t)(eu >> 2) ^ (uint32_t)cb) & 7u) << 4) + ((uint32_t)(eu & 3) << 2);
+  uint8_t *pl_e = xw_gen + cb * 128 + swz;
+  uint8_t *pl_o = xw_gen + cb * 128 + (swz ^ 64u);
+  const float *init_c = init_gen + cb * 32 + eu;
+  const int H4 = 4 * H;
+  const size_t BH = (size_t)B * H;
+  __nv_bfloat16 *o_p = a.out_bf + (size_t)(b0 + cb) * H + uo;             // out[t]
+  __nv_bfloat16 *h_p = a.hprev_bf + ((size_t)B + b0 + cb) * H + uo;       // hprev[t+1]
+  float *c_p = a.cprev + ((size_t)B + b0 + cb) * H + uo;                  // cprev[t+1]
+  const unsigned char *eoc_p = a.eoc + b0 + cb;                            // eoc[t]
 
   for (int t = 0; t < T; ++t) {
-    long long c0 = 0, c1 = 0, c2 = 0, c3 = 0;
-    if (dbg) c0 = clock64();
+    uint32_t lapt = 0;
+    if (dbg) lapt = (uint32_t)clock();
     if (warp == 0) {
       if (elect_one()) {
         if (a.mcast) {
           // every rank expects the whole tile and fetches one half k-block of it for everybody
           fence_proxy_async();
-          mbar_expect_tx(bar_h, nkb * N * 128);
+          for (int kb = 0; kb < nkb; ++kb) mbar_expect_tx(bar_h + 8 * kb, N * 128);
           const int kb = rank >> 1, half = rank & 1;
-          tma_load_3d_multicast(s_h + (uint32_t)kb * (N * 128) + (uint32_t)half * (N / 2) * 128, &tm_h, bar_h, kb * 64,
+          tma_load_3d_multicast(s_h + (uint32_t)kb * (N * 128) + (uint32_t)half * (N / 2) * 128, &tm_h, bar_h + 8 * kb, kb * 64,
                                 b0 + half * (N / 2), t, (uint16_t)((1u << a.CS) - 1u));
         }
         mbar_expect_tx(bar_xw, 4 * N * 128);
@@ -218,26 +244,30 @@ lstm_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_h, const __grid_consta
       }
       __syncwarp();
     } else if (warp == 1) {
-      mbar_wait(bar_h, t & 1);
-      if (dbg) { c1 = clock64(); c2 = c1; }
+      if (!a.mcast) mbar_wait(bar_h, t & 1);
+      if (lane == 0) TCR_LAP(tk[0][0]);
       tc_fence_after();
       if (elect_one()) {
 #pragma unroll
         for (int kb = 0; kb < 8; ++kb) {
           if (kb < nkb) {
+            if (a.mcast) {
+              mbar_wait(bar_h + 8 * kb, t & 1);
+              tc_fence_after();
+            }
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
               if (a.a_tmem)
-                tc_mma_bf16_ts(tmem_acc, tmem_a + (uint32_t)(kb * 32 + k * 8), dB[kb] + (uint64_t)(2 * k), idesc, (kb > 0 || k > 0) ? 1u : 0u);
+                tc_mma_bf16_ts(tmem_acc, tmem_a + (uint32_t)(kb * 32 + k * 8), dB0 + (uint64_t)(kb * (N * 8) + 2 * k), idesc, (kb > 0 || k > 0) ? 1u : 0u);
               else
-                tc_mma_bf16(tmem_acc, dA[kb] + (uint64_t)(2 * k), dB[kb] + (uint64_t)(2 * k), idesc, (kb > 0 || k > 0) ? 1u : 0u);
+                tc_mma_bf16(tmem_acc, dA0 + (uint64_t)(kb * 1024 + 2 * k), dB0 + (uint64_t)(kb * (N * 8) + 2 * k), idesc, (kb > 0 || k > 0) ? 1u : 0u);
             }
           }
         }
         tc_commit(bar_acc);
       }
       __syncwarp();
-      if (dbg) { c3 = clock64(); tk[0] += c1 - c0; tk[1] += c2 - c1; tk[2] += c3 - c2; }
+      if (lane == 0) TCR_LAP(tk[0][2]);
     } else {
       // h_{t-1} tile of my cluster's rows (all H units, written by all ranks last step): L2 -> swizzled smem
       if (!a.mcast) {
@@ -276,41 +306,40 @@ lstm_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_h, const __grid_consta
       float dsc[NCH];
 #pragma unroll
       for (int it = 0; it < NCH; ++it) {
-        const int b = b0 + cg * CPW + 4 * it + eg;
         dsc[it] = 1.0f;
-        if (b < B) {
-          if (__ldg(a.eoc + (size_t)t * B + b)) eoc_bits |= 1u << it;
-          if (a.dropout) dsc[it] = drop_scale(a.mask, b, T, t, H, uo, a.row0, a.seed, a.keep);
+        if ((valid >> it) & 1u) {
+          if (__ldg(eoc_p + 4 * it)) eoc_bits |= 1u << it;
+          if (a.dropout) dsc[it] = drop_scale(a.mask, b0 + cb + 4 * it, T, t, H, uo, a.row0, a.seed, a.keep);
         }
       }
-      if (dbg) c1 = clock64();
+      const bool more = t + 1 < T;
+      TCR_LAP(tk[1][0]);
       mbar_wait(bar_acc, t & 1);
-      if (dbg) c2 = clock64();
+      TCR_LAP(tk[1][1]);
       tc_fence_after();
       uint32_t r[CPW];
       tc_ldn<CPW>(tmem_acc + ((uint32_t)(32 * q) << 16) + (uint32_t)(cg * CPW), r);
       mbar_wait(bar_xw, t & 1);
-      if (dbg) c3 = clock64();
-      const int s1 = eg ^ 1, s2 = eg ^ 2, s3 = eg ^ 3;
+      TCR_LAP(tk[1][2]);
       constexpr bool DEFER = NCH <= 2;  // small tiles are latency-bound: publish h first, store the rest after arriving
-      float sv[DEFER ? NCH : 1][7];
+      float sv[DEFER ? NCH : 1][3];
+      auto items = [&](auto full_tag) {  // FULL: every column of the tile is a real batch row (no per-item bound checks)
+      constexpr bool FULL = decltype(full_tag)::value;
 #pragma unroll
       for (int it = 0; it < NCH; ++it) {
-        const float x0 = __uint_as_float(r[4 * it + 0]), x1 = __uint_as_float(r[4 * it + 1]);
-        const float x2 = __uint_as_float(r[4 * it + 2]), x3 = __uint_as_float(r[4 * it + 3]);
-        // 4-lane exchange: round rr brings gate (eg^rr) of column 4*it + eg from lane^rr
-        const float r0 = sel4(eg, x0, x1, x2, x3);
-        const float r1 = __shfl_xor_sync(0xffffffffu, sel4(s1, x0, x1, x2, x3), 1);
-        const float r2 = __shfl_xor_sync(0xffffffffu, sel4(s2, x0, x1, x2, x3), 2);
-        const float r3 = __shfl_xor_sync(0xffffffffu, sel4(s3, x0, x1, x2, x3), 3);
-        const float p0 = sel4(eg, r0, r1, r2, r3), p1 = sel4(s1, r0, r1, r2, r3);
-        const float p2 = sel4(s2, r0, r1, r2, r3), p3 = sel4(s3, r0, r1, r2, r3);
-        const int c = cg * CPW + 4 * it + eg;
-        const int b = b0 + c;
-        if (b < B) {
-          const uint32_t po = plane_off(c, eu);
-          float *x0p = reinterpret_cast<float *>(xw_gen + 0 * (N * 128) + po), *x1p = reinterpret_cast<float *>(xw_gen + 1 * (N * 128) + po);
-          float *x2p = reinterpret_cast<float *>(xw_gen + 2 * (N * 128) + po), *x3p = reinterpret_cast<float *>(xw_gen + 3 * (N * 128) + po);
+        // 4-lane exchange: lane eg sends gate row eg's value of column 4*it + (eg^k) in round k and so collects
+        // all four gates of its own column 4*it + eg
+        float v0, v1, v2, v3, p0, p1, p2, p3;
+        perm4(g_lo, g_hi, __uint_as_float(r[4 * it + 0]), __uint_as_float(r[4 * it + 1]), __uint_as_float(r[4 * it + 2]),
+              __uint_as_float(r[4 * it + 3]), v0, v1, v2, v3);
+        v1 = __shfl_xor_sync(0xffffffffu, v1, 1);
+        v2 = __shfl_xor_sync(0xffffffffu, v2, 2);
+        v3 = __shfl_xor_sync(0xffffffffu, v3, 3);
+        perm4(g_lo, g_hi, v0, v1, v2, v3, p0, p1, p2, p3);
+        if (FULL || ((valid >> it) & 1u)) {
+          uint8_t *pp = ((it & 1) ? pl_o : pl_e) + it * 512;
+          float *x0p = reinterpret_cast<float *>(pp), *x1p = reinterpret_cast<float *>(pp + 1 * (N * 128));
+          float *x2p = reinterpret_cast<float *>(pp + 2 * (N * 128)), *x3p = reinterpret_cast<float *>(pp + 3 * (N * 128));
           const float ig = sigmoid_approx(p0 + *x0p);
           const float jg = tanh_approx(p1 + *x1p);
           const float fg = sigmoid_approx(p2 + *x2p + 1.0f);
@@ -318,65 +347,66 @@ lstm_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_h, const __grid_consta
           *x0p = ig; *x1p = jg; *x2p = fg; *x3p = og;  // staged for the TMA store
           const float c2 = fmaf(cst[it], fg, ig * jg);
           const float h2 = tanh_approx(c2) * og;
-          const bool eoc = (eoc_bits >> it) & 1u;
-          const float cn = eoc ? init_gen[(0 * N + c) * 32 + eu] : c2;
-          const float hn = eoc ? init_gen[(1 * N + c) * 32 + eu] : h2;
+          float cn = c2, hn = h2;
+          if ((eoc_bits >> it) & 1u) { cn = init_c[it * 128]; hn = init_c[N * 32 + it * 128]; }
           cst[it] = cn;
-          const size_t ix = ((size_t)t * B + b) * H + uo, nx = ix + (size_t)B * H;
-          if (t + 1 < T) a.hprev_bf[nx] = __float2bfloat16_rn(hn);  // exchange medium first
+          if (more) h_p[it * H4] = __float2bfloat16_rn(hn);  // exchange medium first
           if constexpr (DEFER) {
-            sv[it][4] = h2 * dsc[it]; sv[it][5] = cn; sv[it][6] = hn;
+            sv[it][0] = h2 * dsc[it]; sv[it][1] = cn; sv[it][2] = hn;
           } else {
-            a.out_bf[ix] = __float2bfloat16_rn(h2 * dsc[it]);
-            if (t + 1 < T) {
-              a.cprev[nx] = cn;
+            o_p[it * H4] = __float2bfloat16_rn(h2 * dsc[it]);
+            if (more) {
+              c_p[it * H4] = cn;
             } else {
-              a.state_out[(size_t)b * S + uo] = cn;
-              a.state_out[(size_t)b * S + H + uo] = hn;
+              float *so = a.state_out + (size_t)(b0 + cb + 4 * it) * S + uo;
+              so[0] = cn; so[H] = hn;
             }
           }
         }
       }
+      };
+      if (tile_full) items(std::true_type{}); else items(std::false_type{});
+      TCR_LAP(tk[1][3]);
       fence_proxy_async_smem();
       mbar_arrive(bar_out);
       if (a.mcast) fence_proxy_async();  // my h stores -> visible to the other ranks' TMA loads
-      if (dbg) { long long c4 = clock64(); tk[0] += c1 - c0; tk[1] += c2 - c1; tk[2] += c3 - c2; tk[3] += c4 - c3; c0 = c4; }
+      TCR_LAP(tk[1][5]);
       if constexpr (DEFER) {
         __syncwarp();
         tc_fence_before();
         cluster_arrive();  // release: the h stores above are what the other ranks wait for
 #pragma unroll
         for (int it = 0; it < NCH; ++it) {
-          const int b = b0 + cg * CPW + 4 * it + eg;
-          if (b < B) {
-            const size_t row = (size_t)t * B + b;
-            a.out_bf[row * H + uo] = __float2bfloat16_rn(sv[it][4]);
-            if (t + 1 < T) {
-              a.cprev[(row + B) * H + uo] = sv[it][5];
+          if ((valid >> it) & 1u) {
+            o_p[it * H4] = __float2bfloat16_rn(sv[it][0]);
+            if (more) {
+              c_p[it * H4] = sv[it][1];
             } else {
-              a.state_out[(size_t)b * S + uo] = sv[it][5];
-              a.state_out[(size_t)b * S + H + uo] = sv[it][6];
+              float *so = a.state_out + (size_t)(b0 + cb + 4 * it) * S + uo;
+              so[0] = sv[it][1]; so[H] = sv[it][2];
             }
           }
         }
+        o_p += BH; h_p += BH; c_p += BH; eoc_p += B;
         cluster_wait();
         tc_fence_after();
-        if (dbg && tid == 64) tk[4] += clock64() - c0;
+        if (tid == 64) TCR_LAP(tk[1][4]);
         continue;
       }
+      o_p += BH; h_p += BH; c_p += BH; eoc_p += B;
     }
     __syncwarp();
     tc_fence_before();
     cluster_sync_all();  // arrive.release publishes the h stores to the other ranks
     tc_fence_after();
-    if (dbg && tid == 64) tk[4] += clock64() - c0;
+    if (tid == 64) TCR_LAP(tk[1][4]);
   }
   if (dbg && tid == 32)
     printf("[tc fwd N=%d] MMA thread cycles/step: barrier->h tile ready %lld, (unused) %lld, issue+commit %lld\n", N,
-           tk[0] / T, tk[1] / T, tk[2] / T);
+           tk[0][0] / T, tk[0][1] / T, tk[0][2] / T);
   if (dbg && tid == 64)
-    printf("[tc fwd N=%d] epilogue cycles/step: prefetch %lld, wait acc %lld, tmem ld + xw wait %lld, items+stores+fence %lld, cluster barrier %lld\n",
-           N, tk[0] / T, tk[1] / T, tk[2] / T, tk[3] / T, tk[4] / T);
+    printf("[tc fwd N=%d] epilogue cycles/step: prefetch %lld, wait acc %lld, tmem ld + xw wait %lld, items+stores %lld, fences %lld, cluster barrier %lld\n",
+           N, tk[1][0] / T, tk[1][1] / T, tk[1][2] / T, tk[1][3] / T, tk[1][5] / T, tk[1][4] / T);
   if (warp == 0 && elect_one()) tma_store_wait_all();
   __syncthreads();
   if (warp == 1) tc_dealloc(tmem_acc, (uint32_t)a.tmem_cols);
@@ -385,9 +415,10 @@ lstm_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_h, const __grid_consta
 // ------------------------------------------------------------------------------------------------
 // backward
 // ------------------------------------------------------------------------------------------------
-// Elementwise items: thread (unit u = e/4, sub = e%4, column group cg) owns the NCH consecutive
-// columns c = cg*N/4 + sub*NCH + it of unit u.
-template <int NCH>
+// Elementwise items: thread (unit u = e/4, sub = e%4, column group cg) owns the NCH columns
+// c = cg*N/4 + 4*it + sub of unit u (the 4 lanes of a unit touch consecutive rows of the 128B-swizzled
+// staging tiles, i.e. distinct banks).
+template <int NCH, bool DBG>
 __global__ void __launch_bounds__(TCR_THREADS, 1)
 lstm_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm_acts, TcRnnArgs a) {
   constexpr int N = 16 * NCH;
@@ -438,7 +469,7 @@ lstm_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm_acts, TcRnnArgs a) {
   const int e = 32 * q + lane;
   const int eu = e >> 2, esub = e & 3;
   const int uo = u0 + eu;
-  const int c_first = cg * CPW + esub * NCH;
+  const int c0 = cg * CPW + esub;
   float dhc[NCH], dcc[NCH];
   float bsum[4] = {0.f, 0.f, 0.f, 0.f};  // bias gradient of my unit over my columns and all steps
   uint64_t dBk[2];
@@ -448,26 +479,48 @@ lstm_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm_acts, TcRnnArgs a) {
   for (int it = 0; it < NCH; ++it) { dhc[it] = 0.f; dcc[it] = 0.f; }
   const uint32_t idesc = make_idesc_bf16(128, N, false, false);
   __nv_bfloat16 *part_base = a.partial + (size_t)cid * 2 * CS * H * N;
+  // partial d(h) exchange layout, per parity: [dst rank][src rank][column group][chunk j][unit 32][CK columns]:
+  // the writer's lanes (= units of the destination rank) and the reader's lanes both touch whole 128-byte lines
+  constexpr int CK = CPW >= 8 ? 8 : CPW;
+  constexpr int NJ = CPW / CK;
+  const size_t part_blk = (size_t)NJ * 32 * CK;  // one (dst, src, cg) block = 32 units x CPW columns
 
-  long long tk[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-  const bool dbg = a.debug && rank == 0 && cid == 0 && tid == 64;
+  __shared__ long long tk[8];  // debug cycle counters (shared memory, not registers)
+  if (tid < 8) tk[tid] = 0;
+  const bool dbg = DBG && rank == 0 && cid == 0 && tid == 64;
+  // per-thread constants of the elementwise phase: item `it` is column c0 + 4*it of unit uo
+  uint32_t valid = 0;
+#pragma unroll
+  for (int it = 0; it < NCH; ++it)
+    if (b0 + c0 + 4 * it < B) valid |= 1u << it;
+  const bool tile_full = b0 + N <= B;
+  const size_t BH = (size_t)B * H, BG = (size_t)B * G;
+  const float *do_p = a.dout + ((size_t)(T - 1) * B + b0 + c0) * H + uo;
+  const float *cp_p = a.cprev + ((size_t)(T - 1) * B + b0 + c0) * H + uo;
+  const unsigned char *eoc_p = a.eoc + (size_t)(T - 1) * B + b0 + c0;
+  __nv_bfloat16 *d_p = a.dpre_bf + ((size_t)(T - 1) * B + b0 + c0) * G + uo;
+  const int H4 = 4 * H;
+  // columns 4 apart flip bit 2 of the 128B-swizzle phase
+  const uint32_t ac_sw = ((((uint32_t)(eu >> 2) ^ (uint32_t)c0) & 7u) << 4);
+  const uint8_t *ac0 = ac_gen + c0 * 128 + ((eu & 3) << 2);
+  const uint32_t b_sw = (((((uint32_t)(eu & 15) >> 1) ^ (uint32_t)c0) & 7u) << 4);
+  uint8_t *bg0 = b_gen + (eu >> 4) * (N * 128) + c0 * 128 + ((eu & 1) << 3);
   // per-item global inputs of a step: d(out), c fed to the step, eoc flag (dropout folded into d(out))
   float d_o[NCH], cp[NCH];
   uint32_t eoc_bits = 0;
-  auto load_inputs = [&](int tt) {
+  auto load_inputs = [&](int tt) {  // must be called for tt = T-1, T-2, ... in turn (running pointers)
     eoc_bits = 0;
 #pragma unroll
     for (int it = 0; it < NCH; ++it) {
-      const int b = b0 + c_first + it;
       d_o[it] = 0.f; cp[it] = 0.f;
-      if (b < B) {
-        const size_t row = (size_t)tt * B + b;
-        d_o[it] = a.dout[row * H + uo];
-        cp[it] = a.cprev[row * H + uo];
-        if (__ldg(a.eoc + (size_t)tt * B + b)) eoc_bits |= 1u << it;
-        if (a.dropout) d_o[it] *= drop_scale(a.mask, b, T, tt, H, uo, a.row0, a.seed, a.keep);
+      if ((valid >> it) & 1u) {
+        d_o[it] = do_p[it * H4];
+        cp[it] = cp_p[it * H4];
+        if (__ldg(eoc_p + 4 * it)) eoc_bits |= 1u << it;
+        if (a.dropout) d_o[it] *= drop_scale(a.mask, b0 + c0 + 4 * it, T, tt, H, uo, a.row0, a.seed, a.keep);
       }
     }
+    do_p -= BH; cp_p -= BH; eoc_p -= B;
   };
   if (warp >= 2) load_inputs(T - 1);
   if (warp == 0 && elect_one()) {
@@ -477,8 +530,8 @@ lstm_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm_acts, TcRnnArgs a) {
   __syncwarp();
   for (int t = T - 1, step = 0; t >= 0; --t, ++step) {
     const int par = step & 1;
-    long long c0 = 0, c1 = 0, c2 = 0, c3 = 0, c4 = 0, c5 = 0;
-    if (dbg) c0 = clock64();
+    uint32_t lapt = 0;
+    if (dbg) lapt = (uint32_t)clock();
     if (warp == 0) {
       // the staged activations of step t were requested one step ahead; once the elementwise phase has
       // consumed them (bar_ready), request step t-1's so the load overlaps the product and the exchange
@@ -490,17 +543,17 @@ lstm_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm_acts, TcRnnArgs a) {
       __syncwarp();
     } else if (warp >= 2) {
       mbar_wait(bar_acts, step & 1);
-      if (dbg) c1 = clock64();
+      TCR_LAP(tk[0]);
+      auto items = [&](auto full_tag) {
+      constexpr bool FULL = decltype(full_tag)::value;
 #pragma unroll
       for (int it = 0; it < NCH; ++it) {
-        const int c = c_first + it;
-        const int b = b0 + c;
-        if (b < B) {
-          const uint32_t po = plane_off(c, eu);
-          const float ig = *reinterpret_cast<const float *>(ac_gen + 0 * (N * 128) + po);
-          const float jg = *reinterpret_cast<const float *>(ac_gen + 1 * (N * 128) + po);
-          const float fg = *reinterpret_cast<const float *>(ac_gen + 2 * (N * 128) + po);
-          const float og = *reinterpret_cast<const float *>(ac_gen + 3 * (N * 128) + po);
+        if (FULL || ((valid >> it) & 1u)) {
+          const uint8_t *ap = ac0 + it * 512 + (ac_sw ^ (uint32_t)((it & 1) << 6));
+          const float ig = *reinterpret_cast<const float *>(ap + 0 * (N * 128));
+          const float jg = *reinterpret_cast<const float *>(ap + 1 * (N * 128));
+          const float fg = *reinterpret_cast<const float *>(ap + 2 * (N * 128));
+          const float og = *reinterpret_cast<const float *>(ap + 3 * (N * 128));
           const bool eoc = (eoc_bits >> it) & 1u;
           const float dh2 = d_o[it] + (eoc ? 0.f : dhc[it]);
           const float tc = tanh_approx(fmaf(cp[it], fg, ig * jg));
@@ -509,25 +562,23 @@ lstm_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm_acts, TcRnnArgs a) {
           const float d0 = dc2 * jg * ig * (1.0f - ig), d1 = dc2 * ig * (1.0f - jg * jg);
           const float d2 = dc2 * cp[it] * fg * (1.0f - fg), d3 = dh2 * tc * og * (1.0f - og);
           bsum[0] += d0; bsum[1] += d1; bsum[2] += d2; bsum[3] += d3;
-          const size_t row = (size_t)t * B + b;
-          __nv_bfloat16 *db = a.dpre_bf + row * G + uo;
+          __nv_bfloat16 *db = d_p + (size_t)it * 4 * G;
           const __nv_bfloat16 h0 = __float2bfloat16_rn(d0), h1 = __float2bfloat16_rn(d1);
           const __nv_bfloat16 h2 = __float2bfloat16_rn(d2), h3 = __float2bfloat16_rn(d3);
           db[0] = h0; db[H] = h1; db[2 * H] = h2; db[3 * H] = h3;
           // own K slice, local column kk = 4u+g: 8 bytes at (row c, kk = 4u) of the swizzled operand
-          const int kk = 4 * eu;
-          const uint32_t off = (uint32_t)((kk >> 6) * (N * 128) + c * 128 + (((((kk & 63) >> 3) ^ (c & 7)) & 7) << 4) +
-                                          ((kk & 7) << 1));
           uint2 pk;
           pk.x = (uint32_t)__bfloat16_as_ushort(h0) | ((uint32_t)__bfloat16_as_ushort(h1) << 16);
           pk.y = (uint32_t)__bfloat16_as_ushort(h2) | ((uint32_t)__bfloat16_as_ushort(h3) << 16);
-          *reinterpret_cast<uint2 *>(b_gen + off) = pk;
+          *reinterpret_cast<uint2 *>(bg0 + it * 512 + (b_sw ^ (uint32_t)((it & 1) << 6))) = pk;
         }
       }
+      };
+      if (tile_full) items(std::true_type{}); else items(std::false_type{});
+      d_p -= BG;
       fence_proxy_async_smem();
       mbar_arrive(bar_ready);
-      if (dbg) c2 = clock64();
-      if (t > 0) load_inputs(t - 1);  // next step's per-item inputs, in flight during the product
+      TCR_LAP(tk[1]);
     }
     if (t > 0) {
       if (warp == 1) {
@@ -549,24 +600,27 @@ lstm_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm_acts, TcRnnArgs a) {
         __syncwarp();
       } else if (warp >= 2) {
         mbar_wait(bar_acc, step & 1);
-        if (dbg) c3 = clock64();
+        TCR_LAP(tk[2]);
         tc_fence_after();
         for (int mt = 0; mt < nmt; ++mt) {
           const int m = mt * 128 + e;  // hidden unit of this lane's accumulator row
           uint32_t r[CPW];
           tc_ldn<CPW>(tmem_acc + ((uint32_t)(32 * q) << 16) + (uint32_t)(mt * N + cg * CPW), r);
           if (m < H) {
-            __nv_bfloat16 *dst = part_base + ((size_t)(par * CS + rank) * H + m) * N + cg * CPW;
+            // rows 32q..32q+31 of this m-tile are the units of destination rank 4*mt + q; lane = unit
+            __nv_bfloat16 *dst = part_base + (((size_t)(par * CS + (m >> 5)) * CS + rank) * 4 + cg) * part_blk + lane * CK;
             uint32_t pk[CPW / 2];
 #pragma unroll
             for (int j = 0; j < CPW / 2; ++j) {
-              const __nv_bfloat162 v = __floats2bfloat162_rn(__uint_as_float(r[2 * j]), __uint_as_float(r[2 * j + 1]));
+              // position pos = sub*NCH + it of the block row holds column 4*it + sub (the reader's item order)
+              const int ca = 4 * ((2 * j) % NCH) + (2 * j) / NCH, cb2 = 4 * ((2 * j + 1) % NCH) + (2 * j + 1) / NCH;
+              const __nv_bfloat162 v = __floats2bfloat162_rn(__uint_as_float(r[ca]), __uint_as_float(r[cb2]));
               pk[j] = *reinterpret_cast<const uint32_t *>(&v);
             }
             if constexpr (CPW >= 8) {
 #pragma unroll
-              for (int j = 0; j < CPW / 8; ++j)
-                *reinterpret_cast<uint4 *>(dst + 8 * j) = make_uint4(pk[4 * j], pk[4 * j + 1], pk[4 * j + 2], pk[4 * j + 3]);
+              for (int j = 0; j < NJ; ++j)
+                *reinterpret_cast<uint4 *>(dst + j * 32 * CK) = make_uint4(pk[4 * j], pk[4 * j + 1], pk[4 * j + 2], pk[4 * j + 3]);
             } else {
               *reinterpret_cast<uint2 *>(dst) = make_uint2(pk[0], pk[1]);
             }
@@ -574,45 +628,71 @@ lstm_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm_acts, TcRnnArgs a) {
         }
       }
     }
-    if (dbg) c4 = clock64();
+    TCR_LAP(tk[3]);
     __syncwarp();
     tc_fence_before();
     cluster_sync_all();
     tc_fence_after();
-    if (dbg) c5 = clock64();
+    TCR_LAP(tk[4]);
     if (t > 0 && warp >= 2) {
+      // next step's per-item inputs: issued here so that they are in flight during the partial reads but not
+      // live across the accumulator read-out above
+      load_inputs(t - 1);
+      TCR_LAP(tk[6]);
       // d(h_{t-1}) for my units = sum over ranks (fixed order) of their partials
 #pragma unroll
       for (int it = 0; it < NCH; ++it) dhc[it] = 0.f;
-      for (int r = 0; r < CS; ++r) {
-        const __nv_bfloat16 *src = part_base + ((size_t)(par * CS + r) * H + uo) * N + c_first;
+      // my NCH items sit at positions esub*NCH .. +NCH of the block row: chunk (esub*NCH)/CK, offset (esub*NCH)%CK
+      const __nv_bfloat16 *src0 = part_base + (((size_t)(par * CS + rank) * CS) * 4 + cg) * part_blk +
+                                  ((size_t)((esub * NCH) / CK) * 32 + eu) * CK + (esub * NCH) % CK;
+      constexpr int UR = 8;  // loads in flight (L2 latency bound otherwise); the sum stays in rank order
+      for (int r0 = 0; r0 < CS; r0 += UR) {
         if constexpr (NCH == 8) {
-          const uint4 v = __ldcg(reinterpret_cast<const uint4 *>(src));
-          const float2 f0 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162 *>(&v.x));
-          const float2 f1 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162 *>(&v.y));
-          const float2 f2 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162 *>(&v.z));
-          const float2 f3 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162 *>(&v.w));
-          dhc[0] += f0.x; dhc[1] += f0.y; dhc[2] += f1.x; dhc[3] += f1.y;
-          dhc[4] += f2.x; dhc[5] += f2.y; dhc[6] += f3.x; dhc[7] += f3.y;
-        } else if constexpr (NCH % 4 == 0) {
+          uint4 v[UR];
 #pragma unroll
-          for (int it = 0; it < NCH; it += 4) {
-            const uint2 v = __ldcg(reinterpret_cast<const uint2 *>(src + it));
-            const float2 f0 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162 *>(&v.x));
-            const float2 f1 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162 *>(&v.y));
-            dhc[it] += f0.x; dhc[it + 1] += f0.y; dhc[it + 2] += f1.x; dhc[it + 3] += f1.y;
+          for (int j = 0; j < UR; ++j)
+            v[j] = (r0 + j < CS) ? __ldcg(reinterpret_cast<const uint4 *>(src0 + (size_t)(r0 + j) * 4 * part_blk)) : make_uint4(0, 0, 0, 0);
+#pragma unroll
+          for (int j = 0; j < UR; ++j) {
+            const float2 f0 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162 *>(&v[j].x));
+            const float2 f1 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162 *>(&v[j].y));
+            const float2 f2 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162 *>(&v[j].z));
+            const float2 f3 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162 *>(&v[j].w));
+            dhc[0] += f0.x; dhc[1] += f0.y; dhc[2] += f1.x; dhc[3] += f1.y;
+            dhc[4] += f2.x; dhc[5] += f2.y; dhc[6] += f3.x; dhc[7] += f3.y;
+          }
+        } else if constexpr (NCH == 4) {
+          uint2 v[UR];
+#pragma unroll
+          for (int j = 0; j < UR; ++j)
+            v[j] = (r0 + j < CS) ? __ldcg(reinterpret_cast<const uint2 *>(src0 + (size_t)(r0 + j) * 4 * part_blk)) : make_uint2(0, 0);
+#pragma unroll
+          for (int j = 0; j < UR; ++j) {
+            const float2 f0 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162 *>(&v[j].x));
+            const float2 f1 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162 *>(&v[j].y));
+            dhc[0] += f0.x; dhc[1] += f0.y; dhc[2] += f1.x; dhc[3] += f1.y;
+          }
+        } else if constexpr (NCH == 2) {
+          uint32_t v[UR];
+#pragma unroll
+          for (int j = 0; j < UR; ++j)
+            v[j] = (r0 + j < CS) ? __ldcg(reinterpret_cast<const uint32_t *>(src0 + (size_t)(r0 + j) * 4 * part_blk)) : 0u;
+#pragma unroll
+          for (int j = 0; j < UR; ++j) {
+            const float2 f0 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162 *>(&v[j]));
+            dhc[0] += f0.x; dhc[1] += f0.y;
           }
         } else {
+          unsigned short v[UR];
 #pragma unroll
-          for (int it = 0; it < NCH; ++it)
-            dhc[it] += __bfloat162float(__ushort_as_bfloat16(__ldcg(reinterpret_cast<const unsigned short *>(src + it))));
+          for (int j = 0; j < UR; ++j)
+            v[j] = (r0 + j < CS) ? __ldcg(reinterpret_cast<const unsigned short *>(src0 + (size_t)(r0 + j) * 4 * part_blk)) : (unsigned short)0;
+#pragma unroll
+          for (int j = 0; j < UR; ++j) dhc[0] += __bfloat162float(__ushort_as_bfloat16(v[j]));
         }
       }
     }
-    if (dbg && t > 0) {
-      long long c6 = clock64();
-      tk[0] += c1 - c0; tk[1] += c2 - c1; tk[2] += c3 - c2; tk[3] += c4 - c3; tk[4] += c5 - c4; tk[5] += c6 - c5;
-    }
+    TCR_LAP(tk[5]);
   }
   if (warp >= 2 && a.dbias != nullptr) {
     // the 4 lanes of a unit (column sub-blocks) first, then one atomic per gate
@@ -625,8 +705,8 @@ lstm_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm_acts, TcRnnArgs a) {
     }
   }
   if (dbg)
-    printf("[tc bwd N=%d CS=%d] cycles/step: inputs+acts wait %lld, elementwise+stores %lld, MMA wait %lld, tmem ld + partial stores %lld, cluster barrier %lld, partial reads %lld\n",
-           N, CS, tk[0] / (T - 1), tk[1] / (T - 1), tk[2] / (T - 1), tk[3] / (T - 1), tk[4] / (T - 1), tk[5] / (T - 1));
+    printf("[tc bwd N=%d CS=%d] cycles/step: inputs+acts wait %lld, elementwise+stores %lld, MMA wait %lld, tmem ld + partial stores %lld, cluster barrier %lld, next inputs issue %lld, partial reads %lld\n",
+           N, CS, tk[0] / T, tk[1] / T, tk[2] / T, tk[3] / T, tk[4] / T, tk[6] / T, tk[5] / T);
   __syncthreads();
   if (warp == 1) tc_dealloc(tmem_acc, (uint32_t)a.tmem_cols);
 }
@@ -673,7 +753,7 @@ __global__ void pack_tc_image_kernel(int bwd, const float *__restrict__ mat, int
 template <int NCH>
 int launch_fwd(const CUtensorMap &tm_h, const CUtensorMap &tm_xw, const TcRnnArgs &a, int nclusters, size_t smem,
                cudaStream_t st) {
-  auto kern = lstm_fwd_tc_kernel<NCH>;
+  auto kern = a.debug ? lstm_fwd_tc_kernel<NCH, true> : lstm_fwd_tc_kernel<NCH, false>;
   SK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   if (a.CS > 8) SK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
   cudaLaunchConfig_t cfg = {};
@@ -690,7 +770,7 @@ int launch_fwd(const CUtensorMap &tm_h, const CUtensorMap &tm_xw, const TcRnnArg
 }
 template <int NCH>
 int launch_bwd(const CUtensorMap &tm_acts, const TcRnnArgs &a, int nclusters, size_t smem, cudaStream_t st) {
-  auto kern = lstm_bwd_tc_kernel<NCH>;
+  auto kern = a.debug ? lstm_bwd_tc_kernel<NCH, true> : lstm_bwd_tc_kernel<NCH, false>;
   SK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   if (a.CS > 8) SK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
   cudaLaunchConfig_t cfg = {};

@@ -245,6 +245,96 @@ def test_sampler_philox_seeded_mode_runs_and_is_deterministic():
     h.close()
 
 
+def _softmax(z):
+    e = np.exp(z - z.max(axis=1, keepdims=True))
+    return e / e.sum(axis=1, keepdims=True)
+
+
+def test_throughput_sampler_bf16_replayed_by_oracle():
+    """The tensor-core sampler (bf16 handle, many sketches; sampler_tc.cu) is not bit-exact, so it is
+    checked in two halves: (1) its per-step mixture parameters against the fp64 oracle replaying the
+    sampler's OWN trajectory step by step (state hold on eoc included) within the bf16 tolerance 2e-2;
+    (2) its draws against a NumPy redo of model.py:219-261 from the dumped parameters and uniforms."""
+    cfg = so.Config(model="lstm", rnn_size=256, num_layers=2, num_mixture=24)
+    params = so.init_params(cfg, seed=7, trained_like=True)
+    h = make_handle(cfg, params, precision="bf16")
+    n, steps, temp = 192, 24, 0.6
+    M = cfg.num_mixture
+    u = np.random.RandomState(3).rand(n, steps, 4).astype(np.float32)
+    strokes, lengths, mixp = h.sample(n, steps, temp, temp, False, uniforms=u, want_params=True)
+    strokes, lengths, mixp = strokes.cpu().numpy(), lengths.cpu().numpy(), mixp.cpu().numpy()
+    assert np.all(lengths == steps)
+    assert np.all(strokes[:, :, 2:].sum(axis=2) == 1.0)
+    assert strokes[:, :, 3].sum() > 0, "no eoc drawn: the state-hold branch is not covered"
+    p64 = f64(params)
+    state = so.zero_state(cfg, n, np.float64)
+    x = np.zeros((n, 1, 5))
+    worst = {}
+    for i in range(steps):
+        fw = so.forward(cfg, p64, x, state)
+        mdn = fw["mdn"]
+        got = mixp[:, i]
+        pi = mdn["pi"]
+        if i > 1:
+            pi = _softmax(np.log(pi) / temp) / temp
+        ref = {"pen": _softmax(mdn["pen"]), "pi": pi, "mu1": mdn["mu1"], "mu2": mdn["mu2"],
+               "sigma1": mdn["sigma1"], "sigma2": mdn["sigma2"], "corr": mdn["corr"]}
+        blocks = {"pen": got[:, 0:3]}
+        for k, name in enumerate(["pi", "mu1", "mu2", "sigma1", "sigma2", "corr"]):
+            blocks[name] = got[:, 3 + k * M:3 + (k + 1) * M]
+        for name in ref:
+            worst[name] = max(worst.get(name, 0.0), rel_err(blocks[name], ref[name]))
+        # (2) redo the draw from the dumped parameters
+        p = blocks["pi"] * (temp if i > 1 else 1.0)
+        cdf = np.cumsum(p.astype(np.float32), axis=1)
+        hit = cdf >= u[:, i, 0:1]
+        idx = np.where(hit.any(axis=1), hit.argmax(axis=1), M - 1)
+        pen = blocks["pen"]
+        pen_idx = np.where(pen[:, 0] >= u[:, i, 1], 0, np.where(pen[:, 0] + pen[:, 1] >= u[:, i, 1], 1, 2))
+        r = np.arange(n)
+        z1, z2 = so.box_muller(u[:, i, 2], u[:, i, 3])
+        rho = blocks["corr"][r, idx]
+        x1 = blocks["mu1"][r, idx] + blocks["sigma1"][r, idx] * z1
+        x2 = blocks["mu2"][r, idx] + blocks["sigma2"][r, idx] * (rho * z1 + np.sqrt(1 - rho * rho) * z2)
+        ok_pen = strokes[r, i, 2 + pen_idx] == 1.0
+        ok_xy = (np.abs(strokes[:, i, 0] - x1 * cfg.data_scale) < 1e-3 * cfg.data_scale) & \
+                (np.abs(strokes[:, i, 1] - x2 * cfg.data_scale) < 1e-3 * cfg.data_scale)
+        # draws on a CDF boundary may round either way; allow a handful
+        assert ok_pen.mean() > 0.98 and ok_xy.mean() > 0.98, (i, ok_pen.mean(), ok_xy.mean())
+        # the sampler's own point is the next input (model.py:259-261)
+        x = np.zeros((n, 1, 5))
+        x[:, 0, 0:2] = strokes[:, i, 0:2] / cfg.data_scale
+        x[:, 0, 2:5] = strokes[:, i, 2:5]
+        state = fw["final_state"]
+    assert max(worst.values()) < 2e-2, worst
+    h.close()
+
+
+def test_throughput_sampler_stop_determinism_and_sharding():
+    cfg = so.Config(model="lstm", rnn_size=128, num_layers=3, num_mixture=8)
+    params = so.init_params(cfg, seed=5, trained_like=True)
+    h = make_handle(cfg, params, precision="bf16")
+    n, steps = 160, 30
+    u = np.random.RandomState(9).rand(n, steps, 4).astype(np.float32)
+    full, _, _ = h.sample(n, steps, 0.8, 0.8, False, uniforms=u)
+    cut, lens, _ = h.sample(n, steps, 0.8, 0.8, True, uniforms=u)
+    full, cut, lens = full.cpu().numpy(), cut.cpu().numpy(), lens.cpu().numpy()
+    for i in range(n):
+        eoc = np.nonzero(full[i, :, 3])[0]
+        k = eoc[0] + 1 if len(eoc) else steps
+        assert lens[i] == k
+        assert np.array_equal(cut[i, :k], full[i, :k]) and np.all(cut[i, k:] == 0)
+    assert (lens < steps).any()
+    a, _, _ = h.sample(n, steps, 0.5, 0.5, False, seed=42)
+    b, _, _ = h.sample(n, steps, 0.5, 0.5, False, seed=42)
+    c, _, _ = h.sample(n, steps, 0.5, 0.5, False, seed=43)
+    assert np.array_equal(a.cpu().numpy(), b.cpu().numpy())
+    assert not np.array_equal(a.cpu().numpy(), c.cpu().numpy())
+    d, _, _ = h.sample(96, steps, 0.5, 0.5, False, seed=42, sketch0=64)
+    assert np.array_equal(a.cpu().numpy()[64:], d.cpu().numpy())
+    h.close()
+
+
 def test_errors_are_reported_not_thrown():
     from sketch_rnn_b200 import _lib
     with pytest.raises(Exception, match="model type not supported"):
