@@ -80,7 +80,8 @@ void free_workspace(SkWorkspace &w) {
     cudaFree(w.out_bf[l]);
     cudaFree(w.hprev_bf[l]);
     cudaFree(w.aux_bf[l]);
-    w.out_bf[l] = w.hprev_bf[l] = w.aux_bf[l] = nullptr;
+    cudaFree(w.acts_bf[l]);
+    w.out_bf[l] = w.hprev_bf[l] = w.aux_bf[l] = w.acts_bf[l] = nullptr;
   }
   w.cap_rows = 0;
 }
@@ -112,6 +113,7 @@ int ensure_workspace(skrnn_handle *h, int B, int T) {
       SK_CUDA(cudaMalloc(&w.out_bf[l], rows * h->H * e));
       SK_CUDA(cudaMalloc(&w.hprev_bf[l], rows * h->H * e));
       if (h->cfg.cell == SKRNN_CELL_GRU) SK_CUDA(cudaMalloc(&w.aux_bf[l], rows * h->H * e));
+      if (h->cfg.cell == SKRNN_CELL_LSTM) SK_CUDA(cudaMalloc(&w.acts_bf[l], rows * h->G * e));
     }
   }
   w.cap_rows = rows;

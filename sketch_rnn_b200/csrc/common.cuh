@@ -69,6 +69,8 @@ struct SkWorkspace {   // time-major activations for one (B, T) capacity
   __nv_bfloat16 *out_bf[SK_MAX_LAYERS] = {nullptr};  // [T,B,H]
   __nv_bfloat16 *hprev_bf[SK_MAX_LAYERS] = {nullptr};
   __nv_bfloat16 *aux_bf[SK_MAX_LAYERS] = {nullptr};  // gru r*h
+  __nv_bfloat16 *acts_bf[SK_MAX_LAYERS] = {nullptr}; // [T,B,H,4]: lstm gate activations i,j,f,o saved by the tcgen05
+                                                     // forward kernel for its BPTT counterpart
   __nv_bfloat16 *dpre_bf = nullptr;                  // [T,B,G] of the layer being differentiated
   __nv_bfloat16 *dlogits_bf = nullptr;               // [T*B,NOUTP]
   int64_t wpack_floats = 0;
@@ -111,6 +113,8 @@ struct skrnn_handle {
   bool tc_rnn_disabled = false;
   bool bias_grad_done = false;  // set by a backward recurrent kernel that accumulated d(bias) itself
   bool nt_rnn_disabled = false;
+  int fwd_family[SK_MAX_LAYERS] = {0};  // which kernels ran a layer's forward (0 fp32, 1 rnn_tc, 2 rnn_nt): they save
+                                        // activations in different places, so the backward must be the same family
   // optional per-category kernel timing (skrnn_profile_*): CUDA events around every launch
   bool prof_on = false;
   struct ProfRec { int cat; cudaEvent_t a, b; };
@@ -146,9 +150,9 @@ int sk_gemm_f32(skrnn_handle *h, cudaStream_t st, int M, int N, int K, const flo
 int sk_gemm_tc(skrnn_handle *h, cudaStream_t st, int M, int N, int K, const void *A, int lda, bool a_kmajor,
                const void *B, int ldb, bool b_kmajor, float *C, int ldc, const float *bias, bool accumulate);
 extern uint32_t g_tc_override[6];
-// 128B-swizzled tiled tensor map (rank 2 or 3).  elem_bytes: 2 (bf16) or 4 (fp32).
+// Tiled tensor map (rank 2..5), 128B-swizzled unless swizzle128 = false.  elem_bytes: 2 (bf16) or 4 (fp32).
 int sk_make_tmap(CUtensorMap *m, int elem_bytes, const void *ptr, int rank, const uint64_t *dims,
-                 const uint64_t *strides_bytes, const uint32_t *box);
+                 const uint64_t *strides_bytes, const uint32_t *box, bool swizzle128 = true);
 // tcgen05 recurrent kernels, large-batch variant (rnn_nt.cu): 0 ok, -1 not applicable
 int sk_rnn_nt_layer(skrnn_handle *h, cudaStream_t st, bool bwd, int l, int B, int T, const float *state_in,
                     float *state_out, const float *mask, uint64_t seed, int row0, bool training);

@@ -187,7 +187,7 @@ int make_map(CUtensorMap *m, const void *ptr, int64_t inner, int64_t outer, int6
 }  // namespace
 
 int sk_make_tmap(CUtensorMap *m, int elem_bytes, const void *ptr, int rank, const uint64_t *dims,
-                 const uint64_t *strides_bytes, const uint32_t *box) {
+                 const uint64_t *strides_bytes, const uint32_t *box, bool swizzle128) {
   EncodeTiledFn enc = get_encode();
   SK_CHECK(enc != nullptr, "cuTensorMapEncodeTiled is not available from the driver");
   cuuint64_t gdim[5], gstr[4];
@@ -197,7 +197,8 @@ int sk_make_tmap(CUtensorMap *m, int elem_bytes, const void *ptr, int rank, cons
   for (int i = 0; i + 1 < rank; ++i) gstr[i] = strides_bytes[i];
   CUresult r = enc(m, elem_bytes == 2 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32, rank,
                    const_cast<void *>(ptr), gdim, gstr, bx, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                   CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+                   swizzle128 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   SK_CHECK(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled(rank %d) failed with %d", rank, (int)r);
   return 0;
 }

@@ -428,7 +428,8 @@ int sk_rnn_nt_layer(skrnn_handle *h, cudaStream_t st, bool bwd, int l, int B, in
     // partial-exchange kernel of rnn_tc.cu for H = 512 BPTT unless explicitly enabled
     static int nb_env = -1;
     if (nb_env < 0) { const char *e = getenv("SKRNN_NT_BWD16"); nb_env = (e && e[0] == '1') ? 1 : 0; }
-    if (bwd && CS > 8 && !nb_env) return -1;
+    // (declined for the forward too: a layer's BPTT has to run in the family that saved its activations)
+    if (CS > 8 && !nb_env) return -1;
   }
   const int K = bwd ? 4 * H : H;
   const int nA = (K + 63) / 64;
@@ -436,6 +437,10 @@ int sk_rnn_nt_layer(skrnn_handle *h, cudaStream_t st, bool bwd, int l, int B, in
   const int img_bytes = nA * NB * 128;
   const size_t smem = (size_t)img_bytes + NT_RING * NT_KB_BYTES + 1024 + 256;
   if (smem > 227 * 1024) return -1;
+  if (!bwd) {  // same check for the backward configuration of this layer
+    const size_t smem_b = (size_t)((4 * H + 63) / 64) * 32 * 128 + NT_RING * NT_KB_BYTES + 1024 + 256;
+    if (smem_b > 227 * 1024) return -1;
+  }
   SK_CHECK((int64_t)img_bytes * CS <= h->ws.wpack_floats * 4, "weight image workspace too small");
   {
     SkLaunch scope(h, st, SK_CAT_MISC);

@@ -99,7 +99,8 @@ __device__ __forceinline__ void perm4(bool lo, bool hi, float x0, float x1, floa
 // accumulator rows 32q..32q+31 (row e = 4u+g: unit u, gate g) and columns [cg*N/4, (cg+1)*N/4).
 template <int NCH, bool DBG>
 __global__ void __launch_bounds__(TCR_THREADS, 1)
-lstm_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_h, const __grid_constant__ CUtensorMap tm_xw, TcRnnArgs a) {
+lstm_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_h, const __grid_constant__ CUtensorMap tm_xw,
+                   const __grid_constant__ CUtensorMap tm_act, TcRnnArgs a) {
   constexpr int N = 16 * NCH;
   constexpr int CPW = N / 4;  // columns per epilogue warp
   extern __shared__ uint8_t smem_raw[];
@@ -109,16 +110,16 @@ lstm_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_h, const __grid_consta
   const uint32_t s_w = base;                                  // nkb x [128 rows][128 B] (unless weights sit in TMEM)
   const uint32_t s_h = s_w + (a.a_tmem ? 0u : (uint32_t)nkb * 16384u);  // nkb x [N rows][128 B]
   const uint32_t s_xw = s_h + (uint32_t)nkb * (N * 128);      // 4 planes x [N][32] fp32
-  const uint32_t s_init = s_xw + 4u * (N * 128);              // [2][N][32] fp32: fed c / h (eoc reset source)
-  const uint32_t s_bar = s_init + 2u * N * 128;
+  const uint32_t s_act = s_xw + 4u * (N * 128);               // [N][32 units][4 gates] bf16: activations saved for BPTT
+  const uint32_t s_bar = s_act + (uint32_t)N * 256u;
   const uint32_t bar_h = s_bar;          // [8]
   const uint32_t bar_acc = s_bar + 64;
   const uint32_t bar_xw = s_bar + 72;
-  const uint32_t bar_out = s_bar + 88;   // epilogue -> warp 0: gate activations are in the staging planes
+  const uint32_t bar_out = s_bar + 88;   // epilogue -> warp 0: gate activations are staged, the xw planes are consumed
   const uint32_t tmem_holder = s_bar + 80;
   volatile uint32_t *tmem_holder_ptr = reinterpret_cast<volatile uint32_t *>(gbase + (tmem_holder - base));
   uint8_t *xw_gen = gbase + (s_xw - base);
-  float *init_gen = reinterpret_cast<float *>(gbase + (s_init - base));
+  uint8_t *act_gen = gbase + (s_act - base);
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int rank = cluster_ctarank();
@@ -163,8 +164,6 @@ lstm_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_h, const __grid_consta
         const float ci = a.state_in[(size_t)b * S + uo];
         const float hi = a.state_in[(size_t)b * S + H + uo];
         cst[it] = ci;
-        init_gen[(0 * N + c) * 32 + eu] = ci;
-        init_gen[(1 * N + c) * 32 + eu] = hi;
         a.cprev[(size_t)b * H + uo] = ci;
         a.hprev_bf[(size_t)b * H + uo] = __float2bfloat16_rn(hi);
       }
@@ -213,7 +212,8 @@ lstm_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_h, const __grid_consta
   const uint32_t swz = ((((uint32_t)(eu >> 2) ^ (uint32_t)cb) & 7u) << 4) + ((uint32_t)(eu & 3) << 2);
   uint8_t *pl_e = xw_gen + cb * 128 + swz;
   uint8_t *pl_o = xw_gen + cb * 128 + (swz ^ 64u);
-  const float *init_c = init_gen + cb * 32 + eu;
+  uint8_t *act_p = act_gen + cb * 256 + eu * 8;                           // (column cb, unit eu): 4 gates, 8 bytes
+  const float *init_p = a.state_in + (size_t)(b0 + cb) * S + uo;          // fed (c, h): the eoc reset source
   const int H4 = 4 * H;
   const size_t BH = (size_t)B * H;
   __nv_bfloat16 *o_p = a.out_bf + (size_t)(b0 + cb) * H + uo;             // out[t]
@@ -234,13 +234,14 @@ lstm_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_h, const __grid_consta
           tma_load_3d_multicast(s_h + (uint32_t)kb * (N * 128) + (uint32_t)half * (N / 2) * 128, &tm_h, bar_h + 8 * kb, kb * 64,
                                 b0 + half * (N / 2), t, (uint16_t)((1u << a.CS) - 1u));
         }
+        // last step's activation store has left its staging tile (the epilogue writes it again only after it has
+        // seen this step's planes, i.e. after bar_xw)
+        tma_store_wait_read();
         mbar_expect_tx(bar_xw, 4 * N * 128);
         tma_load_4d(s_xw, &tm_xw, bar_xw, u0, b0, 0, t);  // the 4 gate planes of my units in one box
-        // the epilogue overwrites the planes in place with the gate activations: one TMA store puts them
-        // back where the pre-activations came from (saved for BPTT)
+        // gate activations of this step (bf16, [unit][gate] per row) go to their own array for BPTT
         mbar_wait(bar_out, t & 1);
-        tma_store_4d(&tm_xw, s_xw, u0, b0, 0, t);
-        tma_store_wait_read();
+        tma_store_3d(&tm_act, s_act, 4 * u0, b0, t);
       }
       __syncwarp();
     } else if (warp == 1) {
@@ -344,11 +345,19 @@ lstm_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_h, const __grid_consta
           const float jg = tanh_approx(p1 + *x1p);
           const float fg = sigmoid_approx(p2 + *x2p + 1.0f);
           const float og = sigmoid_approx(p3 + *x3p);
-          *x0p = ig; *x1p = jg; *x2p = fg; *x3p = og;  // staged for the TMA store
+          {  // staged for the TMA store.  i and f are positive: their sign bits carry the step's eoc flag and
+             // "this output element was dropped", so BPTT needs no side loads
+            const __nv_bfloat162 a01 = __floats2bfloat162_rn(ig, jg), a23 = __floats2bfloat162_rn(fg, og);
+            uint32_t w0 = *reinterpret_cast<const uint32_t *>(&a01) & 0xffff7fffu;
+            uint32_t w1 = *reinterpret_cast<const uint32_t *>(&a23) & 0xffff7fffu;
+            if ((eoc_bits >> it) & 1u) w0 |= 0x8000u;
+            if (dsc[it] == 0.0f) w1 |= 0x8000u;
+            *reinterpret_cast<uint2 *>(act_p + it * 1024) = make_uint2(w0, w1);
+          }
           const float c2 = fmaf(cst[it], fg, ig * jg);
           const float h2 = tanh_approx(c2) * og;
           float cn = c2, hn = h2;
-          if ((eoc_bits >> it) & 1u) { cn = init_c[it * 128]; hn = init_c[N * 32 + it * 128]; }
+          if ((eoc_bits >> it) & 1u) { cn = __ldg(init_p + (size_t)it * 4 * S); hn = __ldg(init_p + (size_t)it * 4 * S + H); }
           cst[it] = cn;
           if (more) h_p[it * H4] = __float2bfloat16_rn(hn);  // exchange medium first
           if constexpr (DEFER) {
@@ -420,7 +429,8 @@ lstm_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_h, const __grid_consta
 // staging tiles, i.e. distinct banks).
 template <int NCH, bool DBG>
 __global__ void __launch_bounds__(TCR_THREADS, 1)
-lstm_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm_acts, TcRnnArgs a) {
+lstm_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm_acts, const __grid_constant__ CUtensorMap tm_do,
+                   const __grid_constant__ CUtensorMap tm_cp, TcRnnArgs a) {
   constexpr int N = 16 * NCH;
   constexpr int CPW = N / 4;
   extern __shared__ uint8_t smem_raw[];
@@ -431,11 +441,15 @@ lstm_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm_acts, TcRnnArgs a) {
   const int HP = nmt * 128;
   const uint32_t s_w = base;                       // 2 k-blocks x [HP rows][128 B]
   const uint32_t s_b = s_w + 2u * HP * 128u;       // 2 k-blocks x [N rows][128 B]: own d(pre) slice, bf16
-  const uint32_t s_ac = s_b + 2u * (N * 128);      // 4 planes x [N][32] fp32: saved gate activations
-  const uint32_t s_bar = s_ac + 4u * (N * 128);
-  const uint32_t bar_acts = s_bar, bar_ready = s_bar + 8, bar_acc = s_bar + 16, tmem_holder = s_bar + 24;
+  const uint32_t s_ac = s_b + 2u * (N * 128);      // [N][32 units][4 gates] bf16: gate activations saved by the forward
+  const uint32_t s_do = s_ac + (uint32_t)N * 256u; // [N][32] fp32, 128B-swizzled: d(out) of the step
+  const uint32_t s_cp = s_do + (uint32_t)N * 128u; // [N][32] fp32, 128B-swizzled: c fed to the step
+  const uint32_t s_bar = s_cp + (uint32_t)N * 128u;
+  const uint32_t bar_acts = s_bar, bar_ready = s_bar + 8, tmem_holder = s_bar + 24;
+  const uint32_t bar_acc = s_bar + 32;  // [4]: one per accumulator m-tile, so the read-out starts while later tiles multiply
   volatile uint32_t *tmem_holder_ptr = reinterpret_cast<volatile uint32_t *>(gbase + (tmem_holder - base));
   const uint8_t *ac_gen = gbase + (s_ac - base);
+  const uint8_t *do_gen = gbase + (s_do - base);
   uint8_t *b_gen = gbase + (s_b - base);
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -454,7 +468,7 @@ lstm_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm_acts, TcRnnArgs a) {
   if (tid == 0) {
     mbar_init(bar_acts, 1);
     mbar_init(bar_ready, 32 * TCR_EPI_WARPS);
-    mbar_init(bar_acc, 1);
+    for (int mt = 0; mt < 4; ++mt) mbar_init(bar_acc + 8 * mt, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 1) tc_alloc(tmem_holder, (uint32_t)a.tmem_cols);
@@ -494,38 +508,20 @@ lstm_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm_acts, TcRnnArgs a) {
   for (int it = 0; it < NCH; ++it)
     if (b0 + c0 + 4 * it < B) valid |= 1u << it;
   const bool tile_full = b0 + N <= B;
-  const size_t BH = (size_t)B * H, BG = (size_t)B * G;
-  const float *do_p = a.dout + ((size_t)(T - 1) * B + b0 + c0) * H + uo;
-  const float *cp_p = a.cprev + ((size_t)(T - 1) * B + b0 + c0) * H + uo;
-  const unsigned char *eoc_p = a.eoc + (size_t)(T - 1) * B + b0 + c0;
+  const size_t BG = (size_t)B * G;
   __nv_bfloat16 *d_p = a.dpre_bf + ((size_t)(T - 1) * B + b0 + c0) * G + uo;
-  const int H4 = 4 * H;
-  // columns 4 apart flip bit 2 of the 128B-swizzle phase
-  const uint32_t ac_sw = ((((uint32_t)(eu >> 2) ^ (uint32_t)c0) & 7u) << 4);
-  const uint8_t *ac0 = ac_gen + c0 * 128 + ((eu & 3) << 2);
+  const uint8_t *ac0 = ac_gen + c0 * 256 + eu * 8;  // (column c0, unit eu): 4 gates, 8 bytes
+  // d(out) / c tiles: columns 4 apart flip bit 2 of the 128B-swizzle phase
+  const uint32_t do_sw = ((((uint32_t)(eu >> 2) ^ (uint32_t)c0) & 7u) << 4);
+  const uint8_t *do0 = do_gen + c0 * 128 + ((eu & 3) << 2);
   const uint32_t b_sw = (((((uint32_t)(eu & 15) >> 1) ^ (uint32_t)c0) & 7u) << 4);
   uint8_t *bg0 = b_gen + (eu >> 4) * (N * 128) + c0 * 128 + ((eu & 1) << 3);
-  // per-item global inputs of a step: d(out), c fed to the step, eoc flag (dropout folded into d(out))
-  float d_o[NCH], cp[NCH];
-  uint32_t eoc_bits = 0;
-  auto load_inputs = [&](int tt) {  // must be called for tt = T-1, T-2, ... in turn (running pointers)
-    eoc_bits = 0;
-#pragma unroll
-    for (int it = 0; it < NCH; ++it) {
-      d_o[it] = 0.f; cp[it] = 0.f;
-      if ((valid >> it) & 1u) {
-        d_o[it] = do_p[it * H4];
-        cp[it] = cp_p[it * H4];
-        if (__ldg(eoc_p + 4 * it)) eoc_bits |= 1u << it;
-        if (a.dropout) d_o[it] *= drop_scale(a.mask, b0 + c0 + 4 * it, T, tt, H, uo, a.row0, a.seed, a.keep);
-      }
-    }
-    do_p -= BH; cp_p -= BH; eoc_p -= B;
-  };
-  if (warp >= 2) load_inputs(T - 1);
+  const float inv_keep = 1.0f / a.keep;
   if (warp == 0 && elect_one()) {
-    mbar_expect_tx(bar_acts, 4 * N * 128);
-    tma_load_4d(s_ac, &tm_acts, bar_acts, u0, b0, 0, T - 1);
+    mbar_expect_tx(bar_acts, N * 512);
+    tma_load_3d(s_ac, &tm_acts, bar_acts, 4 * u0, b0, T - 1);
+    tma_load_3d(s_do, &tm_do, bar_acts, u0, b0, T - 1);
+    tma_load_3d(s_cp, &tm_cp, bar_acts, u0, b0, T - 1);
   }
   __syncwarp();
   for (int t = T - 1, step = 0; t >= 0; --t, ++step) {
@@ -537,8 +533,10 @@ lstm_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm_acts, TcRnnArgs a) {
       // consumed them (bar_ready), request step t-1's so the load overlaps the product and the exchange
       mbar_wait(bar_ready, step & 1);
       if (t > 0 && elect_one()) {
-        mbar_expect_tx(bar_acts, 4 * N * 128);
-        tma_load_4d(s_ac, &tm_acts, bar_acts, u0, b0, 0, t - 1);
+        mbar_expect_tx(bar_acts, N * 512);
+        tma_load_3d(s_ac, &tm_acts, bar_acts, 4 * u0, b0, t - 1);
+        tma_load_3d(s_do, &tm_do, bar_acts, u0, b0, t - 1);
+        tma_load_3d(s_cp, &tm_cp, bar_acts, u0, b0, t - 1);
       }
       __syncwarp();
     } else if (warp >= 2) {
@@ -549,18 +547,26 @@ lstm_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm_acts, TcRnnArgs a) {
 #pragma unroll
       for (int it = 0; it < NCH; ++it) {
         if (FULL || ((valid >> it) & 1u)) {
-          const uint8_t *ap = ac0 + it * 512 + (ac_sw ^ (uint32_t)((it & 1) << 6));
-          const float ig = *reinterpret_cast<const float *>(ap + 0 * (N * 128));
-          const float jg = *reinterpret_cast<const float *>(ap + 1 * (N * 128));
-          const float fg = *reinterpret_cast<const float *>(ap + 2 * (N * 128));
-          const float og = *reinterpret_cast<const float *>(ap + 3 * (N * 128));
-          const bool eoc = (eoc_bits >> it) & 1u;
-          const float dh2 = d_o[it] + (eoc ? 0.f : dhc[it]);
-          const float tc = tanh_approx(fmaf(cp[it], fg, ig * jg));
+          const uint2 av = *reinterpret_cast<const uint2 *>(ac0 + it * 1024);
+          const uint32_t w0 = av.x & 0xffff7fffu, w1 = av.y & 0xffff7fffu;
+          const float2 a01 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162 *>(&w0));
+          const float2 a23 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162 *>(&w1));
+          const float ig = a01.x, jg = a01.y, fg = a23.x, og = a23.y;
+          const bool eoc = (av.x & 0x8000u) != 0;  // flags the forward left in the sign bits of i and f
+          float dscale = 1.0f;
+          if (a.dropout) {
+            dscale = (av.y & 0x8000u) ? 0.0f : inv_keep;
+            if (a.mask != nullptr) dscale = drop_scale(a.mask, b0 + c0 + 4 * it, T, t, H, uo, a.row0, a.seed, a.keep);
+          }
+          const uint8_t *dp = do0 + it * 512 + (do_sw ^ (uint32_t)((it & 1) << 6));
+          const float d_out = *reinterpret_cast<const float *>(dp) * dscale;
+          const float cpv = *reinterpret_cast<const float *>(dp + N * 128);
+          const float dh2 = d_out + (eoc ? 0.f : dhc[it]);
+          const float tc = tanh_approx(fmaf(cpv, fg, ig * jg));
           const float dc2 = (eoc ? 0.f : dcc[it]) + dh2 * og * (1.0f - tc * tc);
           dcc[it] = dc2 * fg;
           const float d0 = dc2 * jg * ig * (1.0f - ig), d1 = dc2 * ig * (1.0f - jg * jg);
-          const float d2 = dc2 * cp[it] * fg * (1.0f - fg), d3 = dh2 * tc * og * (1.0f - og);
+          const float d2 = dc2 * cpv * fg * (1.0f - fg), d3 = dh2 * tc * og * (1.0f - og);
           bsum[0] += d0; bsum[1] += d1; bsum[2] += d2; bsum[3] += d3;
           __nv_bfloat16 *db = d_p + (size_t)it * 4 * G;
           const __nv_bfloat16 h0 = __float2bfloat16_rn(d0), h1 = __float2bfloat16_rn(d1);
@@ -594,15 +600,15 @@ lstm_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm_acts, TcRnnArgs a) {
                 tc_mma_bf16(tmem_acc + (uint32_t)(mt * N), da + (uint64_t)(2 * k), dBk[kb] + (uint64_t)(2 * k), idesc,
                             (kb > 0 || k > 0) ? 1u : 0u);
             }
+            tc_commit(bar_acc + 8 * mt);
           }
-          tc_commit(bar_acc);
         }
         __syncwarp();
       } else if (warp >= 2) {
-        mbar_wait(bar_acc, step & 1);
-        TCR_LAP(tk[2]);
-        tc_fence_after();
         for (int mt = 0; mt < nmt; ++mt) {
+          mbar_wait(bar_acc + 8 * mt, step & 1);
+          if (mt == 0) TCR_LAP(tk[2]);
+          tc_fence_after();
           const int m = mt * 128 + e;  // hidden unit of this lane's accumulator row
           uint32_t r[CPW];
           tc_ldn<CPW>(tmem_acc + ((uint32_t)(32 * q) << 16) + (uint32_t)(mt * N + cg * CPW), r);
@@ -635,10 +641,6 @@ lstm_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm_acts, TcRnnArgs a) {
     tc_fence_after();
     TCR_LAP(tk[4]);
     if (t > 0 && warp >= 2) {
-      // next step's per-item inputs: issued here so that they are in flight during the partial reads but not
-      // live across the accumulator read-out above
-      load_inputs(t - 1);
-      TCR_LAP(tk[6]);
       // d(h_{t-1}) for my units = sum over ranks (fixed order) of their partials
 #pragma unroll
       for (int it = 0; it < NCH; ++it) dhc[it] = 0.f;
@@ -705,8 +707,8 @@ lstm_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm_acts, TcRnnArgs a) {
     }
   }
   if (dbg)
-    printf("[tc bwd N=%d CS=%d] cycles/step: inputs+acts wait %lld, elementwise+stores %lld, MMA wait %lld, tmem ld + partial stores %lld, cluster barrier %lld, next inputs issue %lld, partial reads %lld\n",
-           N, CS, tk[0] / T, tk[1] / T, tk[2] / T, tk[3] / T, tk[4] / T, tk[6] / T, tk[5] / T);
+    printf("[tc bwd N=%d CS=%d] cycles/step: inputs+acts wait %lld, elementwise+stores %lld, MMA wait %lld, tmem ld + partial stores %lld, cluster barrier %lld, partial reads %lld\n",
+           N, CS, tk[0] / T, tk[1] / T, tk[2] / T, tk[3] / T, tk[4] / T, tk[5] / T);
   __syncthreads();
   if (warp == 1) tc_dealloc(tmem_acc, (uint32_t)a.tmem_cols);
 }
@@ -751,8 +753,8 @@ __global__ void pack_tc_image_kernel(int bwd, const float *__restrict__ mat, int
 }
 
 template <int NCH>
-int launch_fwd(const CUtensorMap &tm_h, const CUtensorMap &tm_xw, const TcRnnArgs &a, int nclusters, size_t smem,
-               cudaStream_t st) {
+int launch_fwd(const CUtensorMap &tm_h, const CUtensorMap &tm_xw, const CUtensorMap &tm_act, const TcRnnArgs &a,
+               int nclusters, size_t smem, cudaStream_t st) {
   auto kern = a.debug ? lstm_fwd_tc_kernel<NCH, true> : lstm_fwd_tc_kernel<NCH, false>;
   SK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   if (a.CS > 8) SK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
@@ -765,11 +767,12 @@ int launch_fwd(const CUtensorMap &tm_h, const CUtensorMap &tm_xw, const TcRnnArg
   at[0].id = cudaLaunchAttributeClusterDimension;
   at[0].val.clusterDim.x = a.CS; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
   cfg.attrs = at; cfg.numAttrs = 1;
-  SK_CUDA(cudaLaunchKernelEx(&cfg, kern, tm_h, tm_xw, a));
+  SK_CUDA(cudaLaunchKernelEx(&cfg, kern, tm_h, tm_xw, tm_act, a));
   return 0;
 }
 template <int NCH>
-int launch_bwd(const CUtensorMap &tm_acts, const TcRnnArgs &a, int nclusters, size_t smem, cudaStream_t st) {
+int launch_bwd(const CUtensorMap &tm_acts, const CUtensorMap &tm_do, const CUtensorMap &tm_cp, const TcRnnArgs &a,
+               int nclusters, size_t smem, cudaStream_t st) {
   auto kern = a.debug ? lstm_bwd_tc_kernel<NCH, true> : lstm_bwd_tc_kernel<NCH, false>;
   SK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   if (a.CS > 8) SK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
@@ -782,7 +785,7 @@ int launch_bwd(const CUtensorMap &tm_acts, const TcRnnArgs &a, int nclusters, si
   at[0].id = cudaLaunchAttributeClusterDimension;
   at[0].val.clusterDim.x = a.CS; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
   cfg.attrs = at; cfg.numAttrs = 1;
-  SK_CUDA(cudaLaunchKernelEx(&cfg, kern, tm_acts, a));
+  SK_CUDA(cudaLaunchKernelEx(&cfg, kern, tm_acts, tm_do, tm_cp, a));
   return 0;
 }
 
@@ -859,16 +862,25 @@ int sk_rnn_tc_layer(skrnn_handle *h, cudaStream_t st, bool bwd, int l, int B, in
     if (dbg_env < 0) { const char *e = getenv("SKRNN_TC_DEBUG"); dbg_env = (e && e[0] == '1') ? 1 : 0; }
     a.debug = dbg_env;
   }
-  CUtensorMap tm_xw;
+  SK_CHECK(h->ws.acts_bf[l] != nullptr, "tcgen05 recurrent kernels: activation workspace missing");
+  CUtensorMap tm_act;
   {
-    // xw[t][b][g*H + u] viewed as (u, b, g, t): one box fetches the 4 gate planes of 32 units for N rows
-    uint64_t dims[4] = {(uint64_t)H, (uint64_t)B, 4, (uint64_t)T};
-    uint64_t str[3] = {(uint64_t)h->G * 4, (uint64_t)H * 4, (uint64_t)B * h->G * 4};
-    uint32_t box[4] = {32, (uint32_t)N, 4, 1};
-    SK_TRY(sk_make_tmap(&tm_xw, 4, h->ws.xw[l], 4, dims, str, box));
+    // saved gate activations acts_bf[t][b][4*u + g] (bf16, not swizzled): one box = 32 units x N rows
+    uint64_t dims[3] = {(uint64_t)h->G, (uint64_t)B, (uint64_t)T};
+    uint64_t str[2] = {(uint64_t)h->G * 2, (uint64_t)B * h->G * 2};
+    uint32_t box[3] = {128, (uint32_t)N, 1};
+    SK_TRY(sk_make_tmap(&tm_act, 2, h->ws.acts_bf[l], 3, dims, str, box, false));
   }
   int rc = 0;
   if (!bwd) {
+    CUtensorMap tm_xw;
+    {
+      // xw[t][b][g*H + u] viewed as (u, b, g, t): one box fetches the 4 gate planes of 32 units for N rows
+      uint64_t dims[4] = {(uint64_t)H, (uint64_t)B, 4, (uint64_t)T};
+      uint64_t str[3] = {(uint64_t)h->G * 4, (uint64_t)H * 4, (uint64_t)B * h->G * 4};
+      uint32_t box[4] = {32, (uint32_t)N, 4, 1};
+      SK_TRY(sk_make_tmap(&tm_xw, 4, h->ws.xw[l], 4, dims, str, box));
+    }
     CUtensorMap tm_h;
     uint64_t dims[3] = {(uint64_t)H, (uint64_t)B, (uint64_t)T};
     uint64_t str[2] = {(uint64_t)H * 2, (uint64_t)B * H * 2};
@@ -878,10 +890,10 @@ int sk_rnn_tc_layer(skrnn_handle *h, cudaStream_t st, bool bwd, int l, int B, in
     uint32_t box[3] = {64, (uint32_t)(a.mcast ? N / 2 : N), 1};
     SK_TRY(sk_make_tmap(&tm_h, 2, h->ws.hprev_bf[l], 3, dims, str, box));
     SkLaunch scope(h, st, SK_CAT_RNN_FWD);
-    if (N == 16) rc = launch_fwd<1>(tm_h, tm_xw, a, nclusters, smem, st);
-    else if (N == 32) rc = launch_fwd<2>(tm_h, tm_xw, a, nclusters, smem, st);
-    else if (N == 64) rc = launch_fwd<4>(tm_h, tm_xw, a, nclusters, smem, st);
-    else rc = launch_fwd<8>(tm_h, tm_xw, a, nclusters, smem, st);
+    if (N == 16) rc = launch_fwd<1>(tm_h, tm_xw, tm_act, a, nclusters, smem, st);
+    else if (N == 32) rc = launch_fwd<2>(tm_h, tm_xw, tm_act, a, nclusters, smem, st);
+    else if (N == 64) rc = launch_fwd<4>(tm_h, tm_xw, tm_act, a, nclusters, smem, st);
+    else rc = launch_fwd<8>(tm_h, tm_xw, tm_act, a, nclusters, smem, st);
   } else {
     const int64_t need = (int64_t)nclusters * 2 * CS * H * N;
     if (need > h->ws.partial_floats) {
@@ -893,11 +905,21 @@ int sk_rnn_tc_layer(skrnn_handle *h, cudaStream_t st, bool bwd, int l, int B, in
       h->ws.partial_floats = need;
     }
     a.partial = h->ws.partial;
+    // d(out) and the c fed to each step, [T,B,H] fp32: boxes of 32 units x N rows, 128B-swizzled
+    CUtensorMap tm_do, tm_cp;
+    {
+      uint64_t dims[3] = {(uint64_t)H, (uint64_t)B, (uint64_t)T};
+      uint64_t str[2] = {(uint64_t)H * 4, (uint64_t)B * H * 4};
+      uint32_t box[3] = {32, (uint32_t)N, 1};
+      SK_TRY(sk_make_tmap(&tm_do, 4, h->ws.dout, 3, dims, str, box));
+      SK_TRY(sk_make_tmap(&tm_cp, 4, h->ws.cprev[l], 3, dims, str, box));
+    }
     SkLaunch scope(h, st, SK_CAT_RNN_BWD);
-    if (N == 16) rc = launch_bwd<1>(tm_xw, a, nclusters, smem, st);
-    else if (N == 32) rc = launch_bwd<2>(tm_xw, a, nclusters, smem, st);
-    else if (N == 64) rc = launch_bwd<4>(tm_xw, a, nclusters, smem, st);
-    else rc = launch_bwd<8>(tm_xw, a, nclusters, smem, st);
+    if (N == 16) rc = launch_bwd<1>(tm_act, tm_do, tm_cp, a, nclusters, smem, st);
+    else if (N == 32) rc = launch_bwd<2>(tm_act, tm_do, tm_cp, a, nclusters, smem, st);
+    else if (N == 64) rc = launch_bwd<4>(tm_act, tm_do, tm_cp, a, nclusters, smem, st);
+    else rc = launch_bwd<8>(tm_act, tm_do, tm_cp, a, nclusters, smem, st);
+    if (rc != 0) return 1;  // the forward's activations live in this family's format: no fallback possible
   }
   if (rc != 0) {
     // e.g. a 16-CTA cluster that this GPU cannot co-schedule: fall back to the CUDA-core recurrent kernels
