@@ -11,6 +11,8 @@
 // canonical shared-memory descriptor, so X^T * dY (both operands MN-major, K = B*T rows) needs no
 // transposed copy.  Split-K over blockIdx.z with an atomic fp32 epilogue serves the tall-skinny
 // weight-gradient products.
+#include <stdlib.h>
+
 #include "common.cuh"
 #include "tc_ptx.cuh"
 
@@ -151,6 +153,156 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   }
 }
 
+// ------------------------------------------------------------------------------------------------
+// Persistent variant for plain (non-accumulating) products with a 16-byte-aligned C: one CTA per SM walks
+// the output tiles, the accumulator is double-buffered in TMEM so the epilogue of tile i overlaps the
+// main loop of tile i+1, and C leaves through shared memory as TMA stores (which also clip the M/N edges).
+// This is the shape of the hoisted input projections (M = T*B rows, K <= 512): they are bound by the
+// write of C, not by the tensor pipe.
+// ------------------------------------------------------------------------------------------------
+constexpr int P_STAGES = 4;
+constexpr int P_STAGING = BM * BN * 4;  // 4 sub-tiles [128 rows][32 cols] fp32, 128B-swizzled
+constexpr int P_SMEM = P_STAGES * STAGE_BYTES + P_STAGING + 512 /*bias*/ + 1024 /*align*/ + 256 /*barriers*/;
+
+template <bool A_KMAJOR, bool B_KMAJOR>
+__global__ void __launch_bounds__(TC_THREADS, 1)
+gemm_tc_persist_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                       const __grid_constant__ CUtensorMap tmC, TcArgs a) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  uint8_t *gen_base = smem_raw + (base - smem_u32(smem_raw));
+  const uint32_t s_stage = base + P_STAGES * STAGE_BYTES;
+  const uint32_t s_bias = s_stage + P_STAGING;
+  const uint32_t bars = s_bias + 512;
+  const uint32_t bar_full = bars, bar_empty = bars + 8 * P_STAGES;
+  const uint32_t bar_tfull = bars + 16 * P_STAGES, bar_tempty = bar_tfull + 16, tmem_holder = bar_tempty + 16;
+  volatile uint32_t *tmem_holder_ptr = reinterpret_cast<volatile uint32_t *>(gen_base + (tmem_holder - base));
+  float *bias_gen = reinterpret_cast<float *>(gen_base + (s_bias - base));
+  uint8_t *stage_gen = gen_base + (s_stage - base);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int ntn = (a.N + BN - 1) / BN, ntm = (a.M + BM - 1) / BM;
+  const int ntiles = ntn * ntm;
+  const int nkb = (a.K + BK - 1) / BK;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < P_STAGES; ++s) { mbar_init(bar_full + 8 * s, 1); mbar_init(bar_empty + 8 * s, 1); }
+    for (int b = 0; b < 2; ++b) { mbar_init(bar_tfull + 8 * b, 1); mbar_init(bar_tempty + 8 * b, 4); }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmA)) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmB)) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmC)) : "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_holder), "r"(2 * BN) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_acc = *tmem_holder_ptr;
+
+  if (warp == 0) {
+    if (elect_one()) {
+      int it = 0;
+      for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+        const int m0 = (tile / ntn) * BM, n0 = (tile % ntn) * BN;
+        for (int kb = 0; kb < nkb; ++kb, ++it) {
+          const int s = it % P_STAGES, ph = (it / P_STAGES) & 1;
+          mbar_wait(bar_empty + 8 * s, ph ^ 1);
+          const uint32_t sa = base + s * STAGE_BYTES, sb = sa + A_BYTES;
+          mbar_expect_tx(bar_full + 8 * s, STAGE_BYTES);
+          const int k0 = kb * BK;
+          if (A_KMAJOR) {
+            tma_load_2d(sa, &tmA, bar_full + 8 * s, k0, m0);
+          } else {
+            tma_load_2d(sa, &tmA, bar_full + 8 * s, m0, k0);
+            tma_load_2d(sa + A_BYTES / 2, &tmA, bar_full + 8 * s, m0 + 64, k0);
+          }
+          if (B_KMAJOR) {
+            tma_load_2d(sb, &tmB, bar_full + 8 * s, k0, n0);
+          } else {
+            tma_load_2d(sb, &tmB, bar_full + 8 * s, n0, k0);
+            tma_load_2d(sb + B_BYTES / 2, &tmB, bar_full + 8 * s, n0 + 64, k0);
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (elect_one()) {
+      const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((A_KMAJOR ? 0u : 1u) << 15) |
+                             ((B_KMAJOR ? 0u : 1u) << 16) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+      int it = 0, lt = 0;
+      for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++lt) {
+        const int buf = lt & 1;
+        mbar_wait(bar_tempty + 8 * buf, ((lt >> 1) & 1) ^ 1);  // the epilogue has drained this accumulator
+        tc_fence_after();
+        const uint32_t acc = tmem_acc + (uint32_t)(buf * BN);
+        for (int kb = 0; kb < nkb; ++kb, ++it) {
+          const int s = it % P_STAGES, ph = (it / P_STAGES) & 1;
+          mbar_wait(bar_full + 8 * s, ph);
+          tc_fence_after();
+          const uint32_t sa = base + s * STAGE_BYTES, sb = sa + A_BYTES;
+          const uint64_t da = make_desc(sa, a.lbo_a, a.sbo_a), db = make_desc(sb, a.lbo_b, a.sbo_b);
+#pragma unroll
+          for (int k = 0; k < BK / 16; ++k)
+            tc_mma_bf16(acc, da + (uint64_t)((a.adv_a * k) >> 4), db + (uint64_t)((a.adv_b * k) >> 4), idesc,
+                        (kb > 0 || k > 0) ? 1u : 0u);
+          tc_commit(bar_empty + 8 * s);
+        }
+        tc_commit(bar_tfull + 8 * buf);
+      }
+    }
+  } else {
+    const int q = warp & 3;              // TMEM lane quarter of this warp
+    const int et = threadIdx.x - 64;     // 0..127
+    const int r = 32 * q + lane;         // accumulator row inside the tile
+    int lt = 0;
+    for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++lt) {
+      const int m0 = (tile / ntn) * BM, n0 = (tile % ntn) * BN;
+      const int buf = lt & 1;
+      // staging tile free again (last tile's stores have read it), bias slice of this tile staged
+      if (warp == 2 && lane == 0) tma_store_wait_read();
+      named_bar_sync(1, 128);
+      bias_gen[et] = (a.bias != nullptr && n0 + et < a.N) ? __ldg(a.bias + n0 + et) : 0.f;
+      named_bar_sync(1, 128);
+      mbar_wait(bar_tfull + 8 * buf, (lt >> 1) & 1);
+      tc_fence_after();
+#pragma unroll 1
+      for (int c = 0; c < BN / 32; ++c) {
+        uint32_t v[32];
+        tc_ld32(tmem_acc + ((uint32_t)(32 * q) << 16) + (uint32_t)(buf * BN + c * 32), v);
+        uint8_t *row = stage_gen + c * 16384 + r * 128;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const float4 bv = *reinterpret_cast<const float4 *>(bias_gen + c * 32 + 4 * i);
+          float4 o;
+          o.x = __uint_as_float(v[4 * i + 0]) + bv.x; o.y = __uint_as_float(v[4 * i + 1]) + bv.y;
+          o.z = __uint_as_float(v[4 * i + 2]) + bv.z; o.w = __uint_as_float(v[4 * i + 3]) + bv.w;
+          *reinterpret_cast<float4 *>(row + ((i ^ (r & 7)) << 4)) = o;
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bar_tempty + 8 * buf);  // accumulator buffer may be overwritten
+      fence_proxy_async_smem();
+      named_bar_sync(1, 128);
+      if (warp == 2 && lane == 0) {
+#pragma unroll
+        for (int c = 0; c < BN / 32; ++c)
+          if (n0 + c * 32 < a.N) tma_store_2d_nocommit(&tmC, s_stage + c * 16384, n0 + c * 32, m0);
+        tma_store_commit();
+      }
+    }
+    if (warp == 2 && lane == 0) tma_store_wait_all();
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_acc), "r"(2 * BN) : "memory");
+  }
+}
+
 typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
                                   const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
                                   CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
@@ -229,6 +381,32 @@ int sk_gemm_tc(skrnn_handle *h, cudaStream_t st, int M, int N, int K, const void
   if (g_tc_override[5]) a.adv_b = g_tc_override[5];
   const int gx = (N + BN - 1) / BN, gy = (M + BM - 1) / BM;
   const int nkb = (K + BK - 1) / BK;
+  static int persist_env = -1;
+  if (persist_env < 0) { const char *e = getenv("SKRNN_GEMM_PERSIST"); persist_env = (e && e[0] == '0') ? 0 : 1; }
+  if (persist_env && !accumulate && (ldc % 4) == 0 && (reinterpret_cast<uintptr_t>(C) & 15) == 0 && gx * gy >= h->num_sms) {
+    CUtensorMap tmC;
+    {
+      uint64_t dims[2] = {(uint64_t)N, (uint64_t)M};
+      uint64_t str[1] = {(uint64_t)ldc * 4};
+      uint32_t box[2] = {32, (uint32_t)BM};
+      SK_TRY(sk_make_tmap(&tmC, 4, C, 2, dims, str, box));
+    }
+    a.kb_per_split = nkb;
+    SkLaunch scope(h, st, SK_CAT_TC_GEMM);
+    const int grid = std::min(gx * gy, h->num_sms);
+#define SK_TCP_LAUNCH(AK, BKM)                                                                                      \
+  do {                                                                                                              \
+    SK_CUDA(cudaFuncSetAttribute(gemm_tc_persist_kernel<AK, BKM>, cudaFuncAttributeMaxDynamicSharedMemorySize, P_SMEM)); \
+    gemm_tc_persist_kernel<AK, BKM><<<grid, TC_THREADS, P_SMEM, st>>>(tmA, tmB, tmC, a);                            \
+  } while (0)
+    if (a_kmajor && b_kmajor) SK_TCP_LAUNCH(true, true);
+    else if (a_kmajor && !b_kmajor) SK_TCP_LAUNCH(true, false);
+    else if (!a_kmajor && b_kmajor) SK_TCP_LAUNCH(false, true);
+    else SK_TCP_LAUNCH(false, false);
+#undef SK_TCP_LAUNCH
+    SK_CUDA(cudaGetLastError());
+    return 0;
+  }
   int nsplit = 1;
   if (accumulate) {
     int tiles = gx * gy;

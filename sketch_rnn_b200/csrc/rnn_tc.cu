@@ -69,6 +69,7 @@ struct TcRnnArgs {
   float *cprev;           // [T,B,H] fp32
   __nv_bfloat16 *out_bf;  // [T,B,H]
   __nv_bfloat16 *hprev_bf;
+  __nv_bfloat16 *acts_bf; // [T,B,H,4]: gate activations + flags saved for BPTT
   const float *dout;      // [T,B,H] fp32
   __nv_bfloat16 *dpre_bf; // [T,B,G]
   __nv_bfloat16 *partial; // [nclusters][2][CS][H][N] partial d(h), bf16
@@ -422,6 +423,355 @@ lstm_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_h, const __grid_consta
 }
 
 // ------------------------------------------------------------------------------------------------
+// forward, two half tiles in flight ("ping-pong")
+// ------------------------------------------------------------------------------------------------
+// The kernel above runs its phases one after the other: h tile in, product, elementwise, publish, cluster
+// barrier.  Here the cluster's N batch rows are two independent half tiles of N2 = N/2 rows, each with its own
+// h tile, accumulator, staging planes and mbarriers.  While the 16 elementwise warps work on one half, the TMA
+// loads, the product and the publication round trip of the other half proceed in the background.  There is no
+// barrier.cluster in the loop: an extra warp waits for the CTA's elementwise pass of a half (mbarrier), makes
+// its h stores visible (fence) and arrives on the `ready` mbarrier of every rank through the cluster's shared
+// memory window; a rank's TMA producer issues its share of the next multicast h tile of that half once all
+// ranks have arrived.  Requires the multicast path with the weights in tensor memory (N >= 64, CS = 2*nkb).
+constexpr int TCR_PP_THREADS = TCR_THREADS + 32;  // + warp 18: publisher
+
+__device__ __forceinline__ void mbar_wait_cluster(uint32_t bar, uint32_t parity) {
+  uint32_t done = 0;
+  while (!done) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n"
+        "selp.u32 %0, 1, 0, p;\n"
+        "}\n" : "=r"(done) : "r"(bar), "r"(parity) : "memory");
+  }
+}
+__device__ __forceinline__ void mbar_arrive_remote(uint32_t bar, uint32_t rank) {
+  asm volatile(
+      "{\n"
+      ".reg .b32 ra;\n"
+      "mapa.shared::cluster.u32 ra, %0, %1;\n"
+      "mbarrier.arrive.release.cluster.shared::cluster.b64 _, [ra];\n"
+      "}\n" ::"r"(bar), "r"(rank) : "memory");
+}
+
+template <int NCH, bool DBG>  // NCH items per thread and half tile
+__global__ void __launch_bounds__(TCR_PP_THREADS, 1)
+lstm_fwd_pp_kernel(const __grid_constant__ CUtensorMap tm_h, const __grid_constant__ CUtensorMap tm_xw,
+                   const __grid_constant__ CUtensorMap tm_hst, TcRnnArgs a) {
+  constexpr int N2 = 16 * NCH, N = 2 * N2;
+  constexpr int CPW = N2 / 4;  // columns per elementwise warp and half tile
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  uint8_t *gbase = smem_raw + (base - smem_u32(smem_raw));
+  const int H = a.H, B = a.B, T = a.T, nkb = a.nkb, CS = a.CS;
+  const uint32_t h_bytes = (uint32_t)nkb * (N2 * 128), xw_bytes = 4u * (N2 * 128), hst_bytes = (uint32_t)N2 * 64u;
+  const uint32_t s_h = base;                       // [2] x nkb x [N2 rows][128 B]
+  const uint32_t s_xw = s_h + 2 * h_bytes;         // [2] x 4 planes x [N2][32] fp32
+  const uint32_t s_hst = s_xw + 2 * xw_bytes;      // [2] x [N2][32 units] bf16: my units of h_t on their way out (TMA store)
+  const uint32_t s_bar = s_hst + 2 * hst_bytes;
+  // mbarriers, index s = half tile
+  const uint32_t bar_h = s_bar, bar_xw = s_bar + 16, bar_acc = s_bar + 32, bar_epi = s_bar + 48, bar_ready = s_bar + 64;
+  const uint32_t tmem_holder = s_bar + 80;
+  volatile uint32_t *tmem_holder_ptr = reinterpret_cast<volatile uint32_t *>(gbase + (tmem_holder - base));
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int rank = cluster_ctarank();
+  const int b0 = cluster_id_x() * N;
+  const int u0 = rank * 32;
+  const int S = 2 * H;
+
+  if (tid == 0) {
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(bar_h + 8 * s, 1);
+      mbar_init(bar_xw + 8 * s, 1);
+      mbar_init(bar_acc + 8 * s, 1);
+      mbar_init(bar_epi + 8 * s, 32 * TCR_EPI_WARPS);
+      mbar_init(bar_ready + 8 * s, CS);
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) tc_alloc(tmem_holder, (uint32_t)a.tmem_cols);
+
+  const int q = warp & 3, cg = (warp - 2) >> 2;
+  const int e = 32 * q + lane;
+  const int eu = e >> 2, eg = e & 3;
+  const int uo = u0 + eu;
+  const int cb = cg * CPW + eg;  // item `it` of half s is column s*N2 + cb + 4*it of the cluster tile
+  float cst[2][NCH];
+  if (warp >= 2 && warp < 2 + TCR_EPI_WARPS) {
+#pragma unroll
+    for (int s = 0; s < 2; ++s) {
+#pragma unroll
+      for (int it = 0; it < NCH; ++it) {
+        const int b = b0 + s * N2 + cb + 4 * it;
+        cst[s][it] = 0.f;
+        if (b < B) {
+          const float ci = a.state_in[(size_t)b * S + uo];
+          const float hi = a.state_in[(size_t)b * S + H + uo];
+          cst[s][it] = ci;
+          a.cprev[(size_t)b * H + uo] = ci;
+          a.hprev_bf[(size_t)b * H + uo] = __float2bfloat16_rn(hi);
+        }
+      }
+    }
+  }
+  fence_proxy_async();
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_acc = *tmem_holder_ptr;
+  const uint32_t tmem_a = tmem_acc + (uint32_t)((N + 31) / 32 * 32);  // weight operand columns, after the accumulators
+  if (warp >= 2 && warp < 6) {
+    const uint32_t *src = reinterpret_cast<const uint32_t *>(a.wimg + (size_t)rank * a.wimg_bytes) + (size_t)e * (nkb * 32);
+    for (int kb = 0; kb < nkb; ++kb) {
+      uint32_t v[32];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const uint4 x = __ldg(reinterpret_cast<const uint4 *>(src + kb * 32) + j);
+        v[4 * j] = x.x; v[4 * j + 1] = x.y; v[4 * j + 2] = x.z; v[4 * j + 3] = x.w;
+      }
+      tc_st32(tmem_a + ((uint32_t)(32 * q) << 16) + (uint32_t)(kb * 32), v);
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  cluster_sync_all();  // everybody's barriers are initialised and the step-0 h rows are in global memory
+
+  __shared__ long long tk[24];
+  if (tid < 24) tk[tid] = 0;
+  __syncthreads();
+  const bool dbg0 = DBG && rank == 0 && cluster_id_x() == 0;
+  const bool dbg = dbg0 && tid == 64;
+
+  if (warp == 0) {
+    // ---------------- TMA producer ----------------
+    if (elect_one()) {
+      const bool dbg = dbg0;
+      uint32_t lapt = 0;
+      if (dbg) lapt = (uint32_t)clock();
+      const int kb_mine = rank >> 1, half = rank & 1;
+      const uint16_t all = (uint16_t)((1u << CS) - 1u);
+      auto load_h = [&](int s, int t) {
+        // every rank expects the whole half tile and fetches 1/CS of it (half a k-block) for everybody
+        mbar_expect_tx(bar_h + 8 * s, h_bytes);
+        tma_load_3d_multicast(s_h + s * h_bytes + (uint32_t)kb_mine * (N2 * 128) + (uint32_t)half * (N2 / 2) * 128, &tm_h,
+                              bar_h + 8 * s, kb_mine * 64, b0 + s * N2 + half * (N2 / 2), t, all);
+      };
+      auto load_xw = [&](int s, int t) {
+        mbar_expect_tx(bar_xw + 8 * s, xw_bytes);
+        tma_load_4d(s_xw + s * xw_bytes, &tm_xw, bar_xw + 8 * s, u0, b0 + s * N2, 0, t);
+      };
+      auto retire = [&](int s, int t) {  // the elementwise pass of (s, t) is over: refill its planes
+        mbar_wait(bar_epi + 8 * s, t & 1);
+        if (t + 1 < T) load_xw(s, t + 1);
+      };
+      load_xw(0, 0);
+      load_xw(1, 0);
+      for (int t = 0; t < T; ++t) {
+        if (t > 0) mbar_wait_cluster(bar_ready + 0, (t - 1) & 1);
+        TCR_LAP(tk[8]);
+        load_h(0, t);
+        TCR_LAP(tk[9]);
+        if (t > 0) retire(1, t - 1);
+        TCR_LAP(tk[10]);
+        if (t > 0) mbar_wait_cluster(bar_ready + 8, (t - 1) & 1);
+        TCR_LAP(tk[11]);
+        load_h(1, t);
+        TCR_LAP(tk[12]);
+        retire(0, t);
+        TCR_LAP(tk[13]);
+      }
+      if (dbg)
+        printf("[tc fwd pp] producer cycles/step: wait ready0 %lld, issue h0 %lld, retire1 %lld, wait ready1 %lld, issue h1 %lld, retire0 %lld\n",
+               tk[8] / T, tk[9] / T, tk[10] / T, tk[11] / T, tk[12] / T, tk[13] / T);
+    }
+    __syncwarp();
+  } else if (warp == 1) {
+    // ---------------- MMA issuer ----------------
+    if (elect_one()) {
+      const bool dbg = dbg0;
+      uint32_t lapt = 0;
+      if (dbg) lapt = (uint32_t)clock();
+      const uint32_t idesc = make_idesc_bf16(128, N2, false, false);
+      const uint64_t dB0 = make_desc(s_h, 0, 1024);
+      for (int t = 0; t < T; ++t) {
+#pragma unroll
+        for (int s = 0; s < 2; ++s) {
+          mbar_wait(bar_h + 8 * s, t & 1);
+          TCR_LAP(tk[16 + 2 * s]);
+          tc_fence_after();
+#pragma unroll
+          for (int kb = 0; kb < 8; ++kb) {
+            if (kb < nkb) {
+#pragma unroll
+              for (int k = 0; k < 4; ++k)
+                tc_mma_bf16_ts(tmem_acc + (uint32_t)(s * N2), tmem_a + (uint32_t)(kb * 32 + k * 8),
+                               dB0 + (uint64_t)((s * h_bytes) >> 4) + (uint64_t)(kb * (N2 * 8) + 2 * k), idesc,
+                               (kb > 0 || k > 0) ? 1u : 0u);
+            }
+          }
+          tc_commit(bar_acc + 8 * s);
+          TCR_LAP(tk[17 + 2 * s]);
+        }
+      }
+      if (dbg)
+        printf("[tc fwd pp] MMA thread cycles/step: wait h0 %lld, issue %lld, wait h1 %lld, issue %lld\n", tk[16] / T, tk[17] / T,
+               tk[18] / T, tk[19] / T);
+    }
+    __syncwarp();
+  } else if (warp == 2 + TCR_EPI_WARPS) {
+    // ---------------- publisher ----------------
+    // h_t of a half tile leaves through the async proxy (TMA store from the staging tile), so no generic-to-async
+    // proxy fence sits on the critical path; once the store is complete lane r arrives at rank r (the CS remote
+    // round trips overlap)
+    {
+      const bool dbg = dbg0 && lane == 0;
+      uint32_t lapt = 0;
+      if (dbg) lapt = (uint32_t)clock();
+      for (int t = 0; t + 1 < T; ++t) {
+#pragma unroll
+        for (int s = 0; s < 2; ++s) {
+          mbar_wait(bar_epi + 8 * s, t & 1);  // the staging tile of (s, t) is complete (writers fenced it for the async proxy)
+          TCR_LAP(tk[20]);
+          if (elect_one()) {
+            tma_store_3d(&tm_hst, s_hst + s * hst_bytes, u0, b0 + s * N2, t + 1);
+            tma_store_wait_all();             // h_t[my units] is in global memory before anybody is told
+          }
+          __syncwarp();
+          TCR_LAP(tk[21]);
+          if (lane < CS) mbar_arrive_remote(bar_ready + 8 * s, (uint32_t)lane);
+          __syncwarp();
+          TCR_LAP(tk[22]);
+        }
+      }
+      if (dbg)
+        printf("[tc fwd pp] publisher cycles/half step: wait elementwise %lld, h store %lld, remote arrives %lld\n", tk[20] / (2 * T),
+               tk[21] / (2 * T), tk[22] / (2 * T));
+    }
+    __syncwarp();
+  } else {
+    // ---------------- elementwise warps ----------------
+    const bool g_lo = (eg & 1) != 0, g_hi = (eg & 2) != 0;
+    uint32_t valid[2] = {0, 0};
+#pragma unroll
+    for (int s = 0; s < 2; ++s)
+#pragma unroll
+      for (int it = 0; it < NCH; ++it)
+        if (b0 + s * N2 + cb + 4 * it < B) valid[s] |= 1u << it;
+    uint8_t *xw_gen = gbase + (s_xw - base);
+    uint8_t *hst_gen = gbase + (s_hst - base);
+    const uint32_t swz = ((((uint32_t)(eu >> 2) ^ (uint32_t)cb) & 7u) << 4) + ((uint32_t)(eu & 3) << 2);
+    uint8_t *pl_e = xw_gen + cb * 128 + swz;
+    uint8_t *pl_o = xw_gen + cb * 128 + (swz ^ 64u);
+    uint8_t *hst_p = hst_gen + cb * 64 + eu * 2;
+    const float *init_p = a.state_in + (size_t)(b0 + cb) * S + uo;
+    const int H4 = 4 * H;
+    const size_t BH = (size_t)B * H, half_off = (size_t)N2 * H;
+    __nv_bfloat16 *o_p = a.out_bf + (size_t)(b0 + cb) * H + uo;        // out[t], half 0
+    uint2 *act_g = reinterpret_cast<uint2 *>(a.acts_bf) + (size_t)(b0 + cb) * H + uo;  // activation record of step t
+    float *c_p = a.cprev + ((size_t)B + b0 + cb) * H + uo;             // cprev[t+1]
+    const unsigned char *eoc_p = a.eoc + b0 + cb;                       // eoc[t]
+    uint32_t eoc_next = 0;  // flags of the half step about to be processed
+#pragma unroll
+    for (int it = 0; it < NCH; ++it)
+      if (((valid[0] >> it) & 1u) && __ldg(eoc_p + 4 * it)) eoc_next |= 1u << it;
+    uint32_t lapt = 0;
+    if (dbg) lapt = (uint32_t)clock();
+    for (int t = 0; t < T; ++t) {
+      const bool more = t + 1 < T;
+#pragma unroll
+      for (int s = 0; s < 2; ++s) {
+        const uint32_t eoc_bits = eoc_next;
+        // eoc flags of the following half step: issued now, looked at after this pass
+        unsigned char en[NCH];
+        {
+          const int s2 = s ^ 1;
+          const unsigned char *ep = eoc_p + s2 * N2 + (s == 1 ? B : 0);
+          const bool in_range = s == 0 || more;
+#pragma unroll
+          for (int it = 0; it < NCH; ++it) en[it] = (in_range && ((valid[s2] >> it) & 1u)) ? __ldg(ep + 4 * it) : (unsigned char)0;
+        }
+        float dsc[NCH];
+#pragma unroll
+        for (int it = 0; it < NCH; ++it) {
+          dsc[it] = 1.0f;
+          if (a.dropout && ((valid[s] >> it) & 1u))
+            dsc[it] = drop_scale(a.mask, b0 + s * N2 + cb + 4 * it, T, t, H, uo, a.row0, a.seed, a.keep);
+        }
+        TCR_LAP(tk[0]);
+        mbar_wait(bar_acc + 8 * s, t & 1);
+        TCR_LAP(tk[1]);
+        tc_fence_after();
+        uint32_t r[CPW];
+        tc_ldn<CPW>(tmem_acc + ((uint32_t)(32 * q) << 16) + (uint32_t)(s * N2 + cg * CPW), r);
+        mbar_wait(bar_xw + 8 * s, t & 1);
+        TCR_LAP(tk[2]);
+#pragma unroll
+        for (int it = 0; it < NCH; ++it) {
+          float v0, v1, v2, v3, p0, p1, p2, p3;
+          perm4(g_lo, g_hi, __uint_as_float(r[4 * it + 0]), __uint_as_float(r[4 * it + 1]), __uint_as_float(r[4 * it + 2]),
+                __uint_as_float(r[4 * it + 3]), v0, v1, v2, v3);
+          v1 = __shfl_xor_sync(0xffffffffu, v1, 1);
+          v2 = __shfl_xor_sync(0xffffffffu, v2, 2);
+          v3 = __shfl_xor_sync(0xffffffffu, v3, 3);
+          perm4(g_lo, g_hi, v0, v1, v2, v3, p0, p1, p2, p3);
+          if ((valid[s] >> it) & 1u) {
+            uint8_t *pp = ((it & 1) ? pl_o : pl_e) + s * xw_bytes + it * 512;
+            const float ig = sigmoid_approx(p0 + *reinterpret_cast<const float *>(pp));
+            const float jg = tanh_approx(p1 + *reinterpret_cast<const float *>(pp + 1 * (N2 * 128)));
+            const float fg = sigmoid_approx(p2 + *reinterpret_cast<const float *>(pp + 2 * (N2 * 128)) + 1.0f);
+            const float og = sigmoid_approx(p3 + *reinterpret_cast<const float *>(pp + 3 * (N2 * 128)));
+            {
+              const __nv_bfloat162 a01 = __floats2bfloat162_rn(ig, jg), a23 = __floats2bfloat162_rn(fg, og);
+              uint32_t w0 = *reinterpret_cast<const uint32_t *>(&a01) & 0xffff7fffu;
+              uint32_t w1 = *reinterpret_cast<const uint32_t *>(&a23) & 0xffff7fffu;
+              if ((eoc_bits >> it) & 1u) w0 |= 0x8000u;
+              if (dsc[it] == 0.0f) w1 |= 0x8000u;
+              act_g[s * half_off + (size_t)it * H4] = make_uint2(w0, w1);
+            }
+            const float c2 = fmaf(cst[s][it], fg, ig * jg);
+            const float h2 = tanh_approx(c2) * og;
+            float cn = c2, hn = h2;
+            if ((eoc_bits >> it) & 1u) {
+              const float *ip = init_p + (size_t)(s * N2 + 4 * it) * S;
+              cn = __ldg(ip); hn = __ldg(ip + H);
+            }
+            cst[s][it] = cn;
+            const size_t off = s * half_off + (size_t)it * H4;
+            *reinterpret_cast<__nv_bfloat16 *>(hst_p + s * hst_bytes + it * 256) = __float2bfloat16_rn(hn);
+            o_p[off] = __float2bfloat16_rn(h2 * dsc[it]);
+            if (more) {
+              c_p[off] = cn;
+            } else {
+              float *so = a.state_out + (size_t)(b0 + s * N2 + cb + 4 * it) * S + uo;
+              so[0] = cn; so[H] = hn;
+            }
+          }
+        }
+        fence_proxy_async_smem();  // h staging tile -> TMA store
+        tc_fence_before();         // accumulator reads -> next product of this half
+        mbar_arrive(bar_epi + 8 * s);
+        eoc_next = 0;
+#pragma unroll
+        for (int it = 0; it < NCH; ++it)
+          if (en[it]) eoc_next |= 1u << it;
+        TCR_LAP(tk[3]);
+      }
+      o_p += BH; act_g += BH; c_p += BH; eoc_p += B;
+    }
+    if (dbg)
+      printf("[tc fwd pp N=2x%d] elementwise thread cycles per half step: prefetch %lld, wait acc %lld, tmem ld + xw wait %lld, items+stores %lld\n",
+             N2, tk[0] / (2 * T), tk[1] / (2 * T), tk[2] / (2 * T), tk[3] / (2 * T));
+  }
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync_all();  // nobody leaves while a peer may still multicast into it or arrive on its barriers
+  if (warp == 1) tc_dealloc(tmem_acc, (uint32_t)a.tmem_cols);
+}
+
+// ------------------------------------------------------------------------------------------------
 // backward
 // ------------------------------------------------------------------------------------------------
 // Elementwise items: thread (unit u = e/4, sub = e%4, column group cg) owns the NCH columns
@@ -771,6 +1121,24 @@ int launch_fwd(const CUtensorMap &tm_h, const CUtensorMap &tm_xw, const CUtensor
   return 0;
 }
 template <int NCH>
+int launch_fwd_pp(const CUtensorMap &tm_h, const CUtensorMap &tm_xw, const CUtensorMap &tm_act, const TcRnnArgs &a,
+                  int nclusters, size_t smem, cudaStream_t st) {
+  auto kern = a.debug ? lstm_fwd_pp_kernel<NCH, true> : lstm_fwd_pp_kernel<NCH, false>;
+  SK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  if (a.CS > 8) SK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(nclusters * a.CS);
+  cfg.blockDim = dim3(TCR_PP_THREADS);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeClusterDimension;
+  at[0].val.clusterDim.x = a.CS; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+  cfg.attrs = at; cfg.numAttrs = 1;
+  SK_CUDA(cudaLaunchKernelEx(&cfg, kern, tm_h, tm_xw, tm_act, a));
+  return 0;
+}
+template <int NCH>
 int launch_bwd(const CUtensorMap &tm_acts, const CUtensorMap &tm_do, const CUtensorMap &tm_cp, const TcRnnArgs &a,
                int nclusters, size_t smem, cudaStream_t st) {
   auto kern = a.debug ? lstm_bwd_tc_kernel<NCH, true> : lstm_bwd_tc_kernel<NCH, false>;
@@ -852,7 +1220,7 @@ int sk_rnn_tc_layer(skrnn_handle *h, cudaStream_t st, bool bwd, int l, int B, in
   (void)x_bt5;
   a.eoc = h->ws.eoc; a.state_in = state_in; a.state_out = state_out; a.mask = mask;
   a.acts = h->ws.xw[l]; a.cprev = h->ws.cprev[l]; a.out_bf = h->ws.out_bf[l]; a.hprev_bf = h->ws.hprev_bf[l];
-  a.dout = h->ws.dout; a.dpre_bf = h->ws.dpre_bf;
+  a.dout = h->ws.dout; a.dpre_bf = h->ws.dpre_bf; a.acts_bf = h->ws.acts_bf[l];
   a.dbias = bwd ? h->grads + h->lp[l].b[0] : nullptr;
   if (bwd) h->bias_grad_done = true;
   a.wimg = reinterpret_cast<const uint8_t *>(h->ws.wpack);
@@ -887,8 +1255,31 @@ int sk_rnn_tc_layer(skrnn_handle *h, cudaStream_t st, bool bwd, int l, int B, in
     static int mc_env = -1;
     if (mc_env < 0) { const char *e = getenv("SKRNN_TC_MCAST"); mc_env = (e && e[0] == '0') ? 0 : 1; }
     a.mcast = (mc_env && N >= 64 && CS >= 2 && CS == 2 * nkb) ? 1 : 0;
-    uint32_t box[3] = {64, (uint32_t)(a.mcast ? N / 2 : N), 1};
+    static int pp_env = -1;
+    if (pp_env < 0) { const char *e = getenv("SKRNN_TC_PP"); pp_env = (e && e[0] == '0') ? 0 : 1; }
+    const bool pp = pp_env && a.mcast && a_tmem && N >= 64;  // two half tiles in flight (lstm_fwd_pp_kernel)
+    uint32_t box[3] = {64, (uint32_t)(pp ? N / 4 : (a.mcast ? N / 2 : N)), 1};
     SK_TRY(sk_make_tmap(&tm_h, 2, h->ws.hprev_bf[l], 3, dims, str, box));
+    if (pp) {
+      // the xw box of a half tile has N/2 rows
+      uint64_t xdims[4] = {(uint64_t)H, (uint64_t)B, 4, (uint64_t)T};
+      uint64_t xstr[3] = {(uint64_t)h->G * 4, (uint64_t)H * 4, (uint64_t)B * h->G * 4};
+      uint32_t xbox[4] = {32, (uint32_t)(N / 2), 4, 1};
+      SK_TRY(sk_make_tmap(&tm_xw, 4, h->ws.xw[l], 4, xdims, xstr, xbox));
+      // my 32 units of h_t for a half tile's rows leave as one plain (unswizzled) box
+      uint32_t sbox[3] = {32, (uint32_t)(N / 2), 1};
+      CUtensorMap tm_hst;
+      SK_TRY(sk_make_tmap(&tm_hst, 2, h->ws.hprev_bf[l], 3, dims, str, sbox, false));
+      SkLaunch scope(h, st, SK_CAT_RNN_FWD);
+      if (N == 64) rc = launch_fwd_pp<2>(tm_h, tm_xw, tm_hst, a, nclusters, smem, st);
+      else rc = launch_fwd_pp<4>(tm_h, tm_xw, tm_hst, a, nclusters, smem, st);
+      if (rc != 0) {
+        fprintf(stderr, "libskrnn: lstm_fwd_pp_kernel launch failed (%s)\n", skrnn_last_error());
+        cudaGetLastError();
+        return 1;
+      }
+      return 0;
+    }
     SkLaunch scope(h, st, SK_CAT_RNN_FWD);
     if (N == 16) rc = launch_fwd<1>(tm_h, tm_xw, tm_act, a, nclusters, smem, st);
     else if (N == 32) rc = launch_fwd<2>(tm_h, tm_xw, tm_act, a, nclusters, smem, st);

@@ -20,6 +20,8 @@ def _mk(rows, cols, seed):
 
 CASES = [  # M, N, K
     (128, 128, 64), (128, 128, 256), (256, 384, 192), (300, 147, 256), (1000, 1024, 264), (77, 50, 40),
+    # >= 148 output tiles with a 16-byte-aligned C: the persistent TMA-store variant (ragged M, N, K; 1 and many k-blocks)
+    (5000, 520, 200), (19000, 128, 8), (2500, 1100, 520),
 ]
 
 

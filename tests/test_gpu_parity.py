@@ -379,10 +379,11 @@ def test_bf16_path_loss_and_gradients(model, H, L, M, B, T):
 
 
 @pytest.mark.parametrize("H,L,B,T", [(32, 1, 1, 1), (64, 2, 3, 2), (128, 2, 17, 5), (256, 1, 129, 3), (256, 2, 300, 4),
-                                     (512, 1, 70, 3), (512, 2, 260, 2)])
+                                     (512, 1, 70, 3), (512, 2, 260, 2), (256, 1, 530, 3), (512, 1, 460, 3)])
 def test_bf16_tcgen05_recurrent_edge_shapes(H, L, B, T):
     """Shapes that exercise the tcgen05 recurrent kernels' corner cases: one timestep, one row, ragged last
-    cluster, several clusters, every cluster size (1..16 CTAs), all batch tiles (16..128 columns)."""
+    cluster, several clusters, every cluster size (1..16 CTAs), all batch tiles (16..128 columns; 64 and 128
+    run the two-half-tile forward kernel)."""
     cfg, params, x, y, s0, mask = _case("lstm", H, L, 4, B, T, seed=3)
     x[:, :, 2:5] = [0, 0, 1]
     x[::3, T // 2, 2:5] = [0, 1, 0]  # eoc on a third of the rows in the middle of the sequence
