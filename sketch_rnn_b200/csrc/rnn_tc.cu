@@ -1064,6 +1064,310 @@ lstm_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm_acts, const __grid_con
 }
 
 // ------------------------------------------------------------------------------------------------
+// backward, two half tiles in flight
+// ------------------------------------------------------------------------------------------------
+// Same idea as lstm_fwd_pp_kernel.  Per half tile s and step: E_s (elementwise: d(pre) from the saved
+// activations, d(out) and the running d(h), d(c)), the K-split product on the tensor core, R_s (accumulator
+// read-out, bf16 partials to L2), publication, P_s (sum of the 16 ranks' partials = d(h) for the next step).
+// The 16 elementwise warps run E_0 E_1 R_0 R_1 P_0 P_1 per step: the product of a half runs while they work on
+// the other half, and the publication round trip of half 0 (fence + remote mbarrier arrivals, done by a
+// publisher warp) hides behind R_1.  No barrier.cluster in the loop.
+template <int NCH, bool DBG>  // NCH items per thread and half tile
+__global__ void __launch_bounds__(TCR_PP_THREADS, 1)
+lstm_bwd_pp_kernel(const __grid_constant__ CUtensorMap tm_acts, const __grid_constant__ CUtensorMap tm_do,
+                   const __grid_constant__ CUtensorMap tm_cp, TcRnnArgs a) {
+  constexpr int N2 = 16 * NCH, N = 2 * N2;
+  constexpr int CPW = N2 / 4;
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  uint8_t *gbase = smem_raw + (base - smem_u32(smem_raw));
+  const int H = a.H, G = a.G, B = a.B, T = a.T, CS = a.CS;
+  const int nmt = (H + 127) / 128;
+  const int HP = nmt * 128;
+  const uint32_t half_bytes = (uint32_t)N2 * 768u;  // per half: d(pre) operand 256 B/row, activations 256, d(out) 128, c 128
+  const uint32_t s_w = base;                        // 2 k-blocks x [HP rows][128 B]
+  const uint32_t s_half = s_w + 2u * HP * 128u;
+  // offsets inside a half's block
+  const uint32_t o_b = 0, o_ac = (uint32_t)N2 * 256u, o_do = (uint32_t)N2 * 512u, o_cp = (uint32_t)N2 * 640u;
+  const uint32_t s_bar = s_half + 2 * half_bytes;
+  const uint32_t bar_in = s_bar, bar_epi = s_bar + 16, bar_rd = s_bar + 32, bar_ready = s_bar + 48, tmem_holder = s_bar + 64;
+  const uint32_t bar_acc = s_bar + 128;  // [2][4]
+  volatile uint32_t *tmem_holder_ptr = reinterpret_cast<volatile uint32_t *>(gbase + (tmem_holder - base));
+  uint8_t *half_gen = gbase + (s_half - base);
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int rank = cluster_ctarank();
+  const int cid = cluster_id_x();
+  const int b0 = cid * N;
+  const int u0 = rank * 32;
+
+  {
+    const uint4 *src = reinterpret_cast<const uint4 *>(a.wimg + (size_t)rank * a.wimg_bytes);
+    uint4 *dst = reinterpret_cast<uint4 *>(gbase + (s_w - base));
+    for (int i = tid; i < a.wimg_bytes / 16; i += TCR_PP_THREADS) dst[i] = __ldg(src + i);
+    // d(pre) operand tiles start as zeros (rows past the batch stay zero)
+    for (int s = 0; s < 2; ++s) {
+      uint4 *bz = reinterpret_cast<uint4 *>(half_gen + s * half_bytes + o_b);
+      for (int i = tid; i < N2 * 256 / 16; i += TCR_PP_THREADS) bz[i] = make_uint4(0, 0, 0, 0);
+    }
+  }
+  if (tid == 0) {
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(bar_in + 8 * s, 1);
+      mbar_init(bar_epi + 8 * s, 32 * TCR_EPI_WARPS);
+      mbar_init(bar_rd + 8 * s, 32 * TCR_EPI_WARPS);
+      mbar_init(bar_ready + 8 * s, CS);
+      for (int mt = 0; mt < 4; ++mt) mbar_init(bar_acc + 8 * (4 * s + mt), 1);
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) tc_alloc(tmem_holder, (uint32_t)a.tmem_cols);
+  fence_proxy_async_smem();
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_acc = *tmem_holder_ptr;
+  cluster_sync_all();
+
+  __shared__ long long tk[8];
+  if (tid < 8) tk[tid] = 0;
+  __syncthreads();
+  const bool dbg = DBG && rank == 0 && cid == 0 && tid == 64;
+
+  if (warp == 0) {
+    // ---------------- TMA producer: the three input tiles of (s, t) ----------------
+    if (elect_one()) {
+      auto load_in = [&](int s, int t) {
+        const uint32_t hb = s_half + s * half_bytes;
+        mbar_expect_tx(bar_in + 8 * s, N2 * 512);
+        tma_load_3d(hb + o_ac, &tm_acts, bar_in + 8 * s, 4 * u0, b0 + s * N2, t);
+        tma_load_3d(hb + o_do, &tm_do, bar_in + 8 * s, u0, b0 + s * N2, t);
+        tma_load_3d(hb + o_cp, &tm_cp, bar_in + 8 * s, u0, b0 + s * N2, t);
+      };
+      load_in(0, T - 1);
+      load_in(1, T - 1);
+      for (int t = T - 1, step = 0; t > 0; --t, ++step) {
+#pragma unroll
+        for (int s = 0; s < 2; ++s) {
+          mbar_wait(bar_epi + 8 * s, step & 1);  // the elementwise pass of (s, t) has consumed its tiles
+          load_in(s, t - 1);
+        }
+      }
+    }
+    __syncwarp();
+  } else if (warp == 1) {
+    // ---------------- MMA issuer ----------------
+    if (elect_one()) {
+      const uint32_t idesc = make_idesc_bf16(128, N2, false, false);
+      for (int t = T - 1, step = 0; t > 0; --t, ++step) {
+#pragma unroll
+        for (int s = 0; s < 2; ++s) {
+          mbar_wait(bar_epi + 8 * s, step & 1);
+          tc_fence_after();
+          const uint32_t sb = s_half + s * half_bytes + o_b;
+          for (int mt = 0; mt < nmt; ++mt) {
+#pragma unroll
+            for (int kb = 0; kb < 2; ++kb) {
+              const uint64_t da = make_desc(s_w + (uint32_t)kb * (HP * 128) + (uint32_t)mt * 16384u, 0, 1024);
+              const uint64_t db = make_desc(sb + (uint32_t)kb * (N2 * 128), 0, 1024);
+#pragma unroll
+              for (int k = 0; k < 4; ++k)
+                tc_mma_bf16(tmem_acc + (uint32_t)((s * nmt + mt) * N2), da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc,
+                            (kb > 0 || k > 0) ? 1u : 0u);
+            }
+            tc_commit(bar_acc + 8 * (4 * s + mt));
+          }
+        }
+      }
+    }
+    __syncwarp();
+  } else if (warp == 2 + TCR_EPI_WARPS) {
+    // ---------------- publisher ----------------
+    for (int t = T - 1, step = 0; t > 0; --t, ++step) {
+#pragma unroll
+      for (int s = 0; s < 2; ++s) {
+        mbar_wait(bar_rd + 8 * s, step & 1);  // this CTA's partial stores of (s, t) happen before this
+        __threadfence();                      // ... and before the arrivals below, at GPU scope (cumulative)
+        if (lane < CS) mbar_arrive_remote(bar_ready + 8 * s, (uint32_t)lane);
+        __syncwarp();
+      }
+    }
+  } else {
+    // ---------------- elementwise warps ----------------
+    const int q = warp & 3, cg = (warp - 2) >> 2;
+    const int e = 32 * q + lane;
+    const int eu = e >> 2, esub = e & 3;
+    const int uo = u0 + eu;
+    const int c0 = cg * CPW + esub;  // item `it` of half s is column s*N2 + c0 + 4*it of the cluster tile
+    float dhc[2][NCH], dcc[2][NCH];
+    float bsum[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+    for (int s = 0; s < 2; ++s)
+#pragma unroll
+      for (int it = 0; it < NCH; ++it) { dhc[s][it] = 0.f; dcc[s][it] = 0.f; }
+    uint32_t valid[2] = {0, 0};
+#pragma unroll
+    for (int s = 0; s < 2; ++s)
+#pragma unroll
+      for (int it = 0; it < NCH; ++it)
+        if (b0 + s * N2 + c0 + 4 * it < B) valid[s] |= 1u << it;
+    // partial exchange, per half and parity: [dst rank][src rank][column group][chunk j][unit 32][CK columns]
+    constexpr int CK = CPW >= 8 ? 8 : CPW;
+    constexpr int NJ = CPW / CK;
+    const size_t part_blk = (size_t)NJ * 32 * CK;
+    const size_t part_par = (size_t)CS * CS * 4 * part_blk;  // one (half, parity) buffer
+    __nv_bfloat16 *part_base = a.partial + (size_t)cid * 4 * part_par;
+    const size_t BG = (size_t)B * G;
+    __nv_bfloat16 *d_p = a.dpre_bf + ((size_t)(T - 1) * B + b0 + c0) * G + uo;
+    const size_t d_half = (size_t)N2 * G;
+    const uint8_t *ac0 = half_gen + o_ac + c0 * 256 + eu * 8;
+    const uint32_t do_sw = ((((uint32_t)(eu >> 2) ^ (uint32_t)c0) & 7u) << 4);
+    const uint8_t *do0 = half_gen + o_do + c0 * 128 + ((eu & 3) << 2);
+    const uint32_t b_sw = (((((uint32_t)(eu & 15) >> 1) ^ (uint32_t)c0) & 7u) << 4);
+    uint8_t *bg0 = half_gen + o_b + (eu >> 4) * (N2 * 128) + c0 * 128 + ((eu & 1) << 3);
+    const float inv_keep = 1.0f / a.keep;
+    uint32_t lapt = 0;
+    if (dbg) lapt = (uint32_t)clock();
+
+    for (int t = T - 1, step = 0; t >= 0; --t, ++step) {
+      const int par = step & 1;
+      // ---- E_s ----
+#pragma unroll
+      for (int s = 0; s < 2; ++s) {
+        mbar_wait(bar_in + 8 * s, step & 1);
+        TCR_LAP(tk[0]);
+#pragma unroll
+        for (int it = 0; it < NCH; ++it) {
+          if ((valid[s] >> it) & 1u) {
+            const uint2 av = *reinterpret_cast<const uint2 *>(ac0 + s * half_bytes + it * 1024);
+            const uint32_t w0 = av.x & 0xffff7fffu, w1 = av.y & 0xffff7fffu;
+            const float2 a01 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162 *>(&w0));
+            const float2 a23 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162 *>(&w1));
+            const float ig = a01.x, jg = a01.y, fg = a23.x, og = a23.y;
+            const bool eoc = (av.x & 0x8000u) != 0;
+            float dscale = 1.0f;
+            if (a.dropout) {
+              dscale = (av.y & 0x8000u) ? 0.0f : inv_keep;
+              if (a.mask != nullptr)
+                dscale = drop_scale(a.mask, b0 + s * N2 + c0 + 4 * it, T, t, H, uo, a.row0, a.seed, a.keep);
+            }
+            const uint8_t *dp = do0 + s * half_bytes + it * 512 + (do_sw ^ (uint32_t)((it & 1) << 6));
+            const float d_out = *reinterpret_cast<const float *>(dp) * dscale;
+            const float cpv = *reinterpret_cast<const float *>(dp + N2 * 128);
+            const float dh2 = d_out + (eoc ? 0.f : dhc[s][it]);
+            const float tc = tanh_approx(fmaf(cpv, fg, ig * jg));
+            const float dc2 = (eoc ? 0.f : dcc[s][it]) + dh2 * og * (1.0f - tc * tc);
+            dcc[s][it] = dc2 * fg;
+            const float d0 = dc2 * jg * ig * (1.0f - ig), d1 = dc2 * ig * (1.0f - jg * jg);
+            const float d2 = dc2 * cpv * fg * (1.0f - fg), d3 = dh2 * tc * og * (1.0f - og);
+            bsum[0] += d0; bsum[1] += d1; bsum[2] += d2; bsum[3] += d3;
+            __nv_bfloat16 *db = d_p + s * d_half + (size_t)it * 4 * G;
+            const __nv_bfloat16 h0 = __float2bfloat16_rn(d0), h1 = __float2bfloat16_rn(d1);
+            const __nv_bfloat16 h2 = __float2bfloat16_rn(d2), h3 = __float2bfloat16_rn(d3);
+            db[0] = h0; db[H] = h1; db[2 * H] = h2; db[3 * H] = h3;
+            uint2 pk;
+            pk.x = (uint32_t)__bfloat16_as_ushort(h0) | ((uint32_t)__bfloat16_as_ushort(h1) << 16);
+            pk.y = (uint32_t)__bfloat16_as_ushort(h2) | ((uint32_t)__bfloat16_as_ushort(h3) << 16);
+            *reinterpret_cast<uint2 *>(bg0 + s * half_bytes + it * 512 + (b_sw ^ (uint32_t)((it & 1) << 6))) = pk;
+          }
+        }
+        fence_proxy_async_smem();  // d(pre) operand tile -> tcgen05.mma
+        mbar_arrive(bar_epi + 8 * s);
+        TCR_LAP(tk[1]);
+      }
+      d_p -= BG;
+      if (t == 0) break;
+      // ---- R_s: accumulator read-out, bf16 partials for every rank ----
+#pragma unroll
+      for (int s = 0; s < 2; ++s) {
+        __nv_bfloat16 *pb = part_base + (size_t)(2 * s + par) * part_par;
+        for (int mt = 0; mt < nmt; ++mt) {
+          mbar_wait(bar_acc + 8 * (4 * s + mt), step & 1);
+          if (mt == 0) TCR_LAP(tk[2]);
+          tc_fence_after();
+          const int m = mt * 128 + e;
+          uint32_t r[CPW];
+          tc_ldn<CPW>(tmem_acc + ((uint32_t)(32 * q) << 16) + (uint32_t)((s * nmt + mt) * N2 + cg * CPW), r);
+          if (m < H) {
+            __nv_bfloat16 *dst = pb + (((size_t)(m >> 5) * CS + rank) * 4 + cg) * part_blk + lane * CK;
+            uint32_t pk[CPW / 2];
+#pragma unroll
+            for (int j = 0; j < CPW / 2; ++j) {
+              const int ca = 4 * ((2 * j) % NCH) + (2 * j) / NCH, cb2 = 4 * ((2 * j + 1) % NCH) + (2 * j + 1) / NCH;
+              const __nv_bfloat162 v = __floats2bfloat162_rn(__uint_as_float(r[ca]), __uint_as_float(r[cb2]));
+              pk[j] = *reinterpret_cast<const uint32_t *>(&v);
+            }
+            if constexpr (CPW >= 8) {
+#pragma unroll
+              for (int j = 0; j < NJ; ++j)
+                *reinterpret_cast<uint4 *>(dst + j * 32 * CK) = make_uint4(pk[4 * j], pk[4 * j + 1], pk[4 * j + 2], pk[4 * j + 3]);
+            } else {
+              *reinterpret_cast<uint2 *>(dst) = make_uint2(pk[0], pk[1]);
+            }
+          }
+        }
+        tc_fence_before();
+        mbar_arrive(bar_rd + 8 * s);
+        TCR_LAP(tk[3]);
+      }
+      // ---- P_s: d(h_{t-1}) of my units = sum over ranks (fixed order) of their partials ----
+#pragma unroll
+      for (int s = 0; s < 2; ++s) {
+        mbar_wait_cluster(bar_ready + 8 * s, step & 1);
+        TCR_LAP(tk[4]);
+        const __nv_bfloat16 *src0 = part_base + (size_t)(2 * s + par) * part_par + (((size_t)rank * CS) * 4 + cg) * part_blk +
+                                    ((size_t)((esub * NCH) / CK) * 32 + eu) * CK + (esub * NCH) % CK;
+#pragma unroll
+        for (int it = 0; it < NCH; ++it) dhc[s][it] = 0.f;
+        constexpr int UR = 8;
+        for (int r0 = 0; r0 < CS; r0 += UR) {
+          if constexpr (NCH == 4) {
+            uint2 v[UR];
+#pragma unroll
+            for (int j = 0; j < UR; ++j)
+              v[j] = (r0 + j < CS) ? __ldcg(reinterpret_cast<const uint2 *>(src0 + (size_t)(r0 + j) * 4 * part_blk)) : make_uint2(0, 0);
+#pragma unroll
+            for (int j = 0; j < UR; ++j) {
+              const float2 f0 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162 *>(&v[j].x));
+              const float2 f1 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162 *>(&v[j].y));
+              dhc[s][0] += f0.x; dhc[s][1] += f0.y; dhc[s][2] += f1.x; dhc[s][3] += f1.y;
+            }
+          } else {
+            static_assert(NCH == 2 || NCH == 4, "half tiles of 32 or 64 columns");
+            uint32_t v[UR];
+#pragma unroll
+            for (int j = 0; j < UR; ++j)
+              v[j] = (r0 + j < CS) ? __ldcg(reinterpret_cast<const uint32_t *>(src0 + (size_t)(r0 + j) * 4 * part_blk)) : 0u;
+#pragma unroll
+            for (int j = 0; j < UR; ++j) {
+              const float2 f0 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162 *>(&v[j]));
+              dhc[s][0] += f0.x; dhc[s][1] += f0.y;
+            }
+          }
+        }
+        TCR_LAP(tk[5]);
+      }
+    }
+    if (a.dbias != nullptr) {
+#pragma unroll
+      for (int g = 0; g < 4; ++g) {
+        float v = bsum[g];
+        v += __shfl_xor_sync(0xffffffffu, v, 1);
+        v += __shfl_xor_sync(0xffffffffu, v, 2);
+        if (esub == 0) atomicAdd(a.dbias + g * H + uo, v);
+      }
+    }
+    if (dbg)
+      printf("[tc bwd pp N=2x%d CS=%d] cycles per half step: inputs wait %lld, elementwise+stores %lld, MMA wait %lld, tmem ld + partial stores %lld, wait ready %lld, partial reads %lld\n",
+             N2, CS, tk[0] / (2 * T), tk[1] / (2 * T), tk[2] / (2 * T), tk[3] / (2 * T), tk[4] / (2 * T), tk[5] / (2 * T));
+  }
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync_all();
+  if (warp == 1) tc_dealloc(tmem_acc, (uint32_t)a.tmem_cols);
+}
+
+// ------------------------------------------------------------------------------------------------
 // weight images: what each rank copies into shared memory, already in the 128B-swizzled K-major
 // UMMA layout.  Wh = rows [I, I+H) of the layer's TF Linear/Matrix, column g*H+v = gate g of unit v.
 //   forward : nkb k-blocks x [128 rows m=4u+g][64 k]: value Wh[k][g*H + u0+u]
@@ -1136,6 +1440,24 @@ int launch_fwd_pp(const CUtensorMap &tm_h, const CUtensorMap &tm_xw, const CUten
   at[0].val.clusterDim.x = a.CS; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
   cfg.attrs = at; cfg.numAttrs = 1;
   SK_CUDA(cudaLaunchKernelEx(&cfg, kern, tm_h, tm_xw, tm_act, a));
+  return 0;
+}
+template <int NCH>
+int launch_bwd_pp(const CUtensorMap &tm_acts, const CUtensorMap &tm_do, const CUtensorMap &tm_cp, const TcRnnArgs &a,
+                  int nclusters, size_t smem, cudaStream_t st) {
+  auto kern = a.debug ? lstm_bwd_pp_kernel<NCH, true> : lstm_bwd_pp_kernel<NCH, false>;
+  SK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  if (a.CS > 8) SK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(nclusters * a.CS);
+  cfg.blockDim = dim3(TCR_PP_THREADS);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeClusterDimension;
+  at[0].val.clusterDim.x = a.CS; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+  cfg.attrs = at; cfg.numAttrs = 1;
+  SK_CUDA(cudaLaunchKernelEx(&cfg, kern, tm_acts, tm_do, tm_cp, a));
   return 0;
 }
 template <int NCH>
@@ -1304,6 +1626,25 @@ int sk_rnn_tc_layer(skrnn_handle *h, cudaStream_t st, bool bwd, int l, int B, in
       uint32_t box[3] = {32, (uint32_t)N, 1};
       SK_TRY(sk_make_tmap(&tm_do, 4, h->ws.dout, 3, dims, str, box));
       SK_TRY(sk_make_tmap(&tm_cp, 4, h->ws.cprev[l], 3, dims, str, box));
+    }
+    static int ppb_env = -1;
+    if (ppb_env < 0) { const char *e = getenv("SKRNN_TC_PP_BWD"); ppb_env = (e && e[0] == '0') ? 0 : 1; }
+    if (ppb_env && N >= 64) {  // two half tiles in flight (lstm_bwd_pp_kernel): boxes of N/2 rows
+      uint64_t adims[3] = {(uint64_t)h->G, (uint64_t)B, (uint64_t)T};
+      uint64_t astr[2] = {(uint64_t)h->G * 2, (uint64_t)B * h->G * 2};
+      uint32_t abox[3] = {128, (uint32_t)(N / 2), 1};
+      CUtensorMap tm_act2;
+      SK_TRY(sk_make_tmap(&tm_act2, 2, h->ws.acts_bf[l], 3, adims, astr, abox, false));
+      uint64_t dims[3] = {(uint64_t)H, (uint64_t)B, (uint64_t)T};
+      uint64_t str[2] = {(uint64_t)H * 4, (uint64_t)B * H * 4};
+      uint32_t box[3] = {32, (uint32_t)(N / 2), 1};
+      SK_TRY(sk_make_tmap(&tm_do, 4, h->ws.dout, 3, dims, str, box));
+      SK_TRY(sk_make_tmap(&tm_cp, 4, h->ws.cprev[l], 3, dims, str, box));
+      SkLaunch scope(h, st, SK_CAT_RNN_BWD);
+      if (N == 64) rc = launch_bwd_pp<2>(tm_act2, tm_do, tm_cp, a, nclusters, smem, st);
+      else rc = launch_bwd_pp<4>(tm_act2, tm_do, tm_cp, a, nclusters, smem, st);
+      if (rc != 0) return 1;
+      return 0;
     }
     SkLaunch scope(h, st, SK_CAT_RNN_BWD);
     if (N == 16) rc = launch_bwd<1>(tm_act, tm_do, tm_cp, a, nclusters, smem, st);
