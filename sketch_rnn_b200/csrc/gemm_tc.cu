@@ -24,6 +24,7 @@ constexpr int A_BYTES = BM * BK * 2, B_BYTES = BN * BK * 2;
 constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
 constexpr int TC_THREADS = 192;  // warp 0: TMA, warp 1: MMA + TMEM alloc, warps 2-5: epilogue
 constexpr int TC_SMEM = STAGES * STAGE_BYTES + 1024 /*align*/ + 256 /*barriers*/;
+constexpr int TC_SMEM_256 = 4 * (A_BYTES + 256 * BK * 2) + 1024 + 256;
 
 struct TcArgs {
   int M, N, K;
@@ -35,9 +36,16 @@ struct TcArgs {
   uint32_t lbo_a, sbo_a, adv_a, lbo_b, sbo_b, adv_b;  // descriptor strides / per-UMMA_K advance (bytes)
 };
 
-template <bool A_KMAJOR, bool B_KMAJOR>
-__global__ void __launch_bounds__(TC_THREADS, 2)
+// BN_ = 128: 3 stages, two CTAs per SM.  BN_ = 256: 4 stages, one CTA per SM -- per k-block the tensor core then
+// reads 48 KB of operands for twice the math, which takes the main loop off the shared-memory bandwidth limit
+// (used for the long-K weight gradients).
+template <bool A_KMAJOR, bool B_KMAJOR, int BN_>
+__global__ void __launch_bounds__(TC_THREADS, BN_ == 128 ? 2 : 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, TcArgs a) {
+  constexpr int BN = BN_;
+  constexpr int STAGES = BN_ == 128 ? 3 : 4;
+  constexpr int B_BYTES = BN * BK * 2;
+  constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const uint32_t bars = base + STAGES * STAGE_BYTES;  // full[S], empty[S], tmem_full, tmem holder
@@ -86,8 +94,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         if (B_KMAJOR) {
           tma_load_2d(sb, &tmB, bar_full + 8 * s, k0, n0);
         } else {
-          tma_load_2d(sb, &tmB, bar_full + 8 * s, n0, k0);
-          tma_load_2d(sb + B_BYTES / 2, &tmB, bar_full + 8 * s, n0 + 64, k0);
+#pragma unroll
+          for (int c = 0; c < BN / 64; ++c) tma_load_2d(sb + c * 8192, &tmB, bar_full + 8 * s, n0 + 64 * c, k0);
         }
       }
     }
@@ -160,25 +168,29 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 // This is the shape of the hoisted input projections (M = T*B rows, K <= 512): they are bound by the
 // write of C, not by the tensor pipe.
 // ------------------------------------------------------------------------------------------------
-constexpr int P_STAGES = 4;
-constexpr int P_STAGING = BM * BN * 4;  // 4 sub-tiles [128 rows][32 cols] fp32, 128B-swizzled
-constexpr int P_SMEM = P_STAGES * STAGE_BYTES + P_STAGING + 512 /*bias*/ + 1024 /*align*/ + 256 /*barriers*/;
+constexpr int P_RING = 2 * BM * 32 * 4;  // two [128 rows][32 cols] fp32 sub-tiles (128B-swizzled): C leaves 32 columns at a time
+constexpr int p_stages(int bn) { return bn == 128 ? 5 : 4; }
+constexpr int p_smem(int bn) { return p_stages(bn) * (A_BYTES + bn * BK * 2) + P_RING + 1024 /*bias*/ + 1024 /*align*/ + 256; }
 
-template <bool A_KMAJOR, bool B_KMAJOR>
+template <bool A_KMAJOR, bool B_KMAJOR, int BN_>
 __global__ void __launch_bounds__(TC_THREADS, 1)
 gemm_tc_persist_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                        const __grid_constant__ CUtensorMap tmC, TcArgs a) {
+  constexpr int BN = BN_;
+  constexpr int P_STAGES = p_stages(BN_);
+  constexpr int B_BYTES = BN * BK * 2;
+  constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   uint8_t *gen_base = smem_raw + (base - smem_u32(smem_raw));
-  const uint32_t s_stage = base + P_STAGES * STAGE_BYTES;
-  const uint32_t s_bias = s_stage + P_STAGING;
-  const uint32_t bars = s_bias + 512;
+  const uint32_t s_ring = base + P_STAGES * STAGE_BYTES;
+  const uint32_t s_bias = s_ring + P_RING;
+  const uint32_t bars = s_bias + 1024;
   const uint32_t bar_full = bars, bar_empty = bars + 8 * P_STAGES;
   const uint32_t bar_tfull = bars + 16 * P_STAGES, bar_tempty = bar_tfull + 16, tmem_holder = bar_tempty + 16;
   volatile uint32_t *tmem_holder_ptr = reinterpret_cast<volatile uint32_t *>(gen_base + (tmem_holder - base));
   float *bias_gen = reinterpret_cast<float *>(gen_base + (s_bias - base));
-  uint8_t *stage_gen = gen_base + (s_stage - base);
+  uint8_t *ring_gen = gen_base + (s_ring - base);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int ntn = (a.N + BN - 1) / BN, ntm = (a.M + BM - 1) / BM;
@@ -222,8 +234,8 @@ gemm_tc_persist_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
           if (B_KMAJOR) {
             tma_load_2d(sb, &tmB, bar_full + 8 * s, k0, n0);
           } else {
-            tma_load_2d(sb, &tmB, bar_full + 8 * s, n0, k0);
-            tma_load_2d(sb + B_BYTES / 2, &tmB, bar_full + 8 * s, n0 + 64, k0);
+#pragma unroll
+            for (int c = 0; c < BN / 64; ++c) tma_load_2d(sb + c * 8192, &tmB, bar_full + 8 * s, n0 + 64 * c, k0);
           }
         }
       }
@@ -257,22 +269,25 @@ gemm_tc_persist_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
     const int q = warp & 3;              // TMEM lane quarter of this warp
     const int et = threadIdx.x - 64;     // 0..127
     const int r = 32 * q + lane;         // accumulator row inside the tile
+    const bool issuer = warp == 2 && lane == 0;
     int lt = 0;
     for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++lt) {
       const int m0 = (tile / ntn) * BM, n0 = (tile % ntn) * BN;
       const int buf = lt & 1;
-      // staging tile free again (last tile's stores have read it), bias slice of this tile staged
-      if (warp == 2 && lane == 0) tma_store_wait_read();
-      named_bar_sync(1, 128);
-      bias_gen[et] = (a.bias != nullptr && n0 + et < a.N) ? __ldg(a.bias + n0 + et) : 0.f;
-      named_bar_sync(1, 128);
+      // bias slice of this tile (everybody is past the previous tile's last read of it: see the barriers below)
+#pragma unroll
+      for (int j = 0; j < BN / 128; ++j)
+        bias_gen[et + 128 * j] = (a.bias != nullptr && n0 + et + 128 * j < a.N) ? __ldg(a.bias + n0 + et + 128 * j) : 0.f;
       mbar_wait(bar_tfull + 8 * buf, (lt >> 1) & 1);
       tc_fence_after();
 #pragma unroll 1
       for (int c = 0; c < BN / 32; ++c) {
+        // ring slot c&1: the store issued two chunks ago has finished reading it
+        if (issuer) tma_store_wait_read_n<1>();
+        named_bar_sync(1, 128);
         uint32_t v[32];
         tc_ld32(tmem_acc + ((uint32_t)(32 * q) << 16) + (uint32_t)(buf * BN + c * 32), v);
-        uint8_t *row = stage_gen + c * 16384 + r * 128;
+        uint8_t *row = ring_gen + (c & 1) * 16384 + r * 128;
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
           const float4 bv = *reinterpret_cast<const float4 *>(bias_gen + c * 32 + 4 * i);
@@ -281,20 +296,18 @@ gemm_tc_persist_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
           o.z = __uint_as_float(v[4 * i + 2]) + bv.z; o.w = __uint_as_float(v[4 * i + 3]) + bv.w;
           *reinterpret_cast<float4 *>(row + ((i ^ (r & 7)) << 4)) = o;
         }
+        fence_proxy_async_smem();
+        named_bar_sync(1, 128);
+        if (issuer) {
+          if (n0 + c * 32 < a.N) tma_store_2d_nocommit(&tmC, s_ring + (c & 1) * 16384, n0 + c * 32, m0);
+          tma_store_commit();  // one group per chunk, written or not, so the ring accounting stays uniform
+        }
       }
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(bar_tempty + 8 * buf);  // accumulator buffer may be overwritten
-      fence_proxy_async_smem();
-      named_bar_sync(1, 128);
-      if (warp == 2 && lane == 0) {
-#pragma unroll
-        for (int c = 0; c < BN / 32; ++c)
-          if (n0 + c * 32 < a.N) tma_store_2d_nocommit(&tmC, s_stage + c * 16384, n0 + c * 32, m0);
-        tma_store_commit();
-      }
     }
-    if (warp == 2 && lane == 0) tma_store_wait_all();
+    if (issuer) tma_store_wait_all();
   }
   tc_fence_before();
   __syncthreads();
@@ -379,11 +392,19 @@ int sk_gemm_tc(skrnn_handle *h, cudaStream_t st, int M, int N, int K, const void
   if (g_tc_override[3]) a.lbo_b = g_tc_override[3];
   if (g_tc_override[4]) a.sbo_b = g_tc_override[4];
   if (g_tc_override[5]) a.adv_b = g_tc_override[5];
-  const int gx = (N + BN - 1) / BN, gy = (M + BM - 1) / BM;
   const int nkb = (K + BK - 1) / BK;
+  static int wide_env = -1;
+  if (wide_env < 0) { const char *e = getenv("SKRNN_GEMM_WIDE"); wide_env = (e && e[0] == '0') ? 0 : 1; }
   static int persist_env = -1;
   if (persist_env < 0) { const char *e = getenv("SKRNN_GEMM_PERSIST"); persist_env = (e && e[0] == '0') ? 0 : 1; }
-  if (persist_env && !accumulate && (ldc % 4) == 0 && (reinterpret_cast<uintptr_t>(C) & 15) == 0 && gx * gy >= h->num_sms) {
+  const bool persist = persist_env && !accumulate && (ldc % 4) == 0 && (reinterpret_cast<uintptr_t>(C) & 15) == 0 &&
+                       ((N + BN - 1) / BN) * ((M + BM - 1) / BM) >= h->num_sms;
+  // 128x256 tiles: long-K accumulating products (weight gradients) and the persistent variant when N allows
+  const bool wide = wide_env && N >= 256 && (persist ? ((N + 255) / 256) * ((M + BM - 1) / BM) >= h->num_sms : (accumulate && nkb >= 64));
+  if (wide && b_kmajor) SK_TRY(make_map(&tmB, B, K, N, ldb, BK, 256));
+  const int bn = wide ? 256 : BN;
+  const int gx = (N + bn - 1) / bn, gy = (M + BM - 1) / BM;
+  if (persist) {
     CUtensorMap tmC;
     {
       uint64_t dims[2] = {(uint64_t)N, (uint64_t)M};
@@ -396,8 +417,13 @@ int sk_gemm_tc(skrnn_handle *h, cudaStream_t st, int M, int N, int K, const void
     const int grid = std::min(gx * gy, h->num_sms);
 #define SK_TCP_LAUNCH(AK, BKM)                                                                                      \
   do {                                                                                                              \
-    SK_CUDA(cudaFuncSetAttribute(gemm_tc_persist_kernel<AK, BKM>, cudaFuncAttributeMaxDynamicSharedMemorySize, P_SMEM)); \
-    gemm_tc_persist_kernel<AK, BKM><<<grid, TC_THREADS, P_SMEM, st>>>(tmA, tmB, tmC, a);                            \
+    if (wide) {                                                                                                     \
+      SK_CUDA(cudaFuncSetAttribute(gemm_tc_persist_kernel<AK, BKM, 256>, cudaFuncAttributeMaxDynamicSharedMemorySize, p_smem(256))); \
+      gemm_tc_persist_kernel<AK, BKM, 256><<<grid, TC_THREADS, p_smem(256), st>>>(tmA, tmB, tmC, a);                \
+    } else {                                                                                                        \
+      SK_CUDA(cudaFuncSetAttribute(gemm_tc_persist_kernel<AK, BKM, 128>, cudaFuncAttributeMaxDynamicSharedMemorySize, p_smem(128))); \
+      gemm_tc_persist_kernel<AK, BKM, 128><<<grid, TC_THREADS, p_smem(128), st>>>(tmA, tmB, tmC, a);                \
+    }                                                                                                               \
   } while (0)
     if (a_kmajor && b_kmajor) SK_TCP_LAUNCH(true, true);
     else if (a_kmajor && !b_kmajor) SK_TCP_LAUNCH(true, false);
@@ -410,8 +436,14 @@ int sk_gemm_tc(skrnn_handle *h, cudaStream_t st, int M, int N, int K, const void
   int nsplit = 1;
   if (accumulate) {
     int tiles = gx * gy;
-    int want = (2 * h->num_sms + tiles - 1) / tiles;
-    nsplit = std::max(1, std::min(want, (nkb + 7) / 8));
+    // split K so that the CTAs fill whole waves of the GPU: minimise ceil(tiles*n / slots) / n
+    const int slots = (wide ? 1 : 2) * h->num_sms;
+    const int nmax = std::max(1, std::min(64, (nkb + 7) / 8));
+    double best = 1e30;
+    for (int n = 1; n <= nmax; ++n) {
+      const double cost = (double)((tiles * n + slots - 1) / slots) / n;
+      if (cost < best * 0.97) { best = cost; nsplit = n; }
+    }
   }
   a.kb_per_split = (nkb + nsplit - 1) / nsplit;
   nsplit = (nkb + a.kb_per_split - 1) / a.kb_per_split;
@@ -419,8 +451,13 @@ int sk_gemm_tc(skrnn_handle *h, cudaStream_t st, int M, int N, int K, const void
   SkLaunch scope(h, st, SK_CAT_TC_GEMM);
 #define SK_TC_LAUNCH(AK, BKM)                                                                                  \
   do {                                                                                                         \
-    SK_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<AK, BKM>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM)); \
-    gemm_tc_kernel<AK, BKM><<<grid, TC_THREADS, TC_SMEM, st>>>(tmA, tmB, a);                                   \
+    if (wide) {                                                                                                \
+      SK_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<AK, BKM, 256>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_256)); \
+      gemm_tc_kernel<AK, BKM, 256><<<grid, TC_THREADS, TC_SMEM_256, st>>>(tmA, tmB, a);                        \
+    } else {                                                                                                   \
+      SK_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<AK, BKM, 128>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM)); \
+      gemm_tc_kernel<AK, BKM, 128><<<grid, TC_THREADS, TC_SMEM, st>>>(tmA, tmB, a);                            \
+    }                                                                                                          \
   } while (0)
   if (a_kmajor && b_kmajor) SK_TC_LAUNCH(true, true);
   else if (a_kmajor && !b_kmajor) SK_TC_LAUNCH(true, false);
