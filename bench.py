@@ -59,45 +59,81 @@ def load_peaks():
     return dict(hbm=6650.0, tc_burst=1590.0, tc_sustained=1400.0, src="fallback")
 
 
+# dram__bytes_read.sum + dram__bytes_write.sum per launch of the dominant kernel, from the `ncu --set full` captures
+# summarised in profiles/r01_ncu_summary_bf16.md (1 GPU, full batch)
+NCU_TRAFFIC = {
+    ("train_h512_l3_b800", "bf16", "rnn_bwd"): 1.968596e9 + 0.971763e9,
+    ("train_h512_l3_b800", "bf16", "rnn_fwd"): 1.985982e9 + 1.931351e9,
+}
+
+
 class ClockSampler(threading.Thread):
-    """nvidia-smi clocks / throttle reasons sampled during the timed region."""
+    """SM clock and throttle reasons sampled DURING the timed region: NVML (a few microseconds per sample, so even a
+    30 ms region gets several) with nvidia-smi as the fallback."""
+
+    REASONS = {0x8: "hw_slowdown", 0x40: "hw_thermal_slowdown", 0x20: "sw_thermal_slowdown", 0x4: "sw_power_cap"}
 
     def __init__(self, index):
         threading.Thread.__init__(self, daemon=True)
         self.index = index
-        self.samples = []
+        self.samples = []   # (sm_mhz, max_mhz, set(reasons))
         self.stop_flag = False
+        self.nv = None
+        try:
+            import pynvml
+            import torch
+            pynvml.nvmlInit()
+            pr = torch.cuda.get_device_properties(index)
+            try:
+                bus = "%08x:%02x:%02x.0" % (pr.pci_domain_id, pr.pci_bus_id, pr.pci_device_id)
+                self.handle = pynvml.nvmlDeviceGetHandleByPciBusId(bus.encode())
+            except Exception:
+                self.handle = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = float(pynvml.nvmlDeviceGetMaxClockInfo(self.handle, pynvml.NVML_CLOCK_SM))
+            self.nv = pynvml
+        except Exception:
+            self.nv = None
 
-    def run(self):
+    def _nvml_sample(self):
+        nv = self.nv
+        sm = float(nv.nvmlDeviceGetClockInfo(self.handle, nv.NVML_CLOCK_SM))
+        try:
+            mask = int(nv.nvmlDeviceGetCurrentClocksEventReasons(self.handle))
+        except Exception:
+            mask = int(nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.handle))
+        self.samples.append((sm, self.max_mhz, {n for b, n in self.REASONS.items() if mask & b}))
+
+    def _smi_sample(self):
         q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,"
              "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
              "clocks_event_reasons.sw_power_cap")
+        out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + q, "--format=csv,noheader,nounits"],
+                             capture_output=True, text=True, timeout=5).stdout.strip()
+        if out:
+            f = [v.strip() for v in out.split(",")]
+            names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+            self.samples.append((float(f[0]), float(f[1]), {n for n, v in zip(names, f[2:6]) if v.lower().startswith("active")}))
+
+    def run(self):
         while not self.stop_flag:
             try:
-                out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + q,
-                                      "--format=csv,noheader,nounits"], capture_output=True, text=True,
-                                     timeout=5).stdout.strip()
-                if out:
-                    self.samples.append([s.strip() for s in out.split(",")])
+                if self.nv is not None:
+                    self._nvml_sample()
+                else:
+                    self._smi_sample()
             except Exception:
                 pass
-            time.sleep(0.2)
+            time.sleep(0.005 if self.nv is not None else 0.2)
 
     def summary(self):
         self.stop_flag = True
-        sm, mx, reasons = [], 0, set()
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for s in self.samples:
-            try:
-                sm.append(float(s[0]))
-                mx = max(mx, float(s[1]))
-                for n, v in zip(names, s[2:6]):
-                    if v.lower().startswith("active"):
-                        reasons.add(n)
-            except Exception:
-                pass
+        sm = [v[0] for v in self.samples]
+        mx = max([v[1] for v in self.samples], default=0)
+        reasons = set()
+        for v in self.samples:
+            reasons |= v[2]
         return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": mx or None,
-                "reasons": sorted(reasons), "samples": len(sm)}
+                "reasons": sorted(reasons), "samples": len(sm), "source": "nvml" if self.nv is not None else "nvidia-smi"}
 
 
 # --------------------------------------------------------------------------------------------
@@ -365,7 +401,8 @@ def run_ours(args, w):
                     "whole_step_tflops": whole, "per_kernel_ms": kern_ms, "per_kernel_launches": kern_cnt}
         else:
             roof = {"bound": "tensor", "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": ach / peak,
-                    "traffic": None, "kernel": dom, "launch_ms": dur_ms, "launches_per_step": n_dom,
+                    "traffic": NCU_TRAFFIC.get((args.workload, args.precision, dom)) if world == 1 else None,
+                    "kernel": dom, "launch_ms": dur_ms, "launches_per_step": n_dom,
                     "algorithmic_flops_per_launch": fpl,
                     "peak_source": ("MEASURED_PEAKS.json bf16 sustained (%s)" % peaks["src"]) if (tc and dom != "sampler") else
                     "fp32 CUDA-core nominal 148 SM x 128 lanes x 2 x 1.965 GHz (this kernel runs no tensor-core math)",

@@ -673,6 +673,8 @@ lstm_fwd_pp_kernel(const __grid_constant__ CUtensorMap tm_h, const __grid_consta
     uint2 *act_g = reinterpret_cast<uint2 *>(a.acts_bf) + (size_t)(b0 + cb) * H + uo;  // activation record of step t
     float *c_p = a.cprev + ((size_t)B + b0 + cb) * H + uo;             // cprev[t+1]
     const unsigned char *eoc_p = a.eoc + b0 + cb;                       // eoc[t]
+    const uint32_t drop_unit = skm_drop_unit(a.seed, (uint32_t)uo);
+    const float inv_keep = 1.0f / a.keep;
     uint32_t eoc_next = 0;  // flags of the half step about to be processed
 #pragma unroll
     for (int it = 0; it < NCH; ++it)
@@ -695,10 +697,17 @@ lstm_fwd_pp_kernel(const __grid_constant__ CUtensorMap tm_h, const __grid_consta
         }
         float dsc[NCH];
 #pragma unroll
-        for (int it = 0; it < NCH; ++it) {
-          dsc[it] = 1.0f;
-          if (a.dropout && ((valid[s] >> it) & 1u))
-            dsc[it] = drop_scale(a.mask, b0 + s * N2 + cb + 4 * it, T, t, H, uo, a.row0, a.seed, a.keep);
+        for (int it = 0; it < NCH; ++it) dsc[it] = 1.0f;
+        if (a.dropout) {
+          const uint32_t pre = skm_drop_prefix(a.seed, drop_unit, (uint32_t)t);  // (unit, t) part of the mask hash
+#pragma unroll
+          for (int it = 0; it < NCH; ++it) {
+            if ((valid[s] >> it) & 1u) {
+              const int b = b0 + s * N2 + cb + 4 * it;
+              dsc[it] = a.mask != nullptr ? a.mask[((int64_t)b * T + t) * H + uo] * inv_keep
+                                          : (skm_u01(skm_drop_finish(pre, (uint32_t)(a.row0 + b))) < a.keep ? inv_keep : 0.0f);
+            }
+          }
         }
         TCR_LAP(tk[0]);
         mbar_wait(bar_acc + 8 * s, t & 1);
@@ -708,6 +717,8 @@ lstm_fwd_pp_kernel(const __grid_constant__ CUtensorMap tm_h, const __grid_consta
         tc_ldn<CPW>(tmem_acc + ((uint32_t)(32 * q) << 16) + (uint32_t)(s * N2 + cg * CPW), r);
         mbar_wait(bar_xw + 8 * s, t & 1);
         TCR_LAP(tk[2]);
+        auto items = [&](auto full_tag) {  // FULL: every column of the half tile is a real batch row
+        constexpr bool FULL = decltype(full_tag)::value;
 #pragma unroll
         for (int it = 0; it < NCH; ++it) {
           float v0, v1, v2, v3, p0, p1, p2, p3;
@@ -717,7 +728,7 @@ lstm_fwd_pp_kernel(const __grid_constant__ CUtensorMap tm_h, const __grid_consta
           v2 = __shfl_xor_sync(0xffffffffu, v2, 2);
           v3 = __shfl_xor_sync(0xffffffffu, v3, 3);
           perm4(g_lo, g_hi, v0, v1, v2, v3, p0, p1, p2, p3);
-          if ((valid[s] >> it) & 1u) {
+          if (FULL || ((valid[s] >> it) & 1u)) {
             uint8_t *pp = ((it & 1) ? pl_o : pl_e) + s * xw_bytes + it * 512;
             const float ig = sigmoid_approx(p0 + *reinterpret_cast<const float *>(pp));
             const float jg = tanh_approx(p1 + *reinterpret_cast<const float *>(pp + 1 * (N2 * 128)));
@@ -750,6 +761,8 @@ lstm_fwd_pp_kernel(const __grid_constant__ CUtensorMap tm_h, const __grid_consta
             }
           }
         }
+        };
+        if (b0 + (s + 1) * N2 <= B) items(std::true_type{}); else items(std::false_type{});
         fence_proxy_async_smem();  // h staging tile -> TMA store
         tc_fence_before();         // accumulator reads -> next product of this half
         mbar_arrive(bar_epi + 8 * s);
@@ -1236,9 +1249,11 @@ lstm_bwd_pp_kernel(const __grid_constant__ CUtensorMap tm_acts, const __grid_con
       for (int s = 0; s < 2; ++s) {
         mbar_wait(bar_in + 8 * s, step & 1);
         TCR_LAP(tk[0]);
+        auto items = [&](auto full_tag) {
+        constexpr bool FULL = decltype(full_tag)::value;
 #pragma unroll
         for (int it = 0; it < NCH; ++it) {
-          if ((valid[s] >> it) & 1u) {
+          if (FULL || ((valid[s] >> it) & 1u)) {
             const uint2 av = *reinterpret_cast<const uint2 *>(ac0 + s * half_bytes + it * 1024);
             const uint32_t w0 = av.x & 0xffff7fffu, w1 = av.y & 0xffff7fffu;
             const float2 a01 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162 *>(&w0));
@@ -1271,6 +1286,8 @@ lstm_bwd_pp_kernel(const __grid_constant__ CUtensorMap tm_acts, const __grid_con
             *reinterpret_cast<uint2 *>(bg0 + s * half_bytes + it * 512 + (b_sw ^ (uint32_t)((it & 1) << 6))) = pk;
           }
         }
+        };
+        if (b0 + (s + 1) * N2 <= B) items(std::true_type{}); else items(std::false_type{});
         fence_proxy_async_smem();  // d(pre) operand tile -> tcgen05.mma
         mbar_arrive(bar_epi + 8 * s);
         TCR_LAP(tk[1]);

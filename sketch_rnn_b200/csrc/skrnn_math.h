@@ -177,15 +177,19 @@ SKM_FN void skm_philox4x32(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, u
   out[0] = c0; out[1] = c1; out[2] = c2; out[3] = c3;
 }
 // Counter hash for in-kernel dropout masks: three rounds of the lowbias32 integer finaliser over
-// (seed, global row, timestep, unit).  Integer only, so host and device agree; ~20 ALU ops.
+// (seed, unit, timestep, global row).  Integer only, so host and device agree.  The row is mixed in last: a
+// thread that owns one hidden unit computes the (unit, t) prefix once per step and pays one round per row.
 SKM_FN uint32_t skm_mix32(uint32_t x) {
   x ^= x >> 16; x *= 0x7feb352du; x ^= x >> 15; x *= 0x846ca68bu; x ^= x >> 16;
   return x;
 }
+SKM_FN uint32_t skm_drop_unit(uint64_t seed, uint32_t unit) { return skm_mix32(unit * 0xC2B2AE3Du ^ (uint32_t)seed); }
+SKM_FN uint32_t skm_drop_prefix(uint64_t seed, uint32_t unit_hash, uint32_t t) {
+  return skm_mix32(unit_hash ^ (t * 0x85EBCA77u) ^ (uint32_t)(seed >> 32));
+}
+SKM_FN uint32_t skm_drop_finish(uint32_t prefix, uint32_t row) { return skm_mix32(prefix ^ (row * 0x9E3779B1u)); }
 SKM_FN uint32_t skm_drop_bits(uint64_t seed, uint32_t row, uint32_t t, uint32_t unit) {
-  uint32_t h = skm_mix32(row * 0x9E3779B1u ^ (uint32_t)seed);
-  h = skm_mix32(h ^ (t * 0x85EBCA77u) ^ (uint32_t)(seed >> 32));
-  return skm_mix32(h ^ (unit * 0xC2B2AE3Du));
+  return skm_drop_finish(skm_drop_prefix(seed, skm_drop_unit(seed, unit), t), row);
 }
 // 24-bit uniform in [0,1): exactly representable, same on host and device.
 SKM_FN float skm_u01(uint32_t r) { return (float)(r >> 8) * 5.9604644775390625e-8f; }
