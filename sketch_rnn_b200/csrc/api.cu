@@ -73,9 +73,10 @@ void free_workspace(SkWorkspace &w) {
   w.eoc = nullptr;
   w.x_tm = w.dout = w.logits = nullptr;
   cudaFree(w.x8_bf);
-  cudaFree(w.dpre_bf);
+  cudaFree(w.dpre_bf_buf[0]);
+  cudaFree(w.dpre_bf_buf[1]);
   cudaFree(w.dlogits_bf);
-  w.x8_bf = w.dpre_bf = w.dlogits_bf = nullptr;
+  w.x8_bf = w.dpre_bf = w.dpre_bf_buf[0] = w.dpre_bf_buf[1] = w.dlogits_bf = nullptr;
   for (int l = 0; l < SK_MAX_LAYERS; ++l) {
     cudaFree(w.out_bf[l]);
     cudaFree(w.hprev_bf[l]);
@@ -106,7 +107,9 @@ int ensure_workspace(skrnn_handle *h, int B, int T) {
     const size_t e = sizeof(__nv_bfloat16);
     SK_CUDA(cudaMalloc(&w.x8_bf, rows * 8 * e));
     SK_CUDA(cudaMemset(w.x8_bf, 0, rows * 8 * e));
-    SK_CUDA(cudaMalloc(&w.dpre_bf, rows * h->G * e));
+    SK_CUDA(cudaMalloc(&w.dpre_bf_buf[0], rows * h->G * e));
+    SK_CUDA(cudaMalloc(&w.dpre_bf_buf[1], rows * h->G * e));
+    w.dpre_bf = w.dpre_bf_buf[0];
     SK_CUDA(cudaMalloc(&w.dlogits_bf, rows * h->NOUTP * e));
     SK_CUDA(cudaMemset(w.dlogits_bf, 0, rows * h->NOUTP * e));
     for (int l = 0; l < h->L; ++l) {
@@ -275,6 +278,14 @@ int skrnn_create(const skrnn_config *cfg, skrnn_handle **out) {
     cudaMemset(h->params_bf, 0, o * sizeof(__nv_bfloat16));
     cudaMemcpy(h->cast_seg_dev, seg.data(), seg.size() * sizeof(int64_t), cudaMemcpyHostToDevice);
   }
+  if (cudaStreamCreateWithFlags(&h->side, cudaStreamNonBlocking) != cudaSuccess) {
+    sk_set_error("skrnn_create: cudaStreamCreate failed");
+    return fail();
+  }
+  for (int i = 0; i < 2; ++i) {
+    cudaEventCreateWithFlags(&h->ev_main[i], cudaEventDisableTiming);
+    cudaEventCreateWithFlags(&h->ev_side[i], cudaEventDisableTiming);
+  }
   h->ws.wpack_floats = (int64_t)h->cluster_size * h->H * 256;
   if (cudaMalloc(&h->ws.wpack, h->ws.wpack_floats * sizeof(float)) != cudaSuccess) {
     sk_set_error("skrnn_create: cudaMalloc of weight pack failed");
@@ -314,6 +325,11 @@ void skrnn_destroy(skrnn_handle *h) {
   cudaFreeHost(h->pin_y);
   cudaFreeHost(h->pin_state);
   cudaFreeHost(h->pin_loss);
+  if (h->side) cudaStreamDestroy(h->side);
+  for (int i = 0; i < 2; ++i) {
+    if (h->ev_main[i]) cudaEventDestroy(h->ev_main[i]);
+    if (h->ev_side[i]) cudaEventDestroy(h->ev_side[i]);
+  }
   for (auto &r : h->prof) { cudaEventDestroy(r.a); cudaEventDestroy(r.b); }
   for (auto e : h->prof_pool) cudaEventDestroy(e);
   delete h;
@@ -463,10 +479,45 @@ int skrnn_loss_grad(skrnn_handle *h, int32_t B, int32_t T, const float *x_dev, c
   SK_TRY(gemm(h, st, H, NOUT, R, top_output(h), false, dlogits_op(h), true, h->grads + h->off_out_w, NOUT, nullptr, true));
   SK_TRY(sk_colsum(h, st, h->ws.logits, R, NOUT, NOUT, h->grads + h->off_out_b));
   SK_TRY(gemm(h, st, R, H, NOUT, dlogits_op(h), true, out_weight(h), false, h->ws.dout, H, nullptr, false));
+  // Weight gradients are off the critical path: on the bf16 path layer l's dW products are enqueued on a side
+  // stream so that they run next to layer l-1's BPTT kernel (which leaves SMs idle: its clusters do not tile the
+  // GPU).  They are handed to the side stream only after that BPTT launch has been enqueued on `st`, so its
+  // clusters are dispatched first.  d(pre) is double-buffered for this.
+  static int ov_env = -1;
+  if (ov_env < 0) { const char *e = getenv("SKRNN_WGRAD_OVERLAP"); ov_env = (e && e[0] == '0') ? 0 : 1; }
+  const bool overlap = ov_env && h->cfg.precision == SKRNN_PREC_BF16 && h->cfg.cell != SKRNN_CELL_GRU && h->L > 1;
+  struct Deferred { int l = -1; int buf = 0; bool bias_done = false; } def;
+  bool side_busy[2] = {false, false};
+  auto wgrad = [&](cudaStream_t s2, int l, int buf, bool bias_done) -> int {
+    const SkLayerParams &lp = h->lp[l];
+    Op dpre = dpre_op(h, l);
+    if (h->ws.dpre_bf_buf[buf]) dpre.b = h->ws.dpre_bf_buf[buf];
+    float *gW = h->grads + lp.w[0];
+    SK_TRY(gemm(h, s2, lp.I, G, R, layer_input(h, l), false, dpre, true, gW, G, nullptr, true));
+    SK_TRY(gemm(h, s2, H, G, R, hprev_op(h, l), false, dpre, true, gW + (size_t)lp.I * G, G, nullptr, true));
+    if (!bias_done) SK_TRY(bias_grad(h, s2, dpre, R, G, h->grads + lp.b[0]));
+    return 0;
+  };
+  auto flush_deferred = [&]() -> int {
+    if (def.l < 0) return 0;
+    SK_CUDA(cudaStreamWaitEvent(h->side, h->ev_main[def.buf], 0));
+    SK_TRY(wgrad(h->side, def.l, def.buf, def.bias_done));
+    SK_CUDA(cudaEventRecord(h->ev_side[def.buf], h->side));
+    side_busy[def.buf] = true;
+    def.l = -1;
+    return 0;
+  };
   for (int l = h->L - 1; l >= 0; --l) {
     const SkLayerParams &lp = h->lp[l];
     h->bias_grad_done = false;
+    const int buf = overlap ? ((h->L - 1 - l) & 1) : 0;
+    if (h->ws.dpre_bf_buf[buf]) h->ws.dpre_bf = h->ws.dpre_bf_buf[buf];
+    if (side_busy[buf]) {  // the dW products that read this d(pre) copy two layers ago must be done
+      SK_CUDA(cudaStreamWaitEvent(st, h->ev_side[buf], 0));
+      side_busy[buf] = false;
+    }
     SK_TRY(sk_rnn_backward_layer(h, st, l, B, T, x_dev, dropout_mask_dev, seed, row0, true));
+    SK_TRY(flush_deferred());  // the previous layer's dW: enqueued after this layer's BPTT launch
     const Op X = layer_input(h, l);
     const Op dpre = dpre_op(h, l);
     const int I = lp.I;
@@ -484,13 +535,19 @@ int skrnn_loss_grad(skrnn_handle *h, int32_t B, int32_t T, const float *x_dev, c
         SK_TRY(gemm(h, st, R, I, H, dc, true, weight(h, l, 1), false, h->ws.dout, H, nullptr, true));
       }
     } else {
-      float *gW = h->grads + lp.w[0];
-      SK_TRY(gemm(h, st, I, G, R, X, false, dpre, true, gW, G, nullptr, true));
-      SK_TRY(gemm(h, st, H, G, R, hprev_op(h, l), false, dpre, true, gW + (size_t)I * G, G, nullptr, true));
-      if (!h->bias_grad_done) SK_TRY(bias_grad(h, st, dpre, R, G, h->grads + lp.b[0]));
+      // d(out) of the layer below first: it is what the next BPTT launch waits for
       if (l > 0) SK_TRY(gemm(h, st, R, I, G, dpre, true, weight(h, l, 0), false, h->ws.dout, H, nullptr, false));
+      if (overlap && l > 0) {
+        SK_CUDA(cudaEventRecord(h->ev_main[buf], st));
+        def.l = l; def.buf = buf; def.bias_done = h->bias_grad_done;
+      } else {
+        SK_TRY(wgrad(st, l, buf, h->bias_grad_done));
+      }
     }
   }
+  SK_TRY(flush_deferred());
+  for (int b2 = 0; b2 < 2; ++b2)
+    if (side_busy[b2]) SK_CUDA(cudaStreamWaitEvent(st, h->ev_side[b2], 0));  // join
   return 0;
 }
 

@@ -71,7 +71,8 @@ struct SkWorkspace {   // time-major activations for one (B, T) capacity
   __nv_bfloat16 *aux_bf[SK_MAX_LAYERS] = {nullptr};  // gru r*h
   __nv_bfloat16 *acts_bf[SK_MAX_LAYERS] = {nullptr}; // [T,B,H,4]: lstm gate activations i,j,f,o saved by the tcgen05
                                                      // forward kernel for its BPTT counterpart
-  __nv_bfloat16 *dpre_bf = nullptr;                  // [T,B,G] of the layer being differentiated
+  __nv_bfloat16 *dpre_bf = nullptr;                  // [T,B,G] of the layer being differentiated (= one of dpre_bf_buf)
+  __nv_bfloat16 *dpre_bf_buf[2] = {nullptr, nullptr}; // two copies: layer l's weight gradients overlap layer l-1's BPTT
   __nv_bfloat16 *dlogits_bf = nullptr;               // [T*B,NOUTP]
   int64_t wpack_floats = 0;
   __nv_bfloat16 *partial = nullptr;         // tcgen05 BPTT: per-rank partial d(h) exchange
@@ -113,6 +114,9 @@ struct skrnn_handle {
   bool tc_rnn_disabled = false;
   bool bias_grad_done = false;  // set by a backward recurrent kernel that accumulated d(bias) itself
   bool nt_rnn_disabled = false;
+  // side stream for work off the critical path of the backward pass (weight gradients), see skrnn_loss_grad
+  cudaStream_t side = nullptr;
+  cudaEvent_t ev_main[2] = {nullptr, nullptr}, ev_side[2] = {nullptr, nullptr};
   int fwd_family[SK_MAX_LAYERS] = {0};  // which kernels ran a layer's forward (0 fp32, 1 rnn_tc, 2 rnn_nt): they save
                                         // activations in different places, so the backward must be the same family
   // optional per-category kernel timing (skrnn_profile_*): CUDA events around every launch
