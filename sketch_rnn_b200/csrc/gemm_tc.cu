@@ -331,8 +331,7 @@ EncodeTiledFn get_encode() {
   return fn;
 }
 
-// 2-D bf16 tensor map: `inner` contiguous elements per row, `outer` rows of `ld` elements.
-int make_map(CUtensorMap *m, const void *ptr, int64_t inner, int64_t outer, int64_t ld, int box_inner, int box_outer) {
+int make_map_uncached(CUtensorMap *m, const void *ptr, int64_t inner, int64_t outer, int64_t ld, int box_inner, int box_outer) {
   EncodeTiledFn enc = get_encode();
   SK_CHECK(enc != nullptr, "cuTensorMapEncodeTiled is not available from the driver");
   SK_CHECK((reinterpret_cast<uintptr_t>(ptr) & 15) == 0 && (ld * 2) % 16 == 0,
@@ -349,10 +348,44 @@ int make_map(CUtensorMap *m, const void *ptr, int64_t inner, int64_t outer, int6
   return 0;
 }
 
+// Encoded tensor maps are memoised per thread: step loops (the sampler issues the same three products 300 times)
+// would otherwise pay the driver's encode call on every launch.  A map only depends on address, shape and box.
+struct MapKey {
+  const void *ptr; int64_t d0, d1, d2, d3, s0, s1, s2; int b0, b1, b2, b3, rank, elem, sw;
+  bool operator==(const MapKey &o) const {
+    return ptr == o.ptr && d0 == o.d0 && d1 == o.d1 && d2 == o.d2 && d3 == o.d3 && s0 == o.s0 && s1 == o.s1 && s2 == o.s2 &&
+           b0 == o.b0 && b1 == o.b1 && b2 == o.b2 && b3 == o.b3 && rank == o.rank && elem == o.elem && sw == o.sw;
+  }
+};
+struct MapSlot { bool used = false; MapKey key; CUtensorMap map; };
+constexpr int MAP_SLOTS = 128;
+MapSlot *map_slot(const MapKey &k) {
+  static thread_local MapSlot slots[MAP_SLOTS];
+  uint64_t hsh = reinterpret_cast<uintptr_t>(k.ptr) * 0x9E3779B97F4A7C15ull;
+  hsh ^= (uint64_t)k.d0 * 0xC2B2AE3D27D4EB4Full + (uint64_t)k.d1 * 0x165667B19E3779F9ull + (uint64_t)k.b1 * 31 + (uint64_t)k.b0 + (uint64_t)k.s0 * 7;
+  return &slots[(hsh >> 32) % MAP_SLOTS];
+}
+
+// 2-D bf16 tensor map: `inner` contiguous elements per row, `outer` rows of `ld` elements.
+int make_map(CUtensorMap *m, const void *ptr, int64_t inner, int64_t outer, int64_t ld, int box_inner, int box_outer) {
+  const MapKey key{ptr, inner, outer, 0, 0, ld, 0, 0, box_inner, box_outer, 0, 0, 2, 2, 1};
+  MapSlot *slot = map_slot(key);
+  if (slot->used && slot->key == key) { *m = slot->map; return 0; }
+  SK_TRY(make_map_uncached(m, ptr, inner, outer, ld, box_inner, box_outer));
+  slot->used = true; slot->key = key; slot->map = *m;
+  return 0;
+}
+
 }  // namespace
 
 int sk_make_tmap(CUtensorMap *m, int elem_bytes, const void *ptr, int rank, const uint64_t *dims,
                  const uint64_t *strides_bytes, const uint32_t *box, bool swizzle128) {
+  SK_CHECK(rank >= 2 && rank <= 5, "tensor map rank %d unsupported", rank);
+  MapKey key{ptr, (int64_t)dims[0], (int64_t)dims[1], rank > 2 ? (int64_t)dims[2] : 0, rank > 3 ? (int64_t)dims[3] : 0,
+             (int64_t)strides_bytes[0], rank > 2 ? (int64_t)strides_bytes[1] : 0, rank > 3 ? (int64_t)strides_bytes[2] : 0,
+             (int)box[0], (int)box[1], rank > 2 ? (int)box[2] : 0, rank > 3 ? (int)box[3] : 0, rank, elem_bytes, swizzle128 ? 1 : 0};
+  MapSlot *slot = rank <= 4 ? map_slot(key) : nullptr;
+  if (slot && slot->used && slot->key == key) { *m = slot->map; return 0; }
   EncodeTiledFn enc = get_encode();
   SK_CHECK(enc != nullptr, "cuTensorMapEncodeTiled is not available from the driver");
   cuuint64_t gdim[5], gstr[4];
@@ -365,6 +398,7 @@ int sk_make_tmap(CUtensorMap *m, int elem_bytes, const void *ptr, int rank, cons
                    swizzle128 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   SK_CHECK(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled(rank %d) failed with %d", rank, (int)r);
+  if (slot) { slot->used = true; slot->key = key; slot->map = *m; }
   return 0;
 }
 

@@ -44,24 +44,41 @@ __global__ void samp_pack_kernel(const float *__restrict__ mat, int I, int H, in
 
 // gates (bias already added by the GEMM) -> c, h.  The layer output always goes on (next layer / head); the
 // state (c and the h slot of this layer's operand) only advances when the step's input had no eoc.
+// One thread = 4 consecutive units of one sketch (H % 8 == 0): 128-bit loads of the gate rows, 64-bit bf16 stores.
+__device__ __forceinline__ float fast_sigmoid(float x) { return 1.0f / (1.0f + __expf(-x)); }
+__device__ __forceinline__ float fast_tanh(float x) {
+  float y;
+  asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
 __global__ void samp_cell_kernel(const float *__restrict__ gates, float *__restrict__ cst, __nv_bfloat16 *__restrict__ xh_self,
                                  int k_self, int h_off, __nv_bfloat16 *__restrict__ out, int k_out, const float *__restrict__ xin,
                                  int n, int H) {
-  const int64_t total = (int64_t)n * H;
+  const int H4 = H >> 2;
+  const int64_t total = (int64_t)n * H4;
   for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
-    const int r = (int)(i / H), u = (int)(i % H);
-    const float *g = gates + (size_t)r * 4 * H;
-    const float ig = 1.0f / (1.0f + __expf(-g[u]));
-    const float jg = tanhf(g[H + u]);
-    const float fg = 1.0f / (1.0f + __expf(-(g[2 * H + u] + 1.0f)));
-    const float og = 1.0f / (1.0f + __expf(-g[3 * H + u]));
-    const float c2 = cst[i] * fg + ig * jg;
-    const float h2 = tanhf(c2) * og;
-    const __nv_bfloat16 hb = __float2bfloat16_rn(h2);
-    out[(size_t)r * k_out + u] = hb;
-    if (!(xin[r * 5 + 3] > 0.f)) {
-      cst[i] = c2;
-      xh_self[(size_t)r * k_self + h_off + u] = hb;
+    const int r = (int)(i / H4), u = (int)(i % H4) * 4;
+    const float *g = gates + (size_t)r * 4 * H + u;
+    const float4 gi = *reinterpret_cast<const float4 *>(g), gj = *reinterpret_cast<const float4 *>(g + H);
+    const float4 gf = *reinterpret_cast<const float4 *>(g + 2 * H), go = *reinterpret_cast<const float4 *>(g + 3 * H);
+    float4 c = *reinterpret_cast<const float4 *>(cst + (size_t)r * H + u);
+    const bool hold = xin[r * 5 + 3] > 0.f;
+    float h2[4];
+    const float ci[4] = {c.x, c.y, c.z, c.w};
+    const float vi[4] = {gi.x, gi.y, gi.z, gi.w}, vj[4] = {gj.x, gj.y, gj.z, gj.w};
+    const float vf[4] = {gf.x, gf.y, gf.z, gf.w}, vo[4] = {go.x, go.y, go.z, go.w};
+    float c2[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      c2[k] = ci[k] * fast_sigmoid(vf[k] + 1.0f) + fast_sigmoid(vi[k]) * fast_tanh(vj[k]);
+      h2[k] = fast_tanh(c2[k]) * fast_sigmoid(vo[k]);
+    }
+    const __nv_bfloat162 h01 = __floats2bfloat162_rn(h2[0], h2[1]), h23 = __floats2bfloat162_rn(h2[2], h2[3]);
+    const uint2 hb = make_uint2(*reinterpret_cast<const uint32_t *>(&h01), *reinterpret_cast<const uint32_t *>(&h23));
+    *reinterpret_cast<uint2 *>(out + (size_t)r * k_out + u) = hb;
+    if (!hold) {
+      *reinterpret_cast<float4 *>(cst + (size_t)r * H + u) = make_float4(c2[0], c2[1], c2[2], c2[3]);
+      *reinterpret_cast<uint2 *>(xh_self + (size_t)r * k_self + h_off + u) = hb;
     }
   }
 }
@@ -209,7 +226,7 @@ int sk_sample_tc(skrnn_handle *h, cudaStream_t st, int n, int steps, float temp_
     samp_pack_kernel<<<4 * h->num_sms, 256, 0, st>>>(h->params + h->lp[l].w[0], h->lp[l].I, H, K[l], b.wsm[l]);
     SK_CUDA(cudaGetLastError());
   }
-  const int eblocks = (int)std::min<int64_t>(((int64_t)n * H + 255) / 256, (int64_t)8 * h->num_sms);
+  const int eblocks = (int)std::min<int64_t>(((int64_t)n * (H / 4) + 255) / 256, (int64_t)8 * h->num_sms);
   for (int step = 0; step < steps; ++step) {
     for (int l = 0; l < L; ++l) {
       SK_TRY(sk_gemm_tc(h, st, n, G, K[l], b.xh[l], K[l], true, b.wsm[l], G, false, b.gates, G, h->params + h->lp[l].b[0], false));
