@@ -432,7 +432,7 @@ lstm_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_h, const __grid_consta
 // barrier.cluster in the loop: an extra warp waits for the CTA's elementwise pass of a half (mbarrier), makes
 // its h stores visible (fence) and arrives on the `ready` mbarrier of every rank through the cluster's shared
 // memory window; a rank's TMA producer issues its share of the next multicast h tile of that half once all
-// ranks have arrived.  Requires the multicast path with the weights in tensor memory (N >= 64, CS = 2*nkb).
+// ranks have arrived.  Requires the multicast path with the weights in tensor memory (N >= 32, CS = 2*nkb).
 constexpr int TCR_PP_THREADS = TCR_THREADS + 32;  // + warp 18: publisher
 
 __device__ __forceinline__ void mbar_wait_cluster(uint32_t bar, uint32_t parity) {
@@ -1349,8 +1349,15 @@ lstm_bwd_pp_kernel(const __grid_constant__ CUtensorMap tm_acts, const __grid_con
               const float2 f1 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162 *>(&v[j].y));
               dhc[s][0] += f0.x; dhc[s][1] += f0.y; dhc[s][2] += f1.x; dhc[s][3] += f1.y;
             }
+          } else if constexpr (NCH == 1) {
+            unsigned short v[UR];
+#pragma unroll
+            for (int j = 0; j < UR; ++j)
+              v[j] = (r0 + j < CS) ? __ldcg(reinterpret_cast<const unsigned short *>(src0 + (size_t)(r0 + j) * 4 * part_blk)) : (unsigned short)0;
+#pragma unroll
+            for (int j = 0; j < UR; ++j) dhc[s][0] += __bfloat162float(__ushort_as_bfloat16(v[j]));
           } else {
-            static_assert(NCH == 2 || NCH == 4, "half tiles of 32 or 64 columns");
+            static_assert(NCH == 2, "half tiles of 16, 32 or 64 columns");
             uint32_t v[UR];
 #pragma unroll
             for (int j = 0; j < UR; ++j)
@@ -1533,6 +1540,15 @@ int sk_rnn_tc_layer(skrnn_handle *h, cudaStream_t st, bool bwd, int l, int B, in
     if ((B + cand - 1) / cand <= cap_clusters) break;
   }
   if (N == 0) return -1;
+  // The two-half-tile kernels need N >= 32 (two MMA tiles of 16 columns): latency-bound small batches prefer two
+  // halves of 16 rows in flight on fewer clusters over one 16-row tile per cluster.
+  static int pp_env = -1, ppb_env = -1;
+  if (pp_env < 0) { const char *e = getenv("SKRNN_TC_PP"); pp_env = (e && e[0] == '0') ? 0 : 1; }
+  if (ppb_env < 0) { const char *e = getenv("SKRNN_TC_PP_BWD"); ppb_env = (e && e[0] == '0') ? 0 : 1; }
+  const bool mcast_ok = CS >= 2 && CS == 2 * nkb;
+  // (measured at H=512, B=100: forward 6.8 K cycles/step with 7 clusters x 16 rows vs 4.6 K with 4 clusters x 2x16;
+  // the backward pass is faster the other way round, 5.2 K vs 8.7 K, so only the forward tile is widened)
+  if (N == 16 && B > 16 && !bwd && pp_env != 0 && mcast_ok && a_tmem) N = 32;
   const int nclusters = (B + N - 1) / N;
   const size_t smem = smem_need(bwd, H, N, a_tmem);
   const int img_bytes = bwd ? 2 * HP * 128 : nkb * 16384;
@@ -1593,10 +1609,8 @@ int sk_rnn_tc_layer(skrnn_handle *h, cudaStream_t st, bool bwd, int l, int B, in
     uint64_t str[2] = {(uint64_t)H * 2, (uint64_t)B * H * 2};
     static int mc_env = -1;
     if (mc_env < 0) { const char *e = getenv("SKRNN_TC_MCAST"); mc_env = (e && e[0] == '0') ? 0 : 1; }
-    a.mcast = (mc_env && N >= 64 && CS >= 2 && CS == 2 * nkb) ? 1 : 0;
-    static int pp_env = -1;
-    if (pp_env < 0) { const char *e = getenv("SKRNN_TC_PP"); pp_env = (e && e[0] == '0') ? 0 : 1; }
-    const bool pp = pp_env && a.mcast && a_tmem && N >= 64;  // two half tiles in flight (lstm_fwd_pp_kernel)
+    const bool pp = pp_env && mc_env && mcast_ok && a_tmem && N >= 32;  // two half tiles in flight (lstm_fwd_pp_kernel)
+    a.mcast = (mc_env && mcast_ok && (N >= 64 || pp)) ? 1 : 0;
     uint32_t box[3] = {64, (uint32_t)(pp ? N / 4 : (a.mcast ? N / 2 : N)), 1};
     SK_TRY(sk_make_tmap(&tm_h, 2, h->ws.hprev_bf[l], 3, dims, str, box));
     if (pp) {
@@ -1610,7 +1624,8 @@ int sk_rnn_tc_layer(skrnn_handle *h, cudaStream_t st, bool bwd, int l, int B, in
       CUtensorMap tm_hst;
       SK_TRY(sk_make_tmap(&tm_hst, 2, h->ws.hprev_bf[l], 3, dims, str, sbox, false));
       SkLaunch scope(h, st, SK_CAT_RNN_FWD);
-      if (N == 64) rc = launch_fwd_pp<2>(tm_h, tm_xw, tm_hst, a, nclusters, smem, st);
+      if (N == 32) rc = launch_fwd_pp<1>(tm_h, tm_xw, tm_hst, a, nclusters, smem, st);
+      else if (N == 64) rc = launch_fwd_pp<2>(tm_h, tm_xw, tm_hst, a, nclusters, smem, st);
       else rc = launch_fwd_pp<4>(tm_h, tm_xw, tm_hst, a, nclusters, smem, st);
       if (rc != 0) {
         fprintf(stderr, "libskrnn: lstm_fwd_pp_kernel launch failed (%s)\n", skrnn_last_error());
@@ -1644,9 +1659,7 @@ int sk_rnn_tc_layer(skrnn_handle *h, cudaStream_t st, bool bwd, int l, int B, in
       SK_TRY(sk_make_tmap(&tm_do, 4, h->ws.dout, 3, dims, str, box));
       SK_TRY(sk_make_tmap(&tm_cp, 4, h->ws.cprev[l], 3, dims, str, box));
     }
-    static int ppb_env = -1;
-    if (ppb_env < 0) { const char *e = getenv("SKRNN_TC_PP_BWD"); ppb_env = (e && e[0] == '0') ? 0 : 1; }
-    if (ppb_env && N >= 64) {  // two half tiles in flight (lstm_bwd_pp_kernel): boxes of N/2 rows
+    if (ppb_env && N >= 32) {  // two half tiles in flight (lstm_bwd_pp_kernel): boxes of N/2 rows
       uint64_t adims[3] = {(uint64_t)h->G, (uint64_t)B, (uint64_t)T};
       uint64_t astr[2] = {(uint64_t)h->G * 2, (uint64_t)B * h->G * 2};
       uint32_t abox[3] = {128, (uint32_t)(N / 2), 1};
@@ -1658,7 +1671,8 @@ int sk_rnn_tc_layer(skrnn_handle *h, cudaStream_t st, bool bwd, int l, int B, in
       SK_TRY(sk_make_tmap(&tm_do, 4, h->ws.dout, 3, dims, str, box));
       SK_TRY(sk_make_tmap(&tm_cp, 4, h->ws.cprev[l], 3, dims, str, box));
       SkLaunch scope(h, st, SK_CAT_RNN_BWD);
-      if (N == 64) rc = launch_bwd_pp<2>(tm_act2, tm_do, tm_cp, a, nclusters, smem, st);
+      if (N == 32) rc = launch_bwd_pp<1>(tm_act2, tm_do, tm_cp, a, nclusters, smem, st);
+      else if (N == 64) rc = launch_bwd_pp<2>(tm_act2, tm_do, tm_cp, a, nclusters, smem, st);
       else rc = launch_bwd_pp<4>(tm_act2, tm_do, tm_cp, a, nclusters, smem, st);
       if (rc != 0) return 1;
       return 0;
