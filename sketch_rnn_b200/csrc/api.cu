@@ -318,6 +318,7 @@ void skrnn_destroy(skrnn_handle *h) {
   cudaFree(h->st_state);
   cudaFree(h->st_loss);
   cudaFree(h->samp_state);
+  if (h->samp_graph) cudaGraphExecDestroy(h->samp_graph);
   cudaFree(h->samp_tc);
   cudaFree(h->params_bf);
   cudaFree(h->cast_seg_dev);

@@ -108,6 +108,8 @@ struct skrnn_handle {
   int64_t samp_state_n = 0;
   void *samp_tc = nullptr;      // throughput sampler buffers (sampler_tc.cu)
   size_t samp_tc_bytes = 0;
+  cudaGraphExec_t samp_graph = nullptr;  // captured step loop of the throughput sampler for (samp_graph_n, samp_graph_steps)
+  int samp_graph_n = 0, samp_graph_steps = 0;
   int num_sms = 0;
   int64_t launches = 0;
   int cluster_size = 1;
@@ -153,6 +155,9 @@ int sk_gemm_f32(skrnn_handle *h, cudaStream_t st, int M, int N, int K, const flo
 // bf16 tensor-core GEMM (gemm_tc.cu): operands bf16, K-major (K contiguous) or MN-major.
 int sk_gemm_tc(skrnn_handle *h, cudaStream_t st, int M, int N, int K, const void *A, int lda, bool a_kmajor,
                const void *B, int ldb, bool b_kmajor, float *C, int ldc, const float *bias, bool accumulate);
+int sk_gemm_tc_lstm_cell(skrnn_handle *h, cudaStream_t st, int M, int H, int K, const void *A, int lda, const void *W,
+                         const float *bias_il, float *cell_c, __nv_bfloat16 *cell_self, int kself, int hoff,
+                         __nv_bfloat16 *cell_out, int kout, const float *xin);
 extern uint32_t g_tc_override[6];
 // Tiled tensor map (rank 2..5), 128B-swizzled unless swizzle128 = false.  elem_bytes: 2 (bf16) or 4 (fp32).
 int sk_make_tmap(CUtensorMap *m, int elem_bytes, const void *ptr, int rank, const uint64_t *dims,

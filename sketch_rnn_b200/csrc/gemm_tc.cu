@@ -34,6 +34,12 @@ struct TcArgs {
   int accumulate;
   int kb_per_split;
   uint32_t lbo_a, sbo_a, adv_a, lbo_b, sbo_b, adv_b;  // descriptor strides / per-UMMA_K advance (bytes)
+  // LSTM-cell epilogue of the persistent kernel (sampler): columns are gate-interleaved (4*unit + gate)
+  float *cell_c;                 // [M, H] cell state, updated in place unless the row holds
+  __nv_bfloat16 *cell_self;      // this layer's operand rows: h slot at column cell_hoff, row pitch cell_kself
+  __nv_bfloat16 *cell_out;       // layer output rows (next layer's operand / head input), row pitch cell_kout
+  const float *cell_xin;         // [M, 5] current input point: column 3 > 0 = eoc = hold the state
+  int cell_kself, cell_hoff, cell_kout, cell_H;
 };
 
 // BN_ = 128: 3 stages, two CTAs per SM.  BN_ = 256: 4 stages, one CTA per SM -- per k-block the tensor core then
@@ -172,8 +178,16 @@ constexpr int P_RING = 2 * BM * 32 * 4;  // two [128 rows][32 cols] fp32 sub-til
 constexpr int p_stages(int bn) { return bn == 128 ? 5 : 4; }
 constexpr int p_smem(int bn) { return p_stages(bn) * (A_BYTES + bn * BK * 2) + P_RING + 1024 /*bias*/ + 1024 /*align*/ + 256; }
 
-template <bool A_KMAJOR, bool B_KMAJOR, int BN_>
-__global__ void __launch_bounds__(TC_THREADS, 1)
+// EPI = 0: C (+ bias) leaves through the TMA-store ring.  EPI = 1: the tile's columns are the gate pre-activations
+// of 64 hidden units (i, j, f, o interleaved per unit) and the epilogue IS the LSTM cell update of the sampler
+// (model.py:82-92 with initial_state = prev_state): nothing but c, h (bf16) and the layer output goes to memory.
+// epilogue warps of the persistent kernel (8 were measured slower than 4 for the cell epilogue: 21.3 vs 19.7 ms per
+// 8192-sketch call, it is bound by the row-strided c / h accesses, not by issue slots)
+constexpr int p_epi_warps(int epi) { return 4; }
+constexpr int p_threads(int epi) { return 64 + 32 * p_epi_warps(epi); }
+
+template <bool A_KMAJOR, bool B_KMAJOR, int BN_, int EPI = 0>
+__global__ void __launch_bounds__(p_threads(EPI), 1)
 gemm_tc_persist_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                        const __grid_constant__ CUtensorMap tmC, TcArgs a) {
   constexpr int BN = BN_;
@@ -199,7 +213,7 @@ gemm_tc_persist_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < P_STAGES; ++s) { mbar_init(bar_full + 8 * s, 1); mbar_init(bar_empty + 8 * s, 1); }
-    for (int b = 0; b < 2; ++b) { mbar_init(bar_tfull + 8 * b, 1); mbar_init(bar_tempty + 8 * b, 4); }
+    for (int b = 0; b < 2; ++b) { mbar_init(bar_tfull + 8 * b, 1); mbar_init(bar_tempty + 8 * b, p_epi_warps(EPI)); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmA)) : "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmB)) : "memory");
@@ -275,11 +289,60 @@ gemm_tc_persist_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
       const int m0 = (tile / ntn) * BM, n0 = (tile % ntn) * BN;
       const int buf = lt & 1;
       // bias slice of this tile (everybody is past the previous tile's last read of it: see the barriers below)
+      if constexpr (EPI == 1) {
+        for (int j = et; j < BN; j += 32 * p_epi_warps(EPI)) bias_gen[j] = (a.bias != nullptr && n0 + j < a.N) ? __ldg(a.bias + n0 + j) : 0.f;
+      } else {
 #pragma unroll
-      for (int j = 0; j < BN / 128; ++j)
-        bias_gen[et + 128 * j] = (a.bias != nullptr && n0 + et + 128 * j < a.N) ? __ldg(a.bias + n0 + et + 128 * j) : 0.f;
+        for (int j = 0; j < BN / 128; ++j)
+          bias_gen[et + 128 * j] = (a.bias != nullptr && n0 + et + 128 * j < a.N) ? __ldg(a.bias + n0 + et + 128 * j) : 0.f;
+      }
       mbar_wait(bar_tfull + 8 * buf, (lt >> 1) & 1);
       tc_fence_after();
+      if constexpr (EPI == 1) {
+        named_bar_sync(1, 32 * p_epi_warps(EPI));  // bias slice visible
+        const int row_g = m0 + r;
+        const bool row_ok = row_g < a.M;
+        const bool hold = row_ok && __ldg(a.cell_xin + (size_t)row_g * 5 + 3) > 0.f;
+        const int Hc = a.cell_H;
+#pragma unroll 1
+        for (int c = (warp - 2) >> 2; c < BN / 32; c += p_epi_warps(EPI) / 4) {  // warps of a lane quarter alternate chunks
+          uint32_t v[32];
+          tc_ld32(tmem_acc + ((uint32_t)(32 * q) << 16) + (uint32_t)(buf * BN + c * 32), v);
+          const int ub = (n0 + c * 32) >> 2;  // first of the 8 units of this chunk
+          if (row_ok && ub < Hc) {
+            float *cp = a.cell_c + (size_t)row_g * Hc + ub;
+            const float4 c0 = *reinterpret_cast<const float4 *>(cp), c1 = *reinterpret_cast<const float4 *>(cp + 4);
+            const float cin[8] = {c0.x, c0.y, c0.z, c0.w, c1.x, c1.y, c1.z, c1.w};
+            float cn[8];
+            uint32_t hb[4];
+#pragma unroll
+            for (int j = 0; j < 8; j += 2) {
+              float hh[2];
+#pragma unroll
+              for (int e = 0; e < 2; ++e) {
+                const int u = j + e;
+                const float4 bv = *reinterpret_cast<const float4 *>(bias_gen + c * 32 + 4 * u);
+                const float ig = sigmoid_approx(__uint_as_float(v[4 * u + 0]) + bv.x);
+                const float jg = tanh_approx(__uint_as_float(v[4 * u + 1]) + bv.y);
+                const float fg = sigmoid_approx(__uint_as_float(v[4 * u + 2]) + bv.z + 1.0f);
+                const float og = sigmoid_approx(__uint_as_float(v[4 * u + 3]) + bv.w);
+                cn[u] = fmaf(cin[u], fg, ig * jg);
+                hh[e] = tanh_approx(cn[u]) * og;
+              }
+              const __nv_bfloat162 hv = __floats2bfloat162_rn(hh[0], hh[1]);
+              hb[j >> 1] = *reinterpret_cast<const uint32_t *>(&hv);
+            }
+            const uint4 hq = make_uint4(hb[0], hb[1], hb[2], hb[3]);
+            *reinterpret_cast<uint4 *>(a.cell_out + (size_t)row_g * a.cell_kout + ub) = hq;
+            if (!hold) {
+              *reinterpret_cast<float4 *>(cp) = make_float4(cn[0], cn[1], cn[2], cn[3]);
+              *reinterpret_cast<float4 *>(cp + 4) = make_float4(cn[4], cn[5], cn[6], cn[7]);
+              *reinterpret_cast<uint4 *>(a.cell_self + (size_t)row_g * a.cell_kself + a.cell_hoff + ub) = hq;
+            }
+          }
+        }
+        named_bar_sync(1, 32 * p_epi_warps(EPI));  // everybody is done with the bias slice before the next tile rewrites it
+      } else {
 #pragma unroll 1
       for (int c = 0; c < BN / 32; ++c) {
         // ring slot c&1: the store issued two chunks ago has finished reading it
@@ -302,6 +365,7 @@ gemm_tc_persist_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
           if (n0 + c * 32 < a.N) tma_store_2d_nocommit(&tmC, s_ring + (c & 1) * 16384, n0 + c * 32, m0);
           tma_store_commit();  // one group per chunk, written or not, so the ring accounting stays uniform
         }
+      }
       }
       tc_fence_before();
       __syncwarp();
@@ -501,3 +565,31 @@ int sk_gemm_tc(skrnn_handle *h, cudaStream_t st, int M, int N, int K, const void
   SK_CUDA(cudaGetLastError());
   return 0;
 }
+
+// gates = A[M,K] * W[K,4H] + b with gate-interleaved columns (4*unit + gate), followed in the same kernel by the
+// LSTM cell update of the sampler (see EPI = 1 above).  A: bf16 K-major rows (pitch lda), W: bf16 [K][4H].
+int sk_gemm_tc_lstm_cell(skrnn_handle *h, cudaStream_t st, int M, int H, int K, const void *A, int lda, const void *W,
+                         const float *bias_il, float *cell_c, __nv_bfloat16 *cell_self, int kself, int hoff,
+                         __nv_bfloat16 *cell_out, int kout, const float *xin) {
+  if (M <= 0) return 0;
+  const int N = 4 * H;
+  SK_CHECK(H % 8 == 0 && kself % 8 == 0 && kout % 8 == 0 && hoff % 8 == 0, "lstm cell epilogue: H and row pitches must be multiples of 8");
+  CUtensorMap tmA, tmB;
+  SK_TRY(make_map(&tmA, A, K, M, lda, BK, BM));
+  SK_TRY(make_map(&tmB, W, N, K, N, 64, BK));
+  TcArgs a = {};
+  a.M = M; a.N = N; a.K = K; a.C = nullptr; a.ldc = 0; a.bias = bias_il; a.accumulate = 0;
+  a.lbo_a = 0; a.sbo_a = 1024; a.adv_a = 32;
+  a.lbo_b = 8192; a.sbo_b = 1024; a.adv_b = 2048;
+  a.kb_per_split = (K + BK - 1) / BK;
+  a.cell_c = cell_c; a.cell_self = cell_self; a.cell_out = cell_out; a.cell_xin = xin;
+  a.cell_kself = kself; a.cell_hoff = hoff; a.cell_kout = kout; a.cell_H = H;
+  const int tiles = ((N + 255) / 256) * ((M + BM - 1) / BM);
+  const int grid = std::min(tiles, h->num_sms);
+  SkLaunch scope(h, st, SK_CAT_TC_GEMM);
+  SK_CUDA(cudaFuncSetAttribute(gemm_tc_persist_kernel<true, false, 256, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, p_smem(256)));
+  gemm_tc_persist_kernel<true, false, 256, 1><<<grid, p_threads(1), p_smem(256), st>>>(tmA, tmB, tmA, a);
+  SK_CUDA(cudaGetLastError());
+  return 0;
+}
+

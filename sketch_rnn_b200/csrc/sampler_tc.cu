@@ -2,10 +2,11 @@
 // (reference Model.sample, model.py:187-264, batched over sketches; BASELINE config 5).
 //
 // With thousands of sketches in flight one sampling step is three real GEMMs
-//   gates_l [n, 4H] = [input_l | h_l] [n, K_l] * W_l [K_l, 4H] + b_l      (l = 0..L-1,  tcgen05 gemm_tc_kernel)
+//   gates_l [n, 4H] = [input_l | h_l] [n, K_l] * W_l [K_l, 4H] + b_l      (l = 0..L-1)
 //   logits  [n, NOUT] = h_top [n, H] * output_w + output_b
-// separated by two small fused kernels: the LSTM cell update with the eoc state hold (model.py:82-92 with
-// initial_state = prev_state, model.py:215) and the per-sketch draw (softmax, temperature from the third
+// The gate GEMMs run the LSTM cell update with the eoc state hold (model.py:82-92 with initial_state = prev_state,
+// model.py:215) as their epilogue (gemm_tc_persist_kernel<.,.,256,1>: gate-interleaved weight columns, so the
+// pre-activations never leave the SM); the logits GEMM is followed by the per-sketch draw (softmax, temperature from the third
 // point on, inverse-CDF categorical draws, Box-Muller bivariate normal, feedback of the sampled point as
 // the next input -- model.py:219-261, same quirks as the exact kernel in sampler.cu).  Everything stays on
 // the device for all steps; the host only enqueues launches.
@@ -13,6 +14,8 @@
 // This path trades the bit-exact contract of sampler.cu for throughput: operands are rounded to bf16, so
 // it is selected only for bf16-precision handles, LSTM cells and n >= 64 sketches; everything else runs the
 // exact fp32 persistent kernel.
+#include <stdlib.h>
+
 #include "common.cuh"
 #include "skrnn_math.h"
 
@@ -23,63 +26,27 @@ struct SampBuf {
   __nv_bfloat16 *wsm[SK_MAX_LAYERS]; // [K_l, 4H] weights in the same row order
   __nv_bfloat16 *htop;               // [n, H] output of the top layer
   float *cst[SK_MAX_LAYERS];         // [n, H] cell state
-  float *gates;                      // [n, 4H]
+  float *bias_il[SK_MAX_LAYERS];     // [4H] bias in the interleaved column order
   float *logits;                     // [n, NOUT]
   float *xin;                        // [n, 5] current input point (fp32)
   int *done;                         // [n]
 };
 
-// W rows: layer 0: 5 x rows, 3 zero rows, H h rows; deeper layers: the TF matrix as it is
-__global__ void samp_pack_kernel(const float *__restrict__ mat, int I, int H, int Kp, __nv_bfloat16 *__restrict__ dst) {
+// W rows: layer 0: 5 x rows, 3 zero rows, H h rows; deeper layers: the TF matrix as it is.  Columns are
+// gate-interleaved (4*unit + gate instead of TF's gate*H + unit) so that a GEMM tile holds whole units and the cell
+// update can be its epilogue; the bias gets the same order.
+__global__ void samp_pack_kernel(const float *__restrict__ mat, const float *__restrict__ bias, int I, int H, int Kp,
+                                 __nv_bfloat16 *__restrict__ dst, float *__restrict__ bias_il) {
   const int64_t total = (int64_t)Kp * 4 * H;
   const int pad = Kp - (I + H);
   for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
-    const int k = (int)(i / (4 * H)), c = (int)(i % (4 * H));
+    const int k = (int)(i / (4 * H)), ci = (int)(i % (4 * H));
+    const int c = (ci & 3) * H + (ci >> 2);  // TF column of interleaved column ci
     float v = 0.f;
     if (k < I) v = mat[(size_t)k * 4 * H + c];
     else if (k >= I + pad) v = mat[(size_t)(k - pad) * 4 * H + c];
     dst[i] = __float2bfloat16_rn(v);
-  }
-}
-
-// gates (bias already added by the GEMM) -> c, h.  The layer output always goes on (next layer / head); the
-// state (c and the h slot of this layer's operand) only advances when the step's input had no eoc.
-// One thread = 4 consecutive units of one sketch (H % 8 == 0): 128-bit loads of the gate rows, 64-bit bf16 stores.
-__device__ __forceinline__ float fast_sigmoid(float x) { return 1.0f / (1.0f + __expf(-x)); }
-__device__ __forceinline__ float fast_tanh(float x) {
-  float y;
-  asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
-  return y;
-}
-__global__ void samp_cell_kernel(const float *__restrict__ gates, float *__restrict__ cst, __nv_bfloat16 *__restrict__ xh_self,
-                                 int k_self, int h_off, __nv_bfloat16 *__restrict__ out, int k_out, const float *__restrict__ xin,
-                                 int n, int H) {
-  const int H4 = H >> 2;
-  const int64_t total = (int64_t)n * H4;
-  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
-    const int r = (int)(i / H4), u = (int)(i % H4) * 4;
-    const float *g = gates + (size_t)r * 4 * H + u;
-    const float4 gi = *reinterpret_cast<const float4 *>(g), gj = *reinterpret_cast<const float4 *>(g + H);
-    const float4 gf = *reinterpret_cast<const float4 *>(g + 2 * H), go = *reinterpret_cast<const float4 *>(g + 3 * H);
-    float4 c = *reinterpret_cast<const float4 *>(cst + (size_t)r * H + u);
-    const bool hold = xin[r * 5 + 3] > 0.f;
-    float h2[4];
-    const float ci[4] = {c.x, c.y, c.z, c.w};
-    const float vi[4] = {gi.x, gi.y, gi.z, gi.w}, vj[4] = {gj.x, gj.y, gj.z, gj.w};
-    const float vf[4] = {gf.x, gf.y, gf.z, gf.w}, vo[4] = {go.x, go.y, go.z, go.w};
-    float c2[4];
-#pragma unroll
-    for (int k = 0; k < 4; ++k) {
-      c2[k] = ci[k] * fast_sigmoid(vf[k] + 1.0f) + fast_sigmoid(vi[k]) * fast_tanh(vj[k]);
-      h2[k] = fast_tanh(c2[k]) * fast_sigmoid(vo[k]);
-    }
-    const __nv_bfloat162 h01 = __floats2bfloat162_rn(h2[0], h2[1]), h23 = __floats2bfloat162_rn(h2[2], h2[3]);
-    const uint2 hb = make_uint2(*reinterpret_cast<const uint32_t *>(&h01), *reinterpret_cast<const uint32_t *>(&h23));
-    *reinterpret_cast<uint2 *>(out + (size_t)r * k_out + u) = hb;
-    if (!hold) {
-      *reinterpret_cast<float4 *>(cst + (size_t)r * H + u) = make_float4(c2[0], c2[1], c2[2], c2[3]);
-      *reinterpret_cast<uint2 *>(xh_self + (size_t)r * k_self + h_off + u) = hb;
-    }
+    if (k == 0) bias_il[ci] = bias[c];
   }
 }
 
@@ -94,12 +61,28 @@ __device__ __forceinline__ float warp_sum_f(float v) {
   return v;
 }
 
+// Everything that changes from one skrnn_sample call to the next lives in this device-side record, so the captured
+// launch sequence of a call (a CUDA graph of steps*(L+2) kernels) can be replayed by later calls.
+struct SampCall {
+  const float *uniforms;
+  float *strokes;
+  int *lengths;
+  float *mixp;
+  uint64_t seed;
+  int sketch0, stop_if_eoc;
+  float temp_mix, temp_pen;
+};
+
 // One warp per sketch; lanes over mixture components (M <= 32 on this path).
-__global__ void samp_draw_kernel(const float *__restrict__ logits, int n, int M, int NOUT, int step, int steps,
-                                 float temp_mix, int stop_if_eoc, float data_scale, const float *__restrict__ uniforms,
-                                 uint64_t seed, int sketch0, float *__restrict__ xin, __nv_bfloat16 *__restrict__ xh0, int k0,
-                                 float *__restrict__ strokes, int *__restrict__ lengths, int *__restrict__ done,
-                                 float *__restrict__ mixp, float temp_pen) {
+__global__ void samp_draw_kernel(const float *__restrict__ logits, int n, int M, int NOUT, int step, int steps, float data_scale,
+                                 const SampCall *__restrict__ call, float *__restrict__ xin, __nv_bfloat16 *__restrict__ xh0,
+                                 int k0, int *__restrict__ done) {
+  const float *uniforms = call->uniforms;
+  float *strokes = call->strokes, *mixp = call->mixp;
+  int *lengths = call->lengths;
+  const uint64_t seed = call->seed;
+  const int sketch0 = call->sketch0, stop_if_eoc = call->stop_if_eoc;
+  const float temp_mix = call->temp_mix, temp_pen = call->temp_pen;
   const int lane = threadIdx.x & 31;
   const int sk = (int)((blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5);
   if (sk >= n) return;
@@ -185,17 +168,19 @@ int sk_sample_tc(skrnn_handle *h, cudaStream_t st, int n, int steps, float temp_
   // one allocation for all buffers, kept on the handle
   size_t off = 0;
   auto take = [&](size_t bytes) { size_t o = off; off += (bytes + 255) / 256 * 256; return o; };
-  size_t o_xh[SK_MAX_LAYERS], o_w[SK_MAX_LAYERS], o_c[SK_MAX_LAYERS];
+  size_t o_xh[SK_MAX_LAYERS], o_w[SK_MAX_LAYERS], o_c[SK_MAX_LAYERS], o_b[SK_MAX_LAYERS];
   int K[SK_MAX_LAYERS];
   for (int l = 0; l < L; ++l) {
     K[l] = (l == 0) ? 8 + H : 2 * H;
     o_xh[l] = take((size_t)n * K[l] * 2);
     o_w[l] = take((size_t)K[l] * G * 2);
     o_c[l] = take((size_t)n * H * 4);
+    o_b[l] = take((size_t)G * 4);
   }
-  const size_t o_top = take((size_t)n * H * 2), o_g = take((size_t)n * G * 4), o_lg = take((size_t)n * NOUT * 4);
-  const size_t o_xin = take((size_t)n * 5 * 4), o_done = take((size_t)n * 4);
+  const size_t o_top = take((size_t)n * H * 2), o_lg = take((size_t)n * NOUT * 4);
+  const size_t o_xin = take((size_t)n * 5 * 4), o_done = take((size_t)n * 4), o_call = take(sizeof(SampCall));
   if (off > h->samp_tc_bytes) {
+    if (h->samp_graph) { cudaGraphExecDestroy(h->samp_graph); h->samp_graph = nullptr; }
     SK_CUDA(cudaStreamSynchronize(st));
     cudaFree(h->samp_tc);
     h->samp_tc = nullptr;
@@ -209,9 +194,9 @@ int sk_sample_tc(skrnn_handle *h, cudaStream_t st, int n, int steps, float temp_
     b.xh[l] = reinterpret_cast<__nv_bfloat16 *>(base + o_xh[l]);
     b.wsm[l] = reinterpret_cast<__nv_bfloat16 *>(base + o_w[l]);
     b.cst[l] = reinterpret_cast<float *>(base + o_c[l]);
+    b.bias_il[l] = reinterpret_cast<float *>(base + o_b[l]);
   }
   b.htop = reinterpret_cast<__nv_bfloat16 *>(base + o_top);
-  b.gates = reinterpret_cast<float *>(base + o_g);
   b.logits = reinterpret_cast<float *>(base + o_lg);
   b.xin = reinterpret_cast<float *>(base + o_xin);
   b.done = reinterpret_cast<int *>(base + o_done);
@@ -220,29 +205,66 @@ int sk_sample_tc(skrnn_handle *h, cudaStream_t st, int n, int steps, float temp_
   SK_CUDA(cudaMemsetAsync(strokes, 0, (size_t)n * steps * 5 * sizeof(float), st));
   SK_CUDA(cudaMemsetAsync(lengths, 0, (size_t)n * sizeof(int), st));
   if (mixp) SK_CUDA(cudaMemsetAsync(mixp, 0, (size_t)n * steps * NOUT * sizeof(float), st));
+  SampCall *call_dev = reinterpret_cast<SampCall *>(base + o_call);
+  {
+    SampCall c;
+    c.uniforms = uniforms; c.strokes = strokes; c.lengths = lengths; c.mixp = mixp; c.seed = seed; c.sketch0 = sketch0;
+    c.stop_if_eoc = stop_if_eoc; c.temp_mix = temp_mix; c.temp_pen = temp_pen;
+    SK_CUDA(cudaMemcpyAsync(call_dev, &c, sizeof(c), cudaMemcpyHostToDevice, st));  // pageable source: staged before return
+  }
   SK_TRY(sk_cast_params(h, st));
   for (int l = 0; l < L; ++l) {
     SkLaunch scope(h, st, SK_CAT_SAMPLER);
-    samp_pack_kernel<<<4 * h->num_sms, 256, 0, st>>>(h->params + h->lp[l].w[0], h->lp[l].I, H, K[l], b.wsm[l]);
+    samp_pack_kernel<<<4 * h->num_sms, 256, 0, st>>>(h->params + h->lp[l].w[0], h->params + h->lp[l].b[0], h->lp[l].I, H, K[l],
+                                                     b.wsm[l], b.bias_il[l]);
     SK_CUDA(cudaGetLastError());
   }
-  const int eblocks = (int)std::min<int64_t>(((int64_t)n * (H / 4) + 255) / 256, (int64_t)8 * h->num_sms);
-  for (int step = 0; step < steps; ++step) {
-    for (int l = 0; l < L; ++l) {
-      SK_TRY(sk_gemm_tc(h, st, n, G, K[l], b.xh[l], K[l], true, b.wsm[l], G, false, b.gates, G, h->params + h->lp[l].b[0], false));
-      __nv_bfloat16 *out = (l + 1 < L) ? b.xh[l + 1] : b.htop;
-      const int k_out = (l + 1 < L) ? K[l + 1] : H;
-      SkLaunch scope(h, st, SK_CAT_SAMPLER);
-      samp_cell_kernel<<<eblocks, 256, 0, st>>>(b.gates, b.cst[l], b.xh[l], K[l], K[l] - H, out, k_out, b.xin, n, H);
+  auto enqueue_steps = [&](cudaStream_t s2) -> int {
+    for (int step = 0; step < steps; ++step) {
+      for (int l = 0; l < L; ++l) {
+        // gates GEMM with the cell update as its epilogue: only c, h and the layer output touch memory
+        __nv_bfloat16 *out = (l + 1 < L) ? b.xh[l + 1] : b.htop;
+        const int k_out = (l + 1 < L) ? K[l + 1] : H;
+        SK_TRY(sk_gemm_tc_lstm_cell(h, s2, n, H, K[l], b.xh[l], K[l], b.wsm[l], b.bias_il[l], b.cst[l], b.xh[l], K[l], K[l] - H,
+                                    out, k_out, b.xin));
+      }
+      SK_TRY(sk_gemm_tc(h, s2, n, NOUT, H, b.htop, H, true, h->params_bf + h->pbf_out_w, h->NOUTP, false, b.logits, NOUT,
+                        h->params + h->off_out_b, false));
+      SkLaunch scope(h, s2, SK_CAT_SAMPLER);
+      samp_draw_kernel<<<(n * 32 + 255) / 256, 256, 0, s2>>>(b.logits, n, h->M, NOUT, step, steps, h->cfg.data_scale, call_dev,
+                                                            b.xin, b.xh[0], K[0], b.done);
       SK_CUDA(cudaGetLastError());
     }
-    SK_TRY(sk_gemm_tc(h, st, n, NOUT, H, b.htop, H, true, h->params_bf + h->pbf_out_w, h->NOUTP, false, b.logits, NOUT,
-                      h->params + h->off_out_b, false));
-    SkLaunch scope(h, st, SK_CAT_SAMPLER);
-    samp_draw_kernel<<<(n * 32 + 255) / 256, 256, 0, st>>>(b.logits, n, h->M, NOUT, step, steps, temp_mix, stop_if_eoc,
-                                                          h->cfg.data_scale, uniforms, seed, sketch0, b.xin, b.xh[0], K[0],
-                                                          strokes, lengths, b.done, mixp, temp_pen);
-    SK_CUDA(cudaGetLastError());
+    return 0;
+  };
+  // The step loop is launch-latency bound for small n: it is captured once per (n, steps) into a CUDA graph (on the
+  // handle's side stream) and replayed; per-category profiling needs the individual launches.
+  static int graph_env = -1;
+  if (graph_env < 0) { const char *e = getenv("SKRNN_SAMPLER_GRAPH"); graph_env = (e && e[0] == '0') ? 0 : 1; }
+  if (!graph_env || h->prof_on) return enqueue_steps(st);
+  if (h->samp_graph == nullptr || h->samp_graph_n != n || h->samp_graph_steps != steps) {
+    if (h->samp_graph) { cudaGraphExecDestroy(h->samp_graph); h->samp_graph = nullptr; }
+    SK_CUDA(cudaStreamBeginCapture(h->side, cudaStreamCaptureModeThreadLocal));
+    const int rc = enqueue_steps(h->side);
+    cudaGraph_t graph = nullptr;
+    const cudaError_t ce = cudaStreamEndCapture(h->side, &graph);
+    if (rc != 0 || ce != cudaSuccess || graph == nullptr) {
+      if (graph) cudaGraphDestroy(graph);
+      cudaGetLastError();
+      if (rc != 0) return rc;
+      return enqueue_steps(st);  // capture not possible here: plain launches
+    }
+    const cudaError_t ie = cudaGraphInstantiate(&h->samp_graph, graph, 0);
+    cudaGraphDestroy(graph);
+    if (ie != cudaSuccess) {
+      h->samp_graph = nullptr;
+      cudaGetLastError();
+      return enqueue_steps(st);
+    }
+    h->samp_graph_n = n; h->samp_graph_steps = steps;
+  } else {
+    h->launches += (int64_t)steps * (L + 2);  // the replayed kernels
   }
+  SK_CUDA(cudaGraphLaunch(h->samp_graph, st));
   return 0;
 }
