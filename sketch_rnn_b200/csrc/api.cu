@@ -82,7 +82,8 @@ void free_workspace(SkWorkspace &w) {
     cudaFree(w.hprev_bf[l]);
     cudaFree(w.aux_bf[l]);
     cudaFree(w.acts_bf[l]);
-    w.out_bf[l] = w.hprev_bf[l] = w.aux_bf[l] = w.acts_bf[l] = nullptr;
+    cudaFree(w.xw_il[l]);
+    w.out_bf[l] = w.hprev_bf[l] = w.aux_bf[l] = w.acts_bf[l] = w.xw_il[l] = nullptr;
   }
   w.cap_rows = 0;
 }
@@ -116,7 +117,10 @@ int ensure_workspace(skrnn_handle *h, int B, int T) {
       SK_CUDA(cudaMalloc(&w.out_bf[l], rows * h->H * e));
       SK_CUDA(cudaMalloc(&w.hprev_bf[l], rows * h->H * e));
       if (h->cfg.cell == SKRNN_CELL_GRU) SK_CUDA(cudaMalloc(&w.aux_bf[l], rows * h->H * e));
-      if (h->cfg.cell == SKRNN_CELL_LSTM) SK_CUDA(cudaMalloc(&w.acts_bf[l], rows * h->G * e));
+      if (h->cfg.cell == SKRNN_CELL_LSTM) {
+        SK_CUDA(cudaMalloc(&w.acts_bf[l], rows * h->G * e));
+        SK_CUDA(cudaMalloc(&w.xw_il[l], rows * h->G * e));
+      }
     }
   }
   w.cap_rows = rows;
@@ -185,6 +189,19 @@ int run_forward(skrnn_handle *h, cudaStream_t st, int B, int T, const float *x, 
       SK_TRY(gemm(h, st, (int)R, 2 * H, lp.I, Xo, true, weight(h, l, 0), true, h->ws.xw[l], G, h->params + lp.b[0], false));
       SK_TRY(gemm(h, st, (int)R, H, lp.I, Xo, true, weight(h, l, 1), true, h->ws.xw[l] + 2 * H, G, h->params + lp.b[1], false));
     } else {
+      h->xw_il_ok[l] = false;
+      static int nt_env = -1;
+      if (nt_env < 0) { const char *e = getenv("SKRNN_NT"); nt_env = (e && e[0] == '1') ? 1 : 0; }
+      if (!nt_env && sk_rnn_tc_eligible(h) && h->ws.xw_il[l] != nullptr && h->wx_il[l] != nullptr) {
+        // tcgen05 lstm kernels: bf16 projection with the four gates of a unit adjacent (half the bytes of the fp32 one)
+        const int ip = (lp.I + 7) / 8 * 8;
+        SK_TRY(sk_gemm_tc_bf16out(h, st, (int)R, G, ip, Xo.b, Xo.ldb, h->wx_il[l], G, h->ws.xw_il[l], G, h->bias_il[l]));
+        h->xw_il_ok[l] = true;
+        SK_TRY(sk_rnn_forward_layer(h, st, l, B, T, x, state_in + (size_t)l * B * h->S,
+                                    state_out + (size_t)l * B * h->S, mask, seed, row0, training));
+        if (h->fwd_family[l] == 1) continue;
+        h->xw_il_ok[l] = false;  // declined (shape, launch failure): redo the layer through the fp32-format projection
+      }
       SK_TRY(gemm(h, st, (int)R, G, lp.I, Xo, true, weight(h, l, 0), true, h->ws.xw[l], G, h->params + lp.b[0], false));
     }
     SK_TRY(sk_rnn_forward_layer(h, st, l, B, T, x, state_in + (size_t)l * B * h->S,
@@ -278,6 +295,16 @@ int skrnn_create(const skrnn_config *cfg, skrnn_handle **out) {
     cudaMemset(h->params_bf, 0, o * sizeof(__nv_bfloat16));
     cudaMemcpy(h->cast_seg_dev, seg.data(), seg.size() * sizeof(int64_t), cudaMemcpyHostToDevice);
   }
+  if (cfg->precision == SKRNN_PREC_BF16 && cfg->cell == SKRNN_CELL_LSTM) {
+    for (int l = 0; l < h->L; ++l) {
+      const int ip = (h->lp[l].I + 7) / 8 * 8;
+      if (cudaMalloc(&h->wx_il[l], (size_t)ip * h->G * sizeof(__nv_bfloat16)) != cudaSuccess ||
+          cudaMalloc(&h->bias_il[l], (size_t)h->G * sizeof(float)) != cudaSuccess) {
+        sk_set_error("skrnn_create: cudaMalloc of the interleaved input weights failed");
+        return fail();
+      }
+    }
+  }
   if (cudaStreamCreateWithFlags(&h->side, cudaStreamNonBlocking) != cudaSuccess) {
     sk_set_error("skrnn_create: cudaStreamCreate failed");
     return fail();
@@ -326,6 +353,7 @@ void skrnn_destroy(skrnn_handle *h) {
   cudaFreeHost(h->pin_y);
   cudaFreeHost(h->pin_state);
   cudaFreeHost(h->pin_loss);
+  for (int l = 0; l < SK_MAX_LAYERS; ++l) { cudaFree(h->wx_il[l]); cudaFree(h->bias_il[l]); }
   if (h->side) cudaStreamDestroy(h->side);
   for (int i = 0; i < 2; ++i) {
     if (h->ev_main[i]) cudaEventDestroy(h->ev_main[i]);

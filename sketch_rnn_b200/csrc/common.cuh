@@ -69,6 +69,8 @@ struct SkWorkspace {   // time-major activations for one (B, T) capacity
   __nv_bfloat16 *out_bf[SK_MAX_LAYERS] = {nullptr};  // [T,B,H]
   __nv_bfloat16 *hprev_bf[SK_MAX_LAYERS] = {nullptr};
   __nv_bfloat16 *aux_bf[SK_MAX_LAYERS] = {nullptr};  // gru r*h
+  __nv_bfloat16 *xw_il[SK_MAX_LAYERS] = {nullptr};   // [T,B,H,4]: hoisted x*Wx+b of an lstm layer in bf16, the four gates of
+                                                     // a unit adjacent (input of the tcgen05 forward kernels)
   __nv_bfloat16 *acts_bf[SK_MAX_LAYERS] = {nullptr}; // [T,B,H,4]: lstm gate activations i,j,f,o saved by the tcgen05
                                                      // forward kernel for its BPTT counterpart
   __nv_bfloat16 *dpre_bf = nullptr;                  // [T,B,G] of the layer being differentiated (= one of dpre_bf_buf)
@@ -119,6 +121,11 @@ struct skrnn_handle {
   // side stream for work off the critical path of the backward pass (weight gradients), see skrnn_loss_grad
   cudaStream_t side = nullptr;
   cudaEvent_t ev_main[2] = {nullptr, nullptr}, ev_side[2] = {nullptr, nullptr};
+  // lstm, bf16: Wx of every layer with gate-interleaved columns (4*unit + gate), rows padded to 8 for layer 0, and the
+  // bias in the same order: the GEMM that produces xw_il
+  __nv_bfloat16 *wx_il[SK_MAX_LAYERS] = {nullptr};
+  float *bias_il[SK_MAX_LAYERS] = {nullptr};
+  bool xw_il_ok[SK_MAX_LAYERS] = {false};  // this step's xw_il[l] is what the forward of layer l reads
   int fwd_family[SK_MAX_LAYERS] = {0};  // which kernels ran a layer's forward (0 fp32, 1 rnn_tc, 2 rnn_nt): they save
                                         // activations in different places, so the backward must be the same family
   // optional per-category kernel timing (skrnn_profile_*): CUDA events around every launch
@@ -158,6 +165,8 @@ int sk_gemm_tc(skrnn_handle *h, cudaStream_t st, int M, int N, int K, const void
 int sk_gemm_tc_lstm_cell(skrnn_handle *h, cudaStream_t st, int M, int H, int K, const void *A, int lda, const void *W,
                          const float *bias_il, float *cell_c, __nv_bfloat16 *cell_self, int kself, int hoff,
                          __nv_bfloat16 *cell_out, int kout, const float *xin);
+int sk_gemm_tc_bf16out(skrnn_handle *h, cudaStream_t st, int M, int N, int K, const void *A, int lda, const void *B, int ldb,
+                       __nv_bfloat16 *C, int ldc, const float *bias);
 extern uint32_t g_tc_override[6];
 // Tiled tensor map (rank 2..5), 128B-swizzled unless swizzle128 = false.  elem_bytes: 2 (bf16) or 4 (fp32).
 int sk_make_tmap(CUtensorMap *m, int elem_bytes, const void *ptr, int rank, const uint64_t *dims,
@@ -165,6 +174,7 @@ int sk_make_tmap(CUtensorMap *m, int elem_bytes, const void *ptr, int rank, cons
 // tcgen05 recurrent kernels, large-batch variant (rnn_nt.cu): 0 ok, -1 not applicable
 int sk_rnn_nt_layer(skrnn_handle *h, cudaStream_t st, bool bwd, int l, int B, int T, const float *state_in,
                     float *state_out, const float *mask, uint64_t seed, int row0, bool training);
+bool sk_rnn_tc_eligible(const skrnn_handle *h);
 // tcgen05 recurrent kernels (rnn_tc.cu): return 0 ok, <0 "not eligible, use the fp32 kernels", >0 error
 int sk_rnn_tc_layer(skrnn_handle *h, cudaStream_t st, bool bwd, int l, int B, int T, const float *x_bt5,
                     const float *state_in, float *state_out, const float *mask, uint64_t seed, int row0,

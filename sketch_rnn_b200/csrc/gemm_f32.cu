@@ -206,6 +206,20 @@ __global__ void cast_params_kernel(const float *__restrict__ p, __nv_bfloat16 *_
   }
 }
 
+// lstm input weights with gate-interleaved columns: dst[k][4u+g] = W[k][g*H+u] for k < I (zero rows up to ipad),
+// bias_il[4u+g] = b[g*H+u]
+__global__ void interleave_wx_kernel(const float *__restrict__ mat, const float *__restrict__ bias, int I, int ipad, int H,
+                                     __nv_bfloat16 *__restrict__ dst, float *__restrict__ bias_il) {
+  const int G = 4 * H;
+  const int64_t total = (int64_t)ipad * G;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int k = (int)(i / G), ci = (int)(i % G);
+    const int c = (ci & 3) * H + (ci >> 2);
+    dst[i] = __float2bfloat16_rn(k < I ? mat[(size_t)k * G + c] : 0.f);
+    if (k == 0) bias_il[ci] = bias[c];
+  }
+}
+
 }  // namespace
 
 int sk_gemm_f32(skrnn_handle *h, cudaStream_t st, int M, int N, int K, const float *A, int lda,
@@ -276,5 +290,14 @@ int sk_cast_params(skrnn_handle *h, cudaStream_t st) {
   int blocks = (int)std::min<int64_t>((h->P + 255) / 256, (int64_t)4 * h->num_sms);
   cast_params_kernel<<<blocks, 256, 0, st>>>(h->params, h->params_bf, h->cast_nseg, h->cast_seg_dev);
   SK_CUDA(cudaGetLastError());
+  for (int l = 0; l < h->L; ++l) {
+    if (h->wx_il[l] == nullptr) continue;
+    const int I = h->lp[l].I, ip = (I + 7) / 8 * 8;
+    const int64_t total = (int64_t)ip * h->G;
+    SkLaunch scope2(h, st, SK_CAT_MISC);
+    interleave_wx_kernel<<<(int)std::min<int64_t>((total + 255) / 256, (int64_t)2 * h->num_sms), 256, 0, st>>>(
+        h->params + h->lp[l].w[0], h->params + h->lp[l].b[0], I, ip, h->H, h->wx_il[l], h->bias_il[l]);
+    SK_CUDA(cudaGetLastError());
+  }
   return 0;
 }

@@ -342,6 +342,37 @@ gemm_tc_persist_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
           }
         }
         named_bar_sync(1, 32 * p_epi_warps(EPI));  // everybody is done with the bias slice before the next tile rewrites it
+      } else if constexpr (EPI == 2) {
+        // bf16 C: 64 columns (one 128-byte swizzled row per accumulator row) per ring slot
+#pragma unroll 1
+        for (int c = 0; c < BN / 64; ++c) {
+          if (issuer) tma_store_wait_read_n<1>();
+          named_bar_sync(1, 128);
+          uint8_t *row = ring_gen + (c & 1) * 16384 + r * 128;
+#pragma unroll
+          for (int hf = 0; hf < 2; ++hf) {
+            uint32_t v[32];
+            tc_ld32(tmem_acc + ((uint32_t)(32 * q) << 16) + (uint32_t)(buf * BN + c * 64 + hf * 32), v);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+              const float4 b0 = *reinterpret_cast<const float4 *>(bias_gen + c * 64 + hf * 32 + 8 * i);
+              const float4 b1 = *reinterpret_cast<const float4 *>(bias_gen + c * 64 + hf * 32 + 8 * i + 4);
+              const __nv_bfloat162 p0 = __floats2bfloat162_rn(__uint_as_float(v[8 * i + 0]) + b0.x, __uint_as_float(v[8 * i + 1]) + b0.y);
+              const __nv_bfloat162 p1 = __floats2bfloat162_rn(__uint_as_float(v[8 * i + 2]) + b0.z, __uint_as_float(v[8 * i + 3]) + b0.w);
+              const __nv_bfloat162 p2 = __floats2bfloat162_rn(__uint_as_float(v[8 * i + 4]) + b1.x, __uint_as_float(v[8 * i + 5]) + b1.y);
+              const __nv_bfloat162 p3 = __floats2bfloat162_rn(__uint_as_float(v[8 * i + 6]) + b1.z, __uint_as_float(v[8 * i + 7]) + b1.w);
+              const uint4 o = make_uint4(*reinterpret_cast<const uint32_t *>(&p0), *reinterpret_cast<const uint32_t *>(&p1),
+                                         *reinterpret_cast<const uint32_t *>(&p2), *reinterpret_cast<const uint32_t *>(&p3));
+              *reinterpret_cast<uint4 *>(row + (((hf * 4 + i) ^ (r & 7)) << 4)) = o;
+            }
+          }
+          fence_proxy_async_smem();
+          named_bar_sync(1, 128);
+          if (issuer) {
+            if (n0 + c * 64 < a.N) tma_store_2d_nocommit(&tmC, s_ring + (c & 1) * 16384, n0 + c * 64, m0);
+            tma_store_commit();
+          }
+        }
       } else {
 #pragma unroll 1
       for (int c = 0; c < BN / 32; ++c) {
@@ -589,6 +620,40 @@ int sk_gemm_tc_lstm_cell(skrnn_handle *h, cudaStream_t st, int M, int H, int K, 
   SkLaunch scope(h, st, SK_CAT_TC_GEMM);
   SK_CUDA(cudaFuncSetAttribute(gemm_tc_persist_kernel<true, false, 256, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, p_smem(256)));
   gemm_tc_persist_kernel<true, false, 256, 1><<<grid, p_threads(1), p_smem(256), st>>>(tmA, tmB, tmA, a);
+  SK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// C (bf16) [M,N] = A[M,K] * B[K,N] + bias through the persistent kernel (A bf16 K-major, B bf16 [K][ldb] N-contiguous).
+int sk_gemm_tc_bf16out(skrnn_handle *h, cudaStream_t st, int M, int N, int K, const void *A, int lda, const void *B, int ldb,
+                       __nv_bfloat16 *C, int ldc, const float *bias) {
+  if (M <= 0 || N <= 0 || K <= 0) return 0;
+  SK_CHECK(ldc % 8 == 0 && (reinterpret_cast<uintptr_t>(C) & 15) == 0, "bf16 GEMM output must be 16-byte aligned (ldc %d)", ldc);
+  CUtensorMap tmA, tmB, tmC;
+  SK_TRY(make_map(&tmA, A, K, M, lda, BK, BM));
+  SK_TRY(make_map(&tmB, B, N, K, ldb, 64, BK));
+  {
+    uint64_t dims[2] = {(uint64_t)N, (uint64_t)M};
+    uint64_t str[1] = {(uint64_t)ldc * 2};
+    uint32_t box[2] = {64, (uint32_t)BM};
+    SK_TRY(sk_make_tmap(&tmC, 2, C, 2, dims, str, box));
+  }
+  TcArgs a = {};
+  a.M = M; a.N = N; a.K = K; a.C = nullptr; a.ldc = ldc; a.bias = bias; a.accumulate = 0;
+  a.lbo_a = 0; a.sbo_a = 1024; a.adv_a = 32;
+  a.lbo_b = 8192; a.sbo_b = 1024; a.adv_b = 2048;
+  a.kb_per_split = (K + BK - 1) / BK;
+  const bool wide = N >= 256;
+  const int tiles = ((N + (wide ? 255 : 127)) / (wide ? 256 : 128)) * ((M + BM - 1) / BM);
+  const int grid = std::min(tiles, h->num_sms);
+  SkLaunch scope(h, st, SK_CAT_TC_GEMM);
+  if (wide) {
+    SK_CUDA(cudaFuncSetAttribute(gemm_tc_persist_kernel<true, false, 256, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, p_smem(256)));
+    gemm_tc_persist_kernel<true, false, 256, 2><<<grid, p_threads(2), p_smem(256), st>>>(tmA, tmB, tmC, a);
+  } else {
+    SK_CUDA(cudaFuncSetAttribute(gemm_tc_persist_kernel<true, false, 128, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, p_smem(128)));
+    gemm_tc_persist_kernel<true, false, 128, 2><<<grid, p_threads(2), p_smem(128), st>>>(tmA, tmB, tmC, a);
+  }
   SK_CUDA(cudaGetLastError());
   return 0;
 }

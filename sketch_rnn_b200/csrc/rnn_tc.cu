@@ -110,8 +110,8 @@ lstm_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_h, const __grid_consta
   const int H = a.H, B = a.B, T = a.T, nkb = a.nkb;
   const uint32_t s_w = base;                                  // nkb x [128 rows][128 B] (unless weights sit in TMEM)
   const uint32_t s_h = s_w + (a.a_tmem ? 0u : (uint32_t)nkb * 16384u);  // nkb x [N rows][128 B]
-  const uint32_t s_xw = s_h + (uint32_t)nkb * (N * 128);      // 4 planes x [N][32] fp32
-  const uint32_t s_act = s_xw + 4u * (N * 128);               // [N][32 units][4 gates] bf16: activations saved for BPTT
+  const uint32_t s_xw = s_h + (uint32_t)nkb * (N * 128);      // [N][32 units][4 gates] bf16: hoisted x*Wx+b of the step
+  const uint32_t s_act = s_xw + (uint32_t)N * 256u;               // [N][32 units][4 gates] bf16: activations saved for BPTT
   const uint32_t s_bar = s_act + (uint32_t)N * 256u;
   const uint32_t bar_h = s_bar;          // [8]
   const uint32_t bar_acc = s_bar + 64;
@@ -210,9 +210,7 @@ lstm_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_h, const __grid_consta
     if (b0 + cb + 4 * it < B) valid |= 1u << it;
   const bool tile_full = b0 + N <= B;
   // staging-plane address of (column, unit): columns 4 apart flip bit 2 of the 128B-swizzle phase
-  const uint32_t swz = ((((uint32_t)(eu >> 2) ^ (uint32_t)cb) & 7u) << 4) + ((uint32_t)(eu & 3) << 2);
-  uint8_t *pl_e = xw_gen + cb * 128 + swz;
-  uint8_t *pl_o = xw_gen + cb * 128 + (swz ^ 64u);
+  const uint8_t *xw_p = xw_gen + cb * 256 + eu * 8;                       // (column cb, unit eu): 4 gates, 8 bytes
   uint8_t *act_p = act_gen + cb * 256 + eu * 8;                           // (column cb, unit eu): 4 gates, 8 bytes
   const float *init_p = a.state_in + (size_t)(b0 + cb) * S + uo;          // fed (c, h): the eoc reset source
   const int H4 = 4 * H;
@@ -238,8 +236,8 @@ lstm_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_h, const __grid_consta
         // last step's activation store has left its staging tile (the epilogue writes it again only after it has
         // seen this step's planes, i.e. after bar_xw)
         tma_store_wait_read();
-        mbar_expect_tx(bar_xw, 4 * N * 128);
-        tma_load_4d(s_xw, &tm_xw, bar_xw, u0, b0, 0, t);  // the 4 gate planes of my units in one box
+        mbar_expect_tx(bar_xw, N * 256);
+        tma_load_3d(s_xw, &tm_xw, bar_xw, 4 * u0, b0, t);  // the 4 gates of my 32 units for the tile's rows
         // gate activations of this step (bf16, [unit][gate] per row) go to their own array for BPTT
         mbar_wait(bar_out, t & 1);
         tma_store_3d(&tm_act, s_act, 4 * u0, b0, t);
@@ -339,13 +337,11 @@ lstm_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_h, const __grid_consta
         v3 = __shfl_xor_sync(0xffffffffu, v3, 3);
         perm4(g_lo, g_hi, v0, v1, v2, v3, p0, p1, p2, p3);
         if (FULL || ((valid >> it) & 1u)) {
-          uint8_t *pp = ((it & 1) ? pl_o : pl_e) + it * 512;
-          float *x0p = reinterpret_cast<float *>(pp), *x1p = reinterpret_cast<float *>(pp + 1 * (N * 128));
-          float *x2p = reinterpret_cast<float *>(pp + 2 * (N * 128)), *x3p = reinterpret_cast<float *>(pp + 3 * (N * 128));
-          const float ig = sigmoid_approx(p0 + *x0p);
-          const float jg = tanh_approx(p1 + *x1p);
-          const float fg = sigmoid_approx(p2 + *x2p + 1.0f);
-          const float og = sigmoid_approx(p3 + *x3p);
+          const uint2 xv = *reinterpret_cast<const uint2 *>(xw_p + it * 1024);  // bf16 i, j, f, o of (column, unit)
+          const float ig = sigmoid_approx(p0 + __uint_as_float(xv.x << 16));
+          const float jg = tanh_approx(p1 + __uint_as_float(xv.x & 0xffff0000u));
+          const float fg = sigmoid_approx(p2 + __uint_as_float(xv.y << 16) + 1.0f);
+          const float og = sigmoid_approx(p3 + __uint_as_float(xv.y & 0xffff0000u));
           {  // staged for the TMA store.  i and f are positive: their sign bits carry the step's eoc flag and
              // "this output element was dropped", so BPTT needs no side loads
             const __nv_bfloat162 a01 = __floats2bfloat162_rn(ig, jg), a23 = __floats2bfloat162_rn(fg, og);
@@ -465,9 +461,9 @@ lstm_fwd_pp_kernel(const __grid_constant__ CUtensorMap tm_h, const __grid_consta
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   uint8_t *gbase = smem_raw + (base - smem_u32(smem_raw));
   const int H = a.H, B = a.B, T = a.T, nkb = a.nkb, CS = a.CS;
-  const uint32_t h_bytes = (uint32_t)nkb * (N2 * 128), xw_bytes = 4u * (N2 * 128), hst_bytes = (uint32_t)N2 * 64u;
+  const uint32_t h_bytes = (uint32_t)nkb * (N2 * 128), xw_bytes = (uint32_t)N2 * 256u, hst_bytes = (uint32_t)N2 * 64u;
   const uint32_t s_h = base;                       // [2] x nkb x [N2 rows][128 B]
-  const uint32_t s_xw = s_h + 2 * h_bytes;         // [2] x 4 planes x [N2][32] fp32
+  const uint32_t s_xw = s_h + 2 * h_bytes;         // [2] x [N2][32 units][4 gates] bf16: hoisted x*Wx+b
   const uint32_t s_hst = s_xw + 2 * xw_bytes;      // [2] x [N2][32 units] bf16: my units of h_t on their way out (TMA store)
   const uint32_t s_bar = s_hst + 2 * hst_bytes;
   // mbarriers, index s = half tile
@@ -561,7 +557,7 @@ lstm_fwd_pp_kernel(const __grid_constant__ CUtensorMap tm_h, const __grid_consta
       };
       auto load_xw = [&](int s, int t) {
         mbar_expect_tx(bar_xw + 8 * s, xw_bytes);
-        tma_load_4d(s_xw + s * xw_bytes, &tm_xw, bar_xw + 8 * s, u0, b0 + s * N2, 0, t);
+        tma_load_3d(s_xw + s * xw_bytes, &tm_xw, bar_xw + 8 * s, 4 * u0, b0 + s * N2, t);
       };
       auto retire = [&](int s, int t) {  // the elementwise pass of (s, t) is over: refill its planes
         mbar_wait(bar_epi + 8 * s, t & 1);
@@ -662,9 +658,7 @@ lstm_fwd_pp_kernel(const __grid_constant__ CUtensorMap tm_h, const __grid_consta
         if (b0 + s * N2 + cb + 4 * it < B) valid[s] |= 1u << it;
     uint8_t *xw_gen = gbase + (s_xw - base);
     uint8_t *hst_gen = gbase + (s_hst - base);
-    const uint32_t swz = ((((uint32_t)(eu >> 2) ^ (uint32_t)cb) & 7u) << 4) + ((uint32_t)(eu & 3) << 2);
-    uint8_t *pl_e = xw_gen + cb * 128 + swz;
-    uint8_t *pl_o = xw_gen + cb * 128 + (swz ^ 64u);
+    const uint8_t *xw_p = xw_gen + cb * 256 + eu * 8;  // (column cb, unit eu): 4 gates, 8 bytes
     uint8_t *hst_p = hst_gen + cb * 64 + eu * 2;
     const float *init_p = a.state_in + (size_t)(b0 + cb) * S + uo;
     const int H4 = 4 * H;
@@ -729,11 +723,11 @@ lstm_fwd_pp_kernel(const __grid_constant__ CUtensorMap tm_h, const __grid_consta
           v3 = __shfl_xor_sync(0xffffffffu, v3, 3);
           perm4(g_lo, g_hi, v0, v1, v2, v3, p0, p1, p2, p3);
           if (FULL || ((valid[s] >> it) & 1u)) {
-            uint8_t *pp = ((it & 1) ? pl_o : pl_e) + s * xw_bytes + it * 512;
-            const float ig = sigmoid_approx(p0 + *reinterpret_cast<const float *>(pp));
-            const float jg = tanh_approx(p1 + *reinterpret_cast<const float *>(pp + 1 * (N2 * 128)));
-            const float fg = sigmoid_approx(p2 + *reinterpret_cast<const float *>(pp + 2 * (N2 * 128)) + 1.0f);
-            const float og = sigmoid_approx(p3 + *reinterpret_cast<const float *>(pp + 3 * (N2 * 128)));
+            const uint2 xv = *reinterpret_cast<const uint2 *>(xw_p + s * xw_bytes + it * 1024);  // bf16 i, j, f, o
+            const float ig = sigmoid_approx(p0 + __uint_as_float(xv.x << 16));
+            const float jg = tanh_approx(p1 + __uint_as_float(xv.x & 0xffff0000u));
+            const float fg = sigmoid_approx(p2 + __uint_as_float(xv.y << 16) + 1.0f);
+            const float og = sigmoid_approx(p3 + __uint_as_float(xv.y & 0xffff0000u));
             {
               const __nv_bfloat162 a01 = __floats2bfloat162_rn(ig, jg), a23 = __floats2bfloat162_rn(fg, og);
               uint32_t w0 = *reinterpret_cast<const uint32_t *>(&a01) & 0xffff7fffu;
@@ -1506,24 +1500,29 @@ int launch_bwd(const CUtensorMap &tm_acts, const CUtensorMap &tm_do, const CUten
 size_t smem_need(bool bwd, int H, int N, bool a_tmem) {
   const int nkb = (H + 63) / 64, HP = (H + 127) / 128 * 128;
   size_t s = bwd ? (size_t)2 * HP * 128 + 2 * (size_t)N * 128 + 4 * (size_t)N * 128
-                 : (a_tmem ? 0 : (size_t)nkb * 16384) + (size_t)nkb * N * 128 + 4 * (size_t)N * 128 + 2 * (size_t)N * 128;
+                 : (a_tmem ? 0 : (size_t)nkb * 16384) + (size_t)nkb * N * 128 + 2 * (size_t)N * 128 + 2 * (size_t)N * 128;
   return s + 1024 + 256;
 }
 
 }  // namespace
 
+// Static part of the eligibility test: run_forward uses it to decide in which format it hoists x*Wx+b.
+bool sk_rnn_tc_eligible(const skrnn_handle *h) {
+  const int H = h->H;
+  if (h->cfg.precision != SKRNN_PREC_BF16 || h->cfg.cell != SKRNN_CELL_LSTM) return false;
+  if (!(H == 32 || H == 64 || H == 128 || H == 256 || H == 512)) return false;
+  if (h->tc_rnn_disabled) return false;
+  static int env_off = -1;
+  if (env_off < 0) { const char *e = getenv("SKRNN_DISABLE_TC_RNN"); env_off = (e && e[0] == '1') ? 1 : 0; }
+  return !env_off;
+}
+
 int sk_rnn_tc_layer(skrnn_handle *h, cudaStream_t st, bool bwd, int l, int B, int T, const float *x_bt5,
                     const float *state_in, float *state_out, const float *mask, uint64_t seed, int row0,
                     bool training) {
   const int H = h->H;
-  if (h->cfg.precision != SKRNN_PREC_BF16 || h->cfg.cell != SKRNN_CELL_LSTM) return -1;
-  if (!(H == 32 || H == 64 || H == 128 || H == 256 || H == 512)) return -1;
-  if (h->tc_rnn_disabled) return -1;
-  {
-    static int env_off = -1;
-    if (env_off < 0) { const char *e = getenv("SKRNN_DISABLE_TC_RNN"); env_off = (e && e[0] == '1') ? 1 : 0; }
-    if (env_off) return -1;
-  }
+  if (!sk_rnn_tc_eligible(h)) return -1;
+  if (!bwd && (!h->xw_il_ok[l] || h->ws.xw_il[l] == nullptr)) return -1;  // the projection was hoisted in the fp32 format
   const int CS = H / 32;
   const int nkb = (H + 63) / 64, HP = (H + 127) / 128 * 128;
   // batch tile: the smallest N whose cluster count fits on the GPU at once, within shared memory / TMEM
@@ -1596,13 +1595,14 @@ int sk_rnn_tc_layer(skrnn_handle *h, cudaStream_t st, bool bwd, int l, int B, in
   }
   int rc = 0;
   if (!bwd) {
+    // hoisted projection xw_il[t][b][4*u + g] (bf16, not swizzled, written by run_forward): one box = 32 units x N rows
+    if (!h->xw_il_ok[l] || h->ws.xw_il[l] == nullptr) return -1;
     CUtensorMap tm_xw;
     {
-      // xw[t][b][g*H + u] viewed as (u, b, g, t): one box fetches the 4 gate planes of 32 units for N rows
-      uint64_t dims[4] = {(uint64_t)H, (uint64_t)B, 4, (uint64_t)T};
-      uint64_t str[3] = {(uint64_t)h->G * 4, (uint64_t)H * 4, (uint64_t)B * h->G * 4};
-      uint32_t box[4] = {32, (uint32_t)N, 4, 1};
-      SK_TRY(sk_make_tmap(&tm_xw, 4, h->ws.xw[l], 4, dims, str, box));
+      uint64_t dims[3] = {(uint64_t)h->G, (uint64_t)B, (uint64_t)T};
+      uint64_t str[2] = {(uint64_t)h->G * 2, (uint64_t)B * h->G * 2};
+      uint32_t box[3] = {128, (uint32_t)N, 1};
+      SK_TRY(sk_make_tmap(&tm_xw, 2, h->ws.xw_il[l], 3, dims, str, box, false));
     }
     CUtensorMap tm_h;
     uint64_t dims[3] = {(uint64_t)H, (uint64_t)B, (uint64_t)T};
@@ -1615,10 +1615,10 @@ int sk_rnn_tc_layer(skrnn_handle *h, cudaStream_t st, bool bwd, int l, int B, in
     SK_TRY(sk_make_tmap(&tm_h, 2, h->ws.hprev_bf[l], 3, dims, str, box));
     if (pp) {
       // the xw box of a half tile has N/2 rows
-      uint64_t xdims[4] = {(uint64_t)H, (uint64_t)B, 4, (uint64_t)T};
-      uint64_t xstr[3] = {(uint64_t)h->G * 4, (uint64_t)H * 4, (uint64_t)B * h->G * 4};
-      uint32_t xbox[4] = {32, (uint32_t)(N / 2), 4, 1};
-      SK_TRY(sk_make_tmap(&tm_xw, 4, h->ws.xw[l], 4, xdims, xstr, xbox));
+      uint64_t xdims[3] = {(uint64_t)h->G, (uint64_t)B, (uint64_t)T};
+      uint64_t xstr[2] = {(uint64_t)h->G * 2, (uint64_t)B * h->G * 2};
+      uint32_t xbox[3] = {128, (uint32_t)(N / 2), 1};
+      SK_TRY(sk_make_tmap(&tm_xw, 2, h->ws.xw_il[l], 3, xdims, xstr, xbox, false));
       // my 32 units of h_t for a half tile's rows leave as one plain (unswizzled) box
       uint32_t sbox[3] = {32, (uint32_t)(N / 2), 1};
       CUtensorMap tm_hst;
