@@ -522,8 +522,12 @@ int skrnn_loss_grad(skrnn_handle *h, int32_t B, int32_t T, const float *x_dev, c
     Op dpre = dpre_op(h, l);
     if (h->ws.dpre_bf_buf[buf]) dpre.b = h->ws.dpre_bf_buf[buf];
     float *gW = h->grads + lp.w[0];
-    SK_TRY(gemm(h, s2, lp.I, G, R, layer_input(h, l), false, dpre, true, gW, G, nullptr, true));
-    SK_TRY(gemm(h, s2, H, G, R, hprev_op(h, l), false, dpre, true, gW + (size_t)lp.I * G, G, nullptr, true));
+    // the tcgen05 lstm kernels leave d(pre) with gate-interleaved columns: the split-K epilogue scatters dW back
+    h->gemm_perm_H = (h->fwd_family[l] == 1) ? H : 0;
+    int rc = gemm(h, s2, lp.I, G, R, layer_input(h, l), false, dpre, true, gW, G, nullptr, true);
+    if (rc == 0) rc = gemm(h, s2, H, G, R, hprev_op(h, l), false, dpre, true, gW + (size_t)lp.I * G, G, nullptr, true);
+    h->gemm_perm_H = 0;
+    SK_TRY(rc);
     if (!bias_done) SK_TRY(bias_grad(h, s2, dpre, R, G, h->grads + lp.b[0]));
     return 0;
   };
@@ -565,7 +569,12 @@ int skrnn_loss_grad(skrnn_handle *h, int32_t B, int32_t T, const float *x_dev, c
       }
     } else {
       // d(out) of the layer below first: it is what the next BPTT launch waits for
-      if (l > 0) SK_TRY(gemm(h, st, R, I, G, dpre, true, weight(h, l, 0), false, h->ws.dout, H, nullptr, false));
+      if (l > 0) {
+        if (h->fwd_family[l] == 1)  // interleaved d(pre) against the interleaved copy of Wx (K order matches)
+          SK_TRY(sk_gemm_tc(h, st, R, I, G, dpre.b, G, true, h->wx_il[l], G, true, h->ws.dout, H, nullptr, false));
+        else
+          SK_TRY(gemm(h, st, R, I, G, dpre, true, weight(h, l, 0), false, h->ws.dout, H, nullptr, false));
+      }
       if (overlap && l > 0) {
         SK_CUDA(cudaEventRecord(h->ev_main[buf], st));
         def.l = l; def.buf = buf; def.bias_done = h->bias_grad_done;

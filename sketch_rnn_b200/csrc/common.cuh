@@ -125,6 +125,8 @@ struct skrnn_handle {
   // bias in the same order: the GEMM that produces xw_il
   __nv_bfloat16 *wx_il[SK_MAX_LAYERS] = {nullptr};
   float *bias_il[SK_MAX_LAYERS] = {nullptr};
+  int gemm_perm_H = 0;  // set around a split-K sk_gemm_tc call whose B operand has gate-interleaved columns (d(pre) of
+                        // the tcgen05 lstm kernels): the epilogue then scatters C back to TF's gate-major columns
   bool xw_il_ok[SK_MAX_LAYERS] = {false};  // this step's xw_il[l] is what the forward of layer l reads
   int fwd_family[SK_MAX_LAYERS] = {0};  // which kernels ran a layer's forward (0 fp32, 1 rnn_tc, 2 rnn_nt): they save
                                         // activations in different places, so the backward must be the same family

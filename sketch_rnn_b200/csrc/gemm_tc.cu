@@ -40,6 +40,7 @@ struct TcArgs {
   __nv_bfloat16 *cell_out;       // layer output rows (next layer's operand / head input), row pitch cell_kout
   const float *cell_xin;         // [M, 5] current input point: column 3 > 0 = eoc = hold the state
   int cell_kself, cell_hoff, cell_kout, cell_H;
+  int perm_H;                    // split-K kernel: un-interleave the columns of C (see the epilogue)
 };
 
 // BN_ = 128: 3 stages, two CTAs per SM.  BN_ = 256: 4 stages, one CTA per SM -- per k-block the tensor core then
@@ -148,7 +149,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         const bool n_ok = n < a.N;
         const float bv = (add_bias && n_ok) ? __ldg(a.bias + n) : 0.f;
         const int rows = min(32, a.M - mb);
-        float *dst = a.C + (size_t)mb * a.ldc + n;
+        // perm_H > 0: column n of the product is (unit n/4, gate n%4); C is stored gate-major (gate*H + unit)
+        const int nd = a.perm_H > 0 ? (n & 3) * a.perm_H + (n >> 2) : n;
+        float *dst = a.C + (size_t)mb * a.ldc + nd;
         if (n_ok) {
           if (a.accumulate) {
             for (int rr = 0; rr < rows; ++rr) atomicAdd(dst + (size_t)rr * a.ldc, stage[rr * 32 + ((lane + rr) & 31)] + bv);
@@ -508,8 +511,9 @@ int sk_gemm_tc(skrnn_handle *h, cudaStream_t st, int M, int N, int K, const void
   else SK_TRY(make_map(&tmA, A, M, K, lda, 64, BK));
   if (b_kmajor) SK_TRY(make_map(&tmB, B, K, N, ldb, BK, BN));
   else SK_TRY(make_map(&tmB, B, N, K, ldb, 64, BK));
-  TcArgs a;
+  TcArgs a = {};
   a.M = M; a.N = N; a.K = K; a.C = C; a.ldc = ldc; a.bias = bias; a.accumulate = accumulate ? 1 : 0;
+  a.perm_H = accumulate ? h->gemm_perm_H : 0;
   // K-major SW128: rows of 128 B, 8-row groups 1024 B apart; next UMMA_K (16 el) is +32 B.
   // MN-major SW128: 64-element MN chunks 8192 B apart (LBO), 8-k-row groups 1024 B apart (SBO);
   // next UMMA_K is two groups = +2048 B.

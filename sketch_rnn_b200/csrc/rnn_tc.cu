@@ -787,7 +787,7 @@ lstm_fwd_pp_kernel(const __grid_constant__ CUtensorMap tm_h, const __grid_consta
 template <int NCH, bool DBG>
 __global__ void __launch_bounds__(TCR_THREADS, 1)
 lstm_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm_acts, const __grid_constant__ CUtensorMap tm_do,
-                   const __grid_constant__ CUtensorMap tm_cp, TcRnnArgs a) {
+                   const __grid_constant__ CUtensorMap tm_cp, const __grid_constant__ CUtensorMap tm_dp, TcRnnArgs a) {
   constexpr int N = 16 * NCH;
   constexpr int CPW = N / 4;
   extern __shared__ uint8_t smem_raw[];
@@ -865,8 +865,6 @@ lstm_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm_acts, const __grid_con
   for (int it = 0; it < NCH; ++it)
     if (b0 + c0 + 4 * it < B) valid |= 1u << it;
   const bool tile_full = b0 + N <= B;
-  const size_t BG = (size_t)B * G;
-  __nv_bfloat16 *d_p = a.dpre_bf + ((size_t)(T - 1) * B + b0 + c0) * G + uo;
   const uint8_t *ac0 = ac_gen + c0 * 256 + eu * 8;  // (column c0, unit eu): 4 gates, 8 bytes
   // d(out) / c tiles: columns 4 apart flip bit 2 of the 128B-swizzle phase
   const uint32_t do_sw = ((((uint32_t)(eu >> 2) ^ (uint32_t)c0) & 7u) << 4);
@@ -889,11 +887,17 @@ lstm_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm_acts, const __grid_con
       // the staged activations of step t were requested one step ahead; once the elementwise phase has
       // consumed them (bar_ready), request step t-1's so the load overlaps the product and the exchange
       mbar_wait(bar_ready, step & 1);
-      if (t > 0 && elect_one()) {
-        mbar_expect_tx(bar_acts, N * 512);
-        tma_load_3d(s_ac, &tm_acts, bar_acts, 4 * u0, b0, t - 1);
-        tma_load_3d(s_do, &tm_do, bar_acts, u0, b0, t - 1);
-        tma_load_3d(s_cp, &tm_cp, bar_acts, u0, b0, t - 1);
+      if (elect_one()) {
+        // d(pre) of the step leaves as it sits in the operand tile: rows x my 128 gate-interleaved columns
+        tma_store_3d(&tm_dp, s_b, 128 * rank, b0, t);
+        tma_store_3d(&tm_dp, s_b + (uint32_t)(N * 128), 128 * rank + 64, b0, t);
+        if (t > 0) {
+          mbar_expect_tx(bar_acts, N * 512);
+          tma_load_3d(s_ac, &tm_acts, bar_acts, 4 * u0, b0, t - 1);
+          tma_load_3d(s_do, &tm_do, bar_acts, u0, b0, t - 1);
+          tma_load_3d(s_cp, &tm_cp, bar_acts, u0, b0, t - 1);
+        }
+        tma_store_wait_read();  // before the cluster barrier: the next elementwise pass rewrites the operand tile
       }
       __syncwarp();
     } else if (warp >= 2) {
@@ -925,11 +929,10 @@ lstm_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm_acts, const __grid_con
           const float d0 = dc2 * jg * ig * (1.0f - ig), d1 = dc2 * ig * (1.0f - jg * jg);
           const float d2 = dc2 * cpv * fg * (1.0f - fg), d3 = dh2 * tc * og * (1.0f - og);
           bsum[0] += d0; bsum[1] += d1; bsum[2] += d2; bsum[3] += d3;
-          __nv_bfloat16 *db = d_p + (size_t)it * 4 * G;
           const __nv_bfloat16 h0 = __float2bfloat16_rn(d0), h1 = __float2bfloat16_rn(d1);
           const __nv_bfloat16 h2 = __float2bfloat16_rn(d2), h3 = __float2bfloat16_rn(d3);
-          db[0] = h0; db[H] = h1; db[2 * H] = h2; db[3 * H] = h3;
-          // own K slice, local column kk = 4u+g: 8 bytes at (row c, kk = 4u) of the swizzled operand
+          // own K slice, local column kk = 4u+g: 8 bytes at (row c, kk = 4u) of the swizzled operand (which is also what
+          // the TMA store sends to the d(pre) array)
           uint2 pk;
           pk.x = (uint32_t)__bfloat16_as_ushort(h0) | ((uint32_t)__bfloat16_as_ushort(h1) << 16);
           pk.y = (uint32_t)__bfloat16_as_ushort(h2) | ((uint32_t)__bfloat16_as_ushort(h3) << 16);
@@ -938,7 +941,6 @@ lstm_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm_acts, const __grid_con
       }
       };
       if (tile_full) items(std::true_type{}); else items(std::false_type{});
-      d_p -= BG;
       fence_proxy_async_smem();
       mbar_arrive(bar_ready);
       TCR_LAP(tk[1]);
@@ -1082,7 +1084,7 @@ lstm_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm_acts, const __grid_con
 template <int NCH, bool DBG>  // NCH items per thread and half tile
 __global__ void __launch_bounds__(TCR_PP_THREADS, 1)
 lstm_bwd_pp_kernel(const __grid_constant__ CUtensorMap tm_acts, const __grid_constant__ CUtensorMap tm_do,
-                   const __grid_constant__ CUtensorMap tm_cp, TcRnnArgs a) {
+                   const __grid_constant__ CUtensorMap tm_cp, const __grid_constant__ CUtensorMap tm_dp, TcRnnArgs a) {
   constexpr int N2 = 16 * NCH, N = 2 * N2;
   constexpr int CPW = N2 / 4;
   extern __shared__ uint8_t smem_raw[];
@@ -1153,13 +1155,21 @@ lstm_bwd_pp_kernel(const __grid_constant__ CUtensorMap tm_acts, const __grid_con
       };
       load_in(0, T - 1);
       load_in(1, T - 1);
-      for (int t = T - 1, step = 0; t > 0; --t, ++step) {
+      for (int t = T - 1, step = 0; t >= 0; --t, ++step) {
 #pragma unroll
         for (int s = 0; s < 2; ++s) {
           mbar_wait(bar_epi + 8 * s, step & 1);  // the elementwise pass of (s, t) has consumed its tiles
-          load_in(s, t - 1);
+          // d(pre) of (s, t) leaves as it sits in the operand tile: rows x my 128 gate-interleaved columns
+          const uint32_t sb = s_half + s * half_bytes + o_b;
+          tma_store_3d(&tm_dp, sb, 128 * rank, b0 + s * N2, t);
+          tma_store_3d(&tm_dp, sb + (uint32_t)(N2 * 128), 128 * rank + 64, b0 + s * N2, t);
+          if (t > 0) {
+            tma_store_wait_read();  // the pass of (s, t-1) rewrites the operand tile once it has its inputs
+            load_in(s, t - 1);
+          }
         }
       }
+      tma_store_wait_all();
     }
     __syncwarp();
   } else if (warp == 1) {
@@ -1224,9 +1234,6 @@ lstm_bwd_pp_kernel(const __grid_constant__ CUtensorMap tm_acts, const __grid_con
     const size_t part_blk = (size_t)NJ * 32 * CK;
     const size_t part_par = (size_t)CS * CS * 4 * part_blk;  // one (half, parity) buffer
     __nv_bfloat16 *part_base = a.partial + (size_t)cid * 4 * part_par;
-    const size_t BG = (size_t)B * G;
-    __nv_bfloat16 *d_p = a.dpre_bf + ((size_t)(T - 1) * B + b0 + c0) * G + uo;
-    const size_t d_half = (size_t)N2 * G;
     const uint8_t *ac0 = half_gen + o_ac + c0 * 256 + eu * 8;
     const uint32_t do_sw = ((((uint32_t)(eu >> 2) ^ (uint32_t)c0) & 7u) << 4);
     const uint8_t *do0 = half_gen + o_do + c0 * 128 + ((eu & 3) << 2);
@@ -1270,10 +1277,8 @@ lstm_bwd_pp_kernel(const __grid_constant__ CUtensorMap tm_acts, const __grid_con
             const float d0 = dc2 * jg * ig * (1.0f - ig), d1 = dc2 * ig * (1.0f - jg * jg);
             const float d2 = dc2 * cpv * fg * (1.0f - fg), d3 = dh2 * tc * og * (1.0f - og);
             bsum[0] += d0; bsum[1] += d1; bsum[2] += d2; bsum[3] += d3;
-            __nv_bfloat16 *db = d_p + s * d_half + (size_t)it * 4 * G;
             const __nv_bfloat16 h0 = __float2bfloat16_rn(d0), h1 = __float2bfloat16_rn(d1);
             const __nv_bfloat16 h2 = __float2bfloat16_rn(d2), h3 = __float2bfloat16_rn(d3);
-            db[0] = h0; db[H] = h1; db[2 * H] = h2; db[3 * H] = h3;
             uint2 pk;
             pk.x = (uint32_t)__bfloat16_as_ushort(h0) | ((uint32_t)__bfloat16_as_ushort(h1) << 16);
             pk.y = (uint32_t)__bfloat16_as_ushort(h2) | ((uint32_t)__bfloat16_as_ushort(h3) << 16);
@@ -1286,7 +1291,6 @@ lstm_bwd_pp_kernel(const __grid_constant__ CUtensorMap tm_acts, const __grid_con
         mbar_arrive(bar_epi + 8 * s);
         TCR_LAP(tk[1]);
       }
-      d_p -= BG;
       if (t == 0) break;
       // ---- R_s: accumulator read-out, bf16 partials for every rank ----
 #pragma unroll
@@ -1461,8 +1465,8 @@ int launch_fwd_pp(const CUtensorMap &tm_h, const CUtensorMap &tm_xw, const CUten
   return 0;
 }
 template <int NCH>
-int launch_bwd_pp(const CUtensorMap &tm_acts, const CUtensorMap &tm_do, const CUtensorMap &tm_cp, const TcRnnArgs &a,
-                  int nclusters, size_t smem, cudaStream_t st) {
+int launch_bwd_pp(const CUtensorMap &tm_acts, const CUtensorMap &tm_do, const CUtensorMap &tm_cp, const CUtensorMap &tm_dp,
+                  const TcRnnArgs &a, int nclusters, size_t smem, cudaStream_t st) {
   auto kern = a.debug ? lstm_bwd_pp_kernel<NCH, true> : lstm_bwd_pp_kernel<NCH, false>;
   SK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   if (a.CS > 8) SK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
@@ -1475,12 +1479,12 @@ int launch_bwd_pp(const CUtensorMap &tm_acts, const CUtensorMap &tm_do, const CU
   at[0].id = cudaLaunchAttributeClusterDimension;
   at[0].val.clusterDim.x = a.CS; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
   cfg.attrs = at; cfg.numAttrs = 1;
-  SK_CUDA(cudaLaunchKernelEx(&cfg, kern, tm_acts, tm_do, tm_cp, a));
+  SK_CUDA(cudaLaunchKernelEx(&cfg, kern, tm_acts, tm_do, tm_cp, tm_dp, a));
   return 0;
 }
 template <int NCH>
-int launch_bwd(const CUtensorMap &tm_acts, const CUtensorMap &tm_do, const CUtensorMap &tm_cp, const TcRnnArgs &a,
-               int nclusters, size_t smem, cudaStream_t st) {
+int launch_bwd(const CUtensorMap &tm_acts, const CUtensorMap &tm_do, const CUtensorMap &tm_cp, const CUtensorMap &tm_dp,
+               const TcRnnArgs &a, int nclusters, size_t smem, cudaStream_t st) {
   auto kern = a.debug ? lstm_bwd_tc_kernel<NCH, true> : lstm_bwd_tc_kernel<NCH, false>;
   SK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   if (a.CS > 8) SK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
@@ -1493,7 +1497,7 @@ int launch_bwd(const CUtensorMap &tm_acts, const CUtensorMap &tm_do, const CUten
   at[0].id = cudaLaunchAttributeClusterDimension;
   at[0].val.clusterDim.x = a.CS; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
   cfg.attrs = at; cfg.numAttrs = 1;
-  SK_CUDA(cudaLaunchKernelEx(&cfg, kern, tm_acts, tm_do, tm_cp, a));
+  SK_CUDA(cudaLaunchKernelEx(&cfg, kern, tm_acts, tm_do, tm_cp, tm_dp, a));
   return 0;
 }
 
@@ -1650,6 +1654,16 @@ int sk_rnn_tc_layer(skrnn_handle *h, cudaStream_t st, bool bwd, int l, int B, in
       h->ws.partial_floats = need;
     }
     a.partial = h->ws.partial;
+    const int ppN = (ppb_env && N >= 32) ? N / 2 : N;  // rows per box (half tiles for the two-half-tile kernel)
+    // d(pre) [T,B,4H] bf16 with gate-interleaved columns (4*unit + gate): what the kernel's operand tile holds, stored
+    // as two 64-column boxes in the operand's own (128B-swizzled) layout
+    CUtensorMap tm_dp;
+    {
+      uint64_t ddims[3] = {(uint64_t)h->G, (uint64_t)B, (uint64_t)T};
+      uint64_t dstr[2] = {(uint64_t)h->G * 2, (uint64_t)B * h->G * 2};
+      uint32_t dbox[3] = {64, (uint32_t)ppN, 1};
+      SK_TRY(sk_make_tmap(&tm_dp, 2, h->ws.dpre_bf, 3, ddims, dstr, dbox));
+    }
     // d(out) and the c fed to each step, [T,B,H] fp32: boxes of 32 units x N rows, 128B-swizzled
     CUtensorMap tm_do, tm_cp;
     {
@@ -1671,17 +1685,17 @@ int sk_rnn_tc_layer(skrnn_handle *h, cudaStream_t st, bool bwd, int l, int B, in
       SK_TRY(sk_make_tmap(&tm_do, 4, h->ws.dout, 3, dims, str, box));
       SK_TRY(sk_make_tmap(&tm_cp, 4, h->ws.cprev[l], 3, dims, str, box));
       SkLaunch scope(h, st, SK_CAT_RNN_BWD);
-      if (N == 32) rc = launch_bwd_pp<1>(tm_act2, tm_do, tm_cp, a, nclusters, smem, st);
-      else if (N == 64) rc = launch_bwd_pp<2>(tm_act2, tm_do, tm_cp, a, nclusters, smem, st);
-      else rc = launch_bwd_pp<4>(tm_act2, tm_do, tm_cp, a, nclusters, smem, st);
+      if (N == 32) rc = launch_bwd_pp<1>(tm_act2, tm_do, tm_cp, tm_dp, a, nclusters, smem, st);
+      else if (N == 64) rc = launch_bwd_pp<2>(tm_act2, tm_do, tm_cp, tm_dp, a, nclusters, smem, st);
+      else rc = launch_bwd_pp<4>(tm_act2, tm_do, tm_cp, tm_dp, a, nclusters, smem, st);
       if (rc != 0) return 1;
       return 0;
     }
     SkLaunch scope(h, st, SK_CAT_RNN_BWD);
-    if (N == 16) rc = launch_bwd<1>(tm_act, tm_do, tm_cp, a, nclusters, smem, st);
-    else if (N == 32) rc = launch_bwd<2>(tm_act, tm_do, tm_cp, a, nclusters, smem, st);
-    else if (N == 64) rc = launch_bwd<4>(tm_act, tm_do, tm_cp, a, nclusters, smem, st);
-    else rc = launch_bwd<8>(tm_act, tm_do, tm_cp, a, nclusters, smem, st);
+    if (N == 16) rc = launch_bwd<1>(tm_act, tm_do, tm_cp, tm_dp, a, nclusters, smem, st);
+    else if (N == 32) rc = launch_bwd<2>(tm_act, tm_do, tm_cp, tm_dp, a, nclusters, smem, st);
+    else if (N == 64) rc = launch_bwd<4>(tm_act, tm_do, tm_cp, tm_dp, a, nclusters, smem, st);
+    else rc = launch_bwd<8>(tm_act, tm_do, tm_cp, tm_dp, a, nclusters, smem, st);
     if (rc != 0) return 1;  // the forward's activations live in this family's format: no fallback possible
   }
   if (rc != 0) {
