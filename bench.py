@@ -62,8 +62,8 @@ def load_peaks():
 # dram__bytes_read.sum + dram__bytes_write.sum per launch of the dominant kernel, from the `ncu --set full` captures
 # summarised in profiles/r01_ncu_summary_bf16.md (1 GPU, full batch)
 NCU_TRAFFIC = {
-    ("train_h512_l3_b800", "bf16", "rnn_bwd"): 1.968596e9 + 0.971763e9,
-    ("train_h512_l3_b800", "bf16", "rnn_fwd"): 1.985982e9 + 1.931351e9,
+    ("train_h512_l3_b800", "bf16", "rnn_bwd"): 1.968534e9 + 0.986176e9,
+    ("train_h512_l3_b800", "bf16", "rnn_fwd"): 1.001468e9 + 1.927235e9,
 }
 
 
@@ -187,7 +187,10 @@ def run_reference(args, w):
     unit, cores, sample = info
     metric = "train_stroke_steps_per_sec" if w["kind"] == "train" else "sampled_sketches_per_sec"
     line = {"impl": "reference", "metric": metric, "value": value, "unit": unit, "n_gpus": args.gpus,
-            "steps": args.steps, "warmup": args.warmup, "ms_per_step": None, "higher_is_better": True,
+            "steps": args.steps, "warmup": args.warmup,
+            # one step of the full workload at the sampled rate (each timed step is the bounded sample in `sample`)
+            "ms_per_step": (w["B"] * (w["T"] if w["kind"] == "train" else 1)) / value * 1e3,
+            "higher_is_better": True,
             "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": workload_config(args, w),
             "cpu_baseline": {"value": value, "unit": unit, "cores": cores, "kind": "port", "sample": sample},
