@@ -793,7 +793,7 @@ lstm_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm_acts, const __grid_con
   extern __shared__ uint8_t smem_raw[];
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   uint8_t *gbase = smem_raw + (base - smem_u32(smem_raw));
-  const int H = a.H, G = a.G, B = a.B, T = a.T, CS = a.CS;
+  const int H = a.H, B = a.B, T = a.T, CS = a.CS;
   const int nmt = (H + 127) / 128;                 // accumulator m-tiles (all hidden units)
   const int HP = nmt * 128;
   const uint32_t s_w = base;                       // 2 k-blocks x [HP rows][128 B]
@@ -1090,7 +1090,7 @@ lstm_bwd_pp_kernel(const __grid_constant__ CUtensorMap tm_acts, const __grid_con
   extern __shared__ uint8_t smem_raw[];
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   uint8_t *gbase = smem_raw + (base - smem_u32(smem_raw));
-  const int H = a.H, G = a.G, B = a.B, T = a.T, CS = a.CS;
+  const int H = a.H, B = a.B, T = a.T, CS = a.CS;
   const int nmt = (H + 127) / 128;
   const int HP = nmt * 128;
   const uint32_t half_bytes = (uint32_t)N2 * 768u;  // per half: d(pre) operand 256 B/row, activations 256, d(out) 128, c 128
