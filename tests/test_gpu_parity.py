@@ -419,3 +419,34 @@ def test_bf16_in_kernel_dropout_is_shard_invariant():
         acc = acc + h.grads_tensor().cpu().numpy()
     assert rel_err(acc, g_full) < 2e-3  # same mask, same bf16 roundings row by row; only sum order differs
     h.close()
+
+
+def test_bf16_training_tracks_fp32_over_many_steps():
+    """Twenty train steps (loss_grad + clip + Adam, state carried, in-kernel dropout) on the bf16 tensor-core path and
+    on the fp32 path from the same initialisation: the loss trajectories and the final weights stay together.  This
+    runs the whole step orchestration repeatedly (side-stream weight gradients, d(pre) double buffering, the
+    interleaved weight copies being refreshed after every update)."""
+    import torch
+    cfg = so.Config(model="lstm", rnn_size=256, num_layers=3, num_mixture=8, batch_size=72, seq_length=24, keep_prob=0.9)
+    params = so.init_params(cfg, seed=4, trained_like=True)
+    x, y = so.synthetic_batch(72, 24, seed=5, p_eoc=0.05)
+    traj = {}
+    final = {}
+    for prec in ("f32", "bf16"):
+        h = make_handle(cfg, params, 72, 24, precision=prec)
+        st = stack_state(so.zero_state(cfg, 72))
+        ls = []
+        for step in range(20):
+            losses, st_t = h.loss_grad(x, y, st, seed=100 + step)
+            h.apply_clip_adam(0.005)
+            st = st_t
+            ls.append(float(losses[0]))
+        torch.cuda.synchronize()
+        traj[prec] = np.array(ls)
+        final[prec] = h.get_params_dict()
+        h.close()
+    assert traj["f32"][-1] < traj["f32"][0], "training did not reduce the loss"
+    assert np.max(np.abs(traj["bf16"] - traj["f32"]) / np.abs(traj["f32"])) < 2e-2, (traj["bf16"], traj["f32"])
+    for n in final["f32"]:
+        d = np.max(np.abs(final["bf16"][n] - final["f32"][n])) / (np.max(np.abs(final["f32"][n])) + 1e-12)
+        assert d < 5e-2, (n, d)
