@@ -312,7 +312,11 @@ def run_ours(args, w):
     # e2e through the host-buffer entry point: H2D of the step's inputs + D2H of its result inside
     e2e = None
     if w["kind"] == "train" and world == 1:
-        st_host = np.zeros((w["L"], Bl, S), dtype=np.float32)
+        # the caller's buffers are page-locked (the library then copies from them directly)
+        xp_, yp_ = torch.from_numpy(x_host).pin_memory(), torch.from_numpy(y_host).pin_memory()
+        x_host, y_host = xp_.numpy(), yp_.numpy()
+        stp_ = torch.zeros((w["L"], Bl, S), dtype=torch.float32).pin_memory()
+        st_host = stp_.numpy()
         for i in range(2):
             h.train_step_host(x_host, y_host, st_host, lr, seed=i)
         torch.cuda.synchronize()

@@ -128,7 +128,8 @@ SKRNN_API int skrnn_apply_clip_adam(skrnn_handle *h, float lr, float *gnorm_out_
 /* One sess.run([cost, cost_shape, cost_pen, final_state, train_op], feed) (train.py:85-86)
  * with HOST buffers: copies x/y/state in, runs loss_grad + clip + Adam, copies the three
  * losses and final_state back, and synchronises.  state_host [L,B,S] is updated in place
- * (the state carry of train.py:85-86). */
+ * (the state carry of train.py:85-86).  Page-locked (cudaHostAlloc / cudaHostRegister) buffers are
+ * copied from and to directly; pageable ones are staged through pinned memory owned by the handle. */
 SKRNN_API int skrnn_train_step_host(skrnn_handle *h, int32_t B, int32_t T, const float *x_host,
                           const float *y_host, float *state_host, float lr, uint64_t seed,
                           float *losses_host);

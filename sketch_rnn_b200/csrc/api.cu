@@ -624,20 +624,29 @@ int skrnn_train_step_host(skrnn_handle *h, int32_t B, int32_t T, const float *x_
     SK_CUDA(cudaMallocHost(&h->pin_loss, 4 * sizeof(float)));
   }
   cudaStream_t st = 0;
-  memcpy(h->pin_x, x_host, rows * 5 * sizeof(float));
-  memcpy(h->pin_y, y_host, rows * 5 * sizeof(float));
-  memcpy(h->pin_state, state_host, nstate * sizeof(float));
-  SK_CUDA(cudaMemcpyAsync(h->st_x, h->pin_x, rows * 5 * sizeof(float), cudaMemcpyHostToDevice, st));
-  SK_CUDA(cudaMemcpyAsync(h->st_y, h->pin_y, rows * 5 * sizeof(float), cudaMemcpyHostToDevice, st));
-  SK_CUDA(cudaMemcpyAsync(h->st_state, h->pin_state, nstate * sizeof(float), cudaMemcpyHostToDevice, st));
+  // page-locked caller buffers are copied from directly; pageable ones go through the handle's pinned staging
+  auto pinned = [](const void *p) {
+    cudaPointerAttributes at;
+    if (cudaPointerGetAttributes(&at, p) != cudaSuccess) { cudaGetLastError(); return false; }
+    return at.type == cudaMemoryTypeHost;
+  };
+  const float *src_x = x_host, *src_y = y_host;
+  float *io_state = state_host;
+  if (!pinned(x_host)) { memcpy(h->pin_x, x_host, rows * 5 * sizeof(float)); src_x = h->pin_x; }
+  if (!pinned(y_host)) { memcpy(h->pin_y, y_host, rows * 5 * sizeof(float)); src_y = h->pin_y; }
+  const bool state_pinned = pinned(state_host);
+  if (!state_pinned) { memcpy(h->pin_state, state_host, nstate * sizeof(float)); io_state = h->pin_state; }
+  SK_CUDA(cudaMemcpyAsync(h->st_x, src_x, rows * 5 * sizeof(float), cudaMemcpyHostToDevice, st));
+  SK_CUDA(cudaMemcpyAsync(h->st_y, src_y, rows * 5 * sizeof(float), cudaMemcpyHostToDevice, st));
+  SK_CUDA(cudaMemcpyAsync(h->st_state, io_state, nstate * sizeof(float), cudaMemcpyHostToDevice, st));
   SK_TRY(skrnn_loss_grad(h, B, T, h->st_x, h->st_y, h->st_state, nullptr, seed, 0, rows, h->st_loss,
                          h->st_state, st));
   SK_TRY(sk_clip_adam(h, st, lr, h->st_loss + 3));
   SK_CUDA(cudaMemcpyAsync(h->pin_loss, h->st_loss, 4 * sizeof(float), cudaMemcpyDeviceToHost, st));
-  SK_CUDA(cudaMemcpyAsync(h->pin_state, h->st_state, nstate * sizeof(float), cudaMemcpyDeviceToHost, st));
+  SK_CUDA(cudaMemcpyAsync(io_state, h->st_state, nstate * sizeof(float), cudaMemcpyDeviceToHost, st));
   SK_CUDA(cudaStreamSynchronize(st));
   memcpy(losses_host, h->pin_loss, 3 * sizeof(float));
-  memcpy(state_host, h->pin_state, nstate * sizeof(float));
+  if (!state_pinned) memcpy(state_host, h->pin_state, nstate * sizeof(float));
   return 0;
 }
 
