@@ -1204,7 +1204,7 @@ lstm_bwd_pp_kernel(const __grid_constant__ CUtensorMap tm_acts, const __grid_con
 #pragma unroll
       for (int s = 0; s < 2; ++s) {
         mbar_wait(bar_rd + 8 * s, step & 1);  // this CTA's partial stores of (s, t) happen before this
-        __threadfence();                      // ... and before the arrivals below, at GPU scope (cumulative)
+        // (no gpu-scope fence: the arrivals below are release operations at cluster scope, cumulative over what the wait above observed)
         if (lane < CS) mbar_arrive_remote(bar_ready + 8 * s, (uint32_t)lane);
         __syncwarp();
       }
