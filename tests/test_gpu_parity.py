@@ -379,7 +379,11 @@ def test_bf16_path_loss_and_gradients(model, H, L, M, B, T):
 
 
 @pytest.mark.parametrize("H,L,B,T", [(32, 1, 1, 1), (64, 2, 3, 2), (128, 2, 17, 5), (256, 1, 129, 3), (256, 2, 300, 4),
-                                     (512, 1, 70, 3), (512, 2, 260, 2), (256, 1, 530, 3), (512, 1, 460, 3)])
+                                     (512, 1, 70, 3), (512, 2, 260, 2), (256, 1, 530, 3), (512, 1, 460, 3),
+                                     # two-half-tile kernels: one timestep, a second half with a single row, every
+                                     # cluster size that can multicast (2, 4, 8, 16 CTAs), exactly full tiles
+                                     (512, 1, 460, 1), (512, 1, 33, 2), (256, 2, 64, 3), (128, 1, 40, 3), (64, 1, 40, 2),
+                                     (512, 1, 128, 2)])
 def test_bf16_tcgen05_recurrent_edge_shapes(H, L, B, T):
     """Shapes that exercise the tcgen05 recurrent kernels' corner cases: one timestep, one row, ragged last
     cluster, several clusters, every cluster size (1..16 CTAs), all batch tiles (16..128 columns; 64 and 128
