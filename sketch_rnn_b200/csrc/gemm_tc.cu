@@ -1,16 +1,19 @@
-// gemm_tc.cu -- bf16 tensor-core GEMM for sm_100a: TMA (cp.async.bulk.tensor) feeds a 3-stage
-// shared-memory ring, one elected thread issues tcgen05.mma with the fp32 accumulator in TMEM, four
-// epilogue warps read it back with tcgen05.ld.  Used by the bf16 path for the hoisted products of
-// the cell stack (reference model.py:77 via TF _linear: X_l * Wx for all timesteps at once), the
-// output projection (model.py:98-99) and every weight / input gradient of model.py:182.
+// gemm_tc.cu -- bf16 tensor-core GEMMs for sm_100a: TMA (cp.async.bulk.tensor) feeds a shared-memory
+// ring, one elected thread issues tcgen05.mma with the fp32 accumulator in TMEM, epilogue warps read it
+// back with tcgen05.ld.  Used by the bf16 path for the hoisted products of the cell stack (reference
+// model.py:77 via TF _linear: X_l * Wx for all timesteps at once), the output projection
+// (model.py:98-99), every weight / input gradient of model.py:182 and the sampler's per-step products.
 //
-//   C[M,N] (+)= A[M,K] * B[K,N] (+ bias[N]),   A, B bf16, C fp32
+//   C[M,N] (+)= A[M,K] * B[K,N] (+ bias[N]),   A, B bf16, C fp32 (or bf16, or none: fused LSTM cell)
 //
 // Either operand may be K-major (K contiguous in memory) or MN-major (M resp. N contiguous); both
 // are loaded with 128-byte-swizzled TMA boxes and described to the tensor core with the matching
 // canonical shared-memory descriptor, so X^T * dY (both operands MN-major, K = B*T rows) needs no
-// transposed copy.  Split-K over blockIdx.z with an atomic fp32 epilogue serves the tall-skinny
-// weight-gradient products.
+// transposed copy.
+//   gemm_tc_kernel          one tile per CTA, split-K over blockIdx.z with an atomic fp32 epilogue
+//                           (weight gradients; 128x128 or 128x256 tiles)
+//   gemm_tc_persist_kernel  one CTA per SM walks the tiles, double-buffered accumulator, C by TMA store
+//                           (fp32 or bf16) or the sampler's LSTM cell update as the epilogue
 #include <stdlib.h>
 
 #include "common.cuh"

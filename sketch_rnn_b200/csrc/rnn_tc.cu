@@ -5,21 +5,27 @@
 //
 // Partition.  A cluster of CS = H/32 CTAs owns N batch rows (N = 16..128); rank r owns hidden units
 // [32r, 32r+32) and keeps the 128 gate columns of those units (row 4u+g <-> unit u, gate g in TF
-// order i,j,f,o) resident in shared memory as a bf16 UMMA operand for the whole launch.
+// order i,j,f,o) resident for the whole launch: in tensor memory as the A operand of the forward
+// product, in shared memory (UMMA K-major, 128B swizzle) for the backward product.
 //
 // Forward step (transposed product, so the MMA M dimension is the 128 gate columns and the batch
 // tile is the flexible N dimension):   D^T[128, N] = Wslice[128, K=H] * h_{t-1}^T[K, N]
-//   * warp 0 issues TMA loads of the h_{t-1} tile (bf16, written by all ranks in the previous step)
-//     and of the hoisted input projection x*Wx+b for this step's gate columns;
-//   * warp 1 issues tcgen05.mma (accumulator in TMEM) k-block by k-block as the loads land;
-//   * warps 2-5 read the accumulator with tcgen05.ld; lane 4u+g holds gate g of unit u, a 3-round
-//     shuffle gives every lane all four gates for its batch columns, then gate nonlinearities, cell
-//     update, eoc reset select and output dropout run in registers and h_t goes back to global memory;
-//   * ranks meet at one barrier.cluster per step.
+//   * warp 0 issues the TMA loads: its share of the h_{t-1} tile (multicast to the whole cluster) and
+//     the hoisted projection x*Wx+b of its 32 units (bf16, four gates of a unit adjacent: xw_il);
+//   * warp 1 issues tcgen05.mma (accumulator in TMEM);
+//   * warps 2-17 read the accumulator with tcgen05.ld; lane 4u+g holds gate g of unit u, a branch-free
+//     4-lane exchange gives every lane all four gates for its batch columns, then gate nonlinearities,
+//     cell update, eoc reset select and output dropout run in registers; the gate activations go to a
+//     bf16 record for BPTT (sign bits of i and f carry the eoc and dropout flags).
 // Backward step: every rank multiplies its own d(pre-activation) slice (K = its 128 gate columns,
-// written to shared memory in the UMMA layout by its epilogue threads) with Wh[:, those columns],
-// giving a partial d(h_{t-1}) for ALL hidden units; partials are exchanged through L2 and summed in a
-// fixed rank order after the cluster barrier.
+// written to shared memory in the UMMA layout by its elementwise threads, and sent to the d(pre) array
+// from there by TMA) with Wh[:, those columns], giving a partial d(h_{t-1}) for ALL hidden units;
+// partials are exchanged as bf16 through L2 and summed in a fixed rank order.
+//
+// Two generations of kernels live here.  lstm_{fwd,bwd}_tc_kernel: one tile per cluster, one
+// barrier.cluster per step (small batches).  lstm_{fwd,bwd}_pp_kernel: two half tiles in flight, no
+// cluster barrier in the loop -- a publisher warp signals every rank's mbarrier through the cluster
+// shared-memory window once the CTA's h_t (forward, TMA-stored) or partials (backward) are out.
 #include <stdlib.h>
 #include <type_traits>
 
