@@ -10,6 +10,7 @@ Workloads (BASELINE.json configs):
   train_kanji         configs[0]: the reference default, 2-layer LSTM 256, batch 100, seq 300
   train_gru / train_rnn   configs[2]
   sample_8192         configs[4]: 8192 concurrent sketches x 300 steps, sharded over N GPUs
+  sample_10           configs[1]: 10 sketches x 300 steps (sample.py's size; bit-exact fp32 persistent kernel, 1 GPU)
 
 One "step" = one full training step (forward, MDN loss, BPTT, global-norm clip, Adam; plus the
 gradient all-reduce when N > 1) over one synthetic batch, or one whole sampling call.  Rank 0
@@ -36,6 +37,7 @@ WORKLOADS = {
     "train_gru": dict(kind="train", model="gru", H=256, L=2, M=24, B=100, T=300),
     "train_rnn": dict(kind="train", model="rnn", H=256, L=2, M=24, B=100, T=300),
     "sample_8192": dict(kind="sample", model="lstm", H=256, L=2, M=24, B=8192, T=300),
+    "sample_10": dict(kind="sample", model="lstm", H=256, L=2, M=24, B=10, T=300),
 }
 
 
