@@ -428,7 +428,8 @@ def run_ours(args, w):
             cb = {"value": v, "unit": u, "cores": cores, "kind": "port", "sample": sample}
         line = {"metric": metric, "value": value, "unit": unit, "n_gpus": world, "steps": args.steps,
                 "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True,
-                "scaling": "strong", "vs_baseline": None, "dtype": args.precision if (w["kind"] == "train" or samp_tc) else "f32", "data": "synthetic",
+                "scaling": "weak" if args.weak else "strong", "vs_baseline": None,
+                "dtype": args.precision if (w["kind"] == "train" or samp_tc) else "f32", "data": "synthetic",
                 "config": workload_config(args, w), "clocks": clk, "e2e": e2e,
                 "gpu_launches": int(launches), "roofline": roof, "cpu_baseline": cb,
                 "last_loss": [float(v) for v in last.float().cpu().numpy()[:3]] if w["kind"] == "train" else None}
@@ -447,8 +448,12 @@ def main():
     ap.add_argument("--workload", default="train_h512_l3_b800", choices=sorted(WORKLOADS))
     ap.add_argument("--precision", default="bf16", choices=["f32", "bf16"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--weak", action="store_true",
+                    help="weak scaling: the workload's batch is the PER-GPU batch (default: it is the global batch)")
     args = ap.parse_args()
-    w = WORKLOADS[args.workload]
+    w = dict(WORKLOADS[args.workload])
+    if args.weak:
+        w["B"] = w["B"] * int(os.environ.get("WORLD_SIZE", "1"))
     if args.impl == "reference":
         run_reference(args, w)
     else:
