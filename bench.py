@@ -38,6 +38,7 @@ WORKLOADS = {
     "train_rnn": dict(kind="train", model="rnn", H=256, L=2, M=24, B=100, T=300),
     "sample_8192": dict(kind="sample", model="lstm", H=256, L=2, M=24, B=8192, T=300),
     "sample_10": dict(kind="sample", model="lstm", H=256, L=2, M=24, B=10, T=300),
+    "train_h512_l3_b100": dict(kind="train", model="lstm", H=512, L=3, M=24, B=100, T=300),  # one rank's share at 8 GPUs
 }
 
 
