@@ -94,6 +94,7 @@ __global__ void __launch_bounds__(512) sample_kernel(SampArgs a) {
           float acc[SB][4];
 #pragma unroll
           for (int r = 0; r < SB; ++r) { acc[r][0] = acc[r][1] = acc[r][2] = acc[r][3] = 0.f; }
+#pragma unroll (SB >= 16 ? 2 : 8)  // weight loads of several k in flight: the chain per accumulator stays sequential
           for (int k = 0; k < K; ++k) {
             const float *wr = W + (size_t)k * (4 * H) + u;
             float w0 = __ldg(wr), w1 = __ldg(wr + H), w2 = __ldg(wr + 2 * H), w3 = __ldg(wr + 3 * H);
@@ -128,6 +129,7 @@ __global__ void __launch_bounds__(512) sample_kernel(SampArgs a) {
           float acc[SB];
 #pragma unroll
           for (int r = 0; r < SB; ++r) acc[r] = 0.f;
+#pragma unroll (SB >= 16 ? 2 : 8)  // weight loads of several k in flight: the chain per accumulator stays sequential
           for (int k = 0; k < K; ++k) {
             float w0 = __ldg(W + (size_t)k * H + u);
 #pragma unroll
@@ -147,6 +149,7 @@ __global__ void __launch_bounds__(512) sample_kernel(SampArgs a) {
         if (act) {  // gates r, u on [x ; h]
 #pragma unroll
           for (int r = 0; r < SB; ++r) { ar[r] = 0.f; az[r] = 0.f; hold[r] = AT[(size_t)(I + u) * SB + r]; }
+#pragma unroll (SB >= 16 ? 2 : 8)  // weight loads of several k in flight: the chain per accumulator stays sequential
           for (int k = 0; k < K; ++k) {
             const float *wr = W + (size_t)k * (2 * H) + u;
             float w0 = __ldg(wr), w1 = __ldg(wr + H);
@@ -176,6 +179,7 @@ __global__ void __launch_bounds__(512) sample_kernel(SampArgs a) {
           float ac[SB];
 #pragma unroll
           for (int r = 0; r < SB; ++r) ac[r] = 0.f;
+#pragma unroll (SB >= 16 ? 2 : 8)  // weight loads of several k in flight: the chain per accumulator stays sequential
           for (int k = 0; k < K; ++k) {
             float w0 = __ldg(Wc + (size_t)k * H + u);
 #pragma unroll
@@ -200,6 +204,7 @@ __global__ void __launch_bounds__(512) sample_kernel(SampArgs a) {
         float acc[SB];
 #pragma unroll
         for (int r = 0; r < SB; ++r) acc[r] = 0.f;
+#pragma unroll (SB >= 16 ? 2 : 8)  // weight loads of several k in flight: the chain per accumulator stays sequential
         for (int k = 0; k < H; ++k) {
           float w0 = __ldg(Wo + (size_t)k * NOUT + j);
 #pragma unroll
