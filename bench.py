@@ -418,6 +418,8 @@ def run_ours(args, w):
                     "traffic": NCU_TRAFFIC.get((args.workload, args.precision, dom)) if world == 1 else None,
                     "kernel": dom, "launch_ms": dur_ms, "launches_per_step": n_dom,
                     "algorithmic_flops_per_launch": fpl,
+                    # recurrent kernels: one launch = T dependent steps; their per-step latency is the figure to watch
+                    "per_timestep_us": (dur_ms * 1e3 / T) if dom in ("rnn_fwd", "rnn_bwd") else None,
                     "peak_source": ("MEASURED_PEAKS.json bf16 sustained (%s)" % peaks["src"]) if (tc and dom != "sampler") else
                     "fp32 CUDA-core nominal 148 SM x 128 lanes x 2 x 1.965 GHz (this kernel runs no tensor-core math)",
                     "note": "persistent recurrent kernels are bound by per-timestep latency and the L2 exchange of h / d(h), "
