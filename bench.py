@@ -225,8 +225,7 @@ def act_mb(w):
 def run_ours(args, w):
     import torch
     import torch.distributed as dist
-    from oracle import sketch_oracle as so   # synthetic inputs + initialiser only (not timed)
-    from sketch_rnn_b200 import _lib, dp
+    from sketch_rnn_b200 import _lib, dp, utils   # the GPU arm never touches oracle/
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -239,13 +238,10 @@ def run_ours(args, w):
     assert w["B"] % world == 0
     Bl = w["B"] // world
     T = w["T"]
-    cfg = so.Config(model=w["model"], rnn_size=w["H"], num_layers=w["L"], num_mixture=w["M"],
-                    batch_size=w["B"], seq_length=T, keep_prob=0.8)
-    params = so.init_params(cfg, seed=0)
     h = _lib.Handle(model=w["model"], rnn_size=w["H"], num_layers=w["L"], num_mixture=w["M"],
                     batch_size=Bl if w["kind"] == "train" else 0, seq_length=T if w["kind"] == "train" else 0,
                     keep_prob=0.8, precision=args.precision, device=local)
-    h.set_params_dict(params)
+    h.set_params(utils.default_init(h, seed=0))
     S = h.S
     peaks = load_peaks()
     clocks = ClockSampler(local)
@@ -257,7 +253,7 @@ def run_ours(args, w):
 
     lr = 0.005
     if w["kind"] == "train":
-        xg, yg = so.synthetic_batch(w["B"], T, seed=1)
+        xg, yg = utils.synthetic_batch(w["B"], T, seed=1)
         x_host = np.ascontiguousarray(xg[rank * Bl:(rank + 1) * Bl])
         y_host = np.ascontiguousarray(yg[rank * Bl:(rank + 1) * Bl])
         x = torch.from_numpy(x_host).to(dev)

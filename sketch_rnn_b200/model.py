@@ -20,6 +20,7 @@ import pickle
 import numpy as np
 
 from . import _lib
+from . import utils
 
 
 class Fetch(object):
@@ -81,17 +82,7 @@ class Model(object):
     def initialize_all_variables(self, seed=0):
         """tf.initialize_all_variables(): TF 0.x default initialiser (uniform_unit_scaling, +-sqrt(3/fan_in));
         _linear biases start at zero except the GRU gate bias (1.0); Adam slots zero."""
-        rng = np.random.RandomState(seed)
-        flat = np.zeros(self.handle.P, dtype=np.float32)
-        for name, off, shape in self.handle.tensors():
-            n = int(np.prod(shape))
-            if name.endswith("/Bias"):
-                v = np.full(n, 1.0 if "Gates" in name else 0.0)
-            else:
-                fan_in = float(np.prod(shape[:-1])) if len(shape) > 1 else 1.0
-                lim = math.sqrt(3.0 / fan_in)
-                v = rng.uniform(-lim, lim, size=n)
-            flat[off:off + n] = v
+        flat = utils.default_init(self.handle, seed)
         self.handle.set_params(flat)
         self.handle.set_adam_state(np.zeros_like(flat), np.zeros_like(flat), 0.9, 0.999)
         self.lr = 0.01

@@ -195,3 +195,37 @@ def make_synthetic_dataset(path, num_sketches=200, seed=0):
     with open(path, "wb") as f:
         pickle.dump(sketches, f, protocol=2)
     return path
+
+
+def default_init(handle, seed=0):
+    """Flat fp32 parameter vector from TF 0.x's default initialiser (uniform_unit_scaling, +-sqrt(3/fan_in);
+    _linear biases zero, GRU gate bias 1.0) for the tensors of `handle` -- what tf.initialize_all_variables()
+    gives the reference graph (model.py:46-47 and the cells of model.py:14-27)."""
+    import math
+    rng = np.random.RandomState(seed)
+    flat = np.zeros(handle.P, dtype=np.float32)
+    for name, off, shape in handle.tensors():
+        n = int(np.prod(shape))
+        if name.endswith("/Bias"):
+            v = np.full(n, 1.0 if "Gates" in name else 0.0)
+        else:
+            fan_in = float(np.prod(shape[:-1])) if len(shape) > 1 else 1.0
+            lim = math.sqrt(3.0 / fan_in)
+            v = rng.uniform(-lim, lim, size=n)
+        flat[off:off + n] = v
+    return flat
+
+
+def synthetic_batch(B, T, seed=0, p_eos=0.10, p_eoc=0.015):
+    """Seeded stand-in for SketchLoader.next_batch output: offsets ~ N(0, 0.5^2), pen state one-hot
+    with P(eos, eoc, cont) = (0.10, 0.015, 0.885), targets = inputs shifted by one point.  Returns x, y [B,T,5]."""
+    rng = np.random.RandomState(seed)
+    seq = np.zeros((B, T + 1, 5), dtype=np.float64)
+    seq[:, :, 0:2] = rng.normal(0.0, 0.5, size=(B, T + 1, 2))
+    u = rng.rand(B, T + 1)
+    pen = np.where(u < p_eoc, 1, np.where(u < p_eoc + p_eos, 0, 2))
+    for k in range(3):
+        seq[:, :, 2 + k] = pen == k
+    seq = seq.astype(np.float32)
+    return np.ascontiguousarray(seq[:, :-1]), np.ascontiguousarray(seq[:, 1:])
+
