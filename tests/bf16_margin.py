@@ -1,4 +1,4 @@
-# bf16 path error levels against the fp64 oracle (margin to the 2e-2 tolerance): python tools/bf16_margin.py
+# bf16 path error levels against the fp64 oracle (margin to the 2e-2 tolerance): python tests/bf16_margin.py
 import os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np

@@ -2,14 +2,12 @@
 import os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np, torch
-from oracle import sketch_oracle as so
-from sketch_rnn_b200 import _lib
+from sketch_rnn_b200 import _lib, utils
 H, L, B, T = [int(v) for v in sys.argv[1:5]]
 prec = sys.argv[5] if len(sys.argv) > 5 else "bf16"
-cfg = so.Config(model="lstm", rnn_size=H, num_layers=L, num_mixture=24)
 h = _lib.Handle(model="lstm", rnn_size=H, num_layers=L, num_mixture=24, batch_size=B, seq_length=T, keep_prob=0.8, precision=prec)
-h.set_params_dict(so.init_params(cfg, seed=0))
-x, y = so.synthetic_batch(B, T, seed=1)
+h.set_params(utils.default_init(h, seed=0))
+x, y = utils.synthetic_batch(B, T, seed=1)
 st = torch.zeros((L, B, h.S), device="cuda")
 for i in range(2):
     losses, _ = h.loss_grad(x, y, st, seed=i)

@@ -3,17 +3,15 @@
 import os, sys, time
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np, torch
-from oracle import sketch_oracle as so
-from sketch_rnn_b200 import _lib
+from sketch_rnn_b200 import _lib, utils
 
 steps = int(sys.argv[1]) if len(sys.argv) > 1 else 200
 for (H, L, B, T) in [(512, 3, 800, 300), (512, 3, 400, 300), (512, 3, 200, 300), (512, 3, 100, 300), (256, 2, 100, 300),
                      (256, 2, 777, 120), (128, 2, 300, 64), (64, 2, 90, 50)]:
-    cfg = so.Config(model="lstm", rnn_size=H, num_layers=L, num_mixture=24, batch_size=B, seq_length=T, keep_prob=0.8)
     h = _lib.Handle(model="lstm", rnn_size=H, num_layers=L, num_mixture=24, batch_size=B, seq_length=T, keep_prob=0.8,
                     precision="bf16")
-    h.set_params_dict(so.init_params(cfg, seed=0))
-    x, y = so.synthetic_batch(B, T, seed=1)
+    h.set_params(utils.default_init(h, seed=0))
+    x, y = utils.synthetic_batch(B, T, seed=1)
     x = torch.from_numpy(x).cuda(); y = torch.from_numpy(y).cuda()
     st = torch.zeros((L, B, h.S), device="cuda")
     t0 = time.time()
