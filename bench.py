@@ -25,6 +25,13 @@ import sys
 import threading
 import time
 
+# The CPU legs use every host core.  torch.distributed.run exports OMP_NUM_THREADS=1 to its workers when more than
+# one is launched, and the BLAS behind NumPy reads that variable when NumPy is first imported: put the real core
+# count back BEFORE the import (the thread count actually used is printed with every CPU number).
+if "reference" in sys.argv or os.environ.get("WORLD_SIZE", "1") == "1":
+    for _v in ("OMP_NUM_THREADS", "OPENBLAS_NUM_THREADS", "MKL_NUM_THREADS"):
+        os.environ[_v] = str(os.cpu_count() or 1)
+
 import numpy as np
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
@@ -62,12 +69,14 @@ def load_peaks():
     return dict(hbm=6650.0, tc_burst=1590.0, tc_sustained=1400.0, src="fallback")
 
 
-# dram__bytes_read.sum + dram__bytes_write.sum per launch of the dominant kernel, from the `ncu --set full` captures
-# summarised in profiles/r01_ncu_summary_bf16.md (1 GPU, full batch)
-NCU_TRAFFIC = {
-    ("train_h512_l3_b800", "bf16", "rnn_bwd"): 1.968534e9 + 0.986176e9,
-    ("train_h512_l3_b800", "bf16", "rnn_fwd"): 1.001468e9 + 1.927235e9,
-}
+def ncu_traffic(workload, precision, kernel):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of `kernel`, from the `ncu --set full` captures
+    summarised under profiles/ (profiles/ncu_traffic.json names the capture each figure comes from)."""
+    p = os.path.join(ROOT, "profiles", "ncu_traffic.json")
+    if not os.path.exists(p):
+        return None
+    e = json.load(open(p)).get("%s/%s/%s" % (workload, precision, kernel))
+    return float(e["dram_bytes_per_launch"]) if e else None
 
 
 class ClockSampler(threading.Thread):
@@ -142,62 +151,91 @@ class ClockSampler(threading.Thread):
 # --------------------------------------------------------------------------------------------
 # CPU arm: the oracle (NumPy restatement of the reference graph) on the host cores
 # --------------------------------------------------------------------------------------------
-def cpu_baseline(w, max_rows=None):
-    """Times the oracle on a bounded sample of the workload. Returns (value, unit, cores, sample)."""
+CPU_SAMPLE_ROWS = 100   # batch rows of the workload the CPU legs time (config 4 has 800; 100 rows x 300 steps ~ 8 s)
+
+
+def blas_threads():
+    """Threads the BLAS behind NumPy will really use (not what we hoped for)."""
+    try:
+        import threadpoolctl
+        n = [i.get("num_threads", 1) for i in threadpoolctl.threadpool_info() if i.get("user_api") == "blas"]
+        return int(max(n)) if n else 1
+    except Exception:
+        return None
+
+
+def cpu_baseline(w, inputs=None):
+    """Times the oracle on a bounded sample of the workload and returns the `cpu_baseline` object.
+    inputs = (flat_params, x_rows, y_rows, mask_rows) from the GPU arm: the CPU step then runs on exactly those rows
+    with exactly those weights, and its losses come back under "losses" for bench.py's loss check."""
     from oracle import sketch_oracle as so
-    cores = os.cpu_count() or 1
     cfg = so.Config(model=w["model"], rnn_size=w["H"], num_layers=w["L"], num_mixture=w["M"],
                     batch_size=w["B"], seq_length=w["T"], keep_prob=0.8)
-    params = so.init_params(cfg, seed=0)
+    nthr = blas_threads()
     if w["kind"] == "train":
-        # ~10-30 s of CPU work: scale the batch rows down, keep T and the model
-        Bs = max_rows or max(4, min(w["B"], int(2.0e11 / (3.0 * fwd_flops_per_stroke_step(w) * w["T"]))))
-        x, y = so.synthetic_batch(Bs, w["T"], seed=1)
-        mask = so.synthetic_dropout_mask(cfg, Bs, w["T"])
+        if inputs is not None:
+            flat, x, y, mask = inputs
+            params = so.unflatten(cfg, np.asarray(flat, dtype=np.float32))
+            Bs = x.shape[0]
+        else:
+            Bs = min(w["B"], CPU_SAMPLE_ROWS)
+            params = so.init_params(cfg, seed=0)
+            x, y = so.synthetic_batch(Bs, w["T"], seed=1)
+            mask = so.synthetic_dropout_mask(cfg, Bs, w["T"])
         opt = so.AdamState(cfg)
         st = so.zero_state(cfg, Bs)
         t0 = time.time()
-        so.train_step(cfg, params, opt, x, y, st, 0.005, mask)
+        losses, _, _ = so.train_step(cfg, params, opt, x, y, st, 0.005, mask)
         dt = time.time() - t0
-        return Bs * w["T"] / dt, "stroke-steps/s", cores, \
-            "1 oracle train step on %d of %d batch rows x %d steps (NumPy fp32, BLAS threads=all)" % (Bs, w["B"], w["T"])
+        out = {"value": Bs * w["T"] / dt, "unit": "stroke-steps/s", "cores": nthr or 1, "kind": "port",
+               "sample": "1 oracle train step (fwd + BPTT + clip + Adam) on %d of %d batch rows x %d steps, NumPy fp32, "
+                         "%s BLAS threads on %d host cores" % (Bs, w["B"], w["T"], nthr, os.cpu_count() or 1),
+               "host_cores": os.cpu_count() or 1, "blas_threads": nthr, "sample_seconds": dt,
+               "losses": [float(v) for v in losses]}
+        if Bs < w["B"]:
+            out["extrapolated_from_rows"] = Bs   # the rate of a Bs-row step stands for the B-row step
+        return out
     from oracle import sampler_ref
+    params = so.init_params(cfg, seed=0)
     ns, steps = 2, w["T"]
     u = np.random.RandomState(1).rand(ns, steps, 4).astype(np.float32)
     t0 = time.time()
     for i in range(ns):
         sampler_ref.sample(cfg, params, u[i], steps, 0.1, 0.1, False)
     dt = time.time() - t0
-    return ns / dt, "sketches/s", 1, "%d sketches x %d steps through oracle/sampler_ref.c (scalar C, 1 thread)" % (ns, steps)
+    return {"value": ns / dt, "unit": "sketches/s", "cores": 1, "kind": "port",
+            "sample": "%d sketches x %d steps through oracle/sampler_ref.c (scalar C, 1 thread)" % (ns, steps),
+            "host_cores": os.cpu_count() or 1, "sample_seconds": dt, "extrapolated_from_rows": ns}
 
 
 def run_reference(args, w):
     """--impl reference: the reference's own path cannot run (Python 2 + TensorFlow 0.x); the
-    timed stand-in is the oracle port of its graph on the host cores, same config and metric."""
+    timed stand-in is the oracle port of its graph on the host cores, same config and metric.
+    Each "step" is one bounded sample (CPU_SAMPLE_ROWS batch rows of the workload, all T timesteps)."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
     vals = []
-    info = None
-    for i in range(max(1, args.warmup > 0) + args.steps):
-        v, unit, cores, sample = cpu_baseline(w)
-        info = (unit, cores, sample)
-        if i >= (1 if args.warmup > 0 else 0):
-            vals.append(v)
-        if len(vals) >= args.steps:
-            break
+    cb = None
+    nwarm = 1 if args.warmup > 0 else 0
+    for i in range(nwarm + args.steps):
+        cb = cpu_baseline(w)
+        if i >= nwarm:
+            vals.append(cb["value"])
     value = float(np.median(vals))
-    unit, cores, sample = info
+    cb["value"] = value
+    cb.pop("losses", None)
     metric = "train_stroke_steps_per_sec" if w["kind"] == "train" else "sampled_sketches_per_sec"
-    line = {"impl": "reference", "metric": metric, "value": value, "unit": unit, "n_gpus": args.gpus,
+    line = {"impl": "reference", "metric": metric, "value": value, "unit": cb["unit"], "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup,
-            # one step of the full workload at the sampled rate (each timed step is the bounded sample in `sample`)
+            # one step of the FULL workload at the sampled rate (each timed step is the bounded sample in `sample`)
             "ms_per_step": (w["B"] * (w["T"] if w["kind"] == "train" else 1)) / value * 1e3,
+            "ms_per_sampled_step": float(np.median([cb["sample_seconds"]])) * 1e3,
             "higher_is_better": True,
             "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": workload_config(args, w),
-            "cpu_baseline": {"value": value, "unit": unit, "cores": cores, "kind": "port", "sample": sample},
-            "e2e": {"value": value, "unit": unit, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+            "cpu_baseline": cb,
+            "e2e": {"value": value, "unit": cb["unit"], "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line))
 
 
@@ -217,6 +255,106 @@ def workload_config(args, w):
 def act_mb(w):
     ng = {"lstm": 4, "gru": 3, "rnn": 1}[w["model"]]
     return w["B"] * w["T"] * w["L"] * (ng + 3) * w["H"] * 4 / 1e6
+
+
+# --------------------------------------------------------------------------------------------
+# loss check: the GPU arm's losses on its first rows against the oracle on the same rows and weights
+# --------------------------------------------------------------------------------------------
+def gpu_slice_losses(h, w, x_rows, y_rows, mask_rows):
+    """cost / cost_shape / cost_pen of the handle on `x_rows` from a zero state with an injected dropout mask."""
+    import torch
+    R, T = x_rows.shape[0], x_rows.shape[1]
+    st = torch.zeros((w["L"], R, h.S), dtype=torch.float32, device="cuda:%d" % h.device)
+    losses, _ = h.loss_grad(x_rows, y_rows, st, dropout_mask=mask_rows, loss_rows=R * T)
+    return [float(v) for v in losses.cpu().numpy()]
+
+
+def compare_losses(gpu, oracle, precision):
+    tol = 1e-4 if precision == "f32" else 2e-2
+    rel = max(abs(g - o) / abs(o) for g, o in zip(gpu, oracle))
+    return {"gpu": gpu, "oracle": oracle, "rel_err": rel, "tolerance": tol, "ok": bool(rel < tol)}
+
+
+def loss_check(w, precision, rows=CPU_SAMPLE_ROWS):
+    """Stand-alone form of the check run_ours makes (used by tests/): build the workload's handle, take the losses
+    of its first `rows` rows on the GPU, run the oracle on the same rows and weights, compare."""
+    from sketch_rnn_b200 import _lib, utils
+    R = min(rows, w["B"])
+    h = _lib.Handle(model=w["model"], rnn_size=w["H"], num_layers=w["L"], num_mixture=w["M"], batch_size=R,
+                    seq_length=w["T"], keep_prob=0.8, precision=precision)
+    flat = utils.default_init(h, seed=0)
+    h.set_params(flat)
+    x, y = utils.synthetic_batch(w["B"], w["T"], seed=1)
+    mask = utils.synthetic_dropout_mask(R, w["T"], w["H"], 0.8, seed=2)
+    gpu = gpu_slice_losses(h, w, x[:R], y[:R], mask)
+    h.close()
+    cb = cpu_baseline(w, inputs=(flat, x[:R], y[:R], mask))
+    out = compare_losses(gpu, cb["losses"], precision)
+    out["rows"] = R
+    return out
+
+
+# --------------------------------------------------------------------------------------------
+# sampling block of the default line (BASELINE configs 2 and 5 next to the training metric)
+# --------------------------------------------------------------------------------------------
+def sampling_block(world, rank, local):
+    """sketches/s of Model.sample's replacement: config 5 (8192 sketches x 300 steps sharded over the ranks) on the
+    bit-exact fp32 kernel and on the bf16 tensor-core sampler, and config 2's size (10 sketches, rank 0 only).
+    CUDA-event times, max over ranks."""
+    import torch
+    import torch.distributed as dist
+    from sketch_rnn_b200 import _lib, utils
+    dev = torch.device("cuda:%d" % local)
+    out = {}
+
+    def timed(h, n, iters, warm, **kw):
+        for i in range(warm):
+            h.sample(n, 300, 0.1, 0.1, False, seed=i, **kw)
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for i in range(iters):
+            h.sample(n, 300, 0.1, 0.1, False, seed=100 + i, **kw)
+        e1.record()
+        torch.cuda.synchronize()
+        t = torch.tensor([e0.elapsed_time(e1) / iters], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    n = 8192 // world
+    for prec, key, iters in (("bf16", "config5_bf16", 5), ("f32", "config5_exact", 2)):
+        h = _lib.Handle(model="lstm", rnn_size=256, num_layers=2, num_mixture=24, precision=prec, device=local)
+        h.set_params(utils.default_init(h, seed=0))
+        l0 = h.launch_count()
+        ms = timed(h, n, iters, 2, sketch0=rank * n)
+        out[key] = {"sketches_per_sec": 8192 / (ms * 1e-3), "ms": ms, "n_sketches": 8192, "steps": 300,
+                    "sketches_per_gpu": n, "bit_exact": prec == "f32",
+                    "launches_per_call": (h.launch_count() - l0) // (iters + 2),
+                    "kernel": "sample_kernel (persistent, fp32, bit-exact)" if prec == "f32" else
+                              "tcgen05 gate GEMM with fused cell update + draw kernel, CUDA-graph replay"}
+        if prec == "f32" and rank == 0:
+            # config 2's size: sample.py draws 10 sketches from one model
+            ms10 = None
+            for i in range(2):
+                h.sample(10, 300, 0.1, 0.1, False, seed=i)
+            torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for i in range(5):
+                h.sample(10, 300, 0.1, 0.1, False, seed=50 + i)
+            e1.record()
+            torch.cuda.synchronize()
+            ms10 = e0.elapsed_time(e1) / 5
+            out["config2_size"] = {"sketches_per_sec": 10 / (ms10 * 1e-3), "ms": ms10, "n_sketches": 10, "steps": 300,
+                                   "bit_exact": True, "note": "synthetic weights (save/kanji/model.ckpt-0 is absent); "
+                                   "fixed 300 steps, no early stop"}
+        h.close()
+    flop = 1.0 * fwd_flops_per_stroke_step(WORKLOADS["sample_8192"]) * 8192 * 300
+    out["config5_bf16"]["tflops"] = flop / (out["config5_bf16"]["ms"] * 1e-3) / 1e12 / world
+    return out
 
 
 # --------------------------------------------------------------------------------------------
@@ -252,6 +390,7 @@ def run_ours(args, w):
         torch.cuda.synchronize()
 
     lr = 0.005
+    timing = None
     if w["kind"] == "train":
         xg, yg = utils.synthetic_batch(w["B"], T, seed=1)
         x_host = np.ascontiguousarray(xg[rank * Bl:(rank + 1) * Bl])
@@ -260,10 +399,18 @@ def run_ours(args, w):
         y = torch.from_numpy(y_host).to(dev)
         state = torch.zeros((w["L"], Bl, S), dtype=torch.float32, device=dev)
         loss_rows = w["B"] * T
+        check_inputs = check_gpu = None
+        if rank == 0 and world == 1 and not args.no_cpu:
+            # loss check, GPU half: the first rows of the batch with the initial weights and an injected mask; the
+            # cpu_baseline leg below runs the oracle on exactly these and the two sets of losses are compared
+            R = min(Bl, CPU_SAMPLE_ROWS)
+            mask_rows = utils.synthetic_dropout_mask(R, T, w["H"], 0.8, seed=2)
+            check_inputs = (h.get_params(), x_host[:R], y_host[:R], mask_rows)
+            check_gpu = gpu_slice_losses(h, w, x_host[:R], y_host[:R], mask_rows)
 
         def step(i):
             nonlocal state
-            losses, state = dp.dp_train_step(h, x, y, state, lr, 1000 + i, rank * Bl, loss_rows)
+            losses, state = dp.dp_train_step(h, x, y, state, lr, 1000 + i, rank * Bl, loss_rows, timing=timing)
             return losses
 
         units_per_step = w["B"] * T
@@ -300,50 +447,54 @@ def run_ours(args, w):
     # per-category kernel time, measured live with CUDA events around every launch (separate pass,
     # so the event overhead is not inside the headline number)
     h.profile_enable(True)
-    for i in range(min(args.steps, 3)):
+    nprof = min(args.steps, 3)
+    if w["kind"] == "train" and world > 1:
+        timing = {}
+    for i in range(nprof):
         step(args.warmup + args.steps + i)
     prof = h.profile_read()
     h.profile_enable(False)
-    nprof = min(args.steps, 3)
     kern_ms = {k: v[0] / nprof for k, v in prof.items() if v[1] > 0}
     kern_cnt = {k: v[1] // nprof for k, v in prof.items() if v[1] > 0}
+    if timing:
+        kern_ms["allreduce"] = timing["allreduce_ms"] / nprof   # NCCL, not one of this library's kernels
+        kern_cnt["allreduce"] = 2
+    timing = None
 
     # e2e through the host-buffer entry point: H2D of the step's inputs + D2H of its result inside
     e2e = None
-    if w["kind"] == "train" and world == 1:
-        # the caller's buffers are page-locked (the library then copies from them directly)
-        xp_, yp_ = torch.from_numpy(x_host).pin_memory(), torch.from_numpy(y_host).pin_memory()
-        x_host, y_host = xp_.numpy(), yp_.numpy()
-        stp_ = torch.zeros((w["L"], Bl, S), dtype=torch.float32).pin_memory()
-        st_host = stp_.numpy()
-        for i in range(2):
-            h.train_step_host(x_host, y_host, st_host, lr, seed=i)
-        torch.cuda.synchronize()
-        t0 = time.perf_counter()
-        ne = max(3, min(args.steps, 10))
-        for i in range(ne):
-            h.train_step_host(x_host, y_host, st_host, lr, seed=10 + i)
-        torch.cuda.synchronize()
-        dt = (time.perf_counter() - t0) / ne
-        e2e = {"value": units_per_step / dt, "unit": unit,
-               "h2d_bytes_per_step": int(x_host.nbytes + y_host.nbytes + st_host.nbytes),
-               "d2h_bytes_per_step": int(12 + st_host.nbytes)}
-    elif w["kind"] == "train":
-        # multi-GPU: pinned host batch -> device, step, losses back, all inside the timed region
+    if w["kind"] == "train":
+        # The same host-buffer step at every N (dp.HostStep: pinned host batch -> device, loss_grad, all-reduce when
+        # N > 1, clip + Adam, losses and final state back to pinned host memory), max over ranks.  At N = 1 the
+        # C-ABI's own host entry point skrnn_train_step_host is timed beside it (`c_abi_value`).
         xp, yp = torch.from_numpy(x_host).pin_memory(), torch.from_numpy(y_host).pin_memory()
+        hs = dp.HostStep(h, Bl, T, loss_rows, row0=rank * Bl)
+        ne = max(3, min(args.steps, 10))
+        for i in range(2):
+            hs(xp, yp, lr, 4000 + i)
         barrier()
         t0 = time.perf_counter()
-        ne = max(3, min(args.steps, 10))
         for i in range(ne):
-            x.copy_(xp, non_blocking=True)
-            y.copy_(yp, non_blocking=True)
-            losses = step(5000 + i)
-            losses.cpu()
+            hs(xp, yp, lr, 5000 + i)
         barrier()
         dt = torch.tensor([(time.perf_counter() - t0) / ne], dtype=torch.float64, device=dev)
-        dist.all_reduce(dt, op=dist.ReduceOp.MAX)
+        if world > 1:
+            dist.all_reduce(dt, op=dist.ReduceOp.MAX)
         e2e = {"value": units_per_step / float(dt.item()), "unit": unit,
-               "h2d_bytes_per_step": int(2 * x_host.nbytes) * world, "d2h_bytes_per_step": 12 * world}
+               "h2d_bytes_per_step": int(hs.h2d_bytes) * world, "d2h_bytes_per_step": int(hs.d2h_bytes) * world,
+               "path": "sketch_rnn_b200.dp.HostStep (same call at every N)"}
+        if world == 1:
+            st_host = torch.zeros((w["L"], Bl, S), dtype=torch.float32).pin_memory().numpy()
+            xh, yh = xp.numpy(), yp.numpy()
+            for i in range(2):
+                h.train_step_host(xh, yh, st_host, lr, seed=i)
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            for i in range(ne):
+                h.train_step_host(xh, yh, st_host, lr, seed=10 + i)
+            torch.cuda.synchronize()
+            e2e["c_abi_value"] = units_per_step / ((time.perf_counter() - t0) / ne)
+            e2e["c_abi_path"] = "skrnn_train_step_host"
     else:
         # results land in pinned host buffers (what a serving caller would keep around)
         sh = torch.empty((Bl, T, 5), dtype=torch.float32).pin_memory()
@@ -370,7 +521,8 @@ def run_ours(args, w):
         else:
             flops_step = 1.0 * fl * Bl * T
         # dominant kernel by measured time; its roofline = algorithmic work of ONE launch / its mean duration
-        dom = max(kern_ms, key=kern_ms.get) if kern_ms else None
+        own = {k: v for k, v in kern_ms.items() if k != "allreduce"}
+        dom = max(own, key=own.get) if own else None
         # bf16 sampling of many LSTM sketches runs per-step tcgen05 GEMMs (csrc/sampler_tc.cu)
         samp_tc = (w["kind"] != "train" and args.precision == "bf16" and w["model"] == "lstm" and Bl >= 64
                    and os.environ.get("SKRNN_SAMPLER_EXACT", "0") != "1")
@@ -411,7 +563,7 @@ def run_ours(args, w):
                     "whole_step_tflops": whole, "per_kernel_ms": kern_ms, "per_kernel_launches": kern_cnt}
         else:
             roof = {"bound": "tensor", "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": ach / peak,
-                    "traffic": NCU_TRAFFIC.get((args.workload, args.precision, dom)) if world == 1 else None,
+                    "traffic": ncu_traffic(args.workload, args.precision, dom) if world == 1 else None,
                     "kernel": dom, "launch_ms": dur_ms, "launches_per_step": n_dom,
                     "algorithmic_flops_per_launch": fpl,
                     # recurrent kernels: one launch = T dependent steps; their per-step latency is the figure to watch
@@ -422,18 +574,30 @@ def run_ours(args, w):
                             "not by the tensor pipe: see DESIGN.md section 4 and profiles/",
                     "whole_step_tflops": whole, "per_kernel_ms": kern_ms, "per_kernel_launches": kern_cnt}
         cb = None
+        lcheck = None
         if world == 1 and not args.no_cpu:
-            v, u, cores, sample = cpu_baseline(w)
-            cb = {"value": v, "unit": u, "cores": cores, "kind": "port", "sample": sample}
+            cb = cpu_baseline(w, inputs=check_inputs if w["kind"] == "train" else None)
+            if w["kind"] == "train":
+                lcheck = compare_losses(check_gpu, cb.pop("losses"), args.precision)
+                lcheck["rows"] = int(check_inputs[1].shape[0])
         line = {"metric": metric, "value": value, "unit": unit, "n_gpus": world, "steps": args.steps,
                 "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True,
                 "scaling": "weak" if args.weak else "strong", "vs_baseline": None,
                 "dtype": args.precision if (w["kind"] == "train" or samp_tc) else "f32", "data": "synthetic",
                 "config": workload_config(args, w), "clocks": clk, "e2e": e2e,
                 "gpu_launches": int(launches), "roofline": roof, "cpu_baseline": cb,
-                "last_loss": [float(v) for v in last.float().cpu().numpy()[:3]] if w["kind"] == "train" else None}
-        print(json.dumps(line))
+                "last_loss": [float(v) for v in last.float().cpu().numpy()[:3]] if w["kind"] == "train" else None,
+                "loss_check": lcheck}
     h.close()
+    if w["kind"] == "train" and args.workload == "train_h512_l3_b800" and not args.no_sampling:
+        samp = sampling_block(world, rank, local)
+        if rank == 0:
+            line["sampling"] = samp
+    if rank == 0:
+        print(json.dumps(line))
+        if line.get("loss_check") and not line["loss_check"]["ok"]:
+            sys.stderr.write("bench.py: GPU losses disagree with the oracle on the checked rows: %r\n" % (line["loss_check"],))
+            sys.exit(3)
     if world > 1:
         dist.destroy_process_group()
 
@@ -446,7 +610,8 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="train_h512_l3_b800", choices=sorted(WORKLOADS))
     ap.add_argument("--precision", default="bf16", choices=["f32", "bf16"])
-    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg (and the loss check that rides on it)")
+    ap.add_argument("--no-sampling", action="store_true", help="skip the sampling block of the default line")
     ap.add_argument("--weak", action="store_true",
                     help="weak scaling: the workload's batch is the PER-GPU batch (default: it is the global batch)")
     args = ap.parse_args()

@@ -44,10 +44,15 @@ enum { SKRNN_CELL_LSTM = 0, SKRNN_CELL_GRU = 1, SKRNN_CELL_RNN = 2 };
  * state / master weights / optimiser (2e-2 parity path). */
 enum { SKRNN_PREC_F32 = 0, SKRNN_PREC_BF16 = 1 };
 
+/* Largest args.rnn_size a handle can be created with (a multiple of 8; the reference takes any size).  Every
+ * kernel family keeps a per-CTA slice of the recurrent weights resident on chip and the widest plan ends here;
+ * skrnn_create rejects larger values instead of failing at the first step. */
+#define SKRNN_MAX_RNN_SIZE 512
+
 /* Hyper-parameters Model.__init__ reads from `args` (model.py:8-47,134,182; train.py:13-44). */
 typedef struct skrnn_config {
   int32_t cell;          /* args.model: SKRNN_CELL_*                       (model.py:14-21) */
-  int32_t rnn_size;      /* args.rnn_size  H                                               */
+  int32_t rnn_size;      /* args.rnn_size  H, a multiple of 8, <= SKRNN_MAX_RNN_SIZE       */
   int32_t num_layers;    /* args.num_layers L (reference runs L == 2 only, model.py:82)    */
   int32_t num_mixture;   /* args.num_mixture M; NOUT = 3 + 6M              (model.py:43)   */
   int32_t batch_size;    /* sizing hint: largest B the handle will see                      */
@@ -176,8 +181,11 @@ SKRNN_API int skrnn_profile_read(skrnn_handle *h, double *ms_out, int64_t *count
  * cudaFree or allocating library call.  Every call on a device shares that array and it keeps the
  * previous call's contents; what must start at zero is cleared on `stream` at the start of each
  * call.  Calls that overlap on the GPU race on it: keep them on one stream or otherwise serialise
- * them.  The first call on a device resolves the array's device address and queries the device;
- * issue that first call before beginning any stream capture. */
+ * them -- host threads included, and the first call included: the first call on a device resolves
+ * the array's device address and queries the device (unsynchronised bookkeeping), so issue it from
+ * one thread and before beginning any stream capture.  The call runs on the GPU that owns
+ * params_dev (the caller's current device is put back before returning); `stream` must belong to
+ * that GPU. */
 #define SKRNN_NOALLOC_MAX_PARAMS (8192LL * 4096LL)
 #define SKRNN_NOALLOC_SCRATCH_BYTES (256 + 8192 * 8)
 SKRNN_API int skrnn_clip_adam_noalloc(int64_t n, const float *grads_dev, float *params_dev, float *m_dev,

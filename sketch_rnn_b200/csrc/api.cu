@@ -86,6 +86,25 @@ void free_workspace(SkWorkspace &w) {
     w.out_bf[l] = w.hprev_bf[l] = w.aux_bf[l] = w.acts_bf[l] = w.xw_il[l] = nullptr;
   }
   w.cap_rows = 0;
+  w.f32_acts = false;
+}
+
+// bf16 lstm handles run the tcgen05 recurrent kernels, which keep their own bf16 activation records: the fp32 set
+// (xw, hprev, out: 6 of the 10 GB of config 4) is then dead weight and is only allocated if a layer ever falls back
+bool needs_f32_acts_upfront(const skrnn_handle *h) {
+  return !(h->cfg.precision == SKRNN_PREC_BF16 && sk_rnn_tc_eligible(h));
+}
+
+int alloc_f32_acts(skrnn_handle *h) {
+  SkWorkspace &w = h->ws;
+  if (w.f32_acts || w.cap_rows == 0) return 0;
+  for (int l = 0; l < h->L; ++l) {
+    SK_CUDA(cudaMalloc(&w.xw[l], w.cap_rows * h->G * sizeof(float)));
+    SK_CUDA(cudaMalloc(&w.hprev[l], w.cap_rows * h->H * sizeof(float)));
+    SK_CUDA(cudaMalloc(&w.out[l], w.cap_rows * h->H * sizeof(float)));
+  }
+  w.f32_acts = true;
+  return 0;
 }
 
 int ensure_workspace(skrnn_handle *h, int B, int T) {
@@ -96,12 +115,8 @@ int ensure_workspace(skrnn_handle *h, int B, int T) {
   free_workspace(w);
   SK_CUDA(cudaMalloc(&w.x_tm, rows * 5 * sizeof(float)));
   SK_CUDA(cudaMalloc(&w.eoc, rows));
-  for (int l = 0; l < h->L; ++l) {
-    SK_CUDA(cudaMalloc(&w.xw[l], rows * h->G * sizeof(float)));
-    SK_CUDA(cudaMalloc(&w.hprev[l], rows * h->H * sizeof(float)));
+  for (int l = 0; l < h->L; ++l)
     if (h->cfg.cell != SKRNN_CELL_RNN) SK_CUDA(cudaMalloc(&w.cprev[l], rows * h->H * sizeof(float)));
-    SK_CUDA(cudaMalloc(&w.out[l], rows * h->H * sizeof(float)));
-  }
   SK_CUDA(cudaMalloc(&w.dout, rows * h->H * sizeof(float)));
   SK_CUDA(cudaMalloc(&w.logits, rows * h->NOUT * sizeof(float)));
   if (h->cfg.precision == SKRNN_PREC_BF16) {
@@ -124,13 +139,13 @@ int ensure_workspace(skrnn_handle *h, int B, int T) {
     }
   }
   w.cap_rows = rows;
+  if (needs_f32_acts_upfront(h)) SK_TRY(alloc_f32_acts(h));
   return 0;
 }
 
 int check_shape(skrnn_handle *h, int B, int T) {
   SK_CHECK(h != nullptr, "null handle");
   SK_CHECK(B > 0 && T > 0, "batch %d and sequence length %d must be positive", B, T);
-  SK_CUDA(cudaSetDevice(h->cfg.device));
   return ensure_workspace(h, B, T);
 }
 
@@ -190,9 +205,7 @@ int run_forward(skrnn_handle *h, cudaStream_t st, int B, int T, const float *x, 
       SK_TRY(gemm(h, st, (int)R, H, lp.I, Xo, true, weight(h, l, 1), true, h->ws.xw[l] + 2 * H, G, h->params + lp.b[1], false));
     } else {
       h->xw_il_ok[l] = false;
-      static int nt_env = -1;
-      if (nt_env < 0) { const char *e = getenv("SKRNN_NT"); nt_env = (e && e[0] == '1') ? 1 : 0; }
-      if (!nt_env && sk_rnn_tc_eligible(h) && h->ws.xw_il[l] != nullptr && h->wx_il[l] != nullptr) {
+      if (sk_rnn_tc_eligible(h) && h->ws.xw_il[l] != nullptr && h->wx_il[l] != nullptr) {
         // tcgen05 lstm kernels: bf16 projection with the four gates of a unit adjacent (half the bytes of the fp32 one)
         const int ip = (lp.I + 7) / 8 * 8;
         SK_TRY(sk_gemm_tc_bf16out(h, st, (int)R, G, ip, Xo.b, Xo.ldb, h->wx_il[l], G, h->ws.xw_il[l], G, h->bias_il[l]));
@@ -201,6 +214,12 @@ int run_forward(skrnn_handle *h, cudaStream_t st, int B, int T, const float *x, 
                                     state_out + (size_t)l * B * h->S, mask, seed, row0, training));
         if (h->fwd_family[l] == 1) continue;
         h->xw_il_ok[l] = false;  // declined (shape, launch failure): redo the layer through the fp32-format projection
+        if (!h->warned_tc_fallback) {  // a large performance cliff: say so, once per handle
+          h->warned_tc_fallback = true;
+          fprintf(stderr, "libskrnn: layer %d (H=%d, B=%d) does not run on the tcgen05 recurrent kernels; this handle "
+                          "falls back to the fp32 CUDA-core recurrent kernels between tensor-core GEMMs\n", l, H, B);
+        }
+        SK_TRY(alloc_f32_acts(h));
       }
       SK_TRY(gemm(h, st, (int)R, G, lp.I, Xo, true, weight(h, l, 0), true, h->ws.xw[l], G, h->params + lp.b[0], false));
     }
@@ -213,6 +232,8 @@ int run_forward(skrnn_handle *h, cudaStream_t st, int B, int T, const float *x, 
 }
 
 }  // namespace
+
+int sk_ensure_f32_acts(skrnn_handle *h) { return alloc_f32_acts(h); }
 
 extern "C" {
 
@@ -227,6 +248,10 @@ int skrnn_create(const skrnn_config *cfg, skrnn_handle **out) {
     return 1;
   }
   SK_CHECK(cfg->rnn_size > 0 && cfg->rnn_size % 8 == 0, "rnn_size %d must be a positive multiple of 8", cfg->rnn_size);
+  // every kernel family keeps a unit slice of the recurrent weights resident per CTA of one cluster; the largest
+  // plan (cluster of 8 x 64 units fp32, cluster of 16 x 32 units tcgen05, sampler with one thread per unit) ends at 512
+  SK_CHECK(cfg->rnn_size <= SKRNN_MAX_RNN_SIZE, "rnn_size %d is not supported: this library runs rnn_size <= %d",
+           cfg->rnn_size, SKRNN_MAX_RNN_SIZE);
   SK_CHECK(cfg->num_layers >= 1 && cfg->num_layers <= SK_MAX_LAYERS, "num_layers %d out of range", cfg->num_layers);
   SK_CHECK(cfg->num_mixture >= 1 && cfg->num_mixture <= 128, "num_mixture %d out of range [1,128]", cfg->num_mixture);
   SK_CHECK(cfg->keep_prob > 0.f && cfg->keep_prob <= 1.f, "keep_prob %f out of (0,1]", cfg->keep_prob);
@@ -239,7 +264,7 @@ int skrnn_create(const skrnn_config *cfg, skrnn_handle **out) {
     return 2;
   }
   SK_CHECK(cfg->device >= 0 && cfg->device < ndev, "device %d out of range (have %d)", cfg->device, ndev);
-  SK_CUDA(cudaSetDevice(cfg->device));
+  SkDeviceGuard guard(cfg->device);
   cudaDeviceProp prop;
   SK_CUDA(cudaGetDeviceProperties(&prop, cfg->device));
   SK_CHECK(prop.major == 10, "libskrnn is built for sm_100a only; device %d is sm_%d%d", cfg->device, prop.major, prop.minor);
@@ -330,10 +355,13 @@ int skrnn_create(const skrnn_config *cfg, skrnn_handle **out) {
 
 void skrnn_destroy(skrnn_handle *h) {
   if (!h) return;
-  cudaSetDevice(h->cfg.device);
+  SkDeviceGuard guard(h->cfg.device);
   cudaDeviceSynchronize();
   free_workspace(h->ws);
   cudaFree(h->ws.wpack);
+  cudaFree(h->ws.partial);
+  h->ws.partial = nullptr;
+  h->ws.partial_floats = 0;
   cudaFree(h->params);
   cudaFree(h->grads);
   cudaFree(h->adam_m);
@@ -385,7 +413,7 @@ int skrnn_tensor_info(const skrnn_handle *h, int32_t index, char *name_buf, int3
 int skrnn_set_params(skrnn_handle *h, const float *host_params, int64_t count) {
   SK_CHECK(h && host_params, "null argument");
   SK_CHECK(count == h->P, "set_params: expected %lld floats, got %lld", (long long)h->P, (long long)count);
-  SK_CUDA(cudaSetDevice(h->cfg.device));
+  SkDeviceGuard guard(h->cfg.device);
   SK_CUDA(cudaMemcpy(h->params, host_params, count * sizeof(float), cudaMemcpyHostToDevice));
   return 0;
 }
@@ -393,7 +421,7 @@ int skrnn_set_params(skrnn_handle *h, const float *host_params, int64_t count) {
 int skrnn_get_params(skrnn_handle *h, float *host_params, int64_t count) {
   SK_CHECK(h && host_params, "null argument");
   SK_CHECK(count == h->P, "get_params: expected %lld floats, got %lld", (long long)h->P, (long long)count);
-  SK_CUDA(cudaSetDevice(h->cfg.device));
+  SkDeviceGuard guard(h->cfg.device);
   SK_CUDA(cudaMemcpy(host_params, h->params, count * sizeof(float), cudaMemcpyDeviceToHost));
   return 0;
 }
@@ -402,7 +430,7 @@ int skrnn_set_adam_state(skrnn_handle *h, const float *host_m, const float *host
                          double beta1_power, double beta2_power) {
   SK_CHECK(h, "null handle");
   SK_CHECK(count == h->P, "set_adam_state: expected %lld floats, got %lld", (long long)h->P, (long long)count);
-  SK_CUDA(cudaSetDevice(h->cfg.device));
+  SkDeviceGuard guard(h->cfg.device);
   if (host_m) SK_CUDA(cudaMemcpy(h->adam_m, host_m, count * sizeof(float), cudaMemcpyHostToDevice));
   if (host_v) SK_CUDA(cudaMemcpy(h->adam_v, host_v, count * sizeof(float), cudaMemcpyHostToDevice));
   h->beta1_power = beta1_power;
@@ -414,7 +442,7 @@ int skrnn_get_adam_state(skrnn_handle *h, float *host_m, float *host_v, int64_t 
                          double *beta1_power, double *beta2_power) {
   SK_CHECK(h, "null handle");
   SK_CHECK(count == h->P, "get_adam_state: expected %lld floats, got %lld", (long long)h->P, (long long)count);
-  SK_CUDA(cudaSetDevice(h->cfg.device));
+  SkDeviceGuard guard(h->cfg.device);
   if (host_m) SK_CUDA(cudaMemcpy(host_m, h->adam_m, count * sizeof(float), cudaMemcpyDeviceToHost));
   if (host_v) SK_CUDA(cudaMemcpy(host_v, h->adam_v, count * sizeof(float), cudaMemcpyDeviceToHost));
   if (beta1_power) *beta1_power = h->beta1_power;
@@ -431,7 +459,7 @@ int skrnn_debug_gemm_bf16(skrnn_handle *h, int32_t M, int32_t N, int32_t K, cons
                           int32_t ldc, const float *bias_dev, int32_t accumulate, const uint32_t *overrides,
                           void *stream) {
   SK_CHECK(h && a_dev && b_dev && c_dev, "debug_gemm: null argument");
-  SK_CUDA(cudaSetDevice(h->cfg.device));
+  SkDeviceGuard guard(h->cfg.device);
   for (int i = 0; i < 6; ++i) g_tc_override[i] = overrides ? overrides[i] : 0;
   int rc = sk_gemm_tc(h, (cudaStream_t)stream, M, N, K, a_dev, lda, a_kmajor != 0, b_dev, ldb, b_kmajor != 0,
                       c_dev, ldc, bias_dev, accumulate != 0);
@@ -464,7 +492,7 @@ int skrnn_profile_enable(skrnn_handle *h, int32_t on) {
 
 int skrnn_profile_read(skrnn_handle *h, double *ms_out, int64_t *count_out) {
   SK_CHECK(h != nullptr && ms_out && count_out, "null argument");
-  SK_CUDA(cudaSetDevice(h->cfg.device));
+  SkDeviceGuard guard(h->cfg.device);
   SK_CUDA(cudaDeviceSynchronize());
   for (int i = 0; i < SK_NUM_CAT; ++i) { ms_out[i] = 0.0; count_out[i] = 0; }
   for (auto &r : h->prof) {
@@ -479,6 +507,8 @@ int skrnn_profile_read(skrnn_handle *h, double *ms_out, int64_t *count_out) {
 
 int skrnn_forward(skrnn_handle *h, int32_t B, int32_t T, const float *x_dev, const float *state_in_dev,
                   float *mdn_out_dev, float *state_out_dev, void *stream) {
+  SK_CHECK(h != nullptr, "null handle");
+  SkDeviceGuard guard(h->cfg.device);
   SK_TRY(check_shape(h, B, T));
   SK_CHECK(x_dev && state_in_dev && state_out_dev, "forward: null buffer");
   cudaStream_t st = (cudaStream_t)stream;
@@ -493,6 +523,8 @@ int skrnn_forward(skrnn_handle *h, int32_t B, int32_t T, const float *x_dev, con
 int skrnn_loss_grad(skrnn_handle *h, int32_t B, int32_t T, const float *x_dev, const float *y_dev,
                     const float *state_in_dev, const float *dropout_mask_dev, uint64_t seed, int32_t row0,
                     int64_t loss_rows, float *losses_dev, float *state_out_dev, void *stream) {
+  SK_CHECK(h != nullptr, "null handle");
+  SkDeviceGuard guard(h->cfg.device);
   SK_TRY(check_shape(h, B, T));
   SK_CHECK(x_dev && y_dev && state_in_dev && state_out_dev && losses_dev, "loss_grad: null buffer");
   SK_CHECK(loss_rows >= (int64_t)B * T, "loss_rows %lld smaller than B*T", (long long)loss_rows);
@@ -591,12 +623,14 @@ int skrnn_loss_grad(skrnn_handle *h, int32_t B, int32_t T, const float *x_dev, c
 
 int skrnn_apply_clip_adam(skrnn_handle *h, float lr, float *gnorm_out_dev, void *stream) {
   SK_CHECK(h != nullptr, "null handle");
-  SK_CUDA(cudaSetDevice(h->cfg.device));
+  SkDeviceGuard guard(h->cfg.device);
   return sk_clip_adam(h, (cudaStream_t)stream, lr, gnorm_out_dev);
 }
 
 int skrnn_train_step_host(skrnn_handle *h, int32_t B, int32_t T, const float *x_host, const float *y_host,
                           float *state_host, float lr, uint64_t seed, float *losses_host) {
+  SK_CHECK(h != nullptr, "null handle");
+  SkDeviceGuard guard(h->cfg.device);
   SK_TRY(check_shape(h, B, T));
   SK_CHECK(x_host && y_host && state_host && losses_host, "train_step_host: null buffer");
   const int64_t rows = (int64_t)B * T;
@@ -656,7 +690,7 @@ int skrnn_sample(skrnn_handle *h, int32_t n_sketches, int32_t num_steps, float t
   SK_CHECK(h != nullptr, "null handle");
   SK_CHECK(strokes_dev && lengths_dev, "sample: null output buffer");
   SK_CHECK(temp_mixture > 0.f && temp_pen > 0.f, "sample: temperatures must be positive");
-  SK_CUDA(cudaSetDevice(h->cfg.device));
+  SkDeviceGuard guard(h->cfg.device);
   // bf16 handles with many sketches: per-step tensor-core GEMMs (sampler_tc.cu); SKRNN_SAMPLER_EXACT=1
   // keeps the bit-exact fp32 persistent kernel
   const char *ex = getenv("SKRNN_SAMPLER_EXACT");

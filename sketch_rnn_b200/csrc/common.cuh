@@ -54,6 +54,7 @@ struct SkLayerParams {
 
 struct SkWorkspace {   // time-major activations for one (B, T) capacity
   int64_t cap_rows = 0;  // T*B rows allocated
+  bool f32_acts = false; // xw / hprev / out are allocated for cap_rows
   int capB = 0, capT = 0;
   float *x_tm = nullptr;                    // [T,B,5]
   unsigned char *eoc = nullptr;             // [T,B]: x[b,t,3] > 0
@@ -116,8 +117,8 @@ struct skrnn_handle {
   int64_t launches = 0;
   int cluster_size = 1;
   bool tc_rnn_disabled = false;
+  bool warned_tc_fallback = false;
   bool bias_grad_done = false;  // set by a backward recurrent kernel that accumulated d(bias) itself
-  bool nt_rnn_disabled = false;
   // side stream for work off the critical path of the backward pass (weight gradients), see skrnn_loss_grad
   cudaStream_t side = nullptr;
   cudaEvent_t ev_main[2] = {nullptr, nullptr}, ev_side[2] = {nullptr, nullptr};
@@ -128,7 +129,7 @@ struct skrnn_handle {
   int gemm_perm_H = 0;  // set around a split-K sk_gemm_tc call whose B operand has gate-interleaved columns (d(pre) of
                         // the tcgen05 lstm kernels): the epilogue then scatters C back to TF's gate-major columns
   bool xw_il_ok[SK_MAX_LAYERS] = {false};  // this step's xw_il[l] is what the forward of layer l reads
-  int fwd_family[SK_MAX_LAYERS] = {0};  // which kernels ran a layer's forward (0 fp32, 1 rnn_tc, 2 rnn_nt): they save
+  int fwd_family[SK_MAX_LAYERS] = {0};  // which kernels ran a layer's forward (0 rnn_f32, 1 rnn_tc): they save
                                         // activations in different places, so the backward must be the same family
   // optional per-category kernel timing (skrnn_profile_*): CUDA events around every launch
   bool prof_on = false;
@@ -139,6 +140,16 @@ struct skrnn_handle {
 
 enum { SK_CAT_GEMM = 0, SK_CAT_RNN_FWD = 1, SK_CAT_RNN_BWD = 2, SK_CAT_HEAD = 3, SK_CAT_OPTIM = 4,
        SK_CAT_MISC = 5, SK_CAT_SAMPLER = 6, SK_CAT_TC_GEMM = 7, SK_NUM_CAT = 8 };
+
+// RAII scope of an entry point: makes the handle's device current and puts the caller's device back on exit.
+struct SkDeviceGuard {
+  int prev = -1;
+  bool changed = false;
+  explicit SkDeviceGuard(int dev) {
+    if (cudaGetDevice(&prev) == cudaSuccess && prev != dev) changed = cudaSetDevice(dev) == cudaSuccess;
+  }
+  ~SkDeviceGuard() { if (changed) cudaSetDevice(prev); }
+};
 
 // RAII scope: counts the launch and, when profiling is on, brackets it with events on `st`.
 struct SkLaunch {
@@ -173,9 +184,9 @@ extern uint32_t g_tc_override[6];
 // Tiled tensor map (rank 2..5), 128B-swizzled unless swizzle128 = false.  elem_bytes: 2 (bf16) or 4 (fp32).
 int sk_make_tmap(CUtensorMap *m, int elem_bytes, const void *ptr, int rank, const uint64_t *dims,
                  const uint64_t *strides_bytes, const uint32_t *box, bool swizzle128 = true);
-// tcgen05 recurrent kernels, large-batch variant (rnn_nt.cu): 0 ok, -1 not applicable
-int sk_rnn_nt_layer(skrnn_handle *h, cudaStream_t st, bool bwd, int l, int B, int T, const float *state_in,
-                    float *state_out, const float *mask, uint64_t seed, int row0, bool training);
+// The fp32 activation set (xw, hprev, out per layer) of the CUDA-core recurrent kernels.  bf16 handles whose layers run
+// the tcgen05 recurrent kernels never touch it, so it is allocated on first use (api.cu).
+int sk_ensure_f32_acts(skrnn_handle *h);
 bool sk_rnn_tc_eligible(const skrnn_handle *h);
 // tcgen05 recurrent kernels (rnn_tc.cu): return 0 ok, <0 "not eligible, use the fp32 kernels", >0 error
 int sk_rnn_tc_layer(skrnn_handle *h, cudaStream_t st, bool bwd, int l, int B, int T, const float *x_bt5,

@@ -17,10 +17,12 @@
 // can be updated per call; larger counts are rejected.  All calls on a device share the array and
 // it keeps whatever the previous call left: the barrier counter is cleared (stream-ordered) at the
 // start of every call and every partial sum that is read is rewritten first, but two calls that
-// overlap on the GPU (different streams, or different host threads) race on it -- serialise them.
+// overlap on the GPU (different streams, or different host threads) race on it -- serialise them,
+// the first call included (its set-up below is plain unsynchronised bookkeeping).
 //
 // The first call on each device looks up the device address of the array (cudaGetSymbolAddress)
-// and queries the device; make that first call before starting any stream capture.
+// and queries the device; make that first call before starting any stream capture.  The device is
+// the one that owns params_dev, not whichever happens to be current.
 #include "common.cuh"
 
 namespace {
@@ -128,9 +130,15 @@ extern "C" int skrnn_clip_adam_noalloc(int64_t n, const float *grads_dev, float 
   SK_CHECK(grad_clip > 0.f, "clip_adam_noalloc: grad_clip must be positive");
   SK_CHECK(beta1_power > 0.0 && beta1_power < 1.0 && beta2_power > 0.0 && beta2_power < 1.0,
            "clip_adam_noalloc: beta powers must lie in (0,1) (0.9 and 0.999 before the first step)");
-  int dev = -1;
-  SK_CUDA(cudaGetDevice(&dev));
+  // run on the GPU that owns the buffers, whatever device happens to be current (handle entry points and other
+  // libraries may have switched it); the caller's device is restored on return
+  cudaPointerAttributes pat;
+  SK_CUDA(cudaPointerGetAttributes(&pat, params_dev));
+  SK_CHECK(pat.type == cudaMemoryTypeDevice || pat.type == cudaMemoryTypeManaged,
+           "clip_adam_noalloc: params_dev is not a device pointer");
+  const int dev = pat.device;
   SK_CHECK(dev >= 0 && dev < NA_MAX_DEVICES, "clip_adam_noalloc: device ordinal %d unsupported", dev);
+  SkDeviceGuard guard(dev);
   NaDevice &d = g_na_dev[dev];
   if (!d.ready) {
     // once per device, with that device current: resolve the device address of the scratch array

@@ -540,21 +540,13 @@ int launch_cell(bool bwd, const Plan &p, const RnnArgs &a, int nc, cudaStream_t 
 int run_layer(skrnn_handle *h, cudaStream_t st, bool bwd, int l, int B, int T, const float *x_bt5,
               const float *state_in, float *state_out, const float *mask, uint64_t seed, int row0,
               bool training) {
-  // The three kernel families save a layer's activations in different places, so a layer's BPTT runs in the
+  // The kernel families save a layer's activations in different places, so a layer's BPTT runs in the
   // family that ran its forward pass.
   if (!bwd) {
     h->fwd_family[l] = 0;
-    if (sk_rnn_nt_layer(h, st, false, l, B, T, state_in, state_out, mask, seed, row0, training) == 0) {
-      h->fwd_family[l] = 2;
-      return 0;
-    }
     int rc = sk_rnn_tc_layer(h, st, false, l, B, T, x_bt5, state_in, state_out, mask, seed, row0, training);
     if (rc == 0) h->fwd_family[l] = 1;
     if (rc >= 0) return rc;  // handled by the tcgen05 kernels (0) or failed hard (>0)
-  } else if (h->fwd_family[l] == 2) {
-    int rc = sk_rnn_nt_layer(h, st, true, l, B, T, state_in, state_out, mask, seed, row0, training);
-    SK_CHECK(rc == 0, "layer %d: forward ran in the rnn_nt kernels but their backward is not available (rc %d)", l, rc);
-    return 0;
   } else if (h->fwd_family[l] == 1) {
     int rc = sk_rnn_tc_layer(h, st, true, l, B, T, x_bt5, state_in, state_out, mask, seed, row0, training);
     SK_CHECK(rc == 0, "layer %d: forward ran in the rnn_tc kernels but their backward failed (rc %d): %s", l, rc,
@@ -563,6 +555,7 @@ int run_layer(skrnn_handle *h, cudaStream_t st, bool bwd, int l, int B, int T, c
   }
   Plan p;
   SK_TRY(make_plan(h, B, bwd ? 1 : 0, &p));
+  SK_TRY(sk_ensure_f32_acts(h));
   const int cell = h->cfg.cell, H = h->H;
   const SkLayerParams &lp = h->lp[l];
   {

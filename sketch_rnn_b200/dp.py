@@ -27,9 +27,48 @@ def allreduce_sum_(tensors, group=None):
         dist.all_reduce(t, op=dist.ReduceOp.SUM, group=group)
 
 
-def dp_train_step(handle, x_shard, y_shard, state, lr, seed, row0, global_rows, group=None):
-    """One data-parallel step on this rank's shard.  Returns (losses[3] summed over ranks, new state)."""
+def dp_train_step(handle, x_shard, y_shard, state, lr, seed, row0, global_rows, group=None, timing=None):
+    """One data-parallel step on this rank's shard.  Returns (losses[3] summed over ranks, new state).
+    timing: optional dict; when given, CUDA events bracket the all-reduce and its milliseconds are added to
+    timing["allreduce_ms"] (this synchronises the stream -- measurement passes only)."""
     losses, state = handle.loss_grad(x_shard, y_shard, state, seed=seed, row0=row0, loss_rows=global_rows)
+    if timing is not None:
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
     allreduce_sum_([handle.grads_tensor(), losses], group)
+    if timing is not None:
+        e1.record()
+        e1.synchronize()
+        timing["allreduce_ms"] = timing.get("allreduce_ms", 0.0) + e0.elapsed_time(e1)
     handle.apply_clip_adam(lr)
     return losses, state
+
+
+class HostStep(object):
+    """The training step a data-parallel caller makes with HOST buffers, the N-GPU counterpart of
+    skrnn_train_step_host (one sess.run([cost, cost_shape, cost_pen, final_state, train_op], feed), train.py:85-86):
+    this rank's rows of the batch go from page-locked host memory to the GPU, loss_grad runs, the flat gradient is
+    all-reduced (when there is more than one rank), clip + Adam, and the three losses and the final state come back
+    to page-locked host memory.  Buffers are allocated once."""
+
+    def __init__(self, handle, rows, T, global_rows, row0=0, group=None):
+        dev = "cuda:%d" % handle.device
+        self.h, self.rows, self.T, self.global_rows, self.row0, self.group = handle, rows, T, global_rows, row0, group
+        self.x = torch.empty((rows, T, 5), dtype=torch.float32, device=dev)
+        self.y = torch.empty_like(self.x)
+        self.state = torch.zeros((handle.L, rows, handle.S), dtype=torch.float32, device=dev)
+        self.losses_host = torch.empty(3, dtype=torch.float32).pin_memory()
+        self.state_host = torch.zeros((handle.L, rows, handle.S), dtype=torch.float32).pin_memory()
+        self.h2d_bytes = 2 * self.x.numel() * 4 + self.state.numel() * 4
+        self.d2h_bytes = 12 + self.state.numel() * 4
+
+    def __call__(self, x_pinned, y_pinned, lr, seed):
+        """x_pinned, y_pinned: page-locked torch tensors [rows, T, 5].  Returns the losses (host, valid on return)."""
+        self.x.copy_(x_pinned, non_blocking=True)
+        self.y.copy_(y_pinned, non_blocking=True)
+        self.state.copy_(self.state_host, non_blocking=True)
+        losses, st = dp_train_step(self.h, self.x, self.y, self.state, lr, seed, self.row0, self.global_rows, self.group)
+        self.losses_host.copy_(losses, non_blocking=True)
+        self.state_host.copy_(st, non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+        return self.losses_host

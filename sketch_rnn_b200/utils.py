@@ -229,3 +229,10 @@ def synthetic_batch(B, T, seed=0, p_eos=0.10, p_eoc=0.015):
     seq = seq.astype(np.float32)
     return np.ascontiguousarray(seq[:, :-1]), np.ascontiguousarray(seq[:, 1:])
 
+
+
+def synthetic_dropout_mask(B, T, H, keep_prob, seed=0):
+    """Seeded 0/1 output-dropout mask [B,T,H] (what TF's floor(keep + U[0,1)) would be for a fixed draw,
+    model.py:29-30) for runs that must be reproducible outside the library (bench.py's loss check)."""
+    rng = np.random.RandomState(seed)
+    return (rng.rand(B, T, H) < keep_prob).astype(np.float32)

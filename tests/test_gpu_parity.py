@@ -93,11 +93,8 @@ def test_loss_and_gradients(model, H, L, M, B, T):
     g = h.get_params_dict(h.grads_tensor().cpu().numpy())
     for i in range(3):
         assert abs(losses[i] - losses_ref[i]) <= TOL * abs(losses_ref[i]) + 1e-6, (i, losses, losses_ref)
-    gscale = max(np.max(np.abs(v)) for v in grads_ref.values())
-    for n in grads_ref:
-        err = np.max(np.abs(g[n].astype(np.float64) - grads_ref[n])) / gscale
-        assert err < TOL, (n, err)
-        assert rel_err(g[n], grads_ref[n]) < 20 * TOL, (n, rel_err(g[n], grads_ref[n]))
+    errs = {n: rel_err(g[n], grads_ref[n]) for n in grads_ref}  # per tensor, against that tensor's own scale
+    assert max(errs.values()) < TOL, errs
     so_state = state_out.cpu().numpy()
     for l in range(L):
         assert rel_err(so_state[l], fstate_ref[l]) < TOL
@@ -366,15 +363,15 @@ def test_bf16_path_loss_and_gradients(model, H, L, M, B, T):
     g = h.get_params_dict(h.grads_tensor().cpu().numpy())
     for i in range(3):
         assert abs(losses[i] - losses_ref[i]) <= BF16_TOL * abs(losses_ref[i]) + 1e-5, (i, losses, losses_ref)
-    gscale = max(np.max(np.abs(v)) for v in grads_ref.values())
-    for n in grads_ref:
-        err = np.max(np.abs(g[n].astype(np.float64) - grads_ref[n])) / gscale
-        assert err < BF16_TOL, (n, err)
+    errs = {n: rel_err(g[n], grads_ref[n]) for n in grads_ref}  # per tensor, against that tensor's own scale
+    assert max(errs.values()) < BF16_TOL, errs
     ref = so.forward(cfg, f64(params), x.astype(np.float64), [s.astype(np.float64) for s in s0])
     mdn, _ = h.forward(x, stack_state(s0))
     mdn = mdn.cpu().numpy()
-    assert rel_err(mdn[:, 3:3 + M], ref["mdn"]["pi"]) < BF16_TOL
-    assert rel_err(mdn[:, 3 + M:3 + 2 * M], ref["mdn"]["mu1"]) < BF16_TOL
+    merr = {"pen": rel_err(mdn[:, 0:3], ref["mdn"]["pen"])}
+    for i, n in enumerate(["pi", "mu1", "mu2", "sigma1", "sigma2", "corr"]):
+        merr[n] = rel_err(mdn[:, 3 + i * M:3 + (i + 1) * M], ref["mdn"][n])
+    assert max(merr.values()) < BF16_TOL, merr
     h.close()
 
 
@@ -400,10 +397,8 @@ def test_bf16_tcgen05_recurrent_edge_shapes(H, L, B, T):
     losses = losses.cpu().numpy()
     g = h.get_params_dict(h.grads_tensor().cpu().numpy())
     assert abs(losses[0] - losses_ref[0]) <= BF16_TOL * abs(losses_ref[0]) + 1e-5, (losses, losses_ref)
-    gscale = max(np.max(np.abs(v)) for v in grads_ref.values())
-    for n in grads_ref:
-        err = np.max(np.abs(g[n].astype(np.float64) - grads_ref[n])) / gscale
-        assert err < BF16_TOL, (n, err)
+    errs = {n: rel_err(g[n], grads_ref[n]) for n in grads_ref}
+    assert max(errs.values()) < BF16_TOL, errs
     so_state = state_out.cpu().numpy()
     for l in range(L):
         assert rel_err(so_state[l], fstate_ref[l]) < BF16_TOL
@@ -454,3 +449,135 @@ def test_bf16_training_tracks_fp32_over_many_steps():
     for n in final["f32"]:
         d = np.max(np.abs(final["bf16"][n] - final["f32"][n])) / (np.max(np.abs(final["f32"][n])) + 1e-12)
         assert d < 5e-2, (n, d)
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# committed known-answer vectors (tests/golden/*.npz) and the edge cases of model.py:130 / model.py:197 on the GPU
+# ---------------------------------------------------------------------------------------------------------------
+import glob
+import os
+
+GOLDEN = sorted(glob.glob(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "*.npz")))
+
+
+@pytest.mark.parametrize("path", GOLDEN, ids=[os.path.basename(p) for p in GOLDEN])
+def test_golden_vectors_on_gpu(path):
+    """The fixtures test_oracle.py pins the oracle with, fed to the CUDA path: losses, every gradient tensor, final
+    state and MDN parameters within 1e-4 (fp32 path), the sampler trace bit for bit."""
+    from sketch_rnn_b200 import _lib
+    z = np.load(path)
+    model, H, L, M, B, T = str(z["model"]), int(z["H"]), int(z["L"]), int(z["M"]), int(z["B"]), int(z["T"])
+    h = _lib.Handle(model=model, rnn_size=H, num_layers=L, num_mixture=M, batch_size=B, seq_length=T, keep_prob=0.8)
+    h.set_params(z["params"])
+    losses, state_out = h.loss_grad(z["x"], z["y"], z["state_in"], dropout_mask=z["mask"])
+    losses = losses.cpu().numpy()
+    for i in range(3):
+        assert abs(losses[i] - z["losses"][i]) <= TOL * abs(z["losses"][i]) + 1e-7
+    g = h.grads_tensor().cpu().numpy()
+    for name, off, shape in h.tensors():
+        k = int(np.prod(shape))
+        assert rel_err(g[off:off + k], z["grads"][off:off + k]) < TOL, name
+    assert rel_err(state_out.cpu().numpy(), z["final_state"]) < TOL
+    mdn, st = h.forward(z["x"], z["state_in"])
+    mdn = mdn.cpu().numpy()
+    assert rel_err(mdn[:, 0:3], z["mdn_nodrop"][:, 0:3]) < TOL
+    for i in range(6):
+        sl = slice(3 + i * M, 3 + (i + 1) * M)
+        assert rel_err(mdn[:, sl], z["mdn_nodrop"][:, sl]) < TOL, i
+    assert rel_err(st.cpu().numpy(), z["final_state_nodrop"]) < TOL
+    u = z["sample_uniforms"]
+    strokes, lengths, mixp = h.sample(1, u.shape[0], 0.4, 0.4, False, uniforms=u[None], want_params=True)
+    assert np.array_equal(strokes.cpu().numpy()[0].view(np.uint32), z["sample_strokes"].view(np.uint32))
+    assert np.array_equal(mixp.cpu().numpy()[0].view(np.uint32), z["sample_mixp"].view(np.uint32))
+    h.close()
+
+
+@pytest.mark.parametrize("precision", ["f32", "bf16"])
+def test_clamped_rows_on_gpu(precision):
+    """model.py:130: rows whose mixture density underflows contribute -log(1e-20) and no mixture gradient.  Half the
+    rows get an absurd target, so both branches of the clamp run in the same launch of mdn_head_kernel."""
+    cfg, params, x, y, s0, mask = _case("lstm", 32, 2, 4, 6, 5)
+    y[::2, :, 0:2] = 1e4
+    losses_ref, grads_ref, _, _ = so.loss_and_grads(cfg, f64(params), x.astype(np.float64), y.astype(np.float64),
+                                                    [s.astype(np.float64) for s in s0], mask.astype(np.float64))
+    assert losses_ref[1] > 0.4 * -np.log(1e-20)  # the clamp really is active in the oracle
+    tol = TOL if precision == "f32" else BF16_TOL
+    h = make_handle(cfg, params, 6, 5, precision=precision)
+    losses, _ = h.loss_grad(x, y, stack_state(s0), dropout_mask=mask)
+    losses = losses.cpu().numpy()
+    g = h.get_params_dict(h.grads_tensor().cpu().numpy())
+    for i in range(3):
+        assert abs(losses[i] - losses_ref[i]) <= tol * abs(losses_ref[i]), (i, losses, losses_ref)
+    for n in grads_ref:
+        assert rel_err(g[n], grads_ref[n]) < tol, (n, rel_err(g[n], grads_ref[n]))
+    # all rows clamped: the mixture columns of the output layer receive exactly no gradient
+    y[:, :, 0:2] = 1e4
+    h.loss_grad(x, y, stack_state(s0), dropout_mask=mask)
+    g = h.get_params_dict(h.grads_tensor().cpu().numpy())
+    assert np.all(g["rnn_mdn/output_b"][3:] == 0) and np.any(g["rnn_mdn/output_b"][:3] != 0)
+    h.close()
+
+
+def test_sampler_pi_idx_minus_one_on_gpu():
+    """model.py:189-197: get_pi_idx returns -1 when the running sum never reaches the draw -> Python's negative index
+    picks the LAST mixture component, and the pen falls through to `cont`.  u >= 1 forces it on every point."""
+    cfg = so.Config(model="lstm", rnn_size=16, num_layers=2, num_mixture=4)
+    params = so.init_params(cfg, seed=5, trained_like=True)
+    h = make_handle(cfg, params)
+    u = np.random.RandomState(2).rand(3, 8, 4).astype(np.float32)
+    u[:, :, 0:2] = 1.5
+    u[1, 3:, 0] = 0.3   # mixed: some points draw normally
+    strokes, lengths, mixp = h.sample(3, 8, 1.0, 1.0, False, uniforms=u, want_params=True)
+    strokes, mixp = strokes.cpu().numpy(), mixp.cpu().numpy()
+    assert np.all(strokes[:, :, 4] == 1) and np.all(strokes[:, :, 2:4] == 0)
+    for i in range(3):
+        ref_s, ref_p = sampler_ref.sample(cfg, params, u[i], 8, 1.0, 1.0, False, want_params=True)
+        assert np.array_equal(strokes[i].view(np.uint32), ref_s.view(np.uint32))
+        ref_np, _ = so.sample(cfg, params, u[i], 8, 1.0, 1.0, False)
+        assert np.array_equal(ref_np[:, 2:], strokes[i, :, 2:])
+    # the point drawn with idx = -1 is centred on the last component: replay sketch 0, step 0 by hand
+    M = 4
+    p = mixp[0, 0]
+    z1, z2 = so.box_muller(u[0, 0, 2], u[0, 0, 3])
+    x1 = p[3 + M + (M - 1)] + p[3 + 3 * M + (M - 1)] * z1
+    assert abs(strokes[0, 0, 0] - x1 * cfg.data_scale) < 1e-4 * cfg.data_scale
+    h.close()
+
+
+@pytest.mark.parametrize("precision", ["f32", "bf16"])
+def test_in_kernel_dropout_keep_rate_and_independence(precision):
+    """Keep rate and independence of the in-kernel dropout hash (the stand-in for TF's random_uniform in
+    model.py:29-30).  A one-layer RNN with zero matrices and bias atanh(0.5) outputs 0.5 for every unit, row and step,
+    and with output_w = 0 the logits do not depend on the mask; then
+        d cost / d output_w[u, j] = sum over rows of 0.5 * mask[row, u] / keep * dlogits[row, j],
+    and its ratio to the same gradient at keep_prob = 1 is the dlogits-weighted kept fraction of unit u divided by
+    keep: expectation 1, different per unit, different per seed."""
+    from sketch_rnn_b200 import _lib
+    H, B, T, keep = 64, 64, 40, 0.8
+    cfg = so.Config(model="rnn", rnn_size=H, num_layers=1, num_mixture=2, batch_size=B, seq_length=T, keep_prob=keep)
+    params = so.init_params(cfg, seed=3)
+    # h_t = tanh(b) = const for every unit, row and step: zero matrices, bias atanh(0.5)
+    params["rnn_mdn/MultiRNNCell/Cell0/BasicRNNCell/Linear/Matrix"][:] = 0
+    params["rnn_mdn/MultiRNNCell/Cell0/BasicRNNCell/Linear/Bias"][:] = np.arctanh(0.5)
+    x, y = so.synthetic_batch(B, T, seed=1)
+    st = np.zeros((1, B, H), dtype=np.float32)
+    params["rnn_mdn/output_w"][:] = 0
+    h1 = _lib.Handle(model="rnn", rnn_size=H, num_layers=1, num_mixture=2, batch_size=B, seq_length=T, keep_prob=1.0,
+                     precision=precision)
+    h1.set_params_dict(params)
+    h1.loss_grad(x, y, st)
+    g_all = h1.get_params_dict(h1.grads_tensor().cpu().numpy())["rnn_mdn/output_w"].astype(np.float64)
+    h1.close()
+    h = make_handle(cfg, params, B, T, precision=precision)
+    gs = []
+    for seed in (11, 12):
+        h.loss_grad(x, y, st, seed=seed)
+        gs.append(h.get_params_dict(h.grads_tensor().cpu().numpy())["rnn_mdn/output_w"].astype(np.float64))
+    h.close()
+    j = int(np.argmax(np.abs(g_all).sum(axis=0)))         # a logit column with a solid gradient
+    ratios = np.stack([g[:, j] / g_all[:, j] for g in gs])   # [2 seeds, H units], expectation 1
+    assert abs(ratios.mean() - 1.0) < 0.01, ratios.mean()
+    assert ratios.std() > 1e-3                             # units really have different masks
+    assert np.abs(ratios[0] - ratios[1]).max() > 1e-3       # and a new seed draws new masks
+    c = np.corrcoef(ratios[0], ratios[1])[0, 1]
+    assert abs(c) < 0.5, c                                  # seeds are not correlated unit by unit

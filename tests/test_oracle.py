@@ -190,3 +190,37 @@ def test_shipped_config_pickle_loads():
 def test_unknown_model_raises_reference_message():
     with pytest.raises(Exception, match="model type not supported: foo"):
         so.Config(model="foo")
+
+
+def test_shared_math_header_against_libm():
+    """oracle/sampler_ref.c and the CUDA sampler share csrc/skrnn_math.h (own exp / log / tanh / sincos so that host
+    and device produce the same bits).  Bit-equality between the two therefore says nothing about whether skm_exp IS
+    exp: this test measures the header's functions against libm (NumPy float64) over the ranges the sampler feeds
+    them -- softmax / sigma exponents, log of probabilities, tanh of rho-hat and cell states, Box-Muller angles."""
+    import ctypes as C
+    lib = sampler_ref.lib()
+    lib.skref_sincos2pi.argtypes = [C.c_float, C.POINTER(C.c_float), C.POINTER(C.c_float)]
+    rng = np.random.RandomState(0)
+
+    def worst_rel(fn, ref, xs):
+        got = np.array([fn(float(v)) for v in xs], dtype=np.float64)
+        want = ref(xs.astype(np.float64))
+        return float(np.max(np.abs(got - want) / np.abs(want)))
+
+    xs = np.concatenate([rng.uniform(-87, 88, 20000), rng.uniform(-1, 1, 5000)]).astype(np.float32)
+    assert worst_rel(lib.skref_exp, np.exp, xs) < 2e-7          # ~1.3 ulp of float32
+    xs = np.concatenate([np.exp(rng.uniform(-87, 88, 20000)), rng.uniform(0.5, 2, 5000)]).astype(np.float32)
+    xs = xs[np.abs(xs - 1.0) > 1e-3]                             # relative error of log is ill-defined at log(1) = 0
+    assert worst_rel(lib.skref_log, np.log, xs) < 3e-7
+    xs = np.concatenate([rng.uniform(-10, 10, 20000), rng.uniform(-0.01, 0.01, 5000)]).astype(np.float32)
+    got = np.array([lib.skref_tanh(float(v)) for v in xs], dtype=np.float64)
+    assert np.max(np.abs(got - np.tanh(xs.astype(np.float64)))) < 1.5e-7
+    s, c = C.c_float(), C.c_float()
+    worst = 0.0
+    for u in rng.uniform(0, 1, 5000).astype(np.float32):
+        lib.skref_sincos2pi(float(u), C.byref(s), C.byref(c))
+        worst = max(worst, abs(s.value - np.sin(2 * np.pi * float(u))), abs(c.value - np.cos(2 * np.pi * float(u))))
+    assert worst < 2e-7
+    # saturation instead of 0 / inf at the ends of the float32 range (documented behaviour of the header)
+    assert 0.0 < lib.skref_exp(-200.0) < 2e-38 and 1e38 < lib.skref_exp(100.0) < np.inf
+    assert lib.skref_tanh(50.0) == 1.0 and lib.skref_tanh(-50.0) == -1.0

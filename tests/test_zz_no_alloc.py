@@ -7,7 +7,11 @@ no-alloc entry point works on their pointers and a fixed scratch array inside th
 test drives it through the C ABI and checks it against the handle-based skrnn_apply_clip_adam on
 the same numbers, for two consecutive calls (the second one proves that the shared scratch, which
 still holds the first call's contents, is reset correctly), and checks that the size limit is
-enforced and that device memory does not shrink across the call.
+enforced and that device memory does not shrink across the call.  A second group checks it against
+the CPU oracle's clip_by_global_norm + adam_apply (reference model.py:182-184) at the sizes that
+take the kernel's other paths: config 4's 5,334,675 parameters (more chunks than blocks, a ragged
+last chunk), exactly SKRNN_NOALLOC_MAX_PARAMS, and a small call right after a large one (stale
+partial sums of the large call are still in the scratch array).
 
 The file name sorts last on purpose: a run that stops at the first failure has then already
 executed every other test."""
@@ -73,3 +77,53 @@ def test_noalloc_rejects_sizes_beyond_the_fixed_scratch():
     rc = lib.skrnn_clip_adam_noalloc(0, t.data_ptr(), t.data_ptr(), t.data_ptr(), t.data_ptr(), 0.005, 5.0,
                                      0.9, 0.999, None, None)
     assert rc != 0
+
+
+class _Opt(object):
+    """The oracle's Adam state for one flat tensor (oracle.sketch_oracle.AdamState without a model config)."""
+
+    def __init__(self, n):
+        self.m = {"p": np.zeros(n, dtype=np.float32)}
+        self.v = {"p": np.zeros(n, dtype=np.float32)}
+        self.beta1_power = 0.9
+        self.beta2_power = 0.999
+
+
+def _oracle_vs_noalloc(sizes_and_scales, seed):
+    """Runs the calls in order on the GPU (fresh tensors per size) and the oracle beside them; two steps per size so
+    the slots and beta powers of the second step are non-trivial."""
+    import torch
+    from oracle import sketch_oracle as so
+    from sketch_rnn_b200 import _lib
+    rng = np.random.RandomState(seed)
+    for n, scales in sizes_and_scales:
+        p_ref = {"p": (rng.standard_normal(n) * 0.1).astype(np.float32)}
+        opt = _Opt(n)
+        p = torch.from_numpy(p_ref["p"].copy()).cuda()
+        m = torch.zeros(n, device="cuda")
+        v = torch.zeros(n, device="cuda")
+        gn_dev = torch.zeros(1, device="cuda")
+        for scale in scales:
+            g = (rng.standard_normal(n) * scale).astype(np.float32)
+            clipped, gn_ref = so.clip_by_global_norm({"p": g}, 5.0)
+            b1, b2 = opt.beta1_power, opt.beta2_power
+            so.adam_apply(p_ref, clipped, opt, 0.005)
+            _lib.clip_adam_noalloc(torch.from_numpy(g).cuda(), p, m, v, 0.005, 5.0, b1, b2, gnorm_out=gn_dev)
+            torch.cuda.synchronize()
+            assert abs(float(gn_dev) - float(gn_ref)) <= TOL * float(gn_ref), (n, scale, float(gn_dev), float(gn_ref))
+            for got, ref, name in ((p, p_ref["p"], "p"), (m, opt.m["p"], "m"), (v, opt.v["p"], "v")):
+                e = _rel(got.cpu(), torch.from_numpy(ref))
+                assert e < TOL, (n, scale, name, e)
+        del p, m, v
+        torch.cuda.empty_cache()
+
+
+def test_noalloc_against_oracle_at_config4_size_then_a_small_call():
+    # 5,334,675 = config 4's parameter count: 1303 chunks on ~592 blocks (grid-stride loop), last chunk ragged;
+    # then 1000 parameters: one chunk, while partial[1..1302] still hold the large call's sums
+    _oracle_vs_noalloc([(5334675, [3.0, 1e-4]), (1000, [2.0, 1e-3]), (4097, [1.0])], seed=1)
+
+
+def test_noalloc_against_oracle_at_the_size_limit():
+    from sketch_rnn_b200 import _lib
+    _oracle_vs_noalloc([(_lib.NOALLOC_MAX_PARAMS, [0.5])], seed=2)
