@@ -132,10 +132,8 @@ int ensure_workspace(skrnn_handle *h, int B, int T) {
       SK_CUDA(cudaMalloc(&w.out_bf[l], rows * h->H * e));
       SK_CUDA(cudaMalloc(&w.hprev_bf[l], rows * h->H * e));
       if (h->cfg.cell == SKRNN_CELL_GRU) SK_CUDA(cudaMalloc(&w.aux_bf[l], rows * h->H * e));
-      if (h->cfg.cell == SKRNN_CELL_LSTM) {
-        SK_CUDA(cudaMalloc(&w.acts_bf[l], rows * h->G * e));
-        SK_CUDA(cudaMalloc(&w.xw_il[l], rows * h->G * e));
-      }
+      SK_CUDA(cudaMalloc(&w.acts_bf[l], rows * h->G * e));  // gate activations saved by the tcgen05 recurrent kernels
+      if (h->cfg.cell == SKRNN_CELL_LSTM) SK_CUDA(cudaMalloc(&w.xw_il[l], rows * h->G * e));
     }
   }
   w.cap_rows = rows;
@@ -591,10 +589,10 @@ int skrnn_loss_grad(skrnn_handle *h, int32_t B, int32_t T, const float *x_dev, c
       float *gWg = h->grads + lp.w[0], *gWc = h->grads + lp.w[1];
       SK_TRY(gemm(h, st, I, 2 * H, R, X, false, dg, true, gWg, 2 * H, nullptr, true));
       SK_TRY(gemm(h, st, H, 2 * H, R, hprev_op(h, l), false, dg, true, gWg + (size_t)I * 2 * H, 2 * H, nullptr, true));
-      SK_TRY(bias_grad(h, st, dg, R, 2 * H, h->grads + lp.b[0]));
+      if (!h->bias_grad_done) SK_TRY(bias_grad(h, st, dg, R, 2 * H, h->grads + lp.b[0]));
       SK_TRY(gemm(h, st, I, H, R, X, false, dc, true, gWc, H, nullptr, true));
       SK_TRY(gemm(h, st, H, H, R, aux_op(h, l), false, dc, true, gWc + (size_t)I * H, H, nullptr, true));
-      SK_TRY(bias_grad(h, st, dc, R, H, h->grads + lp.b[1]));
+      if (!h->bias_grad_done) SK_TRY(bias_grad(h, st, dc, R, H, h->grads + lp.b[1]));
       if (l > 0) {
         SK_TRY(gemm(h, st, R, I, 2 * H, dg, true, weight(h, l, 0), false, h->ws.dout, H, nullptr, false));
         SK_TRY(gemm(h, st, R, I, H, dc, true, weight(h, l, 1), false, h->ws.dout, H, nullptr, true));

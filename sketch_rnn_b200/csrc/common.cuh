@@ -129,7 +129,7 @@ struct skrnn_handle {
   int gemm_perm_H = 0;  // set around a split-K sk_gemm_tc call whose B operand has gate-interleaved columns (d(pre) of
                         // the tcgen05 lstm kernels): the epilogue then scatters C back to TF's gate-major columns
   bool xw_il_ok[SK_MAX_LAYERS] = {false};  // this step's xw_il[l] is what the forward of layer l reads
-  int fwd_family[SK_MAX_LAYERS] = {0};  // which kernels ran a layer's forward (0 rnn_f32, 1 rnn_tc): they save
+  int fwd_family[SK_MAX_LAYERS] = {0};  // which kernels ran a layer's forward (0 rnn_f32, 1 rnn_tc, 3 rnn1_tc): they save
                                         // activations in different places, so the backward must be the same family
   // optional per-category kernel timing (skrnn_profile_*): CUDA events around every launch
   bool prof_on = false;
@@ -192,6 +192,9 @@ bool sk_rnn_tc_eligible(const skrnn_handle *h);
 int sk_rnn_tc_layer(skrnn_handle *h, cudaStream_t st, bool bwd, int l, int B, int T, const float *x_bt5,
                     const float *state_in, float *state_out, const float *mask, uint64_t seed, int row0,
                     bool training);
+// tcgen05 recurrent kernels for the GRU / RNN cells, one CTA per batch tile (rnn1_tc.cu): 0 ok, -1 not eligible, > 0 error
+int sk_rnn1_tc_layer(skrnn_handle *h, cudaStream_t st, bool bwd, int l, int B, int T, const float *state_in,
+                     float *state_out, const float *mask, uint64_t seed, int row0, bool training);
 int sk_colsum_bf16(skrnn_handle *h, cudaStream_t st, const __nv_bfloat16 *A, int64_t rows, int cols, int lda,
                    float *out);
 int sk_colsum(skrnn_handle *h, cudaStream_t st, const float *A, int64_t rows, int cols, int lda,

@@ -1,0 +1,802 @@
+// rnn1_tc.cu -- tcgen05 persistent recurrent kernels for the GRU and vanilla-RNN cells (bf16 tensor-core path):
+// reference model.py:14-25 (GRUCell / BasicRNNCell) unrolled by custom_rnn_autodecoder (model.py:66-95) and their
+// BPTT (model.py:182), one launch per layer and direction running all T steps.
+//
+// Partition.  Unlike the LSTM (rnn_tc.cu), whose recurrent matrix needs a 16-CTA cluster, the recurrent weights of
+// these cells fit on ONE SM at the reference's sizes (GRU, H = 256: Wg_h 256 KB + Wc_h 128 KB in bf16 = 192 KB of
+// shared memory + 192 KB of tensor memory; RNN: 128 KB, all in tensor memory).  So a CTA owns N = 16 batch rows and
+// ALL hidden units, the weights stay resident for the whole launch, and the recurrent state never leaves the SM
+// between steps: no cluster, no exchange through L2, no cluster barrier -- a step is
+// MMA -> tcgen05.ld -> gate math in registers -> next operand tile in shared memory -> MMA.
+//
+// Products are transposed so that the hidden units are the MMA M dimension (128-row tiles; lane = unit) and the
+// batch tile is the N dimension:   D^T[units, N] = W^T[units, K] * h^T[K, N].
+//   * warp 8 issues tcgen05.mma; the A tiles (weights) are read from tensor memory (TS form) or from shared memory
+//     (UMMA K-major, 128B swizzle), whichever the host-side placement gave them.  The same thread sends the operand
+//     tiles to global memory with TMA stores: the tile the next product reads IS h_t (forward: the `hprev` record the
+//     weight-gradient GEMM reads; GRU: also r*h) resp. d(pre-activation) (backward), already in bf16;
+//   * warps 0-7 are elementwise: warp w reads TMEM lane quarter w%4 of m-tile w/4 (unit = 128*(w/4) + 32*(w%4) +
+//     lane) for all N columns, applies the gate math in registers (fp32 state in registers), and writes the next
+//     B operand (bf16, K-major swizzled) straight into shared memory.  Its global loads (hoisted projection, saved
+//     activations, d(out)) are issued before it waits for the product and were prefetched into L2 two steps earlier.
+// GRU (TF 0.x semantics): two dependent products per step -- gates r,u on h, then the candidate on r*h.
+// BPTT mirrors it: d(r*h) = d(pre_c) * Wc_h^T, then d(h) += [d(pre_r), d(pre_u)] * Wg_h^T.
+#include <stdlib.h>
+#include <type_traits>
+
+#include "common.cuh"
+#include "skrnn_math.h"
+#include "tc_ptx.cuh"
+
+namespace {
+
+constexpr int R1_N = 16;          // batch rows per CTA (MMA N)
+constexpr int R1_EPI_WARPS = 8;
+constexpr int R1_THREADS = 32 * (R1_EPI_WARPS + 1);
+constexpr int R1_MAX_TILES = 6;
+
+struct R1Tile {   // one 128-row weight tile (MMA A operand), K = 64 * nkb
+  int in_tmem;    // 1: tensor memory at column `off`; 0: shared memory at byte offset `off`
+  int off;
+  int nkb;
+  int img;        // byte offset of the tile's image in the packed buffer (shared-memory tiles pre-swizzled)
+};
+
+struct R1Args {
+  int B, T, H, G, MU, nkb;
+  int ntiles;
+  R1Tile tile[R1_MAX_TILES];
+  int smem_w_bytes, tmem_cols;
+  int row0, dropout;
+  float keep;
+  uint64_t seed;
+  const unsigned char *eoc;  // [T,B]
+  const float *state_in;     // [B,H]
+  float *state_out;
+  const float *mask;         // [B,T,H] or null
+  const float *xw;           // [T,B,G] fp32: hoisted x*Wx + b
+  __nv_bfloat16 *out_bf, *hprev_bf, *acts_bf;
+  const float *dout;         // [T,B,H] fp32
+  float *dbias0, *dbias1;
+  const uint8_t *wimg;
+  int debug;                 // SKRNN_TC_DEBUG=1: CTA 0 prints its per-phase cycle split
+};
+
+#define R1_WAIT(bar, par, tag) mbar_wait_wd(bar, par, tag, 1u << 22)
+// debug timing: laps of one thread accumulate into shared-memory slots
+#define R1_LAP(slot) do { if (dbg) { const uint32_t now_ = (uint32_t)clock(); tk[slot] += (long long)(now_ - lapt); lapt = now_; } } while (0)
+
+struct R1Smem {
+  uint32_t base, s_w, s_b1, s_b2, s_bar;
+  uint8_t *gen;
+};
+__device__ __forceinline__ R1Smem r1_smem(uint8_t *raw, int w_bytes, int b1_bytes, int b2_bytes) {
+  R1Smem s;
+  const uint32_t r = smem_u32(raw);
+  s.base = (r + 1023u) & ~1023u;
+  s.gen = raw + (s.base - r);
+  s.s_w = s.base;
+  s.s_b1 = s.s_w + (uint32_t)w_bytes;
+  s.s_b2 = s.s_b1 + (uint32_t)b1_bytes;
+  s.s_bar = s.s_b2 + (uint32_t)b2_bytes;
+  return s;
+}
+
+// resident weights: shared-memory tiles are straight copies of their pre-swizzled images, tensor-memory tiles are
+// written row by row (lane = row) with tcgen05.st
+__device__ __forceinline__ void r1_load_smem_tiles(const R1Args &a, const R1Smem &s, int tid) {
+  for (int j = 0; j < a.ntiles; ++j) {
+    if (a.tile[j].in_tmem) continue;
+    const uint4 *src = reinterpret_cast<const uint4 *>(a.wimg + a.tile[j].img);
+    uint4 *dst = reinterpret_cast<uint4 *>(s.gen + a.tile[j].off);
+    for (int i = tid; i < a.tile[j].nkb * 1024; i += R1_THREADS) dst[i] = __ldg(src + i);
+  }
+}
+__device__ __forceinline__ void r1_load_tmem_tiles(const R1Args &a, uint32_t tmem_base, int warp, int lane) {
+  if (warp >= 4) return;
+  const int e = 32 * warp + lane;
+  for (int j = 0; j < a.ntiles; ++j) {
+    if (!a.tile[j].in_tmem) continue;
+    const int nkb = a.tile[j].nkb;
+    const uint32_t *src = reinterpret_cast<const uint32_t *>(a.wimg + a.tile[j].img) + (size_t)e * (nkb * 32);
+    for (int cb = 0; cb < nkb; ++cb) {
+      uint32_t v[32];
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const uint4 x = __ldg(reinterpret_cast<const uint4 *>(src + cb * 32) + i);
+        v[4 * i] = x.x; v[4 * i + 1] = x.y; v[4 * i + 2] = x.z; v[4 * i + 3] = x.w;
+      }
+      tc_st32(tmem_base + (uint32_t)a.tile[j].off + ((uint32_t)(32 * warp) << 16) + (uint32_t)(cb * 32), v);
+    }
+  }
+}
+
+// D[acc] = A(tile) * B: B is a K-major tile of R1_N rows at shared address s_b (k-block stride R1_N*128 bytes)
+__device__ __forceinline__ void r1_issue_tile(uint32_t acc, const R1Tile &tl, uint32_t s_w, uint32_t tmem_base, uint32_t s_b,
+                                              uint32_t idesc) {
+  const uint64_t descB0 = make_desc(s_b, 0, 1024);
+  for (int kb = 0; kb < tl.nkb; ++kb) {
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const uint32_t accum = (kb > 0 || k > 0) ? 1u : 0u;
+      const uint64_t db = descB0 + (uint64_t)(kb * (R1_N * 8) + 2 * k);
+      if (tl.in_tmem)
+        tc_mma_bf16_ts(acc, tmem_base + (uint32_t)tl.off + (uint32_t)(kb * 32 + k * 8), db, idesc, accum);
+      else
+        tc_mma_bf16(acc, make_desc(s_w + (uint32_t)tl.off + (uint32_t)kb * 16384u, 0, 1024) + (uint64_t)(2 * k), db, idesc, accum);
+    }
+  }
+}
+
+// the operand tile at s_b (nkb k-blocks of [R1_N rows][64 bf16], 128B-swizzled) -> columns [col0, col0 + 64*nkb) of rows
+// [b0, b0 + R1_N) at step t of a [T,B,ld] bf16 array (rows past B are clipped by the tensor map)
+__device__ __forceinline__ void r1_store_tile(const CUtensorMap *tm, uint32_t s_b, int nkb, int col0, int b0, int t) {
+  for (int kb = 0; kb < nkb; ++kb) tma_store_3d(tm, s_b + (uint32_t)kb * (R1_N * 128), col0 + 64 * kb, b0, t);
+}
+
+// byte offset of element (row n, column k) in such a tile: per-thread part for a fixed k, then the row part
+__device__ __forceinline__ uint32_t r1_bcol(int k) { return (uint32_t)((k >> 6) * (R1_N * 128) + ((k & 7) << 1)); }
+__device__ __forceinline__ uint32_t r1_bchunk(int k) { return (uint32_t)(((k & 63) >> 3) << 4); }
+#define R1_BOFF(colbase, chunk4, n) ((colbase) + (uint32_t)((n) * 128) + ((chunk4) ^ (uint32_t)(((n) & 7) << 4)))
+__device__ __forceinline__ void r1_sts_bf16(uint8_t *p, float v) { *reinterpret_cast<__nv_bfloat16 *>(p) = __float2bfloat16_rn(v); }
+
+__device__ __forceinline__ float r1_ld_bf16(const char *p) {
+  return __uint_as_float((uint32_t)(*reinterpret_cast<const unsigned short *>(p)) << 16);
+}
+
+// L2 prefetch of the 128-byte line holding (row b0 + lane, column col) of a [T,B,ld] array at step t: one instruction
+// per warp brings in what the warp's 32 units will load for the tile's rows two steps later
+__device__ __forceinline__ void r1_prefetch(const void *base, size_t elem_bytes, int t, int T, int B, int b0, int ld, int col,
+                                            int lane) {
+  if (t < 0 || t >= T || lane >= R1_N || b0 + lane >= B) return;
+  const char *p = reinterpret_cast<const char *>(base) + (((size_t)t * B + b0 + lane) * ld + col) * elem_bytes;
+  asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
+}
+
+// eoc flag byte of (t, b0 + lane), requested one step ahead; the ballot of it is the step's row mask
+__device__ __forceinline__ unsigned char r1_eoc_raw(const unsigned char *eoc, int t, int T, int B, int b0, int lane) {
+  const int b = b0 + lane;
+  return (t >= 0 && t < T && lane < R1_N && b < B) ? __ldg(eoc + (size_t)t * B + b) : (unsigned char)0;
+}
+
+// per-step output-dropout scale of (row b0+n, t, unit): 1/keep or 0 (model.py:29-30); 1 when dropout is off
+__device__ __forceinline__ void r1_drop_scales(const R1Args &a, int t, int b0, int unit, bool uvalid, uint32_t drop_unit,
+                                               float (&dsc)[R1_N]) {
+#pragma unroll
+  for (int n = 0; n < R1_N; ++n) dsc[n] = 1.0f;
+  if (!a.dropout || !uvalid) return;
+  const float inv_keep = 1.0f / a.keep;
+  const uint32_t pre = skm_drop_prefix(a.seed, drop_unit, (uint32_t)t);
+#pragma unroll
+  for (int n = 0; n < R1_N; ++n) {
+    const int b = b0 + n;
+    if (b < a.B)
+      dsc[n] = a.mask != nullptr ? a.mask[((int64_t)b * a.T + t) * a.H + unit] * inv_keep
+                                 : (skm_u01(skm_drop_finish(pre, (uint32_t)(a.row0 + b))) < a.keep ? inv_keep : 0.0f);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// forward.  CELL: 1 gru, 2 rnn
+// ------------------------------------------------------------------------------------------------
+template <int CELL>
+__global__ void __launch_bounds__(R1_THREADS, 1)
+rnn1_fwd_kernel(const __grid_constant__ CUtensorMap tm_hp, const __grid_constant__ CUtensorMap tm_aux, R1Args a) {
+  constexpr int N = R1_N;
+  constexpr int NB1 = CELL == 2 ? 2 : 1;  // rnn: the h tile is double-buffered (see the store ordering below)
+  extern __shared__ uint8_t smem_raw[];
+  const int H = a.H, B = a.B, T = a.T, G = a.G, MU = a.MU, nkb = a.nkb;
+  const int btile = nkb * N * 128;
+  const R1Smem s = r1_smem(smem_raw, a.smem_w_bytes, NB1 * btile, CELL == 1 ? btile : 0);
+  const uint32_t bar_op1 = s.s_bar, bar_acc1 = s.s_bar + 8, bar_op2 = s.s_bar + 16, bar_acc2 = s.s_bar + 24;
+  const uint32_t tmem_holder = s.s_bar + 32;
+  volatile uint32_t *tmem_holder_ptr = reinterpret_cast<volatile uint32_t *>(s.gen + (tmem_holder - s.base));
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int b0 = blockIdx.x * N;
+  __shared__ long long tk[16];
+  if (tid < 16) tk[tid] = 0;
+
+  r1_load_smem_tiles(a, s, tid);
+  if (tid == 0) {
+    mbar_init(bar_op1, 128 * MU);
+    mbar_init(bar_acc1, 1);
+    mbar_init(bar_op2, 128 * MU);
+    mbar_init(bar_acc2, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == R1_EPI_WARPS) tc_alloc(tmem_holder, (uint32_t)a.tmem_cols);
+  {
+    uint4 *z = reinterpret_cast<uint4 *>(s.gen + (s.s_b1 - s.base));
+    const int n16 = (NB1 + (CELL == 1 ? 1 : 0)) * btile / 16;
+    for (int i = tid; i < n16; i += R1_THREADS) z[i] = make_uint4(0, 0, 0, 0);
+  }
+  fence_proxy_async_smem();
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_holder_ptr;
+  r1_load_tmem_tiles(a, tmem_base, warp, lane);
+
+  const int q = warp & 3, mt = warp >> 2;
+  const bool active = warp < R1_EPI_WARPS && mt < MU;
+  const int unit = mt * 128 + 32 * q + lane;
+  const bool uvalid = active && unit < H;
+  const int nvalid = min(N, B - b0);
+  const uint32_t bcol = r1_bcol(unit), bch = r1_bchunk(unit);
+  uint8_t *b1_gen = s.gen + (s.s_b1 - s.base);
+  uint8_t *b2_gen = s.gen + (s.s_b2 - s.base);
+  float hcur[N];
+#pragma unroll
+  for (int n = 0; n < N; ++n) {
+    hcur[n] = (uvalid && n < nvalid) ? a.state_in[(size_t)(b0 + n) * H + unit] : 0.f;
+    if (uvalid) r1_sts_bf16(b1_gen + R1_BOFF(bcol, bch, n), hcur[n]);
+  }
+  fence_proxy_async_smem();
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+
+  if (warp == R1_EPI_WARPS) {
+    // ---------------- MMA issuer + TMA stores of the operand tiles ----------------
+    // Ordering of a tile's store against its next overwrite: the store is issued right after a tcgen05.commit, the
+    // elementwise warps overwrite the tile only after a LATER commit has arrived, and this thread waits for its
+    // outstanding stores to have read shared memory before issuing that later commit (one full elementwise phase
+    // after the store was issued, so the wait costs nothing).  The rnn has one product per step, hence two h tiles.
+    if (elect_one()) {
+      const bool dbg = a.debug && blockIdx.x == 0;
+      uint32_t lapt = dbg ? (uint32_t)clock() : 0u;
+      const uint32_t idesc = make_idesc_bf16(128, N, false, false);
+      const int ngate = CELL == 1 ? 2 : 1;
+      for (int t = 0; t < T; ++t) {
+        if (t > 0) {
+          R1_WAIT(bar_op1, (t - 1) & 1, 1);
+          tc_fence_after();
+        }
+        R1_LAP(8);
+        const uint32_t sb1 = s.s_b1 + (uint32_t)((NB1 == 2 ? (t & 1) : 0) * btile);
+        for (int j = 0; j < ngate * MU; ++j) r1_issue_tile(tmem_base + (uint32_t)(j * N), a.tile[j], s.s_w, tmem_base, sb1, idesc);
+        tma_store_wait_read();
+        tc_commit(bar_acc1);
+        r1_store_tile(&tm_hp, sb1, nkb, 0, b0, t);  // h fed to step t
+        R1_LAP(9);
+        if constexpr (CELL == 1) {
+          R1_WAIT(bar_op2, t & 1, 2);
+          tc_fence_after();
+          R1_LAP(10);
+          for (int j = 2 * MU; j < 3 * MU; ++j) r1_issue_tile(tmem_base + (uint32_t)(j * N), a.tile[j], s.s_w, tmem_base, s.s_b2, idesc);
+          tma_store_wait_read();
+          tc_commit(bar_acc2);
+          r1_store_tile(&tm_aux, s.s_b2, nkb, 0, b0, t);  // r*h of step t
+          R1_LAP(11);
+        }
+      }
+      tma_store_wait_all();
+      if (dbg)
+        printf("[rnn1 fwd cell %d] MMA thread cycles/step: wait operand-1 %lld, issue+store %lld, wait operand-2 %lld, issue+store %lld\n",
+               CELL, tk[8] / T, tk[9] / T, tk[10] / T, tk[11] / T);
+    }
+    __syncwarp();
+  } else if (active) {
+    // ---------------- elementwise warps ----------------
+    const uint32_t lane_addr = tmem_base + ((uint32_t)(32 * q) << 16);
+    const uint32_t drop_unit = skm_drop_unit(a.seed, (uint32_t)unit);
+    const int u0w = unit - lane;  // first unit of this warp
+    // per-thread views of (t, b0, unit) of the step's arrays: base pointer advanced per step, row n at n * row stride
+    const char *xw_p = reinterpret_cast<const char *>(a.xw + (size_t)b0 * G + unit);
+    char *out_p = reinterpret_cast<char *>(a.out_bf + (size_t)b0 * H + unit);
+    char *act_p = reinterpret_cast<char *>(a.acts_bf + (size_t)b0 * G + unit);
+    const uint32_t xw_rs = (uint32_t)G * 4u, out_rs = (uint32_t)H * 2u, act_rs = (uint32_t)G * 2u;
+    const size_t xw_ts = (size_t)B * G * 4, out_ts = (size_t)B * H * 2, act_ts = (size_t)B * G * 2;
+    const uint32_t gH4 = (uint32_t)H * 4u, gH2 = (uint32_t)H * 2u;
+    unsigned char eoc_raw = r1_eoc_raw(a.eoc, 0, T, B, b0, lane);
+    const bool dbg = a.debug && blockIdx.x == 0 && tid == 0;
+    uint32_t lapt = dbg ? (uint32_t)clock() : 0u;
+
+    auto body = [&](auto full_tag, int t) {
+      constexpr bool FULL = decltype(full_tag)::value;
+      // everything that does not depend on the recurrence is requested before waiting for the product
+      float x0[N], x1[N], x2[N];
+#pragma unroll
+      for (int n = 0; n < N; ++n) {
+        const bool ok = uvalid && (FULL || n < nvalid);
+        const char *p = xw_p + (uint32_t)n * xw_rs;
+        x0[n] = ok ? __ldg(reinterpret_cast<const float *>(p)) : 0.f;
+        x1[n] = 0.f; x2[n] = 0.f;
+        if constexpr (CELL == 1) {
+          x1[n] = ok ? __ldg(reinterpret_cast<const float *>(p + gH4)) : 0.f;
+          x2[n] = ok ? __ldg(reinterpret_cast<const float *>(p + 2 * gH4)) : 0.f;
+        }
+      }
+      if (u0w < H) {
+        r1_prefetch(a.xw, 4, t + 2, T, B, b0, G, u0w, lane);
+        if constexpr (CELL == 1) {
+          r1_prefetch(a.xw, 4, t + 2, T, B, b0, G, H + u0w, lane);
+          r1_prefetch(a.xw, 4, t + 2, T, B, b0, G, 2 * H + u0w, lane);
+        }
+      }
+      const uint32_t eoc_m = __ballot_sync(0xffffffffu, eoc_raw != 0);
+      eoc_raw = r1_eoc_raw(a.eoc, t + 1, T, B, b0, lane);
+      float dsc[N];
+      r1_drop_scales(a, t, b0, unit, uvalid, drop_unit, dsc);
+      float ug[N];
+#pragma unroll
+      for (int n = 0; n < N; ++n) ug[n] = 0.f;
+      R1_LAP(0);
+      if constexpr (CELL == 1) {
+        R1_WAIT(bar_acc1, t & 1, 3);
+        R1_LAP(1);
+        tc_fence_after();
+        uint32_t rr[N], ru[N];
+        tc_ldn<N>(lane_addr + (uint32_t)(mt * N), rr);
+        tc_ldn<N>(lane_addr + (uint32_t)((MU + mt) * N), ru);
+        tc_fence_before();
+        float rg[N];
+#pragma unroll
+        for (int n = 0; n < N; ++n) {
+          rg[n] = sigmoid_approx(__uint_as_float(rr[n]) + x0[n]);
+          ug[n] = sigmoid_approx(__uint_as_float(ru[n]) + x1[n]);
+          if (uvalid) r1_sts_bf16(b2_gen + R1_BOFF(bcol, bch, n), rg[n] * hcur[n]);
+        }
+        fence_proxy_async_smem();
+        mbar_arrive(bar_op2);
+        R1_LAP(2);
+        if (uvalid) {
+#pragma unroll
+          for (int n = 0; n < N; ++n) {
+            if (FULL || n < nvalid) {
+              char *p = act_p + (uint32_t)n * act_rs;
+              *reinterpret_cast<__nv_bfloat16 *>(p) = __float2bfloat16_rn(rg[n]);
+              *reinterpret_cast<__nv_bfloat16 *>(p + gH2) = __float2bfloat16_rn(ug[n]);
+            }
+          }
+        }
+        R1_LAP(3);
+      }
+      R1_WAIT(CELL == 1 ? bar_acc2 : bar_acc1, t & 1, 4);
+      R1_LAP(4);
+      tc_fence_after();
+      uint32_t rc[N];
+      tc_ldn<N>(lane_addr + (uint32_t)((CELL == 1 ? 2 * MU + mt : mt) * N), rc);
+      tc_fence_before();
+      float h2[N];
+      uint8_t *b1w = b1_gen + (NB1 == 2 ? ((t + 1) & 1) * btile : 0);
+#pragma unroll
+      for (int n = 0; n < N; ++n) {
+        const float cand = tanh_approx(__uint_as_float(rc[n]) + (CELL == 1 ? x2[n] : x0[n]));
+        h2[n] = CELL == 1 ? fmaf(ug[n], hcur[n] - cand, cand) : cand;   // u*h + (1-u)*c
+        float hn = h2[n];
+        if ((eoc_m >> n) & 1u)  // eoc: back to the FED state (model.py:82-92); warp-uniform and rare
+          hn = uvalid ? __ldg(a.state_in + (size_t)(b0 + n) * H + unit) : 0.f;
+        hcur[n] = hn;
+        if (uvalid) r1_sts_bf16(b1w + R1_BOFF(bcol, bch, n), hn);
+        if constexpr (CELL == 1) x2[n] = cand;
+      }
+      fence_proxy_async_smem();
+      mbar_arrive(bar_op1);
+      R1_LAP(5);
+      // off the dependent chain: layer output (pre reset, dropout applied) and the activation BPTT needs
+      if (uvalid) {
+#pragma unroll
+        for (int n = 0; n < N; ++n) {
+          if (FULL || n < nvalid) {
+            *reinterpret_cast<__nv_bfloat16 *>(out_p + (uint32_t)n * out_rs) = __float2bfloat16_rn(h2[n] * dsc[n]);
+            *reinterpret_cast<__nv_bfloat16 *>(act_p + (uint32_t)n * act_rs + (CELL == 1 ? 2 * gH2 : 0u)) =
+                __float2bfloat16_rn(CELL == 1 ? x2[n] : h2[n]);
+          }
+        }
+      }
+      xw_p += xw_ts; out_p += out_ts; act_p += act_ts;
+      R1_LAP(6);
+    };
+    for (int t = 0; t < T; ++t) {
+      if (nvalid == N) body(std::true_type{}, t); else body(std::false_type{}, t);
+    }
+    if (uvalid) {
+#pragma unroll
+      for (int n = 0; n < N; ++n)
+        if (n < nvalid) a.state_out[(size_t)(b0 + n) * H + unit] = hcur[n];
+    }
+    if (dbg)
+      printf("[rnn1 fwd cell %d] elementwise thread cycles/step: loads issue %lld, wait acc-1 %lld, gates r,u + operand %lld, stores %lld, "
+             "wait acc %lld, cell + operand %lld, stores %lld\n", CELL, tk[0] / T, tk[1] / T, tk[2] / T, tk[3] / T, tk[4] / T, tk[5] / T,
+             tk[6] / T);
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == R1_EPI_WARPS) tc_dealloc(tmem_base, (uint32_t)a.tmem_cols);
+}
+
+// ------------------------------------------------------------------------------------------------
+// backward (BPTT).  d(pre-activation) leaves as TMA stores of the operand tiles: no per-thread global stores.
+// ------------------------------------------------------------------------------------------------
+template <int CELL>
+__global__ void __launch_bounds__(R1_THREADS, 1) rnn1_bwd_kernel(const __grid_constant__ CUtensorMap tm_dp, R1Args a) {
+  constexpr int N = R1_N;
+  constexpr int NB1 = CELL == 2 ? 2 : 1;
+  extern __shared__ uint8_t smem_raw[];
+  const int H = a.H, B = a.B, T = a.T, G = a.G, MU = a.MU, nkb = a.nkb;
+  const int btile = nkb * N * 128;
+  // b1: d(pre) of the candidate (gru) / of the cell (rnn, two buffers), K = H;  b2 (gru): d(pre) of the gates, K = 2H
+  const R1Smem s = r1_smem(smem_raw, a.smem_w_bytes, NB1 * btile, CELL == 1 ? 2 * btile : 0);
+  const uint32_t bar_op1 = s.s_bar, bar_acc1 = s.s_bar + 8, bar_op2 = s.s_bar + 16, bar_acc2 = s.s_bar + 24;
+  const uint32_t tmem_holder = s.s_bar + 32;
+  volatile uint32_t *tmem_holder_ptr = reinterpret_cast<volatile uint32_t *>(s.gen + (tmem_holder - s.base));
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int b0 = blockIdx.x * N;
+  __shared__ long long tk[16];
+  if (tid < 16) tk[tid] = 0;
+
+  r1_load_smem_tiles(a, s, tid);
+  if (tid == 0) {
+    mbar_init(bar_op1, 128 * MU);
+    mbar_init(bar_acc1, 1);
+    mbar_init(bar_op2, 128 * MU);
+    mbar_init(bar_acc2, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == R1_EPI_WARPS) tc_alloc(tmem_holder, (uint32_t)a.tmem_cols);
+  {
+    uint4 *z = reinterpret_cast<uint4 *>(s.gen + (s.s_b1 - s.base));
+    const int n16 = (NB1 + (CELL == 1 ? 2 : 0)) * btile / 16;
+    for (int i = tid; i < n16; i += R1_THREADS) z[i] = make_uint4(0, 0, 0, 0);
+  }
+  fence_proxy_async_smem();
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_holder_ptr;
+  r1_load_tmem_tiles(a, tmem_base, warp, lane);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+
+  const int q = warp & 3, mt = warp >> 2;
+  const bool active = warp < R1_EPI_WARPS && mt < MU;
+  const int unit = mt * 128 + 32 * q + lane;
+  const bool uvalid = active && unit < H;
+  const int nvalid = min(N, B - b0);
+
+  if (warp == R1_EPI_WARPS) {
+    // ---------------- MMA issuer + TMA stores of d(pre) (same ordering argument as in the forward kernel) ----------------
+    if (elect_one()) {
+      const uint32_t idesc = make_idesc_bf16(128, N, false, false);
+      for (int t = T - 1, st = 0; t >= 0; --t, ++st) {
+        if constexpr (CELL == 1) {
+          // d(r*h) = d(pre_c) * Wc_h^T
+          R1_WAIT(bar_op1, st & 1, 11);
+          tc_fence_after();
+          for (int j = 0; j < MU; ++j) r1_issue_tile(tmem_base + (uint32_t)(j * N), a.tile[j], s.s_w, tmem_base, s.s_b1, idesc);
+          tma_store_wait_read();
+          tc_commit(bar_acc1);
+          r1_store_tile(&tm_dp, s.s_b1, nkb, 2 * H, b0, t);
+          R1_WAIT(bar_op2, st & 1, 12);
+          tc_fence_after();
+          if (t > 0)  // d(h_{t-1}) += [d(pre_r), d(pre_u)] * Wg_h^T
+            for (int j = 0; j < MU; ++j)
+              r1_issue_tile(tmem_base + (uint32_t)((MU + j) * N), a.tile[MU + j], s.s_w, tmem_base, s.s_b2, idesc);
+          tma_store_wait_read();
+          if (t > 0) tc_commit(bar_acc2);
+          r1_store_tile(&tm_dp, s.s_b2, 2 * nkb, 0, b0, t);
+        } else {
+          R1_WAIT(bar_op1, st & 1, 13);
+          tc_fence_after();
+          const uint32_t sb1 = s.s_b1 + (uint32_t)((st & 1) * btile);
+          if (t > 0)
+            for (int j = 0; j < MU; ++j) r1_issue_tile(tmem_base + (uint32_t)(j * N), a.tile[j], s.s_w, tmem_base, sb1, idesc);
+          tma_store_wait_read();
+          if (t > 0) tc_commit(bar_acc1);
+          r1_store_tile(&tm_dp, sb1, nkb, 0, b0, t);
+        }
+      }
+      tma_store_wait_all();
+    }
+    __syncwarp();
+  } else if (active) {
+    // ---------------- elementwise warps ----------------
+    const uint32_t lane_addr = tmem_base + ((uint32_t)(32 * q) << 16);
+    const uint32_t drop_unit = skm_drop_unit(a.seed, (uint32_t)unit);
+    const uint32_t bcol = r1_bcol(unit), bch = r1_bchunk(unit);
+    const uint32_t bcol_u = r1_bcol(H + unit), bch_u = r1_bchunk(H + unit);
+    uint8_t *b1_gen = s.gen + (s.s_b1 - s.base);
+    uint8_t *b2_gen = s.gen + (s.s_b2 - s.base);
+    const int u0w = unit - lane;
+    // per-thread views of (t, b0, unit), walking backwards in t
+    const char *act_p = reinterpret_cast<const char *>(a.acts_bf + ((size_t)(T - 1) * B + b0) * G + unit);
+    const char *hp_p = reinterpret_cast<const char *>(a.hprev_bf + ((size_t)(T - 1) * B + b0) * H + unit);
+    const char *do_p = reinterpret_cast<const char *>(a.dout + ((size_t)(T - 1) * B + b0) * H + unit);
+    const uint32_t act_rs = (uint32_t)G * 2u, hp_rs = (uint32_t)H * 2u, do_rs = (uint32_t)H * 4u;
+    const size_t act_ts = (size_t)B * G * 2, hp_ts = (size_t)B * H * 2, do_ts = (size_t)B * H * 4;
+    const uint32_t gH2 = (uint32_t)H * 2u;
+    unsigned char eoc_raw = r1_eoc_raw(a.eoc, T - 1, T, B, b0, lane);
+    float dhc[N];
+#pragma unroll
+    for (int n = 0; n < N; ++n) dhc[n] = 0.f;
+    float bs0 = 0.f, bs1 = 0.f, bs2 = 0.f;  // bias gradients of my unit: rnn: bs0; gru: r, u, c
+    const bool dbg = a.debug && blockIdx.x == 0 && tid == 0;
+    uint32_t lapt = dbg ? (uint32_t)clock() : 0u;
+
+    auto body = [&](auto full_tag, int t, int st) {
+      constexpr bool FULL = decltype(full_tag)::value;
+      // saved activations and d(out) of the step: requested before waiting for the previous step's product
+      float a0[N], a1[N], a2[N], hv[N], d_o[N];
+#pragma unroll
+      for (int n = 0; n < N; ++n) {
+        const bool ok = uvalid && (FULL || n < nvalid);
+        const char *pa = act_p + (uint32_t)n * act_rs;
+        a0[n] = ok ? r1_ld_bf16(pa) : 0.f;
+        d_o[n] = ok ? __ldg(reinterpret_cast<const float *>(do_p + (uint32_t)n * do_rs)) : 0.f;
+        a1[n] = 0.f; a2[n] = 0.f; hv[n] = 0.f;
+        if constexpr (CELL == 1) {
+          a1[n] = ok ? r1_ld_bf16(pa + gH2) : 0.f;
+          a2[n] = ok ? r1_ld_bf16(pa + 2 * gH2) : 0.f;
+          hv[n] = ok ? r1_ld_bf16(hp_p + (uint32_t)n * hp_rs) : 0.f;
+        }
+      }
+      if (u0w < H) {
+        r1_prefetch(a.dout, 4, t - 2, T, B, b0, H, u0w, lane);
+        r1_prefetch(a.acts_bf, 2, t - 2, T, B, b0, G, u0w, lane);
+        if constexpr (CELL == 1) {
+          r1_prefetch(a.acts_bf, 2, t - 2, T, B, b0, G, H + u0w, lane);
+          r1_prefetch(a.acts_bf, 2, t - 2, T, B, b0, G, 2 * H + u0w, lane);
+          r1_prefetch(a.hprev_bf, 2, t - 2, T, B, b0, H, u0w, lane);
+        }
+      }
+      const uint32_t eoc_m = __ballot_sync(0xffffffffu, eoc_raw != 0);
+      eoc_raw = r1_eoc_raw(a.eoc, t - 1, T, B, b0, lane);
+      float dsc[N];
+      r1_drop_scales(a, t, b0, unit, uvalid, drop_unit, dsc);
+      R1_LAP(0);
+      if (st > 0) {  // d(h_t) from the step after: the product issued last iteration
+        R1_WAIT(CELL == 1 ? bar_acc2 : bar_acc1, (st - 1) & 1, 14);
+        tc_fence_after();
+        uint32_t r[N];
+        tc_ldn<N>(lane_addr + (uint32_t)((CELL == 1 ? MU + mt : mt) * N), r);
+        tc_fence_before();
+#pragma unroll
+        for (int n = 0; n < N; ++n) dhc[n] = (CELL == 1 ? dhc[n] : 0.f) + __uint_as_float(r[n]);
+      }
+      R1_LAP(1);
+      if constexpr (CELL == 2) {
+        uint8_t *b1w = b1_gen + (st & 1) * btile;
+#pragma unroll
+        for (int n = 0; n < N; ++n) {
+          const float dh2 = d_o[n] * dsc[n] + (((eoc_m >> n) & 1u) ? 0.f : dhc[n]);
+          const float dp = dh2 * (1.0f - a0[n] * a0[n]);
+          bs0 += dp;
+          if (uvalid) r1_sts_bf16(b1w + R1_BOFF(bcol, bch, n), dp);
+        }
+        fence_proxy_async_smem();
+        mbar_arrive(bar_op1);
+        R1_LAP(2);
+      } else {
+        // a0 = r, a1 = u, a2 = candidate, hv = h fed to the step
+        float du[N];
+#pragma unroll
+        for (int n = 0; n < N; ++n) {
+          const float dh2 = d_o[n] * dsc[n] + (((eoc_m >> n) & 1u) ? 0.f : dhc[n]);
+          du[n] = dh2 * (hv[n] - a2[n]);
+          const float dpc = dh2 * (1.0f - a1[n]) * (1.0f - a2[n] * a2[n]);
+          dhc[n] = dh2 * a1[n];  // direct path h -> h'; the two products add to it below / next iteration
+          bs2 += dpc;
+          if (uvalid) r1_sts_bf16(b1_gen + R1_BOFF(bcol, bch, n), dpc);
+        }
+        fence_proxy_async_smem();
+        mbar_arrive(bar_op1);
+        R1_LAP(2);
+        R1_WAIT(bar_acc1, st & 1, 15);
+        R1_LAP(4);
+        tc_fence_after();
+        uint32_t r[N];
+        tc_ldn<N>(lane_addr + (uint32_t)(mt * N), r);
+        tc_fence_before();
+#pragma unroll
+        for (int n = 0; n < N; ++n) {
+          const float drh = __uint_as_float(r[n]);
+          dhc[n] = fmaf(drh, a0[n], dhc[n]);
+          const float dpr = drh * hv[n] * a0[n] * (1.0f - a0[n]);
+          const float dpu = du[n] * a1[n] * (1.0f - a1[n]);
+          bs0 += dpr;
+          bs1 += dpu;
+          if (uvalid) {
+            r1_sts_bf16(b2_gen + R1_BOFF(bcol, bch, n), dpr);
+            r1_sts_bf16(b2_gen + R1_BOFF(bcol_u, bch_u, n), dpu);
+          }
+        }
+        fence_proxy_async_smem();
+        mbar_arrive(bar_op2);
+        R1_LAP(5);
+      }
+      act_p -= act_ts; hp_p -= hp_ts; do_p -= do_ts;
+    };
+    for (int t = T - 1, st = 0; t >= 0; --t, ++st) {
+      if (nvalid == N) body(std::true_type{}, t, st); else body(std::false_type{}, t, st);
+    }
+    if (uvalid) {
+      if constexpr (CELL == 2) {
+        atomicAdd(a.dbias0 + unit, bs0);
+      } else {
+        atomicAdd(a.dbias0 + unit, bs0);
+        atomicAdd(a.dbias0 + H + unit, bs1);
+        atomicAdd(a.dbias1 + unit, bs2);
+      }
+    }
+    if (dbg)
+      printf("[rnn1 bwd cell %d] elementwise thread cycles/step: loads issue %lld, wait d(h) product %lld, elementwise-1 + operand %lld, "
+             "wait d(r*h) product %lld, elementwise-2 + operand %lld\n", CELL, tk[0] / T, tk[1] / T, tk[2] / T, tk[4] / T, tk[5] / T);
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == R1_EPI_WARPS) tc_dealloc(tmem_base, (uint32_t)a.tmem_cols);
+}
+
+// ------------------------------------------------------------------------------------------------
+// weight images.  Tile value (m, k): trans ? mat[(I + k) * ld + c0 + m0 + m] : mat[(I + m0 + m) * ld + c0 + k]
+//   forward  (trans): A[m][k] = W[k][gate column of unit m0+m]          (h * W: contraction over the input unit k)
+//   backward        : A[m][k] = W[m0+m][k]                              (d(pre) * W^T: contraction over the gate column)
+// Rows m0+m >= H and columns k >= K are zero.
+// ------------------------------------------------------------------------------------------------
+struct R1PackTile { const float *mat; int ld, m0, c0, trans, K, in_tmem, img, nkb; };
+struct R1PackArgs { R1PackTile t[R1_MAX_TILES]; int ntiles, I, H; };
+
+__global__ void r1_pack_kernel(R1PackArgs p, uint8_t *__restrict__ dst) {
+  for (int j = 0; j < p.ntiles; ++j) {
+    const R1PackTile &tl = p.t[j];
+    const int total = 128 * tl.nkb * 64;
+    __nv_bfloat16 *out = reinterpret_cast<__nv_bfloat16 *>(dst + tl.img);
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+      int m, k;
+      if (tl.in_tmem) {
+        m = i / (tl.nkb * 64);
+        k = i % (tl.nkb * 64);
+      } else {
+        const int kb = i / 8192, w = i % 8192;
+        m = w / 64;
+        const int within = w % 64, chunk = within >> 3, el = within & 7;
+        k = kb * 64 + (((chunk ^ (m & 7)) << 3) + el);
+      }
+      const int u = tl.m0 + m;
+      float v = 0.f;
+      if (u < p.H && k < tl.K)
+        v = tl.trans ? tl.mat[(size_t)(p.I + k) * tl.ld + tl.c0 + u] : tl.mat[(size_t)(p.I + u) * tl.ld + tl.c0 + k];
+      out[i] = __float2bfloat16_rn(v);
+    }
+  }
+}
+
+bool r1_eligible(const skrnn_handle *h) {
+  if (h->cfg.precision != SKRNN_PREC_BF16) return false;
+  if (h->cfg.cell != SKRNN_CELL_GRU && h->cfg.cell != SKRNN_CELL_RNN) return false;
+  if (h->H % 64 != 0 || h->H > 256) return false;
+  static int env_off = -1;
+  if (env_off < 0) { const char *e = getenv("SKRNN_DISABLE_TC_RNN"); env_off = (e && e[0] == '1') ? 1 : 0; }
+  return !env_off;
+}
+
+int r1_map(CUtensorMap *m, const void *ptr, int ld, int B, int T) {
+  uint64_t dims[3] = {(uint64_t)ld, (uint64_t)B, (uint64_t)T};
+  uint64_t str[2] = {(uint64_t)ld * 2, (uint64_t)B * ld * 2};
+  uint32_t box[3] = {64, (uint32_t)R1_N, 1};
+  return sk_make_tmap(m, 2, ptr, 3, dims, str, box);
+}
+
+}  // namespace
+
+// 0: the layer ran here; -1: not eligible (the caller uses the fp32 recurrent kernels); > 0: error
+int sk_rnn1_tc_layer(skrnn_handle *h, cudaStream_t st, bool bwd, int l, int B, int T, const float *state_in,
+                     float *state_out, const float *mask, uint64_t seed, int row0, bool training) {
+  if (!r1_eligible(h)) return -1;
+  const int H = h->H, G = h->G, cell = h->cfg.cell;
+  const bool gru = cell == SKRNN_CELL_GRU;
+  if (h->ws.acts_bf[l] == nullptr || h->ws.out_bf[l] == nullptr || h->ws.hprev_bf[l] == nullptr || h->ws.dpre_bf == nullptr ||
+      h->ws.xw[l] == nullptr || (gru && h->ws.aux_bf[l] == nullptr))
+    return -1;
+  const int MU = (H + 127) / 128, nkb = H / 64;
+  const SkLayerParams &lp = h->lp[l];
+  const float *W0 = h->params + lp.w[0];                     // rnn: [I+H, H]; gru gates: [I+H, 2H]
+  const float *W1 = gru ? h->params + lp.w[1] : nullptr;     // gru candidate: [I+H, H]
+
+  // tiles in the order the kernels index them
+  R1PackArgs pk = {};
+  pk.I = lp.I; pk.H = H;
+  int nt = 0;
+  auto add = [&](const float *mat, int ld, int m0, int c0, int trans, int K) {
+    R1PackTile &t = pk.t[nt++];
+    t.mat = mat; t.ld = ld; t.m0 = m0; t.c0 = c0; t.trans = trans; t.K = K; t.nkb = K / 64;
+  };
+  if (!bwd) {
+    if (gru) {
+      for (int g = 0; g < 2; ++g)
+        for (int m = 0; m < MU; ++m) add(W0, 2 * H, 128 * m, g * H, 1, H);
+      for (int m = 0; m < MU; ++m) add(W1, H, 128 * m, 0, 1, H);
+    } else {
+      for (int m = 0; m < MU; ++m) add(W0, H, 128 * m, 0, 1, H);
+    }
+  } else {
+    if (gru) {
+      for (int m = 0; m < MU; ++m) add(W1, H, 128 * m, 0, 0, H);
+      for (int m = 0; m < MU; ++m) add(W0, 2 * H, 128 * m, 0, 0, 2 * H);
+    } else {
+      for (int m = 0; m < MU; ++m) add(W0, H, 128 * m, 0, 0, H);
+    }
+  }
+  pk.ntiles = nt;
+  // placement: the subset of tiles kept in shared memory must fit beside the operand tiles, the rest goes to tensor
+  // memory behind the accumulators (512 columns in all).  A tile read from shared memory costs 4 KB of operand
+  // traffic per MMA (32 cycles at 128 B/clk against 8 cycles of math at N = 16), so take the feasible split with the
+  // MOST tensor memory
+  const int btile = nkb * R1_N * 128;
+  const int b_bytes = (gru ? (bwd ? 3 : 2) : 2) * btile;
+  const int smem_cap = 227 * 1024 - 1024 - 256 - b_bytes;
+  const int acc_cols = (!bwd ? (gru ? 3 : 1) : (gru ? 2 : 1)) * MU * R1_N;
+  int best = -1, best_cols = -1;
+  for (int mask_s = 0; mask_s < (1 << nt); ++mask_s) {
+    int sb = 0, cols = acc_cols;
+    for (int j = 0; j < nt; ++j) {
+      if ((mask_s >> j) & 1) sb += pk.t[j].nkb * 16384;
+      else cols += pk.t[j].nkb * 32;
+    }
+    if (sb <= smem_cap && cols <= 512 && cols > best_cols) { best = mask_s; best_cols = cols; }
+  }
+  if (best < 0) return -1;
+  R1Args a = {};
+  int soff = 0, coff = acc_cols, ioff = 0;
+  for (int j = 0; j < nt; ++j) {
+    R1PackTile &t = pk.t[j];
+    t.in_tmem = ((best >> j) & 1) ? 0 : 1;
+    t.img = ioff;
+    ioff += t.nkb * 16384;
+    a.tile[j].in_tmem = t.in_tmem;
+    a.tile[j].nkb = t.nkb;
+    a.tile[j].img = t.img;
+    if (t.in_tmem) { a.tile[j].off = coff; coff += t.nkb * 32; }
+    else { a.tile[j].off = soff; soff += t.nkb * 16384; }
+  }
+  SK_CHECK((int64_t)ioff <= h->ws.wpack_floats * 4, "weight image workspace too small");
+  {
+    SkLaunch scope(h, st, SK_CAT_MISC);
+    r1_pack_kernel<<<std::min(4 * h->num_sms, (ioff / 2 + 255) / 256), 256, 0, st>>>(pk, reinterpret_cast<uint8_t *>(h->ws.wpack));
+    SK_CUDA(cudaGetLastError());
+  }
+  a.B = B; a.T = T; a.H = H; a.G = G; a.MU = MU; a.nkb = nkb; a.ntiles = nt;
+  a.smem_w_bytes = soff;
+  int tc = 32;
+  while (tc < coff) tc <<= 1;
+  a.tmem_cols = tc;
+  a.row0 = row0;
+  a.dropout = (training && l == h->L - 1 && h->cfg.keep_prob < 1.0f) ? 1 : 0;
+  a.keep = h->cfg.keep_prob;
+  a.seed = seed;
+  a.eoc = h->ws.eoc; a.state_in = state_in; a.state_out = state_out; a.mask = mask;
+  a.xw = h->ws.xw[l];
+  a.out_bf = h->ws.out_bf[l]; a.hprev_bf = h->ws.hprev_bf[l]; a.acts_bf = h->ws.acts_bf[l];
+  a.dout = h->ws.dout;
+  a.dbias0 = h->grads + lp.b[0];
+  a.dbias1 = gru ? h->grads + lp.b[1] : nullptr;
+  a.wimg = reinterpret_cast<const uint8_t *>(h->ws.wpack);
+  {
+    static int dbg_env = -1;
+    if (dbg_env < 0) { const char *e = getenv("SKRNN_TC_DEBUG"); dbg_env = (e && e[0] == '1') ? 1 : 0; }
+    a.debug = dbg_env;
+  }
+  const size_t smem = (size_t)soff + b_bytes + 1024 + 256;
+  const int grid = (B + R1_N - 1) / R1_N;
+  if (!bwd) {
+    CUtensorMap tm_hp, tm_aux;
+    SK_TRY(r1_map(&tm_hp, h->ws.hprev_bf[l], H, B, T));
+    SK_TRY(r1_map(&tm_aux, gru ? h->ws.aux_bf[l] : h->ws.hprev_bf[l], H, B, T));
+    SkLaunch scope(h, st, SK_CAT_RNN_FWD);
+    auto kern = gru ? rnn1_fwd_kernel<1> : rnn1_fwd_kernel<2>;
+    SK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    kern<<<grid, R1_THREADS, smem, st>>>(tm_hp, tm_aux, a);
+  } else {
+    CUtensorMap tm_dp;
+    SK_TRY(r1_map(&tm_dp, h->ws.dpre_bf, G, B, T));
+    SkLaunch scope(h, st, SK_CAT_RNN_BWD);
+    auto kern = gru ? rnn1_bwd_kernel<1> : rnn1_bwd_kernel<2>;
+    SK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    kern<<<grid, R1_THREADS, smem, st>>>(tm_dp, a);
+    h->bias_grad_done = true;
+  }
+  SK_CUDA(cudaGetLastError());
+  return 0;
+}

@@ -547,6 +547,14 @@ int run_layer(skrnn_handle *h, cudaStream_t st, bool bwd, int l, int B, int T, c
     int rc = sk_rnn_tc_layer(h, st, false, l, B, T, x_bt5, state_in, state_out, mask, seed, row0, training);
     if (rc == 0) h->fwd_family[l] = 1;
     if (rc >= 0) return rc;  // handled by the tcgen05 kernels (0) or failed hard (>0)
+    rc = sk_rnn1_tc_layer(h, st, false, l, B, T, state_in, state_out, mask, seed, row0, training);
+    if (rc == 0) h->fwd_family[l] = 3;
+    if (rc >= 0) return rc;
+  } else if (h->fwd_family[l] == 3) {
+    int rc = sk_rnn1_tc_layer(h, st, true, l, B, T, state_in, state_out, mask, seed, row0, training);
+    SK_CHECK(rc == 0, "layer %d: forward ran in the rnn1_tc kernels but their backward failed (rc %d): %s", l, rc,
+             skrnn_last_error());
+    return 0;
   } else if (h->fwd_family[l] == 1) {
     int rc = sk_rnn_tc_layer(h, st, true, l, B, T, x_bt5, state_in, state_out, mask, seed, row0, training);
     SK_CHECK(rc == 0, "layer %d: forward ran in the rnn_tc kernels but their backward failed (rc %d): %s", l, rc,
