@@ -89,10 +89,10 @@ void free_workspace(SkWorkspace &w) {
   w.f32_acts = false;
 }
 
-// bf16 lstm handles run the tcgen05 recurrent kernels, which keep their own bf16 activation records: the fp32 set
+// bf16 handles whose cell runs on the tcgen05 recurrent kernels keep their own bf16 activation records: the fp32 set
 // (xw, hprev, out: 6 of the 10 GB of config 4) is then dead weight and is only allocated if a layer ever falls back
 bool needs_f32_acts_upfront(const skrnn_handle *h) {
-  return !(h->cfg.precision == SKRNN_PREC_BF16 && sk_rnn_tc_eligible(h));
+  return !(h->cfg.precision == SKRNN_PREC_BF16 && (sk_rnn_tc_eligible(h) || sk_rnn1_tc_eligible(h)));
 }
 
 int alloc_f32_acts(skrnn_handle *h) {
@@ -133,7 +133,7 @@ int ensure_workspace(skrnn_handle *h, int B, int T) {
       SK_CUDA(cudaMalloc(&w.hprev_bf[l], rows * h->H * e));
       if (h->cfg.cell == SKRNN_CELL_GRU) SK_CUDA(cudaMalloc(&w.aux_bf[l], rows * h->H * e));
       SK_CUDA(cudaMalloc(&w.acts_bf[l], rows * h->G * e));  // gate activations saved by the tcgen05 recurrent kernels
-      if (h->cfg.cell == SKRNN_CELL_LSTM) SK_CUDA(cudaMalloc(&w.xw_il[l], rows * h->G * e));
+      SK_CUDA(cudaMalloc(&w.xw_il[l], rows * h->G * e));                    // hoisted projection in bf16
     }
   }
   w.cap_rows = rows;
@@ -198,11 +198,26 @@ int run_forward(skrnn_handle *h, cudaStream_t st, int B, int T, const float *x, 
   for (int l = 0; l < h->L; ++l) {
     const SkLayerParams &lp = h->lp[l];
     const Op Xo = layer_input(h, l);
+    h->xw_il_ok[l] = false;
+    if (h->cfg.cell != SKRNN_CELL_LSTM && sk_rnn1_tc_eligible(h) && h->ws.xw_il[l] != nullptr) {
+      // tcgen05 gru / rnn kernels: the projection in bf16, TF's column order (half the bytes the recurrent kernel streams)
+      const int nmat = h->cfg.cell == SKRNN_CELL_GRU ? 2 : 1;
+      for (int wi = 0; wi < nmat; ++wi) {
+        const Op W = weight(h, l, wi);
+        SK_TRY(sk_gemm_tc_bf16out(h, st, (int)R, lp.ncol[wi], lp.I, Xo.b, Xo.ldb, W.b, W.ldb, h->ws.xw_il[l] + (wi ? 2 * H : 0), G,
+                                  h->params + lp.b[wi]));
+      }
+      h->xw_il_ok[l] = true;
+      SK_TRY(sk_rnn_forward_layer(h, st, l, B, T, x, state_in + (size_t)l * B * h->S, state_out + (size_t)l * B * h->S, mask,
+                                  seed, row0, training));
+      if (h->fwd_family[l] == 3) continue;
+      h->xw_il_ok[l] = false;  // declined: redo the layer through the fp32-format projection and the fp32 kernels
+      SK_TRY(alloc_f32_acts(h));
+    }
     if (h->cfg.cell == SKRNN_CELL_GRU) {
       SK_TRY(gemm(h, st, (int)R, 2 * H, lp.I, Xo, true, weight(h, l, 0), true, h->ws.xw[l], G, h->params + lp.b[0], false));
       SK_TRY(gemm(h, st, (int)R, H, lp.I, Xo, true, weight(h, l, 1), true, h->ws.xw[l] + 2 * H, G, h->params + lp.b[1], false));
     } else {
-      h->xw_il_ok[l] = false;
       if (sk_rnn_tc_eligible(h) && h->ws.xw_il[l] != nullptr && h->wx_il[l] != nullptr) {
         // tcgen05 lstm kernels: bf16 projection with the four gates of a unit adjacent (half the bytes of the fp32 one)
         const int ip = (lp.I + 7) / 8 * 8;

@@ -70,8 +70,8 @@ struct SkWorkspace {   // time-major activations for one (B, T) capacity
   __nv_bfloat16 *out_bf[SK_MAX_LAYERS] = {nullptr};  // [T,B,H]
   __nv_bfloat16 *hprev_bf[SK_MAX_LAYERS] = {nullptr};
   __nv_bfloat16 *aux_bf[SK_MAX_LAYERS] = {nullptr};  // gru r*h
-  __nv_bfloat16 *xw_il[SK_MAX_LAYERS] = {nullptr};   // [T,B,H,4]: hoisted x*Wx+b of an lstm layer in bf16, the four gates of
-                                                     // a unit adjacent (input of the tcgen05 forward kernels)
+  __nv_bfloat16 *xw_il[SK_MAX_LAYERS] = {nullptr};   // hoisted x*Wx+b in bf16, the input of the tcgen05 recurrent kernels.  lstm:
+                                                     // [T,B,H,4], the four gates of a unit adjacent; gru / rnn: [T,B,G] in TF's order
   __nv_bfloat16 *acts_bf[SK_MAX_LAYERS] = {nullptr}; // [T,B,H,4]: lstm gate activations i,j,f,o saved by the tcgen05
                                                      // forward kernel for its BPTT counterpart
   __nv_bfloat16 *dpre_bf = nullptr;                  // [T,B,G] of the layer being differentiated (= one of dpre_bf_buf)
@@ -193,6 +193,7 @@ int sk_rnn_tc_layer(skrnn_handle *h, cudaStream_t st, bool bwd, int l, int B, in
                     const float *state_in, float *state_out, const float *mask, uint64_t seed, int row0,
                     bool training);
 // tcgen05 recurrent kernels for the GRU / RNN cells, one CTA per batch tile (rnn1_tc.cu): 0 ok, -1 not eligible, > 0 error
+bool sk_rnn1_tc_eligible(const skrnn_handle *h);
 int sk_rnn1_tc_layer(skrnn_handle *h, cudaStream_t st, bool bwd, int l, int B, int T, const float *state_in,
                      float *state_out, const float *mask, uint64_t seed, int row0, bool training);
 int sk_colsum_bf16(skrnn_handle *h, cudaStream_t st, const __nv_bfloat16 *A, int64_t rows, int cols, int lda,

@@ -54,7 +54,7 @@ struct R1Args {
   const float *state_in;     // [B,H]
   float *state_out;
   const float *mask;         // [B,T,H] or null
-  const float *xw;           // [T,B,G] fp32: hoisted x*Wx + b
+  const __nv_bfloat16 *xw;   // [T,B,G] bf16: hoisted x*Wx + b
   __nv_bfloat16 *out_bf, *hprev_bf, *acts_bf;
   const float *dout;         // [T,B,H] fp32
   float *dbias0, *dbias1;
@@ -111,20 +111,37 @@ __device__ __forceinline__ void r1_load_tmem_tiles(const R1Args &a, uint32_t tme
   }
 }
 
-// D[acc] = A(tile) * B: B is a K-major tile of R1_N rows at shared address s_b (k-block stride R1_N*128 bytes)
-__device__ __forceinline__ void r1_issue_tile(uint32_t acc, const R1Tile &tl, uint32_t s_w, uint32_t tmem_base, uint32_t s_b,
-                                              uint32_t idesc) {
-  const uint64_t descB0 = make_desc(s_b, 0, 1024);
-  for (int kb = 0; kb < tl.nkb; ++kb) {
+// One weight tile as the MMA thread sees it: resolved once before the time loop
+struct R1A {
+  bool in_tmem;
+  uint32_t tm;    // tensor-memory address of the tile (TS form)
+  uint64_t desc;  // shared-memory descriptor of its first k-block
+};
+__device__ __forceinline__ R1A r1_resolve(const R1Tile &tl, uint32_t s_w, uint32_t tmem_base) {
+  R1A r;
+  r.in_tmem = tl.in_tmem != 0;
+  r.tm = tmem_base + (uint32_t)tl.off;
+  r.desc = make_desc(s_w + (uint32_t)tl.off, 0, 1024);
+  return r;
+}
+// D[acc] = A(tile) * B over NKBT k-blocks: B is a K-major tile of R1_N rows with descriptor dB0 (k-block stride
+// R1_N*128 bytes).  Fully unrolled, all operands precomputed: the issuing thread spends ~2 instructions per MMA, so the
+// tensor core's own rate is what counts (measured with tools/mma_rate.cu at N = 16: 9 cycles per MMA with the A tile
+// in tensor memory, 39 from shared memory -- the 4 KB operand read -- and no penalty for chaining on one accumulator).
+template <int NKBT>
+__device__ __forceinline__ void r1_issue(uint32_t acc, const R1A &A, uint64_t dB0, uint32_t idesc) {
+  if (A.in_tmem) {
 #pragma unroll
-    for (int k = 0; k < 4; ++k) {
-      const uint32_t accum = (kb > 0 || k > 0) ? 1u : 0u;
-      const uint64_t db = descB0 + (uint64_t)(kb * (R1_N * 8) + 2 * k);
-      if (tl.in_tmem)
-        tc_mma_bf16_ts(acc, tmem_base + (uint32_t)tl.off + (uint32_t)(kb * 32 + k * 8), db, idesc, accum);
-      else
-        tc_mma_bf16(acc, make_desc(s_w + (uint32_t)tl.off + (uint32_t)kb * 16384u, 0, 1024) + (uint64_t)(2 * k), db, idesc, accum);
-    }
+    for (int kb = 0; kb < NKBT; ++kb)
+#pragma unroll
+      for (int k = 0; k < 4; ++k)
+        tc_mma_bf16_ts(acc, A.tm + (uint32_t)(kb * 32 + k * 8), dB0 + (uint64_t)(kb * (R1_N * 8) + 2 * k), idesc, (kb | k) ? 1u : 0u);
+  } else {
+#pragma unroll
+    for (int kb = 0; kb < NKBT; ++kb)
+#pragma unroll
+      for (int k = 0; k < 4; ++k)
+        tc_mma_bf16(acc, A.desc + (uint64_t)(kb * 1024 + 2 * k), dB0 + (uint64_t)(kb * (R1_N * 8) + 2 * k), idesc, (kb | k) ? 1u : 0u);
   }
 }
 
@@ -159,34 +176,41 @@ __device__ __forceinline__ unsigned char r1_eoc_raw(const unsigned char *eoc, in
   return (t >= 0 && t < T && lane < R1_N && b < B) ? __ldg(eoc + (size_t)t * B + b) : (unsigned char)0;
 }
 
-// per-step output-dropout scale of (row b0+n, t, unit): 1/keep or 0 (model.py:29-30); 1 when dropout is off
-__device__ __forceinline__ void r1_drop_scales(const R1Args &a, int t, int b0, int unit, bool uvalid, uint32_t drop_unit,
-                                               float (&dsc)[R1_N]) {
+// per-step output-dropout scale of (row b0+n, t, unit): 1/keep or 0 (model.py:29-30); 1 when dropout is off.  Rows past
+// the batch get a scale too (their values are never stored).
+__device__ __forceinline__ void r1_drop_scales(const R1Args &a, int t, int b0, int nvalid, int unit, bool uvalid,
+                                               uint32_t drop_unit, float (&dsc)[R1_N]) {
 #pragma unroll
   for (int n = 0; n < R1_N; ++n) dsc[n] = 1.0f;
   if (!a.dropout || !uvalid) return;
   const float inv_keep = 1.0f / a.keep;
-  const uint32_t pre = skm_drop_prefix(a.seed, drop_unit, (uint32_t)t);
+  if (a.mask != nullptr) {  // injected mask (parity tests)
+    const float *mp = a.mask + ((size_t)b0 * a.T + t) * a.H + unit;
+    const size_t rs = (size_t)a.T * a.H;
 #pragma unroll
-  for (int n = 0; n < R1_N; ++n) {
-    const int b = b0 + n;
-    if (b < a.B)
-      dsc[n] = a.mask != nullptr ? a.mask[((int64_t)b * a.T + t) * a.H + unit] * inv_keep
-                                 : (skm_u01(skm_drop_finish(pre, (uint32_t)(a.row0 + b))) < a.keep ? inv_keep : 0.0f);
+    for (int n = 0; n < R1_N; ++n)
+      if (n < nvalid) dsc[n] = __ldg(mp + n * rs) * inv_keep;
+    return;
   }
+  const uint32_t pre = skm_drop_prefix(a.seed, drop_unit, (uint32_t)t);
+  const uint32_t row = (uint32_t)(a.row0 + b0);
+  const float keep = a.keep;
+#pragma unroll
+  for (int n = 0; n < R1_N; ++n) dsc[n] = skm_u01(skm_drop_finish(pre, row + (uint32_t)n)) < keep ? inv_keep : 0.0f;
 }
 
 // ------------------------------------------------------------------------------------------------
 // forward.  CELL: 1 gru, 2 rnn
 // ------------------------------------------------------------------------------------------------
-template <int CELL>
+template <int CELL, int MU, int NKB>
 __global__ void __launch_bounds__(R1_THREADS, 1)
 rnn1_fwd_kernel(const __grid_constant__ CUtensorMap tm_hp, const __grid_constant__ CUtensorMap tm_aux, R1Args a) {
   constexpr int N = R1_N;
   constexpr int NB1 = CELL == 2 ? 2 : 1;  // rnn: the h tile is double-buffered (see the store ordering below)
   extern __shared__ uint8_t smem_raw[];
-  const int H = a.H, B = a.B, T = a.T, G = a.G, MU = a.MU, nkb = a.nkb;
-  const int btile = nkb * N * 128;
+  const int H = a.H, B = a.B, T = a.T, G = a.G;
+  constexpr int nkb = NKB;
+  constexpr int btile = NKB * N * 128;
   const R1Smem s = r1_smem(smem_raw, a.smem_w_bytes, NB1 * btile, CELL == 1 ? btile : 0);
   const uint32_t bar_op1 = s.s_bar, bar_acc1 = s.s_bar + 8, bar_op2 = s.s_bar + 16, bar_acc2 = s.s_bar + 24;
   const uint32_t tmem_holder = s.s_bar + 32;
@@ -246,7 +270,13 @@ rnn1_fwd_kernel(const __grid_constant__ CUtensorMap tm_hp, const __grid_constant
       const bool dbg = a.debug && blockIdx.x == 0;
       uint32_t lapt = dbg ? (uint32_t)clock() : 0u;
       const uint32_t idesc = make_idesc_bf16(128, N, false, false);
-      const int ngate = CELL == 1 ? 2 : 1;
+      constexpr int NG = (CELL == 1 ? 2 : 1) * MU;  // tiles of the first product
+      R1A A1[NG], A2[MU];
+#pragma unroll
+      for (int j = 0; j < NG; ++j) A1[j] = r1_resolve(a.tile[j], s.s_w, tmem_base);
+#pragma unroll
+      for (int j = 0; j < MU; ++j) A2[j] = r1_resolve(a.tile[CELL == 1 ? 2 * MU + j : j], s.s_w, tmem_base);
+      const uint64_t dB2 = make_desc(s.s_b2, 0, 1024);
       for (int t = 0; t < T; ++t) {
         if (t > 0) {
           R1_WAIT(bar_op1, (t - 1) & 1, 1);
@@ -254,7 +284,9 @@ rnn1_fwd_kernel(const __grid_constant__ CUtensorMap tm_hp, const __grid_constant
         }
         R1_LAP(8);
         const uint32_t sb1 = s.s_b1 + (uint32_t)((NB1 == 2 ? (t & 1) : 0) * btile);
-        for (int j = 0; j < ngate * MU; ++j) r1_issue_tile(tmem_base + (uint32_t)(j * N), a.tile[j], s.s_w, tmem_base, sb1, idesc);
+        const uint64_t dB1 = make_desc(sb1, 0, 1024);
+#pragma unroll
+        for (int j = 0; j < NG; ++j) r1_issue<NKB>(tmem_base + (uint32_t)(j * N), A1[j], dB1, idesc);
         tma_store_wait_read();
         tc_commit(bar_acc1);
         r1_store_tile(&tm_hp, sb1, nkb, 0, b0, t);  // h fed to step t
@@ -263,7 +295,8 @@ rnn1_fwd_kernel(const __grid_constant__ CUtensorMap tm_hp, const __grid_constant
           R1_WAIT(bar_op2, t & 1, 2);
           tc_fence_after();
           R1_LAP(10);
-          for (int j = 2 * MU; j < 3 * MU; ++j) r1_issue_tile(tmem_base + (uint32_t)(j * N), a.tile[j], s.s_w, tmem_base, s.s_b2, idesc);
+#pragma unroll
+          for (int j = 0; j < MU; ++j) r1_issue<NKB>(tmem_base + (uint32_t)((2 * MU + j) * N), A2[j], dB2, idesc);
           tma_store_wait_read();
           tc_commit(bar_acc2);
           r1_store_tile(&tm_aux, s.s_b2, nkb, 0, b0, t);  // r*h of step t
@@ -282,12 +315,12 @@ rnn1_fwd_kernel(const __grid_constant__ CUtensorMap tm_hp, const __grid_constant
     const uint32_t drop_unit = skm_drop_unit(a.seed, (uint32_t)unit);
     const int u0w = unit - lane;  // first unit of this warp
     // per-thread views of (t, b0, unit) of the step's arrays: base pointer advanced per step, row n at n * row stride
-    const char *xw_p = reinterpret_cast<const char *>(a.xw + (size_t)b0 * G + unit);
+    const char *xw_p = reinterpret_cast<const char *>(a.xw + (size_t)b0 * G + unit);  // bf16
     char *out_p = reinterpret_cast<char *>(a.out_bf + (size_t)b0 * H + unit);
     char *act_p = reinterpret_cast<char *>(a.acts_bf + (size_t)b0 * G + unit);
-    const uint32_t xw_rs = (uint32_t)G * 4u, out_rs = (uint32_t)H * 2u, act_rs = (uint32_t)G * 2u;
-    const size_t xw_ts = (size_t)B * G * 4, out_ts = (size_t)B * H * 2, act_ts = (size_t)B * G * 2;
-    const uint32_t gH4 = (uint32_t)H * 4u, gH2 = (uint32_t)H * 2u;
+    const uint32_t xw_rs = (uint32_t)G * 2u, out_rs = (uint32_t)H * 2u, act_rs = (uint32_t)G * 2u;
+    const size_t xw_ts = (size_t)B * G * 2, out_ts = (size_t)B * H * 2, act_ts = (size_t)B * G * 2;
+    const uint32_t gH2 = (uint32_t)H * 2u;
     unsigned char eoc_raw = r1_eoc_raw(a.eoc, 0, T, B, b0, lane);
     const bool dbg = a.debug && blockIdx.x == 0 && tid == 0;
     uint32_t lapt = dbg ? (uint32_t)clock() : 0u;
@@ -300,24 +333,24 @@ rnn1_fwd_kernel(const __grid_constant__ CUtensorMap tm_hp, const __grid_constant
       for (int n = 0; n < N; ++n) {
         const bool ok = uvalid && (FULL || n < nvalid);
         const char *p = xw_p + (uint32_t)n * xw_rs;
-        x0[n] = ok ? __ldg(reinterpret_cast<const float *>(p)) : 0.f;
+        x0[n] = ok ? r1_ld_bf16(p) : 0.f;
         x1[n] = 0.f; x2[n] = 0.f;
         if constexpr (CELL == 1) {
-          x1[n] = ok ? __ldg(reinterpret_cast<const float *>(p + gH4)) : 0.f;
-          x2[n] = ok ? __ldg(reinterpret_cast<const float *>(p + 2 * gH4)) : 0.f;
+          x1[n] = ok ? r1_ld_bf16(p + gH2) : 0.f;
+          x2[n] = ok ? r1_ld_bf16(p + 2 * gH2) : 0.f;
         }
       }
       if (u0w < H) {
-        r1_prefetch(a.xw, 4, t + 2, T, B, b0, G, u0w, lane);
+        r1_prefetch(a.xw, 2, t + 2, T, B, b0, G, u0w, lane);
         if constexpr (CELL == 1) {
-          r1_prefetch(a.xw, 4, t + 2, T, B, b0, G, H + u0w, lane);
-          r1_prefetch(a.xw, 4, t + 2, T, B, b0, G, 2 * H + u0w, lane);
+          r1_prefetch(a.xw, 2, t + 2, T, B, b0, G, H + u0w, lane);
+          r1_prefetch(a.xw, 2, t + 2, T, B, b0, G, 2 * H + u0w, lane);
         }
       }
       const uint32_t eoc_m = __ballot_sync(0xffffffffu, eoc_raw != 0);
       eoc_raw = r1_eoc_raw(a.eoc, t + 1, T, B, b0, lane);
       float dsc[N];
-      r1_drop_scales(a, t, b0, unit, uvalid, drop_unit, dsc);
+      r1_drop_scales(a, t, b0, nvalid, unit, uvalid, drop_unit, dsc);
       float ug[N];
 #pragma unroll
       for (int n = 0; n < N; ++n) ug[n] = 0.f;
@@ -409,13 +442,14 @@ rnn1_fwd_kernel(const __grid_constant__ CUtensorMap tm_hp, const __grid_constant
 // ------------------------------------------------------------------------------------------------
 // backward (BPTT).  d(pre-activation) leaves as TMA stores of the operand tiles: no per-thread global stores.
 // ------------------------------------------------------------------------------------------------
-template <int CELL>
+template <int CELL, int MU, int NKB>
 __global__ void __launch_bounds__(R1_THREADS, 1) rnn1_bwd_kernel(const __grid_constant__ CUtensorMap tm_dp, R1Args a) {
   constexpr int N = R1_N;
   constexpr int NB1 = CELL == 2 ? 2 : 1;
   extern __shared__ uint8_t smem_raw[];
-  const int H = a.H, B = a.B, T = a.T, G = a.G, MU = a.MU, nkb = a.nkb;
-  const int btile = nkb * N * 128;
+  const int H = a.H, B = a.B, T = a.T, G = a.G;
+  constexpr int nkb = NKB;
+  constexpr int btile = NKB * N * 128;
   // b1: d(pre) of the candidate (gru) / of the cell (rnn, two buffers), K = H;  b2 (gru): d(pre) of the gates, K = 2H
   const R1Smem s = r1_smem(smem_raw, a.smem_w_bytes, NB1 * btile, CELL == 1 ? 2 * btile : 0);
   const uint32_t bar_op1 = s.s_bar, bar_acc1 = s.s_bar + 8, bar_op2 = s.s_bar + 16, bar_acc2 = s.s_bar + 24;
@@ -460,20 +494,30 @@ __global__ void __launch_bounds__(R1_THREADS, 1) rnn1_bwd_kernel(const __grid_co
     // ---------------- MMA issuer + TMA stores of d(pre) (same ordering argument as in the forward kernel) ----------------
     if (elect_one()) {
       const uint32_t idesc = make_idesc_bf16(128, N, false, false);
+      R1A A1[MU], A2[MU];
+#pragma unroll
+      for (int j = 0; j < MU; ++j) {
+        A1[j] = r1_resolve(a.tile[j], s.s_w, tmem_base);
+        A2[j] = r1_resolve(a.tile[CELL == 1 ? MU + j : j], s.s_w, tmem_base);
+      }
+      const uint64_t dB2 = make_desc(s.s_b2, 0, 1024);
       for (int t = T - 1, st = 0; t >= 0; --t, ++st) {
         if constexpr (CELL == 1) {
           // d(r*h) = d(pre_c) * Wc_h^T
           R1_WAIT(bar_op1, st & 1, 11);
           tc_fence_after();
-          for (int j = 0; j < MU; ++j) r1_issue_tile(tmem_base + (uint32_t)(j * N), a.tile[j], s.s_w, tmem_base, s.s_b1, idesc);
+          const uint64_t dB1 = make_desc(s.s_b1, 0, 1024);
+#pragma unroll
+          for (int j = 0; j < MU; ++j) r1_issue<NKB>(tmem_base + (uint32_t)(j * N), A1[j], dB1, idesc);
           tma_store_wait_read();
           tc_commit(bar_acc1);
           r1_store_tile(&tm_dp, s.s_b1, nkb, 2 * H, b0, t);
           R1_WAIT(bar_op2, st & 1, 12);
           tc_fence_after();
-          if (t > 0)  // d(h_{t-1}) += [d(pre_r), d(pre_u)] * Wg_h^T
-            for (int j = 0; j < MU; ++j)
-              r1_issue_tile(tmem_base + (uint32_t)((MU + j) * N), a.tile[MU + j], s.s_w, tmem_base, s.s_b2, idesc);
+          if (t > 0) {  // d(h_{t-1}) += [d(pre_r), d(pre_u)] * Wg_h^T
+#pragma unroll
+            for (int j = 0; j < MU; ++j) r1_issue<2 * NKB>(tmem_base + (uint32_t)((MU + j) * N), A2[j], dB2, idesc);
+          }
           tma_store_wait_read();
           if (t > 0) tc_commit(bar_acc2);
           r1_store_tile(&tm_dp, s.s_b2, 2 * nkb, 0, b0, t);
@@ -481,8 +525,11 @@ __global__ void __launch_bounds__(R1_THREADS, 1) rnn1_bwd_kernel(const __grid_co
           R1_WAIT(bar_op1, st & 1, 13);
           tc_fence_after();
           const uint32_t sb1 = s.s_b1 + (uint32_t)((st & 1) * btile);
-          if (t > 0)
-            for (int j = 0; j < MU; ++j) r1_issue_tile(tmem_base + (uint32_t)(j * N), a.tile[j], s.s_w, tmem_base, sb1, idesc);
+          const uint64_t dB1 = make_desc(sb1, 0, 1024);
+          if (t > 0) {
+#pragma unroll
+            for (int j = 0; j < MU; ++j) r1_issue<NKB>(tmem_base + (uint32_t)(j * N), A1[j], dB1, idesc);
+          }
           tma_store_wait_read();
           if (t > 0) tc_commit(bar_acc1);
           r1_store_tile(&tm_dp, sb1, nkb, 0, b0, t);
@@ -544,7 +591,7 @@ __global__ void __launch_bounds__(R1_THREADS, 1) rnn1_bwd_kernel(const __grid_co
       const uint32_t eoc_m = __ballot_sync(0xffffffffu, eoc_raw != 0);
       eoc_raw = r1_eoc_raw(a.eoc, t - 1, T, B, b0, lane);
       float dsc[N];
-      r1_drop_scales(a, t, b0, unit, uvalid, drop_unit, dsc);
+      r1_drop_scales(a, t, b0, nvalid, unit, uvalid, drop_unit, dsc);
       R1_LAP(0);
       if (st > 0) {  // d(h_t) from the step after: the product issued last iteration
         R1_WAIT(CELL == 1 ? bar_acc2 : bar_acc1, (st - 1) & 1, 14);
@@ -663,7 +710,9 @@ __global__ void r1_pack_kernel(R1PackArgs p, uint8_t *__restrict__ dst) {
   }
 }
 
-bool r1_eligible(const skrnn_handle *h) {
+}  // namespace
+
+bool sk_rnn1_tc_eligible(const skrnn_handle *h) {
   if (h->cfg.precision != SKRNN_PREC_BF16) return false;
   if (h->cfg.cell != SKRNN_CELL_GRU && h->cfg.cell != SKRNN_CELL_RNN) return false;
   if (h->H % 64 != 0 || h->H > 256) return false;
@@ -671,6 +720,8 @@ bool r1_eligible(const skrnn_handle *h) {
   if (env_off < 0) { const char *e = getenv("SKRNN_DISABLE_TC_RNN"); env_off = (e && e[0] == '1') ? 1 : 0; }
   return !env_off;
 }
+
+namespace {
 
 int r1_map(CUtensorMap *m, const void *ptr, int ld, int B, int T) {
   uint64_t dims[3] = {(uint64_t)ld, (uint64_t)B, (uint64_t)T};
@@ -684,11 +735,11 @@ int r1_map(CUtensorMap *m, const void *ptr, int ld, int B, int T) {
 // 0: the layer ran here; -1: not eligible (the caller uses the fp32 recurrent kernels); > 0: error
 int sk_rnn1_tc_layer(skrnn_handle *h, cudaStream_t st, bool bwd, int l, int B, int T, const float *state_in,
                      float *state_out, const float *mask, uint64_t seed, int row0, bool training) {
-  if (!r1_eligible(h)) return -1;
+  if (!sk_rnn1_tc_eligible(h)) return -1;
   const int H = h->H, G = h->G, cell = h->cfg.cell;
   const bool gru = cell == SKRNN_CELL_GRU;
   if (h->ws.acts_bf[l] == nullptr || h->ws.out_bf[l] == nullptr || h->ws.hprev_bf[l] == nullptr || h->ws.dpre_bf == nullptr ||
-      h->ws.xw[l] == nullptr || (gru && h->ws.aux_bf[l] == nullptr))
+      h->ws.xw_il[l] == nullptr || (gru && h->ws.aux_bf[l] == nullptr))
     return -1;
   const int MU = (H + 127) / 128, nkb = H / 64;
   const SkLayerParams &lp = h->lp[l];
@@ -767,7 +818,7 @@ int sk_rnn1_tc_layer(skrnn_handle *h, cudaStream_t st, bool bwd, int l, int B, i
   a.keep = h->cfg.keep_prob;
   a.seed = seed;
   a.eoc = h->ws.eoc; a.state_in = state_in; a.state_out = state_out; a.mask = mask;
-  a.xw = h->ws.xw[l];
+  a.xw = h->ws.xw_il[l];
   a.out_bf = h->ws.out_bf[l]; a.hprev_bf = h->ws.hprev_bf[l]; a.acts_bf = h->ws.acts_bf[l];
   a.dout = h->ws.dout;
   a.dbias0 = h->grads + lp.b[0];
@@ -780,23 +831,43 @@ int sk_rnn1_tc_layer(skrnn_handle *h, cudaStream_t st, bool bwd, int l, int B, i
   }
   const size_t smem = (size_t)soff + b_bytes + 1024 + 256;
   const int grid = (B + R1_N - 1) / R1_N;
+  // kernel instances by (m-tiles per gate, k-blocks): H = 64, 128, 192, 256
+#define R1_DISPATCH(LAUNCH)                                   \
+  do {                                                        \
+    if (MU == 1 && nkb == 1) { LAUNCH(1, 1); }                \
+    else if (MU == 1 && nkb == 2) { LAUNCH(1, 2); }           \
+    else if (MU == 2 && nkb == 3) { LAUNCH(2, 3); }           \
+    else { LAUNCH(2, 4); }                                    \
+  } while (0)
   if (!bwd) {
+    if (!h->xw_il_ok[l]) return -1;  // the projection was hoisted in the fp32 format
     CUtensorMap tm_hp, tm_aux;
     SK_TRY(r1_map(&tm_hp, h->ws.hprev_bf[l], H, B, T));
     SK_TRY(r1_map(&tm_aux, gru ? h->ws.aux_bf[l] : h->ws.hprev_bf[l], H, B, T));
     SkLaunch scope(h, st, SK_CAT_RNN_FWD);
-    auto kern = gru ? rnn1_fwd_kernel<1> : rnn1_fwd_kernel<2>;
-    SK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    kern<<<grid, R1_THREADS, smem, st>>>(tm_hp, tm_aux, a);
+#define R1_FWD(MUV, KBV)                                                                                          \
+  do {                                                                                                            \
+    auto kern = gru ? rnn1_fwd_kernel<1, MUV, KBV> : rnn1_fwd_kernel<2, MUV, KBV>;                                \
+    SK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));                  \
+    kern<<<grid, R1_THREADS, smem, st>>>(tm_hp, tm_aux, a);                                                       \
+  } while (0)
+    R1_DISPATCH(R1_FWD);
+#undef R1_FWD
   } else {
     CUtensorMap tm_dp;
     SK_TRY(r1_map(&tm_dp, h->ws.dpre_bf, G, B, T));
     SkLaunch scope(h, st, SK_CAT_RNN_BWD);
-    auto kern = gru ? rnn1_bwd_kernel<1> : rnn1_bwd_kernel<2>;
-    SK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    kern<<<grid, R1_THREADS, smem, st>>>(tm_dp, a);
+#define R1_BWD(MUV, KBV)                                                                                          \
+  do {                                                                                                            \
+    auto kern = gru ? rnn1_bwd_kernel<1, MUV, KBV> : rnn1_bwd_kernel<2, MUV, KBV>;                                \
+    SK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));                  \
+    kern<<<grid, R1_THREADS, smem, st>>>(tm_dp, a);                                                               \
+  } while (0)
+    R1_DISPATCH(R1_BWD);
+#undef R1_BWD
     h->bias_grad_done = true;
   }
+#undef R1_DISPATCH
   SK_CUDA(cudaGetLastError());
   return 0;
 }
