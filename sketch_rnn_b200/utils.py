@@ -116,13 +116,76 @@ class SketchLoader(object):
         self.scale_factor = scale_factor  # raw coordinates are divided by this
         data_file = os.path.join(self.data_dir, data_filename + ".cpkl")
         if not os.path.exists(data_file):
-            # the reference would build the file from raw SVGs here (utils.py:115-117); that preprocessing
-            # step is outside this repository's scope
-            raise IOError("%s not found: build it with the reference's preprocess step" % data_file)
+            raw_data_dir = os.path.join(self.data_dir, data_filename)
+            if not os.path.isdir(raw_data_dir):
+                raise IOError("%s not found, and no raw SVG directory %s to build it from" % (data_file, raw_data_dir))
+            print("creating training data cpkl file from raw source")
+            self.length_data = self.preprocess(raw_data_dir, data_file)
         self.load_preprocessed(data_file)
         self.num_samples = len(self.raw_data)
         self.index = list(range(self.num_samples))
         self.reset_index_pointer()
+
+    @staticmethod
+    def svg_to_strokes(svgfile, len_data=None, line_length_threshold=10.0, min_points_per_path=1, max_points_per_path=3):
+        """One SVG file -> float32 [N,4] = (dx, dy, eos, eoc), the reference's build_lines (utils.py:148-192):
+        every `d` attribute in document order; a line contributes its end point, a cubic Bezier
+        n = clamp(int(length / 10) + 1, 1, 3) points at t = 1/n .. 1 (the chord length decides n, utils.py:165-180);
+        a path's first point is a pen-up move; the last point of a path ends the stroke (eos); coordinates become
+        moves relative to the previous point, the last row ends the content (eoc), the first row is dropped.
+        Segments that are neither lines nor cubics are reported and skipped, as the reference does."""
+        import xml.etree.ElementTree as ET
+        from . import svgpath
+        rows = []
+        for elem in ET.parse(svgfile).iter():
+            if "d" not in elem.attrib:
+                continue
+            segs = svgpath.segments(elem.attrib["d"])
+            for i, seg in enumerate(segs):
+                if seg[0] not in ("L", "C"):
+                    print("encountered an element that is not just a line or bezier ")
+                    print("type: ", seg[0])
+                    print(seg)
+                    continue
+                p0, p3 = seg[1], seg[-1]
+                length = float(np.sqrt((p3.real - p0.real) ** 2 + (p3.imag - p0.imag) ** 2))
+                if len_data is not None:
+                    len_data.append(length)
+                if seg[0] == "C":
+                    n = min(max(int(length / line_length_threshold) + 1, min_points_per_path), max_points_per_path)
+                    p1, p2 = seg[2], seg[3]
+                    pts = []
+                    for k in range(n + 1):
+                        t = float(k) / float(n)
+                        z = (1. - t) ** 3 * p0 + 3. * t * (1. - t) ** 2 * p1 + 3.0 * t ** 2 * (1.0 - t) * p2 + t ** 3 * p3
+                        pts.append((z.real, z.imag))
+                else:
+                    pts = [(p0.real, p0.imag), (p3.real, p3.imag)]
+                if i == 0:
+                    rows.append([pts[0][0], pts[0][1], 0, 0])
+                for k in range(1, len(pts)):
+                    rows.append([pts[k][0], pts[k][1], 1 if (k == len(pts) - 1 and i == len(segs) - 1) else 0, 0])
+        lines = np.array(rows, dtype=np.float32)
+        lines[1:, 0:2] -= lines[0:-1, 0:2].copy()
+        lines[-1, 3] = 1
+        return lines[1:]
+
+    def preprocess(self, data_dir, data_file):
+        """data/<name>/**/*.svg -> data/<name>.cpkl (reference utils.py:124-217): a protocol-2 pickle of the list of
+        per-file stroke arrays.  Files are visited in sorted order (the reference takes os.walk's order, which the
+        file system decides; the order is reshuffled every epoch anyway).  Returns the segment lengths seen."""
+        len_data = []
+        files = []
+        for dirpath, dirnames, filenames in os.walk(data_dir):
+            dirnames.sort()
+            files += [os.path.join(dirpath, f) for f in sorted(filenames) if f[-3:] == "svg"]
+        sketch = []
+        for f in files:
+            print("processing " + f)
+            sketch.append(self.svg_to_strokes(f, len_data))
+        with open(data_file, "wb") as fh:
+            pickle.dump(sketch, fh, protocol=2)
+        return len_data
 
     def load_preprocessed(self, data_file):
         with open(data_file, "rb") as f:
