@@ -141,11 +141,7 @@ class Model(object):
         n = int(lengths.cpu().numpy()[0])
         strokes = strokes.cpu().numpy()[0, :n].copy()
         mixp = mixp.cpu().numpy()[0, :n]
-        M = self.num_mixture
-        params = [[mixp[i, 3:3 + M], mixp[i, 3 + M:3 + 2 * M], mixp[i, 3 + 2 * M:3 + 3 * M],
-                   mixp[i, 3 + 3 * M:3 + 4 * M], mixp[i, 3 + 4 * M:3 + 5 * M], mixp[i, 3 + 5 * M:3 + 6 * M],
-                   mixp[i, 0:3]] for i in range(n)]
-        return strokes, params
+        return strokes, self.mixture_params(mixp)
 
     def sample_batch(self, n_sketches, num=300, temp_mixture=1.0, temp_pen=1.0, stop_if_eoc=False, seed=0,
                      uniforms=None, sketch0=0):
@@ -153,6 +149,25 @@ class Model(object):
         strokes, lengths, _ = self.handle.sample(n_sketches, num, temp_mixture, temp_pen, stop_if_eoc,
                                                  uniforms=uniforms, seed=seed, sketch0=sketch0)
         return strokes.cpu().numpy(), lengths.cpu().numpy()
+
+    def mixture_params(self, mixp):
+        """[n, NOUT] rows as the kernel returns them -> the reference's per-point list
+        [pi_pdf, mu1, mu2, sigma1, sigma2, corr, pen_pdf] (model.py:251-252)."""
+        M = self.num_mixture
+        return [[mixp[i, 3:3 + M], mixp[i, 3 + M:3 + 2 * M], mixp[i, 3 + 2 * M:3 + 3 * M], mixp[i, 3 + 3 * M:3 + 4 * M],
+                 mixp[i, 3 + 4 * M:3 + 5 * M], mixp[i, 3 + 5 * M:3 + 6 * M], mixp[i, 0:3]] for i in range(len(mixp))]
+
+    def sample_candidates(self, n_sketches, num=300, temp_mixture=1.0, temp_pen=1.0, stop_if_eoc=False, uniforms=None):
+        """`n_sketches` independent Model.sample calls in ONE launch: returns (strokes [n, num, 5] with zero rows past
+        each length, lengths [n], mixp [n, num, NOUT]) as NumPy arrays.  Candidate k consumes the uniforms
+        np.random.rand(1, num, 4) that the k-th sequential `sample` call would have drawn (one rand(n, num, 4) call
+        yields the same numbers in the same order), so a loop over `sample` and one call here draw identical sketches."""
+        if uniforms is None:
+            uniforms = np.random.rand(n_sketches, num, 4).astype(np.float32)
+        uniforms = np.ascontiguousarray(uniforms, dtype=np.float32).reshape(n_sketches, num, 4)
+        strokes, lengths, mixp = self.handle.sample(n_sketches, num, temp_mixture, temp_pen, stop_if_eoc,
+                                                    uniforms=uniforms, want_params=True)
+        return strokes.cpu().numpy(), lengths.cpu().numpy(), mixp.cpu().numpy()
 
     # -- checkpoints: save/<dataset>/{checkpoint, model.ckpt-N} (train.py:72-75, sample.py:59-64) --------
     def variables(self):

@@ -101,3 +101,35 @@ def test_train_and_sample_scripts_end_to_end(tmp_path):
                        cwd=str(tmp_path), env=env, capture_output=True, text=True, timeout=300)
     assert r.returncode == 0, r.stderr[-2000:]
     assert "loading model: " in r.stdout
+
+
+def test_batched_rejection_sampling_accepts_what_the_one_by_one_loop_accepts(tmp_path):
+    """sample.py draws candidates 64 per launch and filters the batch; the reference (sample.py:81-100) draws and
+    tests one sketch at a time.  Under the same np.random state both keep the same sketches, bit for bit."""
+    import sample as sample_script
+    from sketch_rnn_b200.model import Model
+    model = Model(_args(rnn_size=64, num_mixture=6, batch_size=100, seq_length=300), True, seed=3)
+    p = model.handle.get_params_dict()
+    p["rnn_mdn/output_b"][0:3] += np.array([1.5, -0.5, 0.0], dtype=np.float32)   # pen lifts often, a few ends of content
+    model.handle.set_params_dict(p)
+    num, temp = 60, 0.8
+    # the reference's loop, one model.sample call per candidate, recording every candidate's statistics
+    np.random.seed(11)
+    singles = [model.sample(None, num, temp, temp, stop_if_eoc=True)[0] for _ in range(96)]
+    n_eos = sorted(int(s[:, 2].sum()) for s in singles)
+    lo, hi = n_eos[len(n_eos) // 3], n_eos[2 * len(n_eos) // 3] + 1      # rejects roughly a third on each side
+    ok = [sample_script.accept_sketch(s, 0.0, 1e9, lo, hi) for s in singles]
+    assert 0 < sum(ok) < len(ok), (lo, hi, n_eos)
+    want = [s for s, a in zip(singles, ok) if a][:5]
+    assert len(want) == 5
+    for per_launch in (1, 7, 64):
+        sargs = sample_script.build_parser().parse_args(
+            ["--num_picture", "5", "--sample_length", str(num), "--temperature", str(temp), "--filename",
+             str(tmp_path / ("out%d" % per_launch)), "--candidates_per_launch", str(per_launch), "--picture_size", "1e9"])
+        np.random.seed(11)
+        got, params = sample_script.sample_sketches(model, None, sargs, max_size_ratio=1.0, min_num_stroke=lo,
+                                                    max_num_stroke=hi)
+        assert len(got) == 5 and len(params) == 5 and len(params[0]) == got[0].shape[0]
+        for g, w in zip(got, want):
+            assert g.shape == w.shape and np.array_equal(g.view(np.uint32), w.view(np.uint32)), per_launch
+        assert os.path.exists(str(tmp_path / ("out%d.svg" % per_launch)))
