@@ -161,71 +161,6 @@ __device__ __forceinline__ float r1_ld_bf16(const char *p) {
   return __uint_as_float((uint32_t)(*reinterpret_cast<const unsigned short *>(p)) << 16);
 }
 
-// ---- 8-lane transposes between "my unit x 16 rows" (what the gate math works on: lane = unit) and "rows 2j, 2j+1 x
-// the 8 units of my lane group" (j = lane & 7), which is 16 contiguous bytes per row in every [.., units] array and in
-// the swizzled operand tile.  They turn sixteen 2-byte accesses per thread into two 16-byte ones: shared-memory
-// stores drain 8x faster in front of the fence, and the load/store unit sees an eighth of the instructions.
-__device__ __forceinline__ void r1_xpose8(uint32_t (&p)[8], int j) {
-#pragma unroll
-  for (int m = 1; m < 8; m <<= 1) {
-    const bool up = (j & m) != 0;
-#pragma unroll
-    for (int i = 0; i < 8; ++i) {
-      if ((i & m) == 0) {
-        const uint32_t send = up ? p[i] : p[i | m];
-        const uint32_t recv = __shfl_xor_sync(0xffffffffu, send, m);
-        if (up) p[i] = recv; else p[i | m] = recv;
-      }
-    }
-  }
-}
-// v[n] = value of (row n, my unit)  ->  q0 / q1 = bf16 rows 2j / 2j+1 of my group's 8 units
-__device__ __forceinline__ void r1_pack_rows(const float (&v)[R1_N], int j, uint4 &q0, uint4 &q1) {
-  uint32_t p[8];
-#pragma unroll
-  for (int i = 0; i < 8; ++i) {
-    const __nv_bfloat162 b = __floats2bfloat162_rn(v[2 * i], v[2 * i + 1]);
-    p[i] = *reinterpret_cast<const uint32_t *>(&b);
-  }
-  r1_xpose8(p, j);  // p[i] = (row 2j, row 2j+1) of unit i of the group
-  q0 = make_uint4(__byte_perm(p[0], p[1], 0x5410), __byte_perm(p[2], p[3], 0x5410), __byte_perm(p[4], p[5], 0x5410),
-                  __byte_perm(p[6], p[7], 0x5410));
-  q1 = make_uint4(__byte_perm(p[0], p[1], 0x7632), __byte_perm(p[2], p[3], 0x7632), __byte_perm(p[4], p[5], 0x7632),
-                  __byte_perm(p[6], p[7], 0x7632));
-}
-// the inverse: q0 / q1 = bf16 rows 2j / 2j+1 of my group's 8 units  ->  v[n] = value of (row n, my unit)
-__device__ __forceinline__ void r1_unpack_rows(const uint4 &q0, const uint4 &q1, int j, float (&v)[R1_N]) {
-  uint32_t p[8];
-  p[0] = __byte_perm(q0.x, q1.x, 0x5410); p[1] = __byte_perm(q0.x, q1.x, 0x7632);
-  p[2] = __byte_perm(q0.y, q1.y, 0x5410); p[3] = __byte_perm(q0.y, q1.y, 0x7632);
-  p[4] = __byte_perm(q0.z, q1.z, 0x5410); p[5] = __byte_perm(q0.z, q1.z, 0x7632);
-  p[6] = __byte_perm(q0.w, q1.w, 0x5410); p[7] = __byte_perm(q0.w, q1.w, 0x7632);
-  r1_xpose8(p, j);  // p[i] = (row 2i, row 2i+1) of my unit
-#pragma unroll
-  for (int i = 0; i < 8; ++i) {
-    v[2 * i] = __uint_as_float(p[i] << 16);
-    v[2 * i + 1] = __uint_as_float(p[i] & 0xffff0000u);
-  }
-}
-// A thread's two 16-byte slots (rows 2j and 2j+1, its group's 8 units starting at column `col`) in a [T,B,ld] bf16
-// array, as byte offsets from the array's (t, b0, 0) element, and in an operand tile
-struct R1Slots {
-  uint32_t g0, g1;  // global: row offsets
-  uint32_t s0, s1;  // operand tile (shared memory)
-};
-__device__ __forceinline__ R1Slots r1_slots(int j, int col, int ld, int kcol) {
-  R1Slots r;
-  r.g0 = (uint32_t)(((2 * j) * ld + col) * 2);
-  r.g1 = r.g0 + (uint32_t)(ld * 2);
-  const uint32_t kb = (uint32_t)(kcol >> 6) * (R1_N * 128), c = (uint32_t)((kcol & 63) >> 3);
-  r.s0 = kb + (uint32_t)(2 * j) * 128u + ((c ^ (uint32_t)((2 * j) & 7)) << 4);
-  r.s1 = kb + (uint32_t)(2 * j + 1) * 128u + ((c ^ (uint32_t)((2 * j + 1) & 7)) << 4);
-  return r;
-}
-__device__ __forceinline__ uint4 r1_ldg16(const char *p, bool ok) {
-  return ok ? __ldg(reinterpret_cast<const uint4 *>(p)) : make_uint4(0, 0, 0, 0);
-}
-
 // L2 prefetch of the 128-byte line holding (row b0 + lane, column col) of a [T,B,ld] array at step t: one instruction
 // per warp brings in what the warp's 32 units will load for the tile's rows two steps later
 __device__ __forceinline__ void r1_prefetch(const void *base, size_t elem_bytes, int t, int T, int B, int b0, int ld, int col,
@@ -378,28 +313,32 @@ rnn1_fwd_kernel(const __grid_constant__ CUtensorMap tm_hp, const __grid_constant
     // ---------------- elementwise warps ----------------
     const uint32_t lane_addr = tmem_base + ((uint32_t)(32 * q) << 16);
     const uint32_t drop_unit = skm_drop_unit(a.seed, (uint32_t)unit);
-    const int u0w = unit - lane;          // first unit of this warp
-    const int j8 = lane & 7;              // my rows in the 16-byte view: 2*j8, 2*j8 + 1
-    const int ug = u0w + (lane & 24);     // first unit of my 8-lane group
-    const bool ok0 = uvalid && 2 * j8 < nvalid, ok1 = uvalid && 2 * j8 + 1 < nvalid;
-    const R1Slots sx = r1_slots(j8, ug, G, ug), so = r1_slots(j8, ug, H, ug);
-    // (t, b0, 0) of the step's arrays, advanced per step
-    const char *xw_p = reinterpret_cast<const char *>(a.xw + (size_t)b0 * G);
-    char *out_p = reinterpret_cast<char *>(a.out_bf + (size_t)b0 * H);
-    char *act_p = reinterpret_cast<char *>(a.acts_bf + (size_t)b0 * G);
-    const size_t xw_ts = (size_t)B * G * 2, out_ts = (size_t)B * H * 2;
+    const int u0w = unit - lane;  // first unit of this warp
+    // per-thread views of (t, b0, unit) of the step's arrays: base pointer advanced per step, row n at n * row stride
+    const char *xw_p = reinterpret_cast<const char *>(a.xw + (size_t)b0 * G + unit);  // bf16
+    char *out_p = reinterpret_cast<char *>(a.out_bf + (size_t)b0 * H + unit);
+    char *act_p = reinterpret_cast<char *>(a.acts_bf + (size_t)b0 * G + unit);
+    const uint32_t xw_rs = (uint32_t)G * 2u, out_rs = (uint32_t)H * 2u, act_rs = (uint32_t)G * 2u;
+    const size_t xw_ts = (size_t)B * G * 2, out_ts = (size_t)B * H * 2, act_ts = (size_t)B * G * 2;
     const uint32_t gH2 = (uint32_t)H * 2u;
     unsigned char eoc_raw = r1_eoc_raw(a.eoc, 0, T, B, b0, lane);
     const bool dbg = a.debug && blockIdx.x == 0 && tid == 0;
     uint32_t lapt = dbg ? (uint32_t)clock() : 0u;
 
-    for (int t = 0; t < T; ++t) {
+    auto body = [&](auto full_tag, int t) {
+      constexpr bool FULL = decltype(full_tag)::value;
       // everything that does not depend on the recurrence is requested before waiting for the product
-      uint4 xa0 = r1_ldg16(xw_p + sx.g0, ok0), xb0 = r1_ldg16(xw_p + sx.g1, ok1);
-      uint4 xa1 = make_uint4(0, 0, 0, 0), xb1 = xa1, xa2 = xa1, xb2 = xa1;
-      if constexpr (CELL == 1) {
-        xa1 = r1_ldg16(xw_p + sx.g0 + gH2, ok0); xb1 = r1_ldg16(xw_p + sx.g1 + gH2, ok1);
-        xa2 = r1_ldg16(xw_p + sx.g0 + 2 * gH2, ok0); xb2 = r1_ldg16(xw_p + sx.g1 + 2 * gH2, ok1);
+      float x0[N], x1[N], x2[N];
+#pragma unroll
+      for (int n = 0; n < N; ++n) {
+        const bool ok = uvalid && (FULL || n < nvalid);
+        const char *p = xw_p + (uint32_t)n * xw_rs;
+        x0[n] = ok ? r1_ld_bf16(p) : 0.f;
+        x1[n] = 0.f; x2[n] = 0.f;
+        if constexpr (CELL == 1) {
+          x1[n] = ok ? r1_ld_bf16(p + gH2) : 0.f;
+          x2[n] = ok ? r1_ld_bf16(p + 2 * gH2) : 0.f;
+        }
       }
       if (u0w < H) {
         r1_prefetch(a.xw, 2, t + 2, T, B, b0, G, u0w, lane);
@@ -412,14 +351,11 @@ rnn1_fwd_kernel(const __grid_constant__ CUtensorMap tm_hp, const __grid_constant
       eoc_raw = r1_eoc_raw(a.eoc, t + 1, T, B, b0, lane);
       float dsc[N];
       r1_drop_scales(a, t, b0, nvalid, unit, uvalid, drop_unit, dsc);
-      float ug_[N];
+      float ug[N];
 #pragma unroll
-      for (int n = 0; n < N; ++n) ug_[n] = 0.f;
+      for (int n = 0; n < N; ++n) ug[n] = 0.f;
       R1_LAP(0);
       if constexpr (CELL == 1) {
-        float x0[N], x1[N];
-        r1_unpack_rows(xa0, xb0, j8, x0);
-        r1_unpack_rows(xa1, xb1, j8, x1);
         R1_WAIT(bar_acc1, t & 1, 3);
         R1_LAP(1);
         tc_fence_after();
@@ -427,32 +363,28 @@ rnn1_fwd_kernel(const __grid_constant__ CUtensorMap tm_hp, const __grid_constant
         tc_ldn<N>(lane_addr + (uint32_t)(mt * N), rr);
         tc_ldn<N>(lane_addr + (uint32_t)((MU + mt) * N), ru);
         tc_fence_before();
-        float rg[N], rh[N];
+        float rg[N];
 #pragma unroll
         for (int n = 0; n < N; ++n) {
           rg[n] = sigmoid_approx(__uint_as_float(rr[n]) + x0[n]);
-          ug_[n] = sigmoid_approx(__uint_as_float(ru[n]) + x1[n]);
-          rh[n] = rg[n] * hcur[n];
-        }
-        uint4 q0, q1;
-        r1_pack_rows(rh, j8, q0, q1);
-        if (uvalid) {
-          *reinterpret_cast<uint4 *>(b2_gen + so.s0) = q0;
-          *reinterpret_cast<uint4 *>(b2_gen + so.s1) = q1;
+          ug[n] = sigmoid_approx(__uint_as_float(ru[n]) + x1[n]);
+          if (uvalid) r1_sts_bf16(b2_gen + R1_BOFF(bcol, bch, n), rg[n] * hcur[n]);
         }
         fence_proxy_async_smem();
         mbar_arrive(bar_op2);
         R1_LAP(2);
-        r1_pack_rows(rg, j8, q0, q1);
-        if (ok0) *reinterpret_cast<uint4 *>(act_p + sx.g0) = q0;
-        if (ok1) *reinterpret_cast<uint4 *>(act_p + sx.g1) = q1;
-        r1_pack_rows(ug_, j8, q0, q1);
-        if (ok0) *reinterpret_cast<uint4 *>(act_p + sx.g0 + gH2) = q0;
-        if (ok1) *reinterpret_cast<uint4 *>(act_p + sx.g1 + gH2) = q1;
+        if (uvalid) {
+#pragma unroll
+          for (int n = 0; n < N; ++n) {
+            if (FULL || n < nvalid) {
+              char *p = act_p + (uint32_t)n * act_rs;
+              *reinterpret_cast<__nv_bfloat16 *>(p) = __float2bfloat16_rn(rg[n]);
+              *reinterpret_cast<__nv_bfloat16 *>(p + gH2) = __float2bfloat16_rn(ug[n]);
+            }
+          }
+        }
         R1_LAP(3);
       }
-      float xc[N];
-      if constexpr (CELL == 1) r1_unpack_rows(xa2, xb2, j8, xc); else r1_unpack_rows(xa0, xb0, j8, xc);
       R1_WAIT(CELL == 1 ? bar_acc2 : bar_acc1, t & 1, 4);
       R1_LAP(4);
       tc_fence_after();
@@ -460,43 +392,37 @@ rnn1_fwd_kernel(const __grid_constant__ CUtensorMap tm_hp, const __grid_constant
       tc_ldn<N>(lane_addr + (uint32_t)((CELL == 1 ? 2 * MU + mt : mt) * N), rc);
       tc_fence_before();
       float h2[N];
+      uint8_t *b1w = b1_gen + (NB1 == 2 ? ((t + 1) & 1) * btile : 0);
 #pragma unroll
       for (int n = 0; n < N; ++n) {
-        const float cand = tanh_approx(__uint_as_float(rc[n]) + xc[n]);
-        xc[n] = cand;
-        h2[n] = CELL == 1 ? fmaf(ug_[n], hcur[n] - cand, cand) : cand;   // u*h + (1-u)*c
+        const float cand = tanh_approx(__uint_as_float(rc[n]) + (CELL == 1 ? x2[n] : x0[n]));
+        h2[n] = CELL == 1 ? fmaf(ug[n], hcur[n] - cand, cand) : cand;   // u*h + (1-u)*c
         float hn = h2[n];
         if ((eoc_m >> n) & 1u)  // eoc: back to the FED state (model.py:82-92); warp-uniform and rare
-          hn = (uvalid && n < nvalid) ? __ldg(a.state_in + (size_t)(b0 + n) * H + unit) : 0.f;
+          hn = uvalid ? __ldg(a.state_in + (size_t)(b0 + n) * H + unit) : 0.f;
         hcur[n] = hn;
-      }
-      {
-        uint4 q0, q1;
-        r1_pack_rows(hcur, j8, q0, q1);
-        uint8_t *b1w = b1_gen + (NB1 == 2 ? ((t + 1) & 1) * btile : 0);
-        if (uvalid) {
-          *reinterpret_cast<uint4 *>(b1w + so.s0) = q0;
-          *reinterpret_cast<uint4 *>(b1w + so.s1) = q1;
-        }
+        if (uvalid) r1_sts_bf16(b1w + R1_BOFF(bcol, bch, n), hn);
+        if constexpr (CELL == 1) x2[n] = cand;
       }
       fence_proxy_async_smem();
       mbar_arrive(bar_op1);
       R1_LAP(5);
-      // off the dependent chain: the activation BPTT needs, and the layer output (pre reset, dropout applied)
-      {
-        uint4 q0, q1;
-        r1_pack_rows(CELL == 1 ? xc : h2, j8, q0, q1);
-        const uint32_t co = CELL == 1 ? 2 * gH2 : 0u;
-        if (ok0) *reinterpret_cast<uint4 *>(act_p + sx.g0 + co) = q0;
-        if (ok1) *reinterpret_cast<uint4 *>(act_p + sx.g1 + co) = q1;
+      // off the dependent chain: layer output (pre reset, dropout applied) and the activation BPTT needs
+      if (uvalid) {
 #pragma unroll
-        for (int n = 0; n < N; ++n) h2[n] *= dsc[n];
-        r1_pack_rows(h2, j8, q0, q1);
-        if (ok0) *reinterpret_cast<uint4 *>(out_p + so.g0) = q0;
-        if (ok1) *reinterpret_cast<uint4 *>(out_p + so.g1) = q1;
+        for (int n = 0; n < N; ++n) {
+          if (FULL || n < nvalid) {
+            *reinterpret_cast<__nv_bfloat16 *>(out_p + (uint32_t)n * out_rs) = __float2bfloat16_rn(h2[n] * dsc[n]);
+            *reinterpret_cast<__nv_bfloat16 *>(act_p + (uint32_t)n * act_rs + (CELL == 1 ? 2 * gH2 : 0u)) =
+                __float2bfloat16_rn(CELL == 1 ? x2[n] : h2[n]);
+          }
+        }
       }
-      xw_p += xw_ts; out_p += out_ts; act_p += xw_ts;
+      xw_p += xw_ts; out_p += out_ts; act_p += act_ts;
       R1_LAP(6);
+    };
+    for (int t = 0; t < T; ++t) {
+      if (nvalid == N) body(std::true_type{}, t); else body(std::false_type{}, t);
     }
     if (uvalid) {
 #pragma unroll
@@ -616,18 +542,16 @@ __global__ void __launch_bounds__(R1_THREADS, 1) rnn1_bwd_kernel(const __grid_co
     // ---------------- elementwise warps ----------------
     const uint32_t lane_addr = tmem_base + ((uint32_t)(32 * q) << 16);
     const uint32_t drop_unit = skm_drop_unit(a.seed, (uint32_t)unit);
+    const uint32_t bcol = r1_bcol(unit), bch = r1_bchunk(unit);
+    const uint32_t bcol_u = r1_bcol(H + unit), bch_u = r1_bchunk(H + unit);
     uint8_t *b1_gen = s.gen + (s.s_b1 - s.base);
     uint8_t *b2_gen = s.gen + (s.s_b2 - s.base);
     const int u0w = unit - lane;
-    const int j8 = lane & 7;
-    const int ug = u0w + (lane & 24);
-    const bool ok0 = uvalid && 2 * j8 < nvalid, ok1 = uvalid && 2 * j8 + 1 < nvalid;
-    const R1Slots sa = r1_slots(j8, ug, G, ug), sh = r1_slots(j8, ug, H, ug), su = r1_slots(j8, ug, H, H + ug);
-    // (t, b0, 0) of the step's arrays, walking backwards in t; d(out) is fp32 and read per (row, unit)
-    const char *act_p = reinterpret_cast<const char *>(a.acts_bf + ((size_t)(T - 1) * B + b0) * G);
-    const char *hp_p = reinterpret_cast<const char *>(a.hprev_bf + ((size_t)(T - 1) * B + b0) * H);
+    // per-thread views of (t, b0, unit), walking backwards in t
+    const char *act_p = reinterpret_cast<const char *>(a.acts_bf + ((size_t)(T - 1) * B + b0) * G + unit);
+    const char *hp_p = reinterpret_cast<const char *>(a.hprev_bf + ((size_t)(T - 1) * B + b0) * H + unit);
     const char *do_p = reinterpret_cast<const char *>(a.dout + ((size_t)(T - 1) * B + b0) * H + unit);
-    const uint32_t do_rs = (uint32_t)H * 4u;
+    const uint32_t act_rs = (uint32_t)G * 2u, hp_rs = (uint32_t)H * 2u, do_rs = (uint32_t)H * 4u;
     const size_t act_ts = (size_t)B * G * 2, hp_ts = (size_t)B * H * 2, do_ts = (size_t)B * H * 4;
     const uint32_t gH2 = (uint32_t)H * 2u;
     unsigned char eoc_raw = r1_eoc_raw(a.eoc, T - 1, T, B, b0, lane);
@@ -638,19 +562,23 @@ __global__ void __launch_bounds__(R1_THREADS, 1) rnn1_bwd_kernel(const __grid_co
     const bool dbg = a.debug && blockIdx.x == 0 && tid == 0;
     uint32_t lapt = dbg ? (uint32_t)clock() : 0u;
 
-    for (int t = T - 1, st = 0; t >= 0; --t, ++st) {
+    auto body = [&](auto full_tag, int t, int st) {
+      constexpr bool FULL = decltype(full_tag)::value;
       // saved activations and d(out) of the step: requested before waiting for the previous step's product
-      const uint4 qa0 = r1_ldg16(act_p + sa.g0, ok0), qb0 = r1_ldg16(act_p + sa.g1, ok1);
-      uint4 qa1 = make_uint4(0, 0, 0, 0), qb1 = qa1, qa2 = qa1, qb2 = qa1, qah = qa1, qbh = qa1;
-      if constexpr (CELL == 1) {
-        qa1 = r1_ldg16(act_p + sa.g0 + gH2, ok0); qb1 = r1_ldg16(act_p + sa.g1 + gH2, ok1);
-        qa2 = r1_ldg16(act_p + sa.g0 + 2 * gH2, ok0); qb2 = r1_ldg16(act_p + sa.g1 + 2 * gH2, ok1);
-        qah = r1_ldg16(hp_p + sh.g0, ok0); qbh = r1_ldg16(hp_p + sh.g1, ok1);
-      }
-      float d_o[N];
+      float a0[N], a1[N], a2[N], hv[N], d_o[N];
 #pragma unroll
-      for (int n = 0; n < N; ++n)
-        d_o[n] = (uvalid && n < nvalid) ? __ldg(reinterpret_cast<const float *>(do_p + (uint32_t)n * do_rs)) : 0.f;
+      for (int n = 0; n < N; ++n) {
+        const bool ok = uvalid && (FULL || n < nvalid);
+        const char *pa = act_p + (uint32_t)n * act_rs;
+        a0[n] = ok ? r1_ld_bf16(pa) : 0.f;
+        d_o[n] = ok ? __ldg(reinterpret_cast<const float *>(do_p + (uint32_t)n * do_rs)) : 0.f;
+        a1[n] = 0.f; a2[n] = 0.f; hv[n] = 0.f;
+        if constexpr (CELL == 1) {
+          a1[n] = ok ? r1_ld_bf16(pa + gH2) : 0.f;
+          a2[n] = ok ? r1_ld_bf16(pa + 2 * gH2) : 0.f;
+          hv[n] = ok ? r1_ld_bf16(hp_p + (uint32_t)n * hp_rs) : 0.f;
+        }
+      }
       if (u0w < H) {
         r1_prefetch(a.dout, 4, t - 2, T, B, b0, H, u0w, lane);
         r1_prefetch(a.acts_bf, 2, t - 2, T, B, b0, G, u0w, lane);
@@ -664,8 +592,6 @@ __global__ void __launch_bounds__(R1_THREADS, 1) rnn1_bwd_kernel(const __grid_co
       eoc_raw = r1_eoc_raw(a.eoc, t - 1, T, B, b0, lane);
       float dsc[N];
       r1_drop_scales(a, t, b0, nvalid, unit, uvalid, drop_unit, dsc);
-      float a0[N];
-      r1_unpack_rows(qa0, qb0, j8, a0);
       R1_LAP(0);
       if (st > 0) {  // d(h_t) from the step after: the product issued last iteration
         R1_WAIT(CELL == 1 ? bar_acc2 : bar_acc1, (st - 1) & 1, 14);
@@ -678,45 +604,28 @@ __global__ void __launch_bounds__(R1_THREADS, 1) rnn1_bwd_kernel(const __grid_co
       }
       R1_LAP(1);
       if constexpr (CELL == 2) {
-        float dp[N];
+        uint8_t *b1w = b1_gen + (st & 1) * btile;
 #pragma unroll
         for (int n = 0; n < N; ++n) {
           const float dh2 = d_o[n] * dsc[n] + (((eoc_m >> n) & 1u) ? 0.f : dhc[n]);
-          dp[n] = dh2 * (1.0f - a0[n] * a0[n]);
-          bs0 += dp[n];
-        }
-        uint4 q0, q1;
-        r1_pack_rows(dp, j8, q0, q1);
-        uint8_t *b1w = b1_gen + (st & 1) * btile;
-        if (uvalid) {
-          *reinterpret_cast<uint4 *>(b1w + sh.s0) = q0;
-          *reinterpret_cast<uint4 *>(b1w + sh.s1) = q1;
+          const float dp = dh2 * (1.0f - a0[n] * a0[n]);
+          bs0 += dp;
+          if (uvalid) r1_sts_bf16(b1w + R1_BOFF(bcol, bch, n), dp);
         }
         fence_proxy_async_smem();
         mbar_arrive(bar_op1);
         R1_LAP(2);
       } else {
         // a0 = r, a1 = u, a2 = candidate, hv = h fed to the step
-        float a1[N], a2[N], hv[N], du[N];
-        r1_unpack_rows(qa1, qb1, j8, a1);
-        r1_unpack_rows(qa2, qb2, j8, a2);
-        r1_unpack_rows(qah, qbh, j8, hv);
-        {
-          float dpc[N];
+        float du[N];
 #pragma unroll
-          for (int n = 0; n < N; ++n) {
-            const float dh2 = d_o[n] * dsc[n] + (((eoc_m >> n) & 1u) ? 0.f : dhc[n]);
-            du[n] = dh2 * (hv[n] - a2[n]);
-            dpc[n] = dh2 * (1.0f - a1[n]) * (1.0f - a2[n] * a2[n]);
-            dhc[n] = dh2 * a1[n];  // direct path h -> h'; the two products add to it below / next iteration
-            bs2 += dpc[n];
-          }
-          uint4 q0, q1;
-          r1_pack_rows(dpc, j8, q0, q1);
-          if (uvalid) {
-            *reinterpret_cast<uint4 *>(b1_gen + sh.s0) = q0;
-            *reinterpret_cast<uint4 *>(b1_gen + sh.s1) = q1;
-          }
+        for (int n = 0; n < N; ++n) {
+          const float dh2 = d_o[n] * dsc[n] + (((eoc_m >> n) & 1u) ? 0.f : dhc[n]);
+          du[n] = dh2 * (hv[n] - a2[n]);
+          const float dpc = dh2 * (1.0f - a1[n]) * (1.0f - a2[n] * a2[n]);
+          dhc[n] = dh2 * a1[n];  // direct path h -> h'; the two products add to it below / next iteration
+          bs2 += dpc;
+          if (uvalid) r1_sts_bf16(b1_gen + R1_BOFF(bcol, bch, n), dpc);
         }
         fence_proxy_async_smem();
         mbar_arrive(bar_op1);
@@ -727,32 +636,27 @@ __global__ void __launch_bounds__(R1_THREADS, 1) rnn1_bwd_kernel(const __grid_co
         uint32_t r[N];
         tc_ldn<N>(lane_addr + (uint32_t)(mt * N), r);
         tc_fence_before();
-        float dpr[N];
 #pragma unroll
         for (int n = 0; n < N; ++n) {
           const float drh = __uint_as_float(r[n]);
           dhc[n] = fmaf(drh, a0[n], dhc[n]);
-          dpr[n] = drh * hv[n] * a0[n] * (1.0f - a0[n]);
-          du[n] = du[n] * a1[n] * (1.0f - a1[n]);  // d(pre_u)
-          bs0 += dpr[n];
-          bs1 += du[n];
-        }
-        uint4 q0, q1;
-        r1_pack_rows(dpr, j8, q0, q1);
-        if (uvalid) {
-          *reinterpret_cast<uint4 *>(b2_gen + sh.s0) = q0;
-          *reinterpret_cast<uint4 *>(b2_gen + sh.s1) = q1;
-        }
-        r1_pack_rows(du, j8, q0, q1);
-        if (uvalid) {
-          *reinterpret_cast<uint4 *>(b2_gen + su.s0) = q0;
-          *reinterpret_cast<uint4 *>(b2_gen + su.s1) = q1;
+          const float dpr = drh * hv[n] * a0[n] * (1.0f - a0[n]);
+          const float dpu = du[n] * a1[n] * (1.0f - a1[n]);
+          bs0 += dpr;
+          bs1 += dpu;
+          if (uvalid) {
+            r1_sts_bf16(b2_gen + R1_BOFF(bcol, bch, n), dpr);
+            r1_sts_bf16(b2_gen + R1_BOFF(bcol_u, bch_u, n), dpu);
+          }
         }
         fence_proxy_async_smem();
         mbar_arrive(bar_op2);
         R1_LAP(5);
       }
       act_p -= act_ts; hp_p -= hp_ts; do_p -= do_ts;
+    };
+    for (int t = T - 1, st = 0; t >= 0; --t, ++st) {
+      if (nvalid == N) body(std::true_type{}, t, st); else body(std::false_type{}, t, st);
     }
     if (uvalid) {
       if constexpr (CELL == 2) {

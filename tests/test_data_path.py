@@ -111,3 +111,27 @@ def test_calculate_start_point_and_svg(tmp_path):
     assert text.count(" L ") == 4  # the point after a pen lift is a bare move
     text2 = utils.draw_stroke_color(np.concatenate([d, d]), svg_filename=None)
     assert text2.count("<path") == 6
+
+
+def test_prefetching_loader_yields_the_same_batches(tmp_path):
+    """The background-thread loader hands out exactly what SketchLoader.next_batch would, epoch ends included."""
+    from sketch_rnn_b200 import utils
+    path = utils.make_synthetic_dataset(str(tmp_path / "data" / "toy.cpkl"), num_sketches=23, seed=4)
+    runs = []
+    for wrap in (False, True):
+        np.random.seed(7)
+        ld = utils.SketchLoader(4, 30, 15.0, "toy", data_dir=str(tmp_path / "data"))
+        if wrap:
+            ld = utils.PrefetchingLoader(ld)
+        seen = []
+        for epoch in range(3):
+            ld.reset_index_pointer()
+            while not ld.epoch_finished:
+                x, y = ld.next_batch()
+                seen.append((x.copy(), y.copy(), ld.pointer, ld.epoch_finished))
+        runs.append(seen)
+        if wrap:
+            ld.close()
+    assert len(runs[0]) == len(runs[1]) > 3
+    for a, b in zip(*runs):
+        assert np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1]) and a[2:] == b[2:]

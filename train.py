@@ -6,7 +6,7 @@ import os
 import time
 
 from sketch_rnn_b200.model import Model, Saver, Session, save_config
-from sketch_rnn_b200.utils import SketchLoader
+from sketch_rnn_b200.utils import PrefetchingLoader, SketchLoader
 
 
 def main():
@@ -31,12 +31,17 @@ def main():
     parser.add_argument('--precision', type=str, default="bf16", choices=["bf16", "f32"],
                         help='bf16 tensor-core path or fp32 reference-precision path')
     parser.add_argument('--max_batches', type=int, default=0, help='stop after this many batches (0 = run all epochs)')
+    parser.add_argument('--no_prefetch', action='store_true',
+                        help='build every batch inside the timed region, like the reference (default: one batch ahead '
+                             'on a background thread, into page-locked buffers; same batches either way)')
     args = parser.parse_args()
     train(args)
 
 
 def train(args):
     data_loader = SketchLoader(args.batch_size, args.seq_length, args.data_scale, args.dataset_name)
+    if not args.no_prefetch:
+        data_loader = PrefetchingLoader(data_loader)
 
     dirname = os.path.join('save', args.dataset_name)
     if not os.path.exists(dirname):
