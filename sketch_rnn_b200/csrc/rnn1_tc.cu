@@ -22,6 +22,7 @@
 // GRU (TF 0.x semantics): two dependent products per step -- gates r,u on h, then the candidate on r*h.
 // BPTT mirrors it: d(r*h) = d(pre_c) * Wc_h^T, then d(h) += [d(pre_r), d(pre_u)] * Wg_h^T.
 #include <stdlib.h>
+#include <string.h>
 #include <type_traits>
 
 #include "common.cuh"
@@ -31,7 +32,8 @@
 namespace {
 
 constexpr int R1_N = 16;          // batch rows per CTA (MMA N)
-constexpr int R1_EPI_WARPS = 8;
+constexpr int R1_NR = 8;          // of which one elementwise thread handles 8 (for its unit): two warps per (m-tile, lane quarter)
+constexpr int R1_EPI_WARPS = 16;
 constexpr int R1_THREADS = 32 * (R1_EPI_WARPS + 1);
 constexpr int R1_MAX_TILES = 6;
 
@@ -60,6 +62,7 @@ struct R1Args {
   float *dbias0, *dbias1;
   const uint8_t *wimg;
   int debug;                 // SKRNN_TC_DEBUG=1: CTA 0 prints its per-phase cycle split
+  int pf_dist, pf_l1;        // prefetch distance in steps, and whether it targets L1 (else L2)
 };
 
 #define R1_WAIT(bar, par, tag) mbar_wait_wd(bar, par, tag, 1u << 22)
@@ -164,10 +167,11 @@ __device__ __forceinline__ float r1_ld_bf16(const char *p) {
 // L2 prefetch of the 128-byte line holding (row b0 + lane, column col) of a [T,B,ld] array at step t: one instruction
 // per warp brings in what the warp's 32 units will load for the tile's rows two steps later
 __device__ __forceinline__ void r1_prefetch(const void *base, size_t elem_bytes, int t, int T, int B, int b0, int ld, int col,
-                                            int lane) {
+                                            int lane, int l1) {
   if (t < 0 || t >= T || lane >= R1_N || b0 + lane >= B) return;
   const char *p = reinterpret_cast<const char *>(base) + (((size_t)t * B + b0 + lane) * ld + col) * elem_bytes;
-  asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
+  if (l1) asm volatile("prefetch.global.L1 [%0];" ::"l"(p));
+  else asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
 }
 
 // eoc flag byte of (t, b0 + lane), requested one step ahead; the ballot of it is the step's row mask
@@ -177,26 +181,26 @@ __device__ __forceinline__ unsigned char r1_eoc_raw(const unsigned char *eoc, in
 }
 
 // per-step output-dropout scale of (row b0+n, t, unit): 1/keep or 0 (model.py:29-30); 1 when dropout is off.  Rows past
-// the batch get a scale too (their values are never stored).
-__device__ __forceinline__ void r1_drop_scales(const R1Args &a, int t, int b0, int nvalid, int unit, bool uvalid,
-                                               uint32_t drop_unit, float (&dsc)[R1_N]) {
+// the batch get a scale too (their values are never stored).  The thread's rows are [nb, nb + R1_NR) of the tile.
+__device__ __forceinline__ void r1_drop_scales(const R1Args &a, int t, int b0, int nb, int nvalid, int unit, bool uvalid,
+                                               uint32_t drop_unit, float (&dsc)[R1_NR]) {
 #pragma unroll
-  for (int n = 0; n < R1_N; ++n) dsc[n] = 1.0f;
+  for (int n = 0; n < R1_NR; ++n) dsc[n] = 1.0f;
   if (!a.dropout || !uvalid) return;
   const float inv_keep = 1.0f / a.keep;
   if (a.mask != nullptr) {  // injected mask (parity tests)
-    const float *mp = a.mask + ((size_t)b0 * a.T + t) * a.H + unit;
+    const float *mp = a.mask + ((size_t)(b0 + nb) * a.T + t) * a.H + unit;
     const size_t rs = (size_t)a.T * a.H;
 #pragma unroll
-    for (int n = 0; n < R1_N; ++n)
-      if (n < nvalid) dsc[n] = __ldg(mp + n * rs) * inv_keep;
+    for (int n = 0; n < R1_NR; ++n)
+      if (nb + n < nvalid) dsc[n] = __ldg(mp + n * rs) * inv_keep;
     return;
   }
   const uint32_t pre = skm_drop_prefix(a.seed, drop_unit, (uint32_t)t);
-  const uint32_t row = (uint32_t)(a.row0 + b0);
+  const uint32_t row = (uint32_t)(a.row0 + b0 + nb);
   const float keep = a.keep;
 #pragma unroll
-  for (int n = 0; n < R1_N; ++n) dsc[n] = skm_u01(skm_drop_finish(pre, row + (uint32_t)n)) < keep ? inv_keep : 0.0f;
+  for (int n = 0; n < R1_NR; ++n) dsc[n] = skm_u01(skm_drop_finish(pre, row + (uint32_t)n)) < keep ? inv_keep : 0.0f;
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -222,9 +226,9 @@ rnn1_fwd_kernel(const __grid_constant__ CUtensorMap tm_hp, const __grid_constant
 
   r1_load_smem_tiles(a, s, tid);
   if (tid == 0) {
-    mbar_init(bar_op1, 128 * MU);
+    mbar_init(bar_op1, 256 * MU);
     mbar_init(bar_acc1, 1);
-    mbar_init(bar_op2, 128 * MU);
+    mbar_init(bar_op2, 256 * MU);
     mbar_init(bar_acc2, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -241,7 +245,9 @@ rnn1_fwd_kernel(const __grid_constant__ CUtensorMap tm_hp, const __grid_constant
   const uint32_t tmem_base = *tmem_holder_ptr;
   r1_load_tmem_tiles(a, tmem_base, warp, lane);
 
-  const int q = warp & 3, mt = warp >> 2;
+  constexpr int NR = R1_NR;
+  const int q = warp & 3, hh = (warp >> 2) & 1, mt = warp >> 3;
+  const int nb = NR * hh;  // my rows of the tile: [nb, nb + NR)
   const bool active = warp < R1_EPI_WARPS && mt < MU;
   const int unit = mt * 128 + 32 * q + lane;
   const bool uvalid = active && unit < H;
@@ -249,11 +255,11 @@ rnn1_fwd_kernel(const __grid_constant__ CUtensorMap tm_hp, const __grid_constant
   const uint32_t bcol = r1_bcol(unit), bch = r1_bchunk(unit);
   uint8_t *b1_gen = s.gen + (s.s_b1 - s.base);
   uint8_t *b2_gen = s.gen + (s.s_b2 - s.base);
-  float hcur[N];
+  float hcur[NR];
 #pragma unroll
-  for (int n = 0; n < N; ++n) {
-    hcur[n] = (uvalid && n < nvalid) ? a.state_in[(size_t)(b0 + n) * H + unit] : 0.f;
-    if (uvalid) r1_sts_bf16(b1_gen + R1_BOFF(bcol, bch, n), hcur[n]);
+  for (int n = 0; n < NR; ++n) {
+    hcur[n] = (uvalid && nb + n < nvalid) ? a.state_in[(size_t)(b0 + nb + n) * H + unit] : 0.f;
+    if (uvalid) r1_sts_bf16(b1_gen + R1_BOFF(bcol, bch, nb + n), hcur[n]);
   }
   fence_proxy_async_smem();
   tc_fence_before();
@@ -315,9 +321,9 @@ rnn1_fwd_kernel(const __grid_constant__ CUtensorMap tm_hp, const __grid_constant
     const uint32_t drop_unit = skm_drop_unit(a.seed, (uint32_t)unit);
     const int u0w = unit - lane;  // first unit of this warp
     // per-thread views of (t, b0, unit) of the step's arrays: base pointer advanced per step, row n at n * row stride
-    const char *xw_p = reinterpret_cast<const char *>(a.xw + (size_t)b0 * G + unit);  // bf16
-    char *out_p = reinterpret_cast<char *>(a.out_bf + (size_t)b0 * H + unit);
-    char *act_p = reinterpret_cast<char *>(a.acts_bf + (size_t)b0 * G + unit);
+    const char *xw_p = reinterpret_cast<const char *>(a.xw + (size_t)(b0 + nb) * G + unit);  // bf16
+    char *out_p = reinterpret_cast<char *>(a.out_bf + (size_t)(b0 + nb) * H + unit);
+    char *act_p = reinterpret_cast<char *>(a.acts_bf + (size_t)(b0 + nb) * G + unit);
     const uint32_t xw_rs = (uint32_t)G * 2u, out_rs = (uint32_t)H * 2u, act_rs = (uint32_t)G * 2u;
     const size_t xw_ts = (size_t)B * G * 2, out_ts = (size_t)B * H * 2, act_ts = (size_t)B * G * 2;
     const uint32_t gH2 = (uint32_t)H * 2u;
@@ -328,10 +334,10 @@ rnn1_fwd_kernel(const __grid_constant__ CUtensorMap tm_hp, const __grid_constant
     auto body = [&](auto full_tag, int t) {
       constexpr bool FULL = decltype(full_tag)::value;
       // everything that does not depend on the recurrence is requested before waiting for the product
-      float x0[N], x1[N], x2[N];
+      float x0[NR], x1[NR], x2[NR];
 #pragma unroll
-      for (int n = 0; n < N; ++n) {
-        const bool ok = uvalid && (FULL || n < nvalid);
+      for (int n = 0; n < NR; ++n) {
+        const bool ok = uvalid && (FULL || nb + n < nvalid);
         const char *p = xw_p + (uint32_t)n * xw_rs;
         x0[n] = ok ? r1_ld_bf16(p) : 0.f;
         x1[n] = 0.f; x2[n] = 0.f;
@@ -340,43 +346,43 @@ rnn1_fwd_kernel(const __grid_constant__ CUtensorMap tm_hp, const __grid_constant
           x2[n] = ok ? r1_ld_bf16(p + 2 * gH2) : 0.f;
         }
       }
-      if (u0w < H) {
-        r1_prefetch(a.xw, 2, t + 2, T, B, b0, G, u0w, lane);
+      if (u0w < H && hh == 0) {
+        r1_prefetch(a.xw, 2, t + a.pf_dist, T, B, b0, G, u0w, lane, a.pf_l1);
         if constexpr (CELL == 1) {
-          r1_prefetch(a.xw, 2, t + 2, T, B, b0, G, H + u0w, lane);
-          r1_prefetch(a.xw, 2, t + 2, T, B, b0, G, 2 * H + u0w, lane);
+          r1_prefetch(a.xw, 2, t + a.pf_dist, T, B, b0, G, H + u0w, lane, a.pf_l1);
+          r1_prefetch(a.xw, 2, t + a.pf_dist, T, B, b0, G, 2 * H + u0w, lane, a.pf_l1);
         }
       }
       const uint32_t eoc_m = __ballot_sync(0xffffffffu, eoc_raw != 0);
       eoc_raw = r1_eoc_raw(a.eoc, t + 1, T, B, b0, lane);
-      float dsc[N];
-      r1_drop_scales(a, t, b0, nvalid, unit, uvalid, drop_unit, dsc);
-      float ug[N];
+      float dsc[NR];
+      r1_drop_scales(a, t, b0, nb, nvalid, unit, uvalid, drop_unit, dsc);
+      float ug[NR];
 #pragma unroll
-      for (int n = 0; n < N; ++n) ug[n] = 0.f;
+      for (int n = 0; n < NR; ++n) ug[n] = 0.f;
       R1_LAP(0);
       if constexpr (CELL == 1) {
         R1_WAIT(bar_acc1, t & 1, 3);
         R1_LAP(1);
         tc_fence_after();
-        uint32_t rr[N], ru[N];
-        tc_ldn<N>(lane_addr + (uint32_t)(mt * N), rr);
-        tc_ldn<N>(lane_addr + (uint32_t)((MU + mt) * N), ru);
+        uint32_t rr[NR], ru[NR];
+        tc_ldn<NR>(lane_addr + (uint32_t)nb + (uint32_t)(mt * N), rr);
+        tc_ldn<NR>(lane_addr + (uint32_t)nb + (uint32_t)((MU + mt) * N), ru);
         tc_fence_before();
-        float rg[N];
+        float rg[NR];
 #pragma unroll
-        for (int n = 0; n < N; ++n) {
+        for (int n = 0; n < NR; ++n) {
           rg[n] = sigmoid_approx(__uint_as_float(rr[n]) + x0[n]);
           ug[n] = sigmoid_approx(__uint_as_float(ru[n]) + x1[n]);
-          if (uvalid) r1_sts_bf16(b2_gen + R1_BOFF(bcol, bch, n), rg[n] * hcur[n]);
+          if (uvalid) r1_sts_bf16(b2_gen + R1_BOFF(bcol, bch, nb + n), rg[n] * hcur[n]);
         }
         fence_proxy_async_smem();
         mbar_arrive(bar_op2);
         R1_LAP(2);
         if (uvalid) {
 #pragma unroll
-          for (int n = 0; n < N; ++n) {
-            if (FULL || n < nvalid) {
+          for (int n = 0; n < NR; ++n) {
+            if (FULL || nb + n < nvalid) {
               char *p = act_p + (uint32_t)n * act_rs;
               *reinterpret_cast<__nv_bfloat16 *>(p) = __float2bfloat16_rn(rg[n]);
               *reinterpret_cast<__nv_bfloat16 *>(p + gH2) = __float2bfloat16_rn(ug[n]);
@@ -388,20 +394,20 @@ rnn1_fwd_kernel(const __grid_constant__ CUtensorMap tm_hp, const __grid_constant
       R1_WAIT(CELL == 1 ? bar_acc2 : bar_acc1, t & 1, 4);
       R1_LAP(4);
       tc_fence_after();
-      uint32_t rc[N];
-      tc_ldn<N>(lane_addr + (uint32_t)((CELL == 1 ? 2 * MU + mt : mt) * N), rc);
+      uint32_t rc[NR];
+      tc_ldn<NR>(lane_addr + (uint32_t)nb + (uint32_t)((CELL == 1 ? 2 * MU + mt : mt) * N), rc);
       tc_fence_before();
-      float h2[N];
+      float h2[NR];
       uint8_t *b1w = b1_gen + (NB1 == 2 ? ((t + 1) & 1) * btile : 0);
 #pragma unroll
-      for (int n = 0; n < N; ++n) {
+      for (int n = 0; n < NR; ++n) {
         const float cand = tanh_approx(__uint_as_float(rc[n]) + (CELL == 1 ? x2[n] : x0[n]));
         h2[n] = CELL == 1 ? fmaf(ug[n], hcur[n] - cand, cand) : cand;   // u*h + (1-u)*c
         float hn = h2[n];
-        if ((eoc_m >> n) & 1u)  // eoc: back to the FED state (model.py:82-92); warp-uniform and rare
-          hn = uvalid ? __ldg(a.state_in + (size_t)(b0 + n) * H + unit) : 0.f;
+        if ((eoc_m >> (nb + n)) & 1u)  // eoc: back to the FED state (model.py:82-92); warp-uniform and rare
+          hn = uvalid ? __ldg(a.state_in + (size_t)(b0 + nb + n) * H + unit) : 0.f;
         hcur[n] = hn;
-        if (uvalid) r1_sts_bf16(b1w + R1_BOFF(bcol, bch, n), hn);
+        if (uvalid) r1_sts_bf16(b1w + R1_BOFF(bcol, bch, nb + n), hn);
         if constexpr (CELL == 1) x2[n] = cand;
       }
       fence_proxy_async_smem();
@@ -410,8 +416,8 @@ rnn1_fwd_kernel(const __grid_constant__ CUtensorMap tm_hp, const __grid_constant
       // off the dependent chain: layer output (pre reset, dropout applied) and the activation BPTT needs
       if (uvalid) {
 #pragma unroll
-        for (int n = 0; n < N; ++n) {
-          if (FULL || n < nvalid) {
+        for (int n = 0; n < NR; ++n) {
+          if (FULL || nb + n < nvalid) {
             *reinterpret_cast<__nv_bfloat16 *>(out_p + (uint32_t)n * out_rs) = __float2bfloat16_rn(h2[n] * dsc[n]);
             *reinterpret_cast<__nv_bfloat16 *>(act_p + (uint32_t)n * act_rs + (CELL == 1 ? 2 * gH2 : 0u)) =
                 __float2bfloat16_rn(CELL == 1 ? x2[n] : h2[n]);
@@ -426,8 +432,8 @@ rnn1_fwd_kernel(const __grid_constant__ CUtensorMap tm_hp, const __grid_constant
     }
     if (uvalid) {
 #pragma unroll
-      for (int n = 0; n < N; ++n)
-        if (n < nvalid) a.state_out[(size_t)(b0 + n) * H + unit] = hcur[n];
+      for (int n = 0; n < NR; ++n)
+        if (nb + n < nvalid) a.state_out[(size_t)(b0 + nb + n) * H + unit] = hcur[n];
     }
     if (dbg)
       printf("[rnn1 fwd cell %d] elementwise thread cycles/step: loads issue %lld, wait acc-1 %lld, gates r,u + operand %lld, stores %lld, "
@@ -462,9 +468,9 @@ __global__ void __launch_bounds__(R1_THREADS, 1) rnn1_bwd_kernel(const __grid_co
 
   r1_load_smem_tiles(a, s, tid);
   if (tid == 0) {
-    mbar_init(bar_op1, 128 * MU);
+    mbar_init(bar_op1, 256 * MU);
     mbar_init(bar_acc1, 1);
-    mbar_init(bar_op2, 128 * MU);
+    mbar_init(bar_op2, 256 * MU);
     mbar_init(bar_acc2, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -484,7 +490,9 @@ __global__ void __launch_bounds__(R1_THREADS, 1) rnn1_bwd_kernel(const __grid_co
   __syncthreads();
   tc_fence_after();
 
-  const int q = warp & 3, mt = warp >> 2;
+  constexpr int NR = R1_NR;
+  const int q = warp & 3, hh = (warp >> 2) & 1, mt = warp >> 3;
+  const int nb = NR * hh;  // my rows of the tile: [nb, nb + NR)
   const bool active = warp < R1_EPI_WARPS && mt < MU;
   const int unit = mt * 128 + 32 * q + lane;
   const bool uvalid = active && unit < H;
@@ -548,16 +556,16 @@ __global__ void __launch_bounds__(R1_THREADS, 1) rnn1_bwd_kernel(const __grid_co
     uint8_t *b2_gen = s.gen + (s.s_b2 - s.base);
     const int u0w = unit - lane;
     // per-thread views of (t, b0, unit), walking backwards in t
-    const char *act_p = reinterpret_cast<const char *>(a.acts_bf + ((size_t)(T - 1) * B + b0) * G + unit);
-    const char *hp_p = reinterpret_cast<const char *>(a.hprev_bf + ((size_t)(T - 1) * B + b0) * H + unit);
-    const char *do_p = reinterpret_cast<const char *>(a.dout + ((size_t)(T - 1) * B + b0) * H + unit);
+    const char *act_p = reinterpret_cast<const char *>(a.acts_bf + ((size_t)(T - 1) * B + b0 + nb) * G + unit);
+    const char *hp_p = reinterpret_cast<const char *>(a.hprev_bf + ((size_t)(T - 1) * B + b0 + nb) * H + unit);
+    const char *do_p = reinterpret_cast<const char *>(a.dout + ((size_t)(T - 1) * B + b0 + nb) * H + unit);
     const uint32_t act_rs = (uint32_t)G * 2u, hp_rs = (uint32_t)H * 2u, do_rs = (uint32_t)H * 4u;
     const size_t act_ts = (size_t)B * G * 2, hp_ts = (size_t)B * H * 2, do_ts = (size_t)B * H * 4;
     const uint32_t gH2 = (uint32_t)H * 2u;
     unsigned char eoc_raw = r1_eoc_raw(a.eoc, T - 1, T, B, b0, lane);
-    float dhc[N];
+    float dhc[NR];
 #pragma unroll
-    for (int n = 0; n < N; ++n) dhc[n] = 0.f;
+    for (int n = 0; n < NR; ++n) dhc[n] = 0.f;
     float bs0 = 0.f, bs1 = 0.f, bs2 = 0.f;  // bias gradients of my unit: rnn: bs0; gru: r, u, c
     const bool dbg = a.debug && blockIdx.x == 0 && tid == 0;
     uint32_t lapt = dbg ? (uint32_t)clock() : 0u;
@@ -565,10 +573,10 @@ __global__ void __launch_bounds__(R1_THREADS, 1) rnn1_bwd_kernel(const __grid_co
     auto body = [&](auto full_tag, int t, int st) {
       constexpr bool FULL = decltype(full_tag)::value;
       // saved activations and d(out) of the step: requested before waiting for the previous step's product
-      float a0[N], a1[N], a2[N], hv[N], d_o[N];
+      float a0[NR], a1[NR], a2[NR], hv[NR], d_o[NR];
 #pragma unroll
-      for (int n = 0; n < N; ++n) {
-        const bool ok = uvalid && (FULL || n < nvalid);
+      for (int n = 0; n < NR; ++n) {
+        const bool ok = uvalid && (FULL || nb + n < nvalid);
         const char *pa = act_p + (uint32_t)n * act_rs;
         a0[n] = ok ? r1_ld_bf16(pa) : 0.f;
         d_o[n] = ok ? __ldg(reinterpret_cast<const float *>(do_p + (uint32_t)n * do_rs)) : 0.f;
@@ -579,53 +587,53 @@ __global__ void __launch_bounds__(R1_THREADS, 1) rnn1_bwd_kernel(const __grid_co
           hv[n] = ok ? r1_ld_bf16(hp_p + (uint32_t)n * hp_rs) : 0.f;
         }
       }
-      if (u0w < H) {
-        r1_prefetch(a.dout, 4, t - 2, T, B, b0, H, u0w, lane);
-        r1_prefetch(a.acts_bf, 2, t - 2, T, B, b0, G, u0w, lane);
+      if (u0w < H && hh == 0) {
+        r1_prefetch(a.dout, 4, t - a.pf_dist, T, B, b0, H, u0w, lane, a.pf_l1);
+        r1_prefetch(a.acts_bf, 2, t - a.pf_dist, T, B, b0, G, u0w, lane, a.pf_l1);
         if constexpr (CELL == 1) {
-          r1_prefetch(a.acts_bf, 2, t - 2, T, B, b0, G, H + u0w, lane);
-          r1_prefetch(a.acts_bf, 2, t - 2, T, B, b0, G, 2 * H + u0w, lane);
-          r1_prefetch(a.hprev_bf, 2, t - 2, T, B, b0, H, u0w, lane);
+          r1_prefetch(a.acts_bf, 2, t - a.pf_dist, T, B, b0, G, H + u0w, lane, a.pf_l1);
+          r1_prefetch(a.acts_bf, 2, t - a.pf_dist, T, B, b0, G, 2 * H + u0w, lane, a.pf_l1);
+          r1_prefetch(a.hprev_bf, 2, t - a.pf_dist, T, B, b0, H, u0w, lane, a.pf_l1);
         }
       }
       const uint32_t eoc_m = __ballot_sync(0xffffffffu, eoc_raw != 0);
       eoc_raw = r1_eoc_raw(a.eoc, t - 1, T, B, b0, lane);
-      float dsc[N];
-      r1_drop_scales(a, t, b0, nvalid, unit, uvalid, drop_unit, dsc);
+      float dsc[NR];
+      r1_drop_scales(a, t, b0, nb, nvalid, unit, uvalid, drop_unit, dsc);
       R1_LAP(0);
       if (st > 0) {  // d(h_t) from the step after: the product issued last iteration
         R1_WAIT(CELL == 1 ? bar_acc2 : bar_acc1, (st - 1) & 1, 14);
         tc_fence_after();
-        uint32_t r[N];
-        tc_ldn<N>(lane_addr + (uint32_t)((CELL == 1 ? MU + mt : mt) * N), r);
+        uint32_t r[NR];
+        tc_ldn<NR>(lane_addr + (uint32_t)nb + (uint32_t)((CELL == 1 ? MU + mt : mt) * N), r);
         tc_fence_before();
 #pragma unroll
-        for (int n = 0; n < N; ++n) dhc[n] = (CELL == 1 ? dhc[n] : 0.f) + __uint_as_float(r[n]);
+        for (int n = 0; n < NR; ++n) dhc[n] = (CELL == 1 ? dhc[n] : 0.f) + __uint_as_float(r[n]);
       }
       R1_LAP(1);
       if constexpr (CELL == 2) {
         uint8_t *b1w = b1_gen + (st & 1) * btile;
 #pragma unroll
-        for (int n = 0; n < N; ++n) {
-          const float dh2 = d_o[n] * dsc[n] + (((eoc_m >> n) & 1u) ? 0.f : dhc[n]);
+        for (int n = 0; n < NR; ++n) {
+          const float dh2 = d_o[n] * dsc[n] + (((eoc_m >> (nb + n)) & 1u) ? 0.f : dhc[n]);
           const float dp = dh2 * (1.0f - a0[n] * a0[n]);
           bs0 += dp;
-          if (uvalid) r1_sts_bf16(b1w + R1_BOFF(bcol, bch, n), dp);
+          if (uvalid) r1_sts_bf16(b1w + R1_BOFF(bcol, bch, nb + n), dp);
         }
         fence_proxy_async_smem();
         mbar_arrive(bar_op1);
         R1_LAP(2);
       } else {
         // a0 = r, a1 = u, a2 = candidate, hv = h fed to the step
-        float du[N];
+        float du[NR];
 #pragma unroll
-        for (int n = 0; n < N; ++n) {
-          const float dh2 = d_o[n] * dsc[n] + (((eoc_m >> n) & 1u) ? 0.f : dhc[n]);
+        for (int n = 0; n < NR; ++n) {
+          const float dh2 = d_o[n] * dsc[n] + (((eoc_m >> (nb + n)) & 1u) ? 0.f : dhc[n]);
           du[n] = dh2 * (hv[n] - a2[n]);
           const float dpc = dh2 * (1.0f - a1[n]) * (1.0f - a2[n] * a2[n]);
           dhc[n] = dh2 * a1[n];  // direct path h -> h'; the two products add to it below / next iteration
           bs2 += dpc;
-          if (uvalid) r1_sts_bf16(b1_gen + R1_BOFF(bcol, bch, n), dpc);
+          if (uvalid) r1_sts_bf16(b1_gen + R1_BOFF(bcol, bch, nb + n), dpc);
         }
         fence_proxy_async_smem();
         mbar_arrive(bar_op1);
@@ -633,11 +641,11 @@ __global__ void __launch_bounds__(R1_THREADS, 1) rnn1_bwd_kernel(const __grid_co
         R1_WAIT(bar_acc1, st & 1, 15);
         R1_LAP(4);
         tc_fence_after();
-        uint32_t r[N];
-        tc_ldn<N>(lane_addr + (uint32_t)(mt * N), r);
+        uint32_t r[NR];
+        tc_ldn<NR>(lane_addr + (uint32_t)nb + (uint32_t)(mt * N), r);
         tc_fence_before();
 #pragma unroll
-        for (int n = 0; n < N; ++n) {
+        for (int n = 0; n < NR; ++n) {
           const float drh = __uint_as_float(r[n]);
           dhc[n] = fmaf(drh, a0[n], dhc[n]);
           const float dpr = drh * hv[n] * a0[n] * (1.0f - a0[n]);
@@ -645,8 +653,8 @@ __global__ void __launch_bounds__(R1_THREADS, 1) rnn1_bwd_kernel(const __grid_co
           bs0 += dpr;
           bs1 += dpu;
           if (uvalid) {
-            r1_sts_bf16(b2_gen + R1_BOFF(bcol, bch, n), dpr);
-            r1_sts_bf16(b2_gen + R1_BOFF(bcol_u, bch_u, n), dpu);
+            r1_sts_bf16(b2_gen + R1_BOFF(bcol, bch, nb + n), dpr);
+            r1_sts_bf16(b2_gen + R1_BOFF(bcol_u, bch_u, nb + n), dpu);
           }
         }
         fence_proxy_async_smem();
@@ -828,6 +836,13 @@ int sk_rnn1_tc_layer(skrnn_handle *h, cudaStream_t st, bool bwd, int l, int B, i
     static int dbg_env = -1;
     if (dbg_env < 0) { const char *e = getenv("SKRNN_TC_DEBUG"); dbg_env = (e && e[0] == '1') ? 1 : 0; }
     a.debug = dbg_env;
+    static int pf_d = -1, pf_l = -1;
+    if (pf_d < 0) {
+      const char *e = getenv("SKRNN_R1_PREFETCH");  // "<distance>[L1]", e.g. "2" (default) or "1L1"
+      pf_d = e ? atoi(e) : 2;
+      pf_l = (e && strstr(e, "L1")) ? 1 : 0;
+    }
+    a.pf_dist = pf_d; a.pf_l1 = pf_l;
   }
   const size_t smem = (size_t)soff + b_bytes + 1024 + 256;
   const int grid = (B + R1_N - 1) / R1_N;

@@ -1340,7 +1340,7 @@ lstm_bwd_pp_kernel(const __grid_constant__ CUtensorMap tm_acts, const __grid_con
                                     ((size_t)((esub * NCH) / CK) * 32 + eu) * CK + (esub * NCH) % CK;
 #pragma unroll
         for (int it = 0; it < NCH; ++it) dhc[s][it] = 0.f;
-        constexpr int UR = 8;
+        constexpr int UR = 16;  // all ranks' partials in flight at once: one L2 round trip instead of two
         for (int r0 = 0; r0 < CS; r0 += UR) {
           if constexpr (NCH == 4) {
             uint2 v[UR];
