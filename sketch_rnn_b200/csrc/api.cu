@@ -190,7 +190,7 @@ int bias_grad(skrnn_handle *h, cudaStream_t st, Op d, int64_t rows, int cols, fl
 
 // forward unroll of the whole stack + output projection (model.py:97-99)
 int run_forward(skrnn_handle *h, cudaStream_t st, int B, int T, const float *x, const float *state_in,
-                float *state_out, const float *mask, uint64_t seed, int row0, bool training) {
+                float *state_out, const float *mask, uint64_t seed, int row0, bool training, bool want_logits = true) {
   const int H = h->H, G = h->G;
   const int64_t R = (int64_t)B * T;
   SK_TRY(sk_cast_params(h, st));
@@ -239,8 +239,9 @@ int run_forward(skrnn_handle *h, cudaStream_t st, int B, int T, const float *x, 
     SK_TRY(sk_rnn_forward_layer(h, st, l, B, T, x, state_in + (size_t)l * B * h->S,
                                 state_out + (size_t)l * B * h->S, mask, seed, row0, training));
   }
-  SK_TRY(gemm(h, st, (int)R, h->NOUT, H, top_output(h), true, out_weight(h), true, h->ws.logits, h->NOUT,
-              h->params + h->off_out_b, false));
+  if (want_logits)
+    SK_TRY(gemm(h, st, (int)R, h->NOUT, H, top_output(h), true, out_weight(h), true, h->ws.logits, h->NOUT,
+                h->params + h->off_out_b, false));
   return 0;
 }
 
@@ -546,12 +547,16 @@ int skrnn_loss_grad(skrnn_handle *h, int32_t B, int32_t T, const float *x_dev, c
   const int R = B * T;
   SK_CUDA(cudaMemsetAsync(h->grads, 0, (size_t)h->P * sizeof(float), st));
   SK_CUDA(cudaMemsetAsync(h->scal, 0, 3 * sizeof(double), st));
-  SK_TRY(run_forward(h, st, B, T, x_dev, state_in_dev, state_out_dev, dropout_mask_dev, seed, row0, true));
-  SK_TRY(sk_head(h, st, B, T, y_dev, nullptr, true, loss_rows));
+  // bf16 path: the output layer, the head and d(logits) are one kernel and the logits never reach memory
+  const bool fused_head = sk_head_tc_eligible(h);
+  SK_TRY(run_forward(h, st, B, T, x_dev, state_in_dev, state_out_dev, dropout_mask_dev, seed, row0, true, !fused_head));
+  if (fused_head) SK_TRY(sk_head_tc(h, st, B, T, y_dev, loss_rows));
+  else SK_TRY(sk_head(h, st, B, T, y_dev, nullptr, true, loss_rows));
   SK_TRY(sk_finalize_losses(h, st, losses_dev));
   // head backward: d output_w, d output_b, d(top layer output)
   SK_TRY(gemm(h, st, H, NOUT, R, top_output(h), false, dlogits_op(h), true, h->grads + h->off_out_w, NOUT, nullptr, true));
-  SK_TRY(sk_colsum(h, st, h->ws.logits, R, NOUT, NOUT, h->grads + h->off_out_b));
+  if (fused_head) SK_TRY(sk_colsum_bf16(h, st, h->ws.dlogits_bf, R, NOUT, h->NOUTP, h->grads + h->off_out_b));
+  else SK_TRY(sk_colsum(h, st, h->ws.logits, R, NOUT, NOUT, h->grads + h->off_out_b));
   SK_TRY(gemm(h, st, R, H, NOUT, dlogits_op(h), true, out_weight(h), false, h->ws.dout, H, nullptr, false));
   // Weight gradients are off the critical path: on the bf16 path layer l's dW products are enqueued on a side
   // stream so that they run next to layer l-1's BPTT kernel (which leaves SMs idle: its clusters do not tile the

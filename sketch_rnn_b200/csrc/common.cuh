@@ -209,6 +209,9 @@ int sk_rnn_backward_layer(skrnn_handle *h, cudaStream_t st, int l, int B, int T,
 
 int sk_head(skrnn_handle *h, cudaStream_t st, int B, int T, const float *y_bt5, float *mdn_out,
             bool want_grad, int64_t loss_rows);
+// output layer + MDN head + d(logits) in one tcgen05 kernel (head_tc.cu, bf16 training path)
+bool sk_head_tc_eligible(const skrnn_handle *h);
+int sk_head_tc(skrnn_handle *h, cudaStream_t st, int B, int T, const float *y_bt5, int64_t loss_rows);
 int sk_finalize_losses(skrnn_handle *h, cudaStream_t st, float *losses_dev);
 int sk_clip_adam(skrnn_handle *h, cudaStream_t st, float lr, float *gnorm_out);
 int sk_cast_params(skrnn_handle *h, cudaStream_t st);

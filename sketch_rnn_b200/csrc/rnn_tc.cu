@@ -699,14 +699,19 @@ lstm_fwd_pp_kernel(const __grid_constant__ CUtensorMap tm_h, const __grid_consta
 #pragma unroll
         for (int it = 0; it < NCH; ++it) dsc[it] = 1.0f;
         if (a.dropout) {
-          const uint32_t pre = skm_drop_prefix(a.seed, drop_unit, (uint32_t)t);  // (unit, t) part of the mask hash
+          if (a.mask != nullptr) {  // injected mask (parity tests)
 #pragma unroll
-          for (int it = 0; it < NCH; ++it) {
-            if ((valid[s] >> it) & 1u) {
-              const int b = b0 + s * N2 + cb + 4 * it;
-              dsc[it] = a.mask != nullptr ? a.mask[((int64_t)b * T + t) * H + uo] * inv_keep
-                                          : (skm_u01(skm_drop_finish(pre, (uint32_t)(a.row0 + b))) < a.keep ? inv_keep : 0.0f);
-            }
+            for (int it = 0; it < NCH; ++it)
+              if ((valid[s] >> it) & 1u)
+                dsc[it] = a.mask[((int64_t)(b0 + s * N2 + cb + 4 * it) * T + t) * H + uo] * inv_keep;
+          } else {
+            // rows past the batch get a scale too (never stored): no per-item predicates around the hash
+            const uint32_t pre = skm_drop_prefix(a.seed, drop_unit, (uint32_t)t);  // (unit, t) part of the mask hash
+            const uint32_t row = (uint32_t)(a.row0 + b0 + s * N2 + cb);
+            const float keep = a.keep;
+#pragma unroll
+            for (int it = 0; it < NCH; ++it)
+              dsc[it] = skm_u01(skm_drop_finish(pre, row + (uint32_t)(4 * it))) < keep ? inv_keep : 0.0f;
           }
         }
         TCR_LAP(tk[0]);
