@@ -40,57 +40,73 @@ struct HeadTcArgs {
 
 // The head on one parked row z[0..NOUT): on return z holds d(cost)/d(logits) (zero past NOUT), and the row's two loss
 // terms are returned.  Same formulas as mdn_head_kernel (head.cu); the mixture loop runs serially in one thread.
+__device__ __forceinline__ float ht_rcp(float x) {
+  float y;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+__device__ __forceinline__ float ht_rsqrt(float x) {
+  float y;
+  asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+// One thread runs 24 mixtures serially with one warp per scheduler, so instruction count is what this kernel costs:
+// the transcendental functions are the hardware approximations (ex2 / lg2 / tanh / rcp / rsqrt, relative error
+// ~1e-6 -- three orders below the bf16 rounding of the logits this path starts from).
 __device__ __forceinline__ void ht_row(float *z, int M, int NOUT, const float *tg, float inv_rows, float sif, float sqrt_sif,
                                        float &row_shape, float &row_pen) {
   const float x1 = tg[0], x2 = tg[1], p_eos = tg[2], p_eoc = tg[3], p_cont = tg[4];
   float *zpi = z + 3, *zm1 = zpi + M, *zm2 = zm1 + M, *zs1 = zm2 + M, *zs2 = zs1 + M, *zr = zs2 + M;
+  const float inv_2pi = 0.15915494309189535f;
   float mx = -INFINITY;
   for (int k = 0; k < M; ++k) mx = fmaxf(mx, zpi[k]);
   float se = 0.f;
   for (int k = 0; k < M; ++k) {
-    const float e = expf(zpi[k] - mx);
+    const float e = __expf(zpi[k] - mx);
     zpi[k] = e;
     se += e;
   }
-  const float inv_se = 1.0f / se;
+  const float inv_se = ht_rcp(se);
   float S = 0.f;
   for (int k = 0; k < M; ++k) {
     const float pi = zpi[k] * inv_se;
-    const float s1 = expf(zs1[k]), s2 = expf(zs2[k]), rho = tanhf(zr[k]);
-    const float a = (x1 - zm1[k]) / s1, b = (x2 - zm2[k]) / s2;
+    const float i1 = __expf(-zs1[k]), i2 = __expf(-zs2[k]), rho = tanh_approx(zr[k]);  // 1/sigma1, 1/sigma2
+    const float a = (x1 - zm1[k]) * i1, b = (x2 - zm2[k]) * i2;
     const float q = 1.f - rho * rho;
+    const float iq = ht_rcp(q);
     const float Z = a * a + b * b - 2.f * rho * a * b;
-    const float dens = expf(-Z / (2.f * q)) / (6.283185307179586f * (s1 * s2 * sqrtf(q)));
+    const float dens = __expf(-0.5f * Z * iq) * (inv_2pi * i1 * i2 * ht_rsqrt(q));
     S += dens * pi;
-    zpi[k] = pi; zm1[k] = a; zm2[k] = b; zs1[k] = s1; zs2[k] = s2; zr[k] = rho;
+    zpi[k] = pi; zm1[k] = a; zm2[k] = b; zs1[k] = i1; zs2[k] = i2; zr[k] = rho;
   }
-  row_shape = -logf(fmaxf(S, 1e-20f));  // model.py:130
-  const bool live = S >= 1e-20f;        // the clamp passes no gradient to the mixture
-  const float invS = live ? 1.0f / S : 0.f;
+  row_shape = -__logf(fmaxf(S, 1e-20f));  // model.py:130
+  const bool live = S >= 1e-20f;          // the clamp passes no gradient to the mixture
+  const float invS = live ? ht_rcp(S) : 0.f;
   for (int k = 0; k < M; ++k) {
-    const float pi = zpi[k], a = zm1[k], b = zm2[k], s1 = zs1[k], s2 = zs2[k], rho = zr[k];
+    const float pi = zpi[k], a = zm1[k], b = zm2[k], i1 = zs1[k], i2 = zs2[k], rho = zr[k];
     const float q = 1.f - rho * rho;
+    const float iq = ht_rcp(q);
     const float Z = a * a + b * b - 2.f * rho * a * b;
-    const float dens = expf(-Z / (2.f * q)) / (6.283185307179586f * (s1 * s2 * sqrtf(q)));
+    const float dens = __expf(-0.5f * Z * iq) * (inv_2pi * i1 * i2 * ht_rsqrt(q));
     const float gam = pi * dens * invS;
     const float ga = gam * inv_rows;
     zpi[k] = ((live ? pi : 0.f) - gam) * inv_rows;
-    zm1[k] = -ga * (a - rho * b) / (s1 * q);
-    zm2[k] = -ga * (b - rho * a) / (s2 * q);
-    zs1[k] = -ga * (a * (a - rho * b) / q - 1.f);
-    zs2[k] = -ga * (b * (b - rho * a) / q - 1.f);
-    zr[k] = -ga * (a * b + rho * (1.f - Z / q));
+    zm1[k] = -ga * (a - rho * b) * i1 * iq;
+    zm2[k] = -ga * (b - rho * a) * i2 * iq;
+    zs1[k] = -ga * (a * (a - rho * b) * iq - 1.f);
+    zs2[k] = -ga * (b * (b - rho * a) * iq - 1.f);
+    zr[k] = -ga * (a * b + rho * (1.f - Z * iq));
   }
   // pen softmax cross-entropy weighted by the stroke importance (model.py:132-136)
   const float z0 = z[0], z1 = z[1], z2 = z[2];
   const float zm = fmaxf(z0, fmaxf(z1, z2));
-  const float e0 = expf(z0 - zm), e1 = expf(z1 - zm), e2 = expf(z2 - zm);
-  const float lse = zm + logf(e0 + e1 + e2);
+  const float e0 = __expf(z0 - zm), e1 = __expf(z1 - zm), e2 = __expf(z2 - zm);
+  const float lse = zm + __logf(e0 + e1 + e2);
   const float xent = -(p_eos * (z0 - lse) + p_eoc * (z1 - lse) + p_cont * (z2 - lse));
   const float w = p_cont + sqrt_sif * p_eos + sif * p_eoc;
   row_pen = xent * w;
   const float psum = p_eos + p_eoc + p_cont;
-  const float inv_e = 1.0f / (e0 + e1 + e2);
+  const float inv_e = ht_rcp(e0 + e1 + e2);
   const float ws = w * inv_rows;
   z[0] = ws * (e0 * inv_e * psum - p_eos);
   z[1] = ws * (e1 * inv_e * psum - p_eoc);

@@ -184,6 +184,9 @@ class Model(object):
         out["beta1_power"] = np.float32(b1)
         out["beta2_power"] = np.float32(b2)
         out["Variable"] = np.float32(self.lr)
+        # not a TF variable: the number of training steps taken, which seeds the in-kernel dropout mask of the next
+        # step (a restored model must not replay the masks it has already used)
+        out["skrnn/dropout_step"] = np.float32(self._step)
         return out
 
     def load_variables(self, var):
@@ -200,6 +203,8 @@ class Model(object):
                                        float(var.get("beta2_power", 0.999)))
         if "Variable" in var:
             self.lr = float(var["Variable"])
+        if "skrnn/dropout_step" in var:
+            self._step = int(var["skrnn/dropout_step"])
 
 
 class Session(object):
@@ -237,20 +242,33 @@ class Session(object):
 
 
 class Saver(object):
-    """tf.train.Saver over `save/<dataset>/`: writes `model.ckpt-<step>` and the text index file
-    `checkpoint` (model_checkpoint_path / all_model_checkpoint_paths lines, as TF does)."""
+    """tf.train.Saver over `save/<dataset>/`: writes `model.ckpt-<step>` and the text index file `checkpoint`
+    (model_checkpoint_path / all_model_checkpoint_paths lines, as TF does), keeping the newest `max_to_keep`
+    checkpoints of this Saver and deleting older ones (TF's default is 5)."""
 
-    def __init__(self, model):
+    def __init__(self, model, max_to_keep=5):
         self.model = model
+        self.max_to_keep = max_to_keep
+        self._kept = []
 
     def save(self, sess, checkpoint_path, global_step=0):
         from . import checkpoint as ck
         path = "%s-%d" % (checkpoint_path, global_step)
         ck.write_checkpoint(path, self.model.variables())
+        if path in self._kept:
+            self._kept.remove(path)
+        self._kept.append(path)
+        while self.max_to_keep and len(self._kept) > self.max_to_keep:
+            old = self._kept.pop(0)
+            try:
+                os.remove(old)
+            except OSError:
+                pass
         d = os.path.dirname(path)
         with open(os.path.join(d, "checkpoint"), "w") as f:
-            f.write('model_checkpoint_path: "%s"\nall_model_checkpoint_paths: "%s"\n'
-                    % (os.path.basename(path), os.path.basename(path)))
+            f.write('model_checkpoint_path: "%s"\n' % os.path.basename(path))
+            for k in self._kept:
+                f.write('all_model_checkpoint_paths: "%s"\n' % os.path.basename(k))
         return path
 
     def restore(self, sess, path):

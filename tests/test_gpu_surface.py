@@ -133,3 +133,19 @@ def test_batched_rejection_sampling_accepts_what_the_one_by_one_loop_accepts(tmp
         for g, w in zip(got, want):
             assert g.shape == w.shape and np.array_equal(g.view(np.uint32), w.view(np.uint32)), per_launch
         assert os.path.exists(str(tmp_path / ("out%d.svg" % per_launch)))
+
+
+def test_saver_keeps_the_last_five_checkpoints(tmp_path):
+    """tf.train.Saver's default max_to_keep = 5 (train.py:64,74 relies on it: a 500-epoch run saves hundreds of times)."""
+    from sketch_rnn_b200.model import Model, Saver, Session, get_checkpoint_state
+    m = Model(_args(), precision="f32")
+    d = tmp_path / "save" / "toy"
+    d.mkdir(parents=True)
+    saver = Saver(m)
+    for step in range(1, 8):
+        saver.save(Session(m), str(d / "model.ckpt"), global_step=step * 250)
+    left = sorted(f for f in os.listdir(str(d)) if f.startswith("model.ckpt-"))
+    assert left == sorted("model.ckpt-%d" % (s * 250) for s in range(3, 8)), left
+    idx = open(str(d / "checkpoint")).read()
+    assert idx.count("all_model_checkpoint_paths") == 5 and 'model_checkpoint_path: "model.ckpt-1750"' in idx
+    assert get_checkpoint_state(str(d)).model_checkpoint_path.endswith("model.ckpt-1750")
