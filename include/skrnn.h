@@ -125,6 +125,16 @@ SKRNN_API int skrnn_loss_grad(skrnn_handle *h, int32_t B, int32_t T, const float
                     int32_t row0, int64_t loss_rows, float *losses_dev, float *state_out_dev,
                     void *stream);
 
+/* Data-parallel overlap (no reference counterpart: the reference is single-process; the gradient it would exchange
+ * is the output of tf.gradients, model.py:182).  skrnn_loss_grad finishes the flat gradient back to front: the output
+ * layer's tensors first, then the cell layers from the top one down.  Segment `index` is L for (output_w, output_b)
+ * and l for layer l's tensors; each is one contiguous range [offset, offset + count) of skrnn_grads_dev(h).
+ * skrnn_stream_wait_grad makes `stream` wait (cudaStreamWaitEvent, no host blocking) until the most recent
+ * skrnn_loss_grad has finished writing that segment, so a caller can start reducing it over the ranks on its own
+ * communication stream while the layers below are still being differentiated.  Segment L also covers losses_dev. */
+SKRNN_API int skrnn_grad_segment(const skrnn_handle *h, int32_t index, int64_t *offset, int64_t *count);
+SKRNN_API int skrnn_stream_wait_grad(skrnn_handle *h, int32_t index, void *stream);
+
 /* Replaces tf.clip_by_global_norm + AdamOptimizer(lr, epsilon=1e-3).apply_gradients
  * (model.py:182-184) on the gradient currently in skrnn_grads_dev(h).
  * gnorm_out_dev: [1] global norm before clipping, or NULL. */

@@ -47,6 +47,8 @@ SYMBOLS = {
     "skrnn_forward": (C.c_int, [_P, C.c_int32, C.c_int32, _P, _P, _P, _P, _P]),
     "skrnn_loss_grad": (C.c_int, [_P, C.c_int32, C.c_int32, _P, _P, _P, _P, C.c_uint64, C.c_int32,
                                   C.c_int64, _P, _P, _P]),
+    "skrnn_grad_segment": (C.c_int, [_P, C.c_int32, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]),
+    "skrnn_stream_wait_grad": (C.c_int, [_P, C.c_int32, _P]),
     "skrnn_apply_clip_adam": (C.c_int, [_P, C.c_float, _P, _P]),
     "skrnn_train_step_host": (C.c_int, [_P, C.c_int32, C.c_int32, _P, _P, _P, C.c_float, C.c_uint64, _P]),
     "skrnn_sample": (C.c_int, [_P, C.c_int32, C.c_int32, C.c_float, C.c_float, C.c_int32, _P, C.c_uint64,
@@ -201,6 +203,20 @@ class Handle(object):
                                        B * T if loss_rows is None else loss_rows, losses.data_ptr(),
                                        state_out.data_ptr(), _stream_ptr(stream)))
         return losses, state_out
+
+    def grad_segments(self):
+        """[(index, offset, count)] in the order skrnn_loss_grad finishes them: output layer (index L), then layers
+        L-1 .. 0."""
+        out = []
+        off, cnt = C.c_int64(), C.c_int64()
+        for idx in [self.L] + list(range(self.L - 1, -1, -1)):
+            check(self.lib.skrnn_grad_segment(self._h, idx, C.byref(off), C.byref(cnt)))
+            out.append((idx, off.value, cnt.value))
+        return out
+
+    def stream_wait_grad(self, index, stream):
+        """`stream` (torch.cuda.Stream) waits until the last loss_grad has finished gradient segment `index`."""
+        check(self.lib.skrnn_stream_wait_grad(self._h, index, C.c_void_p(stream.cuda_stream)))
 
     def apply_clip_adam(self, lr, stream=None):
         import torch

@@ -352,6 +352,7 @@ int skrnn_create(const skrnn_config *cfg, skrnn_handle **out) {
     cudaEventCreateWithFlags(&h->ev_main[i], cudaEventDisableTiming);
     cudaEventCreateWithFlags(&h->ev_side[i], cudaEventDisableTiming);
   }
+  for (int i = 0; i <= h->L; ++i) cudaEventCreateWithFlags(&h->ev_grad[i], cudaEventDisableTiming);
   h->ws.wpack_floats = (int64_t)h->cluster_size * h->H * 256;
   if (cudaMalloc(&h->ws.wpack, h->ws.wpack_floats * sizeof(float)) != cudaSuccess) {
     sk_set_error("skrnn_create: cudaMalloc of weight pack failed");
@@ -401,6 +402,8 @@ void skrnn_destroy(skrnn_handle *h) {
     if (h->ev_main[i]) cudaEventDestroy(h->ev_main[i]);
     if (h->ev_side[i]) cudaEventDestroy(h->ev_side[i]);
   }
+  for (int i = 0; i <= SK_MAX_LAYERS; ++i)
+    if (h->ev_grad[i]) cudaEventDestroy(h->ev_grad[i]);
   for (auto &r : h->prof) { cudaEventDestroy(r.a); cudaEventDestroy(r.b); }
   for (auto e : h->prof_pool) cudaEventDestroy(e);
   delete h;
@@ -557,6 +560,7 @@ int skrnn_loss_grad(skrnn_handle *h, int32_t B, int32_t T, const float *x_dev, c
   SK_TRY(gemm(h, st, H, NOUT, R, top_output(h), false, dlogits_op(h), true, h->grads + h->off_out_w, NOUT, nullptr, true));
   if (fused_head) SK_TRY(sk_colsum_bf16(h, st, h->ws.dlogits_bf, R, NOUT, h->NOUTP, h->grads + h->off_out_b));
   else SK_TRY(sk_colsum(h, st, h->ws.logits, R, NOUT, NOUT, h->grads + h->off_out_b));
+  SK_CUDA(cudaEventRecord(h->ev_grad[h->L], st));  // output_w / output_b gradients (and the losses) are final
   SK_TRY(gemm(h, st, R, H, NOUT, dlogits_op(h), true, out_weight(h), false, h->ws.dout, H, nullptr, false));
   // Weight gradients are off the critical path: on the bf16 path layer l's dW products are enqueued on a side
   // stream so that they run next to layer l-1's BPTT kernel (which leaves SMs idle: its clusters do not tile the
@@ -579,6 +583,7 @@ int skrnn_loss_grad(skrnn_handle *h, int32_t B, int32_t T, const float *x_dev, c
     h->gemm_perm_H = 0;
     SK_TRY(rc);
     if (!bias_done) SK_TRY(bias_grad(h, s2, dpre, R, G, h->grads + lp.b[0]));
+    SK_CUDA(cudaEventRecord(h->ev_grad[l], s2));  // layer l's gradient tensors are final
     return 0;
   };
   auto flush_deferred = [&]() -> int {
@@ -613,6 +618,7 @@ int skrnn_loss_grad(skrnn_handle *h, int32_t B, int32_t T, const float *x_dev, c
       SK_TRY(gemm(h, st, I, H, R, X, false, dc, true, gWc, H, nullptr, true));
       SK_TRY(gemm(h, st, H, H, R, aux_op(h, l), false, dc, true, gWc + (size_t)I * H, H, nullptr, true));
       if (!h->bias_grad_done) SK_TRY(bias_grad(h, st, dc, R, H, h->grads + lp.b[1]));
+      SK_CUDA(cudaEventRecord(h->ev_grad[l], st));
       if (l > 0) {
         SK_TRY(gemm(h, st, R, I, 2 * H, dg, true, weight(h, l, 0), false, h->ws.dout, H, nullptr, false));
         SK_TRY(gemm(h, st, R, I, H, dc, true, weight(h, l, 1), false, h->ws.dout, H, nullptr, true));
@@ -636,6 +642,27 @@ int skrnn_loss_grad(skrnn_handle *h, int32_t B, int32_t T, const float *x_dev, c
   SK_TRY(flush_deferred());
   for (int b2 = 0; b2 < 2; ++b2)
     if (side_busy[b2]) SK_CUDA(cudaStreamWaitEvent(st, h->ev_side[b2], 0));  // join
+  return 0;
+}
+
+int skrnn_grad_segment(const skrnn_handle *h, int32_t index, int64_t *offset, int64_t *count) {
+  SK_CHECK(h != nullptr && offset && count, "grad_segment: null argument");
+  SK_CHECK(index >= 0 && index <= h->L, "grad_segment: index %d out of range [0,%d]", index, h->L);
+  if (index == h->L) {  // output_w, output_b: the head of the flat vector
+    *offset = 0;
+    *count = h->lp[0].w[0];
+  } else {
+    *offset = h->lp[index].w[0];
+    *count = (index + 1 < h->L ? h->lp[index + 1].w[0] : h->P) - h->lp[index].w[0];
+  }
+  return 0;
+}
+
+int skrnn_stream_wait_grad(skrnn_handle *h, int32_t index, void *stream) {
+  SK_CHECK(h != nullptr, "null handle");
+  SK_CHECK(index >= 0 && index <= h->L, "stream_wait_grad: index %d out of range [0,%d]", index, h->L);
+  SkDeviceGuard guard(h->cfg.device);
+  SK_CUDA(cudaStreamWaitEvent((cudaStream_t)stream, h->ev_grad[index], 0));
   return 0;
 }
 

@@ -122,6 +122,8 @@ struct skrnn_handle {
   // side stream for work off the critical path of the backward pass (weight gradients), see skrnn_loss_grad
   cudaStream_t side = nullptr;
   cudaEvent_t ev_main[2] = {nullptr, nullptr}, ev_side[2] = {nullptr, nullptr};
+  // recorded by skrnn_loss_grad when a gradient segment is final: [l] = layer l's tensors, [L] = the output layer's
+  cudaEvent_t ev_grad[SK_MAX_LAYERS + 1] = {nullptr};
   // lstm, bf16: Wx of every layer with gate-interleaved columns (4*unit + gate), rows padded to 8 for layer 0, and the
   // bias in the same order: the GEMM that produces xw_il
   __nv_bfloat16 *wx_il[SK_MAX_LAYERS] = {nullptr};

@@ -27,19 +27,67 @@ def allreduce_sum_(tensors, group=None):
         dist.all_reduce(t, op=dist.ReduceOp.SUM, group=group)
 
 
-def dp_train_step(handle, x_shard, y_shard, state, lr, seed, row0, global_rows, group=None, timing=None):
+_comm_streams = {}
+
+
+def _comm_stream(device):
+    st = _comm_streams.get(device)
+    if st is None:
+        st = _comm_streams[device] = torch.cuda.Stream(device=device)
+    return st
+
+
+def allreduce_grads_overlapped_(handle, losses, group=None):
+    """Sum of the flat gradient (and the three losses) over the ranks, started segment by segment while the backward
+    pass is still running: skrnn_loss_grad finishes the output layer's gradient first and the cell layers from the top
+    down, and records an event for each; a communication stream waits for a segment's event and reduces that slice
+    (NCCL over NVLink), so only the last segment's reduction is exposed.  The caller's stream then waits for the
+    communication stream.  Same sums as one all-reduce of the whole vector."""
+    g = handle.grads_tensor()
+    dev = g.device
+    comm = _comm_stream(dev)
+
+    def gate(idx):
+        handle.stream_wait_grad(idx, comm)
+
+    with torch.cuda.stream(comm):
+        reduce_segments_(g, handle.grad_segments(), losses, group, before_segment=gate)
+    torch.cuda.current_stream(dev).wait_stream(comm)
+
+
+def reduce_segments_(g, segments, losses, group=None, before_segment=None):
+    """The segment-wise sum behind allreduce_grads_overlapped_: `segments` = [(index, offset, count)] covering the flat
+    gradient `g`; `before_segment(index)` is called before a segment's collective is enqueued (the GPU path makes the
+    communication stream wait for that segment's event there).  The losses ride with the first segment."""
+    first = True
+    for idx, off, cnt in segments:
+        if before_segment is not None:
+            before_segment(idx)
+        if first:
+            dist.all_reduce(losses, op=dist.ReduceOp.SUM, group=group)
+            first = False
+        dist.all_reduce(g[off:off + cnt], op=dist.ReduceOp.SUM, group=group)
+
+
+def dp_train_step(handle, x_shard, y_shard, state, lr, seed, row0, global_rows, group=None, timing=None, overlap=True):
     """One data-parallel step on this rank's shard.  Returns (losses[3] summed over ranks, new state).
-    timing: optional dict; when given, CUDA events bracket the all-reduce and its milliseconds are added to
-    timing["allreduce_ms"] (this synchronises the stream -- measurement passes only)."""
+    overlap: reduce the gradient per layer while the layers below are still in their backward pass
+    (allreduce_grads_overlapped_); False: one all-reduce of the whole vector after the backward pass.
+    timing: optional dict; when given, the all-reduce runs un-overlapped between CUDA events and its milliseconds are
+    added to timing["allreduce_ms"] (this synchronises the stream -- measurement passes only)."""
     losses, state = handle.loss_grad(x_shard, y_shard, state, seed=seed, row0=row0, loss_rows=global_rows)
+    multi = dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1
     if timing is not None:
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
-    allreduce_sum_([handle.grads_tensor(), losses], group)
-    if timing is not None:
+        allreduce_sum_([handle.grads_tensor(), losses], group)
         e1.record()
         e1.synchronize()
         timing["allreduce_ms"] = timing.get("allreduce_ms", 0.0) + e0.elapsed_time(e1)
+    elif multi and overlap and losses.is_cuda:
+        allreduce_grads_overlapped_(handle, losses, group)
+    else:
+        allreduce_sum_([handle.grads_tensor(), losses], group)
     handle.apply_clip_adam(lr)
     return losses, state
 

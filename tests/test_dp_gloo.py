@@ -32,7 +32,20 @@ def _worker(rank, world, port, out):
                                             loss_scale_rows=B * T)
     flat = torch.from_numpy(so.flatten(cfg, grads, np.float64))
     lt = torch.tensor(losses, dtype=torch.float64)
+    # the segment-wise reduction the overlapped GPU step uses (output layer first, then the layers top down) must
+    # give the same sums as one all-reduce of the whole vector
+    flat2, lt2 = flat.clone(), lt.clone()
+    spec = so.param_spec(cfg)
+    sizes = [int(np.prod(s)) for _, s in spec]
+    offs = np.concatenate([[0], np.cumsum(sizes)])
+    head = int(offs[2])                                   # output_w, output_b; then (Matrix, Bias) per lstm layer
+    segs = [(cfg.num_layers, 0, head)] + [(l, int(offs[2 + 2 * l]), int(offs[4 + 2 * l] - offs[2 + 2 * l]))
+                                          for l in range(cfg.num_layers - 1, -1, -1)]
+    assert sum(c for _, _, c in segs) == flat.numel()
+    seen = []
+    dp.reduce_segments_(flat2, segs, lt2, before_segment=seen.append)
     dp.allreduce_sum_([flat, lt])
+    assert seen == [2, 1, 0] and torch.equal(flat, flat2) and torch.equal(lt, lt2)
     if rank == 0:
         full_l, full_g, _, _ = so.loss_and_grads(cfg, params, x, y, s0, mask)
         np.save(out, np.array([np.max(np.abs(flat.numpy() - so.flatten(cfg, full_g, np.float64))),
