@@ -7,6 +7,8 @@ computes its share of the mean loss and of the gradient (`loss_rows` = B_global 
 gradient is summed across ranks with one all-reduce, and every rank applies the identical clip + Adam.
 Sampling shards sketches with no communication at all.
 """
+import os
+
 import torch
 import torch.distributed as dist
 
@@ -84,7 +86,7 @@ def dp_train_step(handle, x_shard, y_shard, state, lr, seed, row0, global_rows, 
         e1.record()
         e1.synchronize()
         timing["allreduce_ms"] = timing.get("allreduce_ms", 0.0) + e0.elapsed_time(e1)
-    elif multi and overlap and losses.is_cuda:
+    elif multi and overlap and losses.is_cuda and os.environ.get("SKRNN_DP_OVERLAP", "1") != "0":
         allreduce_grads_overlapped_(handle, losses, group)
     else:
         allreduce_sum_([handle.grads_tensor(), losses], group)

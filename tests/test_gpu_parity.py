@@ -581,3 +581,37 @@ def test_in_kernel_dropout_keep_rate_and_independence(precision):
     assert np.abs(ratios[0] - ratios[1]).max() > 1e-3       # and a new seed draws new masks
     c = np.corrcoef(ratios[0], ratios[1])[0, 1]
     assert abs(c) < 0.5, c                                  # seeds are not correlated unit by unit
+
+
+@pytest.mark.parametrize("model,precision,H,L", [("lstm", "bf16", 256, 3), ("gru", "f32", 32, 2), ("rnn", "bf16", 64, 2)])
+def test_gradient_segments_and_their_events(model, precision, H, L):
+    """skrnn_grad_segment / skrnn_stream_wait_grad (the hooks of the overlapped data-parallel all-reduce): the
+    segments tile the flat gradient in the order the backward pass finishes them, and a stream that waits for a
+    segment's event reads that segment's final values although it never synchronised with the compute stream."""
+    import torch
+    cfg, params, x, y, s0, _ = _case(model, H, L, 4, 40, 6)
+    h = make_handle(cfg, params, 40, 6, precision=precision)
+    segs = h.grad_segments()
+    assert [s[0] for s in segs] == [L] + list(range(L - 1, -1, -1))
+    cover = sorted((o, c) for _, o, c in segs)
+    assert cover[0][0] == 0 and all(cover[i][0] + cover[i][1] == cover[i + 1][0] for i in range(L)) and \
+        cover[-1][0] + cover[-1][1] == h.P
+    names = {n: (o, int(np.prod(s))) for n, o, s in h.tensors()}
+    o, c = [(o, c) for i, o, c in segs if i == L][0]
+    assert o == names["rnn_mdn/output_w"][0] and o + c == names["rnn_mdn/output_b"][0] + names["rnn_mdn/output_b"][1]
+    side = torch.cuda.Stream()
+    st = stack_state(s0)
+    for rep in range(3):
+        h.loss_grad(x, y, st, seed=rep)
+        g = h.grads_tensor()
+        parts = []
+        for idx, off, cnt in segs:
+            h.stream_wait_grad(idx, side)
+            with torch.cuda.stream(side):
+                parts.append((off, g[off:off + cnt].clone()))
+        side.synchronize()
+        torch.cuda.synchronize()
+        final = g.cpu().numpy()
+        for off, part in parts:
+            assert np.array_equal(part.cpu().numpy(), final[off:off + part.numel()]), (rep, off)
+    h.close()
