@@ -110,7 +110,7 @@ int alloc_f32_acts(skrnn_handle *h) {
 int ensure_workspace(skrnn_handle *h, int B, int T) {
   const int64_t rows = (int64_t)B * T;
   SkWorkspace &w = h->ws;
-  if (rows <= w.cap_rows) return 0;
+  if (rows <= w.cap_rows && (w.bptt_carry == nullptr || B <= w.carry_B)) return 0;
   SK_CUDA(cudaDeviceSynchronize());
   free_workspace(w);
   SK_CUDA(cudaMalloc(&w.x_tm, rows * 5 * sizeof(float)));
@@ -137,6 +137,12 @@ int ensure_workspace(skrnn_handle *h, int B, int T) {
     }
   }
   w.cap_rows = rows;
+  if (h->cfg.precision == SKRNN_PREC_BF16 && h->cfg.cell == SKRNN_CELL_LSTM) {
+    cudaFree(w.bptt_carry);
+    w.bptt_carry = nullptr;
+    SK_CUDA(cudaMalloc(&w.bptt_carry, (size_t)2 * B * h->H * sizeof(float)));
+    w.carry_B = B;
+  }
   if (needs_f32_acts_upfront(h)) SK_TRY(alloc_f32_acts(h));
   return 0;
 }
@@ -188,6 +194,9 @@ int bias_grad(skrnn_handle *h, cudaStream_t st, Op d, int64_t rows, int cols, fl
   return sk_colsum(h, st, d.f, rows, cols, d.ldf, out);
 }
 
+// first step of time range c when T steps are cut into C ranges (even, so that barrier parities follow t)
+int range_begin(int T, int C, int c) { return c >= C ? T : (int)((int64_t)T * c / C) & ~1; }
+
 // forward unroll of the whole stack + output projection (model.py:97-99)
 int run_forward(skrnn_handle *h, cudaStream_t st, int B, int T, const float *x, const float *state_in,
                 float *state_out, const float *mask, uint64_t seed, int row0, bool training, bool want_logits = true) {
@@ -218,6 +227,36 @@ int run_forward(skrnn_handle *h, cudaStream_t st, int B, int T, const float *x, 
       SK_TRY(gemm(h, st, (int)R, 2 * H, lp.I, Xo, true, weight(h, l, 0), true, h->ws.xw[l], G, h->params + lp.b[0], false));
       SK_TRY(gemm(h, st, (int)R, H, lp.I, Xo, true, weight(h, l, 1), true, h->ws.xw[l] + 2 * H, G, h->params + lp.b[1], false));
     } else {
+      const int C = (h->ws.xw_il[l] != nullptr && h->wx_il[l] != nullptr) ? sk_rnn_tc_ranges(h, B, T) : 1;
+      if (C > 1) {
+        // The layer in C time ranges: the projection of range c runs on the side stream as soon as the layer below
+        // has produced that range, i.e. next to the recurrence of the layer below (whose clusters leave a quarter of
+        // the SMs free), and this layer's recurrent launch for range c only waits for its own projection.
+        const int ip = (lp.I + 7) / 8 * 8;
+        h->xw_il_ok[l] = true;
+        if (l == 0) SK_CUDA(cudaEventRecord(h->ev_main[0], st));  // x8_bf and the weight copies are ready
+        for (int c = 0; c < C; ++c) {
+          const int t0 = range_begin(T, C, c), t1 = range_begin(T, C, c + 1);
+          SK_CUDA(cudaStreamWaitEvent(h->side, l == 0 ? h->ev_main[0] : h->ev_chunk[1][c], 0));
+          SK_TRY(sk_gemm_tc_bf16out(h, h->side, (t1 - t0) * B, G, ip, Xo.b + (size_t)t0 * B * Xo.ldb, Xo.ldb, h->wx_il[l], G,
+                                    h->ws.xw_il[l] + (size_t)t0 * B * G, G, h->bias_il[l]));
+          SK_CUDA(cudaEventRecord(h->ev_chunk[0][c], h->side));
+        }
+        for (int c = 0; c < C; ++c) {
+          SK_CUDA(cudaStreamWaitEvent(st, h->ev_chunk[0][c], 0));
+          h->chunk_t0 = range_begin(T, C, c);
+          h->chunk_t1 = range_begin(T, C, c + 1);
+          const int rc = sk_rnn_forward_layer(h, st, l, B, T, x, state_in + (size_t)l * B * h->S,
+                                              state_out + (size_t)l * B * h->S, mask, seed, row0, training);
+          h->chunk_t0 = h->chunk_t1 = 0;
+          SK_TRY(rc);
+          SK_CHECK(h->fwd_family[l] == 1, "layer %d: the tcgen05 recurrent kernels declined a time range", l);
+          SK_CUDA(cudaEventRecord(h->ev_chunk[1][c], st));
+        }
+        h->fwd_ranges[l] = C;
+        continue;
+      }
+      h->fwd_ranges[l] = 1;
       if (sk_rnn_tc_eligible(h) && h->ws.xw_il[l] != nullptr && h->wx_il[l] != nullptr) {
         // tcgen05 lstm kernels: bf16 projection with the four gates of a unit adjacent (half the bytes of the fp32 one)
         const int ip = (lp.I + 7) / 8 * 8;
@@ -344,7 +383,8 @@ int skrnn_create(const skrnn_config *cfg, skrnn_handle **out) {
       }
     }
   }
-  if (cudaStreamCreateWithFlags(&h->side, cudaStreamNonBlocking) != cudaSuccess) {
+  if (cudaStreamCreateWithFlags(&h->side, cudaStreamNonBlocking) != cudaSuccess ||
+      cudaStreamCreateWithFlags(&h->side2, cudaStreamNonBlocking) != cudaSuccess) {
     sk_set_error("skrnn_create: cudaStreamCreate failed");
     return fail();
   }
@@ -353,6 +393,8 @@ int skrnn_create(const skrnn_config *cfg, skrnn_handle **out) {
     cudaEventCreateWithFlags(&h->ev_side[i], cudaEventDisableTiming);
   }
   for (int i = 0; i <= h->L; ++i) cudaEventCreateWithFlags(&h->ev_grad[i], cudaEventDisableTiming);
+  for (int k = 0; k < 2; ++k)
+    for (int c = 0; c < 8; ++c) cudaEventCreateWithFlags(&h->ev_chunk[k][c], cudaEventDisableTiming);
   h->ws.wpack_floats = (int64_t)h->cluster_size * h->H * 256;
   if (cudaMalloc(&h->ws.wpack, h->ws.wpack_floats * sizeof(float)) != cudaSuccess) {
     sk_set_error("skrnn_create: cudaMalloc of weight pack failed");
@@ -398,6 +440,11 @@ void skrnn_destroy(skrnn_handle *h) {
   cudaFreeHost(h->pin_loss);
   for (int l = 0; l < SK_MAX_LAYERS; ++l) { cudaFree(h->wx_il[l]); cudaFree(h->bias_il[l]); }
   if (h->side) cudaStreamDestroy(h->side);
+  if (h->side2) cudaStreamDestroy(h->side2);
+  for (int k = 0; k < 2; ++k)
+    for (int c = 0; c < 8; ++c)
+      if (h->ev_chunk[k][c]) cudaEventDestroy(h->ev_chunk[k][c]);
+  cudaFree(h->ws.bptt_carry);
   for (int i = 0; i < 2; ++i) {
     if (h->ev_main[i]) cudaEventDestroy(h->ev_main[i]);
     if (h->ev_side[i]) cudaEventDestroy(h->ev_side[i]);
@@ -604,11 +651,41 @@ int skrnn_loss_grad(skrnn_handle *h, int32_t B, int32_t T, const float *x_dev, c
       SK_CUDA(cudaStreamWaitEvent(st, h->ev_side[buf], 0));
       side_busy[buf] = false;
     }
-    SK_TRY(sk_rnn_backward_layer(h, st, l, B, T, x_dev, dropout_mask_dev, seed, row0, true));
-    SK_TRY(flush_deferred());  // the previous layer's dW: enqueued after this layer's BPTT launch
+    const int C = (h->cfg.cell == SKRNN_CELL_LSTM && h->fwd_family[l] == 1) ? h->fwd_ranges[l] : 1;
     const Op X = layer_input(h, l);
     const Op dpre = dpre_op(h, l);
     const int I = lp.I;
+    if (C > 1) {
+      // BPTT in the forward pass's time ranges, last range first.  d(out) of the layer below for range c is a GEMM on
+      // the second side stream that runs next to this layer's BPTT of range c-1; the layer below starts its range c
+      // as soon as that GEMM is done.
+      for (int c = C - 1; c >= 0; --c) {
+        const int t0 = range_begin(T, C, c), t1 = range_begin(T, C, c + 1);
+        if (l < h->L - 1) SK_CUDA(cudaStreamWaitEvent(st, h->ev_chunk[0][c], 0));  // d(out) rows of this range
+        h->chunk_t0 = t0;
+        h->chunk_t1 = t1;
+        const int rc = sk_rnn_backward_layer(h, st, l, B, T, x_dev, dropout_mask_dev, seed, row0, true);
+        h->chunk_t0 = h->chunk_t1 = 0;
+        SK_TRY(rc);
+        if (c == C - 1) SK_TRY(flush_deferred());  // the previous layer's dW: enqueued after this layer's first BPTT launch
+        if (l > 0) {
+          SK_CUDA(cudaEventRecord(h->ev_chunk[1][c], st));
+          SK_CUDA(cudaStreamWaitEvent(h->side2, h->ev_chunk[1][c], 0));
+          SK_TRY(sk_gemm_tc(h, h->side2, (t1 - t0) * B, I, G, dpre.b + (size_t)t0 * B * G, G, true, h->wx_il[l], G, true,
+                            h->ws.dout + (size_t)t0 * B * H, H, nullptr, false));
+          SK_CUDA(cudaEventRecord(h->ev_chunk[0][c], h->side2));
+        }
+      }
+      if (overlap && l > 0) {
+        SK_CUDA(cudaEventRecord(h->ev_main[buf], st));
+        def.l = l; def.buf = buf; def.bias_done = h->bias_grad_done;
+      } else {
+        SK_TRY(wgrad(st, l, buf, h->bias_grad_done));
+      }
+      continue;
+    }
+    SK_TRY(sk_rnn_backward_layer(h, st, l, B, T, x_dev, dropout_mask_dev, seed, row0, true));
+    SK_TRY(flush_deferred());  // the previous layer's dW: enqueued after this layer's BPTT launch
     if (h->cfg.cell == SKRNN_CELL_GRU) {
       const Op dg = dpre, dc = col_offset(dpre, 2 * H);
       float *gWg = h->grads + lp.w[0], *gWc = h->grads + lp.w[1];

@@ -56,6 +56,7 @@ struct SkWorkspace {   // time-major activations for one (B, T) capacity
   int64_t cap_rows = 0;  // T*B rows allocated
   bool f32_acts = false; // xw / hprev / out are allocated for cap_rows
   int capB = 0, capT = 0;
+  int carry_B = 0;       // batch rows bptt_carry holds
   float *x_tm = nullptr;                    // [T,B,5]
   unsigned char *eoc = nullptr;             // [T,B]: x[b,t,3] > 0
   float *xw[SK_MAX_LAYERS] = {nullptr};     // [T,B,G]: input projection -> gate activations -> d(pre)
@@ -78,6 +79,7 @@ struct SkWorkspace {   // time-major activations for one (B, T) capacity
   __nv_bfloat16 *dpre_bf_buf[2] = {nullptr, nullptr}; // two copies: layer l's weight gradients overlap layer l-1's BPTT
   __nv_bfloat16 *dlogits_bf = nullptr;               // [T*B,NOUTP]
   int64_t wpack_floats = 0;
+  float *bptt_carry = nullptr;              // [2][B][H]: d(h), d(c) between the time ranges of a tcgen05 BPTT pass
   __nv_bfloat16 *partial = nullptr;         // tcgen05 BPTT: per-rank partial d(h) exchange
   int64_t partial_floats = 0;
 };
@@ -120,7 +122,8 @@ struct skrnn_handle {
   bool warned_tc_fallback = false;
   bool bias_grad_done = false;  // set by a backward recurrent kernel that accumulated d(bias) itself
   // side stream for work off the critical path of the backward pass (weight gradients), see skrnn_loss_grad
-  cudaStream_t side = nullptr;
+  cudaStream_t side = nullptr, side2 = nullptr;
+  cudaEvent_t ev_chunk[2][8] = {{nullptr}};  // [0][c]: a GEMM range is done, [1][c]: a recurrent range is done
   cudaEvent_t ev_main[2] = {nullptr, nullptr}, ev_side[2] = {nullptr, nullptr};
   // recorded by skrnn_loss_grad when a gradient segment is final: [l] = layer l's tensors, [L] = the output layer's
   cudaEvent_t ev_grad[SK_MAX_LAYERS + 1] = {nullptr};
@@ -128,9 +131,11 @@ struct skrnn_handle {
   // bias in the same order: the GEMM that produces xw_il
   __nv_bfloat16 *wx_il[SK_MAX_LAYERS] = {nullptr};
   float *bias_il[SK_MAX_LAYERS] = {nullptr};
+  int chunk_t0 = 0, chunk_t1 = 0;  // set around a recurrent-layer call that covers only steps [t0, t1) (0, 0: all of them)
   int gemm_perm_H = 0;  // set around a split-K sk_gemm_tc call whose B operand has gate-interleaved columns (d(pre) of
                         // the tcgen05 lstm kernels): the epilogue then scatters C back to TF's gate-major columns
   bool xw_il_ok[SK_MAX_LAYERS] = {false};  // this step's xw_il[l] is what the forward of layer l reads
+  int fwd_ranges[SK_MAX_LAYERS] = {0};  // time ranges the forward pass of a layer ran in (its BPTT uses the same)
   int fwd_family[SK_MAX_LAYERS] = {0};  // which kernels ran a layer's forward (0 rnn_f32, 1 rnn_tc, 3 rnn1_tc): they save
                                         // activations in different places, so the backward must be the same family
   // optional per-category kernel timing (skrnn_profile_*): CUDA events around every launch
@@ -190,6 +195,7 @@ int sk_make_tmap(CUtensorMap *m, int elem_bytes, const void *ptr, int rank, cons
 // the tcgen05 recurrent kernels never touch it, so it is allocated on first use (api.cu).
 int sk_ensure_f32_acts(skrnn_handle *h);
 bool sk_rnn_tc_eligible(const skrnn_handle *h);
+int sk_rnn_tc_ranges(const skrnn_handle *h, int B, int T);
 // tcgen05 recurrent kernels (rnn_tc.cu): return 0 ok, <0 "not eligible, use the fp32 kernels", >0 error
 int sk_rnn_tc_layer(skrnn_handle *h, cudaStream_t st, bool bwd, int l, int B, int T, const float *x_bt5,
                     const float *state_in, float *state_out, const float *mask, uint64_t seed, int row0,

@@ -85,6 +85,10 @@ struct TcRnnArgs {
   int mcast;              // forward: the h tile arrives by TMA multicast (each rank fetches 1/CS of it)
   int a_tmem;             // forward: weights live in tensor memory (wimg is plain row-major [128][nkb*64] bf16)
   int debug;              // SKRNN_TC_DEBUG=1: one CTA prints its per-phase cycle split
+  // time range of this launch (two-half-tile kernels): steps [t0, t1) of the T-step unroll, t0 even.  A layer may be
+  // run as several launches so that the GEMMs around it overlap the neighbouring ranges (api.cu)
+  int t0, t1;
+  float *carry;           // [2][B][H] fp32: d(h), d(c) handed from one BPTT range to the next
 };
 
 // Staging planes are [N columns][32 units] fp32 with the TMA 128B swizzle: element (c, u) sits at byte
@@ -467,6 +471,7 @@ lstm_fwd_pp_kernel(const __grid_constant__ CUtensorMap tm_h, const __grid_consta
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   uint8_t *gbase = smem_raw + (base - smem_u32(smem_raw));
   const int H = a.H, B = a.B, T = a.T, nkb = a.nkb, CS = a.CS;
+  const int t0 = a.t0, t1 = a.t1;  // this launch runs steps [t0, t1); t0 is even, so barrier parities follow t
   const uint32_t h_bytes = (uint32_t)nkb * (N2 * 128), xw_bytes = (uint32_t)N2 * 256u, hst_bytes = (uint32_t)N2 * 64u;
   const uint32_t s_h = base;                       // [2] x nkb x [N2 rows][128 B]
   const uint32_t s_xw = s_h + 2 * h_bytes;         // [2] x [N2][32 units][4 gates] bf16: hoisted x*Wx+b
@@ -509,11 +514,15 @@ lstm_fwd_pp_kernel(const __grid_constant__ CUtensorMap tm_h, const __grid_consta
         const int b = b0 + s * N2 + cb + 4 * it;
         cst[s][it] = 0.f;
         if (b < B) {
-          const float ci = a.state_in[(size_t)b * S + uo];
-          const float hi = a.state_in[(size_t)b * S + H + uo];
-          cst[s][it] = ci;
-          a.cprev[(size_t)b * H + uo] = ci;
-          a.hprev_bf[(size_t)b * H + uo] = __float2bfloat16_rn(hi);
+          if (t0 == 0) {
+            const float ci = a.state_in[(size_t)b * S + uo];
+            const float hi = a.state_in[(size_t)b * S + H + uo];
+            cst[s][it] = ci;
+            a.cprev[(size_t)b * H + uo] = ci;
+            a.hprev_bf[(size_t)b * H + uo] = __float2bfloat16_rn(hi);
+          } else {  // a later range of the same unroll: the previous launch left c and h of step t0 in the records
+            cst[s][it] = a.cprev[((size_t)t0 * B + b) * H + uo];
+          }
         }
       }
     }
@@ -567,18 +576,18 @@ lstm_fwd_pp_kernel(const __grid_constant__ CUtensorMap tm_h, const __grid_consta
       };
       auto retire = [&](int s, int t) {  // the elementwise pass of (s, t) is over: refill its planes
         mbar_wait(bar_epi + 8 * s, t & 1);
-        if (t + 1 < T) load_xw(s, t + 1);
+        if (t + 1 < t1) load_xw(s, t + 1);
       };
-      load_xw(0, 0);
-      load_xw(1, 0);
-      for (int t = 0; t < T; ++t) {
-        if (t > 0) mbar_wait_cluster(bar_ready + 0, (t - 1) & 1);
+      load_xw(0, t0);
+      load_xw(1, t0);
+      for (int t = t0; t < t1; ++t) {
+        if (t > t0) mbar_wait_cluster(bar_ready + 0, (t - 1) & 1);
         TCR_LAP(tk[8]);
         load_h(0, t);
         TCR_LAP(tk[9]);
-        if (t > 0) retire(1, t - 1);
+        if (t > t0) retire(1, t - 1);
         TCR_LAP(tk[10]);
-        if (t > 0) mbar_wait_cluster(bar_ready + 8, (t - 1) & 1);
+        if (t > t0) mbar_wait_cluster(bar_ready + 8, (t - 1) & 1);
         TCR_LAP(tk[11]);
         load_h(1, t);
         TCR_LAP(tk[12]);
@@ -598,7 +607,7 @@ lstm_fwd_pp_kernel(const __grid_constant__ CUtensorMap tm_h, const __grid_consta
       if (dbg) lapt = (uint32_t)clock();
       const uint32_t idesc = make_idesc_bf16(128, N2, false, false);
       const uint64_t dB0 = make_desc(s_h, 0, 1024);
-      for (int t = 0; t < T; ++t) {
+      for (int t = t0; t < t1; ++t) {
 #pragma unroll
         for (int s = 0; s < 2; ++s) {
           mbar_wait(bar_h + 8 * s, t & 1);
@@ -632,7 +641,7 @@ lstm_fwd_pp_kernel(const __grid_constant__ CUtensorMap tm_h, const __grid_consta
       const bool dbg = dbg0 && lane == 0;
       uint32_t lapt = 0;
       if (dbg) lapt = (uint32_t)clock();
-      for (int t = 0; t + 1 < T; ++t) {
+      for (int t = t0; t < t1 && t + 1 < T; ++t) {  // (the last step of a range still stores h for the next launch)
 #pragma unroll
         for (int s = 0; s < 2; ++s) {
           mbar_wait(bar_epi + 8 * s, t & 1);  // the staging tile of (s, t) is complete (writers fenced it for the async proxy)
@@ -669,10 +678,10 @@ lstm_fwd_pp_kernel(const __grid_constant__ CUtensorMap tm_h, const __grid_consta
     const float *init_p = a.state_in + (size_t)(b0 + cb) * S + uo;
     const int H4 = 4 * H;
     const size_t BH = (size_t)B * H, half_off = (size_t)N2 * H;
-    __nv_bfloat16 *o_p = a.out_bf + (size_t)(b0 + cb) * H + uo;        // out[t], half 0
-    uint2 *act_g = reinterpret_cast<uint2 *>(a.acts_bf) + (size_t)(b0 + cb) * H + uo;  // activation record of step t
-    float *c_p = a.cprev + ((size_t)B + b0 + cb) * H + uo;             // cprev[t+1]
-    const unsigned char *eoc_p = a.eoc + b0 + cb;                       // eoc[t]
+    __nv_bfloat16 *o_p = a.out_bf + ((size_t)t0 * B + b0 + cb) * H + uo;        // out[t], half 0
+    uint2 *act_g = reinterpret_cast<uint2 *>(a.acts_bf) + ((size_t)t0 * B + b0 + cb) * H + uo;  // activation record of step t
+    float *c_p = a.cprev + ((size_t)(t0 + 1) * B + b0 + cb) * H + uo;           // cprev[t+1]
+    const unsigned char *eoc_p = a.eoc + (size_t)t0 * B + b0 + cb;               // eoc[t]
     const uint32_t drop_unit = skm_drop_unit(a.seed, (uint32_t)uo);
     const float inv_keep = 1.0f / a.keep;
     uint32_t eoc_next = 0;  // flags of the half step about to be processed
@@ -681,7 +690,7 @@ lstm_fwd_pp_kernel(const __grid_constant__ CUtensorMap tm_h, const __grid_consta
       if (((valid[0] >> it) & 1u) && __ldg(eoc_p + 4 * it)) eoc_next |= 1u << it;
     uint32_t lapt = 0;
     if (dbg) lapt = (uint32_t)clock();
-    for (int t = 0; t < T; ++t) {
+    for (int t = t0; t < t1; ++t) {
       const bool more = t + 1 < T;
 #pragma unroll
       for (int s = 0; s < 2; ++s) {
@@ -1102,6 +1111,7 @@ lstm_bwd_pp_kernel(const __grid_constant__ CUtensorMap tm_acts, const __grid_con
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   uint8_t *gbase = smem_raw + (base - smem_u32(smem_raw));
   const int H = a.H, B = a.B, T = a.T, CS = a.CS;
+  const int t0 = a.t0, t1 = a.t1;  // this launch differentiates steps t1-1 .. t0
   const int nmt = (H + 127) / 128;
   const int HP = nmt * 128;
   const uint32_t half_bytes = (uint32_t)N2 * 768u;  // per half: d(pre) operand 256 B/row, activations 256, d(out) 128, c 128
@@ -1164,9 +1174,9 @@ lstm_bwd_pp_kernel(const __grid_constant__ CUtensorMap tm_acts, const __grid_con
         tma_load_3d(hb + o_do, &tm_do, bar_in + 8 * s, u0, b0 + s * N2, t);
         tma_load_3d(hb + o_cp, &tm_cp, bar_in + 8 * s, u0, b0 + s * N2, t);
       };
-      load_in(0, T - 1);
-      load_in(1, T - 1);
-      for (int t = T - 1, step = 0; t >= 0; --t, ++step) {
+      load_in(0, t1 - 1);
+      load_in(1, t1 - 1);
+      for (int t = t1 - 1, step = 0; t >= t0; --t, ++step) {
 #pragma unroll
         for (int s = 0; s < 2; ++s) {
           mbar_wait(bar_epi + 8 * s, step & 1);  // the elementwise pass of (s, t) has consumed its tiles
@@ -1174,7 +1184,7 @@ lstm_bwd_pp_kernel(const __grid_constant__ CUtensorMap tm_acts, const __grid_con
           const uint32_t sb = s_half + s * half_bytes + o_b;
           tma_store_3d(&tm_dp, sb, 128 * rank, b0 + s * N2, t);
           tma_store_3d(&tm_dp, sb + (uint32_t)(N2 * 128), 128 * rank + 64, b0 + s * N2, t);
-          if (t > 0) {
+          if (t > t0) {
             tma_store_wait_read();  // the pass of (s, t-1) rewrites the operand tile once it has its inputs
             load_in(s, t - 1);
           }
@@ -1187,7 +1197,7 @@ lstm_bwd_pp_kernel(const __grid_constant__ CUtensorMap tm_acts, const __grid_con
     // ---------------- MMA issuer ----------------
     if (elect_one()) {
       const uint32_t idesc = make_idesc_bf16(128, N2, false, false);
-      for (int t = T - 1, step = 0; t > 0; --t, ++step) {
+      for (int t = t1 - 1, step = 0; t >= t0 && t > 0; --t, ++step) {
 #pragma unroll
         for (int s = 0; s < 2; ++s) {
           mbar_wait(bar_epi + 8 * s, step & 1);
@@ -1211,7 +1221,7 @@ lstm_bwd_pp_kernel(const __grid_constant__ CUtensorMap tm_acts, const __grid_con
     __syncwarp();
   } else if (warp == 2 + TCR_EPI_WARPS) {
     // ---------------- publisher ----------------
-    for (int t = T - 1, step = 0; t > 0; --t, ++step) {
+    for (int t = t1 - 1, step = 0; t >= t0 && t > 0; --t, ++step) {
 #pragma unroll
       for (int s = 0; s < 2; ++s) {
         mbar_wait(bar_rd + 8 * s, step & 1);  // this CTA's partial stores of (s, t) happen before this
@@ -1239,6 +1249,18 @@ lstm_bwd_pp_kernel(const __grid_constant__ CUtensorMap tm_acts, const __grid_con
 #pragma unroll
       for (int it = 0; it < NCH; ++it)
         if (b0 + s * N2 + c0 + 4 * it < B) valid[s] |= 1u << it;
+    // a range that does not end the sequence continues from the d(h), d(c) its successor in time left behind
+    float *carry_h = a.carry + (size_t)(b0 + c0) * H + uo, *carry_c = carry_h + (size_t)B * H;
+    if (t1 < T) {
+#pragma unroll
+      for (int s = 0; s < 2; ++s)
+#pragma unroll
+        for (int it = 0; it < NCH; ++it)
+          if ((valid[s] >> it) & 1u) {
+            dhc[s][it] = carry_h[(size_t)(s * N2 + 4 * it) * H];
+            dcc[s][it] = carry_c[(size_t)(s * N2 + 4 * it) * H];
+          }
+    }
     // partial exchange, per half and parity: [dst rank][src rank][column group][chunk j][unit 32][CK columns]
     constexpr int CK = CPW >= 8 ? 8 : CPW;
     constexpr int NJ = CPW / CK;
@@ -1254,7 +1276,7 @@ lstm_bwd_pp_kernel(const __grid_constant__ CUtensorMap tm_acts, const __grid_con
     uint32_t lapt = 0;
     if (dbg) lapt = (uint32_t)clock();
 
-    for (int t = T - 1, step = 0; t >= 0; --t, ++step) {
+    for (int t = t1 - 1, step = 0; t >= t0; --t, ++step) {
       const int par = step & 1;
       // ---- E_s ----
 #pragma unroll
@@ -1380,6 +1402,16 @@ lstm_bwd_pp_kernel(const __grid_constant__ CUtensorMap tm_acts, const __grid_con
         }
         TCR_LAP(tk[5]);
       }
+    }
+    if (t0 > 0) {  // hand d(h_{t0-1}), d(c_{t0-1}) to the launch that continues below t0
+#pragma unroll
+      for (int s = 0; s < 2; ++s)
+#pragma unroll
+        for (int it = 0; it < NCH; ++it)
+          if ((valid[s] >> it) & 1u) {
+            carry_h[(size_t)(s * N2 + 4 * it) * H] = dhc[s][it];
+            carry_c[(size_t)(s * N2 + 4 * it) * H] = dcc[s][it];
+          }
     }
     if (a.dbias != nullptr) {
 #pragma unroll
@@ -1519,7 +1551,55 @@ size_t smem_need(bool bwd, int H, int N, bool a_tmem) {
   return s + 1024 + 256;
 }
 
+struct TcPlan { int N; bool a_tmem, mcast_ok, pp; int pp_fwd_env, pp_bwd_env; };
+
+// batch tile and kernel variant of a layer pass at batch B
+TcPlan tc_plan(const skrnn_handle *h, bool bwd, int B) {
+  const int H = h->H, CS = H / 32;
+  const int nkb = (H + 63) / 64, HP = (H + 127) / 128 * 128;
+  TcPlan p = {};
+  // batch tile: the smallest N whose cluster count fits on the GPU at once, within shared memory / TMEM
+  static int atm_env = -1;
+  if (atm_env < 0) { const char *e = getenv("SKRNN_TC_ATMEM"); atm_env = (e && e[0] == '0') ? 0 : 1; }
+  const bool a_tmem = !bwd && atm_env;
+  int N = 0;
+  const int cap_clusters = std::max(1, h->num_sms / CS - (CS >= 8 ? 2 : 0));
+  for (int cand : {16, 32, 64, 128}) {
+    if (smem_need(bwd, H, cand, a_tmem) > 227 * 1024) break;
+    if (a_tmem && (cand + 31) / 32 * 32 + nkb * 32 > 512) break;
+    if (bwd && (HP / 128) * cand > 512) break;
+    N = cand;
+    if ((B + cand - 1) / cand <= cap_clusters) break;
+  }
+  // The two-half-tile kernels need N >= 32 (two MMA tiles of 16 columns): latency-bound small batches prefer two
+  // halves of 16 rows in flight on fewer clusters over one 16-row tile per cluster.
+  static int pp_env = -1, ppb_env = -1, mc_env = -1;
+  if (pp_env < 0) { const char *e = getenv("SKRNN_TC_PP"); pp_env = (e && e[0] == '0') ? 0 : 1; }
+  if (ppb_env < 0) { const char *e = getenv("SKRNN_TC_PP_BWD"); ppb_env = (e && e[0] == '0') ? 0 : 1; }
+  if (mc_env < 0) { const char *e = getenv("SKRNN_TC_MCAST"); mc_env = (e && e[0] == '0') ? 0 : 1; }
+  const bool mcast_ok = CS >= 2 && CS == 2 * nkb;
+  // (measured at H=512, B=100: forward 6.8 K cycles/step with 7 clusters x 16 rows vs 4.6 K with 4 clusters x 2x16;
+  // the backward pass is faster the other way round, 5.2 K vs 8.7 K, so only the forward tile is widened)
+  if (N == 16 && B > 16 && !bwd && pp_env != 0 && mcast_ok && a_tmem) N = 32;
+  p.N = N; p.a_tmem = a_tmem; p.mcast_ok = mcast_ok; p.pp_fwd_env = pp_env; p.pp_bwd_env = ppb_env;
+  p.pp = bwd ? (ppb_env && N >= 32) : (pp_env && mc_env && mcast_ok && a_tmem && N >= 32);
+  return p;
+}
+
 }  // namespace
+
+// How many time ranges a layer of this handle is run in at batch B (1 = one launch per layer and direction): ranges
+// exist to overlap the hoisted GEMMs with the recurrence, which pays when those GEMMs are long (large batch) and
+// needs the two-half-tile kernels in both directions.
+int sk_rnn_tc_ranges(const skrnn_handle *h, int B, int T) {
+  const char *e = getenv("SKRNN_TC_RANGES");  // 1 switches ranges off, n > 1 forces n (read per call: tests toggle it)
+  const int env = e ? atoi(e) : 0;
+  if (!sk_rnn_tc_eligible(h) || h->ws.bptt_carry == nullptr) return 1;
+  if (!tc_plan(h, false, B).pp || !tc_plan(h, true, B).pp) return 1;
+  int C = env > 0 ? env : (B >= 256 ? 4 : 1);
+  while (C > 1 && (T / C < 16 || (T / C) % 2 != 0)) --C;  // ranges start on even steps and are not tiny
+  return C;
+}
 
 // Static part of the eligibility test: run_forward uses it to decide in which format it hoists x*Wx+b.
 bool sk_rnn_tc_eligible(const skrnn_handle *h) {
@@ -1540,29 +1620,15 @@ int sk_rnn_tc_layer(skrnn_handle *h, cudaStream_t st, bool bwd, int l, int B, in
   if (!bwd && (!h->xw_il_ok[l] || h->ws.xw_il[l] == nullptr)) return -1;  // the projection was hoisted in the fp32 format
   const int CS = H / 32;
   const int nkb = (H + 63) / 64, HP = (H + 127) / 128 * 128;
-  // batch tile: the smallest N whose cluster count fits on the GPU at once, within shared memory / TMEM
-  static int atm_env = -1;
-  if (atm_env < 0) { const char *e = getenv("SKRNN_TC_ATMEM"); atm_env = (e && e[0] == '0') ? 0 : 1; }
-  const bool a_tmem = !bwd && atm_env;
-  int N = 0;
-  const int cap_clusters = std::max(1, h->num_sms / CS - (CS >= 8 ? 2 : 0));
-  for (int cand : {16, 32, 64, 128}) {
-    if (smem_need(bwd, H, cand, a_tmem) > 227 * 1024) break;
-    if (a_tmem && (cand + 31) / 32 * 32 + nkb * 32 > 512) break;
-    if (bwd && (HP / 128) * cand > 512) break;
-    N = cand;
-    if ((B + cand - 1) / cand <= cap_clusters) break;
-  }
+  const TcPlan plan = tc_plan(h, bwd, B);
+  const int N = plan.N;
+  const bool a_tmem = plan.a_tmem, mcast_ok = plan.mcast_ok;
+  const int pp_env = plan.pp_fwd_env, ppb_env = plan.pp_bwd_env;
   if (N == 0) return -1;
-  // The two-half-tile kernels need N >= 32 (two MMA tiles of 16 columns): latency-bound small batches prefer two
-  // halves of 16 rows in flight on fewer clusters over one 16-row tile per cluster.
-  static int pp_env = -1, ppb_env = -1;
-  if (pp_env < 0) { const char *e = getenv("SKRNN_TC_PP"); pp_env = (e && e[0] == '0') ? 0 : 1; }
-  if (ppb_env < 0) { const char *e = getenv("SKRNN_TC_PP_BWD"); ppb_env = (e && e[0] == '0') ? 0 : 1; }
-  const bool mcast_ok = CS >= 2 && CS == 2 * nkb;
-  // (measured at H=512, B=100: forward 6.8 K cycles/step with 7 clusters x 16 rows vs 4.6 K with 4 clusters x 2x16;
-  // the backward pass is faster the other way round, 5.2 K vs 8.7 K, so only the forward tile is widened)
-  if (N == 16 && B > 16 && !bwd && pp_env != 0 && mcast_ok && a_tmem) N = 32;
+  // a time range [t0, t1) of the unroll (api.cu splits a layer into ranges to overlap the GEMMs around it)
+  const int t0 = (h->chunk_t1 > h->chunk_t0) ? h->chunk_t0 : 0, t1 = (h->chunk_t1 > h->chunk_t0) ? h->chunk_t1 : T;
+  const bool ranged = t0 != 0 || t1 != T;
+  SK_CHECK(!ranged || (plan.pp && t0 % 2 == 0 && t0 >= 0 && t1 <= T), "tcgen05 recurrent kernels: time range [%d,%d) not supported here", t0, t1);
   const int nclusters = (B + N - 1) / N;
   const size_t smem = smem_need(bwd, H, N, a_tmem);
   const int img_bytes = bwd ? 2 * HP * 128 : nkb * 16384;
@@ -1582,6 +1648,9 @@ int sk_rnn_tc_layer(skrnn_handle *h, cudaStream_t st, bool bwd, int l, int B, in
   int tc = 32;
   while (tc < cols) tc <<= 1;
   a.tmem_cols = tc;
+  a.t0 = t0; a.t1 = t1;
+  a.carry = h->ws.bptt_carry;
+  SK_CHECK(!ranged || !bwd || a.carry != nullptr, "BPTT time ranges need the carry buffer");
   a.row0 = row0;
   a.dropout = (training && l == h->L - 1 && h->cfg.keep_prob < 1.0f) ? 1 : 0;
   a.keep = h->cfg.keep_prob;

@@ -615,3 +615,32 @@ def test_gradient_segments_and_their_events(model, precision, H, L):
         for off, part in parts:
             assert np.array_equal(part.cpu().numpy(), final[off:off + part.numel()]), (rep, off)
     h.close()
+
+
+def test_bf16_lstm_time_ranges_match_single_launch(monkeypatch):
+    """Large batches run every LSTM layer as several launches over consecutive time ranges (so that the hoisted GEMMs
+    overlap the neighbouring ranges' recurrence).  The ranged step must reproduce the single-launch step: same
+    forward state bit for bit, same losses, gradients equal up to the summation order of the weight-gradient GEMMs;
+    and both sit within the bf16 tolerance of the oracle."""
+    cfg, params, x, y, s0, mask = _case("lstm", 512, 2, 4, 260, 66, seed=5)
+    x[::5, 33, 2:5] = [0, 1, 0]   # eoc right at a range boundary region
+    losses_ref, grads_ref, fstate_ref, _ = so.loss_and_grads(
+        cfg, f64(params), x.astype(np.float64), y.astype(np.float64),
+        [s.astype(np.float64) for s in s0], mask.astype(np.float64))
+    res = {}
+    for ranges in ("1", "3"):
+        monkeypatch.setenv("SKRNN_TC_RANGES", ranges)
+        h = make_handle(cfg, params, 260, 66, precision="bf16")
+        losses, state_out = h.loss_grad(x, y, stack_state(s0), dropout_mask=mask)
+        res[ranges] = (losses.cpu().numpy(), state_out.cpu().numpy(), h.get_params_dict(h.grads_tensor().cpu().numpy()),
+                       h.launch_count())
+        h.close()
+    assert res["3"][3] > res["1"][3], "the ranged run did not launch more kernels: ranges were not taken"
+    assert np.array_equal(res["1"][1], res["3"][1])
+    assert np.allclose(res["1"][0], res["3"][0], rtol=1e-6)
+    for n in grads_ref:
+        assert rel_err(res["3"][2][n], res["1"][2][n]) < 1e-3, n
+        assert rel_err(res["3"][2][n], grads_ref[n]) < BF16_TOL, n
+    for i in range(3):
+        assert abs(res["3"][0][i] - losses_ref[i]) <= BF16_TOL * abs(losses_ref[i])
+    assert rel_err(res["3"][1], np.stack(fstate_ref, 0)) < BF16_TOL
