@@ -50,6 +50,7 @@ def train(args):
 
     model = Model(args)
     b_processed = 0
+    batch_times = []  # addition: the log line keeps the reference's two decimals, the run's mean is printed at the end
 
     with Session(model) as sess:
         saver = Saver(model)
@@ -70,6 +71,7 @@ def train(args):
                 train_loss, shape_loss, pen_loss, state, _ = sess.run(
                     [model.cost, model.cost_shape, model.cost_pen, model.final_state, model.train_op], feed)
                 end = time.time()
+                batch_times.append(end - start)
                 b_processed += 1
                 print("{}/{} (epoch {} batch {}), cost = {:.2f} ({:.2f}+{:.4f}), time/batch = {:.2f}"
                       .format(data_loader.pointer + e * data_loader.num_samples,
@@ -80,8 +82,19 @@ def train(args):
                     save_model()
                 if args.max_batches and b_processed >= args.max_batches:
                     save_model()
+                    report_time(args, batch_times)
                     return
         save_model()
+        report_time(args, batch_times)
+
+
+def report_time(args, batch_times):
+    """Mean of the reference's timed region (next_batch + the step, train.py:83-87) after three warm-up batches."""
+    steady = batch_times[3:] if len(batch_times) > 6 else batch_times
+    if steady:
+        ms = 1e3 * sum(steady) / len(steady)
+        print("mean time/batch = {:.3f} ms over {} batches ({:.0f} stroke-steps/s)".format(
+            ms, len(steady), args.batch_size * args.seq_length / (ms * 1e-3)))
 
 
 if __name__ == '__main__':
