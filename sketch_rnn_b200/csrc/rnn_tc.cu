@@ -1588,15 +1588,19 @@ TcPlan tc_plan(const skrnn_handle *h, bool bwd, int B) {
 
 }  // namespace
 
-// How many time ranges a layer of this handle is run in at batch B (1 = one launch per layer and direction): ranges
-// exist to overlap the hoisted GEMMs with the recurrence, which pays when those GEMMs are long (large batch) and
-// needs the two-half-tile kernels in both directions.
+// How many time ranges a layer of this handle is run in at batch B (1 = one launch per layer and direction).  Ranges
+// let the hoisted GEMMs of a range run next to the neighbouring range's recurrence (api.cu); they need the
+// two-half-tile kernels in both directions.  MEASURED at config 4 (lstm H512 L3 B800 T300): 15.4 ms with 1 range,
+// 15.8 / 15.9 / 15.6 ms with 2 / 4 / 6 -- the GEMMs do leave the critical path, but a GEMM on the 36 free SMs takes
+// L2 bandwidth from the recurrent kernels' exchange and slows them by more than it saves (forward 4.4 -> 5.2 ms, BPTT
+// 7.5 -> 8.6 ms).  So the default is 1; SKRNN_TC_RANGES=n turns ranges on (kept, with its parity test, for GPUs or
+// shapes where the balance differs).
 int sk_rnn_tc_ranges(const skrnn_handle *h, int B, int T) {
   const char *e = getenv("SKRNN_TC_RANGES");  // 1 switches ranges off, n > 1 forces n (read per call: tests toggle it)
   const int env = e ? atoi(e) : 0;
   if (!sk_rnn_tc_eligible(h) || h->ws.bptt_carry == nullptr) return 1;
   if (!tc_plan(h, false, B).pp || !tc_plan(h, true, B).pp) return 1;
-  int C = env > 0 ? env : (B >= 256 ? 4 : 1);
+  int C = env > 0 ? env : 1;
   while (C > 1 && (T / C < 16 || (T / C) % 2 != 0)) --C;  // ranges start on even steps and are not tiny
   return C;
 }
