@@ -12,5 +12,6 @@ x, y = utils.synthetic_batch(B, T, seed=1)
 st = torch.zeros((L, B, h.S), device="cuda")
 for i in range(2):
     losses, _ = h.loss_grad(x, y, st, seed=i)
+    h.apply_clip_adam(0.005)
 torch.cuda.synchronize()
 print("loss", losses.cpu().numpy())
