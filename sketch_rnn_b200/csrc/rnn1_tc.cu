@@ -33,9 +33,9 @@ namespace {
 
 constexpr int R1_N = 16;          // batch rows per CTA (MMA N)
 constexpr int R1_NR = 8;          // of which one elementwise thread handles 8 (for its unit): two warps per (m-tile, lane quarter)
-constexpr int R1_EPI_WARPS = 16;
-constexpr int R1_THREADS = 32 * (R1_EPI_WARPS + 1);
 constexpr int R1_MAX_TILES = 6;
+// threads of a CTA with MU m-tiles of hidden units: 8 elementwise warps per m-tile, then the MMA warp
+__host__ __device__ constexpr int r1_threads(int mu) { return 32 * (8 * mu + 1); }
 
 struct R1Tile {   // one 128-row weight tile (MMA A operand), K = 64 * nkb
   int in_tmem;    // 1: tensor memory at column `off`; 0: shared memory at byte offset `off`
@@ -61,6 +61,7 @@ struct R1Args {
   const float *dout;         // [T,B,H] fp32
   float *dbias0, *dbias1;
   const uint8_t *wimg;
+  int wimg_rank_bytes;       // cluster of 2: each rank's tiles are a separate image
   int debug;                 // SKRNN_TC_DEBUG=1: CTA 0 prints its per-phase cycle split
   int pf_dist, pf_l1;        // prefetch distance in steps, and whether it targets L1 (else L2)
 };
@@ -87,21 +88,21 @@ __device__ __forceinline__ R1Smem r1_smem(uint8_t *raw, int w_bytes, int b1_byte
 
 // resident weights: shared-memory tiles are straight copies of their pre-swizzled images, tensor-memory tiles are
 // written row by row (lane = row) with tcgen05.st
-__device__ __forceinline__ void r1_load_smem_tiles(const R1Args &a, const R1Smem &s, int tid) {
+__device__ __forceinline__ void r1_load_smem_tiles(const R1Args &a, const uint8_t *wimg, const R1Smem &s, int tid, int nthreads) {
   for (int j = 0; j < a.ntiles; ++j) {
     if (a.tile[j].in_tmem) continue;
-    const uint4 *src = reinterpret_cast<const uint4 *>(a.wimg + a.tile[j].img);
+    const uint4 *src = reinterpret_cast<const uint4 *>(wimg + a.tile[j].img);
     uint4 *dst = reinterpret_cast<uint4 *>(s.gen + a.tile[j].off);
-    for (int i = tid; i < a.tile[j].nkb * 1024; i += R1_THREADS) dst[i] = __ldg(src + i);
+    for (int i = tid; i < a.tile[j].nkb * 1024; i += nthreads) dst[i] = __ldg(src + i);
   }
 }
-__device__ __forceinline__ void r1_load_tmem_tiles(const R1Args &a, uint32_t tmem_base, int warp, int lane) {
+__device__ __forceinline__ void r1_load_tmem_tiles(const R1Args &a, const uint8_t *wimg, uint32_t tmem_base, int warp, int lane) {
   if (warp >= 4) return;
   const int e = 32 * warp + lane;
   for (int j = 0; j < a.ntiles; ++j) {
     if (!a.tile[j].in_tmem) continue;
     const int nkb = a.tile[j].nkb;
-    const uint32_t *src = reinterpret_cast<const uint32_t *>(a.wimg + a.tile[j].img) + (size_t)e * (nkb * 32);
+    const uint32_t *src = reinterpret_cast<const uint32_t *>(wimg + a.tile[j].img) + (size_t)e * (nkb * 32);
     for (int cb = 0; cb < nkb; ++cb) {
       uint32_t v[32];
 #pragma unroll
@@ -150,8 +151,9 @@ __device__ __forceinline__ void r1_issue(uint32_t acc, const R1A &A, uint64_t dB
 
 // the operand tile at s_b (nkb k-blocks of [R1_N rows][64 bf16], 128B-swizzled) -> columns [col0, col0 + 64*nkb) of rows
 // [b0, b0 + R1_N) at step t of a [T,B,ld] bf16 array (rows past B are clipped by the tensor map)
-__device__ __forceinline__ void r1_store_tile(const CUtensorMap *tm, uint32_t s_b, int nkb, int col0, int b0, int t) {
-  for (int kb = 0; kb < nkb; ++kb) tma_store_3d(tm, s_b + (uint32_t)kb * (R1_N * 128), col0 + 64 * kb, b0, t);
+// (k-blocks [kb_lo, kb_hi) of the tile: in a cluster each CTA stores the blocks of its own units)
+__device__ __forceinline__ void r1_store_tile(const CUtensorMap *tm, uint32_t s_b, int kb_lo, int kb_hi, int col0, int b0, int t) {
+  for (int kb = kb_lo; kb < kb_hi; ++kb) tma_store_3d(tm, s_b + (uint32_t)kb * (R1_N * 128), col0 + 64 * kb, b0, t);
 }
 
 // byte offset of element (row n, column k) in such a tile: per-thread part for a fixed k, then the row part
@@ -162,6 +164,76 @@ __device__ __forceinline__ void r1_sts_bf16(uint8_t *p, float v) { *reinterpret_
 
 __device__ __forceinline__ float r1_ld_bf16(const char *p) {
   return __uint_as_float((uint32_t)(*reinterpret_cast<const unsigned short *>(p)) << 16);
+}
+
+// ---- cluster of 2 (CL = 2): the hidden units are split over two CTAs, each holding the weight rows of its half in
+// tensor memory.  Both CTAs need the WHOLE operand tile (the contraction runs over all units), so an elementwise
+// thread writes its elements into both CTAs' tiles (st.shared::cluster), makes them visible to the async proxy, and
+// one lane per warp arrives (release, cluster scope) on both CTAs' operand barriers.
+__device__ __forceinline__ uint32_t r1_cluster_rank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ uint32_t r1_mapa(uint32_t addr, uint32_t rank) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(addr), "r"(rank));
+  return r;
+}
+__device__ __forceinline__ void r1_cluster_sync() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\n" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire.aligned;\n" ::: "memory");
+}
+// operand element `v` at byte offset `off` of the tile: local store (CL = 1) or one store per CTA of the cluster
+template <int CL>
+__device__ __forceinline__ void r1_put(uint8_t *gen, const uint32_t (&rem)[2], uint32_t off, float v) {
+  if constexpr (CL == 1) {
+    r1_sts_bf16(gen + off, v);
+  } else {
+    const unsigned short b = __bfloat16_as_ushort(__float2bfloat16_rn(v));
+    asm volatile("st.shared::cluster.u16 [%0], %1;" ::"r"(rem[0] + off), "h"(b) : "memory");
+    asm volatile("st.shared::cluster.u16 [%0], %1;" ::"r"(rem[1] + off), "h"(b) : "memory");
+  }
+}
+// the warp's operand elements are written: publish them to the MMA thread(s).  Barrier counts: 32 per warp (CL = 1),
+// one per warp and CTA (CL = 2)
+template <int CL>
+__device__ __forceinline__ void r1_arrive(uint32_t bar, const uint32_t (&rbar)[2], int lane) {
+  if constexpr (CL == 1) {
+    fence_proxy_async_smem();
+    mbar_arrive(bar);
+  } else {
+    fence_proxy_async();
+    __syncwarp();
+    if (lane == 0) {
+      asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(rbar[0]) : "memory");
+      asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(rbar[1]) : "memory");
+    }
+  }
+}
+// MMA thread: wait for the operand tile (all CTAs' parts of it)
+template <int CL>
+__device__ __forceinline__ void r1_wait_operand(uint32_t bar, uint32_t parity, int tag) {
+  if constexpr (CL == 1) {
+    mbar_wait_wd(bar, parity, tag, 1u << 22);
+  } else {
+    uint32_t done;
+    for (uint32_t spin = 0;; ++spin) {
+      asm volatile(
+          "{\n"
+          ".reg .pred p;\n"
+          "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n"
+          "selp.u32 %0, 1, 0, p;\n"
+          "}\n" : "=r"(done) : "r"(bar), "r"(parity) : "memory");
+      if (done) break;
+      if (spin > (1u << 22)) {
+        printf("libskrnn: operand barrier wait timed out (tag %d, parity %u, block %d)\n", tag, parity, (int)blockIdx.x);
+        __trap();
+      }
+    }
+    fence_proxy_async();
+  }
+  tc_fence_after();
 }
 
 // L2 prefetch of the 128-byte line holding (row b0 + lane, column col) of a [T,B,ld] array at step t: one instruction
@@ -206,8 +278,9 @@ __device__ __forceinline__ void r1_drop_scales(const R1Args &a, int t, int b0, i
 // ------------------------------------------------------------------------------------------------
 // forward.  CELL: 1 gru, 2 rnn
 // ------------------------------------------------------------------------------------------------
-template <int CELL, int MU, int NKB>
-__global__ void __launch_bounds__(R1_THREADS, 1)
+// MU: m-tiles (128 hidden units each) of THIS CTA; NKB: k-blocks of the contraction (all H units); CL: CTAs per cluster
+template <int CELL, int MU, int NKB, int CL>
+__global__ void __launch_bounds__(r1_threads(MU), 1)
 rnn1_fwd_kernel(const __grid_constant__ CUtensorMap tm_hp, const __grid_constant__ CUtensorMap tm_aux, R1Args a) {
   constexpr int N = R1_N;
   constexpr int NB1 = CELL == 2 ? 2 : 1;  // rnn: the h tile is double-buffered (see the store ordering below)
@@ -219,54 +292,74 @@ rnn1_fwd_kernel(const __grid_constant__ CUtensorMap tm_hp, const __grid_constant
   const uint32_t bar_op1 = s.s_bar, bar_acc1 = s.s_bar + 8, bar_op2 = s.s_bar + 16, bar_acc2 = s.s_bar + 24;
   const uint32_t tmem_holder = s.s_bar + 32;
   volatile uint32_t *tmem_holder_ptr = reinterpret_cast<volatile uint32_t *>(s.gen + (tmem_holder - s.base));
+  constexpr int EW = 8 * MU, THREADS = r1_threads(MU);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int b0 = blockIdx.x * N;
+  const int rank = CL == 1 ? 0 : (int)r1_cluster_rank();
+  const int b0 = (blockIdx.x / CL) * N;
+  const uint8_t *wimg = a.wimg + (size_t)rank * a.wimg_rank_bytes;
   __shared__ long long tk[16];
   if (tid < 16) tk[tid] = 0;
 
-  r1_load_smem_tiles(a, s, tid);
+  r1_load_smem_tiles(a, wimg, s, tid, THREADS);
   if (tid == 0) {
-    mbar_init(bar_op1, 256 * MU);
+    mbar_init(bar_op1, CL == 1 ? 32 * EW : EW * CL);
     mbar_init(bar_acc1, 1);
-    mbar_init(bar_op2, 256 * MU);
+    mbar_init(bar_op2, CL == 1 ? 32 * EW : EW * CL);
     mbar_init(bar_acc2, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
-  if (warp == R1_EPI_WARPS) tc_alloc(tmem_holder, (uint32_t)a.tmem_cols);
+  if (warp == EW) tc_alloc(tmem_holder, (uint32_t)a.tmem_cols);
   {
     uint4 *z = reinterpret_cast<uint4 *>(s.gen + (s.s_b1 - s.base));
     const int n16 = (NB1 + (CELL == 1 ? 1 : 0)) * btile / 16;
-    for (int i = tid; i < n16; i += R1_THREADS) z[i] = make_uint4(0, 0, 0, 0);
+    for (int i = tid; i < n16; i += THREADS) z[i] = make_uint4(0, 0, 0, 0);
   }
   fence_proxy_async_smem();
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
+  if constexpr (CL > 1) r1_cluster_sync();  // the peer's tiles are zeroed and its barriers initialised before anything is sent there
   const uint32_t tmem_base = *tmem_holder_ptr;
-  r1_load_tmem_tiles(a, tmem_base, warp, lane);
+  r1_load_tmem_tiles(a, wimg, tmem_base, warp, lane);
 
   constexpr int NR = R1_NR;
   const int q = warp & 3, hh = (warp >> 2) & 1, mt = warp >> 3;
   const int nb = NR * hh;  // my rows of the tile: [nb, nb + NR)
-  const bool active = warp < R1_EPI_WARPS && mt < MU;
-  const int unit = mt * 128 + 32 * q + lane;
+  const bool active = warp < EW;
+  const int unit = (rank * MU + mt) * 128 + 32 * q + lane;
   const bool uvalid = active && unit < H;
   const int nvalid = min(N, B - b0);
   const uint32_t bcol = r1_bcol(unit), bch = r1_bchunk(unit);
   uint8_t *b1_gen = s.gen + (s.s_b1 - s.base);
   uint8_t *b2_gen = s.gen + (s.s_b2 - s.base);
+  // the same tiles and operand barriers in each CTA of the cluster (CL = 2)
+  uint32_t b1_rem[2] = {0, 0}, b2_rem[2] = {0, 0}, op1_rem[2] = {0, 0}, op2_rem[2] = {0, 0};
+  if constexpr (CL > 1) {
+#pragma unroll
+    for (int r = 0; r < 2; ++r) {
+      b1_rem[r] = r1_mapa(s.s_b1, (uint32_t)r);
+      b2_rem[r] = r1_mapa(s.s_b2, (uint32_t)r);
+      op1_rem[r] = r1_mapa(bar_op1, (uint32_t)r);
+      op2_rem[r] = r1_mapa(bar_op2, (uint32_t)r);
+    }
+  }
+  const int kb_lo = CL == 1 ? 0 : rank * MU * 2, kb_hi = CL == 1 ? nkb : min(nkb, kb_lo + MU * 2);  // the k-blocks of my units
   float hcur[NR];
 #pragma unroll
   for (int n = 0; n < NR; ++n) {
     hcur[n] = (uvalid && nb + n < nvalid) ? a.state_in[(size_t)(b0 + nb + n) * H + unit] : 0.f;
-    if (uvalid) r1_sts_bf16(b1_gen + R1_BOFF(bcol, bch, nb + n), hcur[n]);
+    if (uvalid) r1_put<CL>(b1_gen, b1_rem, R1_BOFF(bcol, bch, nb + n), hcur[n]);
   }
-  fence_proxy_async_smem();
+  if constexpr (CL > 1) fence_proxy_async(); else fence_proxy_async_smem();
   tc_fence_before();
   __syncthreads();
+  if constexpr (CL > 1) {
+    r1_cluster_sync();    // both halves of the step-0 tile have landed
+    fence_proxy_async();
+  }
   tc_fence_after();
 
-  if (warp == R1_EPI_WARPS) {
+  if (warp == EW) {
     // ---------------- MMA issuer + TMA stores of the operand tiles ----------------
     // Ordering of a tile's store against its next overwrite: the store is issued right after a tcgen05.commit, the
     // elementwise warps overwrite the tile only after a LATER commit has arrived, and this thread waits for its
@@ -284,10 +377,7 @@ rnn1_fwd_kernel(const __grid_constant__ CUtensorMap tm_hp, const __grid_constant
       for (int j = 0; j < MU; ++j) A2[j] = r1_resolve(a.tile[CELL == 1 ? 2 * MU + j : j], s.s_w, tmem_base);
       const uint64_t dB2 = make_desc(s.s_b2, 0, 1024);
       for (int t = 0; t < T; ++t) {
-        if (t > 0) {
-          R1_WAIT(bar_op1, (t - 1) & 1, 1);
-          tc_fence_after();
-        }
+        if (t > 0) r1_wait_operand<CL>(bar_op1, (t - 1) & 1, 1);
         R1_LAP(8);
         const uint32_t sb1 = s.s_b1 + (uint32_t)((NB1 == 2 ? (t & 1) : 0) * btile);
         const uint64_t dB1 = make_desc(sb1, 0, 1024);
@@ -295,17 +385,16 @@ rnn1_fwd_kernel(const __grid_constant__ CUtensorMap tm_hp, const __grid_constant
         for (int j = 0; j < NG; ++j) r1_issue<NKB>(tmem_base + (uint32_t)(j * N), A1[j], dB1, idesc);
         tma_store_wait_read();
         tc_commit(bar_acc1);
-        r1_store_tile(&tm_hp, sb1, nkb, 0, b0, t);  // h fed to step t
+        r1_store_tile(&tm_hp, sb1, kb_lo, kb_hi, 0, b0, t);  // h fed to step t
         R1_LAP(9);
         if constexpr (CELL == 1) {
-          R1_WAIT(bar_op2, t & 1, 2);
-          tc_fence_after();
+          r1_wait_operand<CL>(bar_op2, t & 1, 2);
           R1_LAP(10);
 #pragma unroll
           for (int j = 0; j < MU; ++j) r1_issue<NKB>(tmem_base + (uint32_t)((2 * MU + j) * N), A2[j], dB2, idesc);
           tma_store_wait_read();
           tc_commit(bar_acc2);
-          r1_store_tile(&tm_aux, s.s_b2, nkb, 0, b0, t);  // r*h of step t
+          r1_store_tile(&tm_aux, s.s_b2, kb_lo, kb_hi, 0, b0, t);  // r*h of step t
           R1_LAP(11);
         }
       }
@@ -374,10 +463,9 @@ rnn1_fwd_kernel(const __grid_constant__ CUtensorMap tm_hp, const __grid_constant
         for (int n = 0; n < NR; ++n) {
           rg[n] = sigmoid_approx(__uint_as_float(rr[n]) + x0[n]);
           ug[n] = sigmoid_approx(__uint_as_float(ru[n]) + x1[n]);
-          if (uvalid) r1_sts_bf16(b2_gen + R1_BOFF(bcol, bch, nb + n), rg[n] * hcur[n]);
+          if (uvalid) r1_put<CL>(b2_gen, b2_rem, R1_BOFF(bcol, bch, nb + n), rg[n] * hcur[n]);
         }
-        fence_proxy_async_smem();
-        mbar_arrive(bar_op2);
+        r1_arrive<CL>(bar_op2, op2_rem, lane);
         R1_LAP(2);
         if (uvalid) {
 #pragma unroll
@@ -398,7 +486,7 @@ rnn1_fwd_kernel(const __grid_constant__ CUtensorMap tm_hp, const __grid_constant
       tc_ldn<NR>(lane_addr + (uint32_t)nb + (uint32_t)((CELL == 1 ? 2 * MU + mt : mt) * N), rc);
       tc_fence_before();
       float h2[NR];
-      uint8_t *b1w = b1_gen + (NB1 == 2 ? ((t + 1) & 1) * btile : 0);
+      const uint32_t b1w = NB1 == 2 ? (uint32_t)(((t + 1) & 1) * btile) : 0u;
 #pragma unroll
       for (int n = 0; n < NR; ++n) {
         const float cand = tanh_approx(__uint_as_float(rc[n]) + (CELL == 1 ? x2[n] : x0[n]));
@@ -407,11 +495,10 @@ rnn1_fwd_kernel(const __grid_constant__ CUtensorMap tm_hp, const __grid_constant
         if ((eoc_m >> (nb + n)) & 1u)  // eoc: back to the FED state (model.py:82-92); warp-uniform and rare
           hn = uvalid ? __ldg(a.state_in + (size_t)(b0 + nb + n) * H + unit) : 0.f;
         hcur[n] = hn;
-        if (uvalid) r1_sts_bf16(b1w + R1_BOFF(bcol, bch, nb + n), hn);
+        if (uvalid) r1_put<CL>(b1_gen, b1_rem, b1w + R1_BOFF(bcol, bch, nb + n), hn);
         if constexpr (CELL == 1) x2[n] = cand;
       }
-      fence_proxy_async_smem();
-      mbar_arrive(bar_op1);
+      r1_arrive<CL>(bar_op1, op1_rem, lane);
       R1_LAP(5);
       // off the dependent chain: layer output (pre reset, dropout applied) and the activation BPTT needs
       if (uvalid) {
@@ -442,14 +529,15 @@ rnn1_fwd_kernel(const __grid_constant__ CUtensorMap tm_hp, const __grid_constant
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == R1_EPI_WARPS) tc_dealloc(tmem_base, (uint32_t)a.tmem_cols);
+  if constexpr (CL > 1) r1_cluster_sync();  // nobody leaves while the peer may still write into it or arrive on its barriers
+  if (warp == EW) tc_dealloc(tmem_base, (uint32_t)a.tmem_cols);
 }
 
 // ------------------------------------------------------------------------------------------------
 // backward (BPTT).  d(pre-activation) leaves as TMA stores of the operand tiles: no per-thread global stores.
 // ------------------------------------------------------------------------------------------------
-template <int CELL, int MU, int NKB>
-__global__ void __launch_bounds__(R1_THREADS, 1) rnn1_bwd_kernel(const __grid_constant__ CUtensorMap tm_dp, R1Args a) {
+template <int CELL, int MU, int NKB, int CL>
+__global__ void __launch_bounds__(r1_threads(MU), 1) rnn1_bwd_kernel(const __grid_constant__ CUtensorMap tm_dp, R1Args a) {
   constexpr int N = R1_N;
   constexpr int NB1 = CELL == 2 ? 2 : 1;
   extern __shared__ uint8_t smem_raw[];
@@ -461,44 +549,49 @@ __global__ void __launch_bounds__(R1_THREADS, 1) rnn1_bwd_kernel(const __grid_co
   const uint32_t bar_op1 = s.s_bar, bar_acc1 = s.s_bar + 8, bar_op2 = s.s_bar + 16, bar_acc2 = s.s_bar + 24;
   const uint32_t tmem_holder = s.s_bar + 32;
   volatile uint32_t *tmem_holder_ptr = reinterpret_cast<volatile uint32_t *>(s.gen + (tmem_holder - s.base));
+  constexpr int EW = 8 * MU, THREADS = r1_threads(MU);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int b0 = blockIdx.x * N;
+  const int rank = CL == 1 ? 0 : (int)r1_cluster_rank();
+  const int b0 = (blockIdx.x / CL) * N;
+  const uint8_t *wimg = a.wimg + (size_t)rank * a.wimg_rank_bytes;
   __shared__ long long tk[16];
   if (tid < 16) tk[tid] = 0;
 
-  r1_load_smem_tiles(a, s, tid);
+  r1_load_smem_tiles(a, wimg, s, tid, THREADS);
   if (tid == 0) {
-    mbar_init(bar_op1, 256 * MU);
+    mbar_init(bar_op1, CL == 1 ? 32 * EW : EW * CL);
     mbar_init(bar_acc1, 1);
-    mbar_init(bar_op2, 256 * MU);
+    mbar_init(bar_op2, CL == 1 ? 32 * EW : EW * CL);
     mbar_init(bar_acc2, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
-  if (warp == R1_EPI_WARPS) tc_alloc(tmem_holder, (uint32_t)a.tmem_cols);
+  if (warp == EW) tc_alloc(tmem_holder, (uint32_t)a.tmem_cols);
   {
     uint4 *z = reinterpret_cast<uint4 *>(s.gen + (s.s_b1 - s.base));
     const int n16 = (NB1 + (CELL == 1 ? 2 : 0)) * btile / 16;
-    for (int i = tid; i < n16; i += R1_THREADS) z[i] = make_uint4(0, 0, 0, 0);
+    for (int i = tid; i < n16; i += THREADS) z[i] = make_uint4(0, 0, 0, 0);
   }
   fence_proxy_async_smem();
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_holder_ptr;
-  r1_load_tmem_tiles(a, tmem_base, warp, lane);
+  r1_load_tmem_tiles(a, wimg, tmem_base, warp, lane);
   tc_fence_before();
   __syncthreads();
+  if constexpr (CL > 1) r1_cluster_sync();  // the peer's tiles are zeroed and its barriers initialised before anything is sent there
   tc_fence_after();
 
   constexpr int NR = R1_NR;
   const int q = warp & 3, hh = (warp >> 2) & 1, mt = warp >> 3;
   const int nb = NR * hh;  // my rows of the tile: [nb, nb + NR)
-  const bool active = warp < R1_EPI_WARPS && mt < MU;
-  const int unit = mt * 128 + 32 * q + lane;
+  const bool active = warp < EW;
+  const int unit = (rank * MU + mt) * 128 + 32 * q + lane;
   const bool uvalid = active && unit < H;
   const int nvalid = min(N, B - b0);
+  const int kb_lo = CL == 1 ? 0 : rank * MU * 2, kb_hi = CL == 1 ? nkb : min(nkb, kb_lo + MU * 2);  // the k-blocks of my units
 
-  if (warp == R1_EPI_WARPS) {
+  if (warp == EW) {
     // ---------------- MMA issuer + TMA stores of d(pre) (same ordering argument as in the forward kernel) ----------------
     if (elect_one()) {
       const uint32_t idesc = make_idesc_bf16(128, N, false, false);
@@ -512,26 +605,24 @@ __global__ void __launch_bounds__(R1_THREADS, 1) rnn1_bwd_kernel(const __grid_co
       for (int t = T - 1, st = 0; t >= 0; --t, ++st) {
         if constexpr (CELL == 1) {
           // d(r*h) = d(pre_c) * Wc_h^T
-          R1_WAIT(bar_op1, st & 1, 11);
-          tc_fence_after();
+          r1_wait_operand<CL>(bar_op1, st & 1, 11);
           const uint64_t dB1 = make_desc(s.s_b1, 0, 1024);
 #pragma unroll
           for (int j = 0; j < MU; ++j) r1_issue<NKB>(tmem_base + (uint32_t)(j * N), A1[j], dB1, idesc);
           tma_store_wait_read();
           tc_commit(bar_acc1);
-          r1_store_tile(&tm_dp, s.s_b1, nkb, 2 * H, b0, t);
-          R1_WAIT(bar_op2, st & 1, 12);
-          tc_fence_after();
+          r1_store_tile(&tm_dp, s.s_b1, kb_lo, kb_hi, 2 * H, b0, t);
+          r1_wait_operand<CL>(bar_op2, st & 1, 12);
           if (t > 0) {  // d(h_{t-1}) += [d(pre_r), d(pre_u)] * Wg_h^T
 #pragma unroll
             for (int j = 0; j < MU; ++j) r1_issue<2 * NKB>(tmem_base + (uint32_t)((MU + j) * N), A2[j], dB2, idesc);
           }
           tma_store_wait_read();
           if (t > 0) tc_commit(bar_acc2);
-          r1_store_tile(&tm_dp, s.s_b2, 2 * nkb, 0, b0, t);
+          r1_store_tile(&tm_dp, s.s_b2, kb_lo, kb_hi, 0, b0, t);              // d(pre_r)
+          r1_store_tile(&tm_dp, s.s_b2, nkb + kb_lo, nkb + kb_hi, 0, b0, t);  // d(pre_u)
         } else {
-          R1_WAIT(bar_op1, st & 1, 13);
-          tc_fence_after();
+          r1_wait_operand<CL>(bar_op1, st & 1, 13);
           const uint32_t sb1 = s.s_b1 + (uint32_t)((st & 1) * btile);
           const uint64_t dB1 = make_desc(sb1, 0, 1024);
           if (t > 0) {
@@ -540,7 +631,7 @@ __global__ void __launch_bounds__(R1_THREADS, 1) rnn1_bwd_kernel(const __grid_co
           }
           tma_store_wait_read();
           if (t > 0) tc_commit(bar_acc1);
-          r1_store_tile(&tm_dp, sb1, nkb, 0, b0, t);
+          r1_store_tile(&tm_dp, sb1, kb_lo, kb_hi, 0, b0, t);
         }
       }
       tma_store_wait_all();
@@ -554,6 +645,16 @@ __global__ void __launch_bounds__(R1_THREADS, 1) rnn1_bwd_kernel(const __grid_co
     const uint32_t bcol_u = r1_bcol(H + unit), bch_u = r1_bchunk(H + unit);
     uint8_t *b1_gen = s.gen + (s.s_b1 - s.base);
     uint8_t *b2_gen = s.gen + (s.s_b2 - s.base);
+    uint32_t b1_rem[2] = {0, 0}, b2_rem[2] = {0, 0}, op1_rem[2] = {0, 0}, op2_rem[2] = {0, 0};
+    if constexpr (CL > 1) {
+#pragma unroll
+      for (int r = 0; r < 2; ++r) {
+        b1_rem[r] = r1_mapa(s.s_b1, (uint32_t)r);
+        b2_rem[r] = r1_mapa(s.s_b2, (uint32_t)r);
+        op1_rem[r] = r1_mapa(bar_op1, (uint32_t)r);
+        op2_rem[r] = r1_mapa(bar_op2, (uint32_t)r);
+      }
+    }
     const int u0w = unit - lane;
     // per-thread views of (t, b0, unit), walking backwards in t
     const char *act_p = reinterpret_cast<const char *>(a.acts_bf + ((size_t)(T - 1) * B + b0 + nb) * G + unit);
@@ -612,16 +713,15 @@ __global__ void __launch_bounds__(R1_THREADS, 1) rnn1_bwd_kernel(const __grid_co
       }
       R1_LAP(1);
       if constexpr (CELL == 2) {
-        uint8_t *b1w = b1_gen + (st & 1) * btile;
+        const uint32_t b1w = (uint32_t)((st & 1) * btile);
 #pragma unroll
         for (int n = 0; n < NR; ++n) {
           const float dh2 = d_o[n] * dsc[n] + (((eoc_m >> (nb + n)) & 1u) ? 0.f : dhc[n]);
           const float dp = dh2 * (1.0f - a0[n] * a0[n]);
           bs0 += dp;
-          if (uvalid) r1_sts_bf16(b1w + R1_BOFF(bcol, bch, nb + n), dp);
+          if (uvalid) r1_put<CL>(b1_gen, b1_rem, b1w + R1_BOFF(bcol, bch, nb + n), dp);
         }
-        fence_proxy_async_smem();
-        mbar_arrive(bar_op1);
+        r1_arrive<CL>(bar_op1, op1_rem, lane);
         R1_LAP(2);
       } else {
         // a0 = r, a1 = u, a2 = candidate, hv = h fed to the step
@@ -633,10 +733,9 @@ __global__ void __launch_bounds__(R1_THREADS, 1) rnn1_bwd_kernel(const __grid_co
           const float dpc = dh2 * (1.0f - a1[n]) * (1.0f - a2[n] * a2[n]);
           dhc[n] = dh2 * a1[n];  // direct path h -> h'; the two products add to it below / next iteration
           bs2 += dpc;
-          if (uvalid) r1_sts_bf16(b1_gen + R1_BOFF(bcol, bch, nb + n), dpc);
+          if (uvalid) r1_put<CL>(b1_gen, b1_rem, R1_BOFF(bcol, bch, nb + n), dpc);
         }
-        fence_proxy_async_smem();
-        mbar_arrive(bar_op1);
+        r1_arrive<CL>(bar_op1, op1_rem, lane);
         R1_LAP(2);
         R1_WAIT(bar_acc1, st & 1, 15);
         R1_LAP(4);
@@ -653,12 +752,11 @@ __global__ void __launch_bounds__(R1_THREADS, 1) rnn1_bwd_kernel(const __grid_co
           bs0 += dpr;
           bs1 += dpu;
           if (uvalid) {
-            r1_sts_bf16(b2_gen + R1_BOFF(bcol, bch, nb + n), dpr);
-            r1_sts_bf16(b2_gen + R1_BOFF(bcol_u, bch_u, nb + n), dpu);
+            r1_put<CL>(b2_gen, b2_rem, R1_BOFF(bcol, bch, nb + n), dpr);
+            r1_put<CL>(b2_gen, b2_rem, R1_BOFF(bcol_u, bch_u, nb + n), dpu);
           }
         }
-        fence_proxy_async_smem();
-        mbar_arrive(bar_op2);
+        r1_arrive<CL>(bar_op2, op2_rem, lane);
         R1_LAP(5);
       }
       act_p -= act_ts; hp_p -= hp_ts; do_p -= do_ts;
@@ -681,7 +779,8 @@ __global__ void __launch_bounds__(R1_THREADS, 1) rnn1_bwd_kernel(const __grid_co
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == R1_EPI_WARPS) tc_dealloc(tmem_base, (uint32_t)a.tmem_cols);
+  if constexpr (CL > 1) r1_cluster_sync();  // nobody leaves while the peer may still write into it or arrive on its barriers
+  if (warp == EW) tc_dealloc(tmem_base, (uint32_t)a.tmem_cols);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -749,7 +848,13 @@ int sk_rnn1_tc_layer(skrnn_handle *h, cudaStream_t st, bool bwd, int l, int B, i
   if (h->ws.acts_bf[l] == nullptr || h->ws.out_bf[l] == nullptr || h->ws.hprev_bf[l] == nullptr || h->ws.dpre_bf == nullptr ||
       h->ws.xw_il[l] == nullptr || (gru && h->ws.aux_bf[l] == nullptr))
     return -1;
-  const int MU = (H + 127) / 128, nkb = H / 64;
+  const int MU_all = (H + 127) / 128, nkb = H / 64;
+  // H > 128: a cluster of 2 CTAs per batch tile, each holding the weight rows of its 128 units in tensor memory (the
+  // whole matrix does not fit in one SM's 512 columns, and a tile read from shared memory runs 4x slower)
+  static int env_cl = -1;
+  if (env_cl < 0) { const char *e = getenv("SKRNN_R1_CLUSTER"); env_cl = (e && e[0] == '0') ? 0 : 1; }
+  const int CL = (MU_all == 2 && env_cl) ? 2 : 1;
+  const int MU = MU_all / CL;  // m-tiles per CTA
   const SkLayerParams &lp = h->lp[l];
   const float *W0 = h->params + lp.w[0];                     // rnn: [I+H, H]; gru gates: [I+H, 2H]
   const float *W1 = gru ? h->params + lp.w[1] : nullptr;     // gru candidate: [I+H, H]
@@ -762,23 +867,27 @@ int sk_rnn1_tc_layer(skrnn_handle *h, cudaStream_t st, bool bwd, int l, int B, i
     R1PackTile &t = pk.t[nt++];
     t.mat = mat; t.ld = ld; t.m0 = m0; t.c0 = c0; t.trans = trans; t.K = K; t.nkb = K / 64;
   };
-  if (!bwd) {
-    if (gru) {
-      for (int g = 0; g < 2; ++g)
-        for (int m = 0; m < MU; ++m) add(W0, 2 * H, 128 * m, g * H, 1, H);
-      for (int m = 0; m < MU; ++m) add(W1, H, 128 * m, 0, 1, H);
+  for (int r = 0; r < CL; ++r) {  // each rank's tiles, in the same order
+    const int u0 = 128 * r * MU;
+    if (!bwd) {
+      if (gru) {
+        for (int g = 0; g < 2; ++g)
+          for (int m = 0; m < MU; ++m) add(W0, 2 * H, u0 + 128 * m, g * H, 1, H);
+        for (int m = 0; m < MU; ++m) add(W1, H, u0 + 128 * m, 0, 1, H);
+      } else {
+        for (int m = 0; m < MU; ++m) add(W0, H, u0 + 128 * m, 0, 1, H);
+      }
     } else {
-      for (int m = 0; m < MU; ++m) add(W0, H, 128 * m, 0, 1, H);
-    }
-  } else {
-    if (gru) {
-      for (int m = 0; m < MU; ++m) add(W1, H, 128 * m, 0, 0, H);
-      for (int m = 0; m < MU; ++m) add(W0, 2 * H, 128 * m, 0, 0, 2 * H);
-    } else {
-      for (int m = 0; m < MU; ++m) add(W0, H, 128 * m, 0, 0, H);
+      if (gru) {
+        for (int m = 0; m < MU; ++m) add(W1, H, u0 + 128 * m, 0, 0, H);
+        for (int m = 0; m < MU; ++m) add(W0, 2 * H, u0 + 128 * m, 0, 0, 2 * H);
+      } else {
+        for (int m = 0; m < MU; ++m) add(W0, H, u0 + 128 * m, 0, 0, H);
+      }
     }
   }
   pk.ntiles = nt;
+  nt /= CL;  // tiles of one rank: placement and offsets are the same in every CTA
   // placement: the subset of tiles kept in shared memory must fit beside the operand tiles, the rest goes to tensor
   // memory behind the accumulators (512 columns in all).  A tile read from shared memory costs 4 KB of operand
   // traffic per MMA (32 cycles at 128 B/clk against 8 cycles of math at N = 16), so take the feasible split with the
@@ -810,6 +919,13 @@ int sk_rnn1_tc_layer(skrnn_handle *h, cudaStream_t st, bool bwd, int l, int B, i
     if (t.in_tmem) { a.tile[j].off = coff; coff += t.nkb * 32; }
     else { a.tile[j].off = soff; soff += t.nkb * 16384; }
   }
+  a.wimg_rank_bytes = ioff;
+  for (int r = 1; r < CL; ++r)
+    for (int j = 0; j < nt; ++j) {
+      pk.t[r * nt + j].in_tmem = pk.t[j].in_tmem;
+      pk.t[r * nt + j].img = r * a.wimg_rank_bytes + pk.t[j].img;
+    }
+  ioff *= CL;
   SK_CHECK((int64_t)ioff <= h->ws.wpack_floats * 4, "weight image workspace too small");
   {
     SkLaunch scope(h, st, SK_CAT_MISC);
@@ -845,14 +961,28 @@ int sk_rnn1_tc_layer(skrnn_handle *h, cudaStream_t st, bool bwd, int l, int B, i
     a.pf_dist = pf_d; a.pf_l1 = pf_l;
   }
   const size_t smem = (size_t)soff + b_bytes + 1024 + 256;
-  const int grid = (B + R1_N - 1) / R1_N;
-  // kernel instances by (m-tiles per gate, k-blocks): H = 64, 128, 192, 256
+  const int grid = CL * ((B + R1_N - 1) / R1_N);
+  cudaLaunchConfig_t lc = {};
+  cudaLaunchAttribute lattr[1];
+  lc.gridDim = dim3((unsigned)grid);
+  lc.blockDim = dim3((unsigned)r1_threads(MU));
+  lc.dynamicSmemBytes = smem;
+  lc.stream = st;
+  lattr[0].id = cudaLaunchAttributeClusterDimension;
+  lattr[0].val.clusterDim.x = (unsigned)CL;
+  lattr[0].val.clusterDim.y = 1;
+  lattr[0].val.clusterDim.z = 1;
+  lc.attrs = lattr;
+  lc.numAttrs = 1;
+  // kernel instances by (m-tiles per CTA, k-blocks, CTAs per cluster): H = 64, 128, 192, 256
 #define R1_DISPATCH(LAUNCH)                                   \
   do {                                                        \
-    if (MU == 1 && nkb == 1) { LAUNCH(1, 1); }                \
-    else if (MU == 1 && nkb == 2) { LAUNCH(1, 2); }           \
-    else if (MU == 2 && nkb == 3) { LAUNCH(2, 3); }           \
-    else { LAUNCH(2, 4); }                                    \
+    if (CL == 2 && nkb == 3) { LAUNCH(1, 3, 2); }             \
+    else if (CL == 2) { LAUNCH(1, 4, 2); }                    \
+    else if (MU == 1 && nkb == 1) { LAUNCH(1, 1, 1); }        \
+    else if (MU == 1 && nkb == 2) { LAUNCH(1, 2, 1); }        \
+    else if (MU == 2 && nkb == 3) { LAUNCH(2, 3, 1); }        \
+    else { LAUNCH(2, 4, 1); }                                 \
   } while (0)
   if (!bwd) {
     if (!h->xw_il_ok[l]) return -1;  // the projection was hoisted in the fp32 format
@@ -860,11 +990,11 @@ int sk_rnn1_tc_layer(skrnn_handle *h, cudaStream_t st, bool bwd, int l, int B, i
     SK_TRY(r1_map(&tm_hp, h->ws.hprev_bf[l], H, B, T));
     SK_TRY(r1_map(&tm_aux, gru ? h->ws.aux_bf[l] : h->ws.hprev_bf[l], H, B, T));
     SkLaunch scope(h, st, SK_CAT_RNN_FWD);
-#define R1_FWD(MUV, KBV)                                                                                          \
+#define R1_FWD(MUV, KBV, CLV)                                                                                     \
   do {                                                                                                            \
-    auto kern = gru ? rnn1_fwd_kernel<1, MUV, KBV> : rnn1_fwd_kernel<2, MUV, KBV>;                                \
+    auto kern = gru ? rnn1_fwd_kernel<1, MUV, KBV, CLV> : rnn1_fwd_kernel<2, MUV, KBV, CLV>;                      \
     SK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));                  \
-    kern<<<grid, R1_THREADS, smem, st>>>(tm_hp, tm_aux, a);                                                       \
+    SK_CUDA(cudaLaunchKernelEx(&lc, kern, tm_hp, tm_aux, a));                                                     \
   } while (0)
     R1_DISPATCH(R1_FWD);
 #undef R1_FWD
@@ -872,11 +1002,11 @@ int sk_rnn1_tc_layer(skrnn_handle *h, cudaStream_t st, bool bwd, int l, int B, i
     CUtensorMap tm_dp;
     SK_TRY(r1_map(&tm_dp, h->ws.dpre_bf, G, B, T));
     SkLaunch scope(h, st, SK_CAT_RNN_BWD);
-#define R1_BWD(MUV, KBV)                                                                                          \
+#define R1_BWD(MUV, KBV, CLV)                                                                                     \
   do {                                                                                                            \
-    auto kern = gru ? rnn1_bwd_kernel<1, MUV, KBV> : rnn1_bwd_kernel<2, MUV, KBV>;                                \
+    auto kern = gru ? rnn1_bwd_kernel<1, MUV, KBV, CLV> : rnn1_bwd_kernel<2, MUV, KBV, CLV>;                      \
     SK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));                  \
-    kern<<<grid, R1_THREADS, smem, st>>>(tm_dp, a);                                                               \
+    SK_CUDA(cudaLaunchKernelEx(&lc, kern, tm_dp, a));                                                             \
   } while (0)
     R1_DISPATCH(R1_BWD);
 #undef R1_BWD
