@@ -162,14 +162,19 @@ __device__ __forceinline__ uint32_t r1_bchunk(int k) { return (uint32_t)(((k & 6
 #define R1_BOFF(colbase, chunk4, n) ((colbase) + (uint32_t)((n) * 128) + ((chunk4) ^ (uint32_t)(((n) & 7) << 4)))
 __device__ __forceinline__ void r1_sts_bf16(uint8_t *p, float v) { *reinterpret_cast<__nv_bfloat16 *>(p) = __float2bfloat16_rn(v); }
 
-__device__ __forceinline__ float r1_ld_bf16(const char *p) {
-  return __uint_as_float((uint32_t)(*reinterpret_cast<const unsigned short *>(p)) << 16);
-}
+// A bf16 value is loaded as its raw 16 bits and widened only after r1_pin, which the compiler cannot move above the
+// mbarrier wait before it (both are volatile asm): otherwise the widening shift is scheduled right behind the load and
+// the thread sits out the whole memory latency BEFORE it starts waiting for the product (measured: ~2000 cycles/step).
+__device__ __forceinline__ uint32_t r1_ld_raw16(const char *p) { return (uint32_t)(*reinterpret_cast<const unsigned short *>(p)); }
+__device__ __forceinline__ void r1_pin(uint32_t &v) { asm volatile("" : "+r"(v)); }
+__device__ __forceinline__ void r1_pin(float &v) { asm volatile("" : "+f"(v)); }
+__device__ __forceinline__ float r1_bf16_of(uint32_t raw) { return __uint_as_float(raw << 16); }
 
 // ---- cluster of 2 (CL = 2): the hidden units are split over two CTAs, each holding the weight rows of its half in
-// tensor memory.  Both CTAs need the WHOLE operand tile (the contraction runs over all units), so an elementwise
-// thread writes its elements into both CTAs' tiles (st.shared::cluster), makes them visible to the async proxy, and
-// one lane per warp arrives (release, cluster scope) on both CTAs' operand barriers.
+// tensor memory.  Both CTAs need the WHOLE operand tile (the contraction runs over all units): the elementwise warps
+// write their units' k-blocks into the local tile exactly as without a cluster, and the MMA thread, once those are
+// complete, sends them to the same place in the peer's tile with one bulk copy through distributed shared memory that
+// reports its bytes on the peer's receive barrier -- async proxy end to end, no cluster-scope fences.
 __device__ __forceinline__ uint32_t r1_cluster_rank() {
   uint32_t r;
   asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
@@ -184,56 +189,45 @@ __device__ __forceinline__ void r1_cluster_sync() {
   asm volatile("barrier.cluster.arrive.release.aligned;\n" ::: "memory");
   asm volatile("barrier.cluster.wait.acquire.aligned;\n" ::: "memory");
 }
-// operand element `v` at byte offset `off` of the tile: local store (CL = 1) or one store per CTA of the cluster
-template <int CL>
-__device__ __forceinline__ void r1_put(uint8_t *gen, const uint32_t (&rem)[2], uint32_t off, float v) {
-  if constexpr (CL == 1) {
-    r1_sts_bf16(gen + off, v);
-  } else {
-    const unsigned short b = __bfloat16_as_ushort(__float2bfloat16_rn(v));
-    asm volatile("st.shared::cluster.u16 [%0], %1;" ::"r"(rem[0] + off), "h"(b) : "memory");
-    asm volatile("st.shared::cluster.u16 [%0], %1;" ::"r"(rem[1] + off), "h"(b) : "memory");
-  }
+__device__ __forceinline__ void r1_dsmem_copy(uint32_t dst_cluster, uint32_t src_cta, uint32_t bytes, uint32_t bar_cluster) {
+  asm volatile("cp.async.bulk.shared::cluster.shared::cta.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+               ::"r"(dst_cluster), "r"(src_cta), "r"(bytes), "r"(bar_cluster) : "memory");
 }
-// the warp's operand elements are written: publish them to the MMA thread(s).  Barrier counts: 32 per warp (CL = 1),
-// one per warp and CTA (CL = 2)
-template <int CL>
-__device__ __forceinline__ void r1_arrive(uint32_t bar, const uint32_t (&rbar)[2], int lane) {
-  if constexpr (CL == 1) {
-    fence_proxy_async_smem();
-    mbar_arrive(bar);
-  } else {
-    fence_proxy_async();
-    __syncwarp();
-    if (lane == 0) {
-      asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(rbar[0]) : "memory");
-      asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(rbar[1]) : "memory");
+__device__ __forceinline__ void r1_wait_cluster(uint32_t bar, uint32_t parity, int tag) {
+  uint32_t done;
+  for (uint32_t spin = 0;; ++spin) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n"
+        "selp.u32 %0, 1, 0, p;\n"
+        "}\n" : "=r"(done) : "r"(bar), "r"(parity) : "memory");
+    if (done) return;
+    if (spin > (1u << 22)) {
+      printf("libskrnn: receive barrier wait timed out (tag %d, parity %u, block %d)\n", tag, parity, (int)blockIdx.x);
+      __trap();
     }
   }
 }
-// MMA thread: wait for the operand tile (all CTAs' parts of it)
+// What the MMA thread of a cluster CTA needs to swap k-blocks [kb_lo, kb_hi) of an operand tile with its peer
+struct R1Xchg {
+  uint32_t peer_tile;   // cluster address of the peer's copy of the tile
+  uint32_t peer_bar;    // cluster address of the peer's receive barrier
+  uint32_t bar;         // my receive barrier
+  uint32_t my_off, my_bytes, peer_bytes;
+};
+// my blocks of the tile at s_tile (+ `second` bytes further for the second half of a two-part tile) -> peer; then wait
+// for the peer's blocks.  `parts` = 1 or 2.
 template <int CL>
-__device__ __forceinline__ void r1_wait_operand(uint32_t bar, uint32_t parity, int tag) {
-  if constexpr (CL == 1) {
-    mbar_wait_wd(bar, parity, tag, 1u << 22);
-  } else {
-    uint32_t done;
-    for (uint32_t spin = 0;; ++spin) {
-      asm volatile(
-          "{\n"
-          ".reg .pred p;\n"
-          "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n"
-          "selp.u32 %0, 1, 0, p;\n"
-          "}\n" : "=r"(done) : "r"(bar), "r"(parity) : "memory");
-      if (done) break;
-      if (spin > (1u << 22)) {
-        printf("libskrnn: operand barrier wait timed out (tag %d, parity %u, block %d)\n", tag, parity, (int)blockIdx.x);
-        __trap();
-      }
-    }
-    fence_proxy_async();
+__device__ __forceinline__ void r1_exchange(const R1Xchg &x, uint32_t s_tile, uint32_t buf_off, int parts, uint32_t second,
+                                            uint32_t parity, int tag) {
+  if constexpr (CL > 1) {
+    mbar_expect_tx(x.bar, x.peer_bytes * (uint32_t)parts);
+    for (int p = 0; p < parts; ++p)
+      r1_dsmem_copy(x.peer_tile + buf_off + x.my_off + (uint32_t)p * second, s_tile + buf_off + x.my_off + (uint32_t)p * second,
+                    x.my_bytes, x.peer_bar);
+    r1_wait_cluster(x.bar, parity, tag);
   }
-  tc_fence_after();
 }
 
 // L2 prefetch of the 128-byte line holding (row b0 + lane, column col) of a [T,B,ld] array at step t: one instruction
@@ -290,7 +284,7 @@ rnn1_fwd_kernel(const __grid_constant__ CUtensorMap tm_hp, const __grid_constant
   constexpr int btile = NKB * N * 128;
   const R1Smem s = r1_smem(smem_raw, a.smem_w_bytes, NB1 * btile, CELL == 1 ? btile : 0);
   const uint32_t bar_op1 = s.s_bar, bar_acc1 = s.s_bar + 8, bar_op2 = s.s_bar + 16, bar_acc2 = s.s_bar + 24;
-  const uint32_t tmem_holder = s.s_bar + 32;
+  const uint32_t tmem_holder = s.s_bar + 32, bar_rx1 = s.s_bar + 40, bar_rx2 = s.s_bar + 48;  // rx: the peer's k-blocks have landed
   volatile uint32_t *tmem_holder_ptr = reinterpret_cast<volatile uint32_t *>(s.gen + (tmem_holder - s.base));
   constexpr int EW = 8 * MU, THREADS = r1_threads(MU);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -302,10 +296,12 @@ rnn1_fwd_kernel(const __grid_constant__ CUtensorMap tm_hp, const __grid_constant
 
   r1_load_smem_tiles(a, wimg, s, tid, THREADS);
   if (tid == 0) {
-    mbar_init(bar_op1, CL == 1 ? 32 * EW : EW * CL);
+    mbar_init(bar_op1, 32 * EW);
     mbar_init(bar_acc1, 1);
-    mbar_init(bar_op2, CL == 1 ? 32 * EW : EW * CL);
+    mbar_init(bar_op2, 32 * EW);
     mbar_init(bar_acc2, 1);
+    mbar_init(bar_rx1, 1);
+    mbar_init(bar_rx2, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == EW) tc_alloc(tmem_holder, (uint32_t)a.tmem_cols);
@@ -332,31 +328,16 @@ rnn1_fwd_kernel(const __grid_constant__ CUtensorMap tm_hp, const __grid_constant
   const uint32_t bcol = r1_bcol(unit), bch = r1_bchunk(unit);
   uint8_t *b1_gen = s.gen + (s.s_b1 - s.base);
   uint8_t *b2_gen = s.gen + (s.s_b2 - s.base);
-  // the same tiles and operand barriers in each CTA of the cluster (CL = 2)
-  uint32_t b1_rem[2] = {0, 0}, b2_rem[2] = {0, 0}, op1_rem[2] = {0, 0}, op2_rem[2] = {0, 0};
-  if constexpr (CL > 1) {
-#pragma unroll
-    for (int r = 0; r < 2; ++r) {
-      b1_rem[r] = r1_mapa(s.s_b1, (uint32_t)r);
-      b2_rem[r] = r1_mapa(s.s_b2, (uint32_t)r);
-      op1_rem[r] = r1_mapa(bar_op1, (uint32_t)r);
-      op2_rem[r] = r1_mapa(bar_op2, (uint32_t)r);
-    }
-  }
   const int kb_lo = CL == 1 ? 0 : rank * MU * 2, kb_hi = CL == 1 ? nkb : min(nkb, kb_lo + MU * 2);  // the k-blocks of my units
   float hcur[NR];
 #pragma unroll
   for (int n = 0; n < NR; ++n) {
     hcur[n] = (uvalid && nb + n < nvalid) ? a.state_in[(size_t)(b0 + nb + n) * H + unit] : 0.f;
-    if (uvalid) r1_put<CL>(b1_gen, b1_rem, R1_BOFF(bcol, bch, nb + n), hcur[n]);
+    if (uvalid) r1_sts_bf16(b1_gen + R1_BOFF(bcol, bch, nb + n), hcur[n]);
   }
-  if constexpr (CL > 1) fence_proxy_async(); else fence_proxy_async_smem();
+  fence_proxy_async_smem();
   tc_fence_before();
   __syncthreads();
-  if constexpr (CL > 1) {
-    r1_cluster_sync();    // both halves of the step-0 tile have landed
-    fence_proxy_async();
-  }
   tc_fence_after();
 
   if (warp == EW) {
@@ -376,10 +357,24 @@ rnn1_fwd_kernel(const __grid_constant__ CUtensorMap tm_hp, const __grid_constant
 #pragma unroll
       for (int j = 0; j < MU; ++j) A2[j] = r1_resolve(a.tile[CELL == 1 ? 2 * MU + j : j], s.s_w, tmem_base);
       const uint64_t dB2 = make_desc(s.s_b2, 0, 1024);
+      R1Xchg x1 = {}, x2 = {};
+      if constexpr (CL > 1) {
+        const int p_lo = (1 - rank) * MU * 2, p_hi = min(nkb, p_lo + MU * 2);
+        x1.peer_tile = r1_mapa(s.s_b1, (uint32_t)(1 - rank)); x1.peer_bar = r1_mapa(bar_rx1, (uint32_t)(1 - rank)); x1.bar = bar_rx1;
+        x2.peer_tile = r1_mapa(s.s_b2, (uint32_t)(1 - rank)); x2.peer_bar = r1_mapa(bar_rx2, (uint32_t)(1 - rank)); x2.bar = bar_rx2;
+        x1.my_off = x2.my_off = (uint32_t)kb_lo * (N * 128);
+        x1.my_bytes = x2.my_bytes = (uint32_t)(kb_hi - kb_lo) * (N * 128);
+        x1.peer_bytes = x2.peer_bytes = (uint32_t)(p_hi - p_lo) * (N * 128);
+      }
       for (int t = 0; t < T; ++t) {
-        if (t > 0) r1_wait_operand<CL>(bar_op1, (t - 1) & 1, 1);
+        if (t > 0) {
+          R1_WAIT(bar_op1, (t - 1) & 1, 1);
+          tc_fence_after();
+        }
+        const uint32_t b1off = (uint32_t)((NB1 == 2 ? (t & 1) : 0) * btile);
+        r1_exchange<CL>(x1, s.s_b1, b1off, 1, 0, t & 1, 21);
         R1_LAP(8);
-        const uint32_t sb1 = s.s_b1 + (uint32_t)((NB1 == 2 ? (t & 1) : 0) * btile);
+        const uint32_t sb1 = s.s_b1 + b1off;
         const uint64_t dB1 = make_desc(sb1, 0, 1024);
 #pragma unroll
         for (int j = 0; j < NG; ++j) r1_issue<NKB>(tmem_base + (uint32_t)(j * N), A1[j], dB1, idesc);
@@ -388,7 +383,9 @@ rnn1_fwd_kernel(const __grid_constant__ CUtensorMap tm_hp, const __grid_constant
         r1_store_tile(&tm_hp, sb1, kb_lo, kb_hi, 0, b0, t);  // h fed to step t
         R1_LAP(9);
         if constexpr (CELL == 1) {
-          r1_wait_operand<CL>(bar_op2, t & 1, 2);
+          R1_WAIT(bar_op2, t & 1, 2);
+          tc_fence_after();
+          r1_exchange<CL>(x2, s.s_b2, 0, 1, 0, t & 1, 22);
           R1_LAP(10);
 #pragma unroll
           for (int j = 0; j < MU; ++j) r1_issue<NKB>(tmem_base + (uint32_t)((2 * MU + j) * N), A2[j], dB2, idesc);
@@ -423,16 +420,16 @@ rnn1_fwd_kernel(const __grid_constant__ CUtensorMap tm_hp, const __grid_constant
     auto body = [&](auto full_tag, int t) {
       constexpr bool FULL = decltype(full_tag)::value;
       // everything that does not depend on the recurrence is requested before waiting for the product
-      float x0[NR], x1[NR], x2[NR];
+      uint32_t xr0[NR], xr1[NR], xr2[NR];
 #pragma unroll
       for (int n = 0; n < NR; ++n) {
         const bool ok = uvalid && (FULL || nb + n < nvalid);
         const char *p = xw_p + (uint32_t)n * xw_rs;
-        x0[n] = ok ? r1_ld_bf16(p) : 0.f;
-        x1[n] = 0.f; x2[n] = 0.f;
+        xr0[n] = ok ? r1_ld_raw16(p) : 0u;
+        xr1[n] = 0u; xr2[n] = 0u;
         if constexpr (CELL == 1) {
-          x1[n] = ok ? r1_ld_bf16(p + gH2) : 0.f;
-          x2[n] = ok ? r1_ld_bf16(p + 2 * gH2) : 0.f;
+          xr1[n] = ok ? r1_ld_raw16(p + gH2) : 0u;
+          xr2[n] = ok ? r1_ld_raw16(p + 2 * gH2) : 0u;
         }
       }
       if (u0w < H && hh == 0) {
@@ -454,6 +451,8 @@ rnn1_fwd_kernel(const __grid_constant__ CUtensorMap tm_hp, const __grid_constant
         R1_WAIT(bar_acc1, t & 1, 3);
         R1_LAP(1);
         tc_fence_after();
+#pragma unroll
+        for (int n = 0; n < NR; ++n) { r1_pin(xr0[n]); r1_pin(xr1[n]); }
         uint32_t rr[NR], ru[NR];
         tc_ldn<NR>(lane_addr + (uint32_t)nb + (uint32_t)(mt * N), rr);
         tc_ldn<NR>(lane_addr + (uint32_t)nb + (uint32_t)((MU + mt) * N), ru);
@@ -461,11 +460,12 @@ rnn1_fwd_kernel(const __grid_constant__ CUtensorMap tm_hp, const __grid_constant
         float rg[NR];
 #pragma unroll
         for (int n = 0; n < NR; ++n) {
-          rg[n] = sigmoid_approx(__uint_as_float(rr[n]) + x0[n]);
-          ug[n] = sigmoid_approx(__uint_as_float(ru[n]) + x1[n]);
-          if (uvalid) r1_put<CL>(b2_gen, b2_rem, R1_BOFF(bcol, bch, nb + n), rg[n] * hcur[n]);
+          rg[n] = sigmoid_approx(__uint_as_float(rr[n]) + r1_bf16_of(xr0[n]));
+          ug[n] = sigmoid_approx(__uint_as_float(ru[n]) + r1_bf16_of(xr1[n]));
+          if (uvalid) r1_sts_bf16(b2_gen + R1_BOFF(bcol, bch, nb + n), rg[n] * hcur[n]);
         }
-        r1_arrive<CL>(bar_op2, op2_rem, lane);
+        fence_proxy_async_smem();
+        mbar_arrive(bar_op2);
         R1_LAP(2);
         if (uvalid) {
 #pragma unroll
@@ -482,6 +482,9 @@ rnn1_fwd_kernel(const __grid_constant__ CUtensorMap tm_hp, const __grid_constant
       R1_WAIT(CELL == 1 ? bar_acc2 : bar_acc1, t & 1, 4);
       R1_LAP(4);
       tc_fence_after();
+#pragma unroll
+      for (int n = 0; n < NR; ++n) r1_pin(CELL == 1 ? xr2[n] : xr0[n]);
+      float x2[NR];
       uint32_t rc[NR];
       tc_ldn<NR>(lane_addr + (uint32_t)nb + (uint32_t)((CELL == 1 ? 2 * MU + mt : mt) * N), rc);
       tc_fence_before();
@@ -489,16 +492,17 @@ rnn1_fwd_kernel(const __grid_constant__ CUtensorMap tm_hp, const __grid_constant
       const uint32_t b1w = NB1 == 2 ? (uint32_t)(((t + 1) & 1) * btile) : 0u;
 #pragma unroll
       for (int n = 0; n < NR; ++n) {
-        const float cand = tanh_approx(__uint_as_float(rc[n]) + (CELL == 1 ? x2[n] : x0[n]));
+        const float cand = tanh_approx(__uint_as_float(rc[n]) + r1_bf16_of(CELL == 1 ? xr2[n] : xr0[n]));
         h2[n] = CELL == 1 ? fmaf(ug[n], hcur[n] - cand, cand) : cand;   // u*h + (1-u)*c
         float hn = h2[n];
         if ((eoc_m >> (nb + n)) & 1u)  // eoc: back to the FED state (model.py:82-92); warp-uniform and rare
           hn = uvalid ? __ldg(a.state_in + (size_t)(b0 + nb + n) * H + unit) : 0.f;
         hcur[n] = hn;
-        if (uvalid) r1_put<CL>(b1_gen, b1_rem, b1w + R1_BOFF(bcol, bch, nb + n), hn);
+        if (uvalid) r1_sts_bf16(b1_gen + b1w + R1_BOFF(bcol, bch, nb + n), hn);
         if constexpr (CELL == 1) x2[n] = cand;
       }
-      r1_arrive<CL>(bar_op1, op1_rem, lane);
+      fence_proxy_async_smem();
+        mbar_arrive(bar_op1);
       R1_LAP(5);
       // off the dependent chain: layer output (pre reset, dropout applied) and the activation BPTT needs
       if (uvalid) {
@@ -547,7 +551,7 @@ __global__ void __launch_bounds__(r1_threads(MU), 1) rnn1_bwd_kernel(const __gri
   // b1: d(pre) of the candidate (gru) / of the cell (rnn, two buffers), K = H;  b2 (gru): d(pre) of the gates, K = 2H
   const R1Smem s = r1_smem(smem_raw, a.smem_w_bytes, NB1 * btile, CELL == 1 ? 2 * btile : 0);
   const uint32_t bar_op1 = s.s_bar, bar_acc1 = s.s_bar + 8, bar_op2 = s.s_bar + 16, bar_acc2 = s.s_bar + 24;
-  const uint32_t tmem_holder = s.s_bar + 32;
+  const uint32_t tmem_holder = s.s_bar + 32, bar_rx1 = s.s_bar + 40, bar_rx2 = s.s_bar + 48;  // rx: the peer's k-blocks have landed
   volatile uint32_t *tmem_holder_ptr = reinterpret_cast<volatile uint32_t *>(s.gen + (tmem_holder - s.base));
   constexpr int EW = 8 * MU, THREADS = r1_threads(MU);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -559,10 +563,12 @@ __global__ void __launch_bounds__(r1_threads(MU), 1) rnn1_bwd_kernel(const __gri
 
   r1_load_smem_tiles(a, wimg, s, tid, THREADS);
   if (tid == 0) {
-    mbar_init(bar_op1, CL == 1 ? 32 * EW : EW * CL);
+    mbar_init(bar_op1, 32 * EW);
     mbar_init(bar_acc1, 1);
-    mbar_init(bar_op2, CL == 1 ? 32 * EW : EW * CL);
+    mbar_init(bar_op2, 32 * EW);
     mbar_init(bar_acc2, 1);
+    mbar_init(bar_rx1, 1);
+    mbar_init(bar_rx2, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == EW) tc_alloc(tmem_holder, (uint32_t)a.tmem_cols);
@@ -602,17 +608,30 @@ __global__ void __launch_bounds__(r1_threads(MU), 1) rnn1_bwd_kernel(const __gri
         A2[j] = r1_resolve(a.tile[CELL == 1 ? MU + j : j], s.s_w, tmem_base);
       }
       const uint64_t dB2 = make_desc(s.s_b2, 0, 1024);
+      R1Xchg x1 = {}, x2 = {};
+      if constexpr (CL > 1) {
+        const int p_lo = (1 - rank) * MU * 2, p_hi = min(nkb, p_lo + MU * 2);
+        x1.peer_tile = r1_mapa(s.s_b1, (uint32_t)(1 - rank)); x1.peer_bar = r1_mapa(bar_rx1, (uint32_t)(1 - rank)); x1.bar = bar_rx1;
+        x2.peer_tile = r1_mapa(s.s_b2, (uint32_t)(1 - rank)); x2.peer_bar = r1_mapa(bar_rx2, (uint32_t)(1 - rank)); x2.bar = bar_rx2;
+        x1.my_off = x2.my_off = (uint32_t)kb_lo * (N * 128);
+        x1.my_bytes = x2.my_bytes = (uint32_t)(kb_hi - kb_lo) * (N * 128);
+        x1.peer_bytes = x2.peer_bytes = (uint32_t)(p_hi - p_lo) * (N * 128);
+      }
       for (int t = T - 1, st = 0; t >= 0; --t, ++st) {
         if constexpr (CELL == 1) {
           // d(r*h) = d(pre_c) * Wc_h^T
-          r1_wait_operand<CL>(bar_op1, st & 1, 11);
+          R1_WAIT(bar_op1, st & 1, 11);
+          tc_fence_after();
+          r1_exchange<CL>(x1, s.s_b1, 0, 1, 0, st & 1, 23);
           const uint64_t dB1 = make_desc(s.s_b1, 0, 1024);
 #pragma unroll
           for (int j = 0; j < MU; ++j) r1_issue<NKB>(tmem_base + (uint32_t)(j * N), A1[j], dB1, idesc);
           tma_store_wait_read();
           tc_commit(bar_acc1);
           r1_store_tile(&tm_dp, s.s_b1, kb_lo, kb_hi, 2 * H, b0, t);
-          r1_wait_operand<CL>(bar_op2, st & 1, 12);
+          R1_WAIT(bar_op2, st & 1, 12);
+          tc_fence_after();
+          if (CL > 1 && t > 0) r1_exchange<CL>(x2, s.s_b2, 0, 2, (uint32_t)btile, st & 1, 24);
           if (t > 0) {  // d(h_{t-1}) += [d(pre_r), d(pre_u)] * Wg_h^T
 #pragma unroll
             for (int j = 0; j < MU; ++j) r1_issue<2 * NKB>(tmem_base + (uint32_t)((MU + j) * N), A2[j], dB2, idesc);
@@ -622,7 +641,9 @@ __global__ void __launch_bounds__(r1_threads(MU), 1) rnn1_bwd_kernel(const __gri
           r1_store_tile(&tm_dp, s.s_b2, kb_lo, kb_hi, 0, b0, t);              // d(pre_r)
           r1_store_tile(&tm_dp, s.s_b2, nkb + kb_lo, nkb + kb_hi, 0, b0, t);  // d(pre_u)
         } else {
-          r1_wait_operand<CL>(bar_op1, st & 1, 13);
+          R1_WAIT(bar_op1, st & 1, 13);
+          tc_fence_after();
+          if (CL > 1 && t > 0) r1_exchange<CL>(x1, s.s_b1, (uint32_t)((st & 1) * btile), 1, 0, st & 1, 25);
           const uint32_t sb1 = s.s_b1 + (uint32_t)((st & 1) * btile);
           const uint64_t dB1 = make_desc(sb1, 0, 1024);
           if (t > 0) {
@@ -645,16 +666,6 @@ __global__ void __launch_bounds__(r1_threads(MU), 1) rnn1_bwd_kernel(const __gri
     const uint32_t bcol_u = r1_bcol(H + unit), bch_u = r1_bchunk(H + unit);
     uint8_t *b1_gen = s.gen + (s.s_b1 - s.base);
     uint8_t *b2_gen = s.gen + (s.s_b2 - s.base);
-    uint32_t b1_rem[2] = {0, 0}, b2_rem[2] = {0, 0}, op1_rem[2] = {0, 0}, op2_rem[2] = {0, 0};
-    if constexpr (CL > 1) {
-#pragma unroll
-      for (int r = 0; r < 2; ++r) {
-        b1_rem[r] = r1_mapa(s.s_b1, (uint32_t)r);
-        b2_rem[r] = r1_mapa(s.s_b2, (uint32_t)r);
-        op1_rem[r] = r1_mapa(bar_op1, (uint32_t)r);
-        op2_rem[r] = r1_mapa(bar_op2, (uint32_t)r);
-      }
-    }
     const int u0w = unit - lane;
     // per-thread views of (t, b0, unit), walking backwards in t
     const char *act_p = reinterpret_cast<const char *>(a.acts_bf + ((size_t)(T - 1) * B + b0 + nb) * G + unit);
@@ -674,18 +685,19 @@ __global__ void __launch_bounds__(r1_threads(MU), 1) rnn1_bwd_kernel(const __gri
     auto body = [&](auto full_tag, int t, int st) {
       constexpr bool FULL = decltype(full_tag)::value;
       // saved activations and d(out) of the step: requested before waiting for the previous step's product
-      float a0[NR], a1[NR], a2[NR], hv[NR], d_o[NR];
+      uint32_t ar0[NR], ar1[NR], ar2[NR], hr[NR];
+      float d_o[NR];
 #pragma unroll
       for (int n = 0; n < NR; ++n) {
         const bool ok = uvalid && (FULL || nb + n < nvalid);
         const char *pa = act_p + (uint32_t)n * act_rs;
-        a0[n] = ok ? r1_ld_bf16(pa) : 0.f;
+        ar0[n] = ok ? r1_ld_raw16(pa) : 0u;
         d_o[n] = ok ? __ldg(reinterpret_cast<const float *>(do_p + (uint32_t)n * do_rs)) : 0.f;
-        a1[n] = 0.f; a2[n] = 0.f; hv[n] = 0.f;
+        ar1[n] = 0u; ar2[n] = 0u; hr[n] = 0u;
         if constexpr (CELL == 1) {
-          a1[n] = ok ? r1_ld_bf16(pa + gH2) : 0.f;
-          a2[n] = ok ? r1_ld_bf16(pa + 2 * gH2) : 0.f;
-          hv[n] = ok ? r1_ld_bf16(hp_p + (uint32_t)n * hp_rs) : 0.f;
+          ar1[n] = ok ? r1_ld_raw16(pa + gH2) : 0u;
+          ar2[n] = ok ? r1_ld_raw16(pa + 2 * gH2) : 0u;
+          hr[n] = ok ? r1_ld_raw16(hp_p + (uint32_t)n * hp_rs) : 0u;
         }
       }
       if (u0w < H && hh == 0) {
@@ -711,6 +723,17 @@ __global__ void __launch_bounds__(r1_threads(MU), 1) rnn1_bwd_kernel(const __gri
 #pragma unroll
         for (int n = 0; n < NR; ++n) dhc[n] = (CELL == 1 ? dhc[n] : 0.f) + __uint_as_float(r[n]);
       }
+      float a0[NR], a1[NR], a2[NR], hv[NR];
+#pragma unroll
+      for (int n = 0; n < NR; ++n) {  // (see r1_pin: the loads above stay in flight across the wait)
+        r1_pin(ar0[n]); r1_pin(d_o[n]);
+        a0[n] = r1_bf16_of(ar0[n]);
+        a1[n] = 0.f; a2[n] = 0.f; hv[n] = 0.f;
+        if constexpr (CELL == 1) {
+          r1_pin(ar1[n]); r1_pin(ar2[n]); r1_pin(hr[n]);
+          a1[n] = r1_bf16_of(ar1[n]); a2[n] = r1_bf16_of(ar2[n]); hv[n] = r1_bf16_of(hr[n]);
+        }
+      }
       R1_LAP(1);
       if constexpr (CELL == 2) {
         const uint32_t b1w = (uint32_t)((st & 1) * btile);
@@ -719,9 +742,10 @@ __global__ void __launch_bounds__(r1_threads(MU), 1) rnn1_bwd_kernel(const __gri
           const float dh2 = d_o[n] * dsc[n] + (((eoc_m >> (nb + n)) & 1u) ? 0.f : dhc[n]);
           const float dp = dh2 * (1.0f - a0[n] * a0[n]);
           bs0 += dp;
-          if (uvalid) r1_put<CL>(b1_gen, b1_rem, b1w + R1_BOFF(bcol, bch, nb + n), dp);
+          if (uvalid) r1_sts_bf16(b1_gen + b1w + R1_BOFF(bcol, bch, nb + n), dp);
         }
-        r1_arrive<CL>(bar_op1, op1_rem, lane);
+        fence_proxy_async_smem();
+        mbar_arrive(bar_op1);
         R1_LAP(2);
       } else {
         // a0 = r, a1 = u, a2 = candidate, hv = h fed to the step
@@ -733,9 +757,10 @@ __global__ void __launch_bounds__(r1_threads(MU), 1) rnn1_bwd_kernel(const __gri
           const float dpc = dh2 * (1.0f - a1[n]) * (1.0f - a2[n] * a2[n]);
           dhc[n] = dh2 * a1[n];  // direct path h -> h'; the two products add to it below / next iteration
           bs2 += dpc;
-          if (uvalid) r1_put<CL>(b1_gen, b1_rem, R1_BOFF(bcol, bch, nb + n), dpc);
+          if (uvalid) r1_sts_bf16(b1_gen + R1_BOFF(bcol, bch, nb + n), dpc);
         }
-        r1_arrive<CL>(bar_op1, op1_rem, lane);
+        fence_proxy_async_smem();
+        mbar_arrive(bar_op1);
         R1_LAP(2);
         R1_WAIT(bar_acc1, st & 1, 15);
         R1_LAP(4);
@@ -752,11 +777,12 @@ __global__ void __launch_bounds__(r1_threads(MU), 1) rnn1_bwd_kernel(const __gri
           bs0 += dpr;
           bs1 += dpu;
           if (uvalid) {
-            r1_put<CL>(b2_gen, b2_rem, R1_BOFF(bcol, bch, nb + n), dpr);
-            r1_put<CL>(b2_gen, b2_rem, R1_BOFF(bcol_u, bch_u, nb + n), dpu);
+            r1_sts_bf16(b2_gen + R1_BOFF(bcol, bch, nb + n), dpr);
+            r1_sts_bf16(b2_gen + R1_BOFF(bcol_u, bch_u, nb + n), dpu);
           }
         }
-        r1_arrive<CL>(bar_op2, op2_rem, lane);
+        fence_proxy_async_smem();
+        mbar_arrive(bar_op2);
         R1_LAP(5);
       }
       act_p -= act_ts; hp_p -= hp_ts; do_p -= do_ts;
