@@ -77,6 +77,11 @@ void free_workspace(SkWorkspace &w) {
   cudaFree(w.dpre_bf_buf[1]);
   cudaFree(w.dlogits_bf);
   w.x8_bf = w.dpre_bf = w.dpre_bf_buf[0] = w.dpre_bf_buf[1] = w.dlogits_bf = nullptr;
+  cudaFree(w.xw_tt);
+  cudaFree(w.dout_tt);
+  w.xw_tt = nullptr;
+  w.dout_tt = nullptr;
+  w.tt_rows = 0;
   for (int l = 0; l < SK_MAX_LAYERS; ++l) {
     cudaFree(w.out_bf[l]);
     cudaFree(w.hprev_bf[l]);
@@ -109,8 +114,10 @@ int alloc_f32_acts(skrnn_handle *h) {
 
 int ensure_workspace(skrnn_handle *h, int B, int T) {
   const int64_t rows = (int64_t)B * T;
+  const bool tt = h->cfg.precision == SKRNN_PREC_BF16 && h->cfg.cell != SKRNN_CELL_LSTM;
+  const int64_t rows_tt = tt ? (int64_t)T * ((B + 15) / 16) * 16 : 0;  // batch padded to the 16-row tiles of rnn1_tc.cu
   SkWorkspace &w = h->ws;
-  if (rows <= w.cap_rows && (w.bptt_carry == nullptr || B <= w.carry_B)) return 0;
+  if (rows <= w.cap_rows && rows_tt <= w.tt_rows && (w.bptt_carry == nullptr || B <= w.carry_B)) return 0;
   SK_CUDA(cudaDeviceSynchronize());
   free_workspace(w);
   SK_CUDA(cudaMalloc(&w.x_tm, rows * 5 * sizeof(float)));
@@ -132,9 +139,16 @@ int ensure_workspace(skrnn_handle *h, int B, int T) {
       SK_CUDA(cudaMalloc(&w.out_bf[l], rows * h->H * e));
       SK_CUDA(cudaMalloc(&w.hprev_bf[l], rows * h->H * e));
       if (h->cfg.cell == SKRNN_CELL_GRU) SK_CUDA(cudaMalloc(&w.aux_bf[l], rows * h->H * e));
-      SK_CUDA(cudaMalloc(&w.acts_bf[l], rows * h->G * e));  // gate activations saved by the tcgen05 recurrent kernels
+      // gate activations saved by the tcgen05 recurrent kernels (gru / rnn: tile-transposed, gru with the fed state as a 4th plane)
+      if (!tt) SK_CUDA(cudaMalloc(&w.acts_bf[l], rows * h->G * e));
+      else SK_CUDA(cudaMalloc(&w.acts_bf[l], rows_tt * (h->cfg.cell == SKRNN_CELL_GRU ? 4 * h->H : h->H) * e));
       SK_CUDA(cudaMalloc(&w.xw_il[l], rows * h->G * e));                    // hoisted projection in bf16
     }
+  }
+  if (tt) {
+    SK_CUDA(cudaMalloc(&w.xw_tt, rows_tt * h->G * sizeof(__nv_bfloat16)));
+    SK_CUDA(cudaMalloc(&w.dout_tt, rows_tt * h->H * sizeof(float)));
+    w.tt_rows = rows_tt;
   }
   w.cap_rows = rows;
   if (h->cfg.precision == SKRNN_PREC_BF16 && h->cfg.cell == SKRNN_CELL_LSTM) {

@@ -75,6 +75,11 @@ struct SkWorkspace {   // time-major activations for one (B, T) capacity
                                                      // [T,B,H,4], the four gates of a unit adjacent; gru / rnn: [T,B,G] in TF's order
   __nv_bfloat16 *acts_bf[SK_MAX_LAYERS] = {nullptr}; // [T,B,H,4]: lstm gate activations i,j,f,o saved by the tcgen05
                                                      // forward kernel for its BPTT counterpart
+  // gru / rnn tensor-core kernels (rnn1_tc.cu): per-step arrays in the tile-transposed layout [T][B/16][2][cols][8];
+  // acts_bf[l] of these cells has that layout too (gru: 4H columns, rnn: H)
+  __nv_bfloat16 *xw_tt = nullptr;                    // hoisted projection of the layer being run
+  float *dout_tt = nullptr;                          // d(out) of the layer being differentiated
+  int64_t tt_rows = 0;                               // T * ceil16(B) these were sized for
   __nv_bfloat16 *dpre_bf = nullptr;                  // [T,B,G] of the layer being differentiated (= one of dpre_bf_buf)
   __nv_bfloat16 *dpre_bf_buf[2] = {nullptr, nullptr}; // two copies: layer l's weight gradients overlap layer l-1's BPTT
   __nv_bfloat16 *dlogits_bf = nullptr;               // [T*B,NOUTP]

@@ -56,9 +56,10 @@ struct R1Args {
   const float *state_in;     // [B,H]
   float *state_out;
   const float *mask;         // [B,T,H] or null
-  const __nv_bfloat16 *xw;   // [T,B,G] bf16: hoisted x*Wx + b
-  __nv_bfloat16 *out_bf, *hprev_bf, *acts_bf;
-  const float *dout;         // [T,B,H] fp32
+  const uint4 *xw_tt;        // tile-transposed bf16 [.., G, 8]: hoisted x*Wx + b
+  __nv_bfloat16 *out_bf, *hprev_bf;
+  uint4 *acts_tt;            // tile-transposed bf16 [.., AC, 8]: gru r, u, candidate, h fed (AC = 4H); rnn: tanh output (AC = H)
+  const float4 *dout_tt;     // tile-transposed fp32 [.., H, 8]
   float *dbias0, *dbias1;
   const uint8_t *wimg;
   int wimg_rank_bytes;       // cluster of 2: each rank's tiles are a separate image
@@ -169,6 +170,29 @@ __device__ __forceinline__ uint32_t r1_ld_raw16(const char *p) { return (uint32_
 __device__ __forceinline__ void r1_pin(uint32_t &v) { asm volatile("" : "+r"(v)); }
 __device__ __forceinline__ void r1_pin(float &v) { asm volatile("" : "+f"(v)); }
 __device__ __forceinline__ float r1_bf16_of(uint32_t raw) { return __uint_as_float(raw << 16); }
+// Per-step arrays the elementwise threads read or write for THEMSELVES are kept "tile-transposed":
+//   X_tt[t][batch tile of 16][half of 8 rows][column][8 rows]
+// so that a thread (one column = hidden unit, 8 batch rows) moves its 8 values with ONE 16-byte access, coalesced
+// across the warp's 32 units -- instead of 8 two-byte accesses with 8 address computations.  Rows past the batch are
+// zero (r1_tt_kernel) or finite (written by the forward kernel).
+__device__ __forceinline__ void r1_pin(uint4 &v) { r1_pin(v.x); r1_pin(v.y); r1_pin(v.z); r1_pin(v.w); }
+__device__ __forceinline__ float r1_bf16_at(const uint4 &v, int n) {  // n is a compile-time constant after unrolling
+  const uint32_t w = (n >> 1) == 0 ? v.x : (n >> 1) == 1 ? v.y : (n >> 1) == 2 ? v.z : v.w;
+  return __uint_as_float((n & 1) ? (w & 0xffff0000u) : (w << 16));
+}
+__device__ __forceinline__ uint4 r1_pack8(const float (&v)[8]) {
+  uint4 r;
+  __nv_bfloat162 p;
+  p = __floats2bfloat162_rn(v[0], v[1]); r.x = *reinterpret_cast<const uint32_t *>(&p);
+  p = __floats2bfloat162_rn(v[2], v[3]); r.y = *reinterpret_cast<const uint32_t *>(&p);
+  p = __floats2bfloat162_rn(v[4], v[5]); r.z = *reinterpret_cast<const uint32_t *>(&p);
+  p = __floats2bfloat162_rn(v[6], v[7]); r.w = *reinterpret_cast<const uint32_t *>(&p);
+  return r;
+}
+__device__ __forceinline__ void r1_prefetch_line(const void *p, int l1) {
+  if (l1) asm volatile("prefetch.global.L1 [%0];" ::"l"(p));
+  else asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
+}
 
 // ---- cluster of 2 (CL = 2): the hidden units are split over two CTAs, each holding the weight rows of its half in
 // tensor memory.  Both CTAs need the WHOLE operand tile (the contraction runs over all units): the elementwise warps
@@ -407,12 +431,15 @@ rnn1_fwd_kernel(const __grid_constant__ CUtensorMap tm_hp, const __grid_constant
     const uint32_t drop_unit = skm_drop_unit(a.seed, (uint32_t)unit);
     const int u0w = unit - lane;  // first unit of this warp
     // per-thread views of (t, b0, unit) of the step's arrays: base pointer advanced per step, row n at n * row stride
-    const char *xw_p = reinterpret_cast<const char *>(a.xw + (size_t)(b0 + nb) * G + unit);  // bf16
+    const int NT = (B + N - 1) / N, tile = blockIdx.x / CL;
+    const int AC = CELL == 1 ? 4 * H : H;
+    const uint4 *xw_p = a.xw_tt + (size_t)(tile * 2 + hh) * G + unit;
+    uint4 *act_p = a.acts_tt + (size_t)(tile * 2 + hh) * AC + unit;
+    const size_t xw_ts = (size_t)NT * 2 * G, act_ts = (size_t)NT * 2 * AC;
     char *out_p = reinterpret_cast<char *>(a.out_bf + (size_t)(b0 + nb) * H + unit);
-    char *act_p = reinterpret_cast<char *>(a.acts_bf + (size_t)(b0 + nb) * G + unit);
-    const uint32_t xw_rs = (uint32_t)G * 2u, out_rs = (uint32_t)H * 2u, act_rs = (uint32_t)G * 2u;
-    const size_t xw_ts = (size_t)B * G * 2, out_ts = (size_t)B * H * 2, act_ts = (size_t)B * G * 2;
-    const uint32_t gH2 = (uint32_t)H * 2u;
+    const uint32_t out_rs = (uint32_t)H * 2u;
+    const size_t out_ts = (size_t)B * H * 2;
+    const bool pf_lane = uvalid && (lane & 7) == 0;  // one lane per 128-byte line of the warp's 512 bytes
     unsigned char eoc_raw = r1_eoc_raw(a.eoc, 0, T, B, b0, lane);
     const bool dbg = a.debug && blockIdx.x == 0 && tid == 0;
     uint32_t lapt = dbg ? (uint32_t)clock() : 0u;
@@ -420,23 +447,24 @@ rnn1_fwd_kernel(const __grid_constant__ CUtensorMap tm_hp, const __grid_constant
     auto body = [&](auto full_tag, int t) {
       constexpr bool FULL = decltype(full_tag)::value;
       // everything that does not depend on the recurrence is requested before waiting for the product
-      uint32_t xr0[NR], xr1[NR], xr2[NR];
-#pragma unroll
-      for (int n = 0; n < NR; ++n) {
-        const bool ok = uvalid && (FULL || nb + n < nvalid);
-        const char *p = xw_p + (uint32_t)n * xw_rs;
-        xr0[n] = ok ? r1_ld_raw16(p) : 0u;
-        xr1[n] = 0u; xr2[n] = 0u;
+      uint4 xq0 = make_uint4(0, 0, 0, 0), xq1 = xq0, xq2 = xq0;
+      if (uvalid) {
+        xq0 = __ldg(xw_p);
         if constexpr (CELL == 1) {
-          xr1[n] = ok ? r1_ld_raw16(p + gH2) : 0u;
-          xr2[n] = ok ? r1_ld_raw16(p + 2 * gH2) : 0u;
+          xq1 = __ldg(xw_p + H);
+          xq2 = __ldg(xw_p + 2 * H);
+          float hf[NR];
+#pragma unroll
+          for (int n = 0; n < NR; ++n) hf[n] = hcur[n];
+          act_p[3 * H] = r1_pack8(hf);  // the state fed to this step (BPTT reads it back in the same layout)
         }
       }
-      if (u0w < H && hh == 0) {
-        r1_prefetch(a.xw, 2, t + a.pf_dist, T, B, b0, G, u0w, lane, a.pf_l1);
+      if (pf_lane && t + a.pf_dist < T) {
+        const uint4 *pp = xw_p + (size_t)a.pf_dist * xw_ts;
+        r1_prefetch_line(pp, a.pf_l1);
         if constexpr (CELL == 1) {
-          r1_prefetch(a.xw, 2, t + a.pf_dist, T, B, b0, G, H + u0w, lane, a.pf_l1);
-          r1_prefetch(a.xw, 2, t + a.pf_dist, T, B, b0, G, 2 * H + u0w, lane, a.pf_l1);
+          r1_prefetch_line(pp + H, a.pf_l1);
+          r1_prefetch_line(pp + 2 * H, a.pf_l1);
         }
       }
       const uint32_t eoc_m = __ballot_sync(0xffffffffu, eoc_raw != 0);
@@ -451,8 +479,7 @@ rnn1_fwd_kernel(const __grid_constant__ CUtensorMap tm_hp, const __grid_constant
         R1_WAIT(bar_acc1, t & 1, 3);
         R1_LAP(1);
         tc_fence_after();
-#pragma unroll
-        for (int n = 0; n < NR; ++n) { r1_pin(xr0[n]); r1_pin(xr1[n]); }
+        r1_pin(xq0); r1_pin(xq1);
         uint32_t rr[NR], ru[NR];
         tc_ldn<NR>(lane_addr + (uint32_t)nb + (uint32_t)(mt * N), rr);
         tc_ldn<NR>(lane_addr + (uint32_t)nb + (uint32_t)((MU + mt) * N), ru);
@@ -460,30 +487,23 @@ rnn1_fwd_kernel(const __grid_constant__ CUtensorMap tm_hp, const __grid_constant
         float rg[NR];
 #pragma unroll
         for (int n = 0; n < NR; ++n) {
-          rg[n] = sigmoid_approx(__uint_as_float(rr[n]) + r1_bf16_of(xr0[n]));
-          ug[n] = sigmoid_approx(__uint_as_float(ru[n]) + r1_bf16_of(xr1[n]));
+          rg[n] = sigmoid_approx(__uint_as_float(rr[n]) + r1_bf16_at(xq0, n));
+          ug[n] = sigmoid_approx(__uint_as_float(ru[n]) + r1_bf16_at(xq1, n));
           if (uvalid) r1_sts_bf16(b2_gen + R1_BOFF(bcol, bch, nb + n), rg[n] * hcur[n]);
         }
         fence_proxy_async_smem();
         mbar_arrive(bar_op2);
         R1_LAP(2);
         if (uvalid) {
-#pragma unroll
-          for (int n = 0; n < NR; ++n) {
-            if (FULL || nb + n < nvalid) {
-              char *p = act_p + (uint32_t)n * act_rs;
-              *reinterpret_cast<__nv_bfloat16 *>(p) = __float2bfloat16_rn(rg[n]);
-              *reinterpret_cast<__nv_bfloat16 *>(p + gH2) = __float2bfloat16_rn(ug[n]);
-            }
-          }
+          act_p[0] = r1_pack8(rg);
+          act_p[H] = r1_pack8(ug);
         }
         R1_LAP(3);
       }
       R1_WAIT(CELL == 1 ? bar_acc2 : bar_acc1, t & 1, 4);
       R1_LAP(4);
       tc_fence_after();
-#pragma unroll
-      for (int n = 0; n < NR; ++n) r1_pin(CELL == 1 ? xr2[n] : xr0[n]);
+      if constexpr (CELL == 1) r1_pin(xq2); else r1_pin(xq0);
       float x2[NR];
       uint32_t rc[NR];
       tc_ldn<NR>(lane_addr + (uint32_t)nb + (uint32_t)((CELL == 1 ? 2 * MU + mt : mt) * N), rc);
@@ -492,28 +512,25 @@ rnn1_fwd_kernel(const __grid_constant__ CUtensorMap tm_hp, const __grid_constant
       const uint32_t b1w = NB1 == 2 ? (uint32_t)(((t + 1) & 1) * btile) : 0u;
 #pragma unroll
       for (int n = 0; n < NR; ++n) {
-        const float cand = tanh_approx(__uint_as_float(rc[n]) + r1_bf16_of(CELL == 1 ? xr2[n] : xr0[n]));
+        const float cand = tanh_approx(__uint_as_float(rc[n]) + r1_bf16_at(CELL == 1 ? xq2 : xq0, n));
         h2[n] = CELL == 1 ? fmaf(ug[n], hcur[n] - cand, cand) : cand;   // u*h + (1-u)*c
         float hn = h2[n];
         if ((eoc_m >> (nb + n)) & 1u)  // eoc: back to the FED state (model.py:82-92); warp-uniform and rare
           hn = uvalid ? __ldg(a.state_in + (size_t)(b0 + nb + n) * H + unit) : 0.f;
         hcur[n] = hn;
         if (uvalid) r1_sts_bf16(b1_gen + b1w + R1_BOFF(bcol, bch, nb + n), hn);
-        if constexpr (CELL == 1) x2[n] = cand;
+        x2[n] = CELL == 1 ? cand : h2[n];
       }
       fence_proxy_async_smem();
         mbar_arrive(bar_op1);
       R1_LAP(5);
       // off the dependent chain: layer output (pre reset, dropout applied) and the activation BPTT needs
       if (uvalid) {
+        act_p[CELL == 1 ? 2 * H : 0] = r1_pack8(x2);  // gru: candidate; rnn: the tanh output
 #pragma unroll
-        for (int n = 0; n < NR; ++n) {
-          if (FULL || nb + n < nvalid) {
+        for (int n = 0; n < NR; ++n)
+          if (FULL || nb + n < nvalid)
             *reinterpret_cast<__nv_bfloat16 *>(out_p + (uint32_t)n * out_rs) = __float2bfloat16_rn(h2[n] * dsc[n]);
-            *reinterpret_cast<__nv_bfloat16 *>(act_p + (uint32_t)n * act_rs + (CELL == 1 ? 2 * gH2 : 0u)) =
-                __float2bfloat16_rn(CELL == 1 ? x2[n] : h2[n]);
-          }
-        }
       }
       xw_p += xw_ts; out_p += out_ts; act_p += act_ts;
       R1_LAP(6);
@@ -666,14 +683,13 @@ __global__ void __launch_bounds__(r1_threads(MU), 1) rnn1_bwd_kernel(const __gri
     const uint32_t bcol_u = r1_bcol(H + unit), bch_u = r1_bchunk(H + unit);
     uint8_t *b1_gen = s.gen + (s.s_b1 - s.base);
     uint8_t *b2_gen = s.gen + (s.s_b2 - s.base);
-    const int u0w = unit - lane;
-    // per-thread views of (t, b0, unit), walking backwards in t
-    const char *act_p = reinterpret_cast<const char *>(a.acts_bf + ((size_t)(T - 1) * B + b0 + nb) * G + unit);
-    const char *hp_p = reinterpret_cast<const char *>(a.hprev_bf + ((size_t)(T - 1) * B + b0 + nb) * H + unit);
-    const char *do_p = reinterpret_cast<const char *>(a.dout + ((size_t)(T - 1) * B + b0 + nb) * H + unit);
-    const uint32_t act_rs = (uint32_t)G * 2u, hp_rs = (uint32_t)H * 2u, do_rs = (uint32_t)H * 4u;
-    const size_t act_ts = (size_t)B * G * 2, hp_ts = (size_t)B * H * 2, do_ts = (size_t)B * H * 4;
-    const uint32_t gH2 = (uint32_t)H * 2u;
+    // per-thread views of (t, tile, unit) of the tile-transposed arrays, walking backwards in t
+    const int NT = (B + N - 1) / N, tile = blockIdx.x / CL;
+    const int AC = CELL == 1 ? 4 * H : H;
+    const size_t act_ts = (size_t)NT * 2 * AC, do_ts = (size_t)NT * 2 * H * 2;
+    const uint4 *act_p = a.acts_tt + (size_t)(T - 1) * act_ts + (size_t)(tile * 2 + hh) * AC + unit;
+    const float4 *do_p = a.dout_tt + (size_t)(T - 1) * do_ts + ((size_t)(tile * 2 + hh) * H + unit) * 2;
+    const bool pf_lane = uvalid && (lane & 7) == 0;
     unsigned char eoc_raw = r1_eoc_raw(a.eoc, T - 1, T, B, b0, lane);
     float dhc[NR];
 #pragma unroll
@@ -685,28 +701,28 @@ __global__ void __launch_bounds__(r1_threads(MU), 1) rnn1_bwd_kernel(const __gri
     auto body = [&](auto full_tag, int t, int st) {
       constexpr bool FULL = decltype(full_tag)::value;
       // saved activations and d(out) of the step: requested before waiting for the previous step's product
-      uint32_t ar0[NR], ar1[NR], ar2[NR], hr[NR];
-      float d_o[NR];
-#pragma unroll
-      for (int n = 0; n < NR; ++n) {
-        const bool ok = uvalid && (FULL || nb + n < nvalid);
-        const char *pa = act_p + (uint32_t)n * act_rs;
-        ar0[n] = ok ? r1_ld_raw16(pa) : 0u;
-        d_o[n] = ok ? __ldg(reinterpret_cast<const float *>(do_p + (uint32_t)n * do_rs)) : 0.f;
-        ar1[n] = 0u; ar2[n] = 0u; hr[n] = 0u;
+      uint4 aq0 = make_uint4(0, 0, 0, 0), aq1 = aq0, aq2 = aq0, hq = aq0;
+      float4 dq0 = make_float4(0.f, 0.f, 0.f, 0.f), dq1 = dq0;
+      if (uvalid) {
+        aq0 = __ldg(act_p);
+        dq0 = __ldg(do_p);
+        dq1 = __ldg(do_p + 1);
         if constexpr (CELL == 1) {
-          ar1[n] = ok ? r1_ld_raw16(pa + gH2) : 0u;
-          ar2[n] = ok ? r1_ld_raw16(pa + 2 * gH2) : 0u;
-          hr[n] = ok ? r1_ld_raw16(hp_p + (uint32_t)n * hp_rs) : 0u;
+          aq1 = __ldg(act_p + H);
+          aq2 = __ldg(act_p + 2 * H);
+          hq = __ldg(act_p + 3 * H);
         }
       }
-      if (u0w < H && hh == 0) {
-        r1_prefetch(a.dout, 4, t - a.pf_dist, T, B, b0, H, u0w, lane, a.pf_l1);
-        r1_prefetch(a.acts_bf, 2, t - a.pf_dist, T, B, b0, G, u0w, lane, a.pf_l1);
+      if (pf_lane && t - a.pf_dist >= 0) {
+        const uint4 *pa = act_p - (size_t)a.pf_dist * act_ts;
+        const float4 *pd = do_p - (size_t)a.pf_dist * do_ts;
+        r1_prefetch_line(pa, a.pf_l1);
+        r1_prefetch_line(pd, a.pf_l1);        // 8 lanes x 32 bytes = two lines
+        r1_prefetch_line(pd + 8, a.pf_l1);
         if constexpr (CELL == 1) {
-          r1_prefetch(a.acts_bf, 2, t - a.pf_dist, T, B, b0, G, H + u0w, lane, a.pf_l1);
-          r1_prefetch(a.acts_bf, 2, t - a.pf_dist, T, B, b0, G, 2 * H + u0w, lane, a.pf_l1);
-          r1_prefetch(a.hprev_bf, 2, t - a.pf_dist, T, B, b0, H, u0w, lane, a.pf_l1);
+          r1_prefetch_line(pa + H, a.pf_l1);
+          r1_prefetch_line(pa + 2 * H, a.pf_l1);
+          r1_prefetch_line(pa + 3 * H, a.pf_l1);
         }
       }
       const uint32_t eoc_m = __ballot_sync(0xffffffffu, eoc_raw != 0);
@@ -723,16 +739,16 @@ __global__ void __launch_bounds__(r1_threads(MU), 1) rnn1_bwd_kernel(const __gri
 #pragma unroll
         for (int n = 0; n < NR; ++n) dhc[n] = (CELL == 1 ? dhc[n] : 0.f) + __uint_as_float(r[n]);
       }
+      // (see r1_pin: the loads above stay in flight across the wait)
+      r1_pin(aq0); r1_pin(dq0.x); r1_pin(dq0.y); r1_pin(dq0.z); r1_pin(dq0.w); r1_pin(dq1.x); r1_pin(dq1.y); r1_pin(dq1.z); r1_pin(dq1.w);
+      if constexpr (CELL == 1) { r1_pin(aq1); r1_pin(aq2); r1_pin(hq); }
+      const float d_o[NR] = {dq0.x, dq0.y, dq0.z, dq0.w, dq1.x, dq1.y, dq1.z, dq1.w};
       float a0[NR], a1[NR], a2[NR], hv[NR];
 #pragma unroll
-      for (int n = 0; n < NR; ++n) {  // (see r1_pin: the loads above stay in flight across the wait)
-        r1_pin(ar0[n]); r1_pin(d_o[n]);
-        a0[n] = r1_bf16_of(ar0[n]);
+      for (int n = 0; n < NR; ++n) {
+        a0[n] = r1_bf16_at(aq0, n);
         a1[n] = 0.f; a2[n] = 0.f; hv[n] = 0.f;
-        if constexpr (CELL == 1) {
-          r1_pin(ar1[n]); r1_pin(ar2[n]); r1_pin(hr[n]);
-          a1[n] = r1_bf16_of(ar1[n]); a2[n] = r1_bf16_of(ar2[n]); hv[n] = r1_bf16_of(hr[n]);
-        }
+        if constexpr (CELL == 1) { a1[n] = r1_bf16_at(aq1, n); a2[n] = r1_bf16_at(aq2, n); hv[n] = r1_bf16_at(hq, n); }
       }
       R1_LAP(1);
       if constexpr (CELL == 2) {
@@ -785,7 +801,7 @@ __global__ void __launch_bounds__(r1_threads(MU), 1) rnn1_bwd_kernel(const __gri
         mbar_arrive(bar_op2);
         R1_LAP(5);
       }
-      act_p -= act_ts; hp_p -= hp_ts; do_p -= do_ts;
+      act_p -= act_ts; do_p -= do_ts;
     };
     for (int t = T - 1, st = 0; t >= 0; --t, ++st) {
       if (nvalid == N) body(std::true_type{}, t, st); else body(std::false_type{}, t, st);
@@ -843,6 +859,22 @@ __global__ void r1_pack_kernel(R1PackArgs p, uint8_t *__restrict__ dst) {
   }
 }
 
+// [T][B][ld >= C] row-major -> tile-transposed [T][NT][2][C][8] (rows past the batch: zero).  One thread per 8 values.
+template <typename E>
+__global__ void r1_tt_kernel(const E *__restrict__ in, int ld, E *__restrict__ out, int B, int C, int NT) {
+  const int col = blockIdx.y * blockDim.x + threadIdx.x;
+  if (col >= C) return;
+  const int hh = blockIdx.x & 1, tile = (blockIdx.x >> 1) % NT, t = (blockIdx.x >> 1) / NT;
+  const int b = tile * R1_N + hh * 8;
+  alignas(16) E v[8];
+#pragma unroll
+  for (int n = 0; n < 8; ++n) v[n] = (b + n < B) ? in[((size_t)t * B + b + n) * ld + col] : E(0.f);
+  uint4 *dst = reinterpret_cast<uint4 *>(out + ((size_t)blockIdx.x * C + col) * 8);
+  const uint4 *src = reinterpret_cast<const uint4 *>(v);
+#pragma unroll
+  for (int i = 0; i < (int)(8 * sizeof(E) / 16); ++i) dst[i] = src[i];
+}
+
 }  // namespace
 
 bool sk_rnn1_tc_eligible(const skrnn_handle *h) {
@@ -871,6 +903,7 @@ int sk_rnn1_tc_layer(skrnn_handle *h, cudaStream_t st, bool bwd, int l, int B, i
   if (!sk_rnn1_tc_eligible(h)) return -1;
   const int H = h->H, G = h->G, cell = h->cfg.cell;
   const bool gru = cell == SKRNN_CELL_GRU;
+  if (h->ws.xw_tt == nullptr || h->ws.dout_tt == nullptr || h->ws.tt_rows < (int64_t)T * ((B + R1_N - 1) / R1_N) * R1_N) return -1;
   if (h->ws.acts_bf[l] == nullptr || h->ws.out_bf[l] == nullptr || h->ws.hprev_bf[l] == nullptr || h->ws.dpre_bf == nullptr ||
       h->ws.xw_il[l] == nullptr || (gru && h->ws.aux_bf[l] == nullptr))
     return -1;
@@ -968,9 +1001,10 @@ int sk_rnn1_tc_layer(skrnn_handle *h, cudaStream_t st, bool bwd, int l, int B, i
   a.keep = h->cfg.keep_prob;
   a.seed = seed;
   a.eoc = h->ws.eoc; a.state_in = state_in; a.state_out = state_out; a.mask = mask;
-  a.xw = h->ws.xw_il[l];
-  a.out_bf = h->ws.out_bf[l]; a.hprev_bf = h->ws.hprev_bf[l]; a.acts_bf = h->ws.acts_bf[l];
-  a.dout = h->ws.dout;
+  a.xw_tt = reinterpret_cast<const uint4 *>(h->ws.xw_tt);
+  a.out_bf = h->ws.out_bf[l]; a.hprev_bf = h->ws.hprev_bf[l];
+  a.acts_tt = reinterpret_cast<uint4 *>(h->ws.acts_bf[l]);  // (allocated with the tile-transposed size for these cells)
+  a.dout_tt = reinterpret_cast<const float4 *>(h->ws.dout_tt);
   a.dbias0 = h->grads + lp.b[0];
   a.dbias1 = gru ? h->grads + lp.b[1] : nullptr;
   a.wimg = reinterpret_cast<const uint8_t *>(h->ws.wpack);
@@ -1015,6 +1049,12 @@ int sk_rnn1_tc_layer(skrnn_handle *h, cudaStream_t st, bool bwd, int l, int B, i
     CUtensorMap tm_hp, tm_aux;
     SK_TRY(r1_map(&tm_hp, h->ws.hprev_bf[l], H, B, T));
     SK_TRY(r1_map(&tm_aux, gru ? h->ws.aux_bf[l] : h->ws.hprev_bf[l], H, B, T));
+    {  // the hoisted projection in the layout the elementwise threads read
+      SkLaunch scope(h, st, SK_CAT_MISC);
+      const int NT = (B + R1_N - 1) / R1_N;
+      r1_tt_kernel<__nv_bfloat16><<<dim3((unsigned)(T * NT * 2), (unsigned)((G + 255) / 256)), 256, 0, st>>>(h->ws.xw_il[l], G, h->ws.xw_tt, B, G, NT);
+      SK_CUDA(cudaGetLastError());
+    }
     SkLaunch scope(h, st, SK_CAT_RNN_FWD);
 #define R1_FWD(MUV, KBV, CLV)                                                                                     \
   do {                                                                                                            \
@@ -1027,6 +1067,12 @@ int sk_rnn1_tc_layer(skrnn_handle *h, cudaStream_t st, bool bwd, int l, int B, i
   } else {
     CUtensorMap tm_dp;
     SK_TRY(r1_map(&tm_dp, h->ws.dpre_bf, G, B, T));
+    {  // d(out) of the layer in the layout the elementwise threads read
+      SkLaunch scope(h, st, SK_CAT_MISC);
+      const int NT = (B + R1_N - 1) / R1_N;
+      r1_tt_kernel<float><<<dim3((unsigned)(T * NT * 2), (unsigned)((H + 255) / 256)), 256, 0, st>>>(h->ws.dout, H, h->ws.dout_tt, B, H, NT);
+      SK_CUDA(cudaGetLastError());
+    }
     SkLaunch scope(h, st, SK_CAT_RNN_BWD);
 #define R1_BWD(MUV, KBV, CLV)                                                                                     \
   do {                                                                                                            \
