@@ -32,10 +32,13 @@
 namespace {
 
 constexpr int R1_N = 16;          // batch rows per CTA (MMA N)
-constexpr int R1_NR = 8;          // of which one elementwise thread handles 8 (for its unit): two warps per (m-tile, lane quarter)
+// An elementwise thread handles NR = 4 * MU of the 16 rows for its unit (MU = 128-unit m-tiles of the CTA): always 16
+// elementwise warps -- 4 TMEM lane quarters x (16 / NR) row groups x MU m-tiles -- so that a one-m-tile CTA splits the
+// per-step chain over twice the threads (these warps are instruction-latency bound, not issue bound).
+constexpr int R1_EW = 16;
+constexpr int R1_THREADS = 32 * (R1_EW + 1);
 constexpr int R1_MAX_TILES = 6;
-// threads of a CTA with MU m-tiles of hidden units: 8 elementwise warps per m-tile, then the MMA warp
-__host__ __device__ constexpr int r1_threads(int mu) { return 32 * (8 * mu + 1); }
+
 
 struct R1Tile {   // one 128-row weight tile (MMA A operand), K = 64 * nkb
   int in_tmem;    // 1: tensor memory at column `off`; 0: shared memory at byte offset `off`
@@ -56,10 +59,10 @@ struct R1Args {
   const float *state_in;     // [B,H]
   float *state_out;
   const float *mask;         // [B,T,H] or null
-  const uint4 *xw_tt;        // tile-transposed bf16 [.., G, 8]: hoisted x*Wx + b
+  const char *xw_tt;         // tile-transposed bf16 [.., G, NR]: hoisted x*Wx + b
   __nv_bfloat16 *out_bf, *hprev_bf;
-  uint4 *acts_tt;            // tile-transposed bf16 [.., AC, 8]: gru r, u, candidate, h fed (AC = 4H); rnn: tanh output (AC = H)
-  const float4 *dout_tt;     // tile-transposed fp32 [.., H, 8]
+  char *acts_tt;             // tile-transposed bf16 [.., AC, NR]: gru r, u, candidate, h fed (AC = 4H); rnn: tanh output (AC = H)
+  const char *dout_tt;       // tile-transposed fp32 [.., H, NR]
   float *dbias0, *dbias1;
   const uint8_t *wimg;
   int wimg_rank_bytes;       // cluster of 2: each rank's tiles are a separate image
@@ -171,23 +174,58 @@ __device__ __forceinline__ void r1_pin(uint32_t &v) { asm volatile("" : "+r"(v))
 __device__ __forceinline__ void r1_pin(float &v) { asm volatile("" : "+f"(v)); }
 __device__ __forceinline__ float r1_bf16_of(uint32_t raw) { return __uint_as_float(raw << 16); }
 // Per-step arrays the elementwise threads read or write for THEMSELVES are kept "tile-transposed":
-//   X_tt[t][batch tile of 16][half of 8 rows][column][8 rows]
-// so that a thread (one column = hidden unit, 8 batch rows) moves its 8 values with ONE 16-byte access, coalesced
-// across the warp's 32 units -- instead of 8 two-byte accesses with 8 address computations.  Rows past the batch are
+//   X_tt[t][batch tile of 16][row group of NR][column][NR rows]
+// so that a thread (one column = hidden unit, NR batch rows) moves its NR values with ONE vector access, coalesced
+// across the warp's 32 units -- instead of NR two-byte accesses with NR address computations.  Rows past the batch are
 // zero (r1_tt_kernel) or finite (written by the forward kernel).
-__device__ __forceinline__ void r1_pin(uint4 &v) { r1_pin(v.x); r1_pin(v.y); r1_pin(v.z); r1_pin(v.w); }
-__device__ __forceinline__ float r1_bf16_at(const uint4 &v, int n) {  // n is a compile-time constant after unrolling
-  const uint32_t w = (n >> 1) == 0 ? v.x : (n >> 1) == 1 ? v.y : (n >> 1) == 2 ? v.z : v.w;
+template <int NR> struct R1G { uint32_t w[NR / 2]; };  // NR bf16 values
+template <int NR>
+__device__ __forceinline__ R1G<NR> r1_ld_group(const char *p) {
+  R1G<NR> g;
+  if constexpr (NR == 8) {
+    const uint4 v = __ldg(reinterpret_cast<const uint4 *>(p));
+    g.w[0] = v.x; g.w[1] = v.y; g.w[2] = v.z; g.w[3] = v.w;
+  } else {
+    const uint2 v = __ldg(reinterpret_cast<const uint2 *>(p));
+    g.w[0] = v.x; g.w[1] = v.y;
+  }
+  return g;
+}
+template <int NR>
+__device__ __forceinline__ R1G<NR> r1_zero_group() {
+  R1G<NR> g;
+#pragma unroll
+  for (int i = 0; i < NR / 2; ++i) g.w[i] = 0u;
+  return g;
+}
+template <int NR>
+__device__ __forceinline__ void r1_pin(R1G<NR> &g) {
+#pragma unroll
+  for (int i = 0; i < NR / 2; ++i) r1_pin(g.w[i]);
+}
+template <int NR>
+__device__ __forceinline__ float r1_at(const R1G<NR> &g, int n) {  // n is a compile-time constant after unrolling
+  const uint32_t w = g.w[n >> 1];
   return __uint_as_float((n & 1) ? (w & 0xffff0000u) : (w << 16));
 }
-__device__ __forceinline__ uint4 r1_pack8(const float (&v)[8]) {
-  uint4 r;
-  __nv_bfloat162 p;
-  p = __floats2bfloat162_rn(v[0], v[1]); r.x = *reinterpret_cast<const uint32_t *>(&p);
-  p = __floats2bfloat162_rn(v[2], v[3]); r.y = *reinterpret_cast<const uint32_t *>(&p);
-  p = __floats2bfloat162_rn(v[4], v[5]); r.z = *reinterpret_cast<const uint32_t *>(&p);
-  p = __floats2bfloat162_rn(v[6], v[7]); r.w = *reinterpret_cast<const uint32_t *>(&p);
-  return r;
+template <int NR>
+__device__ __forceinline__ void r1_st_group(char *p, const float (&v)[NR]) {
+  uint32_t w[NR / 2];
+#pragma unroll
+  for (int i = 0; i < NR / 2; ++i) {
+    const __nv_bfloat162 b = __floats2bfloat162_rn(v[2 * i], v[2 * i + 1]);
+    w[i] = *reinterpret_cast<const uint32_t *>(&b);
+  }
+  if constexpr (NR == 8) *reinterpret_cast<uint4 *>(p) = make_uint4(w[0], w[1], w[2], w[3]);
+  else *reinterpret_cast<uint2 *>(p) = make_uint2(w[0], w[1]);
+}
+template <int NR>
+__device__ __forceinline__ void r1_ld_f32(const char *p, float (&d)[NR]) {
+#pragma unroll
+  for (int i = 0; i < NR / 4; ++i) {
+    const float4 v = __ldg(reinterpret_cast<const float4 *>(p) + i);
+    d[4 * i] = v.x; d[4 * i + 1] = v.y; d[4 * i + 2] = v.z; d[4 * i + 3] = v.w;
+  }
 }
 __device__ __forceinline__ void r1_prefetch_line(const void *p, int l1) {
   if (l1) asm volatile("prefetch.global.L1 [%0];" ::"l"(p));
@@ -271,18 +309,19 @@ __device__ __forceinline__ unsigned char r1_eoc_raw(const unsigned char *eoc, in
 }
 
 // per-step output-dropout scale of (row b0+n, t, unit): 1/keep or 0 (model.py:29-30); 1 when dropout is off.  Rows past
-// the batch get a scale too (their values are never stored).  The thread's rows are [nb, nb + R1_NR) of the tile.
+// the batch get a scale too (their values are never stored).  The thread's rows are [nb, nb + NR) of the tile.
+template <int NR>
 __device__ __forceinline__ void r1_drop_scales(const R1Args &a, int t, int b0, int nb, int nvalid, int unit, bool uvalid,
-                                               uint32_t drop_unit, float (&dsc)[R1_NR]) {
+                                               uint32_t drop_unit, float (&dsc)[NR]) {
 #pragma unroll
-  for (int n = 0; n < R1_NR; ++n) dsc[n] = 1.0f;
+  for (int n = 0; n < NR; ++n) dsc[n] = 1.0f;
   if (!a.dropout || !uvalid) return;
   const float inv_keep = 1.0f / a.keep;
   if (a.mask != nullptr) {  // injected mask (parity tests)
     const float *mp = a.mask + ((size_t)(b0 + nb) * a.T + t) * a.H + unit;
     const size_t rs = (size_t)a.T * a.H;
 #pragma unroll
-    for (int n = 0; n < R1_NR; ++n)
+    for (int n = 0; n < NR; ++n)
       if (nb + n < nvalid) dsc[n] = __ldg(mp + n * rs) * inv_keep;
     return;
   }
@@ -290,7 +329,7 @@ __device__ __forceinline__ void r1_drop_scales(const R1Args &a, int t, int b0, i
   const uint32_t row = (uint32_t)(a.row0 + b0 + nb);
   const float keep = a.keep;
 #pragma unroll
-  for (int n = 0; n < R1_NR; ++n) dsc[n] = skm_u01(skm_drop_finish(pre, row + (uint32_t)n)) < keep ? inv_keep : 0.0f;
+  for (int n = 0; n < NR; ++n) dsc[n] = skm_u01(skm_drop_finish(pre, row + (uint32_t)n)) < keep ? inv_keep : 0.0f;
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -298,7 +337,7 @@ __device__ __forceinline__ void r1_drop_scales(const R1Args &a, int t, int b0, i
 // ------------------------------------------------------------------------------------------------
 // MU: m-tiles (128 hidden units each) of THIS CTA; NKB: k-blocks of the contraction (all H units); CL: CTAs per cluster
 template <int CELL, int MU, int NKB, int CL>
-__global__ void __launch_bounds__(r1_threads(MU), 1)
+__global__ void __launch_bounds__(R1_THREADS, 1)
 rnn1_fwd_kernel(const __grid_constant__ CUtensorMap tm_hp, const __grid_constant__ CUtensorMap tm_aux, R1Args a) {
   constexpr int N = R1_N;
   constexpr int NB1 = CELL == 2 ? 2 : 1;  // rnn: the h tile is double-buffered (see the store ordering below)
@@ -310,7 +349,7 @@ rnn1_fwd_kernel(const __grid_constant__ CUtensorMap tm_hp, const __grid_constant
   const uint32_t bar_op1 = s.s_bar, bar_acc1 = s.s_bar + 8, bar_op2 = s.s_bar + 16, bar_acc2 = s.s_bar + 24;
   const uint32_t tmem_holder = s.s_bar + 32, bar_rx1 = s.s_bar + 40, bar_rx2 = s.s_bar + 48;  // rx: the peer's k-blocks have landed
   volatile uint32_t *tmem_holder_ptr = reinterpret_cast<volatile uint32_t *>(s.gen + (tmem_holder - s.base));
-  constexpr int EW = 8 * MU, THREADS = r1_threads(MU);
+  constexpr int EW = R1_EW, THREADS = R1_THREADS;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int rank = CL == 1 ? 0 : (int)r1_cluster_rank();
   const int b0 = (blockIdx.x / CL) * N;
@@ -342,8 +381,8 @@ rnn1_fwd_kernel(const __grid_constant__ CUtensorMap tm_hp, const __grid_constant
   const uint32_t tmem_base = *tmem_holder_ptr;
   r1_load_tmem_tiles(a, wimg, tmem_base, warp, lane);
 
-  constexpr int NR = R1_NR;
-  const int q = warp & 3, hh = (warp >> 2) & 1, mt = warp >> 3;
+  constexpr int NR = 4 * MU, RG = R1_N / NR;  // rows per thread, row groups
+  const int q = warp & 3, hh = (warp >> 2) % RG, mt = warp / (4 * RG);
   const int nb = NR * hh;  // my rows of the tile: [nb, nb + NR)
   const bool active = warp < EW;
   const int unit = (rank * MU + mt) * 128 + 32 * q + lane;
@@ -433,13 +472,15 @@ rnn1_fwd_kernel(const __grid_constant__ CUtensorMap tm_hp, const __grid_constant
     // per-thread views of (t, b0, unit) of the step's arrays: base pointer advanced per step, row n at n * row stride
     const int NT = (B + N - 1) / N, tile = blockIdx.x / CL;
     const int AC = CELL == 1 ? 4 * H : H;
-    const uint4 *xw_p = a.xw_tt + (size_t)(tile * 2 + hh) * G + unit;
-    uint4 *act_p = a.acts_tt + (size_t)(tile * 2 + hh) * AC + unit;
-    const size_t xw_ts = (size_t)NT * 2 * G, act_ts = (size_t)NT * 2 * AC;
+    constexpr int GB = NR * 2;  // bytes of one thread's group of bf16 values
+    const char *xw_p = a.xw_tt + ((size_t)(tile * RG + hh) * G + unit) * GB;
+    char *act_p = a.acts_tt + ((size_t)(tile * RG + hh) * AC + unit) * GB;
+    const size_t xw_ts = (size_t)NT * RG * G * GB, act_ts = (size_t)NT * RG * AC * GB;
+    const uint32_t gs = (uint32_t)H * GB;  // from one gate's plane to the next
     char *out_p = reinterpret_cast<char *>(a.out_bf + (size_t)(b0 + nb) * H + unit);
     const uint32_t out_rs = (uint32_t)H * 2u;
     const size_t out_ts = (size_t)B * H * 2;
-    const bool pf_lane = uvalid && (lane & 7) == 0;  // one lane per 128-byte line of the warp's 512 bytes
+    const bool pf_lane = uvalid && (lane * GB) % 128 == 0;  // one lane per 128-byte line of the warp's groups
     unsigned char eoc_raw = r1_eoc_raw(a.eoc, 0, T, B, b0, lane);
     const bool dbg = a.debug && blockIdx.x == 0 && tid == 0;
     uint32_t lapt = dbg ? (uint32_t)clock() : 0u;
@@ -447,30 +488,27 @@ rnn1_fwd_kernel(const __grid_constant__ CUtensorMap tm_hp, const __grid_constant
     auto body = [&](auto full_tag, int t) {
       constexpr bool FULL = decltype(full_tag)::value;
       // everything that does not depend on the recurrence is requested before waiting for the product
-      uint4 xq0 = make_uint4(0, 0, 0, 0), xq1 = xq0, xq2 = xq0;
+      R1G<NR> xq0 = r1_zero_group<NR>(), xq1 = xq0, xq2 = xq0;
       if (uvalid) {
-        xq0 = __ldg(xw_p);
+        xq0 = r1_ld_group<NR>(xw_p);
         if constexpr (CELL == 1) {
-          xq1 = __ldg(xw_p + H);
-          xq2 = __ldg(xw_p + 2 * H);
-          float hf[NR];
-#pragma unroll
-          for (int n = 0; n < NR; ++n) hf[n] = hcur[n];
-          act_p[3 * H] = r1_pack8(hf);  // the state fed to this step (BPTT reads it back in the same layout)
+          xq1 = r1_ld_group<NR>(xw_p + gs);
+          xq2 = r1_ld_group<NR>(xw_p + 2 * gs);
+          r1_st_group<NR>(act_p + 3 * gs, hcur);  // the state fed to this step (BPTT reads it back in the same layout)
         }
       }
       if (pf_lane && t + a.pf_dist < T) {
-        const uint4 *pp = xw_p + (size_t)a.pf_dist * xw_ts;
+        const char *pp = xw_p + (size_t)a.pf_dist * xw_ts;
         r1_prefetch_line(pp, a.pf_l1);
         if constexpr (CELL == 1) {
-          r1_prefetch_line(pp + H, a.pf_l1);
-          r1_prefetch_line(pp + 2 * H, a.pf_l1);
+          r1_prefetch_line(pp + gs, a.pf_l1);
+          r1_prefetch_line(pp + 2 * gs, a.pf_l1);
         }
       }
       const uint32_t eoc_m = __ballot_sync(0xffffffffu, eoc_raw != 0);
       eoc_raw = r1_eoc_raw(a.eoc, t + 1, T, B, b0, lane);
       float dsc[NR];
-      r1_drop_scales(a, t, b0, nb, nvalid, unit, uvalid, drop_unit, dsc);
+      r1_drop_scales<NR>(a, t, b0, nb, nvalid, unit, uvalid, drop_unit, dsc);
       float ug[NR];
 #pragma unroll
       for (int n = 0; n < NR; ++n) ug[n] = 0.f;
@@ -479,7 +517,7 @@ rnn1_fwd_kernel(const __grid_constant__ CUtensorMap tm_hp, const __grid_constant
         R1_WAIT(bar_acc1, t & 1, 3);
         R1_LAP(1);
         tc_fence_after();
-        r1_pin(xq0); r1_pin(xq1);
+        r1_pin<NR>(xq0); r1_pin<NR>(xq1);
         uint32_t rr[NR], ru[NR];
         tc_ldn<NR>(lane_addr + (uint32_t)nb + (uint32_t)(mt * N), rr);
         tc_ldn<NR>(lane_addr + (uint32_t)nb + (uint32_t)((MU + mt) * N), ru);
@@ -487,23 +525,23 @@ rnn1_fwd_kernel(const __grid_constant__ CUtensorMap tm_hp, const __grid_constant
         float rg[NR];
 #pragma unroll
         for (int n = 0; n < NR; ++n) {
-          rg[n] = sigmoid_approx(__uint_as_float(rr[n]) + r1_bf16_at(xq0, n));
-          ug[n] = sigmoid_approx(__uint_as_float(ru[n]) + r1_bf16_at(xq1, n));
+          rg[n] = sigmoid_approx(__uint_as_float(rr[n]) + r1_at<NR>(xq0, n));
+          ug[n] = sigmoid_approx(__uint_as_float(ru[n]) + r1_at<NR>(xq1, n));
           if (uvalid) r1_sts_bf16(b2_gen + R1_BOFF(bcol, bch, nb + n), rg[n] * hcur[n]);
         }
         fence_proxy_async_smem();
         mbar_arrive(bar_op2);
         R1_LAP(2);
         if (uvalid) {
-          act_p[0] = r1_pack8(rg);
-          act_p[H] = r1_pack8(ug);
+          r1_st_group<NR>(act_p, rg);
+          r1_st_group<NR>(act_p + gs, ug);
         }
         R1_LAP(3);
       }
       R1_WAIT(CELL == 1 ? bar_acc2 : bar_acc1, t & 1, 4);
       R1_LAP(4);
       tc_fence_after();
-      if constexpr (CELL == 1) r1_pin(xq2); else r1_pin(xq0);
+      if constexpr (CELL == 1) r1_pin<NR>(xq2); else r1_pin<NR>(xq0);
       float x2[NR];
       uint32_t rc[NR];
       tc_ldn<NR>(lane_addr + (uint32_t)nb + (uint32_t)((CELL == 1 ? 2 * MU + mt : mt) * N), rc);
@@ -512,7 +550,7 @@ rnn1_fwd_kernel(const __grid_constant__ CUtensorMap tm_hp, const __grid_constant
       const uint32_t b1w = NB1 == 2 ? (uint32_t)(((t + 1) & 1) * btile) : 0u;
 #pragma unroll
       for (int n = 0; n < NR; ++n) {
-        const float cand = tanh_approx(__uint_as_float(rc[n]) + r1_bf16_at(CELL == 1 ? xq2 : xq0, n));
+        const float cand = tanh_approx(__uint_as_float(rc[n]) + r1_at<NR>(CELL == 1 ? xq2 : xq0, n));
         h2[n] = CELL == 1 ? fmaf(ug[n], hcur[n] - cand, cand) : cand;   // u*h + (1-u)*c
         float hn = h2[n];
         if ((eoc_m >> (nb + n)) & 1u)  // eoc: back to the FED state (model.py:82-92); warp-uniform and rare
@@ -526,7 +564,7 @@ rnn1_fwd_kernel(const __grid_constant__ CUtensorMap tm_hp, const __grid_constant
       R1_LAP(5);
       // off the dependent chain: layer output (pre reset, dropout applied) and the activation BPTT needs
       if (uvalid) {
-        act_p[CELL == 1 ? 2 * H : 0] = r1_pack8(x2);  // gru: candidate; rnn: the tanh output
+        r1_st_group<NR>(act_p + (CELL == 1 ? 2 * gs : 0u), x2);  // gru: candidate; rnn: the tanh output
 #pragma unroll
         for (int n = 0; n < NR; ++n)
           if (FULL || nb + n < nvalid)
@@ -558,7 +596,7 @@ rnn1_fwd_kernel(const __grid_constant__ CUtensorMap tm_hp, const __grid_constant
 // backward (BPTT).  d(pre-activation) leaves as TMA stores of the operand tiles: no per-thread global stores.
 // ------------------------------------------------------------------------------------------------
 template <int CELL, int MU, int NKB, int CL>
-__global__ void __launch_bounds__(r1_threads(MU), 1) rnn1_bwd_kernel(const __grid_constant__ CUtensorMap tm_dp, R1Args a) {
+__global__ void __launch_bounds__(R1_THREADS, 1) rnn1_bwd_kernel(const __grid_constant__ CUtensorMap tm_dp, R1Args a) {
   constexpr int N = R1_N;
   constexpr int NB1 = CELL == 2 ? 2 : 1;
   extern __shared__ uint8_t smem_raw[];
@@ -570,7 +608,7 @@ __global__ void __launch_bounds__(r1_threads(MU), 1) rnn1_bwd_kernel(const __gri
   const uint32_t bar_op1 = s.s_bar, bar_acc1 = s.s_bar + 8, bar_op2 = s.s_bar + 16, bar_acc2 = s.s_bar + 24;
   const uint32_t tmem_holder = s.s_bar + 32, bar_rx1 = s.s_bar + 40, bar_rx2 = s.s_bar + 48;  // rx: the peer's k-blocks have landed
   volatile uint32_t *tmem_holder_ptr = reinterpret_cast<volatile uint32_t *>(s.gen + (tmem_holder - s.base));
-  constexpr int EW = 8 * MU, THREADS = r1_threads(MU);
+  constexpr int EW = R1_EW, THREADS = R1_THREADS;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int rank = CL == 1 ? 0 : (int)r1_cluster_rank();
   const int b0 = (blockIdx.x / CL) * N;
@@ -605,8 +643,8 @@ __global__ void __launch_bounds__(r1_threads(MU), 1) rnn1_bwd_kernel(const __gri
   if constexpr (CL > 1) r1_cluster_sync();  // the peer's tiles are zeroed and its barriers initialised before anything is sent there
   tc_fence_after();
 
-  constexpr int NR = R1_NR;
-  const int q = warp & 3, hh = (warp >> 2) & 1, mt = warp >> 3;
+  constexpr int NR = 4 * MU, RG = R1_N / NR;  // rows per thread, row groups
+  const int q = warp & 3, hh = (warp >> 2) % RG, mt = warp / (4 * RG);
   const int nb = NR * hh;  // my rows of the tile: [nb, nb + NR)
   const bool active = warp < EW;
   const int unit = (rank * MU + mt) * 128 + 32 * q + lane;
@@ -686,10 +724,12 @@ __global__ void __launch_bounds__(r1_threads(MU), 1) rnn1_bwd_kernel(const __gri
     // per-thread views of (t, tile, unit) of the tile-transposed arrays, walking backwards in t
     const int NT = (B + N - 1) / N, tile = blockIdx.x / CL;
     const int AC = CELL == 1 ? 4 * H : H;
-    const size_t act_ts = (size_t)NT * 2 * AC, do_ts = (size_t)NT * 2 * H * 2;
-    const uint4 *act_p = a.acts_tt + (size_t)(T - 1) * act_ts + (size_t)(tile * 2 + hh) * AC + unit;
-    const float4 *do_p = a.dout_tt + (size_t)(T - 1) * do_ts + ((size_t)(tile * 2 + hh) * H + unit) * 2;
-    const bool pf_lane = uvalid && (lane & 7) == 0;
+    constexpr int GB = NR * 2, DB = NR * 4;  // bytes of one thread's group of bf16 / fp32 values
+    const size_t act_ts = (size_t)NT * RG * AC * GB, do_ts = (size_t)NT * RG * H * DB;
+    const char *act_p = a.acts_tt + (size_t)(T - 1) * act_ts + ((size_t)(tile * RG + hh) * AC + unit) * GB;
+    const char *do_p = a.dout_tt + (size_t)(T - 1) * do_ts + ((size_t)(tile * RG + hh) * H + unit) * DB;
+    const uint32_t gs = (uint32_t)H * GB;
+    const bool pf_lane = uvalid && (lane * GB) % 128 == 0, pf_lane_d = uvalid && (lane * DB) % 128 == 0;
     unsigned char eoc_raw = r1_eoc_raw(a.eoc, T - 1, T, B, b0, lane);
     float dhc[NR];
 #pragma unroll
@@ -701,34 +741,35 @@ __global__ void __launch_bounds__(r1_threads(MU), 1) rnn1_bwd_kernel(const __gri
     auto body = [&](auto full_tag, int t, int st) {
       constexpr bool FULL = decltype(full_tag)::value;
       // saved activations and d(out) of the step: requested before waiting for the previous step's product
-      uint4 aq0 = make_uint4(0, 0, 0, 0), aq1 = aq0, aq2 = aq0, hq = aq0;
-      float4 dq0 = make_float4(0.f, 0.f, 0.f, 0.f), dq1 = dq0;
+      R1G<NR> aq0 = r1_zero_group<NR>(), aq1 = aq0, aq2 = aq0, hq = aq0;
+      float d_o[NR];
+#pragma unroll
+      for (int n = 0; n < NR; ++n) d_o[n] = 0.f;
       if (uvalid) {
-        aq0 = __ldg(act_p);
-        dq0 = __ldg(do_p);
-        dq1 = __ldg(do_p + 1);
+        aq0 = r1_ld_group<NR>(act_p);
+        r1_ld_f32<NR>(do_p, d_o);
         if constexpr (CELL == 1) {
-          aq1 = __ldg(act_p + H);
-          aq2 = __ldg(act_p + 2 * H);
-          hq = __ldg(act_p + 3 * H);
+          aq1 = r1_ld_group<NR>(act_p + gs);
+          aq2 = r1_ld_group<NR>(act_p + 2 * gs);
+          hq = r1_ld_group<NR>(act_p + 3 * gs);
         }
       }
-      if (pf_lane && t - a.pf_dist >= 0) {
-        const uint4 *pa = act_p - (size_t)a.pf_dist * act_ts;
-        const float4 *pd = do_p - (size_t)a.pf_dist * do_ts;
-        r1_prefetch_line(pa, a.pf_l1);
-        r1_prefetch_line(pd, a.pf_l1);        // 8 lanes x 32 bytes = two lines
-        r1_prefetch_line(pd + 8, a.pf_l1);
-        if constexpr (CELL == 1) {
-          r1_prefetch_line(pa + H, a.pf_l1);
-          r1_prefetch_line(pa + 2 * H, a.pf_l1);
-          r1_prefetch_line(pa + 3 * H, a.pf_l1);
+      if (t - a.pf_dist >= 0) {
+        if (pf_lane_d) r1_prefetch_line(do_p - (size_t)a.pf_dist * do_ts, a.pf_l1);
+        if (pf_lane) {
+          const char *pa = act_p - (size_t)a.pf_dist * act_ts;
+          r1_prefetch_line(pa, a.pf_l1);
+          if constexpr (CELL == 1) {
+            r1_prefetch_line(pa + gs, a.pf_l1);
+            r1_prefetch_line(pa + 2 * gs, a.pf_l1);
+            r1_prefetch_line(pa + 3 * gs, a.pf_l1);
+          }
         }
       }
       const uint32_t eoc_m = __ballot_sync(0xffffffffu, eoc_raw != 0);
       eoc_raw = r1_eoc_raw(a.eoc, t - 1, T, B, b0, lane);
       float dsc[NR];
-      r1_drop_scales(a, t, b0, nb, nvalid, unit, uvalid, drop_unit, dsc);
+      r1_drop_scales<NR>(a, t, b0, nb, nvalid, unit, uvalid, drop_unit, dsc);
       R1_LAP(0);
       if (st > 0) {  // d(h_t) from the step after: the product issued last iteration
         R1_WAIT(CELL == 1 ? bar_acc2 : bar_acc1, (st - 1) & 1, 14);
@@ -740,15 +781,16 @@ __global__ void __launch_bounds__(r1_threads(MU), 1) rnn1_bwd_kernel(const __gri
         for (int n = 0; n < NR; ++n) dhc[n] = (CELL == 1 ? dhc[n] : 0.f) + __uint_as_float(r[n]);
       }
       // (see r1_pin: the loads above stay in flight across the wait)
-      r1_pin(aq0); r1_pin(dq0.x); r1_pin(dq0.y); r1_pin(dq0.z); r1_pin(dq0.w); r1_pin(dq1.x); r1_pin(dq1.y); r1_pin(dq1.z); r1_pin(dq1.w);
-      if constexpr (CELL == 1) { r1_pin(aq1); r1_pin(aq2); r1_pin(hq); }
-      const float d_o[NR] = {dq0.x, dq0.y, dq0.z, dq0.w, dq1.x, dq1.y, dq1.z, dq1.w};
+      r1_pin<NR>(aq0);
+#pragma unroll
+      for (int n = 0; n < NR; ++n) r1_pin(d_o[n]);
+      if constexpr (CELL == 1) { r1_pin<NR>(aq1); r1_pin<NR>(aq2); r1_pin<NR>(hq); }
       float a0[NR], a1[NR], a2[NR], hv[NR];
 #pragma unroll
       for (int n = 0; n < NR; ++n) {
-        a0[n] = r1_bf16_at(aq0, n);
+        a0[n] = r1_at<NR>(aq0, n);
         a1[n] = 0.f; a2[n] = 0.f; hv[n] = 0.f;
-        if constexpr (CELL == 1) { a1[n] = r1_bf16_at(aq1, n); a2[n] = r1_bf16_at(aq2, n); hv[n] = r1_bf16_at(hq, n); }
+        if constexpr (CELL == 1) { a1[n] = r1_at<NR>(aq1, n); a2[n] = r1_at<NR>(aq2, n); hv[n] = r1_at<NR>(hq, n); }
       }
       R1_LAP(1);
       if constexpr (CELL == 2) {
@@ -859,20 +901,24 @@ __global__ void r1_pack_kernel(R1PackArgs p, uint8_t *__restrict__ dst) {
   }
 }
 
-// [T][B][ld >= C] row-major -> tile-transposed [T][NT][2][C][8] (rows past the batch: zero).  One thread per 8 values.
-template <typename E>
+// [T][B][ld >= C] row-major -> tile-transposed [T][NT][16/NR][C][NR] (rows past the batch: zero).  One thread per group.
+template <typename E, int NR>
 __global__ void r1_tt_kernel(const E *__restrict__ in, int ld, E *__restrict__ out, int B, int C, int NT) {
+  constexpr int RG = R1_N / NR;
   const int col = blockIdx.y * blockDim.x + threadIdx.x;
   if (col >= C) return;
-  const int hh = blockIdx.x & 1, tile = (blockIdx.x >> 1) % NT, t = (blockIdx.x >> 1) / NT;
-  const int b = tile * R1_N + hh * 8;
-  alignas(16) E v[8];
+  const int rg = blockIdx.x % RG, tile = (blockIdx.x / RG) % NT, t = (blockIdx.x / RG) / NT;
+  const int b = tile * R1_N + rg * NR;
+  alignas(16) E v[NR];
 #pragma unroll
-  for (int n = 0; n < 8; ++n) v[n] = (b + n < B) ? in[((size_t)t * B + b + n) * ld + col] : E(0.f);
-  uint4 *dst = reinterpret_cast<uint4 *>(out + ((size_t)blockIdx.x * C + col) * 8);
-  const uint4 *src = reinterpret_cast<const uint4 *>(v);
+  for (int n = 0; n < NR; ++n) v[n] = (b + n < B) ? in[((size_t)t * B + b + n) * ld + col] : E(0.f);
+  E *dst = out + ((size_t)blockIdx.x * C + col) * NR;
+  if constexpr (NR * sizeof(E) == 8) {
+    *reinterpret_cast<uint2 *>(dst) = *reinterpret_cast<const uint2 *>(v);
+  } else {
 #pragma unroll
-  for (int i = 0; i < (int)(8 * sizeof(E) / 16); ++i) dst[i] = src[i];
+    for (int i = 0; i < (int)(NR * sizeof(E) / 16); ++i) reinterpret_cast<uint4 *>(dst)[i] = reinterpret_cast<const uint4 *>(v)[i];
+  }
 }
 
 }  // namespace
@@ -1001,10 +1047,10 @@ int sk_rnn1_tc_layer(skrnn_handle *h, cudaStream_t st, bool bwd, int l, int B, i
   a.keep = h->cfg.keep_prob;
   a.seed = seed;
   a.eoc = h->ws.eoc; a.state_in = state_in; a.state_out = state_out; a.mask = mask;
-  a.xw_tt = reinterpret_cast<const uint4 *>(h->ws.xw_tt);
+  a.xw_tt = reinterpret_cast<const char *>(h->ws.xw_tt);
   a.out_bf = h->ws.out_bf[l]; a.hprev_bf = h->ws.hprev_bf[l];
-  a.acts_tt = reinterpret_cast<uint4 *>(h->ws.acts_bf[l]);  // (allocated with the tile-transposed size for these cells)
-  a.dout_tt = reinterpret_cast<const float4 *>(h->ws.dout_tt);
+  a.acts_tt = reinterpret_cast<char *>(h->ws.acts_bf[l]);  // (allocated with the tile-transposed size for these cells)
+  a.dout_tt = reinterpret_cast<const char *>(h->ws.dout_tt);
   a.dbias0 = h->grads + lp.b[0];
   a.dbias1 = gru ? h->grads + lp.b[1] : nullptr;
   a.wimg = reinterpret_cast<const uint8_t *>(h->ws.wpack);
@@ -1025,7 +1071,7 @@ int sk_rnn1_tc_layer(skrnn_handle *h, cudaStream_t st, bool bwd, int l, int B, i
   cudaLaunchConfig_t lc = {};
   cudaLaunchAttribute lattr[1];
   lc.gridDim = dim3((unsigned)grid);
-  lc.blockDim = dim3((unsigned)r1_threads(MU));
+  lc.blockDim = dim3((unsigned)R1_THREADS);
   lc.dynamicSmemBytes = smem;
   lc.stream = st;
   lattr[0].id = cudaLaunchAttributeClusterDimension;
@@ -1052,7 +1098,8 @@ int sk_rnn1_tc_layer(skrnn_handle *h, cudaStream_t st, bool bwd, int l, int B, i
     {  // the hoisted projection in the layout the elementwise threads read
       SkLaunch scope(h, st, SK_CAT_MISC);
       const int NT = (B + R1_N - 1) / R1_N;
-      r1_tt_kernel<__nv_bfloat16><<<dim3((unsigned)(T * NT * 2), (unsigned)((G + 255) / 256)), 256, 0, st>>>(h->ws.xw_il[l], G, h->ws.xw_tt, B, G, NT);
+      if (MU == 1) r1_tt_kernel<__nv_bfloat16, 4><<<dim3((unsigned)(T * NT * 4), (unsigned)((G + 255) / 256)), 256, 0, st>>>(h->ws.xw_il[l], G, h->ws.xw_tt, B, G, NT);
+      else r1_tt_kernel<__nv_bfloat16, 8><<<dim3((unsigned)(T * NT * 2), (unsigned)((G + 255) / 256)), 256, 0, st>>>(h->ws.xw_il[l], G, h->ws.xw_tt, B, G, NT);
       SK_CUDA(cudaGetLastError());
     }
     SkLaunch scope(h, st, SK_CAT_RNN_FWD);
@@ -1070,7 +1117,8 @@ int sk_rnn1_tc_layer(skrnn_handle *h, cudaStream_t st, bool bwd, int l, int B, i
     {  // d(out) of the layer in the layout the elementwise threads read
       SkLaunch scope(h, st, SK_CAT_MISC);
       const int NT = (B + R1_N - 1) / R1_N;
-      r1_tt_kernel<float><<<dim3((unsigned)(T * NT * 2), (unsigned)((H + 255) / 256)), 256, 0, st>>>(h->ws.dout, H, h->ws.dout_tt, B, H, NT);
+      if (MU == 1) r1_tt_kernel<float, 4><<<dim3((unsigned)(T * NT * 4), (unsigned)((H + 255) / 256)), 256, 0, st>>>(h->ws.dout, H, h->ws.dout_tt, B, H, NT);
+      else r1_tt_kernel<float, 8><<<dim3((unsigned)(T * NT * 2), (unsigned)((H + 255) / 256)), 256, 0, st>>>(h->ws.dout, H, h->ws.dout_tt, B, H, NT);
       SK_CUDA(cudaGetLastError());
     }
     SkLaunch scope(h, st, SK_CAT_RNN_BWD);
