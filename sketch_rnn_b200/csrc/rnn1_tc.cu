@@ -497,7 +497,8 @@ rnn1_fwd_kernel(const __grid_constant__ CUtensorMap tm_hp, const __grid_constant
           r1_st_group<NR>(act_p + 3 * gs, hcur);  // the state fed to this step (BPTT reads it back in the same layout)
         }
       }
-      if (pf_lane && t + a.pf_dist < T) {
+      R1_LAP(7);
+      if (a.pf_dist >= 0 && pf_lane && t + a.pf_dist < T) {
         const char *pp = xw_p + (size_t)a.pf_dist * xw_ts;
         r1_prefetch_line(pp, a.pf_l1);
         if constexpr (CELL == 1) {
@@ -505,6 +506,7 @@ rnn1_fwd_kernel(const __grid_constant__ CUtensorMap tm_hp, const __grid_constant
           r1_prefetch_line(pp + 2 * gs, a.pf_l1);
         }
       }
+      R1_LAP(12);
       const uint32_t eoc_m = __ballot_sync(0xffffffffu, eoc_raw != 0);
       eoc_raw = r1_eoc_raw(a.eoc, t + 1, T, B, b0, lane);
       float dsc[NR];
@@ -582,8 +584,8 @@ rnn1_fwd_kernel(const __grid_constant__ CUtensorMap tm_hp, const __grid_constant
         if (nb + n < nvalid) a.state_out[(size_t)(b0 + nb + n) * H + unit] = hcur[n];
     }
     if (dbg)
-      printf("[rnn1 fwd cell %d] elementwise thread cycles/step: loads issue %lld, wait acc-1 %lld, gates r,u + operand %lld, stores %lld, "
-             "wait acc %lld, cell + operand %lld, stores %lld\n", CELL, tk[0] / T, tk[1] / T, tk[2] / T, tk[3] / T, tk[4] / T, tk[5] / T,
+      printf("[rnn1 fwd cell %d] elementwise thread cycles/step: loads %lld, prefetch %lld, eoc + dropout %lld, wait acc-1 %lld, gates r,u + operand %lld, stores %lld, "
+             "wait acc %lld, cell + operand %lld, stores %lld\n", CELL, tk[7] / T, tk[12] / T, tk[0] / T, tk[1] / T, tk[2] / T, tk[3] / T, tk[4] / T, tk[5] / T,
              tk[6] / T);
   }
   tc_fence_before();
@@ -754,7 +756,8 @@ __global__ void __launch_bounds__(R1_THREADS, 1) rnn1_bwd_kernel(const __grid_co
           hq = r1_ld_group<NR>(act_p + 3 * gs);
         }
       }
-      if (t - a.pf_dist >= 0) {
+      R1_LAP(7);
+      if (a.pf_dist >= 0 && t - a.pf_dist >= 0) {
         if (pf_lane_d) r1_prefetch_line(do_p - (size_t)a.pf_dist * do_ts, a.pf_l1);
         if (pf_lane) {
           const char *pa = act_p - (size_t)a.pf_dist * act_ts;
@@ -766,6 +769,7 @@ __global__ void __launch_bounds__(R1_THREADS, 1) rnn1_bwd_kernel(const __grid_co
           }
         }
       }
+      R1_LAP(12);
       const uint32_t eoc_m = __ballot_sync(0xffffffffu, eoc_raw != 0);
       eoc_raw = r1_eoc_raw(a.eoc, t - 1, T, B, b0, lane);
       float dsc[NR];
@@ -858,8 +862,8 @@ __global__ void __launch_bounds__(R1_THREADS, 1) rnn1_bwd_kernel(const __grid_co
       }
     }
     if (dbg)
-      printf("[rnn1 bwd cell %d] elementwise thread cycles/step: loads issue %lld, wait d(h) product %lld, elementwise-1 + operand %lld, "
-             "wait d(r*h) product %lld, elementwise-2 + operand %lld\n", CELL, tk[0] / T, tk[1] / T, tk[2] / T, tk[4] / T, tk[5] / T);
+      printf("[rnn1 bwd cell %d] elementwise thread cycles/step: loads %lld, prefetch %lld, eoc + dropout %lld, wait d(h) product %lld, elementwise-1 + operand %lld, "
+             "wait d(r*h) product %lld, elementwise-2 + operand %lld\n", CELL, tk[7] / T, tk[12] / T, tk[0] / T, tk[1] / T, tk[2] / T, tk[4] / T, tk[5] / T);
   }
   tc_fence_before();
   __syncthreads();
