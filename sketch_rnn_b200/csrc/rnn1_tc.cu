@@ -67,6 +67,7 @@ struct R1Args {
   const uint8_t *wimg;
   int wimg_rank_bytes;       // cluster of 2: each rank's tiles are a separate image
   int debug;                 // SKRNN_TC_DEBUG=1: CTA 0 prints its per-phase cycle split
+  int publish_mode;          // 0: every thread fences and arrives; 1: CTA-wide named barrier, then one fence and one arrival
   int pf_dist, pf_l1;        // prefetch distance in steps, and whether it targets L1 (else L2)
 };
 
@@ -292,6 +293,21 @@ __device__ __forceinline__ void r1_exchange(const R1Xchg &x, uint32_t s_tile, ui
   }
 }
 
+// The elementwise warps have written their part of an operand tile: make it visible to the async proxy (tcgen05.mma,
+// bulk copies) and tell the MMA thread
+__device__ __forceinline__ void r1_publish(uint32_t bar, int mode, int warp, int lane) {
+  if (mode == 0) {
+    fence_proxy_async_smem();
+    mbar_arrive(bar);
+  } else {
+    named_bar_sync(1, 32 * R1_EW);
+    if (warp == 0 && lane == 0) {
+      fence_proxy_async_smem();
+      mbar_arrive(bar);
+    }
+  }
+}
+
 // L2 prefetch of the 128-byte line holding (row b0 + lane, column col) of a [T,B,ld] array at step t: one instruction
 // per warp brings in what the warp's 32 units will load for the tile's rows two steps later
 __device__ __forceinline__ void r1_prefetch(const void *base, size_t elem_bytes, int t, int T, int B, int b0, int ld, int col,
@@ -359,9 +375,9 @@ rnn1_fwd_kernel(const __grid_constant__ CUtensorMap tm_hp, const __grid_constant
 
   r1_load_smem_tiles(a, wimg, s, tid, THREADS);
   if (tid == 0) {
-    mbar_init(bar_op1, 32 * EW);
+    mbar_init(bar_op1, a.publish_mode ? 1 : 32 * EW);
     mbar_init(bar_acc1, 1);
-    mbar_init(bar_op2, 32 * EW);
+    mbar_init(bar_op2, a.publish_mode ? 1 : 32 * EW);
     mbar_init(bar_acc2, 1);
     mbar_init(bar_rx1, 1);
     mbar_init(bar_rx2, 1);
@@ -531,8 +547,7 @@ rnn1_fwd_kernel(const __grid_constant__ CUtensorMap tm_hp, const __grid_constant
           ug[n] = sigmoid_approx(__uint_as_float(ru[n]) + r1_at<NR>(xq1, n));
           if (uvalid) r1_sts_bf16(b2_gen + R1_BOFF(bcol, bch, nb + n), rg[n] * hcur[n]);
         }
-        fence_proxy_async_smem();
-        mbar_arrive(bar_op2);
+        r1_publish(bar_op2, a.publish_mode, warp, lane);
         R1_LAP(2);
         if (uvalid) {
           r1_st_group<NR>(act_p, rg);
@@ -561,8 +576,7 @@ rnn1_fwd_kernel(const __grid_constant__ CUtensorMap tm_hp, const __grid_constant
         if (uvalid) r1_sts_bf16(b1_gen + b1w + R1_BOFF(bcol, bch, nb + n), hn);
         x2[n] = CELL == 1 ? cand : h2[n];
       }
-      fence_proxy_async_smem();
-        mbar_arrive(bar_op1);
+      r1_publish(bar_op1, a.publish_mode, warp, lane);
       R1_LAP(5);
       // off the dependent chain: layer output (pre reset, dropout applied) and the activation BPTT needs
       if (uvalid) {
@@ -620,9 +634,9 @@ __global__ void __launch_bounds__(R1_THREADS, 1) rnn1_bwd_kernel(const __grid_co
 
   r1_load_smem_tiles(a, wimg, s, tid, THREADS);
   if (tid == 0) {
-    mbar_init(bar_op1, 32 * EW);
+    mbar_init(bar_op1, a.publish_mode ? 1 : 32 * EW);
     mbar_init(bar_acc1, 1);
-    mbar_init(bar_op2, 32 * EW);
+    mbar_init(bar_op2, a.publish_mode ? 1 : 32 * EW);
     mbar_init(bar_acc2, 1);
     mbar_init(bar_rx1, 1);
     mbar_init(bar_rx2, 1);
@@ -806,8 +820,7 @@ __global__ void __launch_bounds__(R1_THREADS, 1) rnn1_bwd_kernel(const __grid_co
           bs0 += dp;
           if (uvalid) r1_sts_bf16(b1_gen + b1w + R1_BOFF(bcol, bch, nb + n), dp);
         }
-        fence_proxy_async_smem();
-        mbar_arrive(bar_op1);
+        r1_publish(bar_op1, a.publish_mode, warp, lane);
         R1_LAP(2);
       } else {
         // a0 = r, a1 = u, a2 = candidate, hv = h fed to the step
@@ -821,8 +834,7 @@ __global__ void __launch_bounds__(R1_THREADS, 1) rnn1_bwd_kernel(const __grid_co
           bs2 += dpc;
           if (uvalid) r1_sts_bf16(b1_gen + R1_BOFF(bcol, bch, nb + n), dpc);
         }
-        fence_proxy_async_smem();
-        mbar_arrive(bar_op1);
+        r1_publish(bar_op1, a.publish_mode, warp, lane);
         R1_LAP(2);
         R1_WAIT(bar_acc1, st & 1, 15);
         R1_LAP(4);
@@ -843,8 +855,7 @@ __global__ void __launch_bounds__(R1_THREADS, 1) rnn1_bwd_kernel(const __grid_co
             r1_sts_bf16(b2_gen + R1_BOFF(bcol_u, bch_u, nb + n), dpu);
           }
         }
-        fence_proxy_async_smem();
-        mbar_arrive(bar_op2);
+        r1_publish(bar_op2, a.publish_mode, warp, lane);
         R1_LAP(5);
       }
       act_p -= act_ts; do_p -= do_ts;
@@ -1069,6 +1080,9 @@ int sk_rnn1_tc_layer(skrnn_handle *h, cudaStream_t st, bool bwd, int l, int B, i
       pf_l = (e && strstr(e, "L1")) ? 1 : 0;
     }
     a.pf_dist = pf_d; a.pf_l1 = pf_l;
+    static int pub = -1;
+    if (pub < 0) { const char *e = getenv("SKRNN_R1_PUBLISH"); pub = e ? atoi(e) : 0; }
+    a.publish_mode = pub;
   }
   const size_t smem = (size_t)soff + b_bytes + 1024 + 256;
   const int grid = CL * ((B + R1_N - 1) / R1_N);
