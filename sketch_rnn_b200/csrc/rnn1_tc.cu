@@ -3,22 +3,29 @@
 // BPTT (model.py:182), one launch per layer and direction running all T steps.
 //
 // Partition.  Unlike the LSTM (rnn_tc.cu), whose recurrent matrix needs a 16-CTA cluster, the recurrent weights of
-// these cells fit on ONE SM at the reference's sizes (GRU, H = 256: Wg_h 256 KB + Wc_h 128 KB in bf16 = 192 KB of
-// shared memory + 192 KB of tensor memory; RNN: 128 KB, all in tensor memory).  So a CTA owns N = 16 batch rows and
-// ALL hidden units, the weights stay resident for the whole launch, and the recurrent state never leaves the SM
-// between steps: no cluster, no exchange through L2, no cluster barrier -- a step is
-// MMA -> tcgen05.ld -> gate math in registers -> next operand tile in shared memory -> MMA.
+// these cells fit on one or two SMs at the reference's sizes.  A batch tile of N = 16 rows is owned
+//   * by ONE CTA when H <= 128 (all weight tiles in tensor memory), or
+//   * by a CLUSTER OF TWO CTAs when 128 < H <= 256: each CTA owns 128 hidden units and keeps their weight rows in
+//     tensor memory (gru, H = 256: three 128-column tiles forward, 128 + 256 columns backward).  The contraction runs
+//     over all units, so both CTAs need the whole operand tile: each writes the k-blocks of its own units locally and
+//     the MMA thread swaps them with the peer by one bulk copy through distributed shared memory per product (the copy
+//     reports on the peer's mbarrier: async proxy end to end, no cluster-scope fence in the loop).
+//   (SKRNN_R1_CLUSTER=0 keeps H > 128 on one CTA: half of the weight tiles then sit in shared memory, and an MMA that
+//   reads its A tile from there runs 39 cycles instead of 9 -- measured 4.9 ms against 3.1 ms per gru training step.)
+// The weights stay resident for the whole launch and the recurrent state never goes through L2 between steps: a step is
+// MMA -> tcgen05.ld -> gate math in registers -> next operand tile in shared memory (-> peer) -> MMA.
 //
 // Products are transposed so that the hidden units are the MMA M dimension (128-row tiles; lane = unit) and the
 // batch tile is the N dimension:   D^T[units, N] = W^T[units, K] * h^T[K, N].
-//   * warp 8 issues tcgen05.mma; the A tiles (weights) are read from tensor memory (TS form) or from shared memory
+//   * warp 16 issues tcgen05.mma; the A tiles (weights) are read from tensor memory (TS form) or from shared memory
 //     (UMMA K-major, 128B swizzle), whichever the host-side placement gave them.  The same thread sends the operand
 //     tiles to global memory with TMA stores: the tile the next product reads IS h_t (forward: the `hprev` record the
 //     weight-gradient GEMM reads; GRU: also r*h) resp. d(pre-activation) (backward), already in bf16;
-//   * warps 0-7 are elementwise: warp w reads TMEM lane quarter w%4 of m-tile w/4 (unit = 128*(w/4) + 32*(w%4) +
-//     lane) for all N columns, applies the gate math in registers (fp32 state in registers), and writes the next
-//     B operand (bf16, K-major swizzled) straight into shared memory.  Its global loads (hoisted projection, saved
-//     activations, d(out)) are issued before it waits for the product and were prefetched into L2 two steps earlier.
+//   * warps 0-15 are elementwise: a warp reads one TMEM lane quarter of one m-tile (lane = unit) for NR = 4 or 8 of
+//     the 16 batch columns, applies the gate math in registers (fp32 state in registers), and writes the next B operand
+//     (bf16, K-major swizzled) straight into shared memory.  What it reads and writes per step for itself -- the
+//     hoisted projection, the saved activations, d(out) -- is kept tile-transposed so that it is one 16-byte (8-byte)
+//     access per gate, requested before it waits for the product and prefetched into L2 two steps earlier.
 // GRU (TF 0.x semantics): two dependent products per step -- gates r,u on h, then the candidate on r*h.
 // BPTT mirrors it: d(r*h) = d(pre_c) * Wc_h^T, then d(h) += [d(pre_r), d(pre_u)] * Wg_h^T.
 #include <stdlib.h>
@@ -67,7 +74,6 @@ struct R1Args {
   const uint8_t *wimg;
   int wimg_rank_bytes;       // cluster of 2: each rank's tiles are a separate image
   int debug;                 // SKRNN_TC_DEBUG=1: CTA 0 prints its per-phase cycle split
-  int publish_mode;          // 0: every thread fences and arrives; 1: CTA-wide named barrier, then one fence and one arrival
   int pf_dist, pf_l1;        // prefetch distance in steps, and whether it targets L1 (else L2)
 };
 
@@ -294,18 +300,11 @@ __device__ __forceinline__ void r1_exchange(const R1Xchg &x, uint32_t s_tile, ui
 }
 
 // The elementwise warps have written their part of an operand tile: make it visible to the async proxy (tcgen05.mma,
-// bulk copies) and tell the MMA thread
-__device__ __forceinline__ void r1_publish(uint32_t bar, int mode, int warp, int lane) {
-  if (mode == 0) {
-    fence_proxy_async_smem();
-    mbar_arrive(bar);
-  } else {
-    named_bar_sync(1, 32 * R1_EW);
-    if (warp == 0 && lane == 0) {
-      fence_proxy_async_smem();
-      mbar_arrive(bar);
-    }
-  }
+// bulk copies) and tell the MMA thread.  (One CTA-wide named barrier followed by a single fence and arrival was
+// measured too: no faster.)
+__device__ __forceinline__ void r1_publish(uint32_t bar) {
+  fence_proxy_async_smem();
+  mbar_arrive(bar);
 }
 
 // L2 prefetch of the 128-byte line holding (row b0 + lane, column col) of a [T,B,ld] array at step t: one instruction
@@ -375,9 +374,9 @@ rnn1_fwd_kernel(const __grid_constant__ CUtensorMap tm_hp, const __grid_constant
 
   r1_load_smem_tiles(a, wimg, s, tid, THREADS);
   if (tid == 0) {
-    mbar_init(bar_op1, a.publish_mode ? 1 : 32 * EW);
+    mbar_init(bar_op1, 32 * EW);
     mbar_init(bar_acc1, 1);
-    mbar_init(bar_op2, a.publish_mode ? 1 : 32 * EW);
+    mbar_init(bar_op2, 32 * EW);
     mbar_init(bar_acc2, 1);
     mbar_init(bar_rx1, 1);
     mbar_init(bar_rx2, 1);
@@ -547,7 +546,7 @@ rnn1_fwd_kernel(const __grid_constant__ CUtensorMap tm_hp, const __grid_constant
           ug[n] = sigmoid_approx(__uint_as_float(ru[n]) + r1_at<NR>(xq1, n));
           if (uvalid) r1_sts_bf16(b2_gen + R1_BOFF(bcol, bch, nb + n), rg[n] * hcur[n]);
         }
-        r1_publish(bar_op2, a.publish_mode, warp, lane);
+        r1_publish(bar_op2);
         R1_LAP(2);
         if (uvalid) {
           r1_st_group<NR>(act_p, rg);
@@ -576,7 +575,7 @@ rnn1_fwd_kernel(const __grid_constant__ CUtensorMap tm_hp, const __grid_constant
         if (uvalid) r1_sts_bf16(b1_gen + b1w + R1_BOFF(bcol, bch, nb + n), hn);
         x2[n] = CELL == 1 ? cand : h2[n];
       }
-      r1_publish(bar_op1, a.publish_mode, warp, lane);
+      r1_publish(bar_op1);
       R1_LAP(5);
       // off the dependent chain: layer output (pre reset, dropout applied) and the activation BPTT needs
       if (uvalid) {
@@ -634,9 +633,9 @@ __global__ void __launch_bounds__(R1_THREADS, 1) rnn1_bwd_kernel(const __grid_co
 
   r1_load_smem_tiles(a, wimg, s, tid, THREADS);
   if (tid == 0) {
-    mbar_init(bar_op1, a.publish_mode ? 1 : 32 * EW);
+    mbar_init(bar_op1, 32 * EW);
     mbar_init(bar_acc1, 1);
-    mbar_init(bar_op2, a.publish_mode ? 1 : 32 * EW);
+    mbar_init(bar_op2, 32 * EW);
     mbar_init(bar_acc2, 1);
     mbar_init(bar_rx1, 1);
     mbar_init(bar_rx2, 1);
@@ -820,7 +819,7 @@ __global__ void __launch_bounds__(R1_THREADS, 1) rnn1_bwd_kernel(const __grid_co
           bs0 += dp;
           if (uvalid) r1_sts_bf16(b1_gen + b1w + R1_BOFF(bcol, bch, nb + n), dp);
         }
-        r1_publish(bar_op1, a.publish_mode, warp, lane);
+        r1_publish(bar_op1);
         R1_LAP(2);
       } else {
         // a0 = r, a1 = u, a2 = candidate, hv = h fed to the step
@@ -834,7 +833,7 @@ __global__ void __launch_bounds__(R1_THREADS, 1) rnn1_bwd_kernel(const __grid_co
           bs2 += dpc;
           if (uvalid) r1_sts_bf16(b1_gen + R1_BOFF(bcol, bch, nb + n), dpc);
         }
-        r1_publish(bar_op1, a.publish_mode, warp, lane);
+        r1_publish(bar_op1);
         R1_LAP(2);
         R1_WAIT(bar_acc1, st & 1, 15);
         R1_LAP(4);
@@ -855,7 +854,7 @@ __global__ void __launch_bounds__(R1_THREADS, 1) rnn1_bwd_kernel(const __grid_co
             r1_sts_bf16(b2_gen + R1_BOFF(bcol_u, bch_u, nb + n), dpu);
           }
         }
-        r1_publish(bar_op2, a.publish_mode, warp, lane);
+        r1_publish(bar_op2);
         R1_LAP(5);
       }
       act_p -= act_ts; do_p -= do_ts;
@@ -1080,9 +1079,6 @@ int sk_rnn1_tc_layer(skrnn_handle *h, cudaStream_t st, bool bwd, int l, int B, i
       pf_l = (e && strstr(e, "L1")) ? 1 : 0;
     }
     a.pf_dist = pf_d; a.pf_l1 = pf_l;
-    static int pub = -1;
-    if (pub < 0) { const char *e = getenv("SKRNN_R1_PUBLISH"); pub = e ? atoi(e) : 0; }
-    a.publish_mode = pub;
   }
   const size_t smem = (size_t)soff + b_bytes + 1024 + 256;
   const int grid = CL * ((B + R1_N - 1) / R1_N);
