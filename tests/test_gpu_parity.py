@@ -346,7 +346,11 @@ def test_errors_are_reported_not_thrown():
 
 BF16_TOL = 2e-2
 BF16_CASES = [("lstm", 16, 2, 3, 5, 7), ("gru", 64, 3, 5, 11, 6), ("rnn", 40, 3, 24, 9, 8),
-              ("lstm", 256, 2, 24, 23, 12), ("gru", 256, 2, 24, 10, 10), ("lstm", 512, 3, 24, 9, 5)]
+              ("lstm", 256, 2, 24, 23, 12), ("gru", 256, 2, 24, 10, 10), ("lstm", 512, 3, 24, 9, 5),
+              # gru / rnn tensor-core kernels: one CTA per batch tile (H <= 128), the cluster of two with an uneven
+              # split of the units (H = 192: 128 + 64), several ragged 16-row tiles
+              ("gru", 128, 2, 24, 37, 9), ("rnn", 128, 2, 24, 16, 7), ("gru", 192, 2, 24, 21, 8),
+              ("rnn", 192, 3, 24, 33, 6), ("rnn", 256, 2, 24, 50, 9), ("gru", 256, 3, 24, 49, 7)]
 
 
 @pytest.mark.parametrize("model,H,L,M,B,T", BF16_CASES)
