@@ -14,6 +14,8 @@
 // Thread u of a CTA owns hidden unit u of every layer (blockDim >= H), so all gates of a unit
 // meet in one thread and the cell update needs no exchange; the [x ; h] operand of the SB
 // sketches is staged k-major in shared memory and broadcast to all threads.
+#include <stdlib.h>
+
 #include "common.cuh"
 #include "skrnn_math.h"
 
@@ -321,6 +323,18 @@ int sk_sample_f32(skrnn_handle *h, cudaStream_t st, int n, int steps, float temp
                   int *lengths, float *mixp) {
   SK_CHECK(h->H <= 512, "sampler supports rnn_size <= 512 (got %d)", h->H);
   SK_CHECK(n > 0 && steps > 0, "sample: n and num_steps must be positive");
+  SK_CUDA(cudaMemsetAsync(strokes, 0, (size_t)n * steps * 5 * sizeof(float), st));
+  if (mixp) SK_CUDA(cudaMemsetAsync(mixp, 0, (size_t)n * steps * h->NOUT * sizeof(float), st));
+  {
+    // few sketches: the cluster-resident kernel (sampler_cl.cu), same arithmetic; above the threshold the streaming
+    // kernel below wins because it keeps every SM busy with its own group of sketches
+    const char *e = getenv("SKRNN_SAMPLE_CLUSTER_MAX");
+    const int cl_max = e ? atoi(e) : 512;
+    if (n <= cl_max) {
+      const int r = sk_sample_cluster(h, st, n, steps, temp_mix, temp_pen, stop_if_eoc, uniforms, seed, sketch0, strokes, lengths, mixp);
+      if (r >= 0) return r;
+    }
+  }
   int64_t need = (int64_t)n * h->L * h->S;
   if (need > h->samp_state_n) {
     if (h->samp_state) cudaFree(h->samp_state);
@@ -330,8 +344,6 @@ int sk_sample_f32(skrnn_handle *h, cudaStream_t st, int n, int steps, float temp
     h->samp_state_n = need;
   }
   SK_CUDA(cudaMemsetAsync(h->samp_state, 0, need * sizeof(float), st));  // zero_state (model.py:208)
-  SK_CUDA(cudaMemsetAsync(strokes, 0, (size_t)n * steps * 5 * sizeof(float), st));
-  if (mixp) SK_CUDA(cudaMemsetAsync(mixp, 0, (size_t)n * steps * h->NOUT * sizeof(float), st));
   SampArgs a = {};
   a.n = n; a.steps = steps; a.H = h->H; a.L = h->L; a.M = h->M; a.NOUT = h->NOUT; a.cell = h->cfg.cell;
   a.temp_mix = temp_mix; a.temp_pen = temp_pen; a.data_scale = h->cfg.data_scale;

@@ -189,11 +189,15 @@ def test_train_step_host_entry_point():
     h.close()
 
 
+@pytest.mark.parametrize("kernel", ["cluster", "streaming"])
 @pytest.mark.parametrize("model,H,L,M", [("lstm", 16, 2, 3), ("gru", 32, 2, 5), ("rnn", 24, 3, 4),
-                                         ("lstm", 256, 2, 24)])
-def test_sampler_bit_exact(model, H, L, M):
+                                         ("lstm", 256, 2, 24), ("gru", 256, 2, 24), ("rnn", 64, 3, 7)])
+def test_sampler_bit_exact(model, H, L, M, kernel, monkeypatch):
     """Sampled stroke sequences are bit-identical to the CPU restatement when both are fed the same
-    uniforms; covers temperature, stop_if_eoc and several sketches per CTA."""
+    uniforms; covers temperature, stop_if_eoc and several sketches per CTA -- through the cluster-resident
+    kernel (sampler_cl.cu; rnn_size 24 is not a multiple of 16 and stays on the streaming kernel) and through
+    the streaming kernel (sampler.cu)."""
+    monkeypatch.setenv("SKRNN_SAMPLE_CLUSTER", "1" if kernel == "cluster" else "0")
     cfg = so.Config(model=model, rnn_size=H, num_layers=L, num_mixture=M)
     params = so.init_params(cfg, seed=7, trained_like=True)
     h = make_handle(cfg, params)
