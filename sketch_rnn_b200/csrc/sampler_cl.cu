@@ -8,9 +8,11 @@
 // exactly those weight columns in its shared memory for the whole launch (kanji model, lstm H = 256 L = 2: 3.3 MB of
 // fp32 weights = 204 KB per CTA), and the cluster runs SB = 4 sketches together:
 //   per layer:  every rank computes its units' gates for the 4 sketches (one thread per (unit, sketch): all gates of a
-//               unit meet in one thread, the cell state lives in its registers), writes h into EVERY rank's operand
-//               buffers through distributed shared memory, barrier.cluster;
-//   output:     its OC logits per sketch -> every rank's logits buffer, barrier.cluster;
+//               unit meet in one thread, the cell state lives in its registers) and sends h into EVERY rank's operand
+//               buffers with st.async: the store itself reports its bytes on the receiver's mbarrier, so an exchange
+//               is "wait until H*SB*4 bytes have landed" -- no barrier.cluster (a gpu-scope fence plus an L1
+//               invalidate, ~5 us per step for three of them) in the loop;
+//   output:     its OC logits per sketch -> every rank's logits buffer, same mechanism;
 //   draw:       every rank draws the next point of all 4 sketches redundantly (one warp per sketch), so the feedback
 //               (dx, dy, eos, eoc, cont) needs no further exchange; rank 0 writes the strokes.
 // Same arithmetic contract as sampler.cu: every output element is ONE sequential fused-multiply-add chain over
@@ -57,14 +59,36 @@ __device__ __forceinline__ void scl_cluster_sync() {
   asm volatile("barrier.cluster.arrive.release.aligned;\n" ::: "memory");
   asm volatile("barrier.cluster.wait.acquire.aligned;\n" ::: "memory");
 }
-// v -> the same shared-memory location in every CTA of the cluster
-__device__ __forceinline__ void scl_bcast(const float *local, float v) {
+// v -> the same shared-memory location in every CTA of the cluster; each store adds its 4 bytes to the transaction
+// count of the receiving CTA's mbarrier `bar` (same offset everywhere)
+__device__ __forceinline__ void scl_send(const float *local, float v, uint32_t bar) {
   const uint32_t a = (uint32_t)__cvta_generic_to_shared(local);
 #pragma unroll
   for (int r = 0; r < SCL_CS; ++r) {
-    uint32_t ra;
+    uint32_t ra, rb;
     asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(ra) : "r"(a), "r"(r));
-    asm volatile("st.shared::cluster.f32 [%0], %1;" ::"r"(ra), "f"(v) : "memory");
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(rb) : "r"(bar), "r"(r));
+    asm volatile("st.async.shared::cluster.mbarrier::complete_tx::bytes.b32 [%0], %1, [%2];" ::"r"(ra), "r"(__float_as_uint(v)), "r"(rb)
+                 : "memory");
+  }
+}
+__device__ __forceinline__ void scl_arm(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void scl_wait(uint32_t bar, uint32_t parity) {
+  uint32_t done;
+  for (uint32_t spin = 0;; ++spin) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n"
+        "selp.u32 %0, 1, 0, p;\n"
+        "}\n" : "=r"(done) : "r"(bar), "r"(parity) : "memory");
+    if (done) return;
+    if (spin > (1u << 24)) {
+      printf("libskrnn: cluster sampler exchange timed out (block %d, thread %d)\n", (int)blockIdx.x, (int)threadIdx.x);
+      __trap();
+    }
   }
 }
 
@@ -88,6 +112,7 @@ struct SclPlan {
   int rh;                                    // gru: [SB][H]  r*h of the layer being computed
   int hlast;                                 // [SB][H]  output of the last layer
   int lg, xin, pdf, flags;                   // [SB][NOUT], [SB][5 -> 8], [SB][M], 2*SB ints
+  int bars;                                  // mbarriers (8 bytes each): per layer A (output), R (gru r*h), Hb (state); then LG
   int total;
 };
 
@@ -119,6 +144,8 @@ __host__ __device__ inline SclPlan scl_plan(int cell, int H, int L, int M, int N
   p.xin = o; o += SCL_SB * 8;
   p.pdf = o; o += SCL_SB * ((M + 3) & ~3);
   p.flags = o; o += 2 * SCL_SB;
+  o = (o + 3) & ~3;
+  p.bars = o; o += 2 * (3 * SK_MAX_LAYERS + 1);
   p.total = o;
   return p;
 }
@@ -140,9 +167,9 @@ sample_cluster_kernel(const __grid_constant__ SclArgs a, const __grid_constant__
     const int K = (l == 0 ? 5 : H) + H;
     const float *W = a.params + a.w0[l];
     const float *bias = a.params + a.b0[l];
-    for (int i = tid; i < K * UPC * ng; i += SCL_THREADS) {
-      const int g = i % ng, u = (i / ng) % UPC, k = i / (ng * UPC);
-      sm[p.w[l] + i] = W[(size_t)k * (ng * H) + g * H + u0 + u];
+    for (int i = tid; i < K * UPC * ng; i += SCL_THREADS) {  // (u fastest: runs of UPC contiguous floats in global memory)
+      const int u = i % UPC, g = (i / UPC) % ng, k = i / (ng * UPC);
+      sm[p.w[l] + (k * UPC + u) * ng + g] = __ldg(W + (size_t)k * (ng * H) + g * H + u0 + u);
     }
     for (int i = tid; i < UPC * ng; i += SCL_THREADS) sm[p.b[l] + i] = bias[(i % ng) * H + u0 + i / ng];
     if (cell == 1) {
@@ -161,9 +188,20 @@ sample_cluster_kernel(const __grid_constant__ SclArgs a, const __grid_constant__
   __syncthreads();
   int *flags = reinterpret_cast<int *>(sm + p.flags);  // [SB] done, [SB] length
   if (tid < SCL_SB) { flags[tid] = tid < rows_valid ? 0 : 1; flags[SCL_SB + tid] = 0; }
+  const uint32_t bars = (uint32_t)__cvta_generic_to_shared(sm + p.bars);
+  auto bar_A = [&](int l) { return bars + 8u * (uint32_t)l; };
+  auto bar_R = [&](int l) { return bars + 8u * (uint32_t)(SK_MAX_LAYERS + l); };
+  auto bar_H = [&](int l) { return bars + 8u * (uint32_t)(2 * SK_MAX_LAYERS + l); };
+  const uint32_t bar_LG = bars + 8u * (uint32_t)(3 * SK_MAX_LAYERS);
+  if (tid == 0) {
+    for (int i = 0; i < 3 * SK_MAX_LAYERS + 1; ++i)
+      asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bars + 8u * (uint32_t)i));
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  const uint32_t xbytes = (uint32_t)(H * SCL_SB * 4), lgbytes = (uint32_t)(NOUT * SCL_SB * 4);
   float *xin = sm + p.xin;
   float *lg = sm + p.lg;
-  scl_cluster_sync();  // nobody writes into a peer before it has zeroed its buffers
+  scl_cluster_sync();  // nobody sends into a peer before it has zeroed its buffers and initialised its barriers
 
   // cell threads: one per (unit, sketch); the lstm cell state stays in its registers
   const bool cth = tid < UPC * SCL_SB;
@@ -172,7 +210,22 @@ sample_cluster_kernel(const __grid_constant__ SclArgs a, const __grid_constant__
 #pragma unroll
   for (int l = 0; l < SK_MAX_LAYERS; ++l) cstate[l] = 0.f;
 
+  int last_step = 0;
   for (int step = 0; step < a.steps; ++step) {
+    const uint32_t par = (uint32_t)(step & 1);
+    last_step = step;
+    // the recurrent state every rank sent at the end of the previous step's layers has landed
+    if (step > 0)
+      for (int l = 0; l < L; ++l) scl_wait(bar_H(l), par ^ 1u);
+    __syncthreads();  // nobody still polls last step's phases when this step's exchanges complete
+    if (tid == 0) {   // this step's exchanges: expected bytes per barrier (data may arrive before or after this)
+      for (int l = 0; l < L; ++l) {
+        scl_arm(bar_A(l), xbytes);
+        scl_arm(bar_H(l), xbytes);
+        if (cell == 1) scl_arm(bar_R(l), xbytes);
+      }
+      scl_arm(bar_LG, lgbytes);
+    }
 #pragma unroll
     for (int l = 0; l < SK_MAX_LAYERS; ++l) {
       if (l >= L) break;
@@ -234,9 +287,9 @@ sample_cluster_kernel(const __grid_constant__ SclArgs a, const __grid_constant__
           hold_h = As[I + u0 + cu];
           ar = SKM_MUL(skm_sigmoid(SKM_ADD(ar, bb.x)), hold_h);  // r * h
           az = skm_sigmoid(SKM_ADD(az, bb.y));
-          scl_bcast(rh + cs * H + u0 + cu, ar);
+          scl_send(rh + cs * H + u0 + cu, ar, bar_R(l));
         }
-        scl_cluster_sync();
+        scl_wait(bar_R(l), par);
         if (cth) {  // candidate on [x ; r*h]
           const float *Wc = sm + p.wc[l] + cu;
           const float *Ax = xh + cs * Kp;
@@ -252,11 +305,11 @@ sample_cluster_kernel(const __grid_constant__ SclArgs a, const __grid_constant__
       }
       // the layer's output: input of the next layer (nobody reads that buffer now), or of the output projection
       if (cth) {
-        if (l + 1 < L) scl_bcast(sm + p.xh[l + 1] + cs * scl_kp(2 * H) + u0 + cu, hnew);
-        else scl_bcast(sm + p.hlast + cs * H + u0 + cu, hnew);
+        if (l + 1 < L) scl_send(sm + p.xh[l + 1] + cs * scl_kp(2 * H) + u0 + cu, hnew, bar_A(l));
+        else scl_send(sm + p.hlast + cs * H + u0 + cu, hnew, bar_A(l));
       }
-      scl_cluster_sync();  // ... and every rank is done reading this layer's [x ; h]
-      if (cth) scl_bcast(xh + cs * Kp + I + u0 + cu, hkeep);  // read next at this layer of the NEXT step (barriers in between)
+      scl_wait(bar_A(l), par);  // every rank's output is here, so every rank is done reading this layer's [x ; h]
+      if (cth) scl_send(xh + cs * Kp + I + u0 + cu, hkeep, bar_H(l));  // waited for at the top of the next step
     }
     // ---- output projection (model.py:98-99): my OC columns for the SB sketches ----
     if (tid < OC * SCL_SB) {
@@ -266,9 +319,9 @@ sample_cluster_kernel(const __grid_constant__ SclArgs a, const __grid_constant__
       float acc = 0.f;
 #pragma unroll 4
       for (int k = 0; k < H; ++k) acc = SKM_FMA(hl[k], Wo[(size_t)k * OC], acc);
-      if (rank * OC + j < NOUT) scl_bcast(lg + s * NOUTP + rank * OC + j, SKM_ADD(acc, sm[p.bo + j]));
+      if (rank * OC + j < NOUT) scl_send(lg + s * NOUTP + rank * OC + j, SKM_ADD(acc, sm[p.bo + j]), bar_LG);
     }
-    scl_cluster_sync();
+    scl_wait(bar_LG, par);
     // ---- per-sketch draw and feedback (model.py:219-261): warp s draws sketch s; lanes share the transcendentals,
     //      lane 0 does every reduction sequentially, in the order the reference sums ----
     if (warp < rows_valid && !flags[warp]) {
@@ -381,7 +434,10 @@ sample_cluster_kernel(const __grid_constant__ SclArgs a, const __grid_constant__
     if (all_done) break;  // every rank computed the same flags
   }
   if (rank == 0 && tid < rows_valid) a.lengths[sk_base + tid] = flags[SCL_SB + tid];
-  scl_cluster_sync();  // nobody leaves while a peer may still write into it
+  // nobody leaves while a peer may still send into it: the last step's state exchange has landed here, and once every
+  // rank can say so nothing is in flight anywhere in the cluster
+  for (int l = 0; l < L; ++l) scl_wait(bar_H(l), (uint32_t)(last_step & 1));
+  scl_cluster_sync();
 }
 
 }  // namespace
