@@ -43,7 +43,9 @@ struct SclArgs {
   float *strokes;  // [n, steps, 5]
   int *lengths;    // [n]
   float *mixp;     // [n, steps, NOUT] or null
+  int debug;       // SKRNN_TC_DEBUG=1: block 0 prints its per-phase cycle split
 };
+#define SCL_LAP(slot) do { if (dbg) { const long long now_ = clock64(); tk[slot] += now_ - lapt; lapt = now_; } } while (0)
 
 __device__ __forceinline__ uint32_t scl_rank() {
   uint32_t r;
@@ -211,6 +213,9 @@ sample_cluster_kernel(const __grid_constant__ SclArgs a, const __grid_constant__
   for (int l = 0; l < SK_MAX_LAYERS; ++l) cstate[l] = 0.f;
 
   int last_step = 0;
+  const bool dbg = a.debug && blockIdx.x == 0 && tid == 0;
+  long long tk[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  long long lapt = dbg ? clock64() : 0;
   for (int step = 0; step < a.steps; ++step) {
     const uint32_t par = (uint32_t)(step & 1);
     last_step = step;
@@ -226,6 +231,7 @@ sample_cluster_kernel(const __grid_constant__ SclArgs a, const __grid_constant__
       }
       scl_arm(bar_LG, lgbytes);
     }
+    SCL_LAP(0);
 #pragma unroll
     for (int l = 0; l < SK_MAX_LAYERS; ++l) {
       if (l >= L) break;
@@ -308,8 +314,11 @@ sample_cluster_kernel(const __grid_constant__ SclArgs a, const __grid_constant__
         if (l + 1 < L) scl_send(sm + p.xh[l + 1] + cs * scl_kp(2 * H) + u0 + cu, hnew, bar_A(l));
         else scl_send(sm + p.hlast + cs * H + u0 + cu, hnew, bar_A(l));
       }
+      SCL_LAP(1);
       scl_wait(bar_A(l), par);  // every rank's output is here, so every rank is done reading this layer's [x ; h]
+      SCL_LAP(2);
       if (cth) scl_send(xh + cs * Kp + I + u0 + cu, hkeep, bar_H(l));  // waited for at the top of the next step
+      SCL_LAP(3);
     }
     // ---- output projection (model.py:98-99): my OC columns for the SB sketches ----
     if (tid < OC * SCL_SB) {
@@ -321,7 +330,9 @@ sample_cluster_kernel(const __grid_constant__ SclArgs a, const __grid_constant__
       for (int k = 0; k < H; ++k) acc = SKM_FMA(hl[k], Wo[(size_t)k * OC], acc);
       if (rank * OC + j < NOUT) scl_send(lg + s * NOUTP + rank * OC + j, SKM_ADD(acc, sm[p.bo + j]), bar_LG);
     }
+    SCL_LAP(4);
     scl_wait(bar_LG, par);
+    SCL_LAP(5);
     // ---- per-sketch draw and feedback (model.py:219-261): warp s draws sketch s; lanes share the transcendentals,
     //      lane 0 does every reduction sequentially, in the order the reference sums ----
     if (warp < rows_valid && !flags[warp]) {
@@ -428,12 +439,18 @@ sample_cluster_kernel(const __grid_constant__ SclArgs a, const __grid_constant__
         }
       }
     }
+    SCL_LAP(6);
     __syncthreads();
+    SCL_LAP(7);
     int all_done = 1;
     for (int r = 0; r < SCL_SB; ++r) all_done &= flags[r];
     if (all_done) break;  // every rank computed the same flags
   }
   if (rank == 0 && tid < rows_valid) a.lengths[sk_base + tid] = flags[SCL_SB + tid];
+  if (dbg)
+    printf("[sampler_cl] cycles/step: top wait+arm %lld, layers compute+send %lld, wait outputs %lld, state send %lld, output projection %lld, "
+           "wait logits %lld, draw (warp 0) %lld, end barrier %lld\n", tk[0] / (last_step + 1), tk[1] / (last_step + 1), tk[2] / (last_step + 1),
+           tk[3] / (last_step + 1), tk[4] / (last_step + 1), tk[5] / (last_step + 1), tk[6] / (last_step + 1), tk[7] / (last_step + 1));
   // nobody leaves while a peer may still send into it: the last step's state exchange has landed here, and once every
   // rank can say so nothing is in flight anywhere in the cluster
   for (int l = 0; l < L; ++l) scl_wait(bar_H(l), (uint32_t)(last_step & 1));
@@ -469,6 +486,10 @@ int sk_sample_cluster(skrnn_handle *h, cudaStream_t st, int n, int steps, float 
   }
   a.out_w = h->off_out_w; a.out_b = h->off_out_b;
   a.strokes = strokes; a.lengths = lengths; a.mixp = mixp;
+  {
+    const char *e = getenv("SKRNN_TC_DEBUG");
+    a.debug = (e && e[0] == '1') ? 1 : 0;
+  }
   SK_CUDA(cudaFuncSetAttribute(sample_cluster_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   SK_CUDA(cudaFuncSetAttribute(sample_cluster_kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
   cudaLaunchConfig_t lc = {};
