@@ -94,6 +94,57 @@ __device__ __forceinline__ void scl_wait(uint32_t bar, uint32_t parity) {
   }
 }
 
+// acc[g] = sequential fma chain over k = 0..K-1 of As[k] * W[k][g]  (W: NG adjacent floats per k, `stride` floats from
+// one k to the next).  The chain itself costs 4 cycles per k; the operands of the NEXT batch of 8 are requested before
+// the current batch is consumed so that the shared-memory latency hides behind it (one warp per scheduler: nothing
+// else would).  `As` is 16-byte aligned.
+template <int NG>
+__device__ __forceinline__ void scl_dot(const float *__restrict__ As, const float *__restrict__ W, int stride, int K, float (&acc)[NG]) {
+  constexpr int UB = 8;
+  float wc[UB][NG], ac[UB];
+  auto load = [&](int k0, float (&w)[UB][NG], float (&av)[UB]) {
+    const float4 a0 = *reinterpret_cast<const float4 *>(As + k0), a1 = *reinterpret_cast<const float4 *>(As + k0 + 4);
+    av[0] = a0.x; av[1] = a0.y; av[2] = a0.z; av[3] = a0.w; av[4] = a1.x; av[5] = a1.y; av[6] = a1.z; av[7] = a1.w;
+#pragma unroll
+    for (int j = 0; j < UB; ++j) {
+      const float *wp = W + (size_t)(k0 + j) * stride;
+      if constexpr (NG == 4) {
+        const float4 v = *reinterpret_cast<const float4 *>(wp);
+        w[j][0] = v.x; w[j][1] = v.y; w[j][2] = v.z; w[j][3] = v.w;
+      } else if constexpr (NG == 2) {
+        const float2 v = *reinterpret_cast<const float2 *>(wp);
+        w[j][0] = v.x; w[j][1] = v.y;
+      } else {
+        w[j][0] = *wp;
+      }
+    }
+  };
+  const int KB = K / UB * UB;
+  if (KB > 0) load(0, wc, ac);
+  for (int k0 = 0; k0 < KB; k0 += UB) {
+    float wn[UB][NG], an[UB];
+    const bool more = k0 + UB < KB;
+    if (more) load(k0 + UB, wn, an);
+#pragma unroll
+    for (int j = 0; j < UB; ++j)
+#pragma unroll
+      for (int g = 0; g < NG; ++g) acc[g] = SKM_FMA(ac[j], wc[j][g], acc[g]);
+    if (more) {
+#pragma unroll
+      for (int j = 0; j < UB; ++j) {
+        ac[j] = an[j];
+#pragma unroll
+        for (int g = 0; g < NG; ++g) wc[j][g] = wn[j][g];
+      }
+    }
+  }
+  for (int k = KB; k < K; ++k) {
+    const float av = As[k];
+#pragma unroll
+    for (int g = 0; g < NG; ++g) acc[g] = SKM_FMA(av, W[(size_t)k * stride + g], acc[g]);
+  }
+}
+
 // first index with running (fp64) sum >= u, else -1   (get_pi_idx, model.py:189-197)
 __device__ __forceinline__ int scl_pick_idx(const float *pdf, int n, float u) {
   double acc = 0.0;
@@ -114,6 +165,7 @@ struct SclPlan {
   int rh;                                    // gru: [SB][H]  r*h of the layer being computed
   int hlast;                                 // [SB][H]  output of the last layer
   int lg, xin, pdf, flags;                   // [SB][NOUT], [SB][5 -> 8], [SB][M], 2*SB ints
+  int cst;                                   // lstm cell state: [L][UPC*SB], one slot per cell thread
   int bars;                                  // mbarriers (8 bytes each): per layer A (output), R (gru r*h), Hb (state); then LG
   int total;
 };
@@ -146,6 +198,7 @@ __host__ __device__ inline SclPlan scl_plan(int cell, int H, int L, int M, int N
   p.xin = o; o += SCL_SB * 8;
   p.pdf = o; o += SCL_SB * ((M + 3) & ~3);
   p.flags = o; o += 2 * SCL_SB;
+  p.cst = o; o += L * UPC * SCL_SB;
   o = (o + 3) & ~3;
   p.bars = o; o += 2 * (3 * SK_MAX_LAYERS + 1);
   p.total = o;
@@ -208,9 +261,7 @@ sample_cluster_kernel(const __grid_constant__ SclArgs a, const __grid_constant__
   // cell threads: one per (unit, sketch); the lstm cell state stays in its registers
   const bool cth = tid < UPC * SCL_SB;
   const int cu = tid % UPC, cs = tid / UPC;
-  float cstate[SK_MAX_LAYERS];
-#pragma unroll
-  for (int l = 0; l < SK_MAX_LAYERS; ++l) cstate[l] = 0.f;
+  float *cst = sm + p.cst + tid;  // + l * UPC * SB
 
   int last_step = 0;
   const bool dbg = a.debug && blockIdx.x == 0 && tid == 0;
@@ -232,9 +283,7 @@ sample_cluster_kernel(const __grid_constant__ SclArgs a, const __grid_constant__
       scl_arm(bar_LG, lgbytes);
     }
     SCL_LAP(0);
-#pragma unroll
-    for (int l = 0; l < SK_MAX_LAYERS; ++l) {
-      if (l >= L) break;
+    for (int l = 0; l < L; ++l) {
       const int I = (l == 0) ? 5 : H;
       const int K = I + H, Kp = scl_kp(K);
       float *xh = sm + p.xh[l];
@@ -242,20 +291,12 @@ sample_cluster_kernel(const __grid_constant__ SclArgs a, const __grid_constant__
       float hnew = 0.f, hkeep = 0.f;
       if (cell == 0) {
         if (cth) {
-          const float4 *W4 = reinterpret_cast<const float4 *>(sm + p.w[l]) + cu;
           const float *As = xh + cs * Kp;
-          float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
-#pragma unroll 4
-          for (int k = 0; k < K; ++k) {
-            const float av = As[k];
-            const float4 w = W4[(size_t)k * UPC];
-            a0 = SKM_FMA(av, w.x, a0);
-            a1 = SKM_FMA(av, w.y, a1);
-            a2 = SKM_FMA(av, w.z, a2);
-            a3 = SKM_FMA(av, w.w, a3);
-          }
+          float acc[4] = {0.f, 0.f, 0.f, 0.f};
+          scl_dot<4>(As, sm + p.w[l] + 4 * cu, 4 * UPC, K, acc);
+          const float a0 = acc[0], a1 = acc[1], a2 = acc[2], a3 = acc[3];
           const float4 bb = reinterpret_cast<const float4 *>(sm + p.b[l])[cu];
-          const float c = cstate[l];
+          const float c = cst[l * UPC * SCL_SB];
           const float ig = skm_sigmoid(SKM_ADD(a0, bb.x));
           const float jg = skm_tanh(SKM_ADD(a1, bb.y));
           const float fg = skm_sigmoid(SKM_ADD(SKM_ADD(a2, bb.z), 1.0f));
@@ -263,32 +304,25 @@ sample_cluster_kernel(const __grid_constant__ SclArgs a, const __grid_constant__
           const float c2 = SKM_FMA(c, fg, SKM_MUL(ig, jg));
           hnew = SKM_MUL(skm_tanh(c2), og);
           hkeep = hold ? As[I + u0 + cu] : hnew;
-          if (!hold) cstate[l] = c2;
+          if (!hold) cst[l * UPC * SCL_SB] = c2;
         }
       } else if (cell == 2) {
         if (cth) {
-          const float *W1 = sm + p.w[l] + cu;
           const float *As = xh + cs * Kp;
-          float acc = 0.f;
-#pragma unroll 4
-          for (int k = 0; k < K; ++k) acc = SKM_FMA(As[k], W1[(size_t)k * UPC], acc);
-          hnew = skm_tanh(SKM_ADD(acc, sm[p.b[l] + cu]));
+          float acc[1] = {0.f};
+          scl_dot<1>(As, sm + p.w[l] + cu, UPC, K, acc);
+          hnew = skm_tanh(SKM_ADD(acc[0], sm[p.b[l] + cu]));
           hkeep = hold ? As[I + u0 + cu] : hnew;
         }
       } else {
         float az = 0.f, hold_h = 0.f;
         float *rh = sm + p.rh;
         if (cth) {  // gates r, u on [x ; h]
-          const float2 *W2 = reinterpret_cast<const float2 *>(sm + p.w[l]) + cu;
           const float *As = xh + cs * Kp;
-          float ar = 0.f;
-#pragma unroll 4
-          for (int k = 0; k < K; ++k) {
-            const float av = As[k];
-            const float2 w = W2[(size_t)k * UPC];
-            ar = SKM_FMA(av, w.x, ar);
-            az = SKM_FMA(av, w.y, az);
-          }
+          float acc[2] = {0.f, 0.f};
+          scl_dot<2>(As, sm + p.w[l] + 2 * cu, 2 * UPC, K, acc);
+          float ar = acc[0];
+          az = acc[1];
           const float2 bb = reinterpret_cast<const float2 *>(sm + p.b[l])[cu];
           hold_h = As[I + u0 + cu];
           ar = SKM_MUL(skm_sigmoid(SKM_ADD(ar, bb.x)), hold_h);  // r * h
@@ -300,11 +334,14 @@ sample_cluster_kernel(const __grid_constant__ SclArgs a, const __grid_constant__
           const float *Wc = sm + p.wc[l] + cu;
           const float *Ax = xh + cs * Kp;
           const float *Ar = rh + cs * H;
-          float ac = 0.f;
-          for (int k = 0; k < I; ++k) ac = SKM_FMA(Ax[k], Wc[(size_t)k * UPC], ac);
-#pragma unroll 4
-          for (int k = 0; k < H; ++k) ac = SKM_FMA(Ar[k], Wc[(size_t)(I + k) * UPC], ac);
-          const float cand = skm_tanh(SKM_ADD(ac, sm[p.bc[l] + cu]));
+          float acc[1] = {0.f};
+          if (l == 0) {  // 5 input columns, then r*h (the continuation of the same chain)
+            for (int k = 0; k < I; ++k) acc[0] = SKM_FMA(Ax[k], Wc[(size_t)k * UPC], acc[0]);
+          } else {
+            scl_dot<1>(Ax, Wc, UPC, I, acc);
+          }
+          scl_dot<1>(Ar, Wc + (size_t)I * UPC, UPC, H, acc);
+          const float cand = skm_tanh(SKM_ADD(acc[0], sm[p.bc[l] + cu]));
           hnew = SKM_FMA(az, hold_h, SKM_MUL(SKM_SUB(1.0f, az), cand));
           hkeep = hold ? hold_h : hnew;
         }
@@ -325,10 +362,9 @@ sample_cluster_kernel(const __grid_constant__ SclArgs a, const __grid_constant__
       const int j = tid % OC, s = tid / OC;
       const float *Wo = sm + p.wo + j;
       const float *hl = sm + p.hlast + s * H;
-      float acc = 0.f;
-#pragma unroll 4
-      for (int k = 0; k < H; ++k) acc = SKM_FMA(hl[k], Wo[(size_t)k * OC], acc);
-      if (rank * OC + j < NOUT) scl_send(lg + s * NOUTP + rank * OC + j, SKM_ADD(acc, sm[p.bo + j]), bar_LG);
+      float acc[1] = {0.f};
+      scl_dot<1>(hl, Wo, OC, H, acc);
+      if (rank * OC + j < NOUT) scl_send(lg + s * NOUTP + rank * OC + j, SKM_ADD(acc[0], sm[p.bo + j]), bar_LG);
     }
     SCL_LAP(4);
     scl_wait(bar_LG, par);
