@@ -119,24 +119,26 @@ __device__ __forceinline__ void scl_dot(const float *__restrict__ As, const floa
       }
     }
   };
-  const int KB = K / UB * UB;
-  if (KB > 0) load(0, wc, ac);
-  for (int k0 = 0; k0 < KB; k0 += UB) {
-    float wn[UB][NG], an[UB];
-    const bool more = k0 + UB < KB;
-    if (more) load(k0 + UB, wn, an);
+  auto fma8 = [&](const float (&w)[UB][NG], const float (&av)[UB]) {
 #pragma unroll
     for (int j = 0; j < UB; ++j)
 #pragma unroll
-      for (int g = 0; g < NG; ++g) acc[g] = SKM_FMA(ac[j], wc[j][g], acc[g]);
-    if (more) {
-#pragma unroll
-      for (int j = 0; j < UB; ++j) {
-        ac[j] = an[j];
-#pragma unroll
-        for (int g = 0; g < NG; ++g) wc[j][g] = wn[j][g];
-      }
+      for (int g = 0; g < NG; ++g) acc[g] = SKM_FMA(av[j], w[j][g], acc[g]);
+  };
+  const int KB = K & ~(2 * UB - 1);  // blocks of 16: two register sets in ping-pong, no copies
+  if (KB > 0) {
+    float wd[UB][NG], ad[UB];
+    load(0, wc, ac);
+    int k0 = 0;
+    for (; k0 + 2 * UB < KB; k0 += 2 * UB) {
+      load(k0 + UB, wd, ad);
+      fma8(wc, ac);
+      load(k0 + 2 * UB, wc, ac);
+      fma8(wd, ad);
     }
+    load(k0 + UB, wd, ad);
+    fma8(wc, ac);
+    fma8(wd, ad);
   }
   for (int k = KB; k < K; ++k) {
     const float av = As[k];
