@@ -326,14 +326,10 @@ int sk_sample_f32(skrnn_handle *h, cudaStream_t st, int n, int steps, float temp
   SK_CUDA(cudaMemsetAsync(strokes, 0, (size_t)n * steps * 5 * sizeof(float), st));
   if (mixp) SK_CUDA(cudaMemsetAsync(mixp, 0, (size_t)n * steps * h->NOUT * sizeof(float), st));
   {
-    // few sketches: the cluster-resident kernel (sampler_cl.cu), same arithmetic; above the threshold the streaming
-    // kernel below wins because it keeps every SM busy with its own group of sketches
-    const char *e = getenv("SKRNN_SAMPLE_CLUSTER_MAX");
-    const int cl_max = e ? atoi(e) : 512;
-    if (n <= cl_max) {
-      const int r = sk_sample_cluster(h, st, n, steps, temp_mix, temp_pen, stop_if_eoc, uniforms, seed, sketch0, strokes, lengths, mixp);
-      if (r >= 0) return r;
-    }
+    // few sketches: the cluster-resident kernel (sampler_cl.cu), same arithmetic; it declines (-1) when the stack does
+    // not fit a cluster's shared memory or when there are so many sketches that the streaming kernel below wins
+    const int r = sk_sample_cluster(h, st, n, steps, temp_mix, temp_pen, stop_if_eoc, uniforms, seed, sketch0, strokes, lengths, mixp);
+    if (r >= 0) return r;
   }
   int64_t need = (int64_t)n * h->L * h->S;
   if (need > h->samp_state_n) {

@@ -547,6 +547,13 @@ int sk_sample_cluster(skrnn_handle *h, cudaStream_t st, int n, int steps, float 
     cudaGetLastError();
     return -1;
   }
+  {
+    // Worth it up to about four waves of clusters (measured on the kanji model: ~4.1 ms per wave of 300 steps against
+    // ~24 ms for the streaming kernel, which takes that long for anything from 1 to ~600 sketches)
+    const char *e = getenv("SKRNN_SAMPLE_CLUSTER_MAX");
+    const int n_max = e ? atoi(e) : 4 * SCL_SB * nclusters;
+    if (n > n_max) return -1;
+  }
   SkLaunch scope(h, st, SK_CAT_SAMPLER);
   SK_CUDA(cudaLaunchKernelEx(&lc, sample_cluster_kernel, a, p));
   return 0;
