@@ -216,6 +216,26 @@ def test_sampler_bit_exact(model, H, L, M, kernel, monkeypatch):
     h.close()
 
 
+@pytest.mark.parametrize("model,H", [("lstm", 256), ("gru", 64)])
+def test_sampler_bit_exact_many_sketches(model, H):
+    """More sketches than 4 per SM: the streaming kernel's 16-sketches-per-CTA instance (weights prefetched one
+    batch of k ahead), ragged last CTA; a spread of sketches replayed by the CPU restatement."""
+    cfg = so.Config(model=model, rnn_size=H, num_layers=2, num_mixture=24)
+    params = so.init_params(cfg, seed=11, trained_like=True)
+    h = make_handle(cfg, params)
+    n, steps, temp = 4 * h.num_sms() + 37 if hasattr(h, "num_sms") else 629, 14, 0.6
+    u = np.random.RandomState(5).rand(n, steps, 4).astype(np.float32)
+    strokes, lengths, _ = h.sample(n, steps, temp, temp, True, uniforms=u)
+    strokes, lengths = strokes.cpu().numpy(), lengths.cpu().numpy()
+    for i in [0, 1, 15, 16, 17, 300, n - 17, n - 2, n - 1]:
+        ref_s, _ = sampler_ref.sample(cfg, params, u[i], steps, temp, temp, True, want_params=True)
+        k = ref_s.shape[0]
+        assert lengths[i] == k, (i, lengths[i], k)
+        assert np.array_equal(strokes[i, :k].view(np.uint32), ref_s.view(np.uint32)), (model, i)
+        assert np.all(strokes[i, k:] == 0)
+    h.close()
+
+
 def test_sampler_against_numpy_transcription():
     """Independent check of the sampler against the NumPy transcription of model.py:187-264."""
     cfg = so.Config(model="lstm", rnn_size=32, num_layers=2, num_mixture=6)
