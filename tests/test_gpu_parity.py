@@ -216,14 +216,15 @@ def test_sampler_bit_exact(model, H, L, M, kernel, monkeypatch):
     h.close()
 
 
-@pytest.mark.parametrize("model,H", [("lstm", 256), ("gru", 64)])
-def test_sampler_bit_exact_many_sketches(model, H):
-    """More sketches than 4 per SM: the streaming kernel's 16-sketches-per-CTA instance (weights prefetched one
-    batch of k ahead), ragged last CTA; a spread of sketches replayed by the CPU restatement."""
+@pytest.mark.parametrize("model,H,n", [("lstm", 256, 629), ("gru", 64, 629), ("lstm", 256, 2405), ("lstm", 72, 2405)])
+def test_sampler_bit_exact_many_sketches(model, H, n):
+    """More sketches than 4 per SM: the streaming kernel's 16-sketches-per-CTA instance and, beyond 16 per SM, the
+    lstm instance with 32 sketches per CTA and a unit's gates split over two threads; ragged last CTA; a spread of
+    sketches replayed by the CPU restatement."""
     cfg = so.Config(model=model, rnn_size=H, num_layers=2, num_mixture=24)
     params = so.init_params(cfg, seed=11, trained_like=True)
     h = make_handle(cfg, params)
-    n, steps, temp = 4 * h.num_sms() + 37 if hasattr(h, "num_sms") else 629, 14, 0.6
+    steps, temp = 14, 0.6
     u = np.random.RandomState(5).rand(n, steps, 4).astype(np.float32)
     strokes, lengths, _ = h.sample(n, steps, temp, temp, True, uniforms=u)
     strokes, lengths = strokes.cpu().numpy(), lengths.cpu().numpy()
