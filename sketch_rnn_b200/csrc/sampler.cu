@@ -48,11 +48,8 @@ __device__ __forceinline__ int pick_idx(const float *pdf, int n, float u) {
   return -1;
 }
 
-// GH = 2 (lstm, blockDim = 2H): a unit's gates are split over two threads -- (i, j) and (f, o) -- so that a CTA carries
-// twice the sketches with the same 4 * SB / GH accumulators per thread: the weights of a step are then fetched from L2
-// once per 32 sketches instead of once per 16 (at 8192 sketches the 16-sketch form moves 3.8 TB/s out of L2).
-template <int SB, int GH>
-__global__ void __launch_bounds__(512) sample_kernel(SampArgs a) {
+template <int SB, int MAXT>  // MAXT: 256 when rnn_size <= 256 (lets the compiler keep two prefetch sets next to 4 * SB accumulators)
+__global__ void __launch_bounds__(MAXT) sample_kernel(SampArgs a) {
   extern __shared__ __align__(16) float smem[];
   const int tid = threadIdx.x, NT = blockDim.x;
   const int H = a.H, L = a.L, M = a.M, NOUT = a.NOUT;
@@ -69,7 +66,6 @@ __global__ void __launch_bounds__(512) sample_kernel(SampArgs a) {
   float *xin = lg + (size_t)SB * NOUT;    // [SB][5] current input point
   float *pdf = xin + SB * 5;              // [SB][M] scratch for the per-sketch draw
   int *flags = reinterpret_cast<int *>(pdf + (size_t)SB * M);  // [SB] done, [SB] length
-  float *ex = reinterpret_cast<float *>(flags + 2 * SB);       // GH = 2: [SB][H][2] activated f, o gates on their way to the (i, j) thread
 
   for (int i = tid; i < SB * 5; i += NT) xin[i] = 0.f;  // first input is all zeros (model.py:205)
   for (int i = tid; i < SB; i += NT) { flags[i] = (i < rows_valid) ? 0 : 1; flags[SB + i] = 0; }
@@ -95,68 +91,64 @@ __global__ void __launch_bounds__(512) sample_kernel(SampArgs a) {
       __syncthreads();
       const float *W = a.params + a.w0[l];
       const float *bias = a.params + a.b0[l];
-      if (a.cell == 0 && GH == 2) {
-        const int half = tid / H, uu = tid - half * H;
-        float acc[SB][2];
-        if (tid < 2 * H) {
-#pragma unroll
-          for (int r = 0; r < SB; ++r) { acc[r][0] = acc[r][1] = 0.f; }
-#pragma unroll 2  // weight loads of two k in flight: the chain per accumulator stays sequential
-          for (int k = 0; k < K; ++k) {
-            const float *wr = W + (size_t)k * (4 * H) + half * 2 * H + uu;
-            float w0 = __ldg(wr), w1 = __ldg(wr + H);
-#pragma unroll
-            for (int r = 0; r < SB; ++r) {
-              float av = AT[(size_t)k * SB + r];
-              acc[r][0] = SKM_FMA(av, w0, acc[r][0]);
-              acc[r][1] = SKM_FMA(av, w1, acc[r][1]);
-            }
-          }
-          if (half == 1) {
-            const float bf = bias[2 * H + uu], bo = bias[3 * H + uu];
-#pragma unroll
-            for (int r = 0; r < SB; ++r) {
-              ex[((size_t)r * H + uu) * 2] = skm_sigmoid(SKM_ADD(SKM_ADD(acc[r][0], bf), 1.0f));
-              ex[((size_t)r * H + uu) * 2 + 1] = skm_sigmoid(SKM_ADD(acc[r][1], bo));
-            }
-          }
-        }
-        __syncthreads();
-        if (act) {
-          const float bi = bias[u], bj = bias[H + u];
-#pragma unroll
-          for (int r = 0; r < SB; ++r) {
-            if (r >= rows_valid) { nxt[(size_t)u * SB + r] = 0.f; continue; }
-            float *st = a.state + ((size_t)(sk_base + r) * L + l) * S;
-            float c = st[u];
-            float ig = skm_sigmoid(SKM_ADD(acc[r][0], bi));
-            float jg = skm_tanh(SKM_ADD(acc[r][1], bj));
-            float fg = ex[((size_t)r * H + u) * 2];
-            float og = ex[((size_t)r * H + u) * 2 + 1];
-            float c2 = SKM_FMA(c, fg, SKM_MUL(ig, jg));
-            float h2 = SKM_MUL(skm_tanh(c2), og);
-            nxt[(size_t)u * SB + r] = h2;
-            // an eoc input holds the state: initial_state is prev_state (model.py:82-92,215)
-            if (!(xin[r * 5 + 3] > 0.f)) { st[u] = c2; st[H + u] = h2; }
-          }
-        }
-      } else if constexpr (GH == 1) {
       if (a.cell == 0) {
         if (act) {
           float acc[SB][4];
 #pragma unroll
           for (int r = 0; r < SB; ++r) { acc[r][0] = acc[r][1] = acc[r][2] = acc[r][3] = 0.f; }
-#pragma unroll (SB >= 16 ? 2 : 8)  // weight loads of several k in flight: the chain per accumulator stays sequential
-          for (int k = 0; k < K; ++k) {
-            const float *wr = W + (size_t)k * (4 * H) + u;
-            float w0 = __ldg(wr), w1 = __ldg(wr + H), w2 = __ldg(wr + 2 * H), w3 = __ldg(wr + 3 * H);
+          // The four weights of (k, unit) come from L2 (~800 cycles away): they are requested one batch of 8 k ahead, in
+          // two register sets used in ping-pong, so that the latency hides behind the 8 * 4 * SB fmas of the batch in
+          // hand.  The chain per accumulator stays sequential in k.  Past K the weights (and operands) read as zero:
+          // adding +0 leaves an accumulator unchanged bit for bit (it starts at +0 and can never become -0).
+          if constexpr (MAXT <= 256 || SB < 16) {
+          constexpr int UB = 8;
+          auto ldw = [&](int k0, float (&w)[UB][4]) {
 #pragma unroll
-            for (int r = 0; r < SB; ++r) {
-              float av = AT[(size_t)k * SB + r];
-              acc[r][0] = SKM_FMA(av, w0, acc[r][0]);
-              acc[r][1] = SKM_FMA(av, w1, acc[r][1]);
-              acc[r][2] = SKM_FMA(av, w2, acc[r][2]);
-              acc[r][3] = SKM_FMA(av, w3, acc[r][3]);
+            for (int j = 0; j < UB; ++j) {
+              const int k = k0 + j;
+              const float *wr = W + (size_t)k * (4 * H) + u;
+              const bool ok = k < K;
+              w[j][0] = ok ? __ldg(wr) : 0.f;
+              w[j][1] = ok ? __ldg(wr + H) : 0.f;
+              w[j][2] = ok ? __ldg(wr + 2 * H) : 0.f;
+              w[j][3] = ok ? __ldg(wr + 3 * H) : 0.f;
+            }
+          };
+          auto fma8 = [&](int k0, const float (&w)[UB][4]) {
+#pragma unroll
+            for (int j = 0; j < UB; ++j) {
+              const int k = k0 + j;
+#pragma unroll
+              for (int r = 0; r < SB; ++r) {
+                const float av = (k < K) ? AT[(size_t)k * SB + r] : 0.f;
+                acc[r][0] = SKM_FMA(av, w[j][0], acc[r][0]);
+                acc[r][1] = SKM_FMA(av, w[j][1], acc[r][1]);
+                acc[r][2] = SKM_FMA(av, w[j][2], acc[r][2]);
+                acc[r][3] = SKM_FMA(av, w[j][3], acc[r][3]);
+              }
+            }
+          };
+          float wa[UB][4], wb[UB][4];
+          ldw(0, wa);
+          for (int k0 = 0; k0 < K; k0 += 2 * UB) {
+            ldw(k0 + UB, wb);
+            fma8(k0, wa);
+            ldw(k0 + 2 * UB, wa);
+            fma8(k0 + UB, wb);
+          }
+          } else {  // 512 threads x 64 accumulators leave no registers for the prefetch sets
+#pragma unroll 2
+            for (int k = 0; k < K; ++k) {
+              const float *wr = W + (size_t)k * (4 * H) + u;
+              float w0 = __ldg(wr), w1 = __ldg(wr + H), w2 = __ldg(wr + 2 * H), w3 = __ldg(wr + 3 * H);
+#pragma unroll
+              for (int r = 0; r < SB; ++r) {
+                float av = AT[(size_t)k * SB + r];
+                acc[r][0] = SKM_FMA(av, w0, acc[r][0]);
+                acc[r][1] = SKM_FMA(av, w1, acc[r][1]);
+                acc[r][2] = SKM_FMA(av, w2, acc[r][2]);
+                acc[r][3] = SKM_FMA(av, w3, acc[r][3]);
+              }
             }
           }
           const float bi = bias[u], bj = bias[H + u], bf = bias[2 * H + u], bo = bias[3 * H + u];
@@ -247,7 +239,6 @@ __global__ void __launch_bounds__(512) sample_kernel(SampArgs a) {
           }
         }
       }
-      }  // GH == 1
       __syncthreads();
     }
     // ---- output projection (model.py:98-99) ----
@@ -355,14 +346,19 @@ __global__ void __launch_bounds__(512) sample_kernel(SampArgs a) {
   for (int i = tid; i < rows_valid; i += NT) a.lengths[sk_base + i] = flags[SB + i];
 }
 
-template <int SB, int GH = 1>
+template <int SB>
 int launch_sample(skrnn_handle *h, cudaStream_t st, const SampArgs &a, int threads) {
-  size_t smem = ((size_t)3 * a.H * SB + (size_t)SB * a.NOUT + SB * 5 + (size_t)SB * a.M + 2 * SB + (GH == 2 ? (size_t)2 * a.H * SB : 0)) * 4;
+  size_t smem = ((size_t)3 * a.H * SB + (size_t)SB * a.NOUT + SB * 5 + (size_t)SB * a.M + 2 * SB) * 4;
   SK_CHECK(smem <= 227 * 1024, "sampler needs %zu B of shared memory (rnn_size too large)", smem);
-  SK_CUDA(cudaFuncSetAttribute(sample_kernel<SB, GH>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   int blocks = (a.n + SB - 1) / SB;
   SkLaunch scope(h, st, SK_CAT_SAMPLER);
-  sample_kernel<SB, GH><<<blocks, threads, smem, st>>>(a);
+  if (threads <= 256) {
+    SK_CUDA(cudaFuncSetAttribute(sample_kernel<SB, 256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    sample_kernel<SB, 256><<<blocks, threads, smem, st>>>(a);
+  } else {
+    SK_CUDA(cudaFuncSetAttribute(sample_kernel<SB, 512>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    sample_kernel<SB, 512><<<blocks, threads, smem, st>>>(a);
+  }
   SK_CUDA(cudaGetLastError());
   return 0;
 }
@@ -406,9 +402,5 @@ int sk_sample_f32(skrnn_handle *h, cudaStream_t st, int n, int steps, float temp
   int threads = max(256, (h->H + 31) / 32 * 32);
   if (n <= 2) return launch_sample<1>(h, st, a, threads);
   if (n <= 4 * h->num_sms) return launch_sample<4>(h, st, a, threads);
-  if (a.cell == 0 && 2 * h->H <= 512 && n > 16 * h->num_sms) {
-    const char *e = getenv("SKRNN_SAMPLE_WIDE");
-    if (!(e && e[0] == '0')) return launch_sample<32, 2>(h, st, a, (2 * h->H + 31) / 32 * 32);
-  }
   return launch_sample<16>(h, st, a, threads);
 }

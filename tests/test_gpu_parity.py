@@ -216,11 +216,10 @@ def test_sampler_bit_exact(model, H, L, M, kernel, monkeypatch):
     h.close()
 
 
-@pytest.mark.parametrize("model,H,n", [("lstm", 256, 629), ("gru", 64, 629), ("lstm", 256, 2405), ("lstm", 72, 2405)])
+@pytest.mark.parametrize("model,H,n", [("lstm", 256, 629), ("gru", 64, 629), ("lstm", 72, 2405)])
 def test_sampler_bit_exact_many_sketches(model, H, n):
-    """More sketches than 4 per SM: the streaming kernel's 16-sketches-per-CTA instance and, beyond 16 per SM, the
-    lstm instance with 32 sketches per CTA and a unit's gates split over two threads; ragged last CTA; a spread of
-    sketches replayed by the CPU restatement."""
+    """More sketches than 4 per SM: the streaming kernel's 16-sketches-per-CTA instance, ragged last CTA; a spread
+    of sketches replayed by the CPU restatement."""
     cfg = so.Config(model=model, rnn_size=H, num_layers=2, num_mixture=24)
     params = so.init_params(cfg, seed=11, trained_like=True)
     h = make_handle(cfg, params)
