@@ -1,7 +1,7 @@
 #!/bin/bash
 # Round-2 evidence run on one B200 (under gpurun): tests, smoke, bench lines, train.py time/batch, ncu launch list and
-# full captures.  Everything lands in gpurun_out/r02p/.
-O=gpurun_out/r02p; mkdir -p $O
+# full captures.  Everything lands in gpurun_out/<first argument, default r02p>/.
+O=gpurun_out/${1:-r02p}; mkdir -p $O
 python -m pytest tests -m gpu -q > $O/tests.log 2>&1; tail -3 $O/tests.log
 python -c "import __graft_entry__ as g; g.smoke()" > $O/smoke.log 2>&1; tail -2 $O/smoke.log
 python bench.py --steps 20 --warmup 5 > $O/bench_train_h512_l3_b800_bf16.json 2> $O/bench_default.err; tail -c 300 $O/bench_default.err
@@ -22,6 +22,14 @@ ncu --set full --clock-control none --import-source on -k regex:"lstm_bwd_pp|lst
 python tools/run_one.py 256 2 100 300 bf16 gru > $O/plain_gru.log 2>&1 &&
 ncu --set full --clock-control none --import-source on -k regex:"rnn1_" -s 4 -c 4 -o $O/gru \
     python tools/run_one.py 256 2 100 300 bf16 gru > $O/ncu_gru.log 2>&1
+python tools/run_one.py 256 2 100 300 bf16 rnn > $O/plain_rnn.log 2>&1 &&
+ncu --set full --clock-control none --import-source on -k regex:"rnn1_" -s 4 -c 4 -o $O/rnn \
+    python tools/run_one.py 256 2 100 300 bf16 rnn > $O/ncu_rnn.log 2>&1
+for n in 1 10 28 64 512; do python tools/sample_time.py $n 300; done > $O/sample_latency.txt 2>&1; cat $O/sample_latency.txt
+python tools/sample_time.py 10 300 gru >> $O/sample_latency.txt 2>&1; python tools/sample_time.py 10 300 rnn >> $O/sample_latency.txt 2>&1
+python tools/sample_time.py 4 60 > $O/plain_samplecl.log 2>&1 &&
+ncu --set full --clock-control none --import-source on -k regex:"sample_cluster" -s 2 -c 1 -o $O/samplecl \
+    python tools/sample_time.py 4 60 > $O/ncu_samplecl.log 2>&1
 python tools/run_sample.py 8192 12 > $O/plain_sample.log 2>&1 &&
 ncu --set full --clock-control none -k regex:"samp_draw|gemm_tc_persist" -s 40 -c 4 -o $O/sampler \
     python tools/run_sample.py 8192 12 > $O/ncu_sampler.log 2>&1
