@@ -48,8 +48,8 @@ __device__ __forceinline__ int pick_idx(const float *pdf, int n, float u) {
   return -1;
 }
 
-template <int SB, int MAXT>  // MAXT: 256 when rnn_size <= 256 (lets the compiler keep two prefetch sets next to 4 * SB accumulators)
-__global__ void __launch_bounds__(MAXT) sample_kernel(SampArgs a) {
+template <int SB>
+__global__ void __launch_bounds__(512) sample_kernel(SampArgs a) {
   extern __shared__ __align__(16) float smem[];
   const int tid = threadIdx.x, NT = blockDim.x;
   const int H = a.H, L = a.L, M = a.M, NOUT = a.NOUT;
@@ -96,59 +96,17 @@ __global__ void __launch_bounds__(MAXT) sample_kernel(SampArgs a) {
           float acc[SB][4];
 #pragma unroll
           for (int r = 0; r < SB; ++r) { acc[r][0] = acc[r][1] = acc[r][2] = acc[r][3] = 0.f; }
-          // The four weights of (k, unit) come from L2 (~800 cycles away): they are requested one batch of 8 k ahead, in
-          // two register sets used in ping-pong, so that the latency hides behind the 8 * 4 * SB fmas of the batch in
-          // hand.  The chain per accumulator stays sequential in k.  Past K the weights (and operands) read as zero:
-          // adding +0 leaves an accumulator unchanged bit for bit (it starts at +0 and can never become -0).
-          if constexpr (MAXT <= 256 || SB < 16) {
-          constexpr int UB = 8;
-          auto ldw = [&](int k0, float (&w)[UB][4]) {
+#pragma unroll (SB >= 16 ? 2 : 8)  // weight loads of several k in flight: the chain per accumulator stays sequential
+          for (int k = 0; k < K; ++k) {
+            const float *wr = W + (size_t)k * (4 * H) + u;
+            float w0 = __ldg(wr), w1 = __ldg(wr + H), w2 = __ldg(wr + 2 * H), w3 = __ldg(wr + 3 * H);
 #pragma unroll
-            for (int j = 0; j < UB; ++j) {
-              const int k = k0 + j;
-              const float *wr = W + (size_t)k * (4 * H) + u;
-              const bool ok = k < K;
-              w[j][0] = ok ? __ldg(wr) : 0.f;
-              w[j][1] = ok ? __ldg(wr + H) : 0.f;
-              w[j][2] = ok ? __ldg(wr + 2 * H) : 0.f;
-              w[j][3] = ok ? __ldg(wr + 3 * H) : 0.f;
-            }
-          };
-          auto fma8 = [&](int k0, const float (&w)[UB][4]) {
-#pragma unroll
-            for (int j = 0; j < UB; ++j) {
-              const int k = k0 + j;
-#pragma unroll
-              for (int r = 0; r < SB; ++r) {
-                const float av = (k < K) ? AT[(size_t)k * SB + r] : 0.f;
-                acc[r][0] = SKM_FMA(av, w[j][0], acc[r][0]);
-                acc[r][1] = SKM_FMA(av, w[j][1], acc[r][1]);
-                acc[r][2] = SKM_FMA(av, w[j][2], acc[r][2]);
-                acc[r][3] = SKM_FMA(av, w[j][3], acc[r][3]);
-              }
-            }
-          };
-          float wa[UB][4], wb[UB][4];
-          ldw(0, wa);
-          for (int k0 = 0; k0 < K; k0 += 2 * UB) {
-            ldw(k0 + UB, wb);
-            fma8(k0, wa);
-            ldw(k0 + 2 * UB, wa);
-            fma8(k0 + UB, wb);
-          }
-          } else {  // 512 threads x 64 accumulators leave no registers for the prefetch sets
-#pragma unroll 2
-            for (int k = 0; k < K; ++k) {
-              const float *wr = W + (size_t)k * (4 * H) + u;
-              float w0 = __ldg(wr), w1 = __ldg(wr + H), w2 = __ldg(wr + 2 * H), w3 = __ldg(wr + 3 * H);
-#pragma unroll
-              for (int r = 0; r < SB; ++r) {
-                float av = AT[(size_t)k * SB + r];
-                acc[r][0] = SKM_FMA(av, w0, acc[r][0]);
-                acc[r][1] = SKM_FMA(av, w1, acc[r][1]);
-                acc[r][2] = SKM_FMA(av, w2, acc[r][2]);
-                acc[r][3] = SKM_FMA(av, w3, acc[r][3]);
-              }
+            for (int r = 0; r < SB; ++r) {
+              float av = AT[(size_t)k * SB + r];
+              acc[r][0] = SKM_FMA(av, w0, acc[r][0]);
+              acc[r][1] = SKM_FMA(av, w1, acc[r][1]);
+              acc[r][2] = SKM_FMA(av, w2, acc[r][2]);
+              acc[r][3] = SKM_FMA(av, w3, acc[r][3]);
             }
           }
           const float bi = bias[u], bj = bias[H + u], bf = bias[2 * H + u], bo = bias[3 * H + u];
@@ -350,15 +308,10 @@ template <int SB>
 int launch_sample(skrnn_handle *h, cudaStream_t st, const SampArgs &a, int threads) {
   size_t smem = ((size_t)3 * a.H * SB + (size_t)SB * a.NOUT + SB * 5 + (size_t)SB * a.M + 2 * SB) * 4;
   SK_CHECK(smem <= 227 * 1024, "sampler needs %zu B of shared memory (rnn_size too large)", smem);
+  SK_CUDA(cudaFuncSetAttribute(sample_kernel<SB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   int blocks = (a.n + SB - 1) / SB;
   SkLaunch scope(h, st, SK_CAT_SAMPLER);
-  if (threads <= 256) {
-    SK_CUDA(cudaFuncSetAttribute(sample_kernel<SB, 256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    sample_kernel<SB, 256><<<blocks, threads, smem, st>>>(a);
-  } else {
-    SK_CUDA(cudaFuncSetAttribute(sample_kernel<SB, 512>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    sample_kernel<SB, 512><<<blocks, threads, smem, st>>>(a);
-  }
+  sample_kernel<SB><<<blocks, threads, smem, st>>>(a);
   SK_CUDA(cudaGetLastError());
   return 0;
 }
