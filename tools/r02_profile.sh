@@ -33,4 +33,8 @@ ncu --set full --clock-control none --import-source on -k regex:"sample_cluster"
 python tools/run_sample.py 8192 12 > $O/plain_sample.log 2>&1 &&
 ncu --set full --clock-control none -k regex:"samp_draw|gemm_tc_persist" -s 40 -c 4 -o $O/sampler \
     python tools/run_sample.py 8192 12 > $O/ncu_sampler.log 2>&1
-ls -la $O | tail -30
+# gpurun brings back at most 64 MiB: keep the raw-metrics pages, drop the big reports
+for r in c4 gru rnn sampler samplecl; do
+  [ -f $O/$r.ncu-rep ] && ncu -i $O/$r.ncu-rep --page raw --csv > $O/${r}_raw.csv 2>/dev/null && rm -f $O/$r.ncu-rep
+done
+ls -la $O | tail -40
