@@ -7,9 +7,8 @@
 // cluster owns hidden units [r*UPC, (r+1)*UPC) of every layer (UPC = H/16) and output columns [r*OC, (r+1)*OC), keeps
 // exactly those weight columns in its shared memory for the whole launch (kanji model, lstm H = 256 L = 2: 3.3 MB of
 // fp32 weights = 204 KB per CTA), and the cluster runs SB = 4 sketches together:
-//   per layer:  every rank computes its units' gate sums for the 4 sketches (one thread per weight column = (unit,
-//               gate), the four sketches' operands of a k arriving as one broadcast 16-byte load), hands them to the
-//               thread of (unit, sketch) for the cell update, and sends h into EVERY rank's operand
+//   per layer:  every rank computes its units' gates for the 4 sketches (one thread per (unit, sketch): all gates of a
+//               unit meet in one thread, the cell state lives in its registers) and sends h into EVERY rank's operand
 //               buffers with st.async: the store itself reports its bytes on the receiver's mbarrier, so an exchange
 //               is "wait until H*SB*4 bytes have landed" -- no barrier.cluster (a gpu-scope fence plus an L1
 //               invalidate, ~5 us per step for three of them) in the loop;
@@ -95,34 +94,40 @@ __device__ __forceinline__ void scl_wait(uint32_t bar, uint32_t parity) {
   }
 }
 
-// acc[s] (s = sketch 0..3) += sequential fma chain over k = 0..K-1 of A[k][s] * W[k*stride]: one weight column for the
-// cluster's four sketches.  A is [k][4 sketches] (one 16-byte broadcast load per k), W the thread's own column (lanes
-// read consecutive floats).  The chain itself costs 4 cycles per k; the operands of the NEXT batch of 8 are requested
-// before the current batch is consumed -- two register sets in ping-pong, no copies -- so that the shared-memory
-// latency hides behind it (one warp per scheduler: nothing else would).
-__device__ __forceinline__ void scl_dot4(const float *__restrict__ A, const float *__restrict__ W, int stride, int K, float (&acc)[SCL_SB]) {
-  static_assert(SCL_SB == 4, "one float4 of operands per k");
+// acc[g] = sequential fma chain over k = 0..K-1 of As[k] * W[k][g]  (W: NG adjacent floats per k, `stride` floats from
+// one k to the next).  The chain itself costs 4 cycles per k; the operands of the NEXT batch of 8 are requested before
+// the current batch is consumed so that the shared-memory latency hides behind it (one warp per scheduler: nothing
+// else would).  `As` is 16-byte aligned.
+template <int NG>
+__device__ __forceinline__ void scl_dot(const float *__restrict__ As, const float *__restrict__ W, int stride, int K, float (&acc)[NG]) {
   constexpr int UB = 8;
-  auto load = [&](int k0, float (&w)[UB], float4 (&av)[UB]) {
+  float wc[UB][NG], ac[UB];
+  auto load = [&](int k0, float (&w)[UB][NG], float (&av)[UB]) {
+    const float4 a0 = *reinterpret_cast<const float4 *>(As + k0), a1 = *reinterpret_cast<const float4 *>(As + k0 + 4);
+    av[0] = a0.x; av[1] = a0.y; av[2] = a0.z; av[3] = a0.w; av[4] = a1.x; av[5] = a1.y; av[6] = a1.z; av[7] = a1.w;
 #pragma unroll
     for (int j = 0; j < UB; ++j) {
-      av[j] = *reinterpret_cast<const float4 *>(A + (size_t)(k0 + j) * SCL_SB);
-      w[j] = W[(size_t)(k0 + j) * stride];
+      const float *wp = W + (size_t)(k0 + j) * stride;
+      if constexpr (NG == 4) {
+        const float4 v = *reinterpret_cast<const float4 *>(wp);
+        w[j][0] = v.x; w[j][1] = v.y; w[j][2] = v.z; w[j][3] = v.w;
+      } else if constexpr (NG == 2) {
+        const float2 v = *reinterpret_cast<const float2 *>(wp);
+        w[j][0] = v.x; w[j][1] = v.y;
+      } else {
+        w[j][0] = *wp;
+      }
     }
   };
-  auto fma8 = [&](const float (&w)[UB], const float4 (&av)[UB]) {
+  auto fma8 = [&](const float (&w)[UB][NG], const float (&av)[UB]) {
 #pragma unroll
-    for (int j = 0; j < UB; ++j) {
-      acc[0] = SKM_FMA(av[j].x, w[j], acc[0]);
-      acc[1] = SKM_FMA(av[j].y, w[j], acc[1]);
-      acc[2] = SKM_FMA(av[j].z, w[j], acc[2]);
-      acc[3] = SKM_FMA(av[j].w, w[j], acc[3]);
-    }
+    for (int j = 0; j < UB; ++j)
+#pragma unroll
+      for (int g = 0; g < NG; ++g) acc[g] = SKM_FMA(av[j], w[j][g], acc[g]);
   };
-  const int KB = K & ~(2 * UB - 1);  // blocks of 16
+  const int KB = K & ~(2 * UB - 1);  // blocks of 16: two register sets in ping-pong, no copies
   if (KB > 0) {
-    float wc[UB], wd[UB];
-    float4 ac[UB], ad[UB];
+    float wd[UB][NG], ad[UB];
     load(0, wc, ac);
     int k0 = 0;
     for (; k0 + 2 * UB < KB; k0 += 2 * UB) {
@@ -136,12 +141,9 @@ __device__ __forceinline__ void scl_dot4(const float *__restrict__ A, const floa
     fma8(wd, ad);
   }
   for (int k = KB; k < K; ++k) {
-    const float4 av = *reinterpret_cast<const float4 *>(A + (size_t)k * SCL_SB);
-    const float w = W[(size_t)k * stride];
-    acc[0] = SKM_FMA(av.x, w, acc[0]);
-    acc[1] = SKM_FMA(av.y, w, acc[1]);
-    acc[2] = SKM_FMA(av.z, w, acc[2]);
-    acc[3] = SKM_FMA(av.w, w, acc[3]);
+    const float av = As[k];
+#pragma unroll
+    for (int g = 0; g < NG; ++g) acc[g] = SKM_FMA(av, W[(size_t)k * stride + g], acc[g]);
   }
 }
 
@@ -161,10 +163,9 @@ struct SclPlan {
   int w[SK_MAX_LAYERS], b[SK_MAX_LAYERS];    // lstm: [K][UPC][4], [UPC][4]; gru: [K][UPC][2], [UPC][2]; rnn: [K][UPC], [UPC]
   int wc[SK_MAX_LAYERS], bc[SK_MAX_LAYERS];  // gru candidate: [K][UPC], [UPC]
   int wo, bo;                                // [H][OC], [OC]
-  int xh[SK_MAX_LAYERS];                     // [K][SB]: [x ; h] of the layer, the four sketches of a k adjacent
-  int rh;                                    // gru: [H][SB]  r*h of the layer being computed
-  int hlast;                                 // [H][SB]  output of the last layer
-  int pre;                                   // [gate][UPC][SB] (or [OC][SB]): dot products on their way to the thread that owns (unit, sketch)
+  int xh[SK_MAX_LAYERS];                     // [SB][Kp]: [x ; h] of the layer (Kp = K rounded up to 4)
+  int rh;                                    // gru: [SB][H]  r*h of the layer being computed
+  int hlast;                                 // [SB][H]  output of the last layer
   int lg, xin, pdf, flags;                   // [SB][NOUT], [SB][5 -> 8], [SB][M], 2*SB ints
   int cst;                                   // lstm cell state: [L][UPC*SB], one slot per cell thread
   int bars;                                  // mbarriers (8 bytes each): per layer A (output), R (gru r*h), Hb (state); then LG
@@ -191,11 +192,10 @@ __host__ __device__ inline SclPlan scl_plan(int cell, int H, int L, int M, int N
   o = (o + 3) & ~3;
   for (int l = 0; l < L; ++l) {
     p.xh[l] = o;
-    o += SCL_SB * ((l == 0 ? 5 : H) + H);
+    o += SCL_SB * scl_kp((l == 0 ? 5 : H) + H);
   }
   if (cell == 1) { p.rh = o; o += SCL_SB * H; }
   p.hlast = o; o += SCL_SB * H;
-  p.pre = o; o += SCL_SB * (4 * UPC > OC ? 4 * UPC : OC);
   p.lg = o; o += SCL_SB * ((NOUT + 3) & ~3);
   p.xin = o; o += SCL_SB * 8;
   p.pdf = o; o += SCL_SB * ((M + 3) & ~3);
@@ -287,24 +287,16 @@ sample_cluster_kernel(const __grid_constant__ SclArgs a, const __grid_constant__
     SCL_LAP(0);
     for (int l = 0; l < L; ++l) {
       const int I = (l == 0) ? 5 : H;
-      const int K = I + H;
+      const int K = I + H, Kp = scl_kp(K);
       float *xh = sm + p.xh[l];
-      float *pre = sm + p.pre;
       const bool hold = cth && xin[cs * 8 + 3] > 0.f;  // an eoc input holds the state (model.py:82-92,215)
       float hnew = 0.f, hkeep = 0.f;
-      // dot products: thread tid < ng * UPC owns weight column (unit tid / ng, gate tid % ng) for the four sketches; the
-      // sums then go through `pre` to the cell thread of (unit, sketch)
-      if (tid < ng * UPC) {
-        float acc[SCL_SB] = {0.f, 0.f, 0.f, 0.f};
-        scl_dot4(xh, sm + p.w[l] + tid, ng * UPC, K, acc);
-        *reinterpret_cast<float4 *>(pre + tid * SCL_SB) = make_float4(acc[0], acc[1], acc[2], acc[3]);
-      }
-      __syncthreads();
-      const float hold_h = cth ? xh[(size_t)(I + u0 + cu) * SCL_SB + cs] : 0.f;
       if (cell == 0) {
         if (cth) {
-          const float *pp = pre + (size_t)(4 * cu) * SCL_SB + cs;
-          const float a0 = pp[0], a1 = pp[SCL_SB], a2 = pp[2 * SCL_SB], a3 = pp[3 * SCL_SB];
+          const float *As = xh + cs * Kp;
+          float acc[4] = {0.f, 0.f, 0.f, 0.f};
+          scl_dot<4>(As, sm + p.w[l] + 4 * cu, 4 * UPC, K, acc);
+          const float a0 = acc[0], a1 = acc[1], a2 = acc[2], a3 = acc[3];
           const float4 bb = reinterpret_cast<const float4 *>(sm + p.b[l])[cu];
           const float c = cst[l * UPC * SCL_SB];
           const float ig = skm_sigmoid(SKM_ADD(a0, bb.x));
@@ -313,64 +305,68 @@ sample_cluster_kernel(const __grid_constant__ SclArgs a, const __grid_constant__
           const float og = skm_sigmoid(SKM_ADD(a3, bb.w));
           const float c2 = SKM_FMA(c, fg, SKM_MUL(ig, jg));
           hnew = SKM_MUL(skm_tanh(c2), og);
-          hkeep = hold ? hold_h : hnew;
+          hkeep = hold ? As[I + u0 + cu] : hnew;
           if (!hold) cst[l * UPC * SCL_SB] = c2;
         }
       } else if (cell == 2) {
         if (cth) {
-          hnew = skm_tanh(SKM_ADD(pre[(size_t)cu * SCL_SB + cs], sm[p.b[l] + cu]));
-          hkeep = hold ? hold_h : hnew;
+          const float *As = xh + cs * Kp;
+          float acc[1] = {0.f};
+          scl_dot<1>(As, sm + p.w[l] + cu, UPC, K, acc);
+          hnew = skm_tanh(SKM_ADD(acc[0], sm[p.b[l] + cu]));
+          hkeep = hold ? As[I + u0 + cu] : hnew;
         }
       } else {
-        float az = 0.f;
+        float az = 0.f, hold_h = 0.f;
         float *rh = sm + p.rh;
         if (cth) {  // gates r, u on [x ; h]
-          const float *pp = pre + (size_t)(2 * cu) * SCL_SB + cs;
+          const float *As = xh + cs * Kp;
+          float acc[2] = {0.f, 0.f};
+          scl_dot<2>(As, sm + p.w[l] + 2 * cu, 2 * UPC, K, acc);
+          float ar = acc[0];
+          az = acc[1];
           const float2 bb = reinterpret_cast<const float2 *>(sm + p.b[l])[cu];
-          const float ar = SKM_MUL(skm_sigmoid(SKM_ADD(pp[0], bb.x)), hold_h);  // r * h
-          az = skm_sigmoid(SKM_ADD(pp[SCL_SB], bb.y));
-          scl_send(rh + (size_t)(u0 + cu) * SCL_SB + cs, ar, bar_R(l));
+          hold_h = As[I + u0 + cu];
+          ar = SKM_MUL(skm_sigmoid(SKM_ADD(ar, bb.x)), hold_h);  // r * h
+          az = skm_sigmoid(SKM_ADD(az, bb.y));
+          scl_send(rh + cs * H + u0 + cu, ar, bar_R(l));
         }
         scl_wait(bar_R(l), par);
-        __syncthreads();  // (also: every cell thread has read its gate sums before `pre` is reused)
-        if (tid < UPC) {  // candidate on [x ; r*h]: one chain over the I input columns, then the H columns of r*h
-          float acc[SCL_SB] = {0.f, 0.f, 0.f, 0.f};
-          scl_dot4(xh, sm + p.wc[l] + tid, UPC, I, acc);
-          scl_dot4(rh, sm + p.wc[l] + (size_t)I * UPC + tid, UPC, H, acc);
-          *reinterpret_cast<float4 *>(pre + tid * SCL_SB) = make_float4(acc[0], acc[1], acc[2], acc[3]);
-        }
-        __syncthreads();
-        if (cth) {
-          const float cand = skm_tanh(SKM_ADD(pre[(size_t)cu * SCL_SB + cs], sm[p.bc[l] + cu]));
+        if (cth) {  // candidate on [x ; r*h]
+          const float *Wc = sm + p.wc[l] + cu;
+          const float *Ax = xh + cs * Kp;
+          const float *Ar = rh + cs * H;
+          float acc[1] = {0.f};
+          if (l == 0) {  // 5 input columns, then r*h (the continuation of the same chain)
+            for (int k = 0; k < I; ++k) acc[0] = SKM_FMA(Ax[k], Wc[(size_t)k * UPC], acc[0]);
+          } else {
+            scl_dot<1>(Ax, Wc, UPC, I, acc);
+          }
+          scl_dot<1>(Ar, Wc + (size_t)I * UPC, UPC, H, acc);
+          const float cand = skm_tanh(SKM_ADD(acc[0], sm[p.bc[l] + cu]));
           hnew = SKM_FMA(az, hold_h, SKM_MUL(SKM_SUB(1.0f, az), cand));
           hkeep = hold ? hold_h : hnew;
         }
       }
       // the layer's output: input of the next layer (nobody reads that buffer now), or of the output projection
       if (cth) {
-        if (l + 1 < L) scl_send(sm + p.xh[l + 1] + (size_t)(u0 + cu) * SCL_SB + cs, hnew, bar_A(l));
-        else scl_send(sm + p.hlast + (size_t)(u0 + cu) * SCL_SB + cs, hnew, bar_A(l));
+        if (l + 1 < L) scl_send(sm + p.xh[l + 1] + cs * scl_kp(2 * H) + u0 + cu, hnew, bar_A(l));
+        else scl_send(sm + p.hlast + cs * H + u0 + cu, hnew, bar_A(l));
       }
       SCL_LAP(1);
       scl_wait(bar_A(l), par);  // every rank's output is here, so every rank is done reading this layer's [x ; h]
       SCL_LAP(2);
-      if (cth) scl_send(xh + (size_t)(I + u0 + cu) * SCL_SB + cs, hkeep, bar_H(l));  // waited for at the top of the next step
+      if (cth) scl_send(xh + cs * Kp + I + u0 + cu, hkeep, bar_H(l));  // waited for at the top of the next step
       SCL_LAP(3);
-      __syncthreads();  // `pre` is free again
     }
     // ---- output projection (model.py:98-99): my OC columns for the SB sketches ----
-    {
-      float *pre = sm + p.pre;
-      if (tid < OC) {
-        float acc[SCL_SB] = {0.f, 0.f, 0.f, 0.f};
-        scl_dot4(sm + p.hlast, sm + p.wo + tid, OC, H, acc);
-        *reinterpret_cast<float4 *>(pre + tid * SCL_SB) = make_float4(acc[0], acc[1], acc[2], acc[3]);
-      }
-      __syncthreads();
-      if (tid < OC * SCL_SB) {
-        const int j = tid / SCL_SB, sk = tid % SCL_SB;
-        if (rank * OC + j < NOUT) scl_send(lg + sk * NOUTP + rank * OC + j, SKM_ADD(pre[tid], sm[p.bo + j]), bar_LG);
-      }
+    if (tid < OC * SCL_SB) {
+      const int j = tid % OC, s = tid / OC;
+      const float *Wo = sm + p.wo + j;
+      const float *hl = sm + p.hlast + s * H;
+      float acc[1] = {0.f};
+      scl_dot<1>(hl, Wo, OC, H, acc);
+      if (rank * OC + j < NOUT) scl_send(lg + s * NOUTP + rank * OC + j, SKM_ADD(acc[0], sm[p.bo + j]), bar_LG);
     }
     SCL_LAP(4);
     scl_wait(bar_LG, par);
@@ -463,8 +459,8 @@ sample_cluster_kernel(const __grid_constant__ SclArgs a, const __grid_constant__
         }
         // feedback (model.py:259-261): next step's input, also as the x part of layer 0's operand
         xin[r * 8 + 0] = x1; xin[r * 8 + 1] = x2; xin[r * 8 + 2] = eos; xin[r * 8 + 3] = eoc; xin[r * 8 + 4] = cont;
-        float *x0 = sm + p.xh[0] + r;  // [k][SB]
-        x0[0] = x1; x0[SCL_SB] = x2; x0[2 * SCL_SB] = eos; x0[3 * SCL_SB] = eoc; x0[4 * SCL_SB] = cont;
+        float *x0 = sm + p.xh[0] + r * scl_kp(5 + H);
+        x0[0] = x1; x0[1] = x2; x0[2] = eos; x0[3] = eoc; x0[4] = cont;
         flags[SCL_SB + r] = step + 1;
         if (a.stop_if_eoc && eoc > 0.f) flags[r] = 1;  // model.py:255-257
       }
