@@ -83,6 +83,8 @@ struct TcRnnArgs {
   const uint8_t *wimg;    // per-rank shared-memory images of the weight operand
   int wimg_bytes;
   int mcast;              // forward: the h tile arrives by TMA multicast (each rank fetches 1/CS of it)
+  int push;               // forward, two-half-tile kernel, small tiles: every rank sends its units of h_t straight into every
+                          // rank's operand tile (st.async + transaction bytes) instead of store -> signal -> multicast load
   int a_tmem;             // forward: weights live in tensor memory (wimg is plain row-major [128][nkb*64] bf16)
   int debug;              // SKRNN_TC_DEBUG=1: one CTA prints its per-phase cycle split
   // time range of this launch (two-half-tile kernels): steps [t0, t1) of the T-step unroll, t0 even.  A layer may be
@@ -452,6 +454,17 @@ __device__ __forceinline__ void mbar_wait_cluster(uint32_t bar, uint32_t parity)
         "}\n" : "=r"(done) : "r"(bar), "r"(parity) : "memory");
   }
 }
+// 16 bytes into the shared memory of a CTA of the cluster (cluster addresses); the store adds its bytes to the
+// transaction count of the mbarrier at `bar` in the same CTA
+__device__ __forceinline__ void st_async_v4(uint32_t dst, uint4 v, uint32_t bar) {
+  asm volatile("st.async.shared::cluster.mbarrier::complete_tx::bytes.v4.b32 [%0], {%1, %2, %3, %4}, [%5];"
+               ::"r"(dst), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w), "r"(bar) : "memory");
+}
+__device__ __forceinline__ uint32_t mapa_u32(uint32_t addr, uint32_t rank) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(addr), "r"(rank));
+  return r;
+}
 __device__ __forceinline__ void mbar_arrive_remote(uint32_t bar, uint32_t rank) {
   asm volatile(
       "{\n"
@@ -473,8 +486,9 @@ lstm_fwd_pp_kernel(const __grid_constant__ CUtensorMap tm_h, const __grid_consta
   const int H = a.H, B = a.B, T = a.T, nkb = a.nkb, CS = a.CS;
   const int t0 = a.t0, t1 = a.t1;  // this launch runs steps [t0, t1); t0 is even, so barrier parities follow t
   const uint32_t h_bytes = (uint32_t)nkb * (N2 * 128), xw_bytes = (uint32_t)N2 * 256u, hst_bytes = (uint32_t)N2 * 64u;
-  const uint32_t s_h = base;                       // [2] x nkb x [N2 rows][128 B]
-  const uint32_t s_xw = s_h + 2 * h_bytes;         // [2] x [N2][32 units][4 gates] bf16: hoisted x*Wx+b
+  const bool push = a.push != 0;
+  const uint32_t s_h = base;                       // [2] x nkb x [N2 rows][128 B]; push mode: two such sets, used in turn by step parity
+  const uint32_t s_xw = s_h + (push ? 4 : 2) * h_bytes;  // [2] x [N2][32 units][4 gates] bf16: hoisted x*Wx+b
   const uint32_t s_hst = s_xw + 2 * xw_bytes;      // [2] x [N2][32 units] bf16: my units of h_t on their way out (TMA store)
   const uint32_t s_bar = s_hst + 2 * hst_bytes;
   // mbarriers, index s = half tile
@@ -581,15 +595,18 @@ lstm_fwd_pp_kernel(const __grid_constant__ CUtensorMap tm_h, const __grid_consta
       load_xw(0, t0);
       load_xw(1, t0);
       for (int t = t0; t < t1; ++t) {
-        if (t > t0) mbar_wait_cluster(bar_ready + 0, (t - 1) & 1);
+        // push mode: after the first step the tile is SENT by the ranks' publishers; this thread only states how many
+        // bytes the step's barrier phase expects (the previous phase is over: retire() of that half has been passed)
+        const bool pushed = push && t > t0;
+        if (t > t0 && !push) mbar_wait_cluster(bar_ready + 0, (t - 1) & 1);
         TCR_LAP(tk[8]);
-        load_h(0, t);
+        if (pushed) mbar_expect_tx(bar_h + 0, h_bytes); else load_h(0, t);
         TCR_LAP(tk[9]);
         if (t > t0) retire(1, t - 1);
         TCR_LAP(tk[10]);
-        if (t > t0) mbar_wait_cluster(bar_ready + 8, (t - 1) & 1);
+        if (t > t0 && !push) mbar_wait_cluster(bar_ready + 8, (t - 1) & 1);
         TCR_LAP(tk[11]);
-        load_h(1, t);
+        if (pushed) mbar_expect_tx(bar_h + 8, h_bytes); else load_h(1, t);
         TCR_LAP(tk[12]);
         retire(0, t);
         TCR_LAP(tk[13]);
@@ -610,16 +627,22 @@ lstm_fwd_pp_kernel(const __grid_constant__ CUtensorMap tm_h, const __grid_consta
       for (int t = t0; t < t1; ++t) {
 #pragma unroll
         for (int s = 0; s < 2; ++s) {
-          mbar_wait(bar_h + 8 * s, t & 1);
+          if (push) {
+            mbar_wait_cluster(bar_h + 8 * s, t & 1);
+            fence_proxy_async_smem();  // the tile was written by st.async stores: order them before the tensor core's reads
+          } else {
+            mbar_wait(bar_h + 8 * s, t & 1);
+          }
           TCR_LAP(tk[16 + 2 * s]);
           tc_fence_after();
+          const uint32_t hset = push ? (uint32_t)(t & 1) * 2u * h_bytes : 0u;
 #pragma unroll
           for (int kb = 0; kb < 8; ++kb) {
             if (kb < nkb) {
 #pragma unroll
               for (int k = 0; k < 4; ++k)
                 tc_mma_bf16_ts(tmem_acc + (uint32_t)(s * N2), tmem_a + (uint32_t)(kb * 32 + k * 8),
-                               dB0 + (uint64_t)((s * h_bytes) >> 4) + (uint64_t)(kb * (N2 * 8) + 2 * k), idesc,
+                               dB0 + (uint64_t)((hset + s * h_bytes) >> 4) + (uint64_t)(kb * (N2 * 8) + 2 * k), idesc,
                                (kb > 0 || k > 0) ? 1u : 0u);
             }
           }
@@ -646,6 +669,46 @@ lstm_fwd_pp_kernel(const __grid_constant__ CUtensorMap tm_h, const __grid_consta
         for (int s = 0; s < 2; ++s) {
           mbar_wait(bar_epi + 8 * s, t & 1);  // the staging tile of (s, t) is complete (writers fenced it for the async proxy)
           TCR_LAP(tk[20]);
+          if (push) {
+            // Small tiles: the round trip store -> completion -> remote arrivals -> multicast load is most of a step.
+            // Instead every rank's publisher sends its [N2 rows][32 units] of h_{t+1} straight into all ranks' operand
+            // tiles of step t+1 (the set not being read now), 16 bytes per st.async, at the swizzled position the UMMA
+            // K-major layout gives them; each store adds its bytes to the receiver's bar_h phase.  The record of h in
+            // global memory (hprev, read by the weight-gradient GEMM) still leaves by TMA, off the critical path.
+            if (elect_one()) tma_store_3d(&tm_hst, s_hst + s * hst_bytes, u0, b0 + s * N2, t + 1);
+            __syncwarp();
+            if (t + 1 < t1) {
+              const uint32_t dst0 = s_h + (uint32_t)((t + 1) & 1) * 2u * h_bytes + s * h_bytes + (uint32_t)(rank >> 1) * (N2 * 128);
+              const uint8_t *stg = gbase + (s_hst + s * hst_bytes - base);
+              uint4 v[(N2 * 4 + 31) / 32];
+              uint32_t off[(N2 * 4 + 31) / 32];
+#pragma unroll
+              for (int i = 0; i < (N2 * 4 + 31) / 32; ++i) {
+                const int c = lane + 32 * i;  // chunk c: row c / 4, 16-byte piece c % 4 of the rank's 64 bytes of that row
+                const int n = c >> 2, j = c & 3;
+                v[i] = *reinterpret_cast<const uint4 *>(stg + n * 64 + j * 16);
+                off[i] = (uint32_t)(n * 128) + ((uint32_t)((4 * (rank & 1) + j) ^ (n & 7)) << 4);
+              }
+              for (int rr = 1; rr <= CS; ++rr) {
+                // my own tile last, and only once the TMA store above has read the staging tile: my next product (and with
+                // it the next elementwise pass, which rewrites the staging tile) cannot start before that
+                const uint32_t r = (uint32_t)((rank + rr) % CS);
+                if (rr == CS) {
+                  if (elect_one()) tma_store_wait_read();
+                  __syncwarp();
+                }
+                const uint32_t rd = mapa_u32(dst0, r), rb = mapa_u32(bar_h + 8 * s, r);
+#pragma unroll
+                for (int i = 0; i < (N2 * 4 + 31) / 32; ++i)
+                  if (lane + 32 * i < N2 * 4) st_async_v4(rd + off[i], v[i], rb);
+              }
+            } else {
+              if (elect_one()) tma_store_wait_read();
+              __syncwarp();
+            }
+            TCR_LAP(tk[21]);
+            continue;
+          }
           if (elect_one()) {
             tma_store_3d(&tm_hst, s_hst + s * hst_bytes, u0, b0 + s * N2, t + 1);
             tma_store_wait_all();             // h_t[my units] is in global memory before anybody is told
@@ -657,6 +720,7 @@ lstm_fwd_pp_kernel(const __grid_constant__ CUtensorMap tm_h, const __grid_consta
           TCR_LAP(tk[22]);
         }
       }
+      if (push && elect_one()) tma_store_wait_all();
       if (dbg)
         printf("[tc fwd pp] publisher cycles/half step: wait elementwise %lld, h store %lld, remote arrives %lld\n", tk[20] / (2 * T),
                tk[21] / (2 * T), tk[22] / (2 * T));
@@ -1544,10 +1608,10 @@ int launch_bwd(const CUtensorMap &tm_acts, const CUtensorMap &tm_do, const CUten
   return 0;
 }
 
-size_t smem_need(bool bwd, int H, int N, bool a_tmem) {
+size_t smem_need(bool bwd, int H, int N, bool a_tmem, bool push = false) {
   const int nkb = (H + 63) / 64, HP = (H + 127) / 128 * 128;
   size_t s = bwd ? (size_t)2 * HP * 128 + 2 * (size_t)N * 128 + 4 * (size_t)N * 128
-                 : (a_tmem ? 0 : (size_t)nkb * 16384) + (size_t)nkb * N * 128 + 2 * (size_t)N * 128 + 2 * (size_t)N * 128;
+                 : (a_tmem ? 0 : (size_t)nkb * 16384) + (size_t)(push ? 2 : 1) * nkb * N * 128 + 2 * (size_t)N * 128 + 2 * (size_t)N * 128;
   return s + 1024 + 256;
 }
 
@@ -1711,10 +1775,16 @@ int sk_rnn_tc_layer(skrnn_handle *h, cudaStream_t st, bool bwd, int l, int B, in
       uint32_t sbox[3] = {32, (uint32_t)(N / 2), 1};
       CUtensorMap tm_hst;
       SK_TRY(sk_make_tmap(&tm_hst, 2, h->ws.hprev_bf[l], 3, dims, str, sbox, false));
+      // small tiles: h travels rank to rank through distributed shared memory (see the publisher warp); SKRNN_TC_PUSH=<max N>
+      // moves the limit (0: never)
+      static int push_max = -1;
+      if (push_max < 0) { const char *e = getenv("SKRNN_TC_PUSH"); push_max = e ? atoi(e) : 32; }
+      a.push = (N <= push_max) ? 1 : 0;
+      const size_t smem_pp = smem_need(false, H, N, a_tmem, a.push != 0);
       SkLaunch scope(h, st, SK_CAT_RNN_FWD);
-      if (N == 32) rc = launch_fwd_pp<1>(tm_h, tm_xw, tm_hst, a, nclusters, smem, st);
-      else if (N == 64) rc = launch_fwd_pp<2>(tm_h, tm_xw, tm_hst, a, nclusters, smem, st);
-      else rc = launch_fwd_pp<4>(tm_h, tm_xw, tm_hst, a, nclusters, smem, st);
+      if (N == 32) rc = launch_fwd_pp<1>(tm_h, tm_xw, tm_hst, a, nclusters, smem_pp, st);
+      else if (N == 64) rc = launch_fwd_pp<2>(tm_h, tm_xw, tm_hst, a, nclusters, smem_pp, st);
+      else rc = launch_fwd_pp<4>(tm_h, tm_xw, tm_hst, a, nclusters, smem_pp, st);
       if (rc != 0) {
         fprintf(stderr, "libskrnn: lstm_fwd_pp_kernel launch failed (%s)\n", skrnn_last_error());
         cudaGetLastError();
