@@ -489,8 +489,8 @@ lstm_fwd_pp_kernel(const __grid_constant__ CUtensorMap tm_h, const __grid_consta
   const bool push = a.push != 0;
   const uint32_t s_h = base;                       // [2] x nkb x [N2 rows][128 B]; push mode: two such sets, used in turn by step parity
   const uint32_t s_xw = s_h + (push ? 4 : 2) * h_bytes;  // [2] x [N2][32 units][4 gates] bf16: hoisted x*Wx+b
-  const uint32_t s_hst = s_xw + 2 * xw_bytes;      // [2] x [N2][32 units] bf16: my units of h_t on their way out (TMA store)
-  const uint32_t s_bar = s_hst + 2 * hst_bytes;
+  const uint32_t s_hst = s_xw + 2 * xw_bytes;      // [2] x [N2][32 units] bf16: my units of h_t on their way out (TMA store); push mode: two sets by step parity
+  const uint32_t s_bar = s_hst + (push ? 4 : 2) * hst_bytes;
   // mbarriers, index s = half tile
   const uint32_t bar_h = s_bar, bar_xw = s_bar + 16, bar_acc = s_bar + 32, bar_epi = s_bar + 48, bar_ready = s_bar + 64;
   const uint32_t tmem_holder = s_bar + 80;
@@ -675,11 +675,10 @@ lstm_fwd_pp_kernel(const __grid_constant__ CUtensorMap tm_h, const __grid_consta
             // tiles of step t+1 (the set not being read now), 16 bytes per st.async, at the swizzled position the UMMA
             // K-major layout gives them; each store adds its bytes to the receiver's bar_h phase.  The record of h in
             // global memory (hprev, read by the weight-gradient GEMM) still leaves by TMA, off the critical path.
-            if (elect_one()) tma_store_3d(&tm_hst, s_hst + s * hst_bytes, u0, b0 + s * N2, t + 1);
-            __syncwarp();
+            const uint32_t stg_s = s_hst + ((uint32_t)(t & 1) * 2u + s) * hst_bytes;  // staging tiles alternate by step parity
             if (t + 1 < t1) {
               const uint32_t dst0 = s_h + (uint32_t)((t + 1) & 1) * 2u * h_bytes + s * h_bytes + (uint32_t)(rank >> 1) * (N2 * 128);
-              const uint8_t *stg = gbase + (s_hst + s * hst_bytes - base);
+              const uint8_t *stg = gbase + (stg_s - base);
               uint4 v[(N2 * 4 + 31) / 32];
               uint32_t off[(N2 * 4 + 31) / 32];
 #pragma unroll
@@ -689,24 +688,23 @@ lstm_fwd_pp_kernel(const __grid_constant__ CUtensorMap tm_h, const __grid_consta
                 v[i] = *reinterpret_cast<const uint4 *>(stg + n * 64 + j * 16);
                 off[i] = (uint32_t)(n * 128) + ((uint32_t)((4 * (rank & 1) + j) ^ (n & 7)) << 4);
               }
-              for (int rr = 1; rr <= CS; ++rr) {
-                // my own tile last, and only once the TMA store above has read the staging tile: my next product (and with
-                // it the next elementwise pass, which rewrites the staging tile) cannot start before that
+              for (int rr = 0; rr < CS; ++rr) {
                 const uint32_t r = (uint32_t)((rank + rr) % CS);
-                if (rr == CS) {
-                  if (elect_one()) tma_store_wait_read();
-                  __syncwarp();
-                }
                 const uint32_t rd = mapa_u32(dst0, r), rb = mapa_u32(bar_h + 8 * s, r);
 #pragma unroll
                 for (int i = 0; i < (N2 * 4 + 31) / 32; ++i)
                   if (lane + 32 * i < N2 * 4) st_async_v4(rd + off[i], v[i], rb);
               }
-            } else {
-              if (elect_one()) tma_store_wait_read();
-              __syncwarp();
             }
             TCR_LAP(tk[21]);
+            // the record in global memory, after the sends.  This staging tile is rewritten two steps from now, and the
+            // wait below (one step from now, same half) comes before that
+            if (elect_one()) {
+              tma_store_wait_read();
+              tma_store_3d(&tm_hst, stg_s, u0, b0 + s * N2, t + 1);
+            }
+            __syncwarp();
+            TCR_LAP(tk[22]);
             continue;
           }
           if (elect_one()) {
@@ -756,6 +754,7 @@ lstm_fwd_pp_kernel(const __grid_constant__ CUtensorMap tm_h, const __grid_consta
     if (dbg) lapt = (uint32_t)clock();
     for (int t = t0; t < t1; ++t) {
       const bool more = t + 1 < T;
+      const uint32_t hst_par = push ? (uint32_t)(t & 1) * 2u * hst_bytes : 0u;
 #pragma unroll
       for (int s = 0; s < 2; ++s) {
         const uint32_t eoc_bits = eoc_next;
@@ -829,7 +828,7 @@ lstm_fwd_pp_kernel(const __grid_constant__ CUtensorMap tm_h, const __grid_consta
             }
             cst[s][it] = cn;
             const size_t off = s * half_off + (size_t)it * H4;
-            *reinterpret_cast<__nv_bfloat16 *>(hst_p + s * hst_bytes + it * 256) = __float2bfloat16_rn(hn);
+            *reinterpret_cast<__nv_bfloat16 *>(hst_p + hst_par + s * hst_bytes + it * 256) = __float2bfloat16_rn(hn);
             o_p[off] = __float2bfloat16_rn(h2 * dsc[it]);
             if (more) {
               c_p[off] = cn;
