@@ -460,6 +460,13 @@ __device__ __forceinline__ void st_async_v4(uint32_t dst, uint4 v, uint32_t bar)
   asm volatile("st.async.shared::cluster.mbarrier::complete_tx::bytes.v4.b32 [%0], {%1, %2, %3, %4}, [%5];"
                ::"r"(dst), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w), "r"(bar) : "memory");
 }
+__device__ __forceinline__ void st_async_v2(uint32_t dst, uint2 v, uint32_t bar) {
+  asm volatile("st.async.shared::cluster.mbarrier::complete_tx::bytes.v2.b32 [%0], {%1, %2}, [%3];"
+               ::"r"(dst), "r"(v.x), "r"(v.y), "r"(bar) : "memory");
+}
+// a partial-sum element group: from L2 (exchange through global memory) or from this CTA's receive buffer (push mode)
+template <typename V>
+__device__ __forceinline__ V ld_part(const V *p, bool local) { return local ? *p : __ldcg(p); }
 __device__ __forceinline__ uint32_t mapa_u32(uint32_t addr, uint32_t rank) {
   uint32_t r;
   asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(addr), "r"(rank));
@@ -887,6 +894,11 @@ lstm_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm_acts, const __grid_con
   const uint32_t s_bar = s_cp + (uint32_t)N * 128u;
   const uint32_t bar_acts = s_bar, bar_ready = s_bar + 8, tmem_holder = s_bar + 24;
   const uint32_t bar_acc = s_bar + 32;  // [4]: one per accumulator m-tile, so the read-out starts while later tiles multiply
+  // push mode (small tiles): the partial sums go straight into the destination rank's receive buffer (st.async, bytes
+  // counted on its bar_rx) instead of through L2 with a barrier.cluster per step
+  const bool push = a.push != 0;
+  const uint32_t bar_rx = s_bar + 64;
+  const uint32_t s_rx = s_bar + 256;    // [parity][src rank][column group][32 units x CPW columns] bf16
   volatile uint32_t *tmem_holder_ptr = reinterpret_cast<volatile uint32_t *>(gbase + (tmem_holder - base));
   const uint8_t *ac_gen = gbase + (s_ac - base);
   const uint8_t *do_gen = gbase + (s_do - base);
@@ -907,6 +919,7 @@ lstm_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm_acts, const __grid_con
   }
   if (tid == 0) {
     mbar_init(bar_acts, 1);
+    mbar_init(bar_rx, 1);
     mbar_init(bar_ready, 32 * TCR_EPI_WARPS);
     for (int mt = 0; mt < 4; ++mt) mbar_init(bar_acc + 8 * mt, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -938,6 +951,9 @@ lstm_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm_acts, const __grid_con
   constexpr int CK = CPW >= 8 ? 8 : CPW;
   constexpr int NJ = CPW / CK;
   const size_t part_blk = (size_t)NJ * 32 * CK;  // one (dst, src, cg) block = 32 units x CPW columns
+  const uint32_t rx_bytes = (uint32_t)(CS * 4 * part_blk * 2);  // what a rank receives per step
+  const __nv_bfloat16 *rx_gen = reinterpret_cast<const __nv_bfloat16 *>(gbase + (s_rx - base));
+  if (push && tid == 0 && T > 1) mbar_expect_tx(bar_rx, rx_bytes);  // step 0's exchange (later ones are armed after each wait)
 
   __shared__ long long tk[8];  // debug cycle counters (shared memory, not registers)
   if (tid < 8) tk[tid] = 0;
@@ -1057,6 +1073,8 @@ lstm_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm_acts, const __grid_con
           if (m < H) {
             // rows 32q..32q+31 of this m-tile are the units of destination rank 4*mt + q; lane = unit
             __nv_bfloat16 *dst = part_base + (((size_t)(par * CS + (m >> 5)) * CS + rank) * 4 + cg) * part_blk + lane * CK;
+            const uint32_t rdst = push ? mapa_u32(s_rx + (uint32_t)(((((size_t)par * CS + rank) * 4 + cg) * part_blk + lane * CK) * 2), (uint32_t)(m >> 5)) : 0u;
+            const uint32_t rbar = push ? mapa_u32(bar_rx, (uint32_t)(m >> 5)) : 0u;
             uint32_t pk[CPW / 2];
 #pragma unroll
             for (int j = 0; j < CPW / 2; ++j) {
@@ -1067,10 +1085,14 @@ lstm_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm_acts, const __grid_con
             }
             if constexpr (CPW >= 8) {
 #pragma unroll
-              for (int j = 0; j < NJ; ++j)
-                *reinterpret_cast<uint4 *>(dst + j * 32 * CK) = make_uint4(pk[4 * j], pk[4 * j + 1], pk[4 * j + 2], pk[4 * j + 3]);
+              for (int j = 0; j < NJ; ++j) {
+                const uint4 v4 = make_uint4(pk[4 * j], pk[4 * j + 1], pk[4 * j + 2], pk[4 * j + 3]);
+                if (push) st_async_v4(rdst + (uint32_t)(j * 32 * CK * 2), v4, rbar);
+                else *reinterpret_cast<uint4 *>(dst + j * 32 * CK) = v4;
+              }
             } else {
-              *reinterpret_cast<uint2 *>(dst) = make_uint2(pk[0], pk[1]);
+              if (push) st_async_v2(rdst, make_uint2(pk[0], pk[1]), rbar);
+              else *reinterpret_cast<uint2 *>(dst) = make_uint2(pk[0], pk[1]);
             }
           }
         }
@@ -1079,7 +1101,17 @@ lstm_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm_acts, const __grid_con
     TCR_LAP(tk[3]);
     __syncwarp();
     tc_fence_before();
-    cluster_sync_all();
+    if (push) {
+      __syncthreads();  // (the d(pre) store has read the operand tile, every accumulator has been read out)
+      if (t > 0 && warp >= 2) {
+        mbar_wait_cluster(bar_rx, step & 1);  // every rank's partials for my units have landed
+        // the phase is over, so the next one can be announced; the buffers alternate by step parity, and a rank
+        // sends step t-1's partials only after it has consumed step t's, which needs mine: no overwrite before the read
+        if (tid == 64 && t > 1) mbar_expect_tx(bar_rx, rx_bytes);
+      }
+    } else {
+      cluster_sync_all();
+    }
     tc_fence_after();
     TCR_LAP(tk[4]);
     if (t > 0 && warp >= 2) {
@@ -1087,7 +1119,8 @@ lstm_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm_acts, const __grid_con
 #pragma unroll
       for (int it = 0; it < NCH; ++it) dhc[it] = 0.f;
       // my NCH items sit at positions esub*NCH .. +NCH of the block row: chunk (esub*NCH)/CK, offset (esub*NCH)%CK
-      const __nv_bfloat16 *src0 = part_base + (((size_t)(par * CS + rank) * CS) * 4 + cg) * part_blk +
+      const __nv_bfloat16 *src0 = (push ? rx_gen + (((size_t)par * CS) * 4 + cg) * part_blk
+                                        : part_base + (((size_t)(par * CS + rank) * CS) * 4 + cg) * part_blk) +
                                   ((size_t)((esub * NCH) / CK) * 32 + eu) * CK + (esub * NCH) % CK;
       constexpr int UR = 8;  // loads in flight (L2 latency bound otherwise); the sum stays in rank order
       for (int r0 = 0; r0 < CS; r0 += UR) {
@@ -1095,7 +1128,7 @@ lstm_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm_acts, const __grid_con
           uint4 v[UR];
 #pragma unroll
           for (int j = 0; j < UR; ++j)
-            v[j] = (r0 + j < CS) ? __ldcg(reinterpret_cast<const uint4 *>(src0 + (size_t)(r0 + j) * 4 * part_blk)) : make_uint4(0, 0, 0, 0);
+            v[j] = (r0 + j < CS) ? ld_part(reinterpret_cast<const uint4 *>(src0 + (size_t)(r0 + j) * 4 * part_blk), push) : make_uint4(0, 0, 0, 0);
 #pragma unroll
           for (int j = 0; j < UR; ++j) {
             const float2 f0 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162 *>(&v[j].x));
@@ -1109,7 +1142,7 @@ lstm_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm_acts, const __grid_con
           uint2 v[UR];
 #pragma unroll
           for (int j = 0; j < UR; ++j)
-            v[j] = (r0 + j < CS) ? __ldcg(reinterpret_cast<const uint2 *>(src0 + (size_t)(r0 + j) * 4 * part_blk)) : make_uint2(0, 0);
+            v[j] = (r0 + j < CS) ? ld_part(reinterpret_cast<const uint2 *>(src0 + (size_t)(r0 + j) * 4 * part_blk), push) : make_uint2(0, 0);
 #pragma unroll
           for (int j = 0; j < UR; ++j) {
             const float2 f0 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162 *>(&v[j].x));
@@ -1120,7 +1153,7 @@ lstm_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm_acts, const __grid_con
           uint32_t v[UR];
 #pragma unroll
           for (int j = 0; j < UR; ++j)
-            v[j] = (r0 + j < CS) ? __ldcg(reinterpret_cast<const uint32_t *>(src0 + (size_t)(r0 + j) * 4 * part_blk)) : 0u;
+            v[j] = (r0 + j < CS) ? ld_part(reinterpret_cast<const uint32_t *>(src0 + (size_t)(r0 + j) * 4 * part_blk), push) : 0u;
 #pragma unroll
           for (int j = 0; j < UR; ++j) {
             const float2 f0 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162 *>(&v[j]));
@@ -1130,7 +1163,7 @@ lstm_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm_acts, const __grid_con
           unsigned short v[UR];
 #pragma unroll
           for (int j = 0; j < UR; ++j)
-            v[j] = (r0 + j < CS) ? __ldcg(reinterpret_cast<const unsigned short *>(src0 + (size_t)(r0 + j) * 4 * part_blk)) : (unsigned short)0;
+            v[j] = (r0 + j < CS) ? ld_part(reinterpret_cast<const unsigned short *>(src0 + (size_t)(r0 + j) * 4 * part_blk), push) : (unsigned short)0;
 #pragma unroll
           for (int j = 0; j < UR; ++j) dhc[0] += __bfloat162float(__ushort_as_bfloat16(v[j]));
         }
@@ -1152,6 +1185,7 @@ lstm_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm_acts, const __grid_con
     printf("[tc bwd N=%d CS=%d] cycles/step: inputs+acts wait %lld, elementwise+stores %lld, MMA wait %lld, tmem ld + partial stores %lld, cluster barrier %lld, partial reads %lld\n",
            N, CS, tk[0] / T, tk[1] / T, tk[2] / T, tk[3] / T, tk[4] / T, tk[5] / T);
   __syncthreads();
+  if (push) cluster_sync_all();  // nobody leaves while a peer may still send into it
   if (warp == 1) tc_dealloc(tmem_acc, (uint32_t)a.tmem_cols);
 }
 
@@ -1609,7 +1643,7 @@ int launch_bwd(const CUtensorMap &tm_acts, const CUtensorMap &tm_do, const CUten
 
 size_t smem_need(bool bwd, int H, int N, bool a_tmem, bool push = false) {
   const int nkb = (H + 63) / 64, HP = (H + 127) / 128 * 128;
-  size_t s = bwd ? (size_t)2 * HP * 128 + 2 * (size_t)N * 128 + 4 * (size_t)N * 128
+  size_t s = bwd ? (size_t)2 * HP * 128 + 2 * (size_t)N * 128 + 4 * (size_t)N * 128 + (push ? (size_t)2 * (H / 32) * 32 * N * 2 : 0)
                  : (a_tmem ? 0 : (size_t)nkb * 16384) + (size_t)(push ? 2 : 1) * nkb * N * 128 + 2 * (size_t)N * 128 + 2 * (size_t)N * 128;
   return s + 1024 + 256;
 }
@@ -1844,11 +1878,16 @@ int sk_rnn_tc_layer(skrnn_handle *h, cudaStream_t st, bool bwd, int l, int B, in
       if (rc != 0) return 1;
       return 0;
     }
+    // small tiles: the partial sums travel rank to rank through distributed shared memory; SKRNN_TC_PUSH_BWD=<max N>
+    static int pushb_max = -1;
+    if (pushb_max < 0) { const char *e = getenv("SKRNN_TC_PUSH_BWD"); pushb_max = e ? atoi(e) : 16; }
+    a.push = (N <= pushb_max) ? 1 : 0;
+    const size_t smem_b = smem_need(true, H, N, false, a.push != 0);
     SkLaunch scope(h, st, SK_CAT_RNN_BWD);
-    if (N == 16) rc = launch_bwd<1>(tm_act, tm_do, tm_cp, tm_dp, a, nclusters, smem, st);
-    else if (N == 32) rc = launch_bwd<2>(tm_act, tm_do, tm_cp, tm_dp, a, nclusters, smem, st);
-    else if (N == 64) rc = launch_bwd<4>(tm_act, tm_do, tm_cp, tm_dp, a, nclusters, smem, st);
-    else rc = launch_bwd<8>(tm_act, tm_do, tm_cp, tm_dp, a, nclusters, smem, st);
+    if (N == 16) rc = launch_bwd<1>(tm_act, tm_do, tm_cp, tm_dp, a, nclusters, smem_b, st);
+    else if (N == 32) rc = launch_bwd<2>(tm_act, tm_do, tm_cp, tm_dp, a, nclusters, smem_b, st);
+    else if (N == 64) rc = launch_bwd<4>(tm_act, tm_do, tm_cp, tm_dp, a, nclusters, smem_b, st);
+    else rc = launch_bwd<8>(tm_act, tm_do, tm_cp, tm_dp, a, nclusters, smem_b, st);
     if (rc != 0) return 1;  // the forward's activations live in this family's format: no fallback possible
   }
   if (rc != 0) {
