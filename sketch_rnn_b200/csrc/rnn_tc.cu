@@ -466,7 +466,7 @@ __device__ __forceinline__ void st_async_v2(uint32_t dst, uint2 v, uint32_t bar)
 }
 // a partial-sum element group: from L2 (exchange through global memory) or from this CTA's receive buffer (push mode)
 template <typename V>
-__device__ __forceinline__ V ld_part(const V *p, bool local) { return local ? *p : __ldcg(p); }
+__device__ __forceinline__ V ld_part(const V *p, bool local) { return local ? *p : __ldcg(p); }  // `local` is a compile-time constant at the call sites
 __device__ __forceinline__ uint32_t mapa_u32(uint32_t addr, uint32_t rank) {
   uint32_t r;
   asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(addr), "r"(rank));
@@ -913,7 +913,8 @@ lstm_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm_acts, const __grid_con
   {
     const uint4 *src = reinterpret_cast<const uint4 *>(a.wimg + (size_t)rank * a.wimg_bytes);
     uint4 *dst = reinterpret_cast<uint4 *>(gbase + (s_w - base));
-    for (int i = tid; i < a.wimg_bytes / 16; i += TCR_THREADS) dst[i] = __ldg(src + i);
+    if (!a.a_tmem)
+      for (int i = tid; i < a.wimg_bytes / 16; i += TCR_THREADS) dst[i] = __ldg(src + i);
     uint4 *bz = reinterpret_cast<uint4 *>(b_gen);
     for (int i = tid; i < 2 * N * 128 / 16; i += TCR_THREADS) bz[i] = make_uint4(0, 0, 0, 0);
   }
@@ -930,6 +931,28 @@ lstm_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm_acts, const __grid_con
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_acc = *tmem_holder_ptr;
+  // small tiles leave room in tensor memory for the weight operand (64 columns per m-tile): an MMA then reads its A
+  // tile at the 9-cycle rate instead of 39 from shared memory
+  const uint32_t tmem_a = tmem_acc + (uint32_t)((nmt * N + 31) / 32 * 32);
+  if (a.a_tmem && warp >= 2 && warp < 6) {
+    const int qq = warp & 3, ee = 32 * qq + lane;
+    for (int mt = 0; mt < nmt; ++mt) {
+      const uint32_t *src = reinterpret_cast<const uint32_t *>(a.wimg + (size_t)rank * a.wimg_bytes) + ((size_t)mt * 128 + ee) * 64;
+#pragma unroll
+      for (int hb = 0; hb < 2; ++hb) {
+        uint32_t v[32];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const uint4 x = __ldg(reinterpret_cast<const uint4 *>(src + hb * 32) + j);
+          v[4 * j] = x.x; v[4 * j + 1] = x.y; v[4 * j + 2] = x.z; v[4 * j + 3] = x.w;
+        }
+        tc_st32(tmem_a + ((uint32_t)(32 * qq) << 16) + (uint32_t)(mt * 64 + hb * 32), v);
+      }
+    }
+    tc_fence_before();
+  }
+  __syncthreads();
+  tc_fence_after();
   cluster_sync_all();
 
   const int q = warp & 3, cg = (warp - 2) >> 2;
@@ -1054,9 +1077,14 @@ lstm_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm_acts, const __grid_con
             for (int kb = 0; kb < 2; ++kb) {
               const uint64_t da = make_desc(s_w + (uint32_t)kb * (HP * 128) + (uint32_t)mt * 16384u, 0, 1024);
 #pragma unroll
-              for (int k = 0; k < 4; ++k)
-                tc_mma_bf16(tmem_acc + (uint32_t)(mt * N), da + (uint64_t)(2 * k), dBk[kb] + (uint64_t)(2 * k), idesc,
-                            (kb > 0 || k > 0) ? 1u : 0u);
+              for (int k = 0; k < 4; ++k) {
+                if (a.a_tmem)
+                  tc_mma_bf16_ts(tmem_acc + (uint32_t)(mt * N), tmem_a + (uint32_t)(mt * 64 + kb * 32 + k * 8), dBk[kb] + (uint64_t)(2 * k),
+                                 idesc, (kb > 0 || k > 0) ? 1u : 0u);
+                else
+                  tc_mma_bf16(tmem_acc + (uint32_t)(mt * N), da + (uint64_t)(2 * k), dBk[kb] + (uint64_t)(2 * k), idesc,
+                              (kb > 0 || k > 0) ? 1u : 0u);
+              }
             }
             tc_commit(bar_acc + 8 * mt);
           }
@@ -1122,13 +1150,15 @@ lstm_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm_acts, const __grid_con
       const __nv_bfloat16 *src0 = (push ? rx_gen + (((size_t)par * CS) * 4 + cg) * part_blk
                                         : part_base + (((size_t)(par * CS + rank) * CS) * 4 + cg) * part_blk) +
                                   ((size_t)((esub * NCH) / CK) * 32 + eu) * CK + (esub * NCH) % CK;
+      auto sum_parts = [&](auto local_tag) {  // (compile-time flag: a run-time choice per load keeps them from being batched)
+      constexpr bool LOCAL = decltype(local_tag)::value;
       constexpr int UR = 8;  // loads in flight (L2 latency bound otherwise); the sum stays in rank order
       for (int r0 = 0; r0 < CS; r0 += UR) {
         if constexpr (NCH == 8) {
           uint4 v[UR];
 #pragma unroll
           for (int j = 0; j < UR; ++j)
-            v[j] = (r0 + j < CS) ? ld_part(reinterpret_cast<const uint4 *>(src0 + (size_t)(r0 + j) * 4 * part_blk), push) : make_uint4(0, 0, 0, 0);
+            v[j] = (r0 + j < CS) ? ld_part(reinterpret_cast<const uint4 *>(src0 + (size_t)(r0 + j) * 4 * part_blk), LOCAL) : make_uint4(0, 0, 0, 0);
 #pragma unroll
           for (int j = 0; j < UR; ++j) {
             const float2 f0 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162 *>(&v[j].x));
@@ -1142,7 +1172,7 @@ lstm_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm_acts, const __grid_con
           uint2 v[UR];
 #pragma unroll
           for (int j = 0; j < UR; ++j)
-            v[j] = (r0 + j < CS) ? ld_part(reinterpret_cast<const uint2 *>(src0 + (size_t)(r0 + j) * 4 * part_blk), push) : make_uint2(0, 0);
+            v[j] = (r0 + j < CS) ? ld_part(reinterpret_cast<const uint2 *>(src0 + (size_t)(r0 + j) * 4 * part_blk), LOCAL) : make_uint2(0, 0);
 #pragma unroll
           for (int j = 0; j < UR; ++j) {
             const float2 f0 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162 *>(&v[j].x));
@@ -1153,7 +1183,7 @@ lstm_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm_acts, const __grid_con
           uint32_t v[UR];
 #pragma unroll
           for (int j = 0; j < UR; ++j)
-            v[j] = (r0 + j < CS) ? ld_part(reinterpret_cast<const uint32_t *>(src0 + (size_t)(r0 + j) * 4 * part_blk), push) : 0u;
+            v[j] = (r0 + j < CS) ? ld_part(reinterpret_cast<const uint32_t *>(src0 + (size_t)(r0 + j) * 4 * part_blk), LOCAL) : 0u;
 #pragma unroll
           for (int j = 0; j < UR; ++j) {
             const float2 f0 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162 *>(&v[j]));
@@ -1163,11 +1193,13 @@ lstm_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm_acts, const __grid_con
           unsigned short v[UR];
 #pragma unroll
           for (int j = 0; j < UR; ++j)
-            v[j] = (r0 + j < CS) ? ld_part(reinterpret_cast<const unsigned short *>(src0 + (size_t)(r0 + j) * 4 * part_blk), push) : (unsigned short)0;
+            v[j] = (r0 + j < CS) ? ld_part(reinterpret_cast<const unsigned short *>(src0 + (size_t)(r0 + j) * 4 * part_blk), LOCAL) : (unsigned short)0;
 #pragma unroll
           for (int j = 0; j < UR; ++j) dhc[0] += __bfloat162float(__ushort_as_bfloat16(v[j]));
         }
       }
+      };
+      if (push) sum_parts(std::true_type{}); else sum_parts(std::false_type{});
     }
     TCR_LAP(tk[5]);
   }
@@ -1553,7 +1585,11 @@ __global__ void pack_tc_image_kernel(int bwd, const float *__restrict__ mat, int
     const int chunk = within >> 3, el = within & 7;
     const int kloc = ((chunk ^ (m & 7)) << 3) + el;  // un-swizzle: logical k within the block
     const int k = kb * 64 + kloc;
-    if (bwd == 2) {  // forward weights for tensor memory: plain row-major [128 rows m=4u+g][nkb*64]
+    if (bwd == 3) {  // backward weights for tensor memory: per m-tile plain row-major [128 rows m][128 kk], kk = 4u+g
+      const int mm = (int)(o / 128), kk2 = (int)(o % 128);
+      const int u = kk2 >> 2, g = kk2 & 3;
+      if (mm < H) v = mat[(size_t)(I + mm) * G + g * H + u0 + u];
+    } else if (bwd == 2) {  // forward weights for tensor memory: plain row-major [128 rows m=4u+g][nkb*64]
       const int mm = (int)(o / ((int64_t)nkb * 64)), kk2 = (int)(o % ((int64_t)nkb * 64));
       const int u = mm >> 2, g = mm & 3;
       if (kk2 < H) v = mat[(size_t)(I + kk2) * G + g * H + u0 + u];
@@ -1733,19 +1769,24 @@ int sk_rnn_tc_layer(skrnn_handle *h, cudaStream_t st, bool bwd, int l, int B, in
   const int nclusters = (B + N - 1) / N;
   const size_t smem = smem_need(bwd, H, N, a_tmem);
   const int img_bytes = bwd ? 2 * HP * 128 : nkb * 16384;
+  // single-tile BPTT kernel with a small tile: the weight operand fits in tensor memory next to the accumulators
+  static int batm_env = -1;
+  if (batm_env < 0) { const char *e = getenv("SKRNN_TC_ATMEM_BWD"); batm_env = (e && e[0] == '0') ? 0 : 1; }
+  const bool bwd_atmem = bwd && !plan.pp && batm_env && ((HP / 128) * N + 31) / 32 * 32 + (HP / 128) * 64 <= 512;
   SK_CHECK((int64_t)img_bytes * CS <= h->ws.wpack_floats * 4, "weight image workspace too small");
   {
     SkLaunch scope(h, st, SK_CAT_MISC);
     int64_t total = (int64_t)img_bytes / 2 * CS;
     int blocks = (int)std::min<int64_t>((total + 255) / 256, (int64_t)4 * h->num_sms);
-    pack_tc_image_kernel<<<blocks, 256, 0, st>>>(bwd ? 1 : (a_tmem ? 2 : 0), h->params + h->lp[l].w[0], h->lp[l].I, H, CS, nkb, HP,
+    pack_tc_image_kernel<<<blocks, 256, 0, st>>>(bwd ? (bwd_atmem ? 3 : 1) : (a_tmem ? 2 : 0), h->params + h->lp[l].w[0], h->lp[l].I, H, CS, nkb, HP,
                                                 img_bytes, reinterpret_cast<uint8_t *>(h->ws.wpack));
     SK_CUDA(cudaGetLastError());
   }
   TcRnnArgs a = {};
   a.B = B; a.T = T; a.H = H; a.G = h->G; a.N = N; a.CS = CS; a.nkb = nkb;
-  int cols = bwd ? (HP / 128) * N : (a_tmem ? (N + 31) / 32 * 32 + nkb * 32 : N);
-  a.a_tmem = a_tmem ? 1 : 0;
+  int cols = bwd ? (bwd_atmem ? ((HP / 128) * N + 31) / 32 * 32 + (HP / 128) * 64 : (HP / 128) * N)
+                 : (a_tmem ? (N + 31) / 32 * 32 + nkb * 32 : N);
+  a.a_tmem = (a_tmem || bwd_atmem) ? 1 : 0;
   int tc = 32;
   while (tc < cols) tc <<= 1;
   a.tmem_cols = tc;
