@@ -887,7 +887,7 @@ lstm_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm_acts, const __grid_con
   const int nmt = (H + 127) / 128;                 // accumulator m-tiles (all hidden units)
   const int HP = nmt * 128;
   const uint32_t s_w = base;                       // 2 k-blocks x [HP rows][128 B]
-  const uint32_t s_b = s_w + 2u * HP * 128u;       // 2 k-blocks x [N rows][128 B]: own d(pre) slice, bf16
+  const uint32_t s_b = s_w + (a.a_tmem ? 0u : 2u * HP * 128u);  // 2 k-blocks x [N rows][128 B]: own d(pre) slice, bf16
   const uint32_t s_ac = s_b + 2u * (N * 128);      // [N][32 units][4 gates] bf16: gate activations saved by the forward
   const uint32_t s_do = s_ac + (uint32_t)N * 256u; // [N][32] fp32, 128B-swizzled: d(out) of the step
   const uint32_t s_cp = s_do + (uint32_t)N * 128u; // [N][32] fp32, 128B-swizzled: c fed to the step
@@ -1679,12 +1679,20 @@ int launch_bwd(const CUtensorMap &tm_acts, const CUtensorMap &tm_do, const CUten
 
 size_t smem_need(bool bwd, int H, int N, bool a_tmem, bool push = false) {
   const int nkb = (H + 63) / 64, HP = (H + 127) / 128 * 128;
-  size_t s = bwd ? (size_t)2 * HP * 128 + 2 * (size_t)N * 128 + 4 * (size_t)N * 128 + (push ? (size_t)2 * (H / 32) * 32 * N * 2 : 0)
+  size_t s = bwd ? (a_tmem ? 0 : (size_t)2 * HP * 128) + 2 * (size_t)N * 128 + 4 * (size_t)N * 128 + (push ? (size_t)2 * (H / 32) * 32 * N * 2 : 0)
                  : (a_tmem ? 0 : (size_t)nkb * 16384) + (size_t)(push ? 2 : 1) * nkb * N * 128 + 2 * (size_t)N * 128 + 2 * (size_t)N * 128;
   return s + 1024 + 256;
 }
 
 struct TcPlan { int N; bool a_tmem, mcast_ok, pp; int pp_fwd_env, pp_bwd_env; };
+
+// Smallest batch tile the two-half-tile BPTT kernel takes.  Below it the single-tile kernel wins since it sends its
+// partial sums rank to rank (measured at H=512, B=200, N=32: 2.5 ms per layer pass against 3.5 ms).
+int bwd_pp_min() {
+  static int v = -1;
+  if (v < 0) { const char *e = getenv("SKRNN_TC_PP_BWD_MIN"); v = e ? atoi(e) : 64; }
+  return v;
+}
 
 // batch tile and kernel variant of a layer pass at batch B
 TcPlan tc_plan(const skrnn_handle *h, bool bwd, int B) {
@@ -1715,7 +1723,7 @@ TcPlan tc_plan(const skrnn_handle *h, bool bwd, int B) {
   // the backward pass is faster the other way round, 5.2 K vs 8.7 K, so only the forward tile is widened)
   if (N == 16 && B > 16 && !bwd && pp_env != 0 && mcast_ok && a_tmem) N = 32;
   p.N = N; p.a_tmem = a_tmem; p.mcast_ok = mcast_ok; p.pp_fwd_env = pp_env; p.pp_bwd_env = ppb_env;
-  p.pp = bwd ? (ppb_env && N >= 32) : (pp_env && mc_env && mcast_ok && a_tmem && N >= 32);
+  p.pp = bwd ? (ppb_env && N >= bwd_pp_min()) : (pp_env && mc_env && mcast_ok && a_tmem && N >= 32);
   return p;
 }
 
@@ -1882,7 +1890,7 @@ int sk_rnn_tc_layer(skrnn_handle *h, cudaStream_t st, bool bwd, int l, int B, in
       h->ws.partial_floats = need;
     }
     a.partial = h->ws.partial;
-    const int ppN = (ppb_env && N >= 32) ? N / 2 : N;  // rows per box (half tiles for the two-half-tile kernel)
+    const int ppN = (ppb_env && N >= bwd_pp_min()) ? N / 2 : N;  // rows per box (half tiles for the two-half-tile kernel)
     // d(pre) [T,B,4H] bf16 with gate-interleaved columns (4*unit + gate): what the kernel's operand tile holds, stored
     // as two 64-column boxes in the operand's own (128B-swizzled) layout
     CUtensorMap tm_dp;
@@ -1901,7 +1909,7 @@ int sk_rnn_tc_layer(skrnn_handle *h, cudaStream_t st, bool bwd, int l, int B, in
       SK_TRY(sk_make_tmap(&tm_do, 4, h->ws.dout, 3, dims, str, box));
       SK_TRY(sk_make_tmap(&tm_cp, 4, h->ws.cprev[l], 3, dims, str, box));
     }
-    if (ppb_env && N >= 32) {  // two half tiles in flight (lstm_bwd_pp_kernel): boxes of N/2 rows
+    if (ppb_env && N >= bwd_pp_min()) {  // two half tiles in flight (lstm_bwd_pp_kernel): boxes of N/2 rows
       uint64_t adims[3] = {(uint64_t)h->G, (uint64_t)B, (uint64_t)T};
       uint64_t astr[2] = {(uint64_t)h->G * 2, (uint64_t)B * h->G * 2};
       uint32_t abox[3] = {128, (uint32_t)(N / 2), 1};
@@ -1921,14 +1929,16 @@ int sk_rnn_tc_layer(skrnn_handle *h, cudaStream_t st, bool bwd, int l, int B, in
     }
     // small tiles: the partial sums travel rank to rank through distributed shared memory; SKRNN_TC_PUSH_BWD=<max N>
     static int pushb_max = -1;
-    if (pushb_max < 0) { const char *e = getenv("SKRNN_TC_PUSH_BWD"); pushb_max = e ? atoi(e) : 16; }
+    if (pushb_max < 0) { const char *e = getenv("SKRNN_TC_PUSH_BWD"); pushb_max = e ? atoi(e) : 32; }
     a.push = (N <= pushb_max) ? 1 : 0;
-    const size_t smem_b = smem_need(true, H, N, false, a.push != 0);
+    const size_t smem_b = smem_need(true, H, N, bwd_atmem, a.push != 0);
+    if (smem_b > 227 * 1024) { a.push = 0; }
+    const size_t smem_b2 = a.push ? smem_b : smem_need(true, H, N, bwd_atmem, false);
     SkLaunch scope(h, st, SK_CAT_RNN_BWD);
-    if (N == 16) rc = launch_bwd<1>(tm_act, tm_do, tm_cp, tm_dp, a, nclusters, smem_b, st);
-    else if (N == 32) rc = launch_bwd<2>(tm_act, tm_do, tm_cp, tm_dp, a, nclusters, smem_b, st);
-    else if (N == 64) rc = launch_bwd<4>(tm_act, tm_do, tm_cp, tm_dp, a, nclusters, smem_b, st);
-    else rc = launch_bwd<8>(tm_act, tm_do, tm_cp, tm_dp, a, nclusters, smem_b, st);
+    if (N == 16) rc = launch_bwd<1>(tm_act, tm_do, tm_cp, tm_dp, a, nclusters, smem_b2, st);
+    else if (N == 32) rc = launch_bwd<2>(tm_act, tm_do, tm_cp, tm_dp, a, nclusters, smem_b2, st);
+    else if (N == 64) rc = launch_bwd<4>(tm_act, tm_do, tm_cp, tm_dp, a, nclusters, smem_b2, st);
+    else rc = launch_bwd<8>(tm_act, tm_do, tm_cp, tm_dp, a, nclusters, smem_b2, st);
     if (rc != 0) return 1;  // the forward's activations live in this family's format: no fallback possible
   }
   if (rc != 0) {
