@@ -26,6 +26,12 @@
 // barrier.cluster per step (small batches).  lstm_{fwd,bwd}_pp_kernel: two half tiles in flight, no
 // cluster barrier in the loop -- a publisher warp signals every rank's mbarrier through the cluster
 // shared-memory window once the CTA's h_t (forward, TMA-stored) or partials (backward) are out.
+//
+// Small tiles (up to 32 rows per cluster) are pure latency chains, and most of a step used to be the exchange through
+// global memory.  There the ranks send to each other directly: forward, the publisher warp st.async-es the CTA's rows
+// of h_t into every rank's operand tile of the next step (TcRnnArgs::push, lstm_fwd_pp_kernel); backward, every
+// elementwise thread st.async-es its partial sums into the destination rank's receive buffer (lstm_bwd_tc_kernel).
+// Either way the stores' bytes complete an mbarrier phase on the receiver: no fence, no barrier.cluster, no L2 trip.
 #include <stdlib.h>
 #include <type_traits>
 
