@@ -1411,47 +1411,11 @@ lstm_bwd_pp_kernel(const __grid_constant__ CUtensorMap tm_acts, const __grid_con
     uint32_t lapt = 0;
     if (dbg) lapt = (uint32_t)clock();
 
-    // partial sums of one half on their way from L2: raw bf16 groups of the CS ranks
-    uint2 pv[16];
-    bool p1_pending = false;
-    auto p_issue = [&](int s, int par) {
-      const __nv_bfloat16 *src0 = part_base + (size_t)(2 * s + par) * part_par + (((size_t)rank * CS) * 4 + cg) * part_blk +
-                                  ((size_t)((esub * NCH) / CK) * 32 + eu) * CK + (esub * NCH) % CK;
-#pragma unroll
-      for (int j = 0; j < 16; ++j) {
-        pv[j] = make_uint2(0, 0);
-        if (j < CS) {
-          const __nv_bfloat16 *pj = src0 + (size_t)j * 4 * part_blk;
-          if constexpr (NCH == 4) pv[j] = __ldcg(reinterpret_cast<const uint2 *>(pj));
-          else if constexpr (NCH == 2) pv[j].x = __ldcg(reinterpret_cast<const uint32_t *>(pj));
-          else pv[j].x = (uint32_t)__ldcg(reinterpret_cast<const unsigned short *>(pj));
-        }
-      }
-    };
-    auto p_consume = [&](int s) {  // fixed rank order
-      static_assert(NCH == 1 || NCH == 2 || NCH == 4, "half tiles of 16, 32 or 64 columns");
-#pragma unroll
-      for (int it = 0; it < NCH; ++it) dhc[s][it] = 0.f;
-#pragma unroll
-      for (int j = 0; j < 16; ++j) {
-        if constexpr (NCH == 4) {
-          const float2 f0 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162 *>(&pv[j].x));
-          const float2 f1 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162 *>(&pv[j].y));
-          dhc[s][0] += f0.x; dhc[s][1] += f0.y; dhc[s][2] += f1.x; dhc[s][3] += f1.y;
-        } else if constexpr (NCH == 2) {
-          const float2 f0 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162 *>(&pv[j].x));
-          dhc[s][0] += f0.x; dhc[s][1] += f0.y;
-        } else {
-          dhc[s][0] += __bfloat162float(__ushort_as_bfloat16((unsigned short)pv[j].x));
-        }
-      }
-    };
     for (int t = t1 - 1, step = 0; t >= t0; --t, ++step) {
       const int par = step & 1;
       // ---- E_s ----
 #pragma unroll
       for (int s = 0; s < 2; ++s) {
-        if (s == 1 && p1_pending) { p_consume(1); p1_pending = false; }
         mbar_wait(bar_in + 8 * s, step & 1);
         TCR_LAP(tk[0]);
         auto items = [&](auto full_tag) {
@@ -1530,19 +1494,50 @@ lstm_bwd_pp_kernel(const __grid_constant__ CUtensorMap tm_acts, const __grid_con
         TCR_LAP(tk[3]);
       }
       // ---- P_s: d(h_{t-1}) of my units = sum over ranks (fixed order) of their partials ----
-      // The loads are one L2 round trip (~1.7 K cycles) each.  Half 0's are requested as soon as its partials are
-      // published and consumed after the wait for half 1's publication; half 1's are requested then and consumed only
-      // before E_1 of the next step, so they travel while E_0 runs.
-      mbar_wait_cluster(bar_ready + 0, step & 1);
-      TCR_LAP(tk[4]);
-      p_issue(0, par);
-      mbar_wait_cluster(bar_ready + 8, step & 1);
-      p_consume(0);
-      p_issue(1, par);
-      p1_pending = true;
-      TCR_LAP(tk[5]);
+#pragma unroll
+      for (int s = 0; s < 2; ++s) {
+        mbar_wait_cluster(bar_ready + 8 * s, step & 1);
+        TCR_LAP(tk[4]);
+        const __nv_bfloat16 *src0 = part_base + (size_t)(2 * s + par) * part_par + (((size_t)rank * CS) * 4 + cg) * part_blk +
+                                    ((size_t)((esub * NCH) / CK) * 32 + eu) * CK + (esub * NCH) % CK;
+#pragma unroll
+        for (int it = 0; it < NCH; ++it) dhc[s][it] = 0.f;
+        constexpr int UR = 16;  // all ranks' partials in flight at once: one L2 round trip instead of two
+        for (int r0 = 0; r0 < CS; r0 += UR) {
+          if constexpr (NCH == 4) {
+            uint2 v[UR];
+#pragma unroll
+            for (int j = 0; j < UR; ++j)
+              v[j] = (r0 + j < CS) ? __ldcg(reinterpret_cast<const uint2 *>(src0 + (size_t)(r0 + j) * 4 * part_blk)) : make_uint2(0, 0);
+#pragma unroll
+            for (int j = 0; j < UR; ++j) {
+              const float2 f0 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162 *>(&v[j].x));
+              const float2 f1 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162 *>(&v[j].y));
+              dhc[s][0] += f0.x; dhc[s][1] += f0.y; dhc[s][2] += f1.x; dhc[s][3] += f1.y;
+            }
+          } else if constexpr (NCH == 1) {
+            unsigned short v[UR];
+#pragma unroll
+            for (int j = 0; j < UR; ++j)
+              v[j] = (r0 + j < CS) ? __ldcg(reinterpret_cast<const unsigned short *>(src0 + (size_t)(r0 + j) * 4 * part_blk)) : (unsigned short)0;
+#pragma unroll
+            for (int j = 0; j < UR; ++j) dhc[s][0] += __bfloat162float(__ushort_as_bfloat16(v[j]));
+          } else {
+            static_assert(NCH == 2, "half tiles of 16, 32 or 64 columns");
+            uint32_t v[UR];
+#pragma unroll
+            for (int j = 0; j < UR; ++j)
+              v[j] = (r0 + j < CS) ? __ldcg(reinterpret_cast<const uint32_t *>(src0 + (size_t)(r0 + j) * 4 * part_blk)) : 0u;
+#pragma unroll
+            for (int j = 0; j < UR; ++j) {
+              const float2 f0 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162 *>(&v[j]));
+              dhc[s][0] += f0.x; dhc[s][1] += f0.y;
+            }
+          }
+        }
+        TCR_LAP(tk[5]);
+      }
     }
-    if (p1_pending) p_consume(1);
     if (t0 > 0) {  // hand d(h_{t0-1}), d(c_{t0-1}) to the launch that continues below t0
 #pragma unroll
       for (int s = 0; s < 2; ++s)
