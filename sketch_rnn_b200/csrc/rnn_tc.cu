@@ -89,6 +89,7 @@ struct TcRnnArgs {
   const uint8_t *wimg;    // per-rank shared-memory images of the weight operand
   int wimg_bytes;
   int mcast;              // forward: the h tile arrives by TMA multicast (each rank fetches 1/CS of it)
+  int sig_async;          // forward, two-half-tile kernel: h stores are announced with st.async instead of release-arrives
   int push;               // forward, two-half-tile kernel, small tiles: every rank sends its units of h_t straight into every
                           // rank's operand tile (st.async + transaction bytes) instead of store -> signal -> multicast load
   int a_tmem;             // forward: weights live in tensor memory (wimg is plain row-major [128][nkb*64] bf16)
@@ -521,7 +522,7 @@ lstm_fwd_pp_kernel(const __grid_constant__ CUtensorMap tm_h, const __grid_consta
       mbar_init(bar_xw + 8 * s, 1);
       mbar_init(bar_acc + 8 * s, 1);
       mbar_init(bar_epi + 8 * s, 32 * TCR_EPI_WARPS);
-      mbar_init(bar_ready + 8 * s, CS);
+      mbar_init(bar_ready + 8 * s, a.sig_async ? 1 : CS);
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -607,17 +608,27 @@ lstm_fwd_pp_kernel(const __grid_constant__ CUtensorMap tm_h, const __grid_consta
       };
       load_xw(0, t0);
       load_xw(1, t0);
+      // sig_async: the ranks announce their h stores with 4-byte st.async stores whose bytes complete bar_ready's
+      // phase; this thread states the expected bytes of a phase once the previous one is over
+      const bool sig = a.sig_async && !push;
+      if (sig && t0 + 1 < t1) { mbar_expect_tx(bar_ready + 0, (uint32_t)CS * 4u); mbar_expect_tx(bar_ready + 8, (uint32_t)CS * 4u); }
       for (int t = t0; t < t1; ++t) {
         // push mode: after the first step the tile is SENT by the ranks' publishers; this thread only states how many
         // bytes the step's barrier phase expects (the previous phase is over: retire() of that half has been passed)
         const bool pushed = push && t > t0;
-        if (t > t0 && !push) mbar_wait_cluster(bar_ready + 0, (t - 1) & 1);
+        if (t > t0 && !push) {
+          mbar_wait_cluster(bar_ready + 0, (t - 1) & 1);
+          if (sig && t + 1 < t1) mbar_expect_tx(bar_ready + 0, (uint32_t)CS * 4u);
+        }
         TCR_LAP(tk[8]);
         if (pushed) mbar_expect_tx(bar_h + 0, h_bytes); else load_h(0, t);
         TCR_LAP(tk[9]);
         if (t > t0) retire(1, t - 1);
         TCR_LAP(tk[10]);
-        if (t > t0 && !push) mbar_wait_cluster(bar_ready + 8, (t - 1) & 1);
+        if (t > t0 && !push) {
+          mbar_wait_cluster(bar_ready + 8, (t - 1) & 1);
+          if (sig && t + 1 < t1) mbar_expect_tx(bar_ready + 8, (uint32_t)CS * 4u);
+        }
         TCR_LAP(tk[11]);
         if (pushed) mbar_expect_tx(bar_h + 8, h_bytes); else load_h(1, t);
         TCR_LAP(tk[12]);
@@ -726,7 +737,20 @@ lstm_fwd_pp_kernel(const __grid_constant__ CUtensorMap tm_h, const __grid_consta
           }
           __syncwarp();
           TCR_LAP(tk[21]);
-          if (lane < CS) mbar_arrive_remote(bar_ready + 8 * s, (uint32_t)lane);
+          if (lane < CS) {
+            if (a.sig_async) {
+              // the store above is complete (in L2) before this is issued; the announcement itself is a plain 4-byte
+              // st.async into a scratch word of rank `lane` that counts on its bar_ready -- no cluster-scope release
+              // (which costs a gpu-scope fence, ~1.3 K cycles per half step here)
+              if (t + 1 < t1) {
+                const uint32_t rs = mapa_u32(s_bar + 96u + (uint32_t)(s * 16 + rank) * 4u, (uint32_t)lane);
+                const uint32_t rb = mapa_u32(bar_ready + 8 * s, (uint32_t)lane);
+                asm volatile("st.async.shared::cluster.mbarrier::complete_tx::bytes.b32 [%0], %1, [%2];" ::"r"(rs), "r"(1u), "r"(rb) : "memory");
+              }
+            } else {
+              mbar_arrive_remote(bar_ready + 8 * s, (uint32_t)lane);
+            }
+          }
           __syncwarp();
           TCR_LAP(tk[22]);
         }
@@ -1868,6 +1892,9 @@ int sk_rnn_tc_layer(skrnn_handle *h, cudaStream_t st, bool bwd, int l, int B, in
       static int push_max = -1;
       if (push_max < 0) { const char *e = getenv("SKRNN_TC_PUSH"); push_max = e ? atoi(e) : 32; }
       a.push = (N <= push_max) ? 1 : 0;
+      static int sig_env = -1;
+      if (sig_env < 0) { const char *e = getenv("SKRNN_TC_SIG_ASYNC"); sig_env = (e && e[0] == '0') ? 0 : 1; }
+      a.sig_async = sig_env;
       const size_t smem_pp = smem_need(false, H, N, a_tmem, a.push != 0);
       SkLaunch scope(h, st, SK_CAT_RNN_FWD);
       if (N == 32) rc = launch_fwd_pp<1>(tm_h, tm_xw, tm_hst, a, nclusters, smem_pp, st);
