@@ -665,7 +665,8 @@ def test_bf16_lstm_time_ranges_match_single_launch(monkeypatch):
         h.close()
     assert res["3"][3] > res["1"][3], "the ranged run did not launch more kernels: ranges were not taken"
     assert np.array_equal(res["1"][1], res["3"][1])
-    assert np.allclose(res["1"][0], res["3"][0], rtol=1e-6)
+    # (the fused head adds the per-warp loss sums with fp32 atomics, so the last bits of a loss depend on arrival order)
+    assert np.allclose(res["1"][0], res["3"][0], rtol=1e-5)
     for n in grads_ref:
         assert rel_err(res["3"][2][n], res["1"][2][n]) < 1e-3, n
         assert rel_err(res["3"][2][n], grads_ref[n]) < BF16_TOL, n
