@@ -173,13 +173,11 @@ __device__ __forceinline__ uint32_t r1_bchunk(int k) { return (uint32_t)(((k & 6
 #define R1_BOFF(colbase, chunk4, n) ((colbase) + (uint32_t)((n) * 128) + ((chunk4) ^ (uint32_t)(((n) & 7) << 4)))
 __device__ __forceinline__ void r1_sts_bf16(uint8_t *p, float v) { *reinterpret_cast<__nv_bfloat16 *>(p) = __float2bfloat16_rn(v); }
 
-// A bf16 value is loaded as its raw 16 bits and widened only after r1_pin, which the compiler cannot move above the
-// mbarrier wait before it (both are volatile asm): otherwise the widening shift is scheduled right behind the load and
-// the thread sits out the whole memory latency BEFORE it starts waiting for the product (measured: ~2000 cycles/step).
-__device__ __forceinline__ uint32_t r1_ld_raw16(const char *p) { return (uint32_t)(*reinterpret_cast<const unsigned short *>(p)); }
+// Loaded bf16 groups stay raw and are widened only after r1_pin, which the compiler cannot move above the mbarrier
+// wait before it (both are volatile asm): otherwise the widening shift is scheduled right behind the load and the
+// thread sits out the whole memory latency BEFORE it starts waiting for the product (measured: ~2000 cycles/step).
 __device__ __forceinline__ void r1_pin(uint32_t &v) { asm volatile("" : "+r"(v)); }
 __device__ __forceinline__ void r1_pin(float &v) { asm volatile("" : "+f"(v)); }
-__device__ __forceinline__ float r1_bf16_of(uint32_t raw) { return __uint_as_float(raw << 16); }
 // Per-step arrays the elementwise threads read or write for THEMSELVES are kept "tile-transposed":
 //   X_tt[t][batch tile of 16][row group of NR][column][NR rows]
 // so that a thread (one column = hidden unit, NR batch rows) moves its NR values with ONE vector access, coalesced
@@ -305,16 +303,6 @@ __device__ __forceinline__ void r1_exchange(const R1Xchg &x, uint32_t s_tile, ui
 __device__ __forceinline__ void r1_publish(uint32_t bar) {
   fence_proxy_async_smem();
   mbar_arrive(bar);
-}
-
-// L2 prefetch of the 128-byte line holding (row b0 + lane, column col) of a [T,B,ld] array at step t: one instruction
-// per warp brings in what the warp's 32 units will load for the tile's rows two steps later
-__device__ __forceinline__ void r1_prefetch(const void *base, size_t elem_bytes, int t, int T, int B, int b0, int ld, int col,
-                                            int lane, int l1) {
-  if (t < 0 || t >= T || lane >= R1_N || b0 + lane >= B) return;
-  const char *p = reinterpret_cast<const char *>(base) + (((size_t)t * B + b0 + lane) * ld + col) * elem_bytes;
-  if (l1) asm volatile("prefetch.global.L1 [%0];" ::"l"(p));
-  else asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
 }
 
 // eoc flag byte of (t, b0 + lane), requested one step ahead; the ballot of it is the step's row mask
@@ -483,7 +471,6 @@ rnn1_fwd_kernel(const __grid_constant__ CUtensorMap tm_hp, const __grid_constant
     // ---------------- elementwise warps ----------------
     const uint32_t lane_addr = tmem_base + ((uint32_t)(32 * q) << 16);
     const uint32_t drop_unit = skm_drop_unit(a.seed, (uint32_t)unit);
-    const int u0w = unit - lane;  // first unit of this warp
     // per-thread views of (t, b0, unit) of the step's arrays: base pointer advanced per step, row n at n * row stride
     const int NT = (B + N - 1) / N, tile = blockIdx.x / CL;
     const int AC = CELL == 1 ? 4 * H : H;
