@@ -374,7 +374,10 @@ BF16_CASES = [("lstm", 16, 2, 3, 5, 7), ("gru", 64, 3, 5, 11, 6), ("rnn", 40, 3,
               # gru / rnn tensor-core kernels: one CTA per batch tile (H <= 128), the cluster of two with an uneven
               # split of the units (H = 192: 128 + 64), several ragged 16-row tiles
               ("gru", 128, 2, 24, 37, 9), ("rnn", 128, 2, 24, 16, 7), ("gru", 192, 2, 24, 21, 8),
-              ("rnn", 192, 3, 24, 33, 6), ("rnn", 256, 2, 24, 50, 9), ("gru", 256, 3, 24, 49, 7)]
+              ("rnn", 192, 3, 24, 33, 6), ("rnn", 256, 2, 24, 50, 9), ("gru", 256, 3, 24, 49, 7),
+              # lstm, 32-row tiles on 16-CTA clusters: forward two halves of 16 rows with h pushed rank to rank, BPTT on
+              # the single-tile kernel with pushed partial sums (the shapes a 4- or 8-GPU shard of config 4 runs)
+              ("lstm", 512, 2, 24, 130, 10), ("lstm", 512, 2, 24, 70, 9)]
 
 
 @pytest.mark.parametrize("model,H,L,M,B,T", BF16_CASES)
