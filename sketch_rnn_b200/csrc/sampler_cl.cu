@@ -555,6 +555,9 @@ int sk_sample_cluster(skrnn_handle *h, cudaStream_t st, int n, int steps, float 
     if (n > n_max) return -1;
   }
   SkLaunch scope(h, st, SK_CAT_SAMPLER);
-  SK_CUDA(cudaLaunchKernelEx(&lc, sample_cluster_kernel, a, p));
+  if (cudaLaunchKernelEx(&lc, sample_cluster_kernel, a, p) != cudaSuccess) {
+    cudaGetLastError();  // the cluster could not be placed after all: the streaming kernel takes the call
+    return -1;
+  }
   return 0;
 }
