@@ -10,7 +10,7 @@ utils.make_synthetic_dataset(os.path.join(d, "data", "kanji.cpkl"), num_sketches
 for model in ("lstm", "gru", "rnn"):
     r = subprocess.run([sys.executable, os.path.join(ROOT, "train.py"), "--model", model, "--max_batches", n, "--save_every", "100000"],
                        cwd=d, env=dict(os.environ, PYTHONPATH=ROOT), capture_output=True, text=True)
-    losses = [float(m.group(1)) for m in re.finditer(r"train_loss = ([-0-9.einfa]+)", r.stdout)]
+    losses = [float(m.group(1)) for m in re.finditer(r"cost = ([-0-9.einfa]+)", r.stdout)]
     if len(losses) < 20:
         print(model, "no losses parsed:", r.stdout[-400:], r.stderr[-400:])
         continue
