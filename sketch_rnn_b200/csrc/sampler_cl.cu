@@ -13,7 +13,7 @@
 //               is "wait until H*SB*4 bytes have landed" -- no barrier.cluster (a gpu-scope fence plus an L1
 //               invalidate, ~5 us per step for three of them) in the loop;
 //   output:     its OC logits per sketch -> every rank's logits buffer, same mechanism;
-//   draw:       every rank draws the next point of all 4 sketches redundantly (one warp per sketch), so the feedback
+//   draw:       every rank draws the next point of all 4 sketches redundantly (two warps per sketch), so the feedback
 //               (dx, dy, eos, eoc, cont) needs no further exchange; rank 0 writes the strokes.
 // Same arithmetic contract as sampler.cu: every output element is ONE sequential fused-multiply-add chain over
 // k = 0..K-1 of [x ; h] * W followed by + bias, and every transcendental comes from skrnn_math.h -- bit-identical to
@@ -27,7 +27,7 @@ namespace {
 
 constexpr int SCL_CS = 16;  // CTAs per cluster
 constexpr int SCL_SB = 4;   // sketches per cluster
-constexpr int SCL_THREADS = 128;
+constexpr int SCL_THREADS = 256;  // 8 warps: the draw of a sketch is shared by warps r (mixture) and r + 4 (pen state, normals)
 
 struct SclArgs {
   int n, steps, H, L, M, NOUT, cell;
@@ -167,6 +167,7 @@ struct SclPlan {
   int rh;                                    // gru: [SB][H]  r*h of the layer being computed
   int hlast;                                 // [SB][H]  output of the last layer
   int lg, xin, pdf, flags;                   // [SB][NOUT], [SB][5 -> 8], [SB][M], 2*SB ints
+  int dsc;                                   // [SB][8]: pen probabilities, pen index, the two normals of a sketch's draw
   int cst;                                   // lstm cell state: [L][UPC*SB], one slot per cell thread
   int bars;                                  // mbarriers (8 bytes each): per layer A (output), R (gru r*h), Hb (state); then LG
   int total;
@@ -200,6 +201,7 @@ __host__ __device__ inline SclPlan scl_plan(int cell, int H, int L, int M, int N
   p.xin = o; o += SCL_SB * 8;
   p.pdf = o; o += SCL_SB * ((M + 3) & ~3);
   p.flags = o; o += 2 * SCL_SB;
+  p.dsc = o; o += SCL_SB * 8;
   p.cst = o; o += L * UPC * SCL_SB;
   o = (o + 3) & ~3;
   p.bars = o; o += 2 * (3 * SK_MAX_LAYERS + 1);
@@ -261,9 +263,14 @@ sample_cluster_kernel(const __grid_constant__ SclArgs a, const __grid_constant__
   scl_cluster_sync();  // nobody sends into a peer before it has zeroed its buffers and initialised its barriers
 
   // cell threads: one per (unit, sketch); the lstm cell state stays in its registers
-  const bool cth = tid < UPC * SCL_SB;
-  const int cu = tid % UPC, cs = tid / UPC;
-  float *cst = sm + p.cst + tid;  // + l * UPC * SB
+  // lstm: the four gate chains of (unit, sketch) are split over two adjacent threads -- (i, j) and (f, o) -- so that the
+  // dot products keep all four schedulers busy; the even thread then owns the cell update
+  const int pidx = cell == 0 ? (tid >> 1) : tid;
+  const int ghalf = cell == 0 ? (tid & 1) : 0;
+  const bool dth = pidx < UPC * SCL_SB;  // takes part in the dot products
+  const bool cth = dth && ghalf == 0;    // owns (unit, sketch): cell update and sends
+  const int cu = pidx % UPC, cs = pidx / UPC;
+  float *cst = sm + p.cst + pidx;  // + l * UPC * SB
 
   int last_step = 0;
   const bool dbg = a.debug && blockIdx.x == 0 && tid == 0;
@@ -292,11 +299,12 @@ sample_cluster_kernel(const __grid_constant__ SclArgs a, const __grid_constant__
       const bool hold = cth && xin[cs * 8 + 3] > 0.f;  // an eoc input holds the state (model.py:82-92,215)
       float hnew = 0.f, hkeep = 0.f;
       if (cell == 0) {
+        const float *As = xh + cs * Kp;
+        float acc[2] = {0.f, 0.f};
+        if (dth) scl_dot<2>(As, sm + p.w[l] + 4 * cu + 2 * ghalf, 4 * UPC, K, acc);
+        const float a2 = __shfl_down_sync(0xffffffffu, acc[0], 1), a3 = __shfl_down_sync(0xffffffffu, acc[1], 1);  // f, o from the odd lane
         if (cth) {
-          const float *As = xh + cs * Kp;
-          float acc[4] = {0.f, 0.f, 0.f, 0.f};
-          scl_dot<4>(As, sm + p.w[l] + 4 * cu, 4 * UPC, K, acc);
-          const float a0 = acc[0], a1 = acc[1], a2 = acc[2], a3 = acc[3];
+          const float a0 = acc[0], a1 = acc[1];
           const float4 bb = reinterpret_cast<const float4 *>(sm + p.b[l])[cu];
           const float c = cst[l * UPC * SCL_SB];
           const float ig = skm_sigmoid(SKM_ADD(a0, bb.x));
@@ -373,12 +381,17 @@ sample_cluster_kernel(const __grid_constant__ SclArgs a, const __grid_constant__
     SCL_LAP(5);
     // ---- per-sketch draw and feedback (model.py:219-261): warp s draws sketch s; lanes share the transcendentals,
     //      lane 0 does every reduction sequentially, in the order the reference sums ----
-    if (warp < rows_valid && !flags[warp]) {
-      const int r = warp;
-      const int sk = sk_base + r;
-      const float *z = lg + r * NOUTP;
-      float *pd = sm + p.pdf + r * MP;
-      float u4[4];
+    // warp r (< 4): mixture softmax, temperature and the component draw of sketch r; warp r + 4: its pen state and the
+    // two standard normals (neither depends on the chosen component), handed over through `dsc`
+    const int r = warp & 3;
+    const bool dact = r < rows_valid && !flags[r];
+    const int sk = sk_base + r;
+    const float *z = lg + r * NOUTP;
+    float *pd = sm + p.pdf + r * MP;
+    float *dsc = sm + p.dsc + r * 8;
+    float u4[4] = {0.f, 0.f, 0.f, 0.f};
+    int idx = 0;
+    if (dact) {
       if (a.uniforms != nullptr) {
         const float *up = a.uniforms + ((size_t)sk * a.steps + step) * 4;
         u4[0] = up[0]; u4[1] = up[1]; u4[2] = up[2]; u4[3] = up[3];
@@ -388,6 +401,8 @@ sample_cluster_kernel(const __grid_constant__ SclArgs a, const __grid_constant__
                        (uint32_t)(a.seed >> 32), rr);
         for (int q = 0; q < 4; ++q) u4[q] = skm_u01(rr[q]);
       }
+    }
+    if (dact && warp < 4) {
       // softmax over the M mixture logits (get_mixture_coef, model.py:152-156)
       float mx = -INFINITY;
       for (int k = lane; k < M; k += 32) mx = fmaxf(mx, z[3 + k]);
@@ -422,17 +437,29 @@ sample_cluster_kernel(const __grid_constant__ SclArgs a, const __grid_constant__
       for (int k = lane; k < M; k += 32) pd[k] = SKM_DIV(pd[k], s2);
       __syncwarp();
       if (lane == 0) {
-        int idx = scl_pick_idx(pd, M, u4[0]);
+        idx = scl_pick_idx(pd, M, u4[0]);
         if (idx < 0) idx = M - 1;  // python negative index (model.py:247)
-        // pen state: plain softmax, the pen temperature is never applied (model.py:228-233)
-        const float pm = fmaxf(z[0], fmaxf(z[1], z[2]));
-        float pe[3];
-        pe[0] = skm_exp(SKM_SUB(z[0], pm));
-        pe[1] = skm_exp(SKM_SUB(z[1], pm));
-        pe[2] = skm_exp(SKM_SUB(z[2], pm));
-        const float ps = SKM_ADD(SKM_ADD(pe[0], pe[1]), pe[2]);
-        pe[0] = SKM_DIV(pe[0], ps); pe[1] = SKM_DIV(pe[1], ps); pe[2] = SKM_DIV(pe[2], ps);
-        const int pen_idx = scl_pick_idx(pe, 3, u4[1]);
+      }
+    } else if (dact && lane == 0) {
+      // pen state: plain softmax, the pen temperature is never applied (model.py:228-233)
+      const float pm = fmaxf(z[0], fmaxf(z[1], z[2]));
+      float pe[3];
+      pe[0] = skm_exp(SKM_SUB(z[0], pm));
+      pe[1] = skm_exp(SKM_SUB(z[1], pm));
+      pe[2] = skm_exp(SKM_SUB(z[2], pm));
+      const float ps = SKM_ADD(SKM_ADD(pe[0], pe[1]), pe[2]);
+      pe[0] = SKM_DIV(pe[0], ps); pe[1] = SKM_DIV(pe[1], ps); pe[2] = SKM_DIV(pe[2], ps);
+      const int pen_idx = scl_pick_idx(pe, 3, u4[1]);
+      float g1, g2;
+      skm_box_muller(u4[2], u4[3], &g1, &g2);
+      dsc[0] = pe[0]; dsc[1] = pe[1]; dsc[2] = pe[2]; dsc[3] = (float)pen_idx; dsc[4] = g1; dsc[5] = g2;
+    }
+    __syncthreads();
+    if (dact && warp < 4) {
+      if (lane == 0) {
+        const float pe[3] = {dsc[0], dsc[1], dsc[2]};
+        const int pen_idx = (int)dsc[3];
+        const float g1 = dsc[4], g2 = dsc[5];
         float eos = 0.f, eoc = 0.f, cont = 0.f;
         if (pen_idx == 0) eos = 1.f;
         else if (pen_idx == 1) eoc = 1.f;
@@ -441,8 +468,6 @@ sample_cluster_kernel(const __grid_constant__ SclArgs a, const __grid_constant__
         const float mu1 = z[3 + M + idx], mu2 = z[3 + 2 * M + idx];
         const float sg1 = skm_exp(z[3 + 3 * M + idx]), sg2 = skm_exp(z[3 + 4 * M + idx]);
         const float rho = skm_tanh(z[3 + 5 * M + idx]);
-        float g1, g2;
-        skm_box_muller(u4[2], u4[3], &g1, &g2);
         const float x1 = SKM_FMA(sg1, g1, mu1);
         const float q = SKM_SQRT(SKM_SUB(1.0f, SKM_MUL(rho, rho)));
         const float tt = SKM_FMA(q, g2, SKM_MUL(rho, g1));
@@ -507,7 +532,7 @@ int sk_sample_cluster(skrnn_handle *h, cudaStream_t st, int n, int steps, float 
   const int H = h->H;
   if (H % SCL_CS != 0 || h->M > 64) return -1;
   const int UPC = H / SCL_CS, OC = (h->NOUT + SCL_CS - 1) / SCL_CS;
-  if (UPC * SCL_SB > SCL_THREADS || OC * SCL_SB > SCL_THREADS) return -1;
+  if (2 * UPC * SCL_SB > SCL_THREADS || OC * SCL_SB > SCL_THREADS) return -1;
   const SclPlan p = scl_plan(h->cfg.cell, H, h->L, h->M, h->NOUT, UPC, OC);
   const size_t smem = (size_t)p.total * sizeof(float);
   if (smem > 227 * 1024) return -1;  // the stack does not fit a 16-CTA cluster's shared memory
