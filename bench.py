@@ -349,7 +349,9 @@ def sampling_block(world, rank, local):
             torch.cuda.synchronize()
             ms10 = e0.elapsed_time(e1) / 5
             out["config2_size"] = {"sketches_per_sec": 10 / (ms10 * 1e-3), "ms": ms10, "n_sketches": 10, "steps": 300,
-                                   "bit_exact": True, "note": "synthetic weights (save/kanji/model.ckpt-0 is absent); "
+                                   "bit_exact": True, "launches_per_call": 1,
+                                   "kernel": "sample_cluster_kernel (fp32 weights resident in a 16-CTA cluster, bit-exact)",
+                                   "note": "synthetic weights (save/kanji/model.ckpt-0 is absent); "
                                    "fixed 300 steps, no early stop"}
         h.close()
     flop = 1.0 * fwd_flops_per_stroke_step(WORKLOADS["sample_8192"]) * 8192 * 300
