@@ -488,7 +488,7 @@ __device__ __forceinline__ void mbar_arrive_remote(uint32_t bar, uint32_t rank) 
       "}\n" ::"r"(bar), "r"(rank) : "memory");
 }
 
-template <int NCH, bool DBG>  // NCH items per thread and half tile
+template <int NCH, bool DBG, int HT = 0>  // NCH items per thread and half tile; HT: rnn_size as a compile-time constant (0: run time)
 __global__ void __launch_bounds__(TCR_PP_THREADS, 1)
 lstm_fwd_pp_kernel(const __grid_constant__ CUtensorMap tm_h, const __grid_constant__ CUtensorMap tm_xw,
                    const __grid_constant__ CUtensorMap tm_hst, TcRnnArgs a) {
@@ -497,7 +497,8 @@ lstm_fwd_pp_kernel(const __grid_constant__ CUtensorMap tm_h, const __grid_consta
   extern __shared__ uint8_t smem_raw[];
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   uint8_t *gbase = smem_raw + (base - smem_u32(smem_raw));
-  const int H = a.H, B = a.B, T = a.T, nkb = a.nkb, CS = a.CS;
+  // (with rnn_size known at compile time the per-item offsets of the elementwise stores become immediates)
+  const int H = HT ? HT : a.H, B = a.B, T = a.T, nkb = HT ? HT / 64 : a.nkb, CS = HT ? HT / 32 : a.CS;
   const int t0 = a.t0, t1 = a.t1;  // this launch runs steps [t0, t1); t0 is even, so barrier parities follow t
   const uint32_t h_bytes = (uint32_t)nkb * (N2 * 128), xw_bytes = (uint32_t)N2 * 256u, hst_bytes = (uint32_t)N2 * 64u;
   const bool push = a.push != 0;
@@ -1656,6 +1657,9 @@ template <int NCH>
 int launch_fwd_pp(const CUtensorMap &tm_h, const CUtensorMap &tm_xw, const CUtensorMap &tm_act, const TcRnnArgs &a,
                   int nclusters, size_t smem, cudaStream_t st) {
   auto kern = a.debug ? lstm_fwd_pp_kernel<NCH, true> : lstm_fwd_pp_kernel<NCH, false>;
+  if constexpr (NCH == 4) {
+    if (a.H == 512 && !a.debug) kern = lstm_fwd_pp_kernel<NCH, false, 512>;  // the config-4 instance
+  }
   SK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   if (a.CS > 8) SK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
   cudaLaunchConfig_t cfg = {};
