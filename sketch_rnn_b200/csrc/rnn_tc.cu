@@ -905,7 +905,7 @@ lstm_fwd_pp_kernel(const __grid_constant__ CUtensorMap tm_h, const __grid_consta
 // Elementwise items: thread (unit u = e/4, sub = e%4, column group cg) owns the NCH columns
 // c = cg*N/4 + 4*it + sub of unit u (the 4 lanes of a unit touch consecutive rows of the 128B-swizzled
 // staging tiles, i.e. distinct banks).
-template <int NCH, bool DBG>
+template <int NCH, bool DBG, int HT = 0>  // HT: rnn_size as a compile-time constant (0: run time)
 __global__ void __launch_bounds__(TCR_THREADS, 1)
 lstm_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm_acts, const __grid_constant__ CUtensorMap tm_do,
                    const __grid_constant__ CUtensorMap tm_cp, const __grid_constant__ CUtensorMap tm_dp, TcRnnArgs a) {
@@ -914,7 +914,7 @@ lstm_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm_acts, const __grid_con
   extern __shared__ uint8_t smem_raw[];
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   uint8_t *gbase = smem_raw + (base - smem_u32(smem_raw));
-  const int H = a.H, B = a.B, T = a.T, CS = a.CS;
+  const int H = HT ? HT : a.H, B = a.B, T = a.T, CS = HT ? HT / 32 : a.CS;
   const int nmt = (H + 127) / 128;                 // accumulator m-tiles (all hidden units)
   const int HP = nmt * 128;
   const uint32_t s_w = base;                       // 2 k-blocks x [HP rows][128 B]
@@ -1261,7 +1261,7 @@ lstm_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm_acts, const __grid_con
 // The 16 elementwise warps run E_0 E_1 R_0 R_1 P_0 P_1 per step: the product of a half runs while they work on
 // the other half, and the publication round trip of half 0 (fence + remote mbarrier arrivals, done by a
 // publisher warp) hides behind R_1.  No barrier.cluster in the loop.
-template <int NCH, bool DBG>  // NCH items per thread and half tile
+template <int NCH, bool DBG, int HT = 0>  // NCH items per thread and half tile; HT: rnn_size at compile time (0: run time)
 __global__ void __launch_bounds__(TCR_PP_THREADS, 1)
 lstm_bwd_pp_kernel(const __grid_constant__ CUtensorMap tm_acts, const __grid_constant__ CUtensorMap tm_do,
                    const __grid_constant__ CUtensorMap tm_cp, const __grid_constant__ CUtensorMap tm_dp, TcRnnArgs a) {
@@ -1270,7 +1270,7 @@ lstm_bwd_pp_kernel(const __grid_constant__ CUtensorMap tm_acts, const __grid_con
   extern __shared__ uint8_t smem_raw[];
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   uint8_t *gbase = smem_raw + (base - smem_u32(smem_raw));
-  const int H = a.H, B = a.B, T = a.T, CS = a.CS;
+  const int H = HT ? HT : a.H, B = a.B, T = a.T, CS = HT ? HT / 32 : a.CS;
   const int t0 = a.t0, t1 = a.t1;  // this launch differentiates steps t1-1 .. t0
   const int nmt = (H + 127) / 128;
   const int HP = nmt * 128;
@@ -1660,6 +1660,10 @@ int launch_fwd_pp(const CUtensorMap &tm_h, const CUtensorMap &tm_xw, const CUten
   if constexpr (NCH == 4) {
     if (a.H == 512 && !a.debug) kern = lstm_fwd_pp_kernel<NCH, false, 512>;  // the config-4 instance
   }
+  if constexpr (NCH == 1) {  // config 1, and 100-200-row shards of config 4
+    if (a.H == 512 && !a.debug) kern = lstm_fwd_pp_kernel<NCH, false, 512>;
+    if (a.H == 256 && !a.debug) kern = lstm_fwd_pp_kernel<NCH, false, 256>;
+  }
   SK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   if (a.CS > 8) SK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
   cudaLaunchConfig_t cfg = {};
@@ -1678,6 +1682,9 @@ template <int NCH>
 int launch_bwd_pp(const CUtensorMap &tm_acts, const CUtensorMap &tm_do, const CUtensorMap &tm_cp, const CUtensorMap &tm_dp,
                   const TcRnnArgs &a, int nclusters, size_t smem, cudaStream_t st) {
   auto kern = a.debug ? lstm_bwd_pp_kernel<NCH, true> : lstm_bwd_pp_kernel<NCH, false>;
+  if constexpr (NCH == 4) {
+    if (a.H == 512 && !a.debug) kern = lstm_bwd_pp_kernel<NCH, false, 512>;  // the config-4 instance
+  }
   SK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   if (a.CS > 8) SK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
   cudaLaunchConfig_t cfg = {};
@@ -1696,6 +1703,10 @@ template <int NCH>
 int launch_bwd(const CUtensorMap &tm_acts, const CUtensorMap &tm_do, const CUtensorMap &tm_cp, const CUtensorMap &tm_dp,
                const TcRnnArgs &a, int nclusters, size_t smem, cudaStream_t st) {
   auto kern = a.debug ? lstm_bwd_tc_kernel<NCH, true> : lstm_bwd_tc_kernel<NCH, false>;
+  if constexpr (NCH <= 2) {  // the small tiles of config 1 and of multi-GPU shards of config 4
+    if (a.H == 512 && !a.debug) kern = lstm_bwd_tc_kernel<NCH, false, 512>;
+    if (a.H == 256 && !a.debug) kern = lstm_bwd_tc_kernel<NCH, false, 256>;
+  }
   SK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   if (a.CS > 8) SK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
   cudaLaunchConfig_t cfg = {};
