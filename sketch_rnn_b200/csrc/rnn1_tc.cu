@@ -345,7 +345,8 @@ rnn1_fwd_kernel(const __grid_constant__ CUtensorMap tm_hp, const __grid_constant
   constexpr int N = R1_N;
   constexpr int NB1 = CELL == 2 ? 2 : 1;  // rnn: the h tile is double-buffered (see the store ordering below)
   extern __shared__ uint8_t smem_raw[];
-  const int H = a.H, B = a.B, T = a.T, G = a.G;
+  constexpr int H = 64 * NKB, G = (CELL == 1 ? 3 : 1) * H;  // rnn_size is a multiple of 64 here: known at compile time
+  const int B = a.B, T = a.T;
   constexpr int nkb = NKB;
   constexpr int btile = NKB * N * 128;
   const R1Smem s = r1_smem(smem_raw, a.smem_w_bytes, NB1 * btile, CELL == 1 ? btile : 0);
@@ -602,7 +603,8 @@ __global__ void __launch_bounds__(R1_THREADS, 1) rnn1_bwd_kernel(const __grid_co
   constexpr int N = R1_N;
   constexpr int NB1 = CELL == 2 ? 2 : 1;
   extern __shared__ uint8_t smem_raw[];
-  const int H = a.H, B = a.B, T = a.T, G = a.G;
+  constexpr int H = 64 * NKB, G = (CELL == 1 ? 3 : 1) * H;  // rnn_size is a multiple of 64 here: known at compile time
+  const int B = a.B, T = a.T;
   constexpr int nkb = NKB;
   constexpr int btile = NKB * N * 128;
   // b1: d(pre) of the candidate (gru) / of the cell (rnn, two buffers), K = H;  b2 (gru): d(pre) of the gates, K = 2H
