@@ -506,8 +506,6 @@ lstm_fwd_pp_kernel(const __grid_constant__ CUtensorMap tm_h, const __grid_consta
   const uint32_t s_xw = s_h + (push ? 4 : 2) * h_bytes;  // [2] x [N2][32 units][4 gates] bf16: hoisted x*Wx+b
   const uint32_t s_hst = s_xw + 2 * xw_bytes;      // [2] x [N2][32 units] bf16: my units of h_t on their way out (TMA store); push mode: two sets by step parity
   const uint32_t s_bar = s_hst + (push ? 4 : 2) * hst_bytes;
-  // gate exchange scratch (after the barrier block): per elementwise warp two slots of [8 units][20 words]
-  const uint32_t s_xch = s_bar + 256;
   // mbarriers, index s = half tile
   const uint32_t bar_h = s_bar, bar_xw = s_bar + 16, bar_acc = s_bar + 32, bar_epi = s_bar + 48, bar_ready = s_bar + 64;
   const uint32_t tmem_holder = s_bar + 80;
@@ -766,6 +764,7 @@ lstm_fwd_pp_kernel(const __grid_constant__ CUtensorMap tm_h, const __grid_consta
     __syncwarp();
   } else {
     // ---------------- elementwise warps ----------------
+    const bool g_lo = (eg & 1) != 0, g_hi = (eg & 2) != 0;
     uint32_t valid[2] = {0, 0};
 #pragma unroll
     for (int s = 0; s < 2; ++s)
@@ -833,36 +832,17 @@ lstm_fwd_pp_kernel(const __grid_constant__ CUtensorMap tm_h, const __grid_consta
         tc_ldn<CPW>(tmem_acc + ((uint32_t)(32 * q) << 16) + (uint32_t)(s * N2 + cg * CPW), r);
         mbar_wait(bar_xw + 8 * s, t & 1);
         TCR_LAP(tk[2]);
-        // Gate exchange.  Lane (unit, gate g) holds ITS gate for the 4 columns of every item group; the thread that owns
-        // column g of a group needs the four gates of that column: a 4x4 transpose inside each quad of lanes.  Through
-        // shared memory it is 4 stores + one 16-byte load per item; the shuffle form (3 shuffles + 16 selects) was the
-        // largest single block of a pass that is bound by issued instructions.
-        float pg[NCH][4];
-        {
-          float *xs = reinterpret_cast<float *>(gbase + (s_xch - base)) + (warp - 2) * 320 + (lane >> 2) * 20;
-#pragma unroll
-          for (int i0 = 0; i0 < NCH; i0 += 2) {
-#pragma unroll
-            for (int d = 0; d < 2; ++d)
-              if (i0 + d < NCH) {
-#pragma unroll
-                for (int c = 0; c < 4; ++c) xs[d * 160 + c * 4 + eg] = __uint_as_float(r[4 * (i0 + d) + c]);
-              }
-            __syncwarp();
-#pragma unroll
-            for (int d = 0; d < 2; ++d)
-              if (i0 + d < NCH) {
-                const float4 v = *reinterpret_cast<const float4 *>(xs + d * 160 + eg * 4);
-                pg[i0 + d][0] = v.x; pg[i0 + d][1] = v.y; pg[i0 + d][2] = v.z; pg[i0 + d][3] = v.w;
-              }
-            __syncwarp();
-          }
-        }
         auto items = [&](auto full_tag) {  // FULL: every column of the half tile is a real batch row
         constexpr bool FULL = decltype(full_tag)::value;
 #pragma unroll
         for (int it = 0; it < NCH; ++it) {
-          const float p0 = pg[it][0], p1 = pg[it][1], p2 = pg[it][2], p3 = pg[it][3];
+          float v0, v1, v2, v3, p0, p1, p2, p3;
+          perm4(g_lo, g_hi, __uint_as_float(r[4 * it + 0]), __uint_as_float(r[4 * it + 1]), __uint_as_float(r[4 * it + 2]),
+                __uint_as_float(r[4 * it + 3]), v0, v1, v2, v3);
+          v1 = __shfl_xor_sync(0xffffffffu, v1, 1);
+          v2 = __shfl_xor_sync(0xffffffffu, v2, 2);
+          v3 = __shfl_xor_sync(0xffffffffu, v3, 3);
+          perm4(g_lo, g_hi, v0, v1, v2, v3, p0, p1, p2, p3);
           if (FULL || ((valid[s] >> it) & 1u)) {
             const uint2 xv = *reinterpret_cast<const uint2 *>(xw_p + s * xw_bytes + it * 1024);  // bf16 i, j, f, o
             const float ig = sigmoid_approx(p0 + __uint_as_float(xv.x << 16));
@@ -1745,8 +1725,7 @@ int launch_bwd(const CUtensorMap &tm_acts, const CUtensorMap &tm_do, const CUten
 size_t smem_need(bool bwd, int H, int N, bool a_tmem, bool push = false) {
   const int nkb = (H + 63) / 64, HP = (H + 127) / 128 * 128;
   size_t s = bwd ? (a_tmem ? 0 : (size_t)2 * HP * 128) + 2 * (size_t)N * 128 + 4 * (size_t)N * 128 + (push ? (size_t)2 * (H / 32) * 32 * N * 2 : 0)
-                 : (a_tmem ? 0 : (size_t)nkb * 16384) + (size_t)(push ? 2 : 1) * nkb * N * 128 + 2 * (size_t)N * 128 + 2 * (size_t)N * 128 +
-                       (size_t)TCR_EPI_WARPS * 1280 /* gate exchange scratch of the two-half-tile kernel */;
+                 : (a_tmem ? 0 : (size_t)nkb * 16384) + (size_t)(push ? 2 : 1) * nkb * N * 128 + 2 * (size_t)N * 128 + 2 * (size_t)N * 128;
   return s + 1024 + 256;
 }
 
