@@ -471,6 +471,18 @@ __device__ __forceinline__ void st_async_v2(uint32_t dst, uint2 v, uint32_t bar)
   asm volatile("st.async.shared::cluster.mbarrier::complete_tx::bytes.v2.b32 [%0], {%1, %2}, [%3];"
                ::"r"(dst), "r"(v.x), "r"(v.y), "r"(bar) : "memory");
 }
+// tcgen05.ld.16x256b: 16 accumulator rows (lanes base .. base+15 of the warp's quarter) x 8*X columns; thread t gets rows
+// t/4 and t/4 + 8, columns 2*(t%4), 2*(t%4)+1 (+8 per repeat): registers {row a: c0, c1}, {row b: c0, c1}, then the next 8 columns
+__device__ __forceinline__ void tc_ld_16x256b_x2(uint32_t taddr, uint32_t *r) {
+  asm volatile("tcgen05.ld.sync.aligned.16x256b.x2.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]) : "r"(taddr));
+}
+__device__ __forceinline__ void tc_ld_16x256b_x1(uint32_t taddr, uint32_t *r) {
+  asm volatile("tcgen05.ld.sync.aligned.16x256b.x1.b32 {%0, %1, %2, %3}, [%4];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(taddr));
+}
+__device__ __forceinline__ void tc_wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+
 // a partial-sum element group: from L2 (exchange through global memory) or from this CTA's receive buffer (push mode)
 template <typename V>
 __device__ __forceinline__ V ld_part(const V *p, bool local) { return local ? *p : __ldcg(p); }  // `local` is a compile-time constant at the call sites
@@ -533,14 +545,20 @@ lstm_fwd_pp_kernel(const __grid_constant__ CUtensorMap tm_h, const __grid_consta
   const int e = 32 * q + lane;
   const int eu = e >> 2, eg = e & 3;
   const int uo = u0 + eu;
-  const int cb = cg * CPW + eg;  // item `it` of half s is column s*N2 + cb + 4*it of the cluster tile
+  // QUAD (half tiles of 32 and 64 rows): the accumulator rows of a lane quarter are ordered [gate][8 units] (the weight
+  // image is packed that way), so that two tcgen05.ld.16x256b hand a thread the FOUR GATES of its unit for 2 or 4
+  // columns directly -- no exchange between lanes (3 shuffles + 16 selects per item: the largest block of a pass that
+  // is bound by issued instructions).  Thread (unit eu, column pair eg) then owns columns cb + dco(it), cb = first one.
+  constexpr bool QUAD = NCH >= 2;
+  const int cb = QUAD ? cg * CPW + 2 * eg : cg * CPW + eg;
+  auto dco = [](int it) { return QUAD ? 8 * (it >> 1) + (it & 1) : 4 * it; };  // column of item `it` minus cb
   float cst[2][NCH];
   if (warp >= 2 && warp < 2 + TCR_EPI_WARPS) {
 #pragma unroll
     for (int s = 0; s < 2; ++s) {
 #pragma unroll
       for (int it = 0; it < NCH; ++it) {
-        const int b = b0 + s * N2 + cb + 4 * it;
+        const int b = b0 + s * N2 + cb + dco(it);
         cst[s][it] = 0.f;
         if (b < B) {
           if (t0 == 0) {
@@ -770,7 +788,7 @@ lstm_fwd_pp_kernel(const __grid_constant__ CUtensorMap tm_h, const __grid_consta
     for (int s = 0; s < 2; ++s)
 #pragma unroll
       for (int it = 0; it < NCH; ++it)
-        if (b0 + s * N2 + cb + 4 * it < B) valid[s] |= 1u << it;
+        if (b0 + s * N2 + cb + dco(it) < B) valid[s] |= 1u << it;
     uint8_t *xw_gen = gbase + (s_xw - base);
     uint8_t *hst_gen = gbase + (s_hst - base);
     const uint8_t *xw_p = xw_gen + cb * 256 + eu * 8;  // (column cb, unit eu): 4 gates, 8 bytes
@@ -787,7 +805,7 @@ lstm_fwd_pp_kernel(const __grid_constant__ CUtensorMap tm_h, const __grid_consta
     uint32_t eoc_next = 0;  // flags of the half step about to be processed
 #pragma unroll
     for (int it = 0; it < NCH; ++it)
-      if (((valid[0] >> it) & 1u) && __ldg(eoc_p + 4 * it)) eoc_next |= 1u << it;
+      if (((valid[0] >> it) & 1u) && __ldg(eoc_p + dco(it))) eoc_next |= 1u << it;
     uint32_t lapt = 0;
     if (dbg) lapt = (uint32_t)clock();
     for (int t = t0; t < t1; ++t) {
@@ -803,7 +821,7 @@ lstm_fwd_pp_kernel(const __grid_constant__ CUtensorMap tm_h, const __grid_consta
           const unsigned char *ep = eoc_p + s2 * N2 + (s == 1 ? B : 0);
           const bool in_range = s == 0 || more;
 #pragma unroll
-          for (int it = 0; it < NCH; ++it) en[it] = (in_range && ((valid[s2] >> it) & 1u)) ? __ldg(ep + 4 * it) : (unsigned char)0;
+          for (int it = 0; it < NCH; ++it) en[it] = (in_range && ((valid[s2] >> it) & 1u)) ? __ldg(ep + dco(it)) : (unsigned char)0;
         }
         float dsc[NCH];
 #pragma unroll
@@ -813,7 +831,7 @@ lstm_fwd_pp_kernel(const __grid_constant__ CUtensorMap tm_h, const __grid_consta
 #pragma unroll
             for (int it = 0; it < NCH; ++it)
               if ((valid[s] >> it) & 1u)
-                dsc[it] = a.mask[((int64_t)(b0 + s * N2 + cb + 4 * it) * T + t) * H + uo] * inv_keep;
+                dsc[it] = a.mask[((int64_t)(b0 + s * N2 + cb + dco(it)) * T + t) * H + uo] * inv_keep;
           } else {
             // rows past the batch get a scale too (never stored): no per-item predicates around the hash
             const uint32_t pre = skm_drop_prefix(a.seed, drop_unit, (uint32_t)t);  // (unit, t) part of the mask hash
@@ -821,7 +839,7 @@ lstm_fwd_pp_kernel(const __grid_constant__ CUtensorMap tm_h, const __grid_consta
             const float keep = a.keep;
 #pragma unroll
             for (int it = 0; it < NCH; ++it)
-              dsc[it] = skm_u01(skm_drop_finish(pre, row + (uint32_t)(4 * it))) < keep ? inv_keep : 0.0f;
+              dsc[it] = skm_u01(skm_drop_finish(pre, row + (uint32_t)dco(it))) < keep ? inv_keep : 0.0f;
           }
         }
         TCR_LAP(tk[0]);
@@ -829,22 +847,44 @@ lstm_fwd_pp_kernel(const __grid_constant__ CUtensorMap tm_h, const __grid_consta
         TCR_LAP(tk[1]);
         tc_fence_after();
         uint32_t r[CPW];
-        tc_ldn<CPW>(tmem_acc + ((uint32_t)(32 * q) << 16) + (uint32_t)(s * N2 + cg * CPW), r);
+        if constexpr (QUAD) {
+          // rows 32q .. 32q+15 hold gates i, j of the quarter's 8 units, rows 32q+16 .. 32q+31 gates f, o
+          const uint32_t ta = tmem_acc + ((uint32_t)(32 * q) << 16) + (uint32_t)(s * N2 + cg * CPW);
+          if constexpr (CPW == 16) {
+            tc_ld_16x256b_x2(ta, r);
+            tc_ld_16x256b_x2(ta + (16u << 16), r + 8);
+          } else {
+            tc_ld_16x256b_x1(ta, r);
+            tc_ld_16x256b_x1(ta + (16u << 16), r + 4);
+          }
+          tc_wait_ld();
+        } else {
+          tc_ldn<CPW>(tmem_acc + ((uint32_t)(32 * q) << 16) + (uint32_t)(s * N2 + cg * CPW), r);
+        }
         mbar_wait(bar_xw + 8 * s, t & 1);
         TCR_LAP(tk[2]);
         auto items = [&](auto full_tag) {  // FULL: every column of the half tile is a real batch row
         constexpr bool FULL = decltype(full_tag)::value;
 #pragma unroll
         for (int it = 0; it < NCH; ++it) {
-          float v0, v1, v2, v3, p0, p1, p2, p3;
-          perm4(g_lo, g_hi, __uint_as_float(r[4 * it + 0]), __uint_as_float(r[4 * it + 1]), __uint_as_float(r[4 * it + 2]),
-                __uint_as_float(r[4 * it + 3]), v0, v1, v2, v3);
-          v1 = __shfl_xor_sync(0xffffffffu, v1, 1);
-          v2 = __shfl_xor_sync(0xffffffffu, v2, 2);
-          v3 = __shfl_xor_sync(0xffffffffu, v3, 3);
-          perm4(g_lo, g_hi, v0, v1, v2, v3, p0, p1, p2, p3);
+          float p0, p1, p2, p3;
+          if constexpr (QUAD) {
+            // per load: {gate a: c0, c1}, {gate b: c0, c1} (then the same for the columns 8 further on)
+            constexpr int HALF = CPW / 2;  // registers of one load
+            const int j = (it >> 1) * 4 + (it & 1);
+            p0 = __uint_as_float(r[j]); p1 = __uint_as_float(r[j + 2]);
+            p2 = __uint_as_float(r[HALF + j]); p3 = __uint_as_float(r[HALF + j + 2]);
+          } else {
+            float v0, v1, v2, v3;
+            perm4(g_lo, g_hi, __uint_as_float(r[4 * it + 0]), __uint_as_float(r[4 * it + 1]), __uint_as_float(r[4 * it + 2]),
+                  __uint_as_float(r[4 * it + 3]), v0, v1, v2, v3);
+            v1 = __shfl_xor_sync(0xffffffffu, v1, 1);
+            v2 = __shfl_xor_sync(0xffffffffu, v2, 2);
+            v3 = __shfl_xor_sync(0xffffffffu, v3, 3);
+            perm4(g_lo, g_hi, v0, v1, v2, v3, p0, p1, p2, p3);
+          }
           if (FULL || ((valid[s] >> it) & 1u)) {
-            const uint2 xv = *reinterpret_cast<const uint2 *>(xw_p + s * xw_bytes + it * 1024);  // bf16 i, j, f, o
+            const uint2 xv = *reinterpret_cast<const uint2 *>(xw_p + s * xw_bytes + dco(it) * 256);  // bf16 i, j, f, o
             const float ig = sigmoid_approx(p0 + __uint_as_float(xv.x << 16));
             const float jg = tanh_approx(p1 + __uint_as_float(xv.x & 0xffff0000u));
             const float fg = sigmoid_approx(p2 + __uint_as_float(xv.y << 16) + 1.0f);
@@ -855,23 +895,23 @@ lstm_fwd_pp_kernel(const __grid_constant__ CUtensorMap tm_h, const __grid_consta
               uint32_t w1 = *reinterpret_cast<const uint32_t *>(&a23) & 0xffff7fffu;
               if ((eoc_bits >> it) & 1u) w0 |= 0x8000u;
               if (dsc[it] == 0.0f) w1 |= 0x8000u;
-              act_g[s * half_off + (size_t)it * H4] = make_uint2(w0, w1);
+              act_g[s * half_off + (size_t)dco(it) * H] = make_uint2(w0, w1);
             }
             const float c2 = fmaf(cst[s][it], fg, ig * jg);
             const float h2 = tanh_approx(c2) * og;
             float cn = c2, hn = h2;
             if ((eoc_bits >> it) & 1u) {
-              const float *ip = init_p + (size_t)(s * N2 + 4 * it) * S;
+              const float *ip = init_p + (size_t)(s * N2 + dco(it)) * S;
               cn = __ldg(ip); hn = __ldg(ip + H);
             }
             cst[s][it] = cn;
-            const size_t off = s * half_off + (size_t)it * H4;
-            *reinterpret_cast<__nv_bfloat16 *>(hst_p + hst_par + s * hst_bytes + it * 256) = __float2bfloat16_rn(hn);
+            const size_t off = s * half_off + (size_t)dco(it) * H;
+            *reinterpret_cast<__nv_bfloat16 *>(hst_p + hst_par + s * hst_bytes + dco(it) * 64) = __float2bfloat16_rn(hn);
             o_p[off] = __float2bfloat16_rn(h2 * dsc[it]);
             if (more) {
               c_p[off] = cn;
             } else {
-              float *so = a.state_out + (size_t)(b0 + s * N2 + cb + 4 * it) * S + uo;
+              float *so = a.state_out + (size_t)(b0 + s * N2 + cb + dco(it)) * S + uo;
               so[0] = cn; so[H] = hn;
             }
           }
@@ -1616,7 +1656,11 @@ __global__ void pack_tc_image_kernel(int bwd, const float *__restrict__ mat, int
     const int chunk = within >> 3, el = within & 7;
     const int kloc = ((chunk ^ (m & 7)) << 3) + el;  // un-swizzle: logical k within the block
     const int k = kb * 64 + kloc;
-    if (bwd == 3) {  // backward weights for tensor memory: per m-tile plain row-major [128 rows m][128 kk], kk = 4u+g
+    if (bwd == 4) {  // forward weights for tensor memory, rows of a lane quarter ordered [gate][8 units]: row 32q + 8g + ul
+      const int mm = (int)(o / ((int64_t)nkb * 64)), kk2 = (int)(o % ((int64_t)nkb * 64));
+      const int u = 8 * (mm >> 5) + (mm & 7), g = (mm >> 3) & 3;
+      if (kk2 < H) v = mat[(size_t)(I + kk2) * G + g * H + u0 + u];
+    } else if (bwd == 3) {  // backward weights for tensor memory: per m-tile plain row-major [128 rows m][128 kk], kk = 4u+g
       const int mm = (int)(o / 128), kk2 = (int)(o % 128);
       const int u = kk2 >> 2, g = kk2 & 3;
       if (mm < H) v = mat[(size_t)(I + mm) * G + g * H + u0 + u];
@@ -1831,7 +1875,9 @@ int sk_rnn_tc_layer(skrnn_handle *h, cudaStream_t st, bool bwd, int l, int B, in
     SkLaunch scope(h, st, SK_CAT_MISC);
     int64_t total = (int64_t)img_bytes / 2 * CS;
     int blocks = (int)std::min<int64_t>((total + 255) / 256, (int64_t)4 * h->num_sms);
-    pack_tc_image_kernel<<<blocks, 256, 0, st>>>(bwd ? (bwd_atmem ? 3 : 1) : (a_tmem ? 2 : 0), h->params + h->lp[l].w[0], h->lp[l].I, H, CS, nkb, HP,
+    // (forward two-half-tile kernel with half tiles of 32 rows and more: quad row order, see lstm_fwd_pp_kernel)
+    const bool fwd_quad = !bwd && plan.pp && a_tmem && N >= 64;
+    pack_tc_image_kernel<<<blocks, 256, 0, st>>>(bwd ? (bwd_atmem ? 3 : 1) : (a_tmem ? (fwd_quad ? 4 : 2) : 0), h->params + h->lp[l].w[0], h->lp[l].I, H, CS, nkb, HP,
                                                 img_bytes, reinterpret_cast<uint8_t *>(h->ws.wpack));
     SK_CUDA(cudaGetLastError());
   }
