@@ -545,13 +545,15 @@ lstm_fwd_pp_kernel(const __grid_constant__ CUtensorMap tm_h, const __grid_consta
   const int e = 32 * q + lane;
   const int eu = e >> 2, eg = e & 3;
   const int uo = u0 + eu;
-  // QUAD (half tiles of 32 and 64 rows): the accumulator rows of a lane quarter are ordered [gate][8 units] (the weight
-  // image is packed that way), so that two tcgen05.ld.16x256b hand a thread the FOUR GATES of its unit for 2 or 4
-  // columns directly -- no exchange between lanes (3 shuffles + 16 selects per item: the largest block of a pass that
-  // is bound by issued instructions).  Thread (unit eu, column pair eg) then owns columns cb + dco(it), cb = first one.
-  constexpr bool QUAD = NCH >= 2;
-  const int cb = QUAD ? cg * CPW + 2 * eg : cg * CPW + eg;
-  auto dco = [](int it) { return QUAD ? 8 * (it >> 1) + (it & 1) : 4 * it; };  // column of item `it` minus cb
+  // The accumulator rows of a lane quarter are ordered [gate][8 units] (the weight image is packed that way), so that
+  // two tcgen05.ld.16x256b hand a thread the FOUR GATES of its unit for a pair of columns directly -- no exchange
+  // between lanes (3 shuffles + 16 selects per item: it was the largest block of a pass that is bound by issued
+  // instructions).  Thread (unit eu, column pair eg) owns columns cb + dco(it), cb = its first one.  Half tiles of 16
+  // rows have only 4 columns per warp: there the two warps of a column-group pair read the same 8 columns and take
+  // one column of each pair.
+  constexpr bool QUAD = true;
+  const int cb = NCH == 1 ? 8 * (cg >> 1) + 2 * eg + (cg & 1) : cg * CPW + 2 * eg;
+  auto dco = [](int it) { return NCH == 1 ? 0 : 8 * (it >> 1) + (it & 1); };  // column of item `it` minus cb
   float cst[2][NCH];
   if (warp >= 2 && warp < 2 + TCR_EPI_WARPS) {
 #pragma unroll
@@ -846,10 +848,10 @@ lstm_fwd_pp_kernel(const __grid_constant__ CUtensorMap tm_h, const __grid_consta
         mbar_wait(bar_acc + 8 * s, t & 1);
         TCR_LAP(tk[1]);
         tc_fence_after();
-        uint32_t r[CPW];
+        uint32_t r[CPW < 8 ? 8 : CPW];
         if constexpr (QUAD) {
           // rows 32q .. 32q+15 hold gates i, j of the quarter's 8 units, rows 32q+16 .. 32q+31 gates f, o
-          const uint32_t ta = tmem_acc + ((uint32_t)(32 * q) << 16) + (uint32_t)(s * N2 + cg * CPW);
+          const uint32_t ta = tmem_acc + ((uint32_t)(32 * q) << 16) + (uint32_t)(s * N2 + (NCH == 1 ? 8 * (cg >> 1) : cg * CPW));
           if constexpr (CPW == 16) {
             tc_ld_16x256b_x2(ta, r);
             tc_ld_16x256b_x2(ta + (16u << 16), r + 8);
@@ -868,7 +870,11 @@ lstm_fwd_pp_kernel(const __grid_constant__ CUtensorMap tm_h, const __grid_consta
 #pragma unroll
         for (int it = 0; it < NCH; ++it) {
           float p0, p1, p2, p3;
-          if constexpr (QUAD) {
+          if constexpr (QUAD && NCH == 1) {
+            const bool odd = (cg & 1) != 0;  // which column of the pair is mine
+            p0 = __uint_as_float(odd ? r[1] : r[0]); p1 = __uint_as_float(odd ? r[3] : r[2]);
+            p2 = __uint_as_float(odd ? r[5] : r[4]); p3 = __uint_as_float(odd ? r[7] : r[6]);
+          } else if constexpr (QUAD) {
             // per load: {gate a: c0, c1}, {gate b: c0, c1} (then the same for the columns 8 further on)
             constexpr int HALF = CPW / 2;  // registers of one load
             const int j = (it >> 1) * 4 + (it & 1);
@@ -1875,8 +1881,8 @@ int sk_rnn_tc_layer(skrnn_handle *h, cudaStream_t st, bool bwd, int l, int B, in
     SkLaunch scope(h, st, SK_CAT_MISC);
     int64_t total = (int64_t)img_bytes / 2 * CS;
     int blocks = (int)std::min<int64_t>((total + 255) / 256, (int64_t)4 * h->num_sms);
-    // (forward two-half-tile kernel with half tiles of 32 rows and more: quad row order, see lstm_fwd_pp_kernel)
-    const bool fwd_quad = !bwd && plan.pp && a_tmem && N >= 64;
+    // (forward two-half-tile kernel: rows of a lane quarter ordered [gate][8 units], see lstm_fwd_pp_kernel)
+    const bool fwd_quad = !bwd && plan.pp && a_tmem;
     pack_tc_image_kernel<<<blocks, 256, 0, st>>>(bwd ? (bwd_atmem ? 3 : 1) : (a_tmem ? (fwd_quad ? 4 : 2) : 0), h->params + h->lp[l].w[0], h->lp[l].I, H, CS, nkb, HP,
                                                 img_bytes, reinterpret_cast<uint8_t *>(h->ws.wpack));
     SK_CUDA(cudaGetLastError());
