@@ -1307,7 +1307,13 @@ lstm_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm_acts, const __grid_con
 // The 16 elementwise warps run E_0 E_1 R_0 R_1 P_0 P_1 per step: the product of a half runs while they work on
 // the other half, and the publication round trip of half 0 (fence + remote mbarrier arrivals, done by a
 // publisher warp) hides behind R_1.  No barrier.cluster in the loop.
-template <int NCH, bool DBG, int HT = 0>  // NCH items per thread and half tile; HT: rnn_size at compile time (0: run time)
+// V2: the weight operand lives in TENSOR memory (64 columns per m-tile, the A tile of an MMA then costs 32 instead of 48
+// cycles at N = 64); to make room the two half tiles share ONE set of accumulator slots (half 1's m-tile mt is multiplied
+// once half 0's has been read out of the slot).  The 128 KB of shared memory this frees hold a receive buffer per half: once a
+// half's partials are published, the publisher warp fetches this rank's 64 KB slice with ONE bulk copy (async proxy,
+// mbarrier transaction bytes), so the elementwise warps sum from shared memory instead of sitting out an L2 round
+// trip of 16 dependent-latency loads per thread.
+template <int NCH, bool DBG, int HT = 0, bool V2 = false>  // NCH items per thread and half tile; HT: rnn_size at compile time (0: run time)
 __global__ void __launch_bounds__(TCR_PP_THREADS, 1)
 lstm_bwd_pp_kernel(const __grid_constant__ CUtensorMap tm_acts, const __grid_constant__ CUtensorMap tm_do,
                    const __grid_constant__ CUtensorMap tm_cp, const __grid_constant__ CUtensorMap tm_dp, TcRnnArgs a) {
@@ -1321,13 +1327,16 @@ lstm_bwd_pp_kernel(const __grid_constant__ CUtensorMap tm_acts, const __grid_con
   const int nmt = (H + 127) / 128;
   const int HP = nmt * 128;
   const uint32_t half_bytes = (uint32_t)N2 * 768u;  // per half: d(pre) operand 256 B/row, activations 256, d(out) 128, c 128
-  const uint32_t s_w = base;                        // 2 k-blocks x [HP rows][128 B]
-  const uint32_t s_half = s_w + 2u * HP * 128u;
+  const uint32_t s_w = base;                        // 2 k-blocks x [HP rows][128 B]; V2: the two receive buffers instead
+  const uint32_t rx_bytes = (uint32_t)CS * 256u * CPW;  // one half's partials for my 32 units: [src rank][column group][32 units][CPW] bf16
+  const uint32_t s_half = s_w + (V2 ? 2u * rx_bytes : 2u * HP * 128u);
   // offsets inside a half's block
   const uint32_t o_b = 0, o_ac = (uint32_t)N2 * 256u, o_do = (uint32_t)N2 * 512u, o_cp = (uint32_t)N2 * 640u;
   const uint32_t s_bar = s_half + 2 * half_bytes;
   const uint32_t bar_in = s_bar, bar_epi = s_bar + 16, bar_rd = s_bar + 32, bar_ready = s_bar + 48, tmem_holder = s_bar + 64;
   const uint32_t bar_acc = s_bar + 128;  // [2][4]
+  const uint32_t bar_rx = s_bar + 80;    // [2]  V2: my slice of a half's partials has landed in shared memory
+  const uint32_t bar_free = s_bar + 192; // [4]  V2: half 0's m-tile mt has been read out of its accumulator slot
   volatile uint32_t *tmem_holder_ptr = reinterpret_cast<volatile uint32_t *>(gbase + (tmem_holder - base));
   uint8_t *half_gen = gbase + (s_half - base);
 
@@ -1340,7 +1349,8 @@ lstm_bwd_pp_kernel(const __grid_constant__ CUtensorMap tm_acts, const __grid_con
   {
     const uint4 *src = reinterpret_cast<const uint4 *>(a.wimg + (size_t)rank * a.wimg_bytes);
     uint4 *dst = reinterpret_cast<uint4 *>(gbase + (s_w - base));
-    for (int i = tid; i < a.wimg_bytes / 16; i += TCR_PP_THREADS) dst[i] = __ldg(src + i);
+    if constexpr (!V2)
+      for (int i = tid; i < a.wimg_bytes / 16; i += TCR_PP_THREADS) dst[i] = __ldg(src + i);
     // d(pre) operand tiles start as zeros (rows past the batch stay zero)
     for (int s = 0; s < 2; ++s) {
       uint4 *bz = reinterpret_cast<uint4 *>(half_gen + s * half_bytes + o_b);
@@ -1354,6 +1364,8 @@ lstm_bwd_pp_kernel(const __grid_constant__ CUtensorMap tm_acts, const __grid_con
       mbar_init(bar_rd + 8 * s, 32 * TCR_EPI_WARPS);
       mbar_init(bar_ready + 8 * s, CS);
       for (int mt = 0; mt < 4; ++mt) mbar_init(bar_acc + 8 * (4 * s + mt), 1);
+      mbar_init(bar_rx + 8 * s, 1);
+      for (int mt = 0; mt < 4; ++mt) mbar_init(bar_free + 8 * (4 * s + mt), 32 * TCR_EPI_WARPS);
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -1363,6 +1375,28 @@ lstm_bwd_pp_kernel(const __grid_constant__ CUtensorMap tm_acts, const __grid_con
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_acc = *tmem_holder_ptr;
+  const uint32_t tmem_a = tmem_acc + (uint32_t)(4 * N2);  // V2: behind the four accumulator slots
+  if constexpr (V2) {
+    if (warp >= 2 && warp < 6) {  // image: per m-tile plain row-major [128 rows][128 kk] bf16 (pack mode 3)
+      const int qq = warp & 3, ee = 32 * qq + lane;
+      for (int mt = 0; mt < nmt; ++mt) {
+        const uint32_t *src = reinterpret_cast<const uint32_t *>(a.wimg + (size_t)rank * a.wimg_bytes) + ((size_t)mt * 128 + ee) * 64;
+#pragma unroll
+        for (int hb = 0; hb < 2; ++hb) {
+          uint32_t v[32];
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const uint4 x = __ldg(reinterpret_cast<const uint4 *>(src + hb * 32) + j);
+            v[4 * j] = x.x; v[4 * j + 1] = x.y; v[4 * j + 2] = x.z; v[4 * j + 3] = x.w;
+          }
+          tc_st32(tmem_a + ((uint32_t)(32 * qq) << 16) + (uint32_t)(mt * 64 + hb * 32), v);
+        }
+      }
+      tc_fence_before();
+    }
+    __syncthreads();
+    tc_fence_after();
+  }
   cluster_sync_all();
 
   __shared__ long long tk[8];
@@ -1410,14 +1444,28 @@ lstm_bwd_pp_kernel(const __grid_constant__ CUtensorMap tm_acts, const __grid_con
           tc_fence_after();
           const uint32_t sb = s_half + s * half_bytes + o_b;
           for (int mt = 0; mt < nmt; ++mt) {
+            if constexpr (V2) {
+              // the four accumulator slots serve both halves in turn: half 1's m-tile mt goes where half 0's was, once
+              // that has been read out (half 0's next product needs nothing: the elementwise pass that feeds it comes
+              // after half 1's read-out of the step before)
+              if (s == 1) {
+                mbar_wait(bar_free + 8 * mt, step & 1);
+                tc_fence_after();
+              }
+            }
 #pragma unroll
             for (int kb = 0; kb < 2; ++kb) {
               const uint64_t da = make_desc(s_w + (uint32_t)kb * (HP * 128) + (uint32_t)mt * 16384u, 0, 1024);
               const uint64_t db = make_desc(sb + (uint32_t)kb * (N2 * 128), 0, 1024);
 #pragma unroll
-              for (int k = 0; k < 4; ++k)
-                tc_mma_bf16(tmem_acc + (uint32_t)((s * nmt + mt) * N2), da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc,
-                            (kb > 0 || k > 0) ? 1u : 0u);
+              for (int k = 0; k < 4; ++k) {
+                if constexpr (V2)
+                  tc_mma_bf16_ts(tmem_acc + (uint32_t)(mt * N2), tmem_a + (uint32_t)(mt * 64 + kb * 32 + k * 8),
+                                 db + (uint64_t)(2 * k), idesc, (kb > 0 || k > 0) ? 1u : 0u);
+                else
+                  tc_mma_bf16(tmem_acc + (uint32_t)((s * nmt + mt) * N2), da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc,
+                              (kb > 0 || k > 0) ? 1u : 0u);
+              }
             }
             tc_commit(bar_acc + 8 * (4 * s + mt));
           }
@@ -1434,6 +1482,21 @@ lstm_bwd_pp_kernel(const __grid_constant__ CUtensorMap tm_acts, const __grid_con
         // (no gpu-scope fence: the arrivals below are release operations at cluster scope, cumulative over what the wait above observed)
         if (lane < CS) mbar_arrive_remote(bar_ready + 8 * s, (uint32_t)lane);
         __syncwarp();
+        if constexpr (V2) {
+          // every rank has published its partials of (s, t): fetch my 32 units' slice of all of them
+          mbar_wait_cluster(bar_ready + 8 * s, step & 1);
+          if (elect_one()) {
+            fence_proxy_async();  // they were written with ordinary stores; the copy below reads through the async proxy
+            const __nv_bfloat16 *src = a.partial + (size_t)cid * 4 * ((size_t)CS * CS * 128 * CPW) +
+                                       (size_t)(2 * s + (step & 1)) * ((size_t)CS * CS * 128 * CPW) + (size_t)rank * CS * 128 * CPW;
+            mbar_expect_tx(bar_rx + 8 * s, rx_bytes);
+            for (uint32_t off = 0; off < rx_bytes; off += 16384u)
+              asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                           ::"r"(s_w + s * rx_bytes + off), "l"(reinterpret_cast<const char *>(src) + off),
+                             "r"(rx_bytes - off < 16384u ? rx_bytes - off : 16384u), "r"(bar_rx + 8 * s) : "memory");
+          }
+          __syncwarp();
+        }
       }
     }
   } else {
@@ -1541,7 +1604,15 @@ lstm_bwd_pp_kernel(const __grid_constant__ CUtensorMap tm_acts, const __grid_con
           tc_fence_after();
           const int m = mt * 128 + e;
           uint32_t r[CPW];
-          tc_ldn<CPW>(tmem_acc + ((uint32_t)(32 * q) << 16) + (uint32_t)((s * nmt + mt) * N2 + cg * CPW), r);
+          if constexpr (V2) {
+            tc_ldn<CPW>(tmem_acc + ((uint32_t)(32 * q) << 16) + (uint32_t)(mt * N2 + cg * CPW), r);
+            if (s == 0) {  // the slot may take half 1's m-tile now
+              tc_fence_before();
+              mbar_arrive(bar_free + 8 * mt);
+            }
+          } else {
+            tc_ldn<CPW>(tmem_acc + ((uint32_t)(32 * q) << 16) + (uint32_t)((s * nmt + mt) * N2 + cg * CPW), r);
+          }
           if (m < H) {
             __nv_bfloat16 *dst = pb + (((size_t)(m >> 5) * CS + rank) * 4 + cg) * part_blk + lane * CK;
             uint32_t pk[CPW / 2];
@@ -1567,9 +1638,11 @@ lstm_bwd_pp_kernel(const __grid_constant__ CUtensorMap tm_acts, const __grid_con
       // ---- P_s: d(h_{t-1}) of my units = sum over ranks (fixed order) of their partials ----
 #pragma unroll
       for (int s = 0; s < 2; ++s) {
-        mbar_wait_cluster(bar_ready + 8 * s, step & 1);
+        if constexpr (V2) mbar_wait(bar_rx + 8 * s, step & 1);  // (written by the async proxy; the mbarrier orders it)
+        else mbar_wait_cluster(bar_ready + 8 * s, step & 1);
         TCR_LAP(tk[4]);
-        const __nv_bfloat16 *src0 = part_base + (size_t)(2 * s + par) * part_par + (((size_t)rank * CS) * 4 + cg) * part_blk +
+        const __nv_bfloat16 *src0 = (V2 ? reinterpret_cast<const __nv_bfloat16 *>(gbase + (s_w - base) + s * rx_bytes) + (size_t)cg * part_blk
+                                        : part_base + (size_t)(2 * s + par) * part_par + (((size_t)rank * CS) * 4 + cg) * part_blk) +
                                     ((size_t)((esub * NCH) / CK) * 32 + eu) * CK + (esub * NCH) % CK;
 #pragma unroll
         for (int it = 0; it < NCH; ++it) dhc[s][it] = 0.f;
@@ -1579,7 +1652,7 @@ lstm_bwd_pp_kernel(const __grid_constant__ CUtensorMap tm_acts, const __grid_con
             uint2 v[UR];
 #pragma unroll
             for (int j = 0; j < UR; ++j)
-              v[j] = (r0 + j < CS) ? __ldcg(reinterpret_cast<const uint2 *>(src0 + (size_t)(r0 + j) * 4 * part_blk)) : make_uint2(0, 0);
+              v[j] = (r0 + j < CS) ? ld_part(reinterpret_cast<const uint2 *>(src0 + (size_t)(r0 + j) * 4 * part_blk), V2) : make_uint2(0, 0);
 #pragma unroll
             for (int j = 0; j < UR; ++j) {
               const float2 f0 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162 *>(&v[j].x));
@@ -1590,7 +1663,7 @@ lstm_bwd_pp_kernel(const __grid_constant__ CUtensorMap tm_acts, const __grid_con
             unsigned short v[UR];
 #pragma unroll
             for (int j = 0; j < UR; ++j)
-              v[j] = (r0 + j < CS) ? __ldcg(reinterpret_cast<const unsigned short *>(src0 + (size_t)(r0 + j) * 4 * part_blk)) : (unsigned short)0;
+              v[j] = (r0 + j < CS) ? ld_part(reinterpret_cast<const unsigned short *>(src0 + (size_t)(r0 + j) * 4 * part_blk), V2) : (unsigned short)0;
 #pragma unroll
             for (int j = 0; j < UR; ++j) dhc[s][0] += __bfloat162float(__ushort_as_bfloat16(v[j]));
           } else {
@@ -1598,7 +1671,7 @@ lstm_bwd_pp_kernel(const __grid_constant__ CUtensorMap tm_acts, const __grid_con
             uint32_t v[UR];
 #pragma unroll
             for (int j = 0; j < UR; ++j)
-              v[j] = (r0 + j < CS) ? __ldcg(reinterpret_cast<const uint32_t *>(src0 + (size_t)(r0 + j) * 4 * part_blk)) : 0u;
+              v[j] = (r0 + j < CS) ? ld_part(reinterpret_cast<const uint32_t *>(src0 + (size_t)(r0 + j) * 4 * part_blk), V2) : 0u;
 #pragma unroll
             for (int j = 0; j < UR; ++j) {
               const float2 f0 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162 *>(&v[j]));
@@ -1733,7 +1806,7 @@ int launch_bwd_pp(const CUtensorMap &tm_acts, const CUtensorMap &tm_do, const CU
                   const TcRnnArgs &a, int nclusters, size_t smem, cudaStream_t st) {
   auto kern = a.debug ? lstm_bwd_pp_kernel<NCH, true> : lstm_bwd_pp_kernel<NCH, false>;
   if constexpr (NCH == 4) {
-    if (a.H == 512 && !a.debug) kern = lstm_bwd_pp_kernel<NCH, false, 512>;  // the config-4 instance
+    if (a.H == 512 && !a.debug) kern = a.a_tmem ? lstm_bwd_pp_kernel<NCH, false, 512, true> : lstm_bwd_pp_kernel<NCH, false, 512>;  // the config-4 instances
   }
   SK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   if (a.CS > 8) SK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
@@ -1875,7 +1948,13 @@ int sk_rnn_tc_layer(skrnn_handle *h, cudaStream_t st, bool bwd, int l, int B, in
   // single-tile BPTT kernel with a small tile: the weight operand fits in tensor memory next to the accumulators
   static int batm_env = -1;
   if (batm_env < 0) { const char *e = getenv("SKRNN_TC_ATMEM_BWD"); batm_env = (e && e[0] == '0') ? 0 : 1; }
-  const bool bwd_atmem = bwd && !plan.pp && batm_env && ((HP / 128) * N + 31) / 32 * 32 + (HP / 128) * 64 <= 512;
+  const bool bwd_atmem_tc = bwd && !plan.pp && batm_env && ((HP / 128) * N + 31) / 32 * 32 + (HP / 128) * 64 <= 512;
+  // two-half-tile BPTT kernel at config 4's shape: weights in tensor memory, accumulator slots shared by the m-tiles,
+  // partials fetched into shared memory by one bulk copy per half (lstm_bwd_pp_kernel, V2); SKRNN_TC_BWD_V2=0: the older form
+  static int v2_env = -1;
+  if (v2_env < 0) { const char *e = getenv("SKRNN_TC_BWD_V2"); v2_env = (e && e[0] == '0') ? 0 : 1; }
+  const bool bwd_v2 = bwd && plan.pp && v2_env && H == 512 && N == 128;
+  const bool bwd_atmem = bwd_atmem_tc || bwd_v2;
   SK_CHECK((int64_t)img_bytes * CS <= h->ws.wpack_floats * 4, "weight image workspace too small");
   {
     SkLaunch scope(h, st, SK_CAT_MISC);
@@ -1889,7 +1968,7 @@ int sk_rnn_tc_layer(skrnn_handle *h, cudaStream_t st, bool bwd, int l, int B, in
   }
   TcRnnArgs a = {};
   a.B = B; a.T = T; a.H = H; a.G = h->G; a.N = N; a.CS = CS; a.nkb = nkb;
-  int cols = bwd ? (bwd_atmem ? ((HP / 128) * N + 31) / 32 * 32 + (HP / 128) * 64 : (HP / 128) * N)
+  int cols = bwd ? (bwd_v2 ? 512 : bwd_atmem ? ((HP / 128) * N + 31) / 32 * 32 + (HP / 128) * 64 : (HP / 128) * N)
                  : (a_tmem ? (N + 31) / 32 * 32 + nkb * 32 : N);
   a.a_tmem = (a_tmem || bwd_atmem) ? 1 : 0;
   int tc = 32;
