@@ -1429,6 +1429,25 @@ lstm_bwd_pp_kernel(const __grid_constant__ CUtensorMap tm_acts, const __grid_con
             load_in(s, t - 1);
           }
         }
+        if constexpr (V2) {
+          // Between two steps this thread has nothing else to do: as soon as every rank has published a half's
+          // partials, fetch my 32 units' slice of all of them (64 KB, contiguous) into that half's receive buffer.
+          // Half 0's arrives while the elementwise warps still read out half 1.
+          if (t > 0) {
+#pragma unroll
+            for (int s = 0; s < 2; ++s) {
+              mbar_wait_cluster(bar_ready + 8 * s, step & 1);
+              asm volatile("fence.proxy.async.global;" ::: "memory");  // ordinary stores -> read through the async proxy
+              const __nv_bfloat16 *src = a.partial + (size_t)cid * 4 * ((size_t)CS * CS * 128 * CPW) +
+                                         (size_t)(2 * s + (step & 1)) * ((size_t)CS * CS * 128 * CPW) + (size_t)rank * CS * 128 * CPW;
+              mbar_expect_tx(bar_rx + 8 * s, rx_bytes);
+              for (uint32_t off = 0; off < rx_bytes; off += 16384u)
+                asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                             ::"r"(s_w + s * rx_bytes + off), "l"(reinterpret_cast<const char *>(src) + off),
+                               "r"(rx_bytes - off < 16384u ? rx_bytes - off : 16384u), "r"(bar_rx + 8 * s) : "memory");
+            }
+          }
+        }
       }
       tma_store_wait_all();
     }
@@ -1482,21 +1501,6 @@ lstm_bwd_pp_kernel(const __grid_constant__ CUtensorMap tm_acts, const __grid_con
         // (no gpu-scope fence: the arrivals below are release operations at cluster scope, cumulative over what the wait above observed)
         if (lane < CS) mbar_arrive_remote(bar_ready + 8 * s, (uint32_t)lane);
         __syncwarp();
-        if constexpr (V2) {
-          // every rank has published its partials of (s, t): fetch my 32 units' slice of all of them
-          mbar_wait_cluster(bar_ready + 8 * s, step & 1);
-          if (elect_one()) {
-            fence_proxy_async();  // they were written with ordinary stores; the copy below reads through the async proxy
-            const __nv_bfloat16 *src = a.partial + (size_t)cid * 4 * ((size_t)CS * CS * 128 * CPW) +
-                                       (size_t)(2 * s + (step & 1)) * ((size_t)CS * CS * 128 * CPW) + (size_t)rank * CS * 128 * CPW;
-            mbar_expect_tx(bar_rx + 8 * s, rx_bytes);
-            for (uint32_t off = 0; off < rx_bytes; off += 16384u)
-              asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-                           ::"r"(s_w + s * rx_bytes + off), "l"(reinterpret_cast<const char *>(src) + off),
-                             "r"(rx_bytes - off < 16384u ? rx_bytes - off : 16384u), "r"(bar_rx + 8 * s) : "memory");
-          }
-          __syncwarp();
-        }
       }
     }
   } else {
@@ -1806,6 +1810,7 @@ int launch_bwd_pp(const CUtensorMap &tm_acts, const CUtensorMap &tm_do, const CU
                   const TcRnnArgs &a, int nclusters, size_t smem, cudaStream_t st) {
   auto kern = a.debug ? lstm_bwd_pp_kernel<NCH, true> : lstm_bwd_pp_kernel<NCH, false>;
   if constexpr (NCH == 4) {
+    if (a.H == 512 && a.debug && a.a_tmem) kern = lstm_bwd_pp_kernel<NCH, true, 512, true>;
     if (a.H == 512 && !a.debug) kern = a.a_tmem ? lstm_bwd_pp_kernel<NCH, false, 512, true> : lstm_bwd_pp_kernel<NCH, false, 512>;  // the config-4 instances
   }
   SK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
