@@ -142,6 +142,13 @@ def test_config4_full_batch_launch_T300():
     assert not bad, bad
 
 
+def test_config4_full_batch_launch_T300_bptt_v2(monkeypatch):
+    """The same launch with the alternative BPTT kernel instance (weights in tensor memory, accumulator slots shared by
+    the half tiles, partial sums fetched into shared memory by bulk copies): SKRNN_TC_BWD_V2=1."""
+    monkeypatch.setenv("SKRNN_TC_BWD_V2", "1")
+    test_config4_full_batch_launch_T300()
+
+
 def test_bench_loss_check_matches_oracle_slice():
     """bench.py prints `loss_check`: its synthetic batch's first rows through the oracle.  The same helper is
     exercised here on a small shape so a drift between bench inputs and oracle inputs cannot go unnoticed."""
