@@ -848,6 +848,8 @@ lstm_fwd_pp_kernel(const __grid_constant__ CUtensorMap tm_h, const __grid_consta
         mbar_wait(bar_acc + 8 * s, t & 1);
         TCR_LAP(tk[1]);
         tc_fence_after();
+        uint32_t sv_a0[NCH], sv_a1[NCH];
+        float sv_o[NCH], sv_c[NCH], sv_h[NCH];
         uint32_t r[CPW < 8 ? 8 : CPW];
         if constexpr (QUAD) {
           // rows 32q .. 32q+15 hold gates i, j of the quarter's 8 units, rows 32q+16 .. 32q+31 gates f, o
@@ -901,7 +903,7 @@ lstm_fwd_pp_kernel(const __grid_constant__ CUtensorMap tm_h, const __grid_consta
               uint32_t w1 = *reinterpret_cast<const uint32_t *>(&a23) & 0xffff7fffu;
               if ((eoc_bits >> it) & 1u) w0 |= 0x8000u;
               if (dsc[it] == 0.0f) w1 |= 0x8000u;
-              act_g[s * half_off + (size_t)dco(it) * H] = make_uint2(w0, w1);
+              sv_a0[it] = w0; sv_a1[it] = w1;
             }
             const float c2 = fmaf(cst[s][it], fg, ig * jg);
             const float h2 = tanh_approx(c2) * og;
@@ -911,22 +913,32 @@ lstm_fwd_pp_kernel(const __grid_constant__ CUtensorMap tm_h, const __grid_consta
               cn = __ldg(ip); hn = __ldg(ip + H);
             }
             cst[s][it] = cn;
-            const size_t off = s * half_off + (size_t)dco(it) * H;
             *reinterpret_cast<__nv_bfloat16 *>(hst_p + hst_par + s * hst_bytes + dco(it) * 64) = __float2bfloat16_rn(hn);
-            o_p[off] = __float2bfloat16_rn(h2 * dsc[it]);
-            if (more) {
-              c_p[off] = cn;
-            } else {
-              float *so = a.state_out + (size_t)(b0 + s * N2 + cb + dco(it)) * S + uo;
-              so[0] = cn; so[H] = hn;
-            }
+            sv_o[it] = h2 * dsc[it]; sv_c[it] = cn; sv_h[it] = hn;
           }
         }
         };
-        if (b0 + (s + 1) * N2 <= B) items(std::true_type{}); else items(std::false_type{});
+        // the records of the step (activations, output, c) are held back until the pass has been announced: the arrive
+        // below is a release, which otherwise waits for these twelve global stores per thread to drain
+        const bool full_half = b0 + (s + 1) * N2 <= B;
+        if (full_half) items(std::true_type{}); else items(std::false_type{});
         fence_proxy_async_smem();  // h staging tile -> TMA store
         tc_fence_before();         // accumulator reads -> next product of this half
         mbar_arrive(bar_epi + 8 * s);
+#pragma unroll
+        for (int it = 0; it < NCH; ++it) {
+          if (full_half || ((valid[s] >> it) & 1u)) {
+            const size_t off = s * half_off + (size_t)dco(it) * H;
+            act_g[off] = make_uint2(sv_a0[it], sv_a1[it]);
+            o_p[off] = __float2bfloat16_rn(sv_o[it]);
+            if (more) {
+              c_p[off] = sv_c[it];
+            } else {
+              float *so = a.state_out + (size_t)(b0 + s * N2 + cb + dco(it)) * S + uo;
+              so[0] = sv_c[it]; so[H] = sv_h[it];
+            }
+          }
+        }
         eoc_next = 0;
 #pragma unroll
         for (int it = 0; it < NCH; ++it)
