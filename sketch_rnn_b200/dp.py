@@ -81,6 +81,9 @@ def dp_train_step(handle, x_shard, y_shard, state, lr, seed, row0, global_rows, 
     multi = dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1
     if timing is not None:
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        if multi:
+            # line the ranks up first, so that the interval below is the all-reduce and not the wait for the slowest rank
+            dist.all_reduce(torch.zeros(1, device=losses.device), group=group)
         e0.record()
         allreduce_sum_([handle.grads_tensor(), losses], group)
         e1.record()
