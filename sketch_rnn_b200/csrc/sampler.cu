@@ -13,7 +13,11 @@
 //
 // Thread u of a CTA owns hidden unit u of every layer (blockDim >= H), so all gates of a unit
 // meet in one thread and the cell update needs no exchange; the [x ; h] operand of the SB
-// sketches is staged k-major in shared memory and broadcast to all threads.
+// sketches is staged k-major in shared memory and broadcast to all threads.  The weights are the
+// other operand: every thread copies the columns it owns a few k rows ahead into a private ring in
+// shared memory with cp.async (no registers held across the L2 latency, no barrier: a thread only reads
+// what it copied itself).  Matrices with several gate columns per unit are read from a gate-interleaved
+// copy ([k][unit][gate], packed once per call) so that a k row of a thread is one 8- or 16-byte copy.
 #include <stdlib.h>
 
 #include "common.cuh"
@@ -29,6 +33,7 @@ struct SampArgs {
   uint64_t seed;
   int sketch0;
   const float *params;
+  const float *wpk[SK_MAX_LAYERS];  // lstm / gru gate matrix of layer l as [k][unit][gate]
   int64_t w0[SK_MAX_LAYERS], b0[SK_MAX_LAYERS], w1[SK_MAX_LAYERS], b1[SK_MAX_LAYERS];
   int64_t out_w, out_b;
   float *state;           // [n, L, S] zero-initialised
@@ -36,6 +41,92 @@ struct SampArgs {
   int *lengths;           // [n]
   float *mixp;            // [n, steps, NOUT] or null
 };
+
+// ---- weight stream: per-thread cp.async ring ----
+constexpr int SK_KG = 4;     // k rows per copy group
+constexpr int SK_NSLOT = 3;  // groups in the ring: two in flight while one is consumed
+
+template <int BYTES>
+__device__ __forceinline__ void cp_async_n(uint32_t dst, const float *src) {
+  if constexpr (BYTES == 16) asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
+  else asm volatile("cp.async.ca.shared.global [%0], [%1], %2;" ::"r"(dst), "l"(src), "n"(BYTES) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
+// acc[r][g] = sum over k (in order, one fused multiply-add chain per element) of AT[k][r] * w[k][g], where w[k][0..NG)
+// are the NG consecutive floats at wsrc + k * pitch (this thread's columns of row k).  ring: this thread's slice of the
+// ring, element (slot, kk) at ring + ((slot * SK_KG + kk) * NT) * NG floats.
+template <int SB, int SP, int NG>
+__device__ __forceinline__ void stream_dot(const float *__restrict__ wsrc, size_t pitch, int K, const float *__restrict__ AT,
+                                           float *__restrict__ ring, int NT, float (&acc)[SB][NG]) {
+  const uint32_t row_bytes = (uint32_t)(NT * NG * 4), slot_bytes = SK_KG * row_bytes;
+  const uint32_t ring_s = (uint32_t)__cvta_generic_to_shared(ring), ring_e = ring_s + SK_NSLOT * slot_bytes;
+  const int nfull = K / SK_KG, ktail = K - nfull * SK_KG;
+  const size_t gstep = (size_t)SK_KG * pitch;
+  const float *src = wsrc;  // first row of the next group to copy
+  uint32_t si = ring_s;     // its slot
+  int gi = 0;
+  auto issue = [&]() {
+    if (gi < nfull) {
+#pragma unroll
+      for (int kk = 0; kk < SK_KG; ++kk) cp_async_n<4 * NG>(si + kk * row_bytes, src + (size_t)kk * pitch);
+    } else if (gi == nfull) {
+      for (int kk = 0; kk < ktail; ++kk) cp_async_n<4 * NG>(si + kk * row_bytes, src + (size_t)kk * pitch);
+    }
+    cp_async_commit();  // one group per call, empty past the end, so the waits below count uniformly
+    ++gi;
+    src += gstep;
+    si += slot_bytes;
+    if (si == ring_e) si = ring_s;
+  };
+  auto row = [&](const float *rs, const float *at) {
+    float w[NG];
+    if constexpr (NG == 4) {
+      const float4 v = *reinterpret_cast<const float4 *>(rs);
+      w[0] = v.x; w[1] = v.y; w[2] = v.z; w[3] = v.w;
+    } else if constexpr (NG == 2) {
+      const float2 v = *reinterpret_cast<const float2 *>(rs);
+      w[0] = v.x; w[1] = v.y;
+    } else {
+      w[0] = rs[0];
+    }
+#pragma unroll
+    for (int r = 0; r < SB; ++r) {
+      const float av = at[r];
+#pragma unroll
+      for (int g = 0; g < NG; ++g) acc[r][g] = SKM_FMA(av, w[g], acc[r][g]);
+    }
+  };
+#pragma unroll
+  for (int i = 0; i < SK_NSLOT - 1; ++i) issue();
+  const uint32_t row_f = row_bytes / 4, slot_f = slot_bytes / 4;
+  const float *rs = ring, *const ring_end = ring + SK_NSLOT * slot_f;
+  const float *at = AT;
+#pragma unroll 1
+  for (int grp = 0; grp < nfull; ++grp) {
+    issue();
+    cp_async_wait<SK_NSLOT - 1>();
+#pragma unroll
+    for (int kk = 0; kk < SK_KG; ++kk) row(rs + kk * row_f, at + kk * SP);
+    at += SK_KG * SP;
+    rs += slot_f;
+    if (rs == ring_end) rs = ring;
+  }
+  cp_async_wait<0>();
+  for (int kk = 0; kk < ktail; ++kk) row(rs + kk * row_f, at + kk * SP);
+}
+
+// gate matrix [K][NG*H] (TF column order gate*H + unit) -> [K][H][NG]
+__global__ void sample_pack_kernel(const float *__restrict__ src, float *__restrict__ dst, int K, int H, int NG) {
+  const int64_t total = (int64_t)K * H * NG;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int g = (int)(i % NG), u = (int)((i / NG) % H);
+    const int64_t k = i / ((int64_t)NG * H);
+    dst[i] = src[k * NG * H + (int64_t)g * H + u];
+  }
+}
 
 // first index with running (fp64) sum >= u, else -1   (get_pi_idx, model.py:189-197)
 __device__ __forceinline__ int pick_idx(const float *pdf, int n, float u) {
@@ -50,6 +141,7 @@ __device__ __forceinline__ int pick_idx(const float *pdf, int n, float u) {
 
 template <int SB>
 __global__ void __launch_bounds__(512) sample_kernel(SampArgs a) {
+  constexpr int SP = (SB + 3) & ~3;  // row pitch of the k-major operand tiles (16-byte rows)
   extern __shared__ __align__(16) float smem[];
   const int tid = threadIdx.x, NT = blockDim.x;
   const int H = a.H, L = a.L, M = a.M, NOUT = a.NOUT;
@@ -60,12 +152,14 @@ __global__ void __launch_bounds__(512) sample_kernel(SampArgs a) {
   const bool act = tid < H;
   const int u = tid;
 
-  float *AT = smem;                       // [2H rows k][SB]: [x ; h] of the current layer
-  float *nxt = AT + (size_t)2 * H * SB;   // [H][SB]: output of the current layer
-  float *lg = nxt + (size_t)H * SB;       // [SB][NOUT] logits
+  float *AT = smem;                       // [2H rows k][SP]: [x ; h] of the current layer
+  float *nxt = AT + (size_t)2 * H * SP;   // [H][SP]: output of the current layer
+  float *lg = nxt + (size_t)H * SP;       // [SB][NOUT] logits
   float *xin = lg + (size_t)SB * NOUT;    // [SB][5] current input point
   float *pdf = xin + SB * 5;              // [SB][M] scratch for the per-sketch draw
   int *flags = reinterpret_cast<int *>(pdf + (size_t)SB * M);  // [SB] done, [SB] length
+  // weight ring (16-byte aligned; an index into the same array, so that the reads stay shared-memory loads)
+  float *ring = smem + ((3 * H * SP + SB * NOUT + SB * 5 + SB * M + 2 * SB + 3) & ~3);
 
   for (int i = tid; i < SB * 5; i += NT) xin[i] = 0.f;  // first input is all zeros (model.py:205)
   for (int i = tid; i < SB; i += NT) { flags[i] = (i < rows_valid) ? 0 : 1; flags[SB + i] = 0; }
@@ -77,16 +171,16 @@ __global__ void __launch_bounds__(512) sample_kernel(SampArgs a) {
       const int K = I + H;
       // ---- stage [x ; h] ----
       if (l == 0) {
-        for (int i = tid; i < 5 * SB; i += NT) { int k = i / SB, r = i % SB; AT[k * SB + r] = xin[r * 5 + k]; }
+        for (int i = tid; i < 5 * SB; i += NT) { int k = i / SB, r = i % SB; AT[k * SP + r] = xin[r * 5 + k]; }
       } else {
-        for (int i = tid; i < H * SB; i += NT) AT[i] = nxt[i];
+        for (int i = tid; i < H * SP; i += NT) AT[i] = nxt[i];
       }
       __syncthreads();  // nxt fully copied before anyone overwrites it below
       for (int i = tid; i < H * SB; i += NT) {
         int r = i / H, uu = i % H;
         float v = 0.f;
         if (r < rows_valid) v = a.state[((size_t)(sk_base + r) * L + l) * S + hoff + uu];
-        AT[(size_t)(I + uu) * SB + r] = v;
+        AT[(size_t)(I + uu) * SP + r] = v;
       }
       __syncthreads();
       const float *W = a.params + a.w0[l];
@@ -96,23 +190,11 @@ __global__ void __launch_bounds__(512) sample_kernel(SampArgs a) {
           float acc[SB][4];
 #pragma unroll
           for (int r = 0; r < SB; ++r) { acc[r][0] = acc[r][1] = acc[r][2] = acc[r][3] = 0.f; }
-#pragma unroll (SB >= 16 ? 2 : 8)  // weight loads of several k in flight: the chain per accumulator stays sequential
-          for (int k = 0; k < K; ++k) {
-            const float *wr = W + (size_t)k * (4 * H) + u;
-            float w0 = __ldg(wr), w1 = __ldg(wr + H), w2 = __ldg(wr + 2 * H), w3 = __ldg(wr + 3 * H);
-#pragma unroll
-            for (int r = 0; r < SB; ++r) {
-              float av = AT[(size_t)k * SB + r];
-              acc[r][0] = SKM_FMA(av, w0, acc[r][0]);
-              acc[r][1] = SKM_FMA(av, w1, acc[r][1]);
-              acc[r][2] = SKM_FMA(av, w2, acc[r][2]);
-              acc[r][3] = SKM_FMA(av, w3, acc[r][3]);
-            }
-          }
+          stream_dot<SB, SP, 4>(a.wpk[l] + 4 * u, (size_t)4 * H, K, AT, ring + 4 * tid, NT, acc);
           const float bi = bias[u], bj = bias[H + u], bf = bias[2 * H + u], bo = bias[3 * H + u];
 #pragma unroll
           for (int r = 0; r < SB; ++r) {
-            if (r >= rows_valid) { nxt[(size_t)u * SB + r] = 0.f; continue; }
+            if (r >= rows_valid) { nxt[(size_t)u * SP + r] = 0.f; continue; }
             float *st = a.state + ((size_t)(sk_base + r) * L + l) * S;
             float c = st[u];
             float ig = skm_sigmoid(SKM_ADD(acc[r][0], bi));
@@ -121,28 +203,23 @@ __global__ void __launch_bounds__(512) sample_kernel(SampArgs a) {
             float og = skm_sigmoid(SKM_ADD(acc[r][3], bo));
             float c2 = SKM_FMA(c, fg, SKM_MUL(ig, jg));
             float h2 = SKM_MUL(skm_tanh(c2), og);
-            nxt[(size_t)u * SB + r] = h2;
+            nxt[(size_t)u * SP + r] = h2;
             // an eoc input holds the state: initial_state is prev_state (model.py:82-92,215)
             if (!(xin[r * 5 + 3] > 0.f)) { st[u] = c2; st[H + u] = h2; }
           }
         }
       } else if (a.cell == 2) {
         if (act) {
-          float acc[SB];
+          float acc[SB][1];
 #pragma unroll
-          for (int r = 0; r < SB; ++r) acc[r] = 0.f;
-#pragma unroll (SB >= 16 ? 2 : 8)  // weight loads of several k in flight: the chain per accumulator stays sequential
-          for (int k = 0; k < K; ++k) {
-            float w0 = __ldg(W + (size_t)k * H + u);
-#pragma unroll
-            for (int r = 0; r < SB; ++r) acc[r] = SKM_FMA(AT[(size_t)k * SB + r], w0, acc[r]);
-          }
+          for (int r = 0; r < SB; ++r) acc[r][0] = 0.f;
+          stream_dot<SB, SP, 1>(W + u, (size_t)H, K, AT, ring + tid, NT, acc);
           const float bb = bias[u];
 #pragma unroll
           for (int r = 0; r < SB; ++r) {
-            if (r >= rows_valid) { nxt[(size_t)u * SB + r] = 0.f; continue; }
-            float h2 = skm_tanh(SKM_ADD(acc[r], bb));
-            nxt[(size_t)u * SB + r] = h2;
+            if (r >= rows_valid) { nxt[(size_t)u * SP + r] = 0.f; continue; }
+            float h2 = skm_tanh(SKM_ADD(acc[r][0], bb));
+            nxt[(size_t)u * SP + r] = h2;
             if (!(xin[r * 5 + 3] > 0.f)) a.state[((size_t)(sk_base + r) * L + l) * S + u] = h2;
           }
         }
@@ -150,49 +227,36 @@ __global__ void __launch_bounds__(512) sample_kernel(SampArgs a) {
         float az[SB], hold[SB], ar[SB];
         if (act) {  // gates r, u on [x ; h]
 #pragma unroll
-          for (int r = 0; r < SB; ++r) { ar[r] = 0.f; az[r] = 0.f; hold[r] = AT[(size_t)(I + u) * SB + r]; }
-#pragma unroll (SB >= 16 ? 2 : 8)  // weight loads of several k in flight: the chain per accumulator stays sequential
-          for (int k = 0; k < K; ++k) {
-            const float *wr = W + (size_t)k * (2 * H) + u;
-            float w0 = __ldg(wr), w1 = __ldg(wr + H);
+          float g2[SB][2];
 #pragma unroll
-            for (int r = 0; r < SB; ++r) {
-              float av = AT[(size_t)k * SB + r];
-              ar[r] = SKM_FMA(av, w0, ar[r]);
-              az[r] = SKM_FMA(av, w1, az[r]);
-            }
-          }
+          for (int r = 0; r < SB; ++r) { g2[r][0] = 0.f; g2[r][1] = 0.f; hold[r] = AT[(size_t)(I + u) * SP + r]; }
+          stream_dot<SB, SP, 2>(a.wpk[l] + 2 * u, (size_t)2 * H, K, AT, ring + 2 * tid, NT, g2);
           const float br = bias[u], bz = bias[H + u];
 #pragma unroll
           for (int r = 0; r < SB; ++r) {
-            ar[r] = SKM_MUL(skm_sigmoid(SKM_ADD(ar[r], br)), hold[r]);  // r * h
-            az[r] = skm_sigmoid(SKM_ADD(az[r], bz));
+            ar[r] = SKM_MUL(skm_sigmoid(SKM_ADD(g2[r][0], br)), hold[r]);  // r * h
+            az[r] = skm_sigmoid(SKM_ADD(g2[r][1], bz));
           }
         }
         __syncthreads();  // every thread is done reading h from AT
         if (act) {
 #pragma unroll
-          for (int r = 0; r < SB; ++r) AT[(size_t)(I + u) * SB + r] = ar[r];
+          for (int r = 0; r < SB; ++r) AT[(size_t)(I + u) * SP + r] = ar[r];
         }
         __syncthreads();
         if (act) {  // candidate on [x ; r*h]
           const float *Wc = a.params + a.w1[l];
           const float bc = a.params[a.b1[l] + u];
-          float ac[SB];
+          float ac[SB][1];
 #pragma unroll
-          for (int r = 0; r < SB; ++r) ac[r] = 0.f;
-#pragma unroll (SB >= 16 ? 2 : 8)  // weight loads of several k in flight: the chain per accumulator stays sequential
-          for (int k = 0; k < K; ++k) {
-            float w0 = __ldg(Wc + (size_t)k * H + u);
-#pragma unroll
-            for (int r = 0; r < SB; ++r) ac[r] = SKM_FMA(AT[(size_t)k * SB + r], w0, ac[r]);
-          }
+          for (int r = 0; r < SB; ++r) ac[r][0] = 0.f;
+          stream_dot<SB, SP, 1>(Wc + u, (size_t)H, K, AT, ring + tid, NT, ac);
 #pragma unroll
           for (int r = 0; r < SB; ++r) {
-            if (r >= rows_valid) { nxt[(size_t)u * SB + r] = 0.f; continue; }
-            float cand = skm_tanh(SKM_ADD(ac[r], bc));
+            if (r >= rows_valid) { nxt[(size_t)u * SP + r] = 0.f; continue; }
+            float cand = skm_tanh(SKM_ADD(ac[r][0], bc));
             float h2 = SKM_FMA(az[r], hold[r], SKM_MUL(SKM_SUB(1.0f, az[r]), cand));
-            nxt[(size_t)u * SB + r] = h2;
+            nxt[(size_t)u * SP + r] = h2;
             if (!(xin[r * 5 + 3] > 0.f)) a.state[((size_t)(sk_base + r) * L + l) * S + u] = h2;
           }
         }
@@ -203,18 +267,13 @@ __global__ void __launch_bounds__(512) sample_kernel(SampArgs a) {
     {
       const float *Wo = a.params + a.out_w;
       for (int j = tid; j < NOUT; j += NT) {
-        float acc[SB];
+        float acc[SB][1];
 #pragma unroll
-        for (int r = 0; r < SB; ++r) acc[r] = 0.f;
-#pragma unroll (SB >= 16 ? 2 : 8)  // weight loads of several k in flight: the chain per accumulator stays sequential
-        for (int k = 0; k < H; ++k) {
-          float w0 = __ldg(Wo + (size_t)k * NOUT + j);
-#pragma unroll
-          for (int r = 0; r < SB; ++r) acc[r] = SKM_FMA(nxt[(size_t)k * SB + r], w0, acc[r]);
-        }
+        for (int r = 0; r < SB; ++r) acc[r][0] = 0.f;
+        stream_dot<SB, SP, 1>(Wo + j, (size_t)NOUT, H, nxt, ring + tid, NT, acc);
         const float bb = a.params[a.out_b + j];
 #pragma unroll
-        for (int r = 0; r < SB; ++r) lg[(size_t)r * NOUT + j] = SKM_ADD(acc[r], bb);
+        for (int r = 0; r < SB; ++r) lg[(size_t)r * NOUT + j] = SKM_ADD(acc[r][0], bb);
       }
     }
     __syncthreads();
@@ -306,7 +365,10 @@ __global__ void __launch_bounds__(512) sample_kernel(SampArgs a) {
 
 template <int SB>
 int launch_sample(skrnn_handle *h, cudaStream_t st, const SampArgs &a, int threads) {
-  size_t smem = ((size_t)3 * a.H * SB + (size_t)SB * a.NOUT + SB * 5 + (size_t)SB * a.M + 2 * SB) * 4;
+  constexpr int SP = (SB + 3) & ~3;
+  const int ng = a.cell == 0 ? 4 : (a.cell == 1 ? 2 : 1);
+  size_t smem = ((size_t)3 * a.H * SP + (size_t)SB * a.NOUT + SB * 5 + (size_t)SB * a.M + 2 * SB) * 4 + 16 +
+                (size_t)SK_NSLOT * SK_KG * threads * ng * 4;
   SK_CHECK(smem <= 227 * 1024, "sampler needs %zu B of shared memory (rnn_size too large)", smem);
   SK_CUDA(cudaFuncSetAttribute(sample_kernel<SB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   int blocks = (a.n + SB - 1) / SB;
@@ -331,7 +393,12 @@ int sk_sample_f32(skrnn_handle *h, cudaStream_t st, int n, int steps, float temp
     const int r = sk_sample_cluster(h, st, n, steps, temp_mix, temp_pen, stop_if_eoc, uniforms, seed, sketch0, strokes, lengths, mixp);
     if (r >= 0) return r;
   }
-  int64_t need = (int64_t)n * h->L * h->S;
+  // recurrent state [n, L, S], then the gate-interleaved weight copies (lstm, gru gates)
+  const int ng = h->cfg.cell == SKRNN_CELL_LSTM ? 4 : (h->cfg.cell == SKRNN_CELL_GRU ? 2 : 1);
+  const int64_t state_n = ((int64_t)n * h->L * h->S + 63) / 64 * 64;
+  int64_t need = state_n;
+  if (ng > 1)
+    for (int l = 0; l < h->L; ++l) need += ((int64_t)(h->lp[l].I + h->H) * ng * h->H + 63) / 64 * 64;
   if (need > h->samp_state_n) {
     if (h->samp_state) cudaFree(h->samp_state);
     h->samp_state = nullptr;
@@ -339,7 +406,7 @@ int sk_sample_f32(skrnn_handle *h, cudaStream_t st, int n, int steps, float temp
     SK_CUDA(cudaMalloc(&h->samp_state, need * sizeof(float)));
     h->samp_state_n = need;
   }
-  SK_CUDA(cudaMemsetAsync(h->samp_state, 0, need * sizeof(float), st));  // zero_state (model.py:208)
+  SK_CUDA(cudaMemsetAsync(h->samp_state, 0, state_n * sizeof(float), st));  // zero_state (model.py:208)
   SampArgs a = {};
   a.n = n; a.steps = steps; a.H = h->H; a.L = h->L; a.M = h->M; a.NOUT = h->NOUT; a.cell = h->cfg.cell;
   a.temp_mix = temp_mix; a.temp_pen = temp_pen; a.data_scale = h->cfg.data_scale;
@@ -350,10 +417,50 @@ int sk_sample_f32(skrnn_handle *h, cudaStream_t st, int n, int steps, float temp
     a.w0[l] = h->lp[l].w[0]; a.b0[l] = h->lp[l].b[0];
     a.w1[l] = h->lp[l].w[1]; a.b1[l] = h->lp[l].b[1];
   }
+  if (ng > 1) {
+    float *dst = h->samp_state + state_n;
+    for (int l = 0; l < h->L; ++l) {
+      const int K = h->lp[l].I + h->H;
+      SkLaunch scope(h, st, SK_CAT_SAMPLER);
+      sample_pack_kernel<<<2 * h->num_sms, 256, 0, st>>>(h->params + h->lp[l].w[0], dst, K, h->H, ng);
+      SK_CUDA(cudaGetLastError());
+      a.wpk[l] = dst;
+      dst += ((int64_t)K * ng * h->H + 63) / 64 * 64;
+    }
+  }
   a.out_w = h->off_out_w; a.out_b = h->off_out_b;
   a.state = h->samp_state; a.strokes = strokes; a.lengths = lengths; a.mixp = mixp;
   int threads = max(256, (h->H + 31) / 32 * 32);
   if (n <= 2) return launch_sample<1>(h, st, a, threads);
   if (n <= 4 * h->num_sms) return launch_sample<4>(h, st, a, threads);
-  return launch_sample<16>(h, st, a, threads);
+  // Many sketches: 12..16 per CTA, whichever fills the GPU's CTA slots in the fewest (waves x sketches per CTA) --
+  // 8192 sketches on 2 x 148 slots are 1.73 waves of 16 but 1.98 waves of 14.
+  int sb_env = 0;  // read per call: the parity tests walk through the instances
+  { const char *e = getenv("SKRNN_SAMPLE_SB"); sb_env = e ? atoi(e) : 0; }
+  int per_sm = 1;
+  {
+    const int ng = a.cell == 0 ? 4 : (a.cell == 1 ? 2 : 1);
+    const size_t smem16 = ((size_t)3 * a.H * 16 + (size_t)16 * a.NOUT + 16 * 5 + (size_t)16 * a.M + 2 * 16) * 4 + 16 +
+                          (size_t)SK_NSLOT * SK_KG * threads * ng * 4;
+    if (smem16 <= 227 * 1024) {
+      SK_CUDA(cudaFuncSetAttribute(sample_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem16));
+      SK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, sample_kernel<16>, threads, smem16));
+      if (per_sm < 1) per_sm = 1;
+    }
+  }
+  const int64_t slots = (int64_t)per_sm * h->num_sms;
+  int best = 16;
+  int64_t best_cost = INT64_MAX;
+  for (int sb = 16; sb >= 12; --sb) {
+    const int64_t ctas = (n + sb - 1) / sb, cost = (ctas + slots - 1) / slots * sb;
+    if (cost < best_cost) { best_cost = cost; best = sb; }
+  }
+  if (sb_env >= 12 && sb_env <= 16) best = sb_env;
+  switch (best) {
+    case 12: return launch_sample<12>(h, st, a, threads);
+    case 13: return launch_sample<13>(h, st, a, threads);
+    case 14: return launch_sample<14>(h, st, a, threads);
+    case 15: return launch_sample<15>(h, st, a, threads);
+    default: return launch_sample<16>(h, st, a, threads);
+  }
 }

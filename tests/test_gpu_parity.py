@@ -236,6 +236,27 @@ def test_sampler_bit_exact_many_sketches(model, H, n):
     h.close()
 
 
+@pytest.mark.parametrize("sb", [13, 14, 15, 16])
+@pytest.mark.parametrize("model,H", [("lstm", 256), ("gru", 96), ("rnn", 40)])
+def test_sampler_bit_exact_sketches_per_cta(monkeypatch, model, H, sb):
+    """Every sketches-per-CTA instance of the streaming kernel (the library picks the one that fills the CTA slots of
+    the GPU best; SKRNN_SAMPLE_SB pins it), ragged last CTA, rnn_size that is not a multiple of the copy group."""
+    monkeypatch.setenv("SKRNN_SAMPLE_SB", str(sb))
+    cfg = so.Config(model=model, rnn_size=H, num_layers=2, num_mixture=24)
+    params = so.init_params(cfg, seed=13, trained_like=True)
+    h = make_handle(cfg, params)
+    n, steps, temp = 611, 9, 0.7
+    u = np.random.RandomState(6).rand(n, steps, 4).astype(np.float32)
+    strokes, lengths, mixp = h.sample(n, steps, temp, temp, False, uniforms=u, want_params=True)
+    strokes, lengths, mixp = strokes.cpu().numpy(), lengths.cpu().numpy(), mixp.cpu().numpy()
+    for i in [0, sb - 1, sb, 2 * sb + 1, 305, n - sb, n - 1]:
+        ref_s, ref_p = sampler_ref.sample(cfg, params, u[i], steps, temp, temp, False, want_params=True)
+        assert lengths[i] == steps
+        assert np.array_equal(strokes[i].view(np.uint32), ref_s.view(np.uint32)), (model, sb, i)
+        assert np.array_equal(mixp[i].view(np.uint32), ref_p.view(np.uint32)), (model, sb, i)
+    h.close()
+
+
 def test_sampler_against_numpy_transcription():
     """Independent check of the sampler against the NumPy transcription of model.py:187-264."""
     cfg = so.Config(model="lstm", rnn_size=32, num_layers=2, num_mixture=6)
