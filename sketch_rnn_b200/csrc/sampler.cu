@@ -55,6 +55,17 @@ __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commi
 template <int N>
 __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 
+// Two fused multiply-adds per instruction (FFMA2 on sm_100: c.x = fma(a.x, w, c.x), c.y = fma(a.y, w, c.y), each rounded
+// once to nearest like __fmaf_rn; ptxas folds the duplicated w into a scalar operand).  The streaming loop is bound by
+// issue slots, and this halves the slots its arithmetic takes.
+__device__ __forceinline__ void fma2_rn(float2 &c, const float2 a, const float w) {
+  unsigned long long cc = *reinterpret_cast<unsigned long long *>(&c), ww, d;
+  const unsigned long long aa = *reinterpret_cast<const unsigned long long *>(&a);
+  asm("mov.b64 %0, {%1, %1};" : "=l"(ww) : "f"(w));
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(aa), "l"(ww), "l"(cc));
+  c = *reinterpret_cast<float2 *>(&d);
+}
+
 // acc[r][g] = sum over k (in order, one fused multiply-add chain per element) of AT[k][r] * w[k][g], where w[k][0..NG)
 // are the NG consecutive floats at wsrc + k * pitch (this thread's columns of row k).  ring: this thread's slice of the
 // ring, element (slot, kk) at ring + ((slot * SK_KG + kk) * NT) * NG floats.
@@ -63,6 +74,12 @@ __device__ __forceinline__ void stream_dot(const float *__restrict__ wsrc, size_
                                            float *__restrict__ ring, int NT, float (&acc)[SB][NG]) {
   const uint32_t row_bytes = (uint32_t)(NT * NG * 4), slot_bytes = SK_KG * row_bytes;
   const uint32_t ring_s = (uint32_t)__cvta_generic_to_shared(ring), ring_e = ring_s + SK_NSLOT * slot_bytes;
+  constexpr int SBH = (SB + 1) / 2;  // sketches in pairs (SP is a multiple of 4, so an odd SB reads a pad lane)
+  float2 a2[SBH][NG];
+#pragma unroll
+  for (int p = 0; p < SBH; ++p)
+#pragma unroll
+    for (int g = 0; g < NG; ++g) a2[p][g] = make_float2(acc[2 * p][g], 2 * p + 1 < SB ? acc[2 * p + 1][g] : 0.f);
   const int nfull = K / SK_KG, ktail = K - nfull * SK_KG;
   const size_t gstep = (size_t)SK_KG * pitch;
   const float *src = wsrc;  // first row of the next group to copy
@@ -93,10 +110,10 @@ __device__ __forceinline__ void stream_dot(const float *__restrict__ wsrc, size_
       w[0] = rs[0];
     }
 #pragma unroll
-    for (int r = 0; r < SB; ++r) {
-      const float av = at[r];
+    for (int p = 0; p < SBH; ++p) {
+      const float2 av = *reinterpret_cast<const float2 *>(at + 2 * p);
 #pragma unroll
-      for (int g = 0; g < NG; ++g) acc[r][g] = SKM_FMA(av, w[g], acc[r][g]);
+      for (int g = 0; g < NG; ++g) fma2_rn(a2[p][g], av, w[g]);
     }
   };
 #pragma unroll
@@ -116,6 +133,10 @@ __device__ __forceinline__ void stream_dot(const float *__restrict__ wsrc, size_
   }
   cp_async_wait<0>();
   for (int kk = 0; kk < ktail; ++kk) row(rs + kk * row_f, at + kk * SP);
+#pragma unroll
+  for (int r = 0; r < SB; ++r)
+#pragma unroll
+    for (int g = 0; g < NG; ++g) acc[r][g] = (r & 1) ? a2[r >> 1][g].y : a2[r >> 1][g].x;
 }
 
 // gate matrix [K][NG*H] (TF column order gate*H + unit) -> [K][H][NG]
