@@ -197,12 +197,16 @@ __global__ void __launch_bounds__(512) sample_kernel(SampArgs a) {
         for (int i = tid; i < H * SP; i += NT) AT[i] = nxt[i];
       }
       __syncthreads();  // nxt fully copied before anyone overwrites it below
-      for (int i = tid; i < H * SB; i += NT) {
+      for (int i = tid; i < H * SB; i += NT) {  // all of a thread's copies in flight at once
         int r = i / H, uu = i % H;
-        float v = 0.f;
-        if (r < rows_valid) v = a.state[((size_t)(sk_base + r) * L + l) * S + hoff + uu];
-        AT[(size_t)(I + uu) * SP + r] = v;
+        float *dst = AT + (size_t)(I + uu) * SP + r;
+        if (r < rows_valid)
+          cp_async_n<4>((uint32_t)__cvta_generic_to_shared(dst), a.state + ((size_t)(sk_base + r) * L + l) * S + hoff + uu);
+        else
+          *dst = 0.f;
       }
+      cp_async_commit();
+      cp_async_wait<0>();
       __syncthreads();
       const float *W = a.params + a.w0[l];
       const float *bias = a.params + a.b0[l];
@@ -287,94 +291,147 @@ __global__ void __launch_bounds__(512) sample_kernel(SampArgs a) {
     // ---- output projection (model.py:98-99) ----
     {
       const float *Wo = a.params + a.out_w;
-      for (int j = tid; j < NOUT; j += NT) {
-        float acc[SB][1];
+      constexpr int SBA = SB >= 4 ? (((SB / 2) + 1) & ~1) : SB, SBB = SB - SBA;  // sketches of the two thread halves
+      if (SBB > 0 && 2 * NOUT <= NT) {
+        // NOUT < blockDim / 2: the two halves of the CTA take SBA and SBB of the sketches, so that every warp has work
+        const int half = tid >= NT / 2 ? 1 : 0, j = tid - half * (NT / 2);
+        if (j < NOUT) {
+          const float bb = a.params[a.out_b + j];
+          if (half == 0) {
+            float acc[SBA][1];
 #pragma unroll
-        for (int r = 0; r < SB; ++r) acc[r][0] = 0.f;
-        stream_dot<SB, SP, 1>(Wo + j, (size_t)NOUT, H, nxt, ring + tid, NT, acc);
-        const float bb = a.params[a.out_b + j];
+            for (int r = 0; r < SBA; ++r) acc[r][0] = 0.f;
+            stream_dot<SBA, SP, 1>(Wo + j, (size_t)NOUT, H, nxt, ring + tid, NT, acc);
 #pragma unroll
-        for (int r = 0; r < SB; ++r) lg[(size_t)r * NOUT + j] = SKM_ADD(acc[r][0], bb);
+            for (int r = 0; r < SBA; ++r) lg[(size_t)r * NOUT + j] = SKM_ADD(acc[r][0], bb);
+          } else {
+            constexpr int SBB1 = SBB > 0 ? SBB : 1;
+            float acc[SBB1][1];
+#pragma unroll
+            for (int r = 0; r < SBB1; ++r) acc[r][0] = 0.f;
+            stream_dot<SBB1, SP, 1>(Wo + j, (size_t)NOUT, H, nxt + SBA, ring + tid, NT, acc);
+#pragma unroll
+            for (int r = 0; r < SBB1; ++r) lg[(size_t)(SBA + r) * NOUT + j] = SKM_ADD(acc[r][0], bb);
+          }
+        }
+      } else {
+        for (int j = tid; j < NOUT; j += NT) {
+          float acc[SB][1];
+#pragma unroll
+          for (int r = 0; r < SB; ++r) acc[r][0] = 0.f;
+          stream_dot<SB, SP, 1>(Wo + j, (size_t)NOUT, H, nxt, ring + tid, NT, acc);
+          const float bb = a.params[a.out_b + j];
+#pragma unroll
+          for (int r = 0; r < SB; ++r) lg[(size_t)r * NOUT + j] = SKM_ADD(acc[r][0], bb);
+        }
       }
     }
     __syncthreads();
-    // ---- per-sketch draw and feedback (model.py:219-261) ----
-    if (tid < rows_valid && !flags[tid]) {
-      const int r = tid;
-      const int sk = sk_base + r;
-      const float *z = lg + (size_t)r * NOUT;
-      float *p = pdf + (size_t)r * M;
-      float u4[4];
-      if (a.uniforms != nullptr) {
-        const float *up = a.uniforms + ((size_t)sk * a.steps + step) * 4;
-        u4[0] = up[0]; u4[1] = up[1]; u4[2] = up[2]; u4[3] = up[3];
-      } else {
-        uint32_t rr[4];
-        skm_philox4x32((uint32_t)(a.sketch0 + sk), (uint32_t)step, 0u, 0x5a3711eu, (uint32_t)a.seed,
-                       (uint32_t)(a.seed >> 32), rr);
-        for (int q = 0; q < 4; ++q) u4[q] = skm_u01(rr[q]);
-      }
-      // softmax over the M mixture logits (get_mixture_coef, model.py:152-156)
-      float mx = z[3];
-      for (int k = 1; k < M; ++k) mx = fmaxf(mx, z[3 + k]);
-      float sum = 0.f;
-      for (int k = 0; k < M; ++k) { p[k] = skm_exp(SKM_SUB(z[3 + k], mx)); sum = SKM_ADD(sum, p[k]); }
-      float inv = SKM_DIV(1.0f, sum);
-      for (int k = 0; k < M; ++k) p[k] = SKM_MUL(p[k], inv);
-      if (step > 1) {  // temperature only from the third point (model.py:220)
-        float m2 = -INFINITY;
-        for (int k = 0; k < M; ++k) { p[k] = SKM_DIV(skm_log(p[k]), a.temp_mix); m2 = fmaxf(m2, p[k]); }
-        for (int k = 0; k < M; ++k) p[k] = skm_exp(SKM_SUB(p[k], m2));
-      }
-      float s2 = 0.f;
-      for (int k = 0; k < M; ++k) s2 = SKM_ADD(s2, p[k]);
-      for (int k = 0; k < M; ++k) p[k] = SKM_DIV(p[k], s2);
-      int idx = pick_idx(p, M, u4[0]);
-      if (idx < 0) idx = M - 1;  // python negative index (model.py:247)
-      // pen state: plain softmax, the pen temperature is never applied (model.py:228-233)
-      float pm = fmaxf(z[0], fmaxf(z[1], z[2]));
-      float pe[3];
-      pe[0] = skm_exp(SKM_SUB(z[0], pm));
-      pe[1] = skm_exp(SKM_SUB(z[1], pm));
-      pe[2] = skm_exp(SKM_SUB(z[2], pm));
-      float ps = SKM_ADD(SKM_ADD(pe[0], pe[1]), pe[2]);
-      pe[0] = SKM_DIV(pe[0], ps); pe[1] = SKM_DIV(pe[1], ps); pe[2] = SKM_DIV(pe[2], ps);
-      int pen_idx = pick_idx(pe, 3, u4[1]);
-      float eos = 0.f, eoc = 0.f, cont = 0.f;
-      if (pen_idx == 0) eos = 1.f;
-      else if (pen_idx == 1) eoc = 1.f;
-      else cont = 1.f;
-      // bivariate normal of the chosen component (model.py:199-203,247); no temperature
-      float mu1 = z[3 + M + idx], mu2 = z[3 + 2 * M + idx];
-      float sg1 = skm_exp(z[3 + 3 * M + idx]), sg2 = skm_exp(z[3 + 4 * M + idx]);
-      float rho = skm_tanh(z[3 + 5 * M + idx]);
-      float g1, g2;
-      skm_box_muller(u4[2], u4[3], &g1, &g2);
-      float x1 = SKM_FMA(sg1, g1, mu1);
-      float q = SKM_SQRT(SKM_SUB(1.0f, SKM_MUL(rho, rho)));
-      float tt = SKM_FMA(q, g2, SKM_MUL(rho, g1));
-      float x2 = SKM_FMA(sg2, tt, mu2);
-      float *so = a.strokes + ((size_t)sk * a.steps + step) * 5;
-      so[0] = SKM_MUL(x1, a.data_scale);  // model.py:263
-      so[1] = SKM_MUL(x2, a.data_scale);
-      so[2] = eos; so[3] = eoc; so[4] = cont;
-      if (a.mixp != nullptr) {
-        float *mo = a.mixp + ((size_t)sk * a.steps + step) * NOUT;
-        mo[0] = pe[0]; mo[1] = pe[1]; mo[2] = pe[2];
-        for (int k = 0; k < M; ++k) {
-          // the stray `pi_pdf /= temp_pen` of model.py:230 shows up in the returned params
-          mo[3 + k] = (step > 1) ? SKM_DIV(p[k], a.temp_pen) : p[k];
-          mo[3 + M + k] = z[3 + M + k];
-          mo[3 + 2 * M + k] = z[3 + 2 * M + k];
-          mo[3 + 3 * M + k] = skm_exp(z[3 + 3 * M + k]);
-          mo[3 + 4 * M + k] = skm_exp(z[3 + 4 * M + k]);
-          mo[3 + 5 * M + k] = skm_tanh(z[3 + 5 * M + k]);
+    // ---- per-sketch draw and feedback (model.py:219-261): one half warp per sketch.  The 16 lanes share the
+    //      transcendentals of the mixture weights; lane 0 of the half does every sum sequentially, in the order the
+    //      reference sums, and the scalar rest (pen state, the two normals, the chosen component's point) ----
+    {
+      const int r = tid >> 4, hl = tid & 15;
+      const unsigned hmask = 0xffffu << (tid & 16);
+      if (r < rows_valid && !flags[r]) {
+        const int sk = sk_base + r;
+        const float *z = lg + (size_t)r * NOUT;
+        float *p = pdf + (size_t)r * M;
+        // softmax over the M mixture logits (get_mixture_coef, model.py:152-156)
+        float mx = -INFINITY;
+        for (int k = hl; k < M; k += 16) mx = fmaxf(mx, z[3 + k]);
+#pragma unroll
+        for (int o = 8; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(hmask, mx, o, 16));
+        for (int k = hl; k < M; k += 16) p[k] = skm_exp(SKM_SUB(z[3 + k], mx));
+        __syncwarp(hmask);
+        float inv = 0.f;
+        if (hl == 0) {
+          float sum = 0.f;
+          for (int k = 0; k < M; ++k) sum = SKM_ADD(sum, p[k]);
+          inv = SKM_DIV(1.0f, sum);
+        }
+        inv = __shfl_sync(hmask, inv, 0, 16);
+        for (int k = hl; k < M; k += 16) p[k] = SKM_MUL(p[k], inv);
+        if (step > 1) {  // temperature only from the third point (model.py:220)
+          float m2 = -INFINITY;
+          for (int k = hl; k < M; k += 16) {
+            const float v = SKM_DIV(skm_log(p[k]), a.temp_mix);
+            p[k] = v;
+            m2 = fmaxf(m2, v);
+          }
+#pragma unroll
+          for (int o = 8; o > 0; o >>= 1) m2 = fmaxf(m2, __shfl_xor_sync(hmask, m2, o, 16));
+          for (int k = hl; k < M; k += 16) p[k] = skm_exp(SKM_SUB(p[k], m2));
+        }
+        __syncwarp(hmask);
+        float s2 = 0.f;
+        if (hl == 0)
+          for (int k = 0; k < M; ++k) s2 = SKM_ADD(s2, p[k]);
+        s2 = __shfl_sync(hmask, s2, 0, 16);
+        for (int k = hl; k < M; k += 16) p[k] = SKM_DIV(p[k], s2);
+        __syncwarp(hmask);
+        if (a.mixp != nullptr) {
+          float *mo = a.mixp + ((size_t)sk * a.steps + step) * NOUT;
+          for (int k = hl; k < M; k += 16) {
+            // the stray `pi_pdf /= temp_pen` of model.py:230 shows up in the returned params
+            mo[3 + k] = (step > 1) ? SKM_DIV(p[k], a.temp_pen) : p[k];
+            mo[3 + M + k] = z[3 + M + k];
+            mo[3 + 2 * M + k] = z[3 + 2 * M + k];
+            mo[3 + 3 * M + k] = skm_exp(z[3 + 3 * M + k]);
+            mo[3 + 4 * M + k] = skm_exp(z[3 + 4 * M + k]);
+            mo[3 + 5 * M + k] = skm_tanh(z[3 + 5 * M + k]);
+          }
+        }
+        if (hl == 0) {
+          float u4[4];
+          if (a.uniforms != nullptr) {
+            const float *up = a.uniforms + ((size_t)sk * a.steps + step) * 4;
+            u4[0] = up[0]; u4[1] = up[1]; u4[2] = up[2]; u4[3] = up[3];
+          } else {
+            uint32_t rr[4];
+            skm_philox4x32((uint32_t)(a.sketch0 + sk), (uint32_t)step, 0u, 0x5a3711eu, (uint32_t)a.seed,
+                           (uint32_t)(a.seed >> 32), rr);
+            for (int q = 0; q < 4; ++q) u4[q] = skm_u01(rr[q]);
+          }
+          int idx = pick_idx(p, M, u4[0]);
+          if (idx < 0) idx = M - 1;  // python negative index (model.py:247)
+          // pen state: plain softmax, the pen temperature is never applied (model.py:228-233)
+          float pm = fmaxf(z[0], fmaxf(z[1], z[2]));
+          float pe[3];
+          pe[0] = skm_exp(SKM_SUB(z[0], pm));
+          pe[1] = skm_exp(SKM_SUB(z[1], pm));
+          pe[2] = skm_exp(SKM_SUB(z[2], pm));
+          float ps = SKM_ADD(SKM_ADD(pe[0], pe[1]), pe[2]);
+          pe[0] = SKM_DIV(pe[0], ps); pe[1] = SKM_DIV(pe[1], ps); pe[2] = SKM_DIV(pe[2], ps);
+          int pen_idx = pick_idx(pe, 3, u4[1]);
+          float eos = 0.f, eoc = 0.f, cont = 0.f;
+          if (pen_idx == 0) eos = 1.f;
+          else if (pen_idx == 1) eoc = 1.f;
+          else cont = 1.f;
+          // bivariate normal of the chosen component (model.py:199-203,247); no temperature
+          float mu1 = z[3 + M + idx], mu2 = z[3 + 2 * M + idx];
+          float sg1 = skm_exp(z[3 + 3 * M + idx]), sg2 = skm_exp(z[3 + 4 * M + idx]);
+          float rho = skm_tanh(z[3 + 5 * M + idx]);
+          float g1, g2;
+          skm_box_muller(u4[2], u4[3], &g1, &g2);
+          float x1 = SKM_FMA(sg1, g1, mu1);
+          float q = SKM_SQRT(SKM_SUB(1.0f, SKM_MUL(rho, rho)));
+          float tt = SKM_FMA(q, g2, SKM_MUL(rho, g1));
+          float x2 = SKM_FMA(sg2, tt, mu2);
+          float *so = a.strokes + ((size_t)sk * a.steps + step) * 5;
+          so[0] = SKM_MUL(x1, a.data_scale);  // model.py:263
+          so[1] = SKM_MUL(x2, a.data_scale);
+          so[2] = eos; so[3] = eoc; so[4] = cont;
+          if (a.mixp != nullptr) {
+            float *mo = a.mixp + ((size_t)sk * a.steps + step) * NOUT;
+            mo[0] = pe[0]; mo[1] = pe[1]; mo[2] = pe[2];
+          }
+          // feedback (model.py:259-261): nobody reads xin between the barrier above and the next one
+          xin[r * 5 + 0] = x1; xin[r * 5 + 1] = x2; xin[r * 5 + 2] = eos; xin[r * 5 + 3] = eoc; xin[r * 5 + 4] = cont;
+          flags[SB + r] = step + 1;
+          if (a.stop_if_eoc && eoc > 0.f) flags[r] = 1;  // model.py:255-257
         }
       }
-      // feedback (model.py:259-261): nobody reads xin between the barrier above and the next one
-      xin[r * 5 + 0] = x1; xin[r * 5 + 1] = x2; xin[r * 5 + 2] = eos; xin[r * 5 + 3] = eoc; xin[r * 5 + 4] = cont;
-      flags[SB + r] = step + 1;
-      if (a.stop_if_eoc && eoc > 0.f) flags[r] = 1;  // model.py:255-257
     }
     __syncthreads();
     int all_done = 1;
