@@ -20,7 +20,7 @@ def sources():
 
 
 def headers():
-    hs = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".h", ".cuh"))]
+    hs = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".h", ".cuh", ".inl"))]
     hs.append(os.path.join(HERE, "..", "include", "skrnn.h"))
     return hs
 

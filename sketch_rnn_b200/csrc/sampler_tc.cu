@@ -179,6 +179,7 @@ int sk_sample_tc(skrnn_handle *h, cudaStream_t st, int n, int steps, float temp_
   }
   const size_t o_top = take((size_t)n * H * 2), o_lg = take((size_t)n * NOUT * 4);
   const size_t o_xin = take((size_t)n * 5 * 4), o_done = take((size_t)n * 4), o_call = take(sizeof(SampCall));
+  const size_t o_tab = take(((size_t)2 * G + 192) * 32 * 2);  // input-term weight images of the persistent kernel (sampler_tp.cu)
   if (off > h->samp_tc_bytes) {
     if (h->samp_graph) { cudaGraphExecDestroy(h->samp_graph); h->samp_graph = nullptr; }
     SK_CUDA(cudaStreamSynchronize(st));
@@ -218,6 +219,12 @@ int sk_sample_tc(skrnn_handle *h, cudaStream_t st, int n, int steps, float temp_
     samp_pack_kernel<<<4 * h->num_sms, 256, 0, st>>>(h->params + h->lp[l].w[0], h->params + h->lp[l].b[0], h->lp[l].I, H, K[l],
                                                      b.wsm[l], b.bias_il[l]);
     SK_CUDA(cudaGetLastError());
+  }
+  {
+    // rnn_size 256, two layers: every step of every sketch in one persistent kernel (sampler_tp.cu)
+    const int r = sk_sample_tp(h, st, n, steps, temp_mix, temp_pen, stop_if_eoc, uniforms, seed, sketch0, strokes, lengths, mixp,
+                               b.wsm, b.bias_il, b.cst, reinterpret_cast<float *>(base + o_tab));
+    if (r >= 0) return r;
   }
   auto enqueue_steps = [&](cudaStream_t s2) -> int {
     for (int step = 0; step < steps; ++step) {

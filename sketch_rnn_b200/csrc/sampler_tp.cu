@@ -1,0 +1,357 @@
+// sampler_tp.cu -- the throughput sampler as ONE persistent kernel (reference Model.sample, model.py:187-264, many
+// sketches in flight; BASELINE config 5: lstm, rnn_size 256, 2 layers).
+//
+// sampler_tc.cu runs a sampling step as four launches (two gate GEMMs with the cell update as their epilogue, the
+// output projection, the draw), 300 x 4 graph-replayed kernels whose ramp-up and drain cost more than their math.
+// Sketches never interact, so here a CTA owns 64 sketches for ALL steps and nothing but the weights crosses the SM
+// boundary inside the loop:
+//   * the operands h0 / h1 of the CTA's 64 sketches stay in shared memory in the tensor core's K-major 128-byte-swizzled
+//     layout, double-buffered by step parity (the cell update writes step s+1's operand while step s's products may
+//     still read the old one); the cell state c stays in global memory, one row-contiguous slice per thread;
+//   * the weights (bf16, gate-interleaved columns, 1.6 MB for the stack) stream from L2 through a five-stage TMA ring
+//     (16 KB stages), once per step and CTA: they are the B operand, M = 64 sketches x N = 256 gate columns per accumulator;
+//   * warp 0 streams, warp 1 issues tcgen05.mma, eight epilogue warps in two groups (one per accumulator buffer in tensor
+//     memory) run the LSTM cell update straight from tensor memory, and after the output projection the per-sketch draw
+//     (softmax, temperature, categorical draws, bivariate normal) whose point is the next step's input;
+//   * the input point and the bias ride in one extra K = 16 product per accumulator: operand columns (dx, dy, eos, eoc,
+//     cont, 1, 1) against the rows (W_dx, W_dy, W_eos, W_eoc, W_cont, bias rounded to bf16, the rounding's remainder),
+//     so that the epilogue reads nothing but tensor memory and the cell state;
+//   * an eoc input holds the recurrent state (model.py:82-92 with initial_state = prev_state) while the layer output
+//     still feeds the layer above: the new h is always written, and once the products that read it are complete the
+//     held rows are copied back from the other buffer.
+// Same arithmetic contract as sampler_tc.cu (operands rounded to bf16, fp32 accumulation; not the bit-exact path).
+#include <stdlib.h>
+
+#include "common.cuh"
+#include "skrnn_math.h"
+#include "tc_ptx.cuh"
+
+namespace {
+
+constexpr int TP_M = 64;                 // sketches per CTA (accumulator rows)
+constexpr int TP_H = 256, TP_G = 4 * TP_H;
+constexpr int TP_BK = 32;                // K rows per ring stage
+constexpr int TP_STAGES = 5;
+constexpr int TP_CHUNK_BYTES = TP_BK * 128;      // one 64-column chunk of a stage: [32 k rows][128 B]
+constexpr int TP_STAGE_BYTES = 4 * TP_CHUNK_BYTES;  // 16 KB
+constexpr int TP_KBLK_BYTES = TP_M * 128;        // one [64 rows x 64 k] operand block
+constexpr int TP_HBUF_BYTES = 4 * TP_KBLK_BYTES; // 32 KB: h of one layer, one step parity
+constexpr int TP_THREADS = 64 + 256;             // warp 0: TMA, warp 1: MMA, warps 2-9: epilogue
+constexpr int TP_CHUNKS = 9;                     // accumulators per step: 4 + 4 gate chunks, 1 output projection
+constexpr int TP_XROWS = 32;                     // rows of the input-term weight image (7 used; one ring stage)
+constexpr int TP_XO_PITCH = 192;                 // columns of the output projection's bias image
+constexpr int TP_SMEM = 4 * TP_HBUF_BYTES + TP_STAGES * TP_STAGE_BYTES + TP_KBLK_BYTES + 2 * TP_M * 8 + 256 + 1024 /*align*/;
+
+struct TpArgs {
+  int n, steps, M, NOUT, nh;     // nh: columns of the output-projection product (multiple of 64 covering NOUT)
+  float data_scale, temp_mix, temp_pen;
+  int stop_if_eoc, sketch0;
+  uint64_t seed;
+  const float *uniforms;
+  float *strokes, *mixp;
+  int *lengths;
+  float *cst0, *cst1;            // [n, 256] cell states, zero on entry
+  int debug;                     // SKRNN_TP_DEBUG=1: CTA 0 prints where its MMA warp waited
+};
+
+// Input-term weight images [TP_XROWS][1024] (interleaved columns like the operand images of sampler_tc.cu, whose rows
+// 0..4 of wsm[0] are the x rows): rows 0..4 W_x (layer 0 only), row 5 the bias rounded to bf16, row 6 what the rounding
+// dropped, the rest zero.
+__global__ void tp_ximage_kernel(const __nv_bfloat16 *__restrict__ wsm0, const float *__restrict__ bias_il0,
+                                 const float *__restrict__ bias_il1, __nv_bfloat16 *__restrict__ wx0,
+                                 __nv_bfloat16 *__restrict__ wx1, const float *__restrict__ out_b, int NOUT,
+                                 __nv_bfloat16 *__restrict__ wxo) {
+  const int j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= TP_G) return;
+  const __nv_bfloat16 zero = __float2bfloat16_rn(0.f);
+  if (j < TP_XO_PITCH) {  // output projection: bias rows only
+    for (int k = 0; k < TP_XROWS; ++k) wxo[k * TP_XO_PITCH + j] = zero;
+    if (j < NOUT) {
+      const float b = out_b[j];
+      const __nv_bfloat16 hb = __float2bfloat16_rn(b);
+      wxo[5 * TP_XO_PITCH + j] = hb; wxo[6 * TP_XO_PITCH + j] = __float2bfloat16_rn(b - __bfloat162float(hb));
+    }
+  }
+  for (int k = 0; k < TP_XROWS; ++k) { wx0[k * TP_G + j] = zero; wx1[k * TP_G + j] = zero; }
+  for (int k = 0; k < 5; ++k) wx0[k * TP_G + j] = wsm0[k * TP_G + j];
+  const float b0 = bias_il0[j], b1 = bias_il1[j];
+  const __nv_bfloat16 h0 = __float2bfloat16_rn(b0), h1 = __float2bfloat16_rn(b1);
+  wx0[5 * TP_G + j] = h0; wx0[6 * TP_G + j] = __float2bfloat16_rn(b0 - __bfloat162float(h0));
+  wx1[5 * TP_G + j] = h1; wx1[6 * TP_G + j] = __float2bfloat16_rn(b1 - __bfloat162float(h1));
+}
+
+// tcgen05.ld of 32 columns without the wait, and the wait that also ties the destination registers to itself (the
+// compiler must not consume them earlier: it cannot see that the load completes asynchronously)
+__device__ __forceinline__ void tp_ld32_issue(uint32_t taddr, uint32_t (&r)[32]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+        "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]),
+        "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]),
+        "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+      : "r"(taddr));
+}
+__device__ __forceinline__ void tp_ld_wait(uint32_t (&r)[32]) {
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+  asm volatile("" : "+r"(r[0]), "+r"(r[1]), "+r"(r[2]), "+r"(r[3]), "+r"(r[4]), "+r"(r[5]), "+r"(r[6]), "+r"(r[7]),
+                    "+r"(r[8]), "+r"(r[9]), "+r"(r[10]), "+r"(r[11]), "+r"(r[12]), "+r"(r[13]), "+r"(r[14]), "+r"(r[15]));
+  asm volatile("" : "+r"(r[16]), "+r"(r[17]), "+r"(r[18]), "+r"(r[19]), "+r"(r[20]), "+r"(r[21]), "+r"(r[22]), "+r"(r[23]),
+                    "+r"(r[24]), "+r"(r[25]), "+r"(r[26]), "+r"(r[27]), "+r"(r[28]), "+r"(r[29]), "+r"(r[30]), "+r"(r[31]));
+}
+
+// LSTM cell update of 8 units of one sketch row: v = the 32 accumulator columns (4 gates per unit, i j f o; bias and
+// input term included by the products).  Writes c' into cn and returns h' packed.
+__device__ __forceinline__ uint4 tp_cell8(const uint32_t (&v)[32], const float (&cin)[8], float (&cn)[8]) {
+  uint32_t hb[4];
+#pragma unroll
+  for (int j = 0; j < 8; j += 2) {
+    float hh[2];
+#pragma unroll
+    for (int e = 0; e < 2; ++e) {
+      const int u = j + e;
+      const float ig = sigmoid_approx(__uint_as_float(v[4 * u + 0]));
+      const float jg = tanh_approx(__uint_as_float(v[4 * u + 1]));
+      const float fg = sigmoid_approx(__uint_as_float(v[4 * u + 2]) + 1.0f);
+      const float og = sigmoid_approx(__uint_as_float(v[4 * u + 3]));
+      cn[u] = fmaf(cin[u], fg, ig * jg);
+      hh[e] = tanh_approx(cn[u]) * og;
+    }
+    const __nv_bfloat162 hv = __floats2bfloat162_rn(hh[0], hh[1]);
+    hb[j >> 1] = *reinterpret_cast<const uint32_t *>(&hv);
+  }
+  return make_uint4(hb[0], hb[1], hb[2], hb[3]);
+}
+
+__global__ void __launch_bounds__(TP_THREADS, 1)
+sample_tp_kernel(const __grid_constant__ CUtensorMap tmW0, const __grid_constant__ CUtensorMap tmW1,
+                 const __grid_constant__ CUtensorMap tmWo, const __grid_constant__ CUtensorMap tmX0,
+                 const __grid_constant__ CUtensorMap tmX1, const __grid_constant__ CUtensorMap tmXo, const TpArgs a) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  uint8_t *gen = smem_raw + (base - smem_u32(smem_raw));
+  // H0[parity], H1[parity]: operand blocks; ring; xa: input-point operand block (the K = 16 slice `parity` of each row);
+  // xs[parity][row] = {unused, pen | done << 8}; barriers
+  const uint32_t s_h0 = base, s_h1 = base + 2 * TP_HBUF_BYTES;
+  const uint32_t s_ring = base + 4 * TP_HBUF_BYTES;
+  const uint32_t s_xa = s_ring + TP_STAGES * TP_STAGE_BYTES;
+  const uint32_t s_xs = s_xa + TP_KBLK_BYTES;
+  const uint32_t bars = s_xs + 2 * TP_M * 8;
+  const uint32_t bar_full = bars, bar_empty = bars + 8 * TP_STAGES;       // ring (5 + 5)
+  const uint32_t bar_tfull = bars + 80, bar_tempty = bars + 96;             // accumulator buffers
+  const uint32_t bar_h0 = bars + 112, bar_h1 = bars + 144;                  // new h k-blocks written (4 each)
+  const uint32_t bar_s0 = bars + 176, bar_s1 = bars + 184, bar_x = bars + 192;  // state final for the next step; next input
+  const uint32_t tmem_holder = bars + 200;
+  uint8_t *h0_gen = gen, *h1_gen = gen + 2 * TP_HBUF_BYTES, *xa_gen = gen + (s_xa - base);
+  uint2 *xs_gen = reinterpret_cast<uint2 *>(gen + (s_xs - base));
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int row0 = blockIdx.x * TP_M;
+  const int steps = a.steps;
+
+  for (int i = threadIdx.x; i < 4 * TP_HBUF_BYTES / 16; i += TP_THREADS) reinterpret_cast<uint4 *>(gen)[i] = make_uint4(0, 0, 0, 0);
+  for (int i = threadIdx.x; i < TP_KBLK_BYTES / 16; i += TP_THREADS) reinterpret_cast<uint4 *>(xa_gen)[i] = make_uint4(0, 0, 0, 0);
+  if (threadIdx.x < 2 * TP_M) xs_gen[threadIdx.x] = make_uint2(0u, 3u);  // first input: zeros (model.py:205)
+  __syncthreads();
+  if (threadIdx.x < TP_M) {  // the two bias columns of the input operand are constant ones, in both parity slices
+    const int r = threadIdx.x;
+    const uint4 ones = make_uint4(0u, 0u, 0x3f800000u, 0x00003f80u);  // bf16 columns 5 and 6 = 1.0
+#pragma unroll
+    for (int par = 0; par < 2; ++par) *reinterpret_cast<uint4 *>(xa_gen + r * 128 + (((2 * par) ^ (r & 7)) << 4)) = ones;
+  }
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < TP_STAGES; ++s) { mbar_init(bar_full + 8 * s, 1); mbar_init(bar_empty + 8 * s, 1); }
+    for (int b = 0; b < 2; ++b) { mbar_init(bar_tfull + 8 * b, 1); mbar_init(bar_tempty + 8 * b, 8); }
+    for (int k = 0; k < 4; ++k) { mbar_init(bar_h0 + 8 * k, 8); mbar_init(bar_h1 + 8 * k, 8); }
+    mbar_init(bar_s0, 4); mbar_init(bar_s1, 4); mbar_init(bar_x, 4);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmW0)) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmW1)) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmWo)) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmX0)) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmX1)) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmXo)) : "memory");
+  }
+  if (warp == 1) tc_alloc(tmem_holder, 512);
+  fence_proxy_async_smem();  // the zeroed operand blocks are read by the tensor core
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = *reinterpret_cast<volatile uint32_t *>(gen + (tmem_holder - base));
+  const int nhb = a.nh / 64;  // 64-column boxes of the output projection
+
+  if (warp == 0) {
+    // ---- weight stream: the same sequence of stages every step, as far ahead as the ring allows ----
+    if (elect_one()) {
+      int it = 0;
+      auto stage = [&](const CUtensorMap *tm, int n0, int k0, int boxes) {
+        const int s = it % TP_STAGES, ph = (it / TP_STAGES) & 1;
+        mbar_wait(bar_empty + 8 * s, ph ^ 1);
+        const uint32_t sb = s_ring + s * TP_STAGE_BYTES;
+        mbar_expect_tx(bar_full + 8 * s, boxes * TP_CHUNK_BYTES);
+        for (int c = 0; c < boxes; ++c) tma_load_2d(sb + c * TP_CHUNK_BYTES, tm, bar_full + 8 * s, n0 + 64 * c, k0);
+        ++it;
+      };
+      for (int step = 0; step < steps; ++step) {
+        // layer 0 (h0 rows of W0 start at row 8; rows 0..7 are the x rows and padding): chunks 0 and 1 take their input-term
+        // stages last, chunks 2 and 3 first -- the order the MMA warp consumes them in
+        for (int c = 0; c < 2; ++c)
+          for (int j = 0; j < 8; ++j) stage(&tmW0, 256 * c, 8 + TP_BK * j, 4);
+        stage(&tmX0, 0, 0, 4);
+        stage(&tmX0, 256, 0, 4);
+        for (int c = 2; c < 4; ++c) {
+          stage(&tmX0, 256 * c, 0, 4);
+          for (int j = 0; j < 8; ++j) stage(&tmW0, 256 * c, 8 + TP_BK * j, 4);
+        }
+        for (int c = 0; c < 4; ++c) {
+          for (int j = 0; j < 16; ++j) stage(&tmW1, 256 * c, j < 8 ? TP_H + TP_BK * j : TP_BK * (j - 8), 4);  // h1 rows, then input rows
+          stage(&tmX1, 256 * c, 0, 4);
+        }
+        for (int j = 0; j < 8; ++j) stage(&tmWo, 0, TP_BK * j, nhb);
+        stage(&tmXo, 0, 0, nhb);
+      }
+    }
+  } else if (warp == 1) {
+    // ---- products ----
+    if (elect_one()) {
+      const uint32_t idesc = make_idesc_bf16(TP_M, 256, false, true);
+      const uint32_t idesc_o = make_idesc_bf16(TP_M, a.nh, false, true);
+      int it = 0;
+      uint32_t g = 0;
+      long long tw[4] = {0, 0, 0, 0};  // cycles waited for: ring stage, accumulator buffer, new h / state, input point
+      const long long t_begin = clock64();
+#define TP_TIMED(slot, stmt) do { const long long t0_ = clock64(); stmt; tw[slot] += clock64() - t0_; } while (0)
+      // one ring stage against the operand bytes at a_addr: nk products of K = 16
+      auto kstage = [&](uint32_t acc, uint32_t a_addr, uint32_t id, bool first, int nk) {
+        const int s = it % TP_STAGES, ph = (it / TP_STAGES) & 1;
+        TP_TIMED(0, mbar_wait(bar_full + 8 * s, ph));
+        tc_fence_after();
+        const uint64_t da = make_desc(a_addr, 0, 1024), db = make_desc(s_ring + s * TP_STAGE_BYTES, TP_CHUNK_BYTES, 1024);
+        for (int k = 0; k < nk; ++k)
+          tc_mma_bf16(acc, da + (uint64_t)((32 * k) >> 4), db + (uint64_t)((2048 * k) >> 4), id, (!first || k > 0) ? 1u : 0u);
+        tc_commit(bar_empty + 8 * s);
+        ++it;
+      };
+      auto acc_begin = [&]() -> uint32_t {
+        const uint32_t buf = g & 1;
+        TP_TIMED(1, mbar_wait(bar_tempty + 8 * buf, ((g >> 1) & 1) ^ 1));
+        tc_fence_after();
+        return tmem + buf * 256;
+      };
+      auto acc_end = [&]() { tc_commit(bar_tfull + 8 * (g & 1)); ++g; };
+      for (int step = 0; step < steps; ++step) {
+        const uint32_t p = step & 1, prev = (step - 1) & 1;
+        const uint32_t h0s = s_h0 + p * TP_HBUF_BYTES, h0n = s_h0 + (p ^ 1) * TP_HBUF_BYTES;
+        const uint32_t h1s = s_h1 + p * TP_HBUF_BYTES, h1n = s_h1 + (p ^ 1) * TP_HBUF_BYTES;
+        const uint32_t xa = s_xa + p * 32;  // this step's K = 16 slice of the input operand
+        if (step > 0) { TP_TIMED(2, mbar_wait(bar_s0, prev)); tc_fence_after(); }
+        {
+          // chunks 0 and 1: both accumulators take their h0 stages first, then -- once the point drawn at the previous step
+          // is known -- their input-term stage (so that the draw overlaps two chunks of products)
+          const uint32_t accA = acc_begin();
+          for (int j = 0; j < 8; ++j) kstage(accA, h0s + (j >> 1) * TP_KBLK_BYTES + (j & 1) * 64, idesc, j == 0, 2);
+          const uint32_t bufA = g & 1, bufB = bufA ^ 1;
+          TP_TIMED(1, mbar_wait(bar_tempty + 8 * bufB, (((g + 1) >> 1) & 1) ^ 1));
+          tc_fence_after();
+          const uint32_t accB = tmem + bufB * 256;
+          for (int j = 0; j < 8; ++j) kstage(accB, h0s + (j >> 1) * TP_KBLK_BYTES + (j & 1) * 64, idesc, j == 0, 2);
+          if (step > 0) { TP_TIMED(3, mbar_wait(bar_x, prev)); tc_fence_after(); }
+          kstage(accA, xa, idesc, false, 1);
+          tc_commit(bar_tfull + 8 * bufA);
+          kstage(accB, xa, idesc, false, 1);
+          tc_commit(bar_tfull + 8 * bufB);
+          g += 2;
+        }
+        for (int c = 2; c < 4; ++c) {
+          const uint32_t acc = acc_begin();
+          kstage(acc, xa, idesc, true, 1);
+          for (int j = 0; j < 8; ++j) kstage(acc, h0s + (j >> 1) * TP_KBLK_BYTES + (j & 1) * 64, idesc, false, 2);
+          acc_end();
+        }
+        if (step > 0) { TP_TIMED(2, mbar_wait(bar_s1, prev)); tc_fence_after(); }
+        for (int c = 0; c < 4; ++c) {
+          const uint32_t acc = acc_begin();
+          for (int j = 0; j < 16; ++j) {
+            if (j < 8) {
+              kstage(acc, h1s + (j >> 1) * TP_KBLK_BYTES + (j & 1) * 64, idesc, j == 0, 2);
+            } else {
+              const int kb = (j - 8) >> 1;
+              if (c == 0 && (j & 1) == 0) { TP_TIMED(2, mbar_wait(bar_h0 + 8 * kb, p)); tc_fence_after(); }
+              kstage(acc, h0n + kb * TP_KBLK_BYTES + (j & 1) * 64, idesc, false, 2);
+            }
+          }
+          kstage(acc, xa, idesc, false, 1);
+          acc_end();
+        }
+        {
+          const uint32_t acc = acc_begin();
+          for (int j = 0; j < 8; ++j) {
+            if ((j & 1) == 0) { TP_TIMED(2, mbar_wait(bar_h1 + 8 * (j >> 1), p)); tc_fence_after(); }
+            kstage(acc, h1n + (j >> 1) * TP_KBLK_BYTES + (j & 1) * 64, idesc_o, j == 0, 2);
+          }
+          kstage(acc, xa, idesc_o, false, 1);  // + output bias
+          acc_end();
+        }
+      }
+#undef TP_TIMED
+      if (a.debug && blockIdx.x == 0)
+        printf("sample_tp: %lld cycles per step; MMA warp waited for ring %lld, accumulator %lld, h/state %lld, input %lld\n",
+               (clock64() - t_begin) / steps, tw[0] / steps, tw[1] / steps, tw[2] / steps, tw[3] / steps);
+    }
+  } else {
+#include "sampler_tp_epi.inl"
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tc_dealloc(tmem, 512);
+}
+
+}  // namespace
+
+// 0: drawn here; -1: not eligible (sampler_tc.cu continues with its step-by-step path); > 0: error.
+// wsm / bias_il / cst: the packed operand images and zeroed cell states sampler_tc.cu has just prepared;
+// tables: (2 * 1024 + 192) * 32 bf16 of scratch for the input-term / bias weight images.
+int sk_sample_tp(skrnn_handle *h, cudaStream_t st, int n, int steps, float temp_mix, float temp_pen, int stop_if_eoc,
+                 const float *uniforms, uint64_t seed, int sketch0, float *strokes, int *lengths, float *mixp,
+                 const __nv_bfloat16 *const *wsm, const float *const *bias_il, float *const *cst, float *tables) {
+  {
+    const char *e = getenv("SKRNN_SAMPLE_TP");
+    if (e && e[0] == '0') return -1;
+  }
+  if (h->cfg.cell != SKRNN_CELL_LSTM || h->H != TP_H || h->L != 2 || h->M > 32 || h->NOUT > 192 || n < TP_M) return -1;
+  CUtensorMap tmW0, tmW1, tmWo, tmX0, tmX1, tmXo;
+  __nv_bfloat16 *wx0 = reinterpret_cast<__nv_bfloat16 *>(tables), *wx1 = wx0 + (size_t)TP_XROWS * TP_G;
+  __nv_bfloat16 *wxo = wx1 + (size_t)TP_XROWS * TP_G;
+  {
+    uint64_t dims[2] = {(uint64_t)TP_G, (uint64_t)(8 + TP_H)}, str[1] = {(uint64_t)TP_G * 2};
+    uint32_t box[2] = {64, (uint32_t)TP_BK};
+    SK_TRY(sk_make_tmap(&tmW0, 2, wsm[0], 2, dims, str, box));
+    dims[1] = 2 * TP_H;
+    SK_TRY(sk_make_tmap(&tmW1, 2, wsm[1], 2, dims, str, box));
+    dims[1] = TP_XROWS;
+    SK_TRY(sk_make_tmap(&tmX0, 2, wx0, 2, dims, str, box));
+    SK_TRY(sk_make_tmap(&tmX1, 2, wx1, 2, dims, str, box));
+    uint64_t dimo[2] = {(uint64_t)h->NOUTP, (uint64_t)TP_H}, stro[1] = {(uint64_t)h->NOUTP * 2};
+    SK_TRY(sk_make_tmap(&tmWo, 2, h->params_bf + h->pbf_out_w, 2, dimo, stro, box));
+    uint64_t dimx[2] = {(uint64_t)TP_XO_PITCH, (uint64_t)TP_XROWS}, strx[1] = {(uint64_t)TP_XO_PITCH * 2};
+    SK_TRY(sk_make_tmap(&tmXo, 2, wxo, 2, dimx, strx, box));
+  }
+  TpArgs a = {};
+  a.n = n; a.steps = steps; a.M = h->M; a.NOUT = h->NOUT; a.nh = (h->NOUT + 63) / 64 * 64;
+  a.data_scale = h->cfg.data_scale; a.temp_mix = temp_mix; a.temp_pen = temp_pen;
+  a.stop_if_eoc = stop_if_eoc; a.sketch0 = sketch0; a.seed = seed; a.uniforms = uniforms;
+  a.strokes = strokes; a.mixp = mixp; a.lengths = lengths;
+  a.cst0 = cst[0]; a.cst1 = cst[1];
+  { const char *e = getenv("SKRNN_TP_DEBUG"); a.debug = (e && e[0] == '1') ? 1 : 0; }
+  {
+    SkLaunch scope(h, st, SK_CAT_SAMPLER);
+    tp_ximage_kernel<<<TP_G / 256, 256, 0, st>>>(wsm[0], bias_il[0], bias_il[1], wx0, wx1, h->params + h->off_out_b, h->NOUT, wxo);
+    SK_CUDA(cudaGetLastError());
+  }
+  SK_CUDA(cudaFuncSetAttribute(sample_tp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TP_SMEM));
+  SkLaunch scope(h, st, SK_CAT_SAMPLER);
+  sample_tp_kernel<<<(n + TP_M - 1) / TP_M, TP_THREADS, TP_SMEM, st>>>(tmW0, tmW1, tmWo, tmX0, tmX1, tmXo, a);
+  SK_CUDA(cudaGetLastError());
+  return 0;
+}

@@ -1,0 +1,239 @@
+    // ---- epilogue warps of sample_tp_kernel (included into its body) ----
+    // Both groups (warps 2-5 / 6-9) work on every accumulator of the sequence [4 chunks of layer 0][4 chunks of layer 1]
+    // [output projection] per step: a chunk's 64 units are split between them (the step is a chain of dependent
+    // chunks, so a chunk's latency counts, not only the warps' throughput).  An M = 64 accumulator keeps row 16q + i in
+    // lane i (< 16) of lane quarter q; the upper 16 lanes of a warp only take part in the collective loads.
+    const int e = (warp - 2) >> 2;
+    const int q = warp & 3;
+    const bool active = lane < 16;
+    const int r = 16 * q + (lane & 15);
+    const int sk = row0 + r;
+    const bool valid = active && sk < a.n;
+    const uint32_t tq = tmem + ((uint32_t)(32 * q) << 16);
+    const uint32_t swz = (uint32_t)(r & 7);
+    float *const c0p = a.cst0 + (size_t)(valid ? sk : 0) * TP_H;
+    float *const c1p = a.cst1 + (size_t)(valid ? sk : 0) * TP_H;
+    int pen = 3, done = 0;
+    bool hold = false;
+    const uint32_t nchunks = (uint32_t)steps * TP_CHUNKS;
+    for (uint32_t g = 0; g < nchunks; ++g) {
+      const int step = (int)(g / TP_CHUNKS), cs = (int)(g % TP_CHUNKS);
+      const int p = step & 1;
+      const uint32_t buf = g & 1;
+      const uint32_t tacc = tq + buf * 256;
+      if (cs == 0) {  // this step's input point (drawn by group 0 after the previous output projection)
+        if (step > 0) mbar_wait(bar_x, (uint32_t)((step - 1) & 1));
+        const uint2 xv = xs_gen[p * TP_M + r];
+        pen = (int)(xv.y & 0xffu);
+        done = (int)((xv.y >> 8) & 1u);
+        hold = pen == 1;  // an eoc input holds the state
+      }
+      mbar_wait(bar_tfull + 8 * buf, (g >> 1) & 1);
+      tc_fence_after();
+      if (cs < 8) {
+        const int layer = cs >> 2, c = cs & 3;
+        if (cs == 7 && e == 0) {
+          // every product of layer 1 is complete: nobody reads this step's new h0 any more, held rows get the old state back
+          if (active && hold) {
+            const uint4 *src = reinterpret_cast<const uint4 *>(h0_gen + p * TP_HBUF_BYTES + r * 128);
+            uint4 *dst = reinterpret_cast<uint4 *>(h0_gen + (p ^ 1) * TP_HBUF_BYTES + r * 128);
+#pragma unroll
+            for (int kb = 0; kb < 4; ++kb)
+#pragma unroll
+              for (int ch = 0; ch < 8; ++ch) dst[kb * (TP_KBLK_BYTES / 16) + ch] = src[kb * (TP_KBLK_BYTES / 16) + ch];
+          }
+          fence_proxy_async_smem();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(bar_s0);
+        }
+        uint8_t *hnew = (layer == 0 ? h0_gen : h1_gen) + (p ^ 1) * TP_HBUF_BYTES + c * TP_KBLK_BYTES + r * 128;
+        float *cp = (layer == 0 ? c0p : c1p) + 64 * c;
+        // this group's 4 passes of 8 units; the tensor-memory load and the cell-state load of the next pass are in flight
+        // during the current one
+        const int sub0 = 4 * e;
+        uint32_t va[32], vb[32];
+        float4 ca0 = make_float4(0.f, 0.f, 0.f, 0.f), ca1 = ca0, cb0 = ca0, cb1 = ca0;
+        tp_ld32_issue(tacc + (uint32_t)(sub0 * 32), va);
+        if (valid) { ca0 = *reinterpret_cast<const float4 *>(cp + 8 * sub0); ca1 = *reinterpret_cast<const float4 *>(cp + 8 * sub0 + 4); }
+        auto pass = [&](int sub, const uint32_t (&v)[32], const float4 &q0, const float4 &q1) {
+          const float cin[8] = {q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, q1.z, q1.w};
+          float cn[8];
+          const uint4 hq = tp_cell8(v, cin, cn);
+          if (active) *reinterpret_cast<uint4 *>(hnew + (((uint32_t)sub ^ swz) << 4)) = hq;
+          if (valid && !hold) {
+            *reinterpret_cast<float4 *>(cp + 8 * sub) = make_float4(cn[0], cn[1], cn[2], cn[3]);
+            *reinterpret_cast<float4 *>(cp + 8 * sub + 4) = make_float4(cn[4], cn[5], cn[6], cn[7]);
+          }
+        };
+#pragma unroll 1
+        for (int sub = sub0; sub < sub0 + 4; sub += 2) {
+          tp_ld_wait(va);
+          tp_ld32_issue(tacc + (uint32_t)((sub + 1) * 32), vb);
+          if (valid) { cb0 = *reinterpret_cast<const float4 *>(cp + 8 * (sub + 1)); cb1 = *reinterpret_cast<const float4 *>(cp + 8 * (sub + 1) + 4); }
+          pass(sub, va, ca0, ca1);
+          tp_ld_wait(vb);
+          if (sub + 2 < sub0 + 4) {
+            tp_ld32_issue(tacc + (uint32_t)((sub + 2) * 32), va);
+            if (valid) { ca0 = *reinterpret_cast<const float4 *>(cp + 8 * (sub + 2)); ca1 = *reinterpret_cast<const float4 *>(cp + 8 * (sub + 2) + 4); }
+          }
+          pass(sub + 1, vb, cb0, cb1);
+        }
+        fence_proxy_async_smem();  // the new h block is an operand of the tensor core
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) {
+          mbar_arrive((layer == 0 ? bar_h0 : bar_h1) + 8 * c);
+          mbar_arrive(bar_tempty + 8 * buf);
+        }
+      } else if (e == 1) {
+        // output projection complete: nobody reads this step's new h1 any more, held rows get the old state back
+        if (lane == 0) mbar_arrive(bar_tempty + 8 * buf);  // this group reads nothing of the logits
+        if (active && hold) {
+          const uint4 *src = reinterpret_cast<const uint4 *>(h1_gen + p * TP_HBUF_BYTES + r * 128);
+          uint4 *dst = reinterpret_cast<uint4 *>(h1_gen + (p ^ 1) * TP_HBUF_BYTES + r * 128);
+#pragma unroll
+          for (int kb = 0; kb < 4; ++kb)
+#pragma unroll
+            for (int ch = 0; ch < 8; ++ch) dst[kb * (TP_KBLK_BYTES / 16) + ch] = src[kb * (TP_KBLK_BYTES / 16) + ch];
+        }
+        fence_proxy_async_smem();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(bar_s1);
+      } else {
+        // ---- the draw (model.py:219-261) from this row's logits (bias included by the product), all in registers ----
+        const int NOUT = a.NOUT, M = a.M;
+        uint32_t v0[32], v1[32];
+        tc_ld32(tacc, v0);
+        tc_ld32(tacc + 32u, v1);
+        float pm[32];
+        // mixture weights: softmax, then (from the third point on) the temperature re-softmax of model.py:220-224
+        float mx = -INFINITY;
+#pragma unroll
+        for (int k = 0; k < 32; ++k) {
+          const float zl = __uint_as_float(3 + k < 32 ? v0[(3 + k) & 31] : v1[(3 + k) & 31]);
+          pm[k] = k < M ? zl : -INFINITY;
+          mx = fmaxf(mx, pm[k]);
+        }
+        float sum = 0.f;
+#pragma unroll
+        for (int k = 0; k < 32; ++k) { pm[k] = __expf(pm[k] - mx); sum += pm[k]; }
+        float rs = __frcp_rn(sum);
+#pragma unroll
+        for (int k = 0; k < 32; ++k) pm[k] *= rs;
+        if (step > 1) {
+          const float rt = __frcp_rn(a.temp_mix);
+          float m2 = -INFINITY;
+#pragma unroll
+          for (int k = 0; k < 32; ++k) {
+            pm[k] = k < M ? __logf(fmaxf(pm[k], 1e-37f)) * rt : -INFINITY;
+            m2 = fmaxf(m2, pm[k]);
+          }
+          sum = 0.f;
+#pragma unroll
+          for (int k = 0; k < 32; ++k) { pm[k] = __expf(pm[k] - m2); sum += pm[k]; }
+          rs = __frcp_rn(sum);
+#pragma unroll
+          for (int k = 0; k < 32; ++k) pm[k] *= rs;
+        }
+        float u4[4] = {0.f, 0.f, 0.f, 0.f};
+        if (valid) {
+          if (a.uniforms != nullptr) {
+            const float4 uu = __ldg(reinterpret_cast<const float4 *>(a.uniforms + ((size_t)sk * steps + step) * 4));
+            u4[0] = uu.x; u4[1] = uu.y; u4[2] = uu.z; u4[3] = uu.w;
+          } else {
+            uint32_t rr[4];
+            skm_philox4x32((uint32_t)(a.sketch0 + sk), (uint32_t)step, 0u, 0x5a3711eu, (uint32_t)a.seed, (uint32_t)(a.seed >> 32), rr);
+#pragma unroll
+            for (int k = 0; k < 4; ++k) u4[k] = skm_u01(rr[k]);
+          }
+        }
+        int idx = -1;
+        float cdf = 0.f;
+#pragma unroll
+        for (int k = 0; k < 32; ++k) {
+          cdf += pm[k];
+          if (k < M && idx < 0 && cdf >= u4[0]) idx = k;
+        }
+        if (idx < 0) idx = M - 1;  // get_pi_idx == -1 -> last component
+        // pen state (plain softmax; the reference never applies the pen temperature)
+        const float z0 = __uint_as_float(v0[0]), z1 = __uint_as_float(v0[1]), z2 = __uint_as_float(v0[2]);
+        const float pmx = fmaxf(z0, fmaxf(z1, z2));
+        const float e0 = __expf(z0 - pmx), e1 = __expf(z1 - pmx), e2 = __expf(z2 - pmx);
+        const float ps = e0 + e1 + e2;
+        const bool record = a.mixp != nullptr && valid && !done;
+        float *mo = a.mixp + (record ? ((size_t)sk * steps + step) * NOUT : 0);
+        if (record) {  // same record as the exact kernel (include/skrnn.h: mix_params_dev)
+          mo[0] = e0 / ps; mo[1] = e1 / ps; mo[2] = e2 / ps;
+#pragma unroll
+          for (int k = 0; k < 32; ++k)
+            if (k < M) mo[3 + k] = (step > 1) ? pm[k] / a.temp_pen : pm[k];
+        }
+        // the chosen component's five parameters: column 3 + g M + idx of the logits, picked out of the 32-column pieces
+        float val[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+#pragma unroll 1
+        for (int sub = 0; sub * 32 < NOUT; ++sub) {
+          if (sub == 1) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) v0[j] = v1[j];
+          } else if (sub > 1) {
+            tc_ld32(tacc + (uint32_t)(sub * 32), v0);
+          }
+#pragma unroll
+          for (int gq = 1; gq <= 5; ++gq) {
+            const int lo = 3 + gq * M;
+            if (lo < 32 * sub + 32 && lo + M > 32 * sub) {
+              const int want = lo + idx - 32 * sub;
+#pragma unroll
+              for (int j = 0; j < 32; ++j)
+                if (j == want) val[gq] = __uint_as_float(v0[j]);
+            }
+          }
+          if (record) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+              const int col = 32 * sub + j;
+              if (col >= 3 + M && col < NOUT) {
+                const float zz = __uint_as_float(v0[j]);
+                mo[col] = col < 3 + 3 * M ? zz : (col < 3 + 5 * M ? __expf(zz) : tanhf(zz));
+              }
+            }
+          }
+        }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(bar_tempty + 8 * buf);
+        uint32_t xpack = 0u, xflag = 3u | ((uint32_t)done << 8), xpen = 0u, xcont = 0u;
+        if (valid && !done) {
+          float eos = 0.f, eoc = 0.f, cont = 0.f;
+          int pidx = 2;
+          if (e0 / ps >= u4[1]) { eos = 1.f; pidx = 0; }
+          else if ((e0 + e1) / ps >= u4[1]) { eoc = 1.f; pidx = 1; }
+          else cont = 1.f;
+          const float mu1 = val[1], mu2 = val[2];
+          const float s1 = __expf(val[3]), s2 = __expf(val[4]);
+          const float rho = tanhf(val[5]);
+          float g1, g2;
+          skm_box_muller(u4[2], u4[3], &g1, &g2);
+          const float x1 = mu1 + s1 * g1;
+          const float x2 = mu2 + s2 * (rho * g1 + sqrtf(fmaxf(0.f, 1.0f - rho * rho)) * g2);
+          float *so = a.strokes + ((size_t)sk * steps + step) * 5;
+          so[0] = x1 * a.data_scale; so[1] = x2 * a.data_scale; so[2] = eos; so[3] = eoc; so[4] = cont;
+          a.lengths[sk] = step + 1;
+          if (a.stop_if_eoc && eoc > 0.f) done = 1;
+          const __nv_bfloat162 xb = __floats2bfloat162_rn(x1, x2);  // the next input, rounded like every operand of this path
+          xpack = *reinterpret_cast<const uint32_t *>(&xb);
+          xflag = (uint32_t)pidx | ((uint32_t)done << 8);
+          xpen = pidx == 0 ? 0x00003f80u : (pidx == 1 ? 0x3f800000u : 0u);  // (eos, eoc) as a bf16 pair
+          xcont = pidx == 2 ? 0x00003f80u : 0u;
+        }
+        if (active) {
+          xs_gen[(p ^ 1) * TP_M + r] = make_uint2(xpack, xflag);
+          // operand columns (dx, dy, eos, eoc, cont, 1, 1, 0) of the next step's K = 16 slice
+          *reinterpret_cast<uint4 *>(xa_gen + r * 128 + (((uint32_t)(2 * (p ^ 1)) ^ swz) << 4)) =
+              make_uint4(xpack, xpen, xcont | 0x3f800000u, 0x00003f80u);
+        }
+        fence_proxy_async_smem();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(bar_x);
+      }
+    }
