@@ -235,6 +235,7 @@ int sk_sample_f32(skrnn_handle *h, cudaStream_t st, int n, int steps, float temp
 // bf16 tensor-core throughput sampler (sampler_tc.cu): 0 ok, -1 not applicable, >0 error
 int sk_sample_cluster(skrnn_handle *h, cudaStream_t st, int n, int steps, float temp_mix, float temp_pen, int stop_if_eoc,
                       const float *uniforms, uint64_t seed, int sketch0, float *strokes, int *lengths, float *mixp);
+size_t sk_sample_tp_scratch_bytes();
 int sk_sample_tp(skrnn_handle *h, cudaStream_t st, int n, int steps, float temp_mix, float temp_pen, int stop_if_eoc,
                  const float *uniforms, uint64_t seed, int sketch0, float *strokes, int *lengths, float *mixp,
                  const __nv_bfloat16 *const *wsm, const float *const *bias_il, float *const *cst, float *tables);

@@ -179,7 +179,7 @@ int sk_sample_tc(skrnn_handle *h, cudaStream_t st, int n, int steps, float temp_
   }
   const size_t o_top = take((size_t)n * H * 2), o_lg = take((size_t)n * NOUT * 4);
   const size_t o_xin = take((size_t)n * 5 * 4), o_done = take((size_t)n * 4), o_call = take(sizeof(SampCall));
-  const size_t o_tab = take(((size_t)2 * G + 192) * 32 * 2);  // input-term weight images of the persistent kernel (sampler_tp.cu)
+  const size_t o_tab = take(sk_sample_tp_scratch_bytes());  // input-term weight images of the persistent kernel (sampler_tp.cu)
   if (off > h->samp_tc_bytes) {
     if (h->samp_graph) { cudaGraphExecDestroy(h->samp_graph); h->samp_graph = nullptr; }
     SK_CUDA(cudaStreamSynchronize(st));

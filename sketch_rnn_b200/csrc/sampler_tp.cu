@@ -19,6 +19,9 @@
 //   * an eoc input holds the recurrent state (model.py:82-92 with initial_state = prev_state) while the layer output
 //     still feeds the layer above: the new h is always written, and once the products that read it are complete the
 //     held rows are copied back from the other buffer.
+//   * within a 256-column chunk the gate columns are permuted (tp_src_col) so that tcgen05.ld.16x256b hands each of a
+//     warp's 32 threads the four gates of 8 consecutive units for two sketch rows: an M = 64 accumulator only fills 16 of a
+//     warp's 32 lanes, and the cell update is bound by the transcendental unit, which a half-empty warp occupies in full.
 // Same arithmetic contract as sampler_tc.cu (operands rounded to bf16, fp32 accumulation; not the bit-exact path).
 #include <stdlib.h>
 
@@ -54,9 +57,25 @@ struct TpArgs {
   int debug;                     // SKRNN_TP_DEBUG=1: CTA 0 prints where its MMA warp waited
 };
 
-// Input-term weight images [TP_XROWS][1024] (interleaved columns like the operand images of sampler_tc.cu, whose rows
-// 0..4 of wsm[0] are the x rows): rows 0..4 W_x (layer 0 only), row 5 the bias rounded to bf16, row 6 what the rounding
-// dropped, the rest zero.
+// Column order of the streamed weight images.  Position P = 256 c + 16 j + 8 a + 2 m + b holds gate 2a + b of unit
+// 64 c + 16 m + j: tcgen05.ld.16x256b gives thread t (m = t % 4) columns 2m, 2m+1 of every group of 8, so it ends up with
+// the gates (i, j | f, o) of units 16m .. 16m+15 of the chunk.  Returns the column of sampler_tc.cu's images (4 unit + gate).
+__host__ __device__ inline int tp_src_col(int P) {
+  const int c = P >> 8, w = P & 255;
+  const int j = w >> 4, a2 = (w >> 3) & 1, m = (w >> 1) & 3, b = w & 1;
+  return 4 * (64 * c + 16 * m + j) + 2 * a2 + b;
+}
+
+__global__ void tp_wperm_kernel(const __nv_bfloat16 *__restrict__ src, __nv_bfloat16 *__restrict__ dst, int K) {
+  const int total = K * TP_G;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    const int k = i / TP_G, P = i % TP_G;
+    dst[i] = src[k * TP_G + tp_src_col(P)];
+  }
+}
+
+// Input-term weight images [TP_XROWS][1024] (same column order; rows 0..4 of sampler_tc.cu's wsm[0] are the x rows):
+// rows 0..4 W_x (layer 0 only), row 5 the bias rounded to bf16, row 6 what the rounding dropped, the rest zero.
 __global__ void tp_ximage_kernel(const __nv_bfloat16 *__restrict__ wsm0, const float *__restrict__ bias_il0,
                                  const float *__restrict__ bias_il1, __nv_bfloat16 *__restrict__ wx0,
                                  __nv_bfloat16 *__restrict__ wx1, const float *__restrict__ out_b, int NOUT,
@@ -64,7 +83,7 @@ __global__ void tp_ximage_kernel(const __nv_bfloat16 *__restrict__ wsm0, const f
   const int j = blockIdx.x * blockDim.x + threadIdx.x;
   if (j >= TP_G) return;
   const __nv_bfloat16 zero = __float2bfloat16_rn(0.f);
-  if (j < TP_XO_PITCH) {  // output projection: bias rows only
+  if (j < TP_XO_PITCH) {  // output projection: bias rows only, natural column order
     for (int k = 0; k < TP_XROWS; ++k) wxo[k * TP_XO_PITCH + j] = zero;
     if (j < NOUT) {
       const float b = out_b[j];
@@ -72,12 +91,27 @@ __global__ void tp_ximage_kernel(const __nv_bfloat16 *__restrict__ wsm0, const f
       wxo[5 * TP_XO_PITCH + j] = hb; wxo[6 * TP_XO_PITCH + j] = __float2bfloat16_rn(b - __bfloat162float(hb));
     }
   }
+  const int sc = tp_src_col(j);
   for (int k = 0; k < TP_XROWS; ++k) { wx0[k * TP_G + j] = zero; wx1[k * TP_G + j] = zero; }
-  for (int k = 0; k < 5; ++k) wx0[k * TP_G + j] = wsm0[k * TP_G + j];
-  const float b0 = bias_il0[j], b1 = bias_il1[j];
+  for (int k = 0; k < 5; ++k) wx0[k * TP_G + j] = wsm0[k * TP_G + sc];
+  const float b0 = bias_il0[sc], b1 = bias_il1[sc];
   const __nv_bfloat16 h0 = __float2bfloat16_rn(b0), h1 = __float2bfloat16_rn(b1);
   wx0[5 * TP_G + j] = h0; wx0[6 * TP_G + j] = __float2bfloat16_rn(b0 - __bfloat162float(h0));
   wx1[5 * TP_G + j] = h1; wx1[6 * TP_G + j] = __float2bfloat16_rn(b1 - __bfloat162float(h1));
+}
+
+// tcgen05.ld.16x256b.x8: 16 accumulator rows x 64 columns; thread t gets rows t/4 (registers 4i, 4i+1) and t/4 + 8
+// (registers 4i+2, 4i+3), columns 8i + 2(t%4), + 1.  No wait (see tp_ld_wait).
+__device__ __forceinline__ void tp_ld16x8_issue(uint32_t taddr, uint32_t (&r)[32]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.16x256b.x8.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+        "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]),
+        "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]),
+        "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+      : "r"(taddr));
 }
 
 // tcgen05.ld of 32 columns without the wait, and the wait that also ties the destination registers to itself (the
@@ -101,27 +135,14 @@ __device__ __forceinline__ void tp_ld_wait(uint32_t (&r)[32]) {
                     "+r"(r[24]), "+r"(r[25]), "+r"(r[26]), "+r"(r[27]), "+r"(r[28]), "+r"(r[29]), "+r"(r[30]), "+r"(r[31]));
 }
 
-// LSTM cell update of 8 units of one sketch row: v = the 32 accumulator columns (4 gates per unit, i j f o; bias and
-// input term included by the products).  Writes c' into cn and returns h' packed.
-__device__ __forceinline__ uint4 tp_cell8(const uint32_t (&v)[32], const float (&cin)[8], float (&cn)[8]) {
-  uint32_t hb[4];
-#pragma unroll
-  for (int j = 0; j < 8; j += 2) {
-    float hh[2];
-#pragma unroll
-    for (int e = 0; e < 2; ++e) {
-      const int u = j + e;
-      const float ig = sigmoid_approx(__uint_as_float(v[4 * u + 0]));
-      const float jg = tanh_approx(__uint_as_float(v[4 * u + 1]));
-      const float fg = sigmoid_approx(__uint_as_float(v[4 * u + 2]) + 1.0f);
-      const float og = sigmoid_approx(__uint_as_float(v[4 * u + 3]));
-      cn[u] = fmaf(cin[u], fg, ig * jg);
-      hh[e] = tanh_approx(cn[u]) * og;
-    }
-    const __nv_bfloat162 hv = __floats2bfloat162_rn(hh[0], hh[1]);
-    hb[j >> 1] = *reinterpret_cast<const uint32_t *>(&hv);
-  }
-  return make_uint4(hb[0], hb[1], hb[2], hb[3]);
+// LSTM cell update of one unit (bias and input term are in the accumulator): returns h', writes c' to cn.
+__device__ __forceinline__ float tp_cell(uint32_t vi, uint32_t vj, uint32_t vf, uint32_t vo, float cin, float &cn) {
+  const float ig = sigmoid_approx(__uint_as_float(vi));
+  const float jg = tanh_approx(__uint_as_float(vj));
+  const float fg = sigmoid_approx(__uint_as_float(vf) + 1.0f);
+  const float og = sigmoid_approx(__uint_as_float(vo));
+  cn = fmaf(cin, fg, ig * jg);
+  return tanh_approx(cn) * og;
 }
 
 __global__ void __launch_bounds__(TP_THREADS, 1)
@@ -309,9 +330,11 @@ sample_tp_kernel(const __grid_constant__ CUtensorMap tmW0, const __grid_constant
 
 }  // namespace
 
+size_t sk_sample_tp_scratch_bytes() { return (((size_t)(8 + TP_H) + 2 * TP_H + 2 * TP_XROWS) * TP_G + (size_t)TP_XROWS * TP_XO_PITCH) * 2; }
+
 // 0: drawn here; -1: not eligible (sampler_tc.cu continues with its step-by-step path); > 0: error.
 // wsm / bias_il / cst: the packed operand images and zeroed cell states sampler_tc.cu has just prepared;
-// tables: (2 * 1024 + 192) * 32 bf16 of scratch for the input-term / bias weight images.
+// tables: sk_sample_tp_scratch_bytes() of scratch for the column-permuted weight images and the input-term / bias images.
 int sk_sample_tp(skrnn_handle *h, cudaStream_t st, int n, int steps, float temp_mix, float temp_pen, int stop_if_eoc,
                  const float *uniforms, uint64_t seed, int sketch0, float *strokes, int *lengths, float *mixp,
                  const __nv_bfloat16 *const *wsm, const float *const *bias_il, float *const *cst, float *tables) {
@@ -321,14 +344,15 @@ int sk_sample_tp(skrnn_handle *h, cudaStream_t st, int n, int steps, float temp_
   }
   if (h->cfg.cell != SKRNN_CELL_LSTM || h->H != TP_H || h->L != 2 || h->M > 32 || h->NOUT > 192 || n < TP_M) return -1;
   CUtensorMap tmW0, tmW1, tmWo, tmX0, tmX1, tmXo;
-  __nv_bfloat16 *wx0 = reinterpret_cast<__nv_bfloat16 *>(tables), *wx1 = wx0 + (size_t)TP_XROWS * TP_G;
+  __nv_bfloat16 *wp0 = reinterpret_cast<__nv_bfloat16 *>(tables), *wp1 = wp0 + (size_t)(8 + TP_H) * TP_G;
+  __nv_bfloat16 *wx0 = wp1 + (size_t)2 * TP_H * TP_G, *wx1 = wx0 + (size_t)TP_XROWS * TP_G;
   __nv_bfloat16 *wxo = wx1 + (size_t)TP_XROWS * TP_G;
   {
     uint64_t dims[2] = {(uint64_t)TP_G, (uint64_t)(8 + TP_H)}, str[1] = {(uint64_t)TP_G * 2};
     uint32_t box[2] = {64, (uint32_t)TP_BK};
-    SK_TRY(sk_make_tmap(&tmW0, 2, wsm[0], 2, dims, str, box));
+    SK_TRY(sk_make_tmap(&tmW0, 2, wp0, 2, dims, str, box));
     dims[1] = 2 * TP_H;
-    SK_TRY(sk_make_tmap(&tmW1, 2, wsm[1], 2, dims, str, box));
+    SK_TRY(sk_make_tmap(&tmW1, 2, wp1, 2, dims, str, box));
     dims[1] = TP_XROWS;
     SK_TRY(sk_make_tmap(&tmX0, 2, wx0, 2, dims, str, box));
     SK_TRY(sk_make_tmap(&tmX1, 2, wx1, 2, dims, str, box));
@@ -344,6 +368,16 @@ int sk_sample_tp(skrnn_handle *h, cudaStream_t st, int n, int steps, float temp_
   a.strokes = strokes; a.mixp = mixp; a.lengths = lengths;
   a.cst0 = cst[0]; a.cst1 = cst[1];
   { const char *e = getenv("SKRNN_TP_DEBUG"); a.debug = (e && e[0] == '1') ? 1 : 0; }
+  {
+    SkLaunch scope(h, st, SK_CAT_SAMPLER);
+    tp_wperm_kernel<<<2 * h->num_sms, 256, 0, st>>>(wsm[0], wp0, 8 + TP_H);
+    SK_CUDA(cudaGetLastError());
+  }
+  {
+    SkLaunch scope(h, st, SK_CAT_SAMPLER);
+    tp_wperm_kernel<<<2 * h->num_sms, 256, 0, st>>>(wsm[1], wp1, 2 * TP_H);
+    SK_CUDA(cudaGetLastError());
+  }
   {
     SkLaunch scope(h, st, SK_CAT_SAMPLER);
     tp_ximage_kernel<<<TP_G / 256, 256, 0, st>>>(wsm[0], bias_il[0], bias_il[1], wx0, wx1, h->params + h->off_out_b, h->NOUT, wxo);

@@ -2,7 +2,8 @@
     // Both groups (warps 2-5 / 6-9) work on every accumulator of the sequence [4 chunks of layer 0][4 chunks of layer 1]
     // [output projection] per step: a chunk's 64 units are split between them (the step is a chain of dependent
     // chunks, so a chunk's latency counts, not only the warps' throughput).  An M = 64 accumulator keeps row 16q + i in
-    // lane i (< 16) of lane quarter q; the upper 16 lanes of a warp only take part in the collective loads.
+    // lane i (< 16) of lane quarter q: the draw and the state hold work thread-per-row on lanes 0..15, the cell update
+    // spreads the rows over all 32 lanes (see below).
     const int e = (warp - 2) >> 2;
     const int q = warp & 3;
     const bool active = lane < 16;
@@ -11,10 +12,12 @@
     const bool valid = active && sk < a.n;
     const uint32_t tq = tmem + ((uint32_t)(32 * q) << 16);
     const uint32_t swz = (uint32_t)(r & 7);
-    float *const c0p = a.cst0 + (size_t)(valid ? sk : 0) * TP_H;
-    float *const c1p = a.cst1 + (size_t)(valid ? sk : 0) * TP_H;
+    // the cell update's view of the quarter's rows (tcgen05.ld.16x256b): thread (t4 = lane / 4, m4 = lane % 4), rows rA, rB
+    const int m4 = lane & 3, rA = 16 * q + (lane >> 2), rB = rA + 8;
+    const int skA = row0 + rA, skB = row0 + rB;
+    const bool validA = skA < a.n, validB = skB < a.n;
     int pen = 3, done = 0;
-    bool hold = false;
+    bool hold = false, holdA = false, holdB = false;
     const uint32_t nchunks = (uint32_t)steps * TP_CHUNKS;
     for (uint32_t g = 0; g < nchunks; ++g) {
       const int step = (int)(g / TP_CHUNKS), cs = (int)(g % TP_CHUNKS);
@@ -27,6 +30,8 @@
         pen = (int)(xv.y & 0xffu);
         done = (int)((xv.y >> 8) & 1u);
         hold = pen == 1;  // an eoc input holds the state
+        holdA = (xs_gen[p * TP_M + rA].y & 0xffu) == 1u;
+        holdB = (xs_gen[p * TP_M + rB].y & 0xffu) == 1u;
       }
       mbar_wait(bar_tfull + 8 * buf, (g >> 1) & 1);
       tc_fence_after();
@@ -46,37 +51,47 @@
           __syncwarp();
           if (lane == 0) mbar_arrive(bar_s0);
         }
-        uint8_t *hnew = (layer == 0 ? h0_gen : h1_gen) + (p ^ 1) * TP_HBUF_BYTES + c * TP_KBLK_BYTES + r * 128;
-        float *cp = (layer == 0 ? c0p : c1p) + 64 * c;
-        // this group's 4 passes of 8 units; the tensor-memory load and the cell-state load of the next pass are in flight
-        // during the current one
-        const int sub0 = 4 * e;
+        // tcgen05.ld.16x256b spreads the 16 rows of this warp's lane quarter over all 32 threads: thread (t4, m) gets the
+        // four gates of units 16m + 8e .. + 7 of the chunk (tp_src_col) for rows rA and rB = rA + 8, in two passes of 4 units;
+        // the second pass's tensor-memory and cell-state loads are in flight during the first
+        uint8_t *hblk = (layer == 0 ? h0_gen : h1_gen) + (p ^ 1) * TP_HBUF_BYTES + c * TP_KBLK_BYTES;
+        const int uoff = 64 * c + 16 * m4 + 8 * e;
+        float *cpA = (layer == 0 ? a.cst0 : a.cst1) + (size_t)(validA ? skA : 0) * TP_H + uoff;
+        float *cpB = (layer == 0 ? a.cst0 : a.cst1) + (size_t)(validB ? skB : 0) * TP_H + uoff;
         uint32_t va[32], vb[32];
-        float4 ca0 = make_float4(0.f, 0.f, 0.f, 0.f), ca1 = ca0, cb0 = ca0, cb1 = ca0;
-        tp_ld32_issue(tacc + (uint32_t)(sub0 * 32), va);
-        if (valid) { ca0 = *reinterpret_cast<const float4 *>(cp + 8 * sub0); ca1 = *reinterpret_cast<const float4 *>(cp + 8 * sub0 + 4); }
-        auto pass = [&](int sub, const uint32_t (&v)[32], const float4 &q0, const float4 &q1) {
-          const float cin[8] = {q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, q1.z, q1.w};
-          float cn[8];
-          const uint4 hq = tp_cell8(v, cin, cn);
-          if (active) *reinterpret_cast<uint4 *>(hnew + (((uint32_t)sub ^ swz) << 4)) = hq;
-          if (valid && !hold) {
-            *reinterpret_cast<float4 *>(cp + 8 * sub) = make_float4(cn[0], cn[1], cn[2], cn[3]);
-            *reinterpret_cast<float4 *>(cp + 8 * sub + 4) = make_float4(cn[4], cn[5], cn[6], cn[7]);
+        const float4 zero4 = make_float4(0.f, 0.f, 0.f, 0.f);
+        tp_ld16x8_issue(tacc + (uint32_t)(128 * e), va);
+        const float4 cA0 = validA ? *reinterpret_cast<const float4 *>(cpA) : zero4;
+        const float4 cB0 = validB ? *reinterpret_cast<const float4 *>(cpB) : zero4;
+        tp_ld_wait(va);
+        tp_ld16x8_issue(tacc + (uint32_t)(128 * e + 64), vb);
+        const float4 cA1 = validA ? *reinterpret_cast<const float4 *>(cpA + 4) : zero4;
+        const float4 cB1 = validB ? *reinterpret_cast<const float4 *>(cpB + 4) : zero4;
+        uint32_t hA[4], hB[4];
+        auto pass = [&](int ps, const uint32_t (&v)[32], const float4 &qa, const float4 &qb) {
+          const float ca[4] = {qa.x, qa.y, qa.z, qa.w}, cb[4] = {qb.x, qb.y, qb.z, qb.w};
+          float na[4], nb[4], ha[4], hb[4];
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            ha[i] = tp_cell(v[8 * i + 0], v[8 * i + 1], v[8 * i + 4], v[8 * i + 5], ca[i], na[i]);
+            hb[i] = tp_cell(v[8 * i + 2], v[8 * i + 3], v[8 * i + 6], v[8 * i + 7], cb[i], nb[i]);
           }
+#pragma unroll
+          for (int i = 0; i < 4; i += 2) {
+            const __nv_bfloat162 pa = __floats2bfloat162_rn(ha[i], ha[i + 1]), pb = __floats2bfloat162_rn(hb[i], hb[i + 1]);
+            hA[2 * ps + (i >> 1)] = *reinterpret_cast<const uint32_t *>(&pa);
+            hB[2 * ps + (i >> 1)] = *reinterpret_cast<const uint32_t *>(&pb);
+          }
+          if (validA && !holdA) *reinterpret_cast<float4 *>(cpA + 4 * ps) = make_float4(na[0], na[1], na[2], na[3]);
+          if (validB && !holdB) *reinterpret_cast<float4 *>(cpB + 4 * ps) = make_float4(nb[0], nb[1], nb[2], nb[3]);
         };
-#pragma unroll 1
-        for (int sub = sub0; sub < sub0 + 4; sub += 2) {
-          tp_ld_wait(va);
-          tp_ld32_issue(tacc + (uint32_t)((sub + 1) * 32), vb);
-          if (valid) { cb0 = *reinterpret_cast<const float4 *>(cp + 8 * (sub + 1)); cb1 = *reinterpret_cast<const float4 *>(cp + 8 * (sub + 1) + 4); }
-          pass(sub, va, ca0, ca1);
-          tp_ld_wait(vb);
-          if (sub + 2 < sub0 + 4) {
-            tp_ld32_issue(tacc + (uint32_t)((sub + 2) * 32), va);
-            if (valid) { ca0 = *reinterpret_cast<const float4 *>(cp + 8 * (sub + 2)); ca1 = *reinterpret_cast<const float4 *>(cp + 8 * (sub + 2) + 4); }
-          }
-          pass(sub + 1, vb, cb0, cb1);
+        pass(0, va, cA0, cB0);
+        tp_ld_wait(vb);
+        pass(1, vb, cA1, cB1);
+        {
+          const uint32_t chunk = (uint32_t)(2 * m4 + e);
+          *reinterpret_cast<uint4 *>(hblk + rA * 128 + ((chunk ^ (uint32_t)(rA & 7)) << 4)) = make_uint4(hA[0], hA[1], hA[2], hA[3]);
+          *reinterpret_cast<uint4 *>(hblk + rB * 128 + ((chunk ^ (uint32_t)(rB & 7)) << 4)) = make_uint4(hB[0], hB[1], hB[2], hB[3]);
         }
         fence_proxy_async_smem();  // the new h block is an operand of the tensor core
         tc_fence_before();
