@@ -273,7 +273,7 @@ sample_tp_kernel(const __grid_constant__ CUtensorMap tmW0, const __grid_constant
           const uint32_t accA = acc_begin();
           for (int j = 0; j < 8; ++j) kstage(accA, h0s + (j >> 1) * TP_KBLK_BYTES + (j & 1) * 64, idesc, j == 0, 2);
           const uint32_t bufA = g & 1, bufB = bufA ^ 1;
-          TP_TIMED(1, mbar_wait(bar_tempty + 8 * bufB, (((g + 1) >> 1) & 1) ^ 1));
+          TP_TIMED(3, mbar_wait(bar_tempty + 8 * bufB, (((g + 1) >> 1) & 1) ^ 1));
           tc_fence_after();
           const uint32_t accB = tmem + bufB * 256;
           for (int j = 0; j < 8; ++j) kstage(accB, h0s + (j >> 1) * TP_KBLK_BYTES + (j & 1) * 64, idesc, j == 0, 2);

@@ -121,7 +121,9 @@
         tc_ld32(tacc, v0);
         tc_ld32(tacc + 32u, v1);
         float pm[32];
-        // mixture weights: softmax, then (from the third point on) the temperature re-softmax of model.py:220-224
+        // mixture weights: softmax; from the third point on the reference re-normalises log(pi) / temperature
+        // (model.py:220-224), which is the softmax of the logits over the temperature -- one exponential per component
+        const float sc = step > 1 ? __frcp_rn(a.temp_mix) : 1.0f;
         float mx = -INFINITY;
 #pragma unroll
         for (int k = 0; k < 32; ++k) {
@@ -131,25 +133,10 @@
         }
         float sum = 0.f;
 #pragma unroll
-        for (int k = 0; k < 32; ++k) { pm[k] = __expf(pm[k] - mx); sum += pm[k]; }
-        float rs = __frcp_rn(sum);
+        for (int k = 0; k < 32; ++k) { pm[k] = __expf((pm[k] - mx) * sc); sum += pm[k]; }
+        const float rs = __frcp_rn(sum);
 #pragma unroll
         for (int k = 0; k < 32; ++k) pm[k] *= rs;
-        if (step > 1) {
-          const float rt = __frcp_rn(a.temp_mix);
-          float m2 = -INFINITY;
-#pragma unroll
-          for (int k = 0; k < 32; ++k) {
-            pm[k] = k < M ? __logf(fmaxf(pm[k], 1e-37f)) * rt : -INFINITY;
-            m2 = fmaxf(m2, pm[k]);
-          }
-          sum = 0.f;
-#pragma unroll
-          for (int k = 0; k < 32; ++k) { pm[k] = __expf(pm[k] - m2); sum += pm[k]; }
-          rs = __frcp_rn(sum);
-#pragma unroll
-          for (int k = 0; k < 32; ++k) pm[k] *= rs;
-        }
         float u4[4] = {0.f, 0.f, 0.f, 0.f};
         if (valid) {
           if (a.uniforms != nullptr) {
