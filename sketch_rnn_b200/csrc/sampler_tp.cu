@@ -145,6 +145,7 @@ __device__ __forceinline__ float tp_cell(uint32_t vi, uint32_t vj, uint32_t vf, 
   return tanh_approx(cn) * og;
 }
 
+template <bool DBG>
 __global__ void __launch_bounds__(TP_THREADS, 1)
 sample_tp_kernel(const __grid_constant__ CUtensorMap tmW0, const __grid_constant__ CUtensorMap tmW1,
                  const __grid_constant__ CUtensorMap tmWo, const __grid_constant__ CUtensorMap tmX0,
@@ -242,7 +243,7 @@ sample_tp_kernel(const __grid_constant__ CUtensorMap tmW0, const __grid_constant
       uint32_t g = 0;
       long long tw[4] = {0, 0, 0, 0};  // cycles waited for: ring stage, accumulator buffer, new h / state, input point
       const long long t_begin = clock64();
-#define TP_TIMED(slot, stmt) do { const long long t0_ = clock64(); stmt; tw[slot] += clock64() - t0_; } while (0)
+#define TP_TIMED(slot, stmt) do { if constexpr (DBG) { const long long t0_ = clock64(); stmt; tw[slot] += clock64() - t0_; } else { stmt; } } while (0)
       // one ring stage against the operand bytes at a_addr: nk products of K = 16
       auto kstage = [&](uint32_t acc, uint32_t a_addr, uint32_t id, bool first, int nk) {
         const int s = it % TP_STAGES, ph = (it / TP_STAGES) & 1;
@@ -316,8 +317,8 @@ sample_tp_kernel(const __grid_constant__ CUtensorMap tmW0, const __grid_constant
         }
       }
 #undef TP_TIMED
-      if (a.debug && blockIdx.x == 0)
-        printf("sample_tp: %lld cycles per step; MMA warp waited for ring %lld, accumulator %lld, h/state %lld, input %lld\n",
+      if (DBG && blockIdx.x == 0)
+        printf("sample_tp: %lld cycles per step; MMA warp waited for ring %lld, accumulator %lld, h/state %lld, logits buffer and input point %lld\n",
                (clock64() - t_begin) / steps, tw[0] / steps, tw[1] / steps, tw[2] / steps, tw[3] / steps);
     }
   } else {
@@ -383,9 +384,14 @@ int sk_sample_tp(skrnn_handle *h, cudaStream_t st, int n, int steps, float temp_
     tp_ximage_kernel<<<TP_G / 256, 256, 0, st>>>(wsm[0], bias_il[0], bias_il[1], wx0, wx1, h->params + h->off_out_b, h->NOUT, wxo);
     SK_CUDA(cudaGetLastError());
   }
-  SK_CUDA(cudaFuncSetAttribute(sample_tp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TP_SMEM));
   SkLaunch scope(h, st, SK_CAT_SAMPLER);
-  sample_tp_kernel<<<(n + TP_M - 1) / TP_M, TP_THREADS, TP_SMEM, st>>>(tmW0, tmW1, tmWo, tmX0, tmX1, tmXo, a);
+  if (a.debug) {
+    SK_CUDA(cudaFuncSetAttribute(sample_tp_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, TP_SMEM));
+    sample_tp_kernel<true><<<(n + TP_M - 1) / TP_M, TP_THREADS, TP_SMEM, st>>>(tmW0, tmW1, tmWo, tmX0, tmX1, tmXo, a);
+  } else {
+    SK_CUDA(cudaFuncSetAttribute(sample_tp_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, TP_SMEM));
+    sample_tp_kernel<false><<<(n + TP_M - 1) / TP_M, TP_THREADS, TP_SMEM, st>>>(tmW0, tmW1, tmWo, tmX0, tmX1, tmXo, a);
+  }
   SK_CUDA(cudaGetLastError());
   return 0;
 }
