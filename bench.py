@@ -334,7 +334,8 @@ def sampling_block(world, rank, local):
                     "sketches_per_gpu": n, "bit_exact": prec == "f32",
                     "launches_per_call": (h.launch_count() - l0) // (iters + 2),
                     "kernel": "sample_kernel (persistent, fp32, bit-exact)" if prec == "f32" else
-                              "tcgen05 gate GEMM with fused cell update + draw kernel, CUDA-graph replay"}
+                              "sample_tp_kernel (persistent tcgen05 kernel: 64 sketches per CTA for all steps, h operands "
+                              "resident in shared memory, weights streamed by TMA, draw in the epilogue)"}
         if prec == "f32" and rank == 0:
             # config 2's size: sample.py draws 10 sketches from one model
             ms10 = None
@@ -552,7 +553,22 @@ def run_ours(args, w):
         peak = peaks["tc_sustained"] if tc and dom != "sampler" else 2 * 128 * 148 * 1.965e-3
         ach = fpl / (dur_ms * 1e-3) / 1e12
         whole = flops_step / (ms_per_step * 1e-3) / 1e12
-        if samp_tc and dom == "sampler":
+        # rnn_size 256 x 2 layers: the whole call is ONE persistent tcgen05 kernel (csrc/sampler_tp.cu), no per-step GEMMs
+        samp_tp = samp_tc and dom == "sampler" and "gemm_tc" not in kern_ms
+        if samp_tp:
+            dur_ms = kern_ms["sampler"]   # the persistent kernel plus microseconds of weight-image packing
+            ach = flops_step / (dur_ms * 1e-3) / 1e12
+            roof = {"bound": "tensor", "achieved": ach, "peak": peaks["tc_sustained"], "unit": "TFLOP/s",
+                    "frac": ach / peaks["tc_sustained"], "traffic": None,
+                    "kernel": "sample_tp_kernel (persistent: every step of 64 sketches per CTA)", "launch_ms": dur_ms,
+                    "launches_per_step": 1, "algorithmic_flops_per_launch": flops_step,
+                    "per_timestep_us": dur_ms * 1e3 / T,
+                    "peak_source": "MEASURED_PEAKS.json bf16 sustained (%s)" % peaks["src"],
+                    "note": "M = 64 products (half the tensor pipe's rows) on 128 of 148 SMs, a step is a chain of dependent "
+                            "chunks, and each CTA streams the stack's 1.6 MB of weights from L2 every step: see DESIGN.md "
+                            "section 4",
+                    "whole_step_tflops": whole, "per_kernel_ms": kern_ms, "per_kernel_launches": kern_cnt}
+        elif samp_tc and dom == "sampler":
             # cell-update + draw kernels between the GEMMs: streaming, HBM/L2 bound.  Bytes per sketch-step:
             # per layer gates 4H fp32 read, c fp32 read+write, h bf16 written twice; logits NOUT fp32 read,
             # point written (fp32 strokes + fp32/bf16 feedback)

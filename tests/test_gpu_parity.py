@@ -292,16 +292,19 @@ def _softmax(z):
     return e / e.sum(axis=1, keepdims=True)
 
 
-def test_throughput_sampler_bf16_replayed_by_oracle():
-    """The tensor-core sampler (bf16 handle, many sketches; sampler_tc.cu) is not bit-exact, so it is
+@pytest.mark.parametrize("tp,M,n", [("1", 24, 192), ("1", 30, 150), ("0", 24, 192)])
+def test_throughput_sampler_bf16_replayed_by_oracle(monkeypatch, tp, M, n):
+    """tp = "1": the persistent kernel (sampler_tp.cu; 30 mixtures put the mixture logits across two 32-column pieces of
+    the accumulator, 150 sketches leave the last CTA ragged); "0": the step-by-step kernels of sampler_tc.cu.
+    The tensor-core sampler (bf16 handle, many sketches) is not bit-exact, so it is
     checked in two halves: (1) its per-step mixture parameters against the fp64 oracle replaying the
     sampler's OWN trajectory step by step (state hold on eoc included) within the bf16 tolerance 2e-2;
     (2) its draws against a NumPy redo of model.py:219-261 from the dumped parameters and uniforms."""
-    cfg = so.Config(model="lstm", rnn_size=256, num_layers=2, num_mixture=24)
+    monkeypatch.setenv("SKRNN_SAMPLE_TP", tp)
+    cfg = so.Config(model="lstm", rnn_size=256, num_layers=2, num_mixture=M)
     params = so.init_params(cfg, seed=7, trained_like=True)
     h = make_handle(cfg, params, precision="bf16")
-    n, steps, temp = 192, 24, 0.6
-    M = cfg.num_mixture
+    steps, temp = 24, 0.6
     u = np.random.RandomState(3).rand(n, steps, 4).astype(np.float32)
     strokes, lengths, mixp = h.sample(n, steps, temp, temp, False, uniforms=u, want_params=True)
     strokes, lengths, mixp = strokes.cpu().numpy(), lengths.cpu().numpy(), mixp.cpu().numpy()
@@ -352,8 +355,11 @@ def test_throughput_sampler_bf16_replayed_by_oracle():
     h.close()
 
 
-def test_throughput_sampler_stop_determinism_and_sharding():
-    cfg = so.Config(model="lstm", rnn_size=128, num_layers=3, num_mixture=8)
+@pytest.mark.parametrize("H,L", [(128, 3), (256, 2)])
+def test_throughput_sampler_stop_determinism_and_sharding(H, L):
+    """(128, 3): the step-by-step kernels; (256, 2): the persistent kernel, whose CTAs own 64 sketches each (160 sketches:
+    a ragged last CTA; the shard of 96 starts in the middle of what was a CTA of the full call)."""
+    cfg = so.Config(model="lstm", rnn_size=H, num_layers=L, num_mixture=8)
     params = so.init_params(cfg, seed=5, trained_like=True)
     h = make_handle(cfg, params, precision="bf16")
     n, steps = 160, 30

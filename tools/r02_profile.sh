@@ -30,11 +30,18 @@ python tools/sample_time.py 10 300 gru >> $O/sample_latency.txt 2>&1; python too
 python tools/sample_time.py 4 60 > $O/plain_samplecl.log 2>&1 &&
 ncu --set full --clock-control none --import-source on -k regex:"sample_cluster" -s 2 -c 1 -o $O/samplecl \
     python tools/sample_time.py 4 60 > $O/ncu_samplecl.log 2>&1
-python tools/run_sample.py 8192 12 > $O/plain_sample.log 2>&1 &&
-ncu --set full --clock-control none -k regex:"samp_draw|gemm_tc_persist" -s 40 -c 4 -o $O/sampler \
-    python tools/run_sample.py 8192 12 > $O/ncu_sampler.log 2>&1
+python tools/run_sample.py 8192 40 > $O/plain_sample.log 2>&1 &&
+ncu --set full --clock-control none --import-source on -k regex:"sample_tp_kernel" -s 1 -c 1 -o $O/sampler \
+    python tools/run_sample.py 8192 40 > $O/ncu_sampler.log 2>&1
+python tools/sample_time.py 8192 40 > $O/plain_stream.log 2>&1 &&
+ncu --set full --clock-control none --import-source on -k regex:"sample_kernel" -s 2 -c 1 -o $O/stream \
+    python tools/sample_time.py 8192 40 > $O/ncu_stream.log 2>&1
+for n in 8192 4096 1024; do python tools/tp_time.py $n 300; done > $O/sample_throughput.txt 2>&1
+SKRNN_SAMPLE_TP=0 python tools/tp_time.py 8192 300 >> $O/sample_throughput.txt 2>&1
+SKRNN_TP_DEBUG=1 python tools/tp_time.py 8192 300 >> $O/sample_throughput.txt 2>&1
+for m in lstm gru rnn; do python tools/sample_time.py 8192 300 $m | tail -1; done >> $O/sample_throughput.txt 2>&1; cat $O/sample_throughput.txt
 # gpurun brings back at most 64 MiB: keep the raw-metrics pages, drop the big reports
-for r in c4 gru rnn sampler samplecl; do
+for r in c4 gru rnn sampler samplecl stream; do
   [ -f $O/$r.ncu-rep ] && ncu -i $O/$r.ncu-rep --page raw --csv > $O/${r}_raw.csv 2>/dev/null && rm -f $O/$r.ncu-rep
 done
 ls -la $O | tail -40
