@@ -164,7 +164,8 @@ sample_tp_kernel(const __grid_constant__ CUtensorMap tmW0, const __grid_constant
   const uint32_t bar_tfull = bars + 80, bar_tempty = bars + 96;             // accumulator buffers
   const uint32_t bar_h0 = bars + 112, bar_h1 = bars + 144;                  // new h k-blocks written (4 each)
   const uint32_t bar_s0 = bars + 176, bar_s1 = bars + 184, bar_x = bars + 192;  // state final for the next step; next input
-  const uint32_t tmem_holder = bars + 200;
+  const uint32_t bar_tfull_h = bars + 200, bar_tempty_h = bars + 208;       // the output projection's own accumulator
+  const uint32_t tmem_holder = bars + 216;
   uint8_t *h0_gen = gen, *h1_gen = gen + 2 * TP_HBUF_BYTES, *xa_gen = gen + (s_xa - base);
   uint2 *xs_gen = reinterpret_cast<uint2 *>(gen + (s_xs - base));
 
@@ -187,6 +188,7 @@ sample_tp_kernel(const __grid_constant__ CUtensorMap tmW0, const __grid_constant
     for (int b = 0; b < 2; ++b) { mbar_init(bar_tfull + 8 * b, 1); mbar_init(bar_tempty + 8 * b, 8); }
     for (int k = 0; k < 4; ++k) { mbar_init(bar_h0 + 8 * k, 8); mbar_init(bar_h1 + 8 * k, 8); }
     mbar_init(bar_s0, 4); mbar_init(bar_s1, 4); mbar_init(bar_x, 4);
+    mbar_init(bar_tfull_h, 1); mbar_init(bar_tempty_h, 4);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmW0)) : "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmW1)) : "memory");
@@ -307,13 +309,17 @@ sample_tp_kernel(const __grid_constant__ CUtensorMap tmW0, const __grid_constant
           acc_end();
         }
         {
-          const uint32_t acc = acc_begin();
+          // output projection: its own accumulator in lanes 16..31 (columns 0 .. nh), so that the draw does not hold one of
+          // the gate chunks' buffers
+          TP_TIMED(1, mbar_wait(bar_tempty_h, p ^ 1));
+          tc_fence_after();
+          const uint32_t acc = tmem + (16u << 16);
           for (int j = 0; j < 8; ++j) {
             if ((j & 1) == 0) { TP_TIMED(2, mbar_wait(bar_h1 + 8 * (j >> 1), p)); tc_fence_after(); }
             kstage(acc, h1n + (j >> 1) * TP_KBLK_BYTES + (j & 1) * 64, idesc_o, j == 0, 2);
           }
           kstage(acc, xa, idesc_o, false, 1);  // + output bias
-          acc_end();
+          tc_commit(bar_tfull_h);
         }
       }
 #undef TP_TIMED

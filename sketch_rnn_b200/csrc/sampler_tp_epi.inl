@@ -22,8 +22,11 @@
     for (uint32_t g = 0; g < nchunks; ++g) {
       const int step = (int)(g / TP_CHUNKS), cs = (int)(g % TP_CHUNKS);
       const int p = step & 1;
-      const uint32_t buf = g & 1;
-      const uint32_t tacc = tq + buf * 256;
+      // gate chunks alternate between the two 256-column accumulators in lanes 0..15 of every quarter; the output
+      // projection has its own accumulator in lanes 16..31 (an M = 64 accumulator may start at lane 16)
+      const uint32_t gg = (uint32_t)(step * 8 + cs);  // gate-chunk count
+      const uint32_t buf = (uint32_t)(cs & 1);
+      const uint32_t tacc = cs < 8 ? tq + buf * 256 : tq;
       if (cs == 0) {  // this step's input point (drawn by group 0 after the previous output projection)
         if (step > 0) mbar_wait(bar_x, (uint32_t)((step - 1) & 1));
         const uint2 xv = xs_gen[p * TP_M + r];
@@ -33,7 +36,8 @@
         holdA = (xs_gen[p * TP_M + rA].y & 0xffu) == 1u;
         holdB = (xs_gen[p * TP_M + rB].y & 0xffu) == 1u;
       }
-      mbar_wait(bar_tfull + 8 * buf, (g >> 1) & 1);
+      if (cs < 8) mbar_wait(bar_tfull + 8 * buf, (gg >> 1) & 1);
+      else mbar_wait(bar_tfull_h, (uint32_t)p);
       tc_fence_after();
       if (cs < 8) {
         const int layer = cs >> 2, c = cs & 3;
@@ -102,7 +106,6 @@
         }
       } else if (e == 1) {
         // output projection complete: nobody reads this step's new h1 any more, held rows get the old state back
-        if (lane == 0) mbar_arrive(bar_tempty + 8 * buf);  // this group reads nothing of the logits
         if (active && hold) {
           const uint4 *src = reinterpret_cast<const uint4 *>(h1_gen + p * TP_HBUF_BYTES + r * 128);
           uint4 *dst = reinterpret_cast<uint4 *>(h1_gen + (p ^ 1) * TP_HBUF_BYTES + r * 128);
@@ -115,7 +118,10 @@
         __syncwarp();
         if (lane == 0) mbar_arrive(bar_s1);
       } else {
-        // ---- the draw (model.py:219-261) from this row's logits (bias included by the product), all in registers ----
+        // ---- the draw (model.py:219-261) from this row's logits (bias included by the product), all in registers; the
+        //      logits' accumulator lives in lanes 16..31 of the quarter, so those lanes draw ----
+        const bool active = lane >= 16;
+        const bool valid = active && sk < a.n;
         const int NOUT = a.NOUT, M = a.M;
         uint32_t v0[32], v1[32];
         tc_ld32(tacc, v0);
@@ -203,7 +209,7 @@
         }
         tc_fence_before();
         __syncwarp();
-        if (lane == 0) mbar_arrive(bar_tempty + 8 * buf);
+        if (lane == 0) mbar_arrive(bar_tempty_h);
         uint32_t xpack = 0u, xflag = 3u | ((uint32_t)done << 8), xpen = 0u, xcont = 0u;
         if (valid && !done) {
           float eos = 0.f, eoc = 0.f, cont = 0.f;

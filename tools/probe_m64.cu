@@ -1,5 +1,6 @@
 // Where do the rows of an M = 64 tcgen05.mma accumulator (cta_group::1) land in tensor memory?
 // A[r][0] = r (all other elements zero), B[n][0] = 1  ->  D[r][n] = r.  All 128 lanes x 32 columns are dumped.
+// Second pass: the same M = 64 product with the accumulator address moved by 16 lanes.
 // build: nvcc -gencode arch=compute_100a,code=sm_100a -I sketch_rnn_b200/csrc -o tools/probe_m64 tools/probe_m64.cu -lcuda
 #include <cuda.h>
 #include <cuda_bf16.h>
@@ -7,7 +8,7 @@
 #include <stdio.h>
 #include "tc_ptx.cuh"
 
-__global__ void __launch_bounds__(128, 1) probe(float *out, int M) {
+__global__ void __launch_bounds__(128, 1) probe(float *out, int M, int lane_off) {
   extern __shared__ uint8_t raw[];
   const uint32_t base = (smem_u32(raw) + 1023u) & ~1023u;
   uint8_t *gen = raw + (base - smem_u32(raw));
@@ -41,7 +42,7 @@ __global__ void __launch_bounds__(128, 1) probe(float *out, int M) {
   tc_fence_after();
   if (threadIdx.x == 0) {
     const uint32_t idesc = make_idesc_bf16(M, 32, false, false);
-    tc_mma_bf16(tm, make_desc(sA, 0, 1024), make_desc(sB, 0, 1024), idesc, 0u);
+    tc_mma_bf16(tm + ((uint32_t)lane_off << 16), make_desc(sA, 0, 1024), make_desc(sB, 0, 1024), idesc, 0u);
     tc_commit(bar);
   }
   mbar_wait(bar, 0);
@@ -57,13 +58,14 @@ __global__ void __launch_bounds__(128, 1) probe(float *out, int M) {
 int main() {
   float *d, h[128 * 32];
   cudaMalloc(&d, sizeof(h));
-  for (int M = 64; M <= 128; M += 64) {
+  for (int pass = 0; pass < 3; ++pass) {
+    const int M = pass == 2 ? 128 : 64, lane_off = pass == 1 ? 16 : 0;
     cudaFuncSetAttribute(probe, cudaFuncAttributeMaxDynamicSharedMemorySize, 40000);
-    probe<<<1, 128, 40000>>>(d, M);
+    probe<<<1, 128, 40000>>>(d, M, lane_off);
     cudaError_t e = cudaDeviceSynchronize();
     if (e != cudaSuccess) { printf("M=%d: %s\n", M, cudaGetErrorString(e)); return 1; }
     cudaMemcpy(h, d, sizeof(h), cudaMemcpyDeviceToHost);
-    printf("M=%d: lane -> D row (column 0 | column 5)\n", M);
+    printf("M=%d, accumulator lane offset %d: lane -> D row (column 0 | column 5)\n", M, lane_off);
     for (int l = 0; l < 128; ++l) printf("%s%3d:%4.0f|%4.0f", (l % 8) ? "  " : "\n", l, h[l * 32], h[l * 32 + 5]);
     printf("\n");
   }
