@@ -161,11 +161,11 @@ sample_tp_kernel(const __grid_constant__ CUtensorMap tmW0, const __grid_constant
   const uint32_t s_xs = s_xa + TP_KBLK_BYTES;
   const uint32_t bars = s_xs + 2 * TP_M * 8;
   const uint32_t bar_full = bars, bar_empty = bars + 8 * TP_STAGES;       // ring (5 + 5)
-  const uint32_t bar_tfull = bars + 80, bar_tempty = bars + 96;             // accumulator buffers
-  const uint32_t bar_h0 = bars + 112, bar_h1 = bars + 144;                  // new h k-blocks written (4 each)
-  const uint32_t bar_s0 = bars + 176, bar_s1 = bars + 184, bar_x = bars + 192;  // state final for the next step; next input
-  const uint32_t bar_tfull_h = bars + 200, bar_tempty_h = bars + 208;       // the output projection's own accumulator
-  const uint32_t tmem_holder = bars + 216;
+  const uint32_t bar_tfull = bars + 80, bar_tempty = bars + 104;            // the three gate-chunk accumulators
+  const uint32_t bar_h0 = bars + 128, bar_h1 = bars + 160;                  // new h k-blocks written (4 each)
+  const uint32_t bar_s0 = bars + 192, bar_s1 = bars + 200, bar_x = bars + 208;  // state final for the next step; next input
+  const uint32_t bar_tfull_h = bars + 216, bar_tempty_h = bars + 224;       // the output projection's own accumulator
+  const uint32_t tmem_holder = bars + 232;
   uint8_t *h0_gen = gen, *h1_gen = gen + 2 * TP_HBUF_BYTES, *xa_gen = gen + (s_xa - base);
   uint2 *xs_gen = reinterpret_cast<uint2 *>(gen + (s_xs - base));
 
@@ -185,7 +185,7 @@ sample_tp_kernel(const __grid_constant__ CUtensorMap tmW0, const __grid_constant
   }
   if (threadIdx.x == 0) {
     for (int s = 0; s < TP_STAGES; ++s) { mbar_init(bar_full + 8 * s, 1); mbar_init(bar_empty + 8 * s, 1); }
-    for (int b = 0; b < 2; ++b) { mbar_init(bar_tfull + 8 * b, 1); mbar_init(bar_tempty + 8 * b, 8); }
+    for (int b = 0; b < 3; ++b) { mbar_init(bar_tfull + 8 * b, 1); mbar_init(bar_tempty + 8 * b, 8); }
     for (int k = 0; k < 4; ++k) { mbar_init(bar_h0 + 8 * k, 8); mbar_init(bar_h1 + 8 * k, 8); }
     mbar_init(bar_s0, 4); mbar_init(bar_s1, 4); mbar_init(bar_x, 4);
     mbar_init(bar_tfull_h, 1); mbar_init(bar_tempty_h, 4);
@@ -218,16 +218,13 @@ sample_tp_kernel(const __grid_constant__ CUtensorMap tmW0, const __grid_constant
         ++it;
       };
       for (int step = 0; step < steps; ++step) {
-        // layer 0 (h0 rows of W0 start at row 8; rows 0..7 are the x rows and padding): chunks 0 and 1 take their input-term
-        // stages last, chunks 2 and 3 first -- the order the MMA warp consumes them in
-        for (int c = 0; c < 2; ++c)
+        // layer 0 (h0 rows of W0 start at row 8; rows 0..7 are the x rows and padding): chunks 0..2 take their input-term
+        // stages last, chunk 3 first -- the order the MMA warp consumes them in
+        for (int c = 0; c < 3; ++c)
           for (int j = 0; j < 8; ++j) stage(&tmW0, 256 * c, 8 + TP_BK * j, 4);
-        stage(&tmX0, 0, 0, 4);
-        stage(&tmX0, 256, 0, 4);
-        for (int c = 2; c < 4; ++c) {
-          stage(&tmX0, 256 * c, 0, 4);
-          for (int j = 0; j < 8; ++j) stage(&tmW0, 256 * c, 8 + TP_BK * j, 4);
-        }
+        for (int c = 0; c < 3; ++c) stage(&tmX0, 256 * c, 0, 4);
+        stage(&tmX0, 256 * 3, 0, 4);
+        for (int j = 0; j < 8; ++j) stage(&tmW0, 256 * 3, 8 + TP_BK * j, 4);
         for (int c = 0; c < 4; ++c) {
           for (int j = 0; j < 16; ++j) stage(&tmW1, 256 * c, j < 8 ? TP_H + TP_BK * j : TP_BK * (j - 8), 4);  // h1 rows, then input rows
           stage(&tmX1, 256 * c, 0, 4);
@@ -257,13 +254,17 @@ sample_tp_kernel(const __grid_constant__ CUtensorMap tmW0, const __grid_constant
         tc_commit(bar_empty + 8 * s);
         ++it;
       };
+      // Tensor memory holds four M = 64 accumulators: an M = 64 accumulator fills lanes 0..15 of every lane quarter and
+      // may as well start at lane 16.  Slots 0, 1 (lanes 0.., columns 0 / 256) and 2 (lanes 16.., column 0) rotate over the
+      // gate chunks; lanes 16.., columns 256.. belong to the output projection.
+      auto slot_addr = [&](uint32_t slot) { return slot == 2 ? tmem + (16u << 16) : tmem + slot * 256; };
       auto acc_begin = [&]() -> uint32_t {
-        const uint32_t buf = g & 1;
-        TP_TIMED(1, mbar_wait(bar_tempty + 8 * buf, ((g >> 1) & 1) ^ 1));
+        const uint32_t slot = g % 3;
+        TP_TIMED(1, mbar_wait(bar_tempty + 8 * slot, ((g / 3) & 1) ^ 1));
         tc_fence_after();
-        return tmem + buf * 256;
+        return slot_addr(slot);
       };
-      auto acc_end = [&]() { tc_commit(bar_tfull + 8 * (g & 1)); ++g; };
+      auto acc_end = [&]() { tc_commit(bar_tfull + 8 * (g % 3)); ++g; };
       for (int step = 0; step < steps; ++step) {
         const uint32_t p = step & 1, prev = (step - 1) & 1;
         const uint32_t h0s = s_h0 + p * TP_HBUF_BYTES, h0n = s_h0 + (p ^ 1) * TP_HBUF_BYTES;
@@ -271,23 +272,23 @@ sample_tp_kernel(const __grid_constant__ CUtensorMap tmW0, const __grid_constant
         const uint32_t xa = s_xa + p * 32;  // this step's K = 16 slice of the input operand
         if (step > 0) { TP_TIMED(2, mbar_wait(bar_s0, prev)); tc_fence_after(); }
         {
-          // chunks 0 and 1: both accumulators take their h0 stages first, then -- once the point drawn at the previous step
-          // is known -- their input-term stage (so that the draw overlaps two chunks of products)
-          const uint32_t accA = acc_begin();
-          for (int j = 0; j < 8; ++j) kstage(accA, h0s + (j >> 1) * TP_KBLK_BYTES + (j & 1) * 64, idesc, j == 0, 2);
-          const uint32_t bufA = g & 1, bufB = bufA ^ 1;
-          TP_TIMED(3, mbar_wait(bar_tempty + 8 * bufB, (((g + 1) >> 1) & 1) ^ 1));
-          tc_fence_after();
-          const uint32_t accB = tmem + bufB * 256;
-          for (int j = 0; j < 8; ++j) kstage(accB, h0s + (j >> 1) * TP_KBLK_BYTES + (j & 1) * 64, idesc, j == 0, 2);
+          // chunks 0, 1, 2: three accumulators take their h0 stages first, then -- once the point drawn at the previous step
+          // is known -- their input-term stage (so that the output projection and the draw overlap three chunks of products)
+          uint32_t acc3[3];
+          for (int c = 0; c < 3; ++c) {
+            const uint32_t slot = (g + c) % 3;
+            TP_TIMED(c == 0 ? 1 : 3, mbar_wait(bar_tempty + 8 * slot, (((g + c) / 3) & 1) ^ 1));
+            tc_fence_after();
+            acc3[c] = slot_addr(slot);
+            for (int j = 0; j < 8; ++j) kstage(acc3[c], h0s + (j >> 1) * TP_KBLK_BYTES + (j & 1) * 64, idesc, j == 0, 2);
+          }
           if (step > 0) { TP_TIMED(3, mbar_wait(bar_x, prev)); tc_fence_after(); }
-          kstage(accA, xa, idesc, false, 1);
-          tc_commit(bar_tfull + 8 * bufA);
-          kstage(accB, xa, idesc, false, 1);
-          tc_commit(bar_tfull + 8 * bufB);
-          g += 2;
+          for (int c = 0; c < 3; ++c) {
+            kstage(acc3[c], xa, idesc, false, 1);
+            acc_end();
+          }
         }
-        for (int c = 2; c < 4; ++c) {
+        {
           const uint32_t acc = acc_begin();
           kstage(acc, xa, idesc, true, 1);
           for (int j = 0; j < 8; ++j) kstage(acc, h0s + (j >> 1) * TP_KBLK_BYTES + (j & 1) * 64, idesc, false, 2);
@@ -309,11 +310,11 @@ sample_tp_kernel(const __grid_constant__ CUtensorMap tmW0, const __grid_constant
           acc_end();
         }
         {
-          // output projection: its own accumulator in lanes 16..31 (columns 0 .. nh), so that the draw does not hold one of
-          // the gate chunks' buffers
+          // output projection: its own accumulator in lanes 16..31, columns 256 .. 256 + nh, so that the draw does not hold one
+          // of the gate chunks' buffers
           TP_TIMED(1, mbar_wait(bar_tempty_h, p ^ 1));
           tc_fence_after();
-          const uint32_t acc = tmem + (16u << 16);
+          const uint32_t acc = tmem + (16u << 16) + 256u;
           for (int j = 0; j < 8; ++j) {
             if ((j & 1) == 0) { TP_TIMED(2, mbar_wait(bar_h1 + 8 * (j >> 1), p)); tc_fence_after(); }
             kstage(acc, h1n + (j >> 1) * TP_KBLK_BYTES + (j & 1) * 64, idesc_o, j == 0, 2);

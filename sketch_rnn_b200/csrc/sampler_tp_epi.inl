@@ -22,11 +22,11 @@
     for (uint32_t g = 0; g < nchunks; ++g) {
       const int step = (int)(g / TP_CHUNKS), cs = (int)(g % TP_CHUNKS);
       const int p = step & 1;
-      // gate chunks alternate between the two 256-column accumulators in lanes 0..15 of every quarter; the output
-      // projection has its own accumulator in lanes 16..31 (an M = 64 accumulator may start at lane 16)
+      // gate chunks rotate over three accumulators: lanes 0..15 of every quarter, columns 0 and 256, and lanes 16..31,
+      // column 0 (an M = 64 accumulator may start at lane 16); the output projection has lanes 16..31, columns 256..
       const uint32_t gg = (uint32_t)(step * 8 + cs);  // gate-chunk count
-      const uint32_t buf = (uint32_t)(cs & 1);
-      const uint32_t tacc = cs < 8 ? tq + buf * 256 : tq;
+      const uint32_t buf = gg % 3;
+      const uint32_t tacc = cs < 8 ? (buf == 2 ? tq + (16u << 16) : tq + buf * 256) : tq + 256u;
       if (cs == 0) {  // this step's input point (drawn by group 0 after the previous output projection)
         if (step > 0) mbar_wait(bar_x, (uint32_t)((step - 1) & 1));
         const uint2 xv = xs_gen[p * TP_M + r];
@@ -36,7 +36,7 @@
         holdA = (xs_gen[p * TP_M + rA].y & 0xffu) == 1u;
         holdB = (xs_gen[p * TP_M + rB].y & 0xffu) == 1u;
       }
-      if (cs < 8) mbar_wait(bar_tfull + 8 * buf, (gg >> 1) & 1);
+      if (cs < 8) mbar_wait(bar_tfull + 8 * buf, (gg / 3) & 1);
       else mbar_wait(bar_tfull_h, (uint32_t)p);
       tc_fence_after();
       if (cs < 8) {
