@@ -209,11 +209,13 @@ sample_tp_kernel(const __grid_constant__ CUtensorMap tmW0, const __grid_constant
     // ---- weight stream: the same sequence of stages every step, as far ahead as the ring allows ----
     if (elect_one()) {
       int it = 0;
-      auto stage = [&](const CUtensorMap *tm, int n0, int k0, int boxes) {
+      // box_bytes: TP_CHUNK_BYTES for the weight maps (32 k rows per box), half of it for the input-term maps (16 rows:
+      // their single product reads no more); the 64-column chunks of a stage stay TP_CHUNK_BYTES apart either way
+      auto stage = [&](const CUtensorMap *tm, int n0, int k0, int boxes, int box_bytes = TP_CHUNK_BYTES) {
         const int s = it % TP_STAGES, ph = (it / TP_STAGES) & 1;
         mbar_wait(bar_empty + 8 * s, ph ^ 1);
         const uint32_t sb = s_ring + s * TP_STAGE_BYTES;
-        mbar_expect_tx(bar_full + 8 * s, boxes * TP_CHUNK_BYTES);
+        mbar_expect_tx(bar_full + 8 * s, boxes * box_bytes);
         for (int c = 0; c < boxes; ++c) tma_load_2d(sb + c * TP_CHUNK_BYTES, tm, bar_full + 8 * s, n0 + 64 * c, k0);
         ++it;
       };
@@ -222,15 +224,15 @@ sample_tp_kernel(const __grid_constant__ CUtensorMap tmW0, const __grid_constant
         // stages last, chunk 3 first -- the order the MMA warp consumes them in
         for (int c = 0; c < 3; ++c)
           for (int j = 0; j < 8; ++j) stage(&tmW0, 256 * c, 8 + TP_BK * j, 4);
-        for (int c = 0; c < 3; ++c) stage(&tmX0, 256 * c, 0, 4);
-        stage(&tmX0, 256 * 3, 0, 4);
+        for (int c = 0; c < 3; ++c) stage(&tmX0, 256 * c, 0, 4, TP_CHUNK_BYTES / 2);
+        stage(&tmX0, 256 * 3, 0, 4, TP_CHUNK_BYTES / 2);
         for (int j = 0; j < 8; ++j) stage(&tmW0, 256 * 3, 8 + TP_BK * j, 4);
         for (int c = 0; c < 4; ++c) {
           for (int j = 0; j < 16; ++j) stage(&tmW1, 256 * c, j < 8 ? TP_H + TP_BK * j : TP_BK * (j - 8), 4);  // h1 rows, then input rows
-          stage(&tmX1, 256 * c, 0, 4);
+          stage(&tmX1, 256 * c, 0, 4, TP_CHUNK_BYTES / 2);
         }
         for (int j = 0; j < 8; ++j) stage(&tmWo, 0, TP_BK * j, nhb);
-        stage(&tmXo, 0, 0, nhb);
+        stage(&tmXo, 0, 0, nhb, TP_CHUNK_BYTES / 2);
       }
     }
   } else if (warp == 1) {
@@ -362,12 +364,13 @@ int sk_sample_tp(skrnn_handle *h, cudaStream_t st, int n, int steps, float temp_
     dims[1] = 2 * TP_H;
     SK_TRY(sk_make_tmap(&tmW1, 2, wp1, 2, dims, str, box));
     dims[1] = TP_XROWS;
-    SK_TRY(sk_make_tmap(&tmX0, 2, wx0, 2, dims, str, box));
-    SK_TRY(sk_make_tmap(&tmX1, 2, wx1, 2, dims, str, box));
+    uint32_t boxx[2] = {64, 16};  // the input-term images feed one K = 16 product per accumulator
+    SK_TRY(sk_make_tmap(&tmX0, 2, wx0, 2, dims, str, boxx));
+    SK_TRY(sk_make_tmap(&tmX1, 2, wx1, 2, dims, str, boxx));
     uint64_t dimo[2] = {(uint64_t)h->NOUTP, (uint64_t)TP_H}, stro[1] = {(uint64_t)h->NOUTP * 2};
     SK_TRY(sk_make_tmap(&tmWo, 2, h->params_bf + h->pbf_out_w, 2, dimo, stro, box));
     uint64_t dimx[2] = {(uint64_t)TP_XO_PITCH, (uint64_t)TP_XROWS}, strx[1] = {(uint64_t)TP_XO_PITCH * 2};
-    SK_TRY(sk_make_tmap(&tmXo, 2, wxo, 2, dimx, strx, box));
+    SK_TRY(sk_make_tmap(&tmXo, 2, wxo, 2, dimx, strx, boxx));
   }
   TpArgs a = {};
   a.n = n; a.steps = steps; a.M = h->M; a.NOUT = h->NOUT; a.nh = (h->NOUT + 63) / 64 * 64;
