@@ -10,9 +10,13 @@
 //     still read the old one); the cell state c stays in global memory, one row-contiguous slice per thread;
 //   * the weights (bf16, gate-interleaved columns, 1.6 MB for the stack) stream from L2 through a five-stage TMA ring
 //     (16 KB stages), once per step and CTA: they are the B operand, M = 64 sketches x N = 256 gate columns per accumulator;
-//   * warp 0 streams, warp 1 issues tcgen05.mma, eight epilogue warps in two groups (one per accumulator buffer in tensor
-//     memory) run the LSTM cell update straight from tensor memory, and after the output projection the per-sketch draw
-//     (softmax, temperature, categorical draws, bivariate normal) whose point is the next step's input;
+//   * warp 0 streams, warp 1 issues tcgen05.mma, eight epilogue warps run the LSTM cell update straight from tensor
+//     memory (both groups of four split every chunk: a step is a chain of dependent chunks, so a chunk's latency counts),
+//     and after the output projection the per-sketch draw (softmax, temperature, categorical draws, bivariate normal)
+//     whose point is the next step's input;
+//   * tensor memory holds four M = 64 accumulators of 256 columns (such an accumulator fills lanes 0..15 of every lane
+//     quarter and may equally start at lane 16: tools/probe_m64.cu): three rotate over the gate chunks, the fourth belongs
+//     to the output projection, so the draw blocks no products and layer 0 opens three chunks before it needs the point;
 //   * the input point and the bias ride in one extra K = 16 product per accumulator: operand columns (dx, dy, eos, eoc,
 //     cont, 1, 1) against the rows (W_dx, W_dy, W_eos, W_eoc, W_cont, bias rounded to bf16, the rounding's remainder),
 //     so that the epilogue reads nothing but tensor memory and the cell state;
