@@ -3,7 +3,7 @@ import collections, os, re, subprocess, sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 bd = os.path.join(ROOT, "sketch_rnn_b200", "build")
 want = re.compile(r"^(UTC\w*MMA|UTCBAR|LDTM|STTM|UTMALDG|UTMASTG|UBLKCP|STAS|UTMAPF|UTMACMDFLUSH|SYNCS|UCGABAR_\w+|HMMA|LDGSTS|MUFU|FENCE|MEMBAR|REDG?|ATOMG?|CCTL)")
-COLS = ["UTC*MMA", "LDTM", "STTM", "UTMALDG", "UTMASTG", "UBLKCP", "STAS", "SYNCS", "UCGABAR", "HMMA"]
+COLS = ["UTC*MMA", "LDTM", "STTM", "UTMALDG", "UTMASTG", "UBLKCP", "STAS", "SYNCS", "UCGABAR", "LDGSTS", "FFMA2", "HMMA"]
 print("| object | " + " | ".join(COLS) + " |")
 print("|---|" + "---:|" * len(COLS))
 for f in sorted(os.listdir(bd)):
@@ -22,4 +22,5 @@ for f in sorted(os.listdir(bd)):
 print()
 print("UTC*MMA = tcgen05.mma; LDTM / STTM = tcgen05.ld / st; UTMALDG / UTMASTG = TMA tensor load / store; UBLKCP = bulk copy")
 print("(shared memory -> peer CTA's shared memory in rnn1_tc); STAS = st.async (store + transaction count on the receiver's")
-print("mbarrier, sampler_cl); SYNCS = mbarrier operations; UCGABAR = barrier.cluster; HMMA = legacy mma.sync (none).")
+print("mbarrier, sampler_cl); SYNCS = mbarrier operations; UCGABAR = barrier.cluster; LDGSTS = cp.async (the streaming sampler's")
+print("weight ring); FFMA2 = two fp32 fused multiply-adds per instruction (same sampler); HMMA = legacy mma.sync (none).")
