@@ -251,7 +251,6 @@ __global__ void __launch_bounds__(512) sample_kernel(SampArgs a) {
       } else {
         float az[SB], hold[SB], ar[SB];
         if (act) {  // gates r, u on [x ; h]
-#pragma unroll
           float g2[SB][2];
 #pragma unroll
           for (int r = 0; r < SB; ++r) { g2[r][0] = 0.f; g2[r][1] = 0.f; hold[r] = AT[(size_t)(I + u) * SP + r]; }

@@ -9,7 +9,6 @@
     const bool active = lane < 16;
     const int r = 16 * q + (lane & 15);
     const int sk = row0 + r;
-    const bool valid = active && sk < a.n;
     const uint32_t tq = tmem + ((uint32_t)(32 * q) << 16);
     const uint32_t swz = (uint32_t)(r & 7);
     // the cell update's view of the quarter's rows (tcgen05.ld.16x256b): thread (t4 = lane / 4, m4 = lane % 4), rows rA, rB
