@@ -383,6 +383,31 @@ def test_throughput_sampler_stop_determinism_and_sharding(H, L):
     h.close()
 
 
+@pytest.mark.parametrize("n,steps,stop", [(64, 1, False), (65, 2, False), (127, 3, True), (9600, 5, False),
+                                            (20000, 4, True), (64, 301, False)])
+def test_persistent_sampler_edge_shapes(n, steps, stop):
+    """sample_tp_kernel at the edges of its launch shape: one step, a one-row second CTA, more CTAs than SMs (two and
+    three waves), an odd number of steps beyond 300; and the same sketches drawn again as the tail of a 70-sketch
+    call (other CTA, other rows of it) are bit-identical."""
+    cfg = so.Config(model="lstm", rnn_size=256, num_layers=2, num_mixture=24)
+    params = so.init_params(cfg, seed=21, trained_like=True)
+    h = make_handle(cfg, params, precision="bf16")
+    s, l, _ = h.sample(n, steps, 0.7, 0.7, stop, seed=3)
+    s, l = s.cpu().numpy(), l.cpu().numpy()
+    assert np.all(np.isfinite(s)) and np.all((l >= 1) & (l <= steps))
+    if not stop:
+        assert np.all(l == steps)
+    for i in (0, n // 2, n - 1):
+        k = l[i]
+        assert np.all(s[i, :k, 2:].sum(axis=1) == 1.0) and np.all(s[i, k:] == 0)
+        if stop and k < steps:
+            assert s[i, k - 1, 3] == 1.0
+    if n >= 70:
+        s2, l2, _ = h.sample(70, steps, 0.7, 0.7, stop, seed=3, sketch0=n - 70)
+        assert np.array_equal(s2.cpu().numpy(), s[n - 70:]) and np.array_equal(l2.cpu().numpy(), l[n - 70:])
+    h.close()
+
+
 def test_errors_are_reported_not_thrown():
     from sketch_rnn_b200 import _lib
     with pytest.raises(Exception, match="model type not supported"):
