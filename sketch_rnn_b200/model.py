@@ -104,13 +104,32 @@ class Model(object):
         assert st.shape == (self.args.num_layers, B, self.state_size), st.shape
         return st
 
+    def _train_state(self, state, B):
+        """The [L, B, S] state buffer of a training step.  train.py feeds back the final_state tuple of the previous
+        step (train.py:84-86): that tuple's arrays are views of this model's page-locked buffer, which the step updates in
+        place, so nothing is stacked or copied.  Any other state is copied in.  (A caller that keeps a returned
+        final_state across later steps must copy it: the views follow the buffer.)"""
+        shape = (self.args.num_layers, B, self.state_size)
+        buf = getattr(self, "_st_buf", None)
+        if buf is None or buf.shape != shape:
+            try:
+                import torch
+                buf = torch.empty(shape, dtype=torch.float32).pin_memory().numpy()
+            except Exception:
+                buf = np.empty(shape, dtype=np.float32)
+            self._st_buf, self._st_tuple = buf, None
+        if state is None or state is not self._st_tuple:
+            buf[...] = self._stack_state(state, B)
+        return buf
+
     def train_step(self, x, y, state=None):
         """One sess.run([cost, cost_shape, cost_pen, final_state, train_op], feed) (train.py:85-86)."""
         x = np.ascontiguousarray(x, dtype=np.float32)
-        st = self._stack_state(state, x.shape[0])
+        st = self._train_state(state, x.shape[0])
         self._step += 1
         losses = self.handle.train_step_host(x, y, st, self.lr, seed=(self.seed << 32) + self._step)
-        return float(losses[0]), float(losses[1]), float(losses[2]), tuple(st[l] for l in range(st.shape[0]))
+        self._st_tuple = tuple(st[l] for l in range(st.shape[0]))
+        return float(losses[0]), float(losses[1]), float(losses[2]), self._st_tuple
 
     def forward(self, x, state=None):
         """sess.run([pi, mu1, mu2, sigma1, sigma2, corr, pen, final_state], feed) (model.py:215-217)."""
