@@ -63,6 +63,27 @@ def test_infer_mutates_args_and_sample_signature():
         Model(_args(model="foo"))
 
 
+def test_state_fed_back_in_place_equals_state_fed_back_as_copies():
+    """train.py feeds the final_state of a step into the next one (train.py:84-86).  Model.train_step keeps that state in
+    one buffer it updates in place; feeding copies (any other tuple) must give the same losses and states."""
+    from sketch_rnn_b200.model import Model
+    x, y = so.synthetic_batch(6, 8, seed=3)
+    ma, mb = Model(_args(), precision="f32", seed=5), Model(_args(), precision="f32", seed=5)
+    sa = sb = None
+    for i in range(4):
+        ca = ma.train_step(x, y, sa)
+        cb = mb.train_step(x, y, sb)
+        sa = ca[3]                                   # the returned tuple itself: in place
+        sb = tuple(np.array(s) for s in cb[3])       # copies: stacked and copied in
+        assert ca[:3] == cb[:3], (i, ca[:3], cb[:3])
+        for u, v in zip(sa, sb):
+            assert np.array_equal(u, v)
+    # a fresh zero state after a run of steps is honoured (train.py:80 resets the state every epoch)
+    ca = ma.train_step(x, y, ma.zero_state(6))
+    cb = mb.train_step(x, y, None)
+    assert ca[:3] == cb[:3]
+
+
 def test_checkpoint_roundtrip(tmp_path):
     from sketch_rnn_b200.model import Model, Saver, Session, get_checkpoint_state
     args = _args()
