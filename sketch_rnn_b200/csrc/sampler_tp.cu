@@ -118,6 +118,34 @@ __device__ __forceinline__ void tp_ld16x8_issue(uint32_t taddr, uint32_t (&r)[32
       : "r"(taddr));
 }
 
+// ---- cluster pieces (sample_tp_kernel<., C > 1>: the gate columns of a tile split over C CTAs) ----
+__device__ __forceinline__ uint32_t tp_mapa(uint32_t addr, uint32_t rank) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(addr), "r"(rank));
+  return r;
+}
+// 16 bytes into the shared memory of a CTA of the cluster; the store adds its bytes to the transaction count of the
+// mbarrier at `bar` in that CTA
+__device__ __forceinline__ void tp_st_async_v4(uint32_t dst, uint4 v, uint32_t bar) {
+  asm volatile("st.async.shared::cluster.mbarrier::complete_tx::bytes.v4.b32 [%0], {%1, %2, %3, %4}, [%5];"
+               ::"r"(dst), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w), "r"(bar) : "memory");
+}
+__device__ __forceinline__ void tp_mbar_wait_cluster(uint32_t bar, uint32_t parity) {
+  uint32_t done = 0;
+  while (!done) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n"
+        "selp.u32 %0, 1, 0, p;\n"
+        "}\n" : "=r"(done) : "r"(bar), "r"(parity) : "memory");
+  }
+}
+__device__ __forceinline__ void tp_cluster_sync() {
+  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+
 // The wait for tp_ld16x8_issue: it also ties the destination registers to itself (the compiler must not consume them
 // earlier: it cannot see that the load completes asynchronously).
 __device__ __forceinline__ void tp_ld_wait(uint32_t (&r)[32]) {
@@ -138,7 +166,11 @@ __device__ __forceinline__ float tp_cell(uint32_t vi, uint32_t vj, uint32_t vf, 
   return tanh_approx(cn) * og;
 }
 
-template <bool DBG>
+// C: CTAs per 64-sketch tile (cluster size).  C = 1: a CTA computes all four 256-column gate chunks of a layer.  C = 2, 4
+// (fewer tiles than a wave of SMs): rank r computes chunks [r * 4 / C, (r + 1) * 4 / C), streams only their weights, and
+// sends every new h block into all C operand buffers with st.async (the bytes complete the receivers' mbarriers); output
+// projection and draw run redundantly in every CTA (identical operands, identical bits), rank 0 writes the strokes.
+template <bool DBG, int C>
 __global__ void __launch_bounds__(TP_THREADS, 1)
 sample_tp_kernel(const __grid_constant__ CUtensorMap tmW0, const __grid_constant__ CUtensorMap tmW1,
                  const __grid_constant__ CUtensorMap tmWo, const __grid_constant__ CUtensorMap tmX0,
@@ -163,7 +195,11 @@ sample_tp_kernel(const __grid_constant__ CUtensorMap tmW0, const __grid_constant
   uint2 *xs_gen = reinterpret_cast<uint2 *>(gen + (s_xs - base));
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int row0 = blockIdx.x * TP_M;
+  constexpr int CH = 4 / C;      // gate chunks of a layer computed by this CTA
+  constexpr int NOPEN = CH < 3 ? CH : 3;  // layer-0 chunks opened before the drawn point is needed
+  uint32_t rank = 0;
+  if constexpr (C > 1) asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(rank));
+  const int row0 = (blockIdx.x / C) * TP_M;
   const int steps = a.steps;
 
   for (int i = threadIdx.x; i < 4 * TP_HBUF_BYTES / 16; i += TP_THREADS) reinterpret_cast<uint4 *>(gen)[i] = make_uint4(0, 0, 0, 0);
@@ -179,7 +215,9 @@ sample_tp_kernel(const __grid_constant__ CUtensorMap tmW0, const __grid_constant
   if (threadIdx.x == 0) {
     for (int s = 0; s < TP_STAGES; ++s) { mbar_init(bar_full + 8 * s, 1); mbar_init(bar_empty + 8 * s, 1); }
     for (int b = 0; b < 3; ++b) { mbar_init(bar_tfull + 8 * b, 1); mbar_init(bar_tempty + 8 * b, 8); }
-    for (int k = 0; k < 4; ++k) { mbar_init(bar_h0 + 8 * k, 8); mbar_init(bar_h1 + 8 * k, 8); }
+    // new h blocks: written by this CTA's 8 epilogue warps (C = 1), or delivered by st.async from the chunk's owner and
+    // counted in bytes (the MMA thread arms them every step)
+    for (int k = 0; k < 4; ++k) { mbar_init(bar_h0 + 8 * k, C == 1 ? 8 : 1); mbar_init(bar_h1 + 8 * k, C == 1 ? 8 : 1); }
     mbar_init(bar_s0, 4); mbar_init(bar_s1, 4); mbar_init(bar_x, 4);
     mbar_init(bar_tfull_h, 1); mbar_init(bar_tempty_h, 4);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -194,6 +232,7 @@ sample_tp_kernel(const __grid_constant__ CUtensorMap tmW0, const __grid_constant
   fence_proxy_async_smem();  // the zeroed operand blocks are read by the tensor core
   tc_fence_before();
   __syncthreads();
+  if constexpr (C > 1) tp_cluster_sync();  // nobody sends into a CTA whose barriers are not initialised
   tc_fence_after();
   const uint32_t tmem = *reinterpret_cast<volatile uint32_t *>(gen + (tmem_holder - base));
   const int nhb = a.nh / 64;  // 64-column boxes of the output projection
@@ -213,16 +252,21 @@ sample_tp_kernel(const __grid_constant__ CUtensorMap tmW0, const __grid_constant
         ++it;
       };
       for (int step = 0; step < steps; ++step) {
-        // layer 0 (h0 rows of W0 start at row 8; rows 0..7 are the x rows and padding): chunks 0..2 take their input-term
-        // stages last, chunk 3 first -- the order the MMA warp consumes them in
-        for (int c = 0; c < 3; ++c)
-          for (int j = 0; j < 8; ++j) stage(&tmW0, 256 * c, 8 + TP_BK * j, 4);
-        for (int c = 0; c < 3; ++c) stage(&tmX0, 256 * c, 0, 4, TP_CHUNK_BYTES / 2);
-        stage(&tmX0, 256 * 3, 0, 4, TP_CHUNK_BYTES / 2);
-        for (int j = 0; j < 8; ++j) stage(&tmW0, 256 * 3, 8 + TP_BK * j, 4);
-        for (int c = 0; c < 4; ++c) {
-          for (int j = 0; j < 16; ++j) stage(&tmW1, 256 * c, j < 8 ? TP_H + TP_BK * j : TP_BK * (j - 8), 4);  // h1 rows, then input rows
-          stage(&tmX1, 256 * c, 0, 4, TP_CHUNK_BYTES / 2);
+        // layer 0 (h0 rows of W0 start at row 8; rows 0..7 are the x rows and padding): the h0 stages of the first NOPEN
+        // chunks, then their input-term stages, then the remaining chunks -- the order the MMA warp consumes them in.  Every
+        // accumulator sums h stages first and the input term last, whichever cluster size computes it: a sketch's
+        // points do not depend on how many CTAs share its tile
+        for (int i = 0; i < NOPEN; ++i)
+          for (int j = 0; j < 8; ++j) stage(&tmW0, 256 * (int)(rank * CH + i), 8 + TP_BK * j, 4);
+        for (int i = 0; i < NOPEN; ++i) stage(&tmX0, 256 * (int)(rank * CH + i), 0, 4, TP_CHUNK_BYTES / 2);
+        for (int i = NOPEN; i < CH; ++i) {
+          for (int j = 0; j < 8; ++j) stage(&tmW0, 256 * (int)(rank * CH + i), 8 + TP_BK * j, 4);
+          stage(&tmX0, 256 * (int)(rank * CH + i), 0, 4, TP_CHUNK_BYTES / 2);
+        }
+        for (int i = 0; i < CH; ++i) {
+          const int n0 = 256 * (int)(rank * CH + i);
+          for (int j = 0; j < 16; ++j) stage(&tmW1, n0, j < 8 ? TP_H + TP_BK * j : TP_BK * (j - 8), 4);  // h1 rows, then input rows
+          stage(&tmX1, n0, 0, 4, TP_CHUNK_BYTES / 2);
         }
         for (int j = 0; j < 8; ++j) stage(&tmWo, 0, TP_BK * j, nhb);
         stage(&tmXo, 0, 0, nhb, TP_CHUNK_BYTES / 2);
@@ -260,17 +304,32 @@ sample_tp_kernel(const __grid_constant__ CUtensorMap tmW0, const __grid_constant
         return slot_addr(slot);
       };
       auto acc_end = [&]() { tc_commit(bar_tfull + 8 * (g % 3)); ++g; };
+      // a new h block is complete: C = 1: the epilogue warps arrived; C > 1: its bytes have landed (st.async from the owner)
+      auto wait_h = [&](uint32_t bar, uint32_t par) {
+        if constexpr (C == 1) {
+          TP_TIMED(2, mbar_wait(bar, par));
+        } else {
+          TP_TIMED(2, tp_mbar_wait_cluster(bar, par));
+          fence_proxy_async_smem();  // written by st.async stores: order them before the tensor core's reads
+        }
+        tc_fence_after();
+      };
       for (int step = 0; step < steps; ++step) {
         const uint32_t p = step & 1, prev = (step - 1) & 1;
         const uint32_t h0s = s_h0 + p * TP_HBUF_BYTES, h0n = s_h0 + (p ^ 1) * TP_HBUF_BYTES;
         const uint32_t h1s = s_h1 + p * TP_HBUF_BYTES, h1n = s_h1 + (p ^ 1) * TP_HBUF_BYTES;
         const uint32_t xa = s_xa + p * 32;  // this step's K = 16 slice of the input operand
+        if constexpr (C > 1) {
+          // this step's h blocks arrive as bytes: one arrival (this one) plus a block's 8 KB complete a barrier's phase.
+          // Every barrier's previous phase is complete: this thread waited for all eight of them during the previous step.
+          for (int k = 0; k < 4; ++k) { mbar_expect_tx(bar_h0 + 8 * k, TP_KBLK_BYTES); mbar_expect_tx(bar_h1 + 8 * k, TP_KBLK_BYTES); }
+        }
         if (step > 0) { TP_TIMED(2, mbar_wait(bar_s0, prev)); tc_fence_after(); }
         {
-          // chunks 0, 1, 2: three accumulators take their h0 stages first, then -- once the point drawn at the previous step
-          // is known -- their input-term stage (so that the output projection and the draw overlap three chunks of products)
-          uint32_t acc3[3];
-          for (int c = 0; c < 3; ++c) {
+          // the first NOPEN chunks: their accumulators take their h0 stages first, then -- once the point drawn at the
+          // previous step is known -- their input-term stage (so that the output projection and the draw overlap products)
+          uint32_t acc3[NOPEN];
+          for (int c = 0; c < NOPEN; ++c) {
             const uint32_t slot = (g + c) % 3;
             TP_TIMED(c == 0 ? 1 : 3, mbar_wait(bar_tempty + 8 * slot, (((g + c) / 3) & 1) ^ 1));
             tc_fence_after();
@@ -278,26 +337,26 @@ sample_tp_kernel(const __grid_constant__ CUtensorMap tmW0, const __grid_constant
             for (int j = 0; j < 8; ++j) kstage(acc3[c], h0s + (j >> 1) * TP_KBLK_BYTES + (j & 1) * 64, idesc, j == 0, 2);
           }
           if (step > 0) { TP_TIMED(3, mbar_wait(bar_x, prev)); tc_fence_after(); }
-          for (int c = 0; c < 3; ++c) {
+          for (int c = 0; c < NOPEN; ++c) {
             kstage(acc3[c], xa, idesc, false, 1);
             acc_end();
           }
         }
-        {
+        for (int c = NOPEN; c < CH; ++c) {
           const uint32_t acc = acc_begin();
-          kstage(acc, xa, idesc, true, 1);
-          for (int j = 0; j < 8; ++j) kstage(acc, h0s + (j >> 1) * TP_KBLK_BYTES + (j & 1) * 64, idesc, false, 2);
+          for (int j = 0; j < 8; ++j) kstage(acc, h0s + (j >> 1) * TP_KBLK_BYTES + (j & 1) * 64, idesc, j == 0, 2);
+          kstage(acc, xa, idesc, false, 1);
           acc_end();
         }
         if (step > 0) { TP_TIMED(2, mbar_wait(bar_s1, prev)); tc_fence_after(); }
-        for (int c = 0; c < 4; ++c) {
+        for (int c = 0; c < CH; ++c) {
           const uint32_t acc = acc_begin();
           for (int j = 0; j < 16; ++j) {
             if (j < 8) {
               kstage(acc, h1s + (j >> 1) * TP_KBLK_BYTES + (j & 1) * 64, idesc, j == 0, 2);
             } else {
               const int kb = (j - 8) >> 1;
-              if (c == 0 && (j & 1) == 0) { TP_TIMED(2, mbar_wait(bar_h0 + 8 * kb, p)); tc_fence_after(); }
+              if (c == 0 && (j & 1) == 0) wait_h(bar_h0 + 8 * kb, p);
               kstage(acc, h0n + kb * TP_KBLK_BYTES + (j & 1) * 64, idesc, false, 2);
             }
           }
@@ -311,7 +370,7 @@ sample_tp_kernel(const __grid_constant__ CUtensorMap tmW0, const __grid_constant
           tc_fence_after();
           const uint32_t acc = tmem + (16u << 16) + 256u;
           for (int j = 0; j < 8; ++j) {
-            if ((j & 1) == 0) { TP_TIMED(2, mbar_wait(bar_h1 + 8 * (j >> 1), p)); tc_fence_after(); }
+            if ((j & 1) == 0) wait_h(bar_h1 + 8 * (j >> 1), p);
             kstage(acc, h1n + (j >> 1) * TP_KBLK_BYTES + (j & 1) * 64, idesc_o, j == 0, 2);
           }
           kstage(acc, xa, idesc_o, false, 1);  // + output bias
@@ -328,6 +387,7 @@ sample_tp_kernel(const __grid_constant__ CUtensorMap tmW0, const __grid_constant
   }
   tc_fence_before();
   __syncthreads();
+  if constexpr (C > 1) tp_cluster_sync();  // a CTA's shared memory stays up until nobody sends into it any more
   if (warp == 1) tc_dealloc(tmem, 512);
 }
 
@@ -387,14 +447,31 @@ int sk_sample_tp(skrnn_handle *h, cudaStream_t st, int n, int steps, float temp_
     tp_ximage_kernel<<<TP_G / 256, 256, 0, st>>>(wsm[0], bias_il[0], bias_il[1], wx0, wx1, h->params + h->off_out_b, h->NOUT, wxo);
     SK_CUDA(cudaGetLastError());
   }
-  SkLaunch scope(h, st, SK_CAT_SAMPLER);
-  if (a.debug) {
-    SK_CUDA(cudaFuncSetAttribute(sample_tp_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, TP_SMEM));
-    sample_tp_kernel<true><<<(n + TP_M - 1) / TP_M, TP_THREADS, TP_SMEM, st>>>(tmW0, tmW1, tmWo, tmX0, tmX1, tmXo, a);
-  } else {
-    SK_CUDA(cudaFuncSetAttribute(sample_tp_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, TP_SMEM));
-    sample_tp_kernel<false><<<(n + TP_M - 1) / TP_M, TP_THREADS, TP_SMEM, st>>>(tmW0, tmW1, tmWo, tmX0, tmX1, tmXo, a);
+  // Fewer tiles than SMs / C: the gate columns of a tile are split over a cluster of C CTAs (see the kernel).
+  const int tiles = (n + TP_M - 1) / TP_M;
+  int cl = 1;
+  {
+    const char *e = getenv("SKRNN_TP_CLUSTER");  // 1, 2, 4: force; default: the largest split that still fits one wave
+    const int want = e ? atoi(e) : 0;
+    if (want == 1 || want == 2 || want == 4) cl = want;
+    else cl = 4 * tiles <= h->num_sms ? 4 : (2 * tiles <= h->num_sms ? 2 : 1);
   }
+  SkLaunch scope(h, st, SK_CAT_SAMPLER);
+  auto launch = [&](auto kern, int c) -> int {
+    SK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, TP_SMEM));
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)(tiles * c)); cfg.blockDim = dim3(TP_THREADS); cfg.dynamicSmemBytes = TP_SMEM; cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = (unsigned)c; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+    cfg.attrs = at; cfg.numAttrs = 1;
+    SK_CUDA(cudaLaunchKernelEx(&cfg, kern, tmW0, tmW1, tmWo, tmX0, tmX1, tmXo, a));
+    return 0;
+  };
+  if (a.debug && cl == 1) SK_TRY(launch(sample_tp_kernel<true, 1>, 1));
+  else if (cl == 4) SK_TRY(launch(sample_tp_kernel<false, 4>, 4));
+  else if (cl == 2) SK_TRY(launch(sample_tp_kernel<false, 2>, 2));
+  else SK_TRY(launch(sample_tp_kernel<false, 1>, 1));
   SK_CUDA(cudaGetLastError());
   return 0;
 }

@@ -17,16 +17,19 @@
     const bool validA = skA < a.n, validB = skB < a.n;
     int pen = 3, done = 0;
     bool hold = false, holdA = false, holdB = false;
-    const uint32_t nchunks = (uint32_t)steps * TP_CHUNKS;
+    // per step this CTA has CH chunks of layer 0, CH of layer 1 (chunk rank * CH + i of the layer) and the output projection
+    constexpr int NACC = 2 * CH + 1;
+    const uint32_t nchunks = (uint32_t)steps * NACC;
     for (uint32_t g = 0; g < nchunks; ++g) {
-      const int step = (int)(g / TP_CHUNKS), cs = (int)(g % TP_CHUNKS);
+      const int step = (int)(g / NACC), ci = (int)(g % NACC);
+      const int cs = ci < 2 * CH ? 0 : 8;   // 8: the output projection
       const int p = step & 1;
       // gate chunks rotate over three accumulators: lanes 0..15 of every quarter, columns 0 and 256, and lanes 16..31,
       // column 0 (an M = 64 accumulator may start at lane 16); the output projection has lanes 16..31, columns 256..
-      const uint32_t gg = (uint32_t)(step * 8 + cs);  // gate-chunk count
+      const uint32_t gg = (uint32_t)(step * 2 * CH + ci);  // gate-chunk count
       const uint32_t buf = gg % 3;
       const uint32_t tacc = cs < 8 ? (buf == 2 ? tq + (16u << 16) : tq + buf * 256) : tq + 256u;
-      if (cs == 0) {  // this step's input point (drawn by group 0 after the previous output projection)
+      if (ci == 0) {  // this step's input point (drawn by group 0 after the previous output projection)
         if (step > 0) mbar_wait(bar_x, (uint32_t)((step - 1) & 1));
         const uint2 xv = xs_gen[p * TP_M + r];
         pen = (int)(xv.y & 0xffu);
@@ -39,9 +42,10 @@
       else mbar_wait(bar_tfull_h, (uint32_t)p);
       tc_fence_after();
       if (cs < 8) {
-        const int layer = cs >> 2, c = cs & 3;
-        if (cs == 7 && e == 0) {
-          // every product of layer 1 is complete: nobody reads this step's new h0 any more, held rows get the old state back
+        const int layer = ci / CH, c = (int)rank * CH + ci % CH;
+        if (ci == 2 * CH - 1 && e == 0) {
+          // every product of layer 1 (of this CTA) is complete: nobody reads this step's new h0 any more, held rows get the
+          // old state back
           if (active && hold) {
             const uint4 *src = reinterpret_cast<const uint4 *>(h0_gen + p * TP_HBUF_BYTES + r * 128);
             uint4 *dst = reinterpret_cast<uint4 *>(h0_gen + (p ^ 1) * TP_HBUF_BYTES + r * 128);
@@ -93,14 +97,29 @@
         pass(1, vb, cA1, cB1);
         {
           const uint32_t chunk = (uint32_t)(2 * m4 + e);
-          *reinterpret_cast<uint4 *>(hblk + rA * 128 + ((chunk ^ (uint32_t)(rA & 7)) << 4)) = make_uint4(hA[0], hA[1], hA[2], hA[3]);
-          *reinterpret_cast<uint4 *>(hblk + rB * 128 + ((chunk ^ (uint32_t)(rB & 7)) << 4)) = make_uint4(hB[0], hB[1], hB[2], hB[3]);
+          const uint32_t offA = (uint32_t)(rA * 128) + ((chunk ^ (uint32_t)(rA & 7)) << 4);
+          const uint32_t offB = (uint32_t)(rB * 128) + ((chunk ^ (uint32_t)(rB & 7)) << 4);
+          if constexpr (C == 1) {
+            *reinterpret_cast<uint4 *>(hblk + offA) = make_uint4(hA[0], hA[1], hA[2], hA[3]);
+            *reinterpret_cast<uint4 *>(hblk + offB) = make_uint4(hB[0], hB[1], hB[2], hB[3]);
+          } else {
+            // into every CTA's operand buffer (this one included); the bytes complete the receivers' h-block barriers
+            const uint32_t blk = (layer == 0 ? s_h0 : s_h1) + (uint32_t)((p ^ 1) * TP_HBUF_BYTES + c * TP_KBLK_BYTES);
+            const uint32_t bar = (layer == 0 ? bar_h0 : bar_h1) + 8u * (uint32_t)c;
+#pragma unroll
+            for (int rr = 0; rr < C; ++rr) {
+              const uint32_t dst = (rank + (uint32_t)rr) % C;
+              const uint32_t rb = tp_mapa(bar, dst);
+              tp_st_async_v4(tp_mapa(blk + offA, dst), make_uint4(hA[0], hA[1], hA[2], hA[3]), rb);
+              tp_st_async_v4(tp_mapa(blk + offB, dst), make_uint4(hB[0], hB[1], hB[2], hB[3]), rb);
+            }
+          }
         }
-        fence_proxy_async_smem();  // the new h block is an operand of the tensor core
+        if constexpr (C == 1) fence_proxy_async_smem();  // the new h block is an operand of the tensor core
         tc_fence_before();
         __syncwarp();
         if (lane == 0) {
-          mbar_arrive((layer == 0 ? bar_h0 : bar_h1) + 8 * c);
+          if constexpr (C == 1) mbar_arrive((layer == 0 ? bar_h0 : bar_h1) + 8 * c);
           mbar_arrive(bar_tempty + 8 * buf);
         }
       } else if (e == 1) {
@@ -121,6 +140,7 @@
         //      logits' accumulator lives in lanes 16..31 of the quarter, so those lanes draw ----
         const bool active = lane >= 16;
         const bool valid = active && sk < a.n;
+        const bool writer = rank == 0;  // every CTA of a tile draws the same point; one of them records it
         const int NOUT = a.NOUT, M = a.M;
         uint32_t v0[32], v1[32];
         tc_ld32(tacc, v0);
@@ -167,7 +187,7 @@
         const float pmx = fmaxf(z0, fmaxf(z1, z2));
         const float e0 = __expf(z0 - pmx), e1 = __expf(z1 - pmx), e2 = __expf(z2 - pmx);
         const float ps = e0 + e1 + e2;
-        const bool record = a.mixp != nullptr && valid && !done;
+        const bool record = a.mixp != nullptr && valid && !done && writer;
         float *mo = a.mixp + (record ? ((size_t)sk * steps + step) * NOUT : 0);
         if (record) {  // same record as the exact kernel (include/skrnn.h: mix_params_dev)
           mo[0] = e0 / ps; mo[1] = e1 / ps; mo[2] = e2 / ps;
@@ -223,9 +243,11 @@
           skm_box_muller(u4[2], u4[3], &g1, &g2);
           const float x1 = mu1 + s1 * g1;
           const float x2 = mu2 + s2 * (rho * g1 + sqrtf(fmaxf(0.f, 1.0f - rho * rho)) * g2);
-          float *so = a.strokes + ((size_t)sk * steps + step) * 5;
-          so[0] = x1 * a.data_scale; so[1] = x2 * a.data_scale; so[2] = eos; so[3] = eoc; so[4] = cont;
-          a.lengths[sk] = step + 1;
+          if (writer) {
+            float *so = a.strokes + ((size_t)sk * steps + step) * 5;
+            so[0] = x1 * a.data_scale; so[1] = x2 * a.data_scale; so[2] = eos; so[3] = eoc; so[4] = cont;
+            a.lengths[sk] = step + 1;
+          }
           if (a.stop_if_eoc && eoc > 0.f) done = 1;
           const __nv_bfloat162 xb = __floats2bfloat162_rn(x1, x2);  // the next input, rounded like every operand of this path
           xpack = *reinterpret_cast<const uint32_t *>(&xb);

@@ -292,15 +292,17 @@ def _softmax(z):
     return e / e.sum(axis=1, keepdims=True)
 
 
-@pytest.mark.parametrize("tp,M,n", [("1", 24, 192), ("1", 30, 150), ("0", 24, 192)])
-def test_throughput_sampler_bf16_replayed_by_oracle(monkeypatch, tp, M, n):
+@pytest.mark.parametrize("tp,cl,M,n", [("1", "1", 24, 192), ("1", "2", 24, 192), ("1", "4", 30, 150), ("0", "1", 24, 192)])
+def test_throughput_sampler_bf16_replayed_by_oracle(monkeypatch, tp, cl, M, n):
     """tp = "1": the persistent kernel (sampler_tp.cu; 30 mixtures put the mixture logits across two 32-column pieces of
-    the accumulator, 150 sketches leave the last CTA ragged); "0": the step-by-step kernels of sampler_tc.cu.
+    the accumulator, 150 sketches leave the last tile ragged) with one CTA per 64-sketch tile (cl = "1") or the tile's gate
+    columns split over a cluster of 2 or 4 CTAs; "0": the step-by-step kernels of sampler_tc.cu.
     The tensor-core sampler (bf16 handle, many sketches) is not bit-exact, so it is
     checked in two halves: (1) its per-step mixture parameters against the fp64 oracle replaying the
     sampler's OWN trajectory step by step (state hold on eoc included) within the bf16 tolerance 2e-2;
     (2) its draws against a NumPy redo of model.py:219-261 from the dumped parameters and uniforms."""
     monkeypatch.setenv("SKRNN_SAMPLE_TP", tp)
+    monkeypatch.setenv("SKRNN_TP_CLUSTER", cl)
     cfg = so.Config(model="lstm", rnn_size=256, num_layers=2, num_mixture=M)
     params = so.init_params(cfg, seed=7, trained_like=True)
     h = make_handle(cfg, params, precision="bf16")
@@ -383,12 +385,16 @@ def test_throughput_sampler_stop_determinism_and_sharding(H, L):
     h.close()
 
 
-@pytest.mark.parametrize("n,steps,stop", [(64, 1, False), (65, 2, False), (127, 3, True), (9600, 5, False),
-                                            (20000, 4, True), (64, 301, False)])
-def test_persistent_sampler_edge_shapes(n, steps, stop):
-    """sample_tp_kernel at the edges of its launch shape: one step, a one-row second CTA, more CTAs than SMs (two and
-    three waves), an odd number of steps beyond 300; and the same sketches drawn again as the tail of a 70-sketch
-    call (other CTA, other rows of it) are bit-identical."""
+@pytest.mark.parametrize("n,steps,stop,cl", [(64, 1, False, ""), (65, 2, False, ""), (127, 3, True, ""), (9600, 5, False, ""),
+                                               (20000, 4, True, ""), (64, 301, False, ""), (3000, 7, True, ""),
+                                               (700, 9, False, "1"), (700, 9, False, "2"), (9600, 3, False, "2")])
+def test_persistent_sampler_edge_shapes(monkeypatch, n, steps, stop, cl):
+    """sample_tp_kernel at the edges of its launch shape: one step, a one-row second tile, more CTAs than SMs (two and
+    three waves), an odd number of steps beyond 300, the sketch counts that select clusters of 4 (up to 2368 sketches), 2
+    (up to 4736) and single CTAs by themselves (cl = "") or forced; and the same sketches drawn again as the tail of a
+    70-sketch call (another tile, other rows of it, possibly another cluster size) are bit-identical."""
+    if cl:
+        monkeypatch.setenv("SKRNN_TP_CLUSTER", cl)
     cfg = so.Config(model="lstm", rnn_size=256, num_layers=2, num_mixture=24)
     params = so.init_params(cfg, seed=21, trained_like=True)
     h = make_handle(cfg, params, precision="bf16")
