@@ -449,22 +449,35 @@ int sk_sample_tp(skrnn_handle *h, cudaStream_t st, int n, int steps, float temp_
   }
   // Fewer tiles than SMs / C: the gate columns of a tile are split over a cluster of C CTAs (see the kernel).
   const int tiles = (n + TP_M - 1) / TP_M;
+  auto config = [&](cudaLaunchConfig_t &cfg, cudaLaunchAttribute *at, int c) {
+    cfg = cudaLaunchConfig_t{};
+    cfg.gridDim = dim3((unsigned)(tiles * c)); cfg.blockDim = dim3(TP_THREADS); cfg.dynamicSmemBytes = TP_SMEM; cfg.stream = st;
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = (unsigned)c; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+    cfg.attrs = at; cfg.numAttrs = 1;
+  };
+  // clusters of c CTAs (223 KB of shared memory each) that are resident at once: GPC sizes decide, not SMs / c
+  auto resident = [&](auto kern, int c) -> int {
+    if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, TP_SMEM) != cudaSuccess) { cudaGetLastError(); return 0; }
+    cudaLaunchConfig_t cfg; cudaLaunchAttribute at[1];
+    config(cfg, at, c);
+    int nc = 0;
+    if (cudaOccupancyMaxActiveClusters(&nc, kern, &cfg) != cudaSuccess) { cudaGetLastError(); return 0; }
+    return nc;
+  };
   int cl = 1;
   {
-    const char *e = getenv("SKRNN_TP_CLUSTER");  // 1, 2, 4: force; default: the largest split that still fits one wave
+    const char *e = getenv("SKRNN_TP_CLUSTER");  // 1, 2, 4: force; default: the largest split whose clusters fit one wave
     const int want = e ? atoi(e) : 0;
     if (want == 1 || want == 2 || want == 4) cl = want;
-    else cl = 4 * tiles <= h->num_sms ? 4 : (2 * tiles <= h->num_sms ? 2 : 1);
+    else if (4 * tiles <= h->num_sms && tiles <= resident(sample_tp_kernel<false, 4>, 4)) cl = 4;
+    else if (2 * tiles <= h->num_sms && tiles <= resident(sample_tp_kernel<false, 2>, 2)) cl = 2;
   }
   SkLaunch scope(h, st, SK_CAT_SAMPLER);
   auto launch = [&](auto kern, int c) -> int {
     SK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, TP_SMEM));
-    cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3((unsigned)(tiles * c)); cfg.blockDim = dim3(TP_THREADS); cfg.dynamicSmemBytes = TP_SMEM; cfg.stream = st;
-    cudaLaunchAttribute at[1];
-    at[0].id = cudaLaunchAttributeClusterDimension;
-    at[0].val.clusterDim.x = (unsigned)c; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
-    cfg.attrs = at; cfg.numAttrs = 1;
+    cudaLaunchConfig_t cfg; cudaLaunchAttribute at[1];
+    config(cfg, at, c);
     SK_CUDA(cudaLaunchKernelEx(&cfg, kern, tmW0, tmW1, tmWo, tmX0, tmX1, tmXo, a));
     return 0;
   };
